@@ -1,0 +1,470 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a.
+//
+//   C[M,N] (+)= op(A)[M,K] * op(B)[K,N]      bf16 or fp16 operands, fp32 accumulate in TMEM
+//
+// One persistent, warp-specialised kernel (1 CTA per SM):
+//   warp 0    : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx-count)
+//   warp 1    : MMA issuer    (one thread issues tcgen05.mma kind::f16 128xBNx16, commits to mbarriers)
+//   warp 2    : TMEM allocator
+//   warps 4-7 : epilogue      (tcgen05.ld 32x32b -> fused epilogue -> swizzled smem -> TMA store /
+//                              TMA reduce-add); overlapped with the next tile's mainloop through a
+//                              double-buffered TMEM accumulator.
+// Operand majors are expressed purely through the UMMA descriptors, so forward (x W^T), dgrad
+// (dy W) and wgrad (dy^T x) all read the tensors in place - no transposes are materialised.
+//
+// Replaces the cuBLAS calls under torch.matmul / F.linear on every path of the reference
+//  and apex's fused_weight_gradient_mlp_cuda (wgrad accumulate into
+// fp32 main_grad, here as split-K TMA reduce-add).
+#include "common.cuh"
+#include "b200dist.h"
+
+using namespace b2;
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;          // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 256;
+constexpr int EPI_THREADS = 128;
+constexpr int EPI_WARP0 = 4;
+constexpr int STAGE_CHUNK_BYTES = 128 * 128;  // 128 rows x 128 B staging tile
+constexpr int SMEM_MAIN_BYTES = 192 * 1024;
+
+struct GemmParams {
+  int M, N, K;
+  int tiles_m, tiles_n, split_k, kb_per_split, num_kb;
+  int epilogue;
+  int fmt;          // 0 fp16, 1 bf16
+  int out_fp32;
+  int reduce_add;   // fp32 output accumulated with TMA reduce-add
+  const void* bias;     // [N] (operand dtype)
+  const void* aux;      // [M, ld_aux] (operand dtype): residual or pre-activation
+  long long ld_aux;
+  float alpha;
+};
+
+B2_DEVICE float gelu_tanh(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * x * (1.f + k1 * x * x);
+  float t = 1.f - 2.f / (1.f + __expf(2.f * u));  // tanh(u)
+  return 0.5f * x * (1.f + t);
+}
+B2_DEVICE float gelu_tanh_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * x * (1.f + k1 * x * x);
+  float t = 1.f - 2.f / (1.f + __expf(2.f * u));
+  float du = k0 * (1.f + 3.f * k1 * x * x);
+  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+}
+B2_DEVICE uint32_t pack2(float lo, float hi, int fmt) {
+  if (fmt == 1) return pack_bf16x2(lo, hi);
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+B2_DEVICE float2 unpack2(uint32_t u, int fmt) {
+  if (fmt == 1) return unpack_bf16x2(u);
+  __half2 h = *reinterpret_cast<__half2*>(&u);
+  return __half22float2(h);
+}
+
+B2_DEVICE void decode_tile(const GemmParams& p, int t, int& tm, int& tn, int& ks) {
+  // grouped rasterisation: 8 M-tiles share each sweep over N so A and B tiles are re-used from L2
+  int mn_tiles = p.tiles_m * p.tiles_n;
+  ks = t / mn_tiles;
+  int r = t - ks * mn_tiles;
+  const int G = 8;
+  int group_sz = G * p.tiles_n;
+  int g = r / group_sz;
+  int first_m = g * G;
+  int gm = min(p.tiles_m - first_m, G);
+  int in_g = r - g * group_sz;
+  tm = first_m + in_g % gm;
+  tn = in_g / gm;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
+                    const GemmParams p) {
+  constexpr int A_BYTES = BM * BK * 2;
+  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr int STAGES = SMEM_MAIN_BYTES / STAGE_BYTES;
+  constexpr uint32_t TMEM_COLS = 512;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* stage_base = smem;
+  uint8_t* epi_buf = smem + STAGES * STAGE_BYTES;  // 2 x 16 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 2 * STAGE_CHUNK_BYTES);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + STAGES;
+  uint64_t* tmem_full = bars + 2 * STAGES;
+  uint64_t* tmem_empty = bars + 2 * STAGES + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    if (p.epilogue == B2_EPI_BIAS_GELU_DUAL) tma_prefetch_desc(&tmC2);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], 1);
+      mbar_init(&tmem_empty[i], EPI_THREADS);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total_tiles = p.tiles_m * p.tiles_n * p.split_k;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        int tm, tn, ks;
+        decode_tile(p, t, tm, tn, ks);
+        const int m0 = tm * BM, n0 = tn * BN;
+        const int kb0 = ks * p.kb_per_split;
+        const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sA = stage_base + stage * STAGE_BYTES;
+          uint8_t* sB = sA + A_BYTES;
+          mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
+          if constexpr (!A_MN) {
+            tma_load_2d(sA, &tmA, &full_bar[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sA + j * (BK * 128), &tmA, &full_bar[stage], m0 + j * 64, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(sB, &tmB, &full_bar[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sB + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * BK);
+          }
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = make_idesc_f16(BM, BN, p.fmt, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    int stage = 0;
+    uint32_t phase = 0;
+    int it = 0;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      int tm, tn, ks;
+      decode_tile(p, t, tm, tn, ks);
+      const int kb0 = ks * p.kb_per_split;
+      const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+      const int buf = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_empty[buf], acc_phase ^ 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + buf * BN;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t sA = smem_u32(stage_base + stage * STAGE_BYTES);
+          const uint32_t sB = sA + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            uint64_t adesc, bdesc;
+            if constexpr (!A_MN) adesc = make_smem_desc(sA + k * 32, 16, 1024);
+            else                 adesc = make_smem_desc(sA + k * 2048, BK * 128, 1024);
+            if constexpr (!B_MN) bdesc = make_smem_desc(sB + k * 32, 16, 1024);
+            else                 bdesc = make_smem_desc(sB + k * 2048, BK * 128, 1024);
+            umma_f16_ss(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);
+          if (kb == kb1 - 1) umma_commit(&tmem_full[buf]);
+        }
+        __syncwarp();
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= EPI_WARP0) {
+    // ===================== epilogue =====================
+    const int et = threadIdx.x - EPI_WARP0 * 32;   // 0..127 == accumulator row
+    const int ew = warp - EPI_WARP0;               // TMEM lane quarter
+    const bool leader = (et == 0);
+    const int fmt = p.fmt;
+    int it = 0;
+    int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+      int tm, tn, ks;
+      decode_tile(p, t, tm, tn, ks);
+      const int m0 = tm * BM, n0 = tn * BN;
+      const int buf = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1;
+      mbar_wait(&tmem_full[buf], acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + buf * BN + (static_cast<uint32_t>(ew * 32) << 16);
+      const int row = m0 + et;
+      const bool row_ok = row < p.M;
+
+      if (p.out_fp32) {
+        // 32-column chunks of fp32 (128 B rows)
+        constexpr int NCH = BN / 32;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (c == NCH - 1) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          if (n0 + c * 32 >= p.N) continue;   // uniform across the CTA
+          uint8_t* sb = epi_buf + (sctr & 1) * STAGE_CHUNK_BYTES;
+          ++sctr;
+          if (leader) tma_store_wait_read<1>();
+          named_bar_sync(1, EPI_THREADS);
+          if (p.alpha != 1.f) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * p.alpha);
+          }
+          uint8_t* rowp = sb + et * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint4 q = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            *reinterpret_cast<uint4*>(rowp + ((j ^ (et & 7)) << 4)) = q;
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, EPI_THREADS);
+          if (leader) {
+            if (p.reduce_add) tma_reduce_add_2d(&tmC, sb, n0 + c * 32, m0);
+            else              tma_store_2d(&tmC, sb, n0 + c * 32, m0);
+            tma_store_commit();
+          }
+        }
+      } else {
+        constexpr int NCH = BN / 64;
+        const bool dual = (p.epilogue == B2_EPI_BIAS_GELU_DUAL);
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          uint32_t v[64];
+          tmem_ld_32x32b_x32(taddr + c * 64, v);
+          tmem_ld_32x32b_x32(taddr + c * 64 + 32, v + 32);
+          tmem_ld_wait();
+          if (c == NCH - 1) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          const int col0 = n0 + c * 64;
+          if (col0 >= p.N) continue;          // uniform across the CTA
+          float* f = reinterpret_cast<float*>(v);
+          if (p.alpha != 1.f) {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) f[i] *= p.alpha;
+          }
+          // ---- bias ----
+          if (p.bias != nullptr) {
+            const uint4* bp = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.bias) + col0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              if (col0 + j * 8 < p.N) {
+                uint4 q = __ldg(bp + j);
+                float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+                f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
+                f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
+              }
+            }
+          }
+          uint8_t* sb0 = epi_buf + (dual ? 0 : (sctr & 1)) * STAGE_CHUNK_BYTES;
+          ++sctr;
+          uint8_t* sb1 = epi_buf + STAGE_CHUNK_BYTES;
+          if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          named_bar_sync(1, EPI_THREADS);
+          if (dual) {
+            // pre-activation z -> C2, gelu(z) -> C
+            uint8_t* rowp = sb1 + et * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              uint4 q = make_uint4(pack2(f[8 * j], f[8 * j + 1], fmt), pack2(f[8 * j + 2], f[8 * j + 3], fmt),
+                                   pack2(f[8 * j + 4], f[8 * j + 5], fmt), pack2(f[8 * j + 6], f[8 * j + 7], fmt));
+              *reinterpret_cast<uint4*>(rowp + ((j ^ (et & 7)) << 4)) = q;
+            }
+#pragma unroll
+            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
+          } else if (p.epilogue == B2_EPI_BIAS_GELU) {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
+          } else if (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU) {
+            const bool is_res = (p.epilogue == B2_EPI_BIAS_RESIDUAL);
+            if (row_ok) {
+              const uint4* ap = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.aux) +
+                                                               static_cast<long long>(row) * p.ld_aux + col0);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) {
+                if (col0 + j * 8 < p.N) {
+                  uint4 q = __ldg(ap + j);
+                  float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+                  float z[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, d.x, d.y};
+#pragma unroll
+                  for (int e = 0; e < 8; ++e) {
+                    if (is_res) f[8 * j + e] += z[e];
+                    else        f[8 * j + e] *= gelu_tanh_grad(z[e]);
+                  }
+                }
+              }
+            }
+          }
+          {
+            uint8_t* rowp = sb0 + et * 128;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              uint4 q = make_uint4(pack2(f[8 * j], f[8 * j + 1], fmt), pack2(f[8 * j + 2], f[8 * j + 3], fmt),
+                                   pack2(f[8 * j + 4], f[8 * j + 5], fmt), pack2(f[8 * j + 6], f[8 * j + 7], fmt));
+              *reinterpret_cast<uint4*>(rowp + ((j ^ (et & 7)) << 4)) = q;
+            }
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, EPI_THREADS);
+          if (leader) {
+            tma_store_2d(&tmC, sb0, col0, m0);
+            if (dual) tma_store_2d(&tmC2, sb1, col0, m0);
+            tma_store_commit();
+          }
+        }
+      }
+    }
+    if (leader) tma_store_wait_all<0>();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
+           const GemmParams& p, int max_ctas, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { b2host::set_error("gemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+    configured = true;
+  }
+  int total = p.tiles_m * p.tiles_n * p.split_k;
+  int grid = total < max_ctas ? total : max_ctas;
+  kern<<<grid, NUM_THREADS, smem, stream>>>(tA, tB, tC, tC2, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { b2host::set_error("gemm launch: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                       long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
+                       const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
+                       int split_k, float alpha, int max_ctas, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (M <= 0 || N <= 0 || K <= 0) { b2host::set_error("gemm: empty problem"); return -1; }
+  if ((lda % 8) || (ldb % 8) || (out_fp32 ? (ldc % 4) : (ldc % 8)) || (N % 8)) {
+    b2host::set_error("gemm: leading dimensions / N must keep 16-byte alignment (lda=%lld ldb=%lld ldc=%lld N=%d)", lda,
+                      ldb, ldc, N);
+    return -1;
+  }
+  if (out_fp32 && epilogue != B2_EPI_NONE) { b2host::set_error("gemm: fp32 output supports no fused epilogue"); return -1; }
+  if (accumulate && !out_fp32) { b2host::set_error("gemm: accumulate requires fp32 output"); return -1; }
+  if (split_k > 1 && !(out_fp32 && accumulate)) { b2host::set_error("gemm: split-K requires fp32 accumulate output"); return -1; }
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+
+  // Tile-N selection: prefer 256 wide tiles unless that leaves most SMs idle.
+  const int sms = max_ctas > 0 ? max_ctas : b2host::num_sms();
+  const int tiles_m = (M + BM - 1) / BM;
+  int bn = 256;
+  {
+    long long t256 = 1LL * tiles_m * ((N + 255) / 256);
+    long long t128 = 1LL * tiles_m * ((N + 127) / 128);
+    if (N <= 128 || (t256 * (split_k > 0 ? split_k : 1) < sms && t128 > t256)) bn = 128;
+  }
+  const int tiles_n = (N + bn - 1) / bn;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (split_k <= 0) {  // auto: only meaningful for fp32 accumulate outputs
+    split_k = 1;
+    if (out_fp32 && accumulate) {
+      int tiles = tiles_m * tiles_n;
+      while (tiles * split_k * 2 <= sms && num_kb / (split_k * 2) >= 4) split_k *= 2;
+      if (tiles * split_k < sms && num_kb / (split_k + 1) >= 4) {
+        int want = (sms + tiles - 1) / tiles;
+        if (num_kb / want >= 4) split_k = want;
+      }
+    }
+  }
+  GemmParams p;
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = tiles_m; p.tiles_n = tiles_n;
+  p.num_kb = num_kb;
+  p.kb_per_split = (num_kb + split_k - 1) / split_k;
+  p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0;
+  p.out_fp32 = out_fp32; p.reduce_add = accumulate;
+  p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = alpha;
+  if ((epilogue == B2_EPI_BIAS_RESIDUAL || epilogue == B2_EPI_DGELU) && (aux == nullptr || (ld_aux % 8))) {
+    b2host::set_error("gemm: epilogue needs a 16-byte aligned aux tensor"); return -1;
+  }
+  if (epilogue == B2_EPI_BIAS_GELU_DUAL && (C2 == nullptr || (ldc2 % 8))) {
+    b2host::set_error("gemm: dual-output epilogue needs C2"); return -1;
+  }
+
+  CUtensorMap tA, tB, tC, tC2;
+  {
+    uint64_t dims[2], strides[2]; uint32_t box[2];
+    if (!a_mn_major) { dims[0] = K; dims[1] = M; box[0] = BK; box[1] = BM; }
+    else             { dims[0] = M; dims[1] = K; box[0] = 64; box[1] = BK; }
+    strides[0] = 0; strides[1] = static_cast<uint64_t>(lda) * 2;
+    if (b2host::encode_tmap(&tA, dt, 2, A, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+    if (!b_mn_major) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = bn; }
+    else             { dims[0] = N; dims[1] = K; box[0] = 64; box[1] = BK; }
+    strides[1] = static_cast<uint64_t>(ldb) * 2;
+    if (b2host::encode_tmap(&tB, dt, 2, B, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+    dims[0] = N; dims[1] = M;
+    if (out_fp32) {
+      box[0] = 32; box[1] = BM; strides[1] = static_cast<uint64_t>(ldc) * 4;
+      if (b2host::encode_tmap(&tC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, C, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+      tC2 = tC;
+    } else {
+      box[0] = 64; box[1] = BM; strides[1] = static_cast<uint64_t>(ldc) * 2;
+      if (b2host::encode_tmap(&tC, dt, 2, C, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+      if (epilogue == B2_EPI_BIAS_GELU_DUAL) {
+        strides[1] = static_cast<uint64_t>(ldc2) * 2;
+        if (b2host::encode_tmap(&tC2, dt, 2, C2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+      } else {
+        tC2 = tC;
+      }
+    }
+  }
+  const int mc = sms;
+#define B2_DISPATCH(BN_)                                                                         \
+  do {                                                                                           \
+    if (!a_mn_major && !b_mn_major) return launch<BN_, false, false>(tA, tB, tC, tC2, p, mc, stream); \
+    if (!a_mn_major && b_mn_major) return launch<BN_, false, true>(tA, tB, tC, tC2, p, mc, stream);   \
+    if (a_mn_major && b_mn_major) return launch<BN_, true, true>(tA, tB, tC, tC2, p, mc, stream);     \
+    return launch<BN_, true, false>(tA, tB, tC, tC2, p, mc, stream);                                  \
+  } while (0)
+  if (bn == 256) B2_DISPATCH(256);
+  B2_DISPATCH(128);
+#undef B2_DISPATCH
+}

@@ -1,0 +1,292 @@
+// LayerNorm / RMSNorm forward and backward (sm_100a, memory-bound: 128-bit loads, one warp per row,
+// row held in registers, fp32 math, bf16/fp16 I/O).
+//
+// replaces: apex fused_layer_norm_cuda (used by Megatron MixedFusedLayerNorm), ATen
+// layer_norm under swin_b / OPT (K6, K24) and the unfused HF LlamaRMSNorm (K24).
+//
+// Backward produces dx in one pass and accumulates dgamma/dbeta partials per CTA into a small fp32
+// workspace [ctas, 2, H] that a second kernel folds (optionally accumulating into fp32 main_grad).
+#include "common.cuh"
+#include "b200dist.h"
+
+using namespace b2;
+
+namespace {
+
+template <typename T> struct Cvt;
+template <> struct Cvt<__nv_bfloat16> {
+  static B2_DEVICE float2 up(uint32_t u) { return unpack_bf16x2(u); }
+  static B2_DEVICE uint32_t down(float a, float b) { return pack_bf16x2(a, b); }
+};
+template <> struct Cvt<__half> {
+  static B2_DEVICE float2 up(uint32_t u) { __half2 h = *reinterpret_cast<__half2*>(&u); return __half22float2(h); }
+  static B2_DEVICE uint32_t down(float a, float b) { __half2 h = __floats2half2_rn(a, b); return *reinterpret_cast<uint32_t*>(&h); }
+};
+
+template <typename T>
+B2_DEVICE void load8(const T* p, float* f) {
+  uint4 q = *reinterpret_cast<const uint4*>(p);
+  float2 a = Cvt<T>::up(q.x), b = Cvt<T>::up(q.y), c = Cvt<T>::up(q.z), d = Cvt<T>::up(q.w);
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+template <typename T>
+B2_DEVICE void store8(T* p, const float* f) {
+  uint4 q = make_uint4(Cvt<T>::down(f[0], f[1]), Cvt<T>::down(f[2], f[3]), Cvt<T>::down(f[4], f[5]),
+                       Cvt<T>::down(f[6], f[7]));
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
+constexpr int CTA_THREADS = 128;
+constexpr int MAXV = 4;   // 8-element vectors per thread: TEAM * MAXV * 8 >= H
+
+// TEAM threads cooperate on one row: TEAM == 32 (one warp per row, 4 rows per CTA, H <= 1024)
+// or TEAM == CTA_THREADS' big sibling 256 (whole CTA per row, H <= 8192).
+template <int TEAM>
+B2_DEVICE float team_sum(float v, float* red) {
+  v = warp_sum(v);
+  if constexpr (TEAM > 32) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < TEAM / 32; ++w) t += red[w];
+    v = t;
+  }
+  return v;
+}
+
+template <typename T, int TEAM, bool RMS>
+__global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM)
+norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* __restrict__ beta, T* __restrict__ y,
+                float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int H, float eps) {
+  __shared__ float red[8];
+  constexpr int ROWS_PER_CTA = TEAM == 32 ? CTA_THREADS / 32 : 1;
+  const int tid = TEAM == 32 ? (threadIdx.x & 31) : threadIdx.x;
+  const int sub = TEAM == 32 ? (threadIdx.x >> 5) : 0;
+  const int nvec = H >> 3;
+  for (int row = blockIdx.x * ROWS_PER_CTA + sub; row < rows; row += gridDim.x * ROWS_PER_CTA) {
+    const T* xr = x + static_cast<size_t>(row) * H;
+    float v[MAXV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+        load8<T>(xr + vi * 8, v[i]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) s += v[i][e];
+      }
+    }
+    float mean = 0.f;
+    if (!RMS) { s = team_sum<TEAM>(s, red); mean = s / H; }
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { float d = v[i][e] - mean; ss += d * d; }
+      }
+    }
+    ss = team_sum<TEAM>(ss, red);
+    const float rstd = rsqrtf(ss / H + eps);
+    if (tid == 0) {
+      if (!RMS && mean_out) mean_out[row] = mean;
+      if (rstd_out) rstd_out[row] = rstd;
+    }
+    T* yr = y + static_cast<size_t>(row) * H;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+        float g[8], b[8], o[8];
+        load8<T>(gamma + vi * 8, g);
+        if (!RMS && beta) load8<T>(beta + vi * 8, b);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float xh = (v[i][e] - mean) * rstd;
+          o[e] = xh * g[e] + ((!RMS && beta) ? b[e] : 0.f);
+        }
+        store8<T>(yr + vi * 8, o);
+      }
+    }
+  }
+}
+
+template <typename T, int TEAM, bool RMS>
+__global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM)
+norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ gamma,
+                const float* __restrict__ mean_in, const float* __restrict__ rstd_in, T* __restrict__ dx,
+                float* __restrict__ ws /* [gridDim.x, 2, H] */, int rows, int H) {
+  extern __shared__ float sm[];  // TEAM == 32: [CTA_THREADS/32][2][H]
+  __shared__ float red[8];
+  constexpr int ROWS_PER_CTA = TEAM == 32 ? CTA_THREADS / 32 : 1;
+  const int tid = TEAM == 32 ? (threadIdx.x & 31) : threadIdx.x;
+  const int sub = TEAM == 32 ? (threadIdx.x >> 5) : 0;
+  const int nvec = H >> 3;
+  float dg[MAXV][8], db[MAXV][8];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { dg[i][e] = 0.f; db[i][e] = 0.f; }
+
+  // TEAM > 32 uses __syncthreads inside team_sum, so every thread must run the same trip count
+  const int first = blockIdx.x * ROWS_PER_CTA + sub;
+  for (int row = first; row < rows; row += gridDim.x * ROWS_PER_CTA) {
+    const T* xr = x + static_cast<size_t>(row) * H;
+    const T* dyr = dy + static_cast<size_t>(row) * H;
+    const float mean = RMS ? 0.f : mean_in[row];
+    const float rstd = rstd_in[row];
+    float xh[MAXV][8], gy[MAXV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+        float xv[8], dv[8], g[8];
+        load8<T>(xr + vi * 8, xv);
+        load8<T>(dyr + vi * 8, dv);
+        load8<T>(gamma + vi * 8, g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          float h = (xv[e] - mean) * rstd;
+          float t = dv[e] * g[e];
+          xh[i][e] = h; gy[i][e] = t;
+          s1 += t; s2 += t * h;
+          dg[i][e] += dv[e] * h;
+          db[i][e] += dv[e];
+        }
+      }
+    }
+    s1 = team_sum<TEAM>(s1, red); s2 = team_sum<TEAM>(s2, red);
+    const float m1 = RMS ? 0.f : s1 / H, m2 = s2 / H;
+    T* dxr = dx + static_cast<size_t>(row) * H;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+        float o[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] = rstd * (gy[i][e] - m1 - xh[i][e] * m2);
+        store8<T>(dxr + vi * 8, o);
+      }
+    }
+  }
+  float* wrow = ws + static_cast<size_t>(blockIdx.x) * 2 * H;
+  if constexpr (TEAM == 32) {
+    // fold the per-warp partials through smem, one workspace row per CTA
+    float* mine = sm + sub * 2 * H;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { mine[vi * 8 + e] = dg[i][e]; mine[H + vi * 8 + e] = db[i][e]; }
+      }
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < 2 * H; j += blockDim.x) {
+      float a = 0.f;
+#pragma unroll
+      for (int w = 0; w < ROWS_PER_CTA; ++w) a += sm[w * 2 * H + j];
+      wrow[j] = a;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { wrow[vi * 8 + e] = dg[i][e]; wrow[H + vi * 8 + e] = db[i][e]; }
+      }
+    }
+  }
+}
+
+// fold workspace rows -> dgamma / dbeta (fp32, optionally accumulated: main_grad semantics)
+__global__ void norm_bwd_fold_kernel(const float* __restrict__ ws, int nparts, int H, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta, int accumulate) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= 2 * H) return;
+  float a = 0.f;
+  for (int p = 0; p < nparts; ++p) a += ws[static_cast<size_t>(p) * 2 * H + j];
+  float* dst = j < H ? (dgamma + j) : (dbeta ? dbeta + (j - H) : nullptr);
+  if (!dst) return;
+  if (accumulate) *dst += a; else *dst = a;
+}
+
+template <typename T, bool RMS>
+int fwd_dispatch(const void* x, const void* g, const void* b, void* y, float* mean, float* rstd, int rows, int H,
+                 float eps, cudaStream_t st) {
+  if (H <= 1024) {
+    int grid = (rows + 3) / 4;
+    int cap = b2host::num_sms() * 16;
+    if (grid > cap) grid = cap;
+    norm_fwd_kernel<T, 32, RMS><<<grid, CTA_THREADS, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps);
+  } else if (H <= 8192) {
+    int grid = rows;
+    int cap = b2host::num_sms() * 8;
+    if (grid > cap) grid = cap;
+    norm_fwd_kernel<T, 256, RMS><<<grid, 256, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps);
+  } else { b2host::set_error("norm: hidden size %d > 8192 unsupported", H); return -1; }
+  return 0;
+}
+
+int bwd_parts(int rows, int H) {
+  int grid = H <= 1024 ? (rows + 3) / 4 : rows;
+  int cap = b2host::num_sms() * 2;
+  return grid < cap ? grid : cap;
+}
+
+template <typename T, bool RMS>
+int bwd_dispatch(const void* dy, const void* x, const void* g, const float* mean, const float* rstd, void* dx,
+                 float* ws, int grid, int rows, int H, cudaStream_t st) {
+  if (H <= 1024) {
+    size_t smem = static_cast<size_t>(CTA_THREADS / 32) * 2 * H * sizeof(float);
+    norm_bwd_kernel<T, 32, RMS><<<grid, CTA_THREADS, smem, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (T*)dx, ws, rows, H);
+  } else if (H <= 8192) {
+    norm_bwd_kernel<T, 256, RMS><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (T*)dx, ws, rows, H);
+  } else { b2host::set_error("norm bwd: hidden size %d > 8192 unsupported", H); return -1; }
+  return 0;
+}
+
+int check(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2_norm_bwd_num_parts(int rows, int H) { return bwd_parts(rows, H); }
+
+extern "C" int b2_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                                int rows, int H, float eps, int dtype, int rms, void* stream) {
+  if (H % 8) { b2host::set_error("norm: hidden size must be a multiple of 8"); return -1; }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int r;
+  if (dtype == B2_DTYPE_BF16) r = rms ? fwd_dispatch<__nv_bfloat16, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, st)
+                                      : fwd_dispatch<__nv_bfloat16, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, st);
+  else r = rms ? fwd_dispatch<__half, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, st)
+               : fwd_dispatch<__half, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, st);
+  return r ? r : check("layernorm_fwd");
+}
+
+// ws: fp32 workspace of b2_norm_bwd_num_parts(rows, H) * 2 * H elements
+extern "C" int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                                void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype, int rms,
+                                int accumulate, void* stream) {
+  if (H % 8) { b2host::set_error("norm: hidden size must be a multiple of 8"); return -1; }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int grid = bwd_parts(rows, H);
+  int r;
+  if (dtype == B2_DTYPE_BF16) r = rms ? bwd_dispatch<__nv_bfloat16, true>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st)
+                                      : bwd_dispatch<__nv_bfloat16, false>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st);
+  else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st)
+               : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st);
+  if (r) return r;
+  norm_bwd_fold_kernel<<<(2 * H + 255) / 256, 256, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
+  return check("layernorm_bwd");
+}

@@ -1,0 +1,144 @@
+/* b200dist native library - C ABI.
+ *
+ * Every entry point takes raw device pointers plus the CUDA stream to launch on (a cudaStream_t
+ * passed as void*), launches asynchronously, and returns 0 on success or -1 on error (call
+ * b2_last_error() for the message).  Nothing here allocates device memory unless it says so.
+ * Python reaches these through ctypes (ops/_native.py); C/C++ callers can link libb200dist.so.
+ *
+ * The "replaces" notes cite the reference components of SURVEY.md section 2 that each kernel
+ * stands in for (the reference tree itself contains no native code; these are the external
+ * libraries its four entry scripts drive).
+ */
+#ifndef B200DIST_H_
+#define B200DIST_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2_DTYPE_FP16 0
+#define B2_DTYPE_BF16 1
+#define B2_DTYPE_FP32 2
+
+/* GEMM epilogues */
+#define B2_EPI_NONE 0
+#define B2_EPI_BIAS 1            /* C = acc + bias[n]                                   */
+#define B2_EPI_BIAS_GELU 2       /* C = gelu_tanh(acc + bias[n])                        */
+#define B2_EPI_BIAS_GELU_DUAL 3  /* C2 = acc + bias[n];  C = gelu_tanh(C2)              */
+#define B2_EPI_BIAS_RESIDUAL 4   /* C = aux[m,n] + acc + bias[n]                        */
+#define B2_EPI_DGELU 5           /* C = acc * gelu_tanh'(aux[m,n])                      */
+
+const char* b2_last_error(void);
+int b2_num_sms(void);
+
+/* ------------------------------------------------------------------------------------------
+ * GEMM (tcgen05 + TMEM + TMA).  C[M,N] (+)= alpha * op(A)[M,K] . op(B)[K,N]
+ *   a_mn_major = 0: A stored [M,K] row-major (lda elements between rows); 1: A stored [K,M].
+ *   b_mn_major = 0: B stored [N,K] row-major (an nn.Linear weight);       1: B stored [K,N].
+ *   out_fp32/accumulate: fp32 C, optionally C += (TMA reduce-add; split-K allowed, 0 = auto).
+ *   max_ctas: 0 = all SMs; smaller values leave SMs free for a concurrent communication kernel.
+ * replaces: cuBLAS under torch.matmul/F.linear; apex
+ *           fused_weight_gradient_mlp_cuda.wgrad_gemm_accum_fp32 (K18); NVFuser bias-GeLU /
+ *           bias-dropout-add epilogues (K16, K17).
+ */
+int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+            long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
+            const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
+            int split_k, float alpha, int max_ctas, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].
+ * Backward needs an fp32 workspace of b2_norm_bwd_num_parts(rows,H) * 2 * H floats (every element is
+ * written before it is read); dgamma/dbeta are fp32 and are accumulated when accumulate != 0.
+ * replaces: apex fused_layer_norm_cuda, ATen layer_norm (K6), HF LlamaRMSNorm (K24).
+ */
+int b2_norm_bwd_num_parts(int rows, int H);
+int b2_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                     int rows, int H, float eps, int dtype, int rms, void* stream);
+int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                     void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype, int rms,
+                     int accumulate, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Fused elementwise ops.  replaces: Megatron jit bias_gelu / bias_dropout_add (K16, K17), HF SwiGLU
+ * and RoPE (K24), autograd's bias-gradient reductions.
+ * act modes: 0 tanh-GeLU, 1 erf-GeLU, 2 ReLU, 3 SiLU.
+ */
+int b2_bias_dropout_add(const void* x, const void* bias, const void* residual, void* out, long long n, int H,
+                        float p, unsigned long long seed, int dtype, void* stream);
+int b2_dropout_bwd(const void* dy, void* dx, long long n, float p, unsigned long long seed, int dtype, void* stream);
+int b2_bias_act_fwd(const void* x, const void* bias, void* out, long long n, int H, int mode, int dtype, void* stream);
+int b2_bias_act_bwd(const void* dy, const void* x, const void* bias, void* dx, long long n, int H, int mode, int dtype, void* stream);
+int b2_swiglu_fwd(const void* gate_up, void* out, long long rows, int F, int dtype, void* stream);
+int b2_swiglu_bwd(const void* dy, const void* gate_up, void* d_gate_up, long long rows, int F, int dtype, void* stream);
+int b2_colsum(const void* dy, float* out_accum, int rows, int N, long long ld, int dtype, void* stream);
+int b2_rope(void* x, const float* cos_t, const float* sin_t, const int* pos, long long tokens, int nheads, int hd,
+            long long tok_stride, int head_stride, int backward, int dtype, void* stream);
+int b2_axpby(const void* a, const void* b, void* out, long long n, float alpha, float beta, int dtype, void* stream);
+int b2_accum_fp32(float* dst, const void* src, long long n, int dtype, void* stream);
+int b2_cast_from_fp32(void* dst, const float* src, long long n, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Softmax cross-entropy on (vocab-sharded) logits - see csrc/xent.cu for the 4-step protocol.
+ * replaces: Megatron _VocabParallelCrossEntropy (E12/K20/C13), ATen CrossEntropyLoss (K9).
+ */
+int b2_xent_stats(const void* logits, const long long* labels, float* rmax, float* rsum, float* rtgt,
+                  long long rows, int V, long long ld, long long vocab_start, int dtype, void* stream);
+int b2_xent_finish(const float* rmax, const float* rsum, const float* rtgt, const long long* labels, float* loss,
+                   long long rows, long long ignore_index, void* stream);
+int b2_xent_bwd(const void* logits, void* dlogits, const long long* labels, const float* gmax, const float* gsum,
+                const float* row_scale, float scalar_scale, long long rows, int V, long long ld,
+                long long vocab_start, long long ignore_index, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Optimizers over flat fp32 arenas.  sumsq / found_inf are DEVICE pointers (may be NULL): the clip
+ * coefficient min(1, max_norm / (sqrt(*sumsq) + 1e-6)) and the overflow skip are evaluated on the GPU.
+ * replaces: apex amp_C multi_tensor_{adam,l2norm,scale} (E25/K21/K22), DeepSpeed FusedAdam (E30/K25),
+ *           ATen Adam / Adadelta (K10, K3).
+ */
+int b2_adam(float* p, float* m, float* v, const void* g, void* p_lp, long long n, float lr, float beta1, float beta2,
+            float eps, float wd, int step, int adamw, float grad_scale, const float* sumsq, float max_norm,
+            const float* found_inf, int grad_dtype, int lp_dtype, void* stream);
+int b2_adadelta(float* p, float* sq, float* acc, const float* g, long long n, float lr, float rho, float eps, float wd,
+                void* stream);
+int b2_sgd(float* p, float* mom, const float* g, long long n, float lr, float momentum, float wd, float grad_scale,
+           int first_step, void* stream);
+/* sum of squares: scratch >= b2_sumsq_scratch_floats() floats, counter = one uint32 that is 0 on entry
+ * (the kernel leaves it 0 again).  out[0] = (or +=) sum x^2. */
+int b2_sumsq_scratch_floats(void);
+int b2_sumsq(const void* x, long long n, float* scratch, unsigned int* counter, float* out, int accumulate, int dtype,
+             void* stream);
+int b2_scale_check(float* x, long long n, float scale, float* found_inf, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Embedding (vocab-parallel aware).  replaces: Megatron VocabParallelEmbedding (E10/K11), nn.Embedding.
+ */
+int b2_embedding_fwd(const long long* tok, const long long* pos, const void* wte, const void* wpe, void* out,
+                     long long tokens, int H, long long vocab_start, long long vocab_local, int dtype, void* stream);
+int b2_embedding_bwd(const void* dy, const long long* tok, const long long* pos, float* dwte, float* dwpe,
+                     long long tokens, int H, long long vocab_start, long long vocab_local, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Flash attention (tcgen05), bf16, head_dim 64 or 128 forward / 64 backward.  Strides are in
+ * elements for (seq, batch, head); head_dim is contiguous.  lse: fp32 [batch, heads, seqlen].
+ * Backward: delta is fp32 scratch [batch, heads, seqlen]; dq_accum is fp32 [seq, batch, heads, D],
+ * contiguous and ZERO on entry (dQ tiles are TMA reduce-added into it).
+ * replaces: Megatron CoreAttention baddbmm/bmm + scaled_upper_triang_masked_softmax_cuda (E17/E19,
+ *           K14/K15), HF eager attention (K24).
+ */
+int b2_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int seqlen, int batch, int heads,
+                int D, long long q_ss, long long q_sb, long long q_sh, long long k_ss, long long k_sb,
+                long long k_sh, long long v_ss, long long v_sb, long long v_sh, long long o_ss, long long o_sb,
+                long long o_sh, float scale, int causal, void* stream);
+int b2_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
+                float* delta, float* dq_accum, void* dk, void* dv, int seqlen, int batch, int heads, int D,
+                long long q_ss, long long q_sb, long long q_sh, long long k_ss, long long k_sb, long long k_sh,
+                long long v_ss, long long v_sb, long long v_sh, long long o_ss, long long o_sb, long long o_sh,
+                long long do_ss, long long do_sb, long long do_sh, long long dk_ss, long long dk_sb,
+                long long dk_sh, long long dv_ss, long long dv_sb, long long dv_sh, float scale, int causal,
+                void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DIST_H_ */

@@ -1,0 +1,633 @@
+"""Raw (non-autograd) bindings to ``libb200dist.so`` plus plain-PyTorch fp32 reference versions.
+
+Every op here has two bodies:
+
+* CUDA tensors -> the hand-written sm_100a kernel through the C ABI declared in ``include/b200dist.h``
+  (ctypes; pointers + the current CUDA stream).  If the shared library is missing on a GPU machine
+  the op raises - there is no silent eager fallback on the GPU.
+* CPU tensors -> a straightforward fp32 PyTorch restatement of the same math.  This is the oracle
+  the GPU tests compare against, and what the gloo/CPU tiers run.
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+import os
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+_PKG = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_LIB_PATH = os.path.join(_PKG, "lib", "libb200dist.so")
+_lib = None
+_launches = 0  # kernels launched through this module (bench.py reports it)
+
+DT_FP16, DT_BF16, DT_FP32 = 0, 1, 2
+EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU = 0, 1, 2, 3, 4, 5
+ACT_GELU_TANH, ACT_GELU_ERF, ACT_RELU, ACT_SILU = 0, 1, 2, 3
+
+c_p, c_i, c_ll, c_f, c_ull = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_ulonglong
+
+_SIGS = {
+    "b2_gemm": [c_p, c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_ll, c_i, c_i, c_i, c_i, c_p, c_p, c_ll, c_p, c_ll, c_i, c_i, c_i, c_f, c_i, c_p],
+    "b2_norm_bwd_num_parts": [c_i, c_i],
+    "b2_layernorm_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_f, c_i, c_i, c_p],
+    "b2_layernorm_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_bias_dropout_add": [c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_ull, c_i, c_p],
+    "b2_dropout_bwd": [c_p, c_p, c_ll, c_f, c_ull, c_i, c_p],
+    "b2_bias_act_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_p],
+    "b2_bias_act_bwd": [c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_p],
+    "b2_swiglu_fwd": [c_p, c_p, c_ll, c_i, c_i, c_p],
+    "b2_swiglu_bwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_p],
+    "b2_colsum": [c_p, c_p, c_i, c_i, c_ll, c_i, c_p],
+    "b2_rope": [c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_ll, c_i, c_i, c_i, c_p],
+    "b2_axpby": [c_p, c_p, c_p, c_ll, c_f, c_f, c_i, c_p],
+    "b2_accum_fp32": [c_p, c_p, c_ll, c_i, c_p],
+    "b2_cast_from_fp32": [c_p, c_p, c_ll, c_i, c_p],
+    "b2_xent_stats": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
+    "b2_xent_finish": [c_p, c_p, c_p, c_p, c_p, c_ll, c_ll, c_p],
+    "b2_xent_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_ll, c_i, c_ll, c_ll, c_ll, c_i, c_p],
+    "b2_adam": [c_p, c_p, c_p, c_p, c_p, c_ll, c_f, c_f, c_f, c_f, c_f, c_i, c_i, c_f, c_p, c_f, c_p, c_i, c_i, c_p],
+    "b2_adadelta": [c_p, c_p, c_p, c_p, c_ll, c_f, c_f, c_f, c_f, c_p],
+    "b2_sgd": [c_p, c_p, c_p, c_ll, c_f, c_f, c_f, c_f, c_i, c_p],
+    "b2_sumsq_scratch_floats": [],
+    "b2_sumsq": [c_p, c_ll, c_p, c_p, c_p, c_i, c_i, c_p],
+    "b2_scale_check": [c_p, c_ll, c_f, c_p, c_p],
+    "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
+    "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
+    "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_p],
+    "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_p],
+    "b2_num_sms": [],
+}
+
+
+def lib_path() -> str:
+    return _LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_LIB_PATH)
+
+
+def lib():
+    """Load (once) and return the ctypes handle; raises if the library has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise RuntimeError(
+                f"{_LIB_PATH} not found: run `python -m b200dist.build_native` (or __graft_entry__.build()); "
+                "the CUDA path has no eager fallback on purpose")
+        L = ctypes.CDLL(_LIB_PATH)
+        L.b2_last_error.restype = ctypes.c_char_p
+        for name, sig in _SIGS.items():
+            fn = getattr(L, name, None)
+            if fn is None:
+                continue
+            fn.argtypes = sig
+            fn.restype = c_i
+        _lib = L
+    return _lib
+
+
+def launches() -> int:
+    return _launches
+
+
+def _call(name: str, *args) -> None:
+    global _launches
+    L = lib()
+    rc = getattr(L, name)(*args)
+    if rc != 0:
+        raise RuntimeError(f"{name} failed: {L.b2_last_error().decode()}")
+    _launches += 1
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _st():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.bfloat16:
+        return DT_BF16
+    if t.dtype == torch.float16:
+        return DT_FP16
+    if t.dtype == torch.float32:
+        return DT_FP32
+    raise TypeError(f"unsupported dtype {t.dtype}")
+
+
+def num_sms() -> int:
+    return lib().b2_num_sms() if torch.cuda.is_available() else 148
+
+
+# =============================================================================================
+# GEMM
+# =============================================================================================
+def gelu_tanh_ref(x: torch.Tensor) -> torch.Tensor:
+    return F.gelu(x, approximate="tanh")
+
+
+def gelu_tanh_grad_ref(x: torch.Tensor) -> torch.Tensor:
+    k0, k1 = 0.7978845608028654, 0.044715
+    t = torch.tanh(k0 * x * (1 + k1 * x * x))
+    return 0.5 * (1 + t) + 0.5 * x * (1 - t * t) * k0 * (1 + 3 * k1 * x * x)
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, epilogue: int = EPI_NONE, bias: Optional[torch.Tensor] = None,
+         aux: Optional[torch.Tensor] = None, out2: Optional[torch.Tensor] = None, out_fp32: bool = False,
+         accumulate: bool = False, alpha: float = 1.0, split_k: int = 0, max_ctas: int = 0) -> torch.Tensor:
+    """C[M,N] (+)= alpha * op(A) @ op(B).
+
+    a: [M,K] (a_mn=False) or [K,M] (a_mn=True); b: [N,K] (b_mn=False, an nn.Linear weight) or [K,N].
+    Rows may be strided (last dim contiguous).  ``out_fp32``/``accumulate`` give an fp32 result that is
+    added into ``out`` (main_grad semantics).
+    """
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"gemm K mismatch {K} vs {Kb}"
+    if out is None:
+        assert not accumulate
+        out = torch.empty((M, N), dtype=torch.float32 if out_fp32 else a.dtype, device=a.device)
+    if not a.is_cuda:
+        A = a.float().t() if a_mn else a.float()
+        Bm = b.float() if b_mn else b.float().t()
+        c = alpha * (A @ Bm)
+        if bias is not None:
+            c = c + bias.float()
+        if epilogue == EPI_BIAS_GELU:
+            c = gelu_tanh_ref(c)
+        elif epilogue == EPI_BIAS_GELU_DUAL:
+            out2.copy_(c.to(out2.dtype))
+            c = gelu_tanh_ref(c)
+        elif epilogue == EPI_BIAS_RESIDUAL:
+            c = c + aux.float()
+        elif epilogue == EPI_DGELU:
+            c = c * gelu_tanh_grad_ref(aux.float())
+        if accumulate:
+            out.add_(c.to(out.dtype))
+        else:
+            out.copy_(c.to(out.dtype))
+        return out
+    assert out.stride(1) == 1
+    _call("b2_gemm", _p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0), int(a_mn), int(b_mn),
+          _dt(a), epilogue, _p(bias), _p(aux), aux.stride(0) if aux is not None else 0, _p(out2),
+          out2.stride(0) if out2 is not None else 0, int(out.dtype == torch.float32), int(accumulate), split_k,
+          float(alpha), max_ctas, _st())
+    return out
+
+
+# =============================================================================================
+# LayerNorm / RMSNorm
+# =============================================================================================
+def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor], eps: float, rms: bool = False):
+    """Returns (y, mean, rstd); mean is None for RMSNorm."""
+    H = x.shape[-1]
+    x2 = x.reshape(-1, H)
+    rows = x2.shape[0]
+    if not x.is_cuda:
+        xf = x2.float()
+        if rms:
+            mean = None
+            rstd = torch.rsqrt(xf.pow(2).mean(-1) + eps)
+            y = xf * rstd[:, None] * gamma.float()
+        else:
+            mean = xf.mean(-1)
+            rstd = torch.rsqrt(xf.var(-1, unbiased=False) + eps)
+            y = (xf - mean[:, None]) * rstd[:, None] * gamma.float() + (beta.float() if beta is not None else 0)
+        return y.to(x.dtype).view_as(x), mean, rstd
+    assert x2.is_contiguous()
+    y = torch.empty_like(x2)
+    mean = None if rms else torch.empty(rows, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+    _call("b2_layernorm_fwd", _p(x2), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, H, float(eps), _dt(x),
+          int(rms), _st())
+    return y.view_as(x), mean, rstd
+
+
+def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch.Tensor] = None,
+             dbeta: Optional[torch.Tensor] = None, accumulate: bool = False):
+    """Returns (dx, dgamma_fp32, dbeta_fp32).  With ``accumulate`` the fp32 grads are added in place."""
+    H = x.shape[-1]
+    x2, dy2 = x.reshape(-1, H), dy.reshape(-1, H)
+    rows = x2.shape[0]
+    if dgamma is None:
+        dgamma = torch.zeros(H, dtype=torch.float32, device=x.device)
+        accumulate = False
+    if dbeta is None and not rms:
+        dbeta = torch.zeros(H, dtype=torch.float32, device=x.device)
+    if not x.is_cuda:
+        xf, dyf, g = x2.float(), dy2.float(), gamma.float()
+        m = 0 if rms else mean[:, None]
+        xh = (xf - m) * rstd[:, None]
+        gy = dyf * g
+        m1 = 0 if rms else gy.mean(-1, keepdim=True)
+        m2 = (gy * xh).mean(-1, keepdim=True)
+        dx = rstd[:, None] * (gy - m1 - xh * m2)
+        dg = (dyf * xh).sum(0)
+        if accumulate:
+            dgamma.add_(dg)
+        else:
+            dgamma.copy_(dg)
+        if not rms:
+            db = dyf.sum(0)
+            if accumulate:
+                dbeta.add_(db)
+            else:
+                dbeta.copy_(db)
+        return dx.to(x.dtype).view_as(x), dgamma, dbeta
+    assert x2.is_contiguous() and dy2.is_contiguous()
+    dx = torch.empty_like(x2)
+    parts = lib().b2_norm_bwd_num_parts(rows, H)
+    ws = torch.empty(parts * 2 * H, dtype=torch.float32, device=x.device)
+    _call("b2_layernorm_bwd", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dgamma), _p(dbeta), _p(ws),
+          rows, H, _dt(x), int(rms), int(accumulate), _st())
+    return dx.view_as(x), dgamma, dbeta
+
+
+# =============================================================================================
+# elementwise
+# =============================================================================================
+def _philox_keep_ref(n: int, p: float, seed: int) -> torch.Tensor:
+    # CPU oracle uses torch's generator; masks only need to be self-consistent fwd<->bwd per backend
+    g = torch.Generator().manual_seed(seed & 0x7FFFFFFF)
+    return torch.rand(n, generator=g) >= p
+
+
+def bias_dropout_add(x, bias, residual, p: float = 0.0, seed: int = 0):
+    H = x.shape[-1]
+    if not x.is_cuda:
+        t = x.float() + (bias.float() if bias is not None else 0)
+        if p > 0:
+            keep = _philox_keep_ref(t.numel(), p, seed).view_as(t)
+            t = torch.where(keep, t / (1 - p), torch.zeros_like(t))
+        if residual is not None:
+            t = t + residual.float()
+        return t.to(x.dtype)
+    out = torch.empty_like(x)
+    _call("b2_bias_dropout_add", _p(x), _p(bias), _p(residual), _p(out), x.numel(), H, float(p), seed, _dt(x), _st())
+    return out
+
+
+def dropout_bwd(dy, p: float, seed: int):
+    if not dy.is_cuda:
+        keep = _philox_keep_ref(dy.numel(), p, seed).view_as(dy)
+        return torch.where(keep, dy.float() / (1 - p), torch.zeros_like(dy, dtype=torch.float32)).to(dy.dtype)
+    dx = torch.empty_like(dy)
+    _call("b2_dropout_bwd", _p(dy), _p(dx), dy.numel(), float(p), seed, _dt(dy), _st())
+    return dx
+
+
+def _act_ref(z, mode):
+    if mode == ACT_GELU_TANH:
+        return gelu_tanh_ref(z)
+    if mode == ACT_GELU_ERF:
+        return F.gelu(z)
+    if mode == ACT_RELU:
+        return F.relu(z)
+    return F.silu(z)
+
+
+def bias_act_fwd(x, bias, mode: int):
+    if not x.is_cuda:
+        return _act_ref(x.float() + (bias.float() if bias is not None else 0), mode).to(x.dtype)
+    out = torch.empty_like(x)
+    _call("b2_bias_act_fwd", _p(x), _p(bias), _p(out), x.numel(), x.shape[-1], mode, _dt(x), _st())
+    return out
+
+
+def bias_act_bwd(dy, x, bias, mode: int):
+    if not x.is_cuda:
+        z = (x.float() + (bias.float() if bias is not None else 0)).requires_grad_(True)
+        with torch.enable_grad():
+            y = _act_ref(z, mode)
+        (g,) = torch.autograd.grad(y, z, dy.float())
+        return g.to(x.dtype)
+    dx = torch.empty_like(x)
+    _call("b2_bias_act_bwd", _p(dy), _p(x), _p(bias), _p(dx), x.numel(), x.shape[-1], mode, _dt(x), _st())
+    return dx
+
+
+def swiglu_fwd(gu: torch.Tensor) -> torch.Tensor:
+    Fdim = gu.shape[-1] // 2
+    if not gu.is_cuda:
+        g, u = gu.float()[..., :Fdim], gu.float()[..., Fdim:]
+        return (F.silu(g) * u).to(gu.dtype)
+    g2 = gu.reshape(-1, 2 * Fdim)
+    out = torch.empty(g2.shape[0], Fdim, dtype=gu.dtype, device=gu.device)
+    _call("b2_swiglu_fwd", _p(g2), _p(out), g2.shape[0], Fdim, _dt(gu), _st())
+    return out.view(*gu.shape[:-1], Fdim)
+
+
+def swiglu_bwd(dy: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    Fdim = gu.shape[-1] // 2
+    if not gu.is_cuda:
+        g, u, d = gu.float()[..., :Fdim], gu.float()[..., Fdim:], dy.float()
+        s = torch.sigmoid(g)
+        return torch.cat([d * u * s * (1 + g * (1 - s)), d * g * s], -1).to(gu.dtype)
+    g2, d2 = gu.reshape(-1, 2 * Fdim), dy.reshape(-1, Fdim)
+    out = torch.empty_like(g2)
+    _call("b2_swiglu_bwd", _p(d2), _p(g2), _p(out), g2.shape[0], Fdim, _dt(gu), _st())
+    return out.view_as(gu)
+
+
+def colsum_accum(dy2: torch.Tensor, out_fp32: torch.Tensor) -> torch.Tensor:
+    """out_fp32[n] += sum_m dy2[m, n]"""
+    if not dy2.is_cuda:
+        out_fp32.add_(dy2.float().sum(0))
+        return out_fp32
+    _call("b2_colsum", _p(dy2), _p(out_fp32), dy2.shape[0], dy2.shape[1], dy2.stride(0), _dt(dy2), _st())
+    return out_fp32
+
+
+def rope_(x: torch.Tensor, cos_t: torch.Tensor, sin_t: torch.Tensor, pos: torch.Tensor, nheads: int, hd: int,
+          tok_stride: int, head_stride: int, backward: bool = False) -> torch.Tensor:
+    """In-place rotate-half RoPE over ``nheads`` heads of width ``hd`` starting at x's data pointer.
+    x: any tensor whose first element is head 0 / dim 0 of token 0; pos: int32 [tokens]."""
+    tokens = pos.numel()
+    if not x.is_cuda:
+        flat = x.view(-1)
+        half = hd // 2
+        idx_t = torch.arange(tokens)[:, None, None] * tok_stride
+        idx_h = torch.arange(nheads)[None, :, None] * head_stride
+        idx_d = torch.arange(half)[None, None, :]
+        ia = (idx_t + idx_h + idx_d).reshape(-1)
+        ib = ia + half
+        a, b = flat[ia].float(), flat[ib].float()
+        c = cos_t[pos.long()][:, None, :].expand(tokens, nheads, half).reshape(-1)
+        s = sin_t[pos.long()][:, None, :].expand(tokens, nheads, half).reshape(-1) * (-1.0 if backward else 1.0)
+        flat[ia] = (a * c - b * s).to(x.dtype)
+        flat[ib] = (b * c + a * s).to(x.dtype)
+        return x
+    _call("b2_rope", _p(x), _p(cos_t), _p(sin_t), _p(pos), tokens, nheads, hd, tok_stride, head_stride, int(backward),
+          _dt(x), _st())
+    return x
+
+
+def axpby(a, b, alpha: float = 1.0, beta: float = 1.0, out=None):
+    if not a.is_cuda:
+        r = a.float() * alpha + (b.float() * beta if b is not None else 0)
+        if out is None:
+            return r.to(a.dtype)
+        out.copy_(r.to(a.dtype))
+        return out
+    if out is None:
+        out = torch.empty_like(a)
+    _call("b2_axpby", _p(a), _p(b), _p(out), a.numel(), float(alpha), float(beta), _dt(a), _st())
+    return out
+
+
+def accum_fp32_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    if not dst.is_cuda:
+        dst.add_(src.float())
+        return dst
+    _call("b2_accum_fp32", _p(dst), _p(src), dst.numel(), _dt(src), _st())
+    return dst
+
+
+def cast_from_fp32_(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    if not dst.is_cuda:
+        dst.copy_(src.to(dst.dtype))
+        return dst
+    _call("b2_cast_from_fp32", _p(dst), _p(src), dst.numel(), _dt(dst), _st())
+    return dst
+
+
+# =============================================================================================
+# cross entropy
+# =============================================================================================
+def xent_stats(logits2: torch.Tensor, labels: torch.Tensor, vocab_start: int = 0):
+    """Per-row (max, sumexp relative to max, target logit or 0) over this vocab shard."""
+    rows, V = logits2.shape
+    if not logits2.is_cuda:
+        lf = logits2.float()
+        m = lf.max(-1).values
+        s = torch.exp(lf - m[:, None]).sum(-1)
+        lab = labels - vocab_start
+        ok = (lab >= 0) & (lab < V)
+        t = torch.where(ok, lf.gather(1, lab.clamp(0, V - 1)[:, None])[:, 0], torch.zeros_like(m))
+        return m, s, t
+    m = torch.empty(rows, dtype=torch.float32, device=logits2.device)
+    s = torch.empty_like(m)
+    t = torch.empty_like(m)
+    _call("b2_xent_stats", _p(logits2), _p(labels), _p(m), _p(s), _p(t), rows, V, logits2.stride(0), vocab_start,
+          _dt(logits2), _st())
+    return m, s, t
+
+
+def xent_finish(m, s, t, labels, ignore_index: int = -100):
+    if not m.is_cuda:
+        loss = torch.log(s) + m - t
+        return torch.where(labels == ignore_index, torch.zeros_like(loss), loss)
+    loss = torch.empty_like(m)
+    _call("b2_xent_finish", _p(m), _p(s), _p(t), _p(labels), _p(loss), m.numel(), ignore_index, _st())
+    return loss
+
+
+def xent_bwd_(logits2, labels, gmax, gsum, row_scale: Optional[torch.Tensor], scalar_scale: float,
+              vocab_start: int = 0, ignore_index: int = -100):
+    """Overwrites logits2 with dlogits = (softmax - onehot) * row_scale * scalar_scale."""
+    rows, V = logits2.shape
+    if not logits2.is_cuda:
+        p = torch.exp(logits2.float() - gmax[:, None]) / gsum[:, None]
+        lab = labels - vocab_start
+        ok = (lab >= 0) & (lab < V)
+        onehot = torch.zeros_like(p)
+        onehot[ok, lab[ok]] = 1.0
+        sc = torch.where(labels == ignore_index, torch.zeros_like(gmax), torch.ones_like(gmax)) * scalar_scale
+        if row_scale is not None:
+            sc = sc * row_scale
+        logits2.copy_(((p - onehot) * sc[:, None]).to(logits2.dtype))
+        return logits2
+    _call("b2_xent_bwd", _p(logits2), _p(logits2), _p(labels), _p(gmax), _p(gsum), _p(row_scale), float(scalar_scale),
+          rows, V, logits2.stride(0), vocab_start, ignore_index, _dt(logits2), _st())
+    return logits2
+
+
+# =============================================================================================
+# optimizers (flat fp32 arenas)
+# =============================================================================================
+def adam_(p32, m, v, g, p_lp: Optional[torch.Tensor], *, lr, beta1, beta2, eps, wd, step: int, adamw: bool = True,
+          grad_scale: float = 1.0, sumsq: Optional[torch.Tensor] = None, max_norm: float = 0.0,
+          found_inf: Optional[torch.Tensor] = None):
+    if not p32.is_cuda:
+        if found_inf is not None and float(found_inf) != 0:
+            return
+        coef = 1.0
+        if sumsq is not None and max_norm > 0:
+            coef = min(1.0, max_norm / (math.sqrt(float(sumsq)) + 1e-6))
+        gr = g.float() * (grad_scale * coef)
+        if not adamw:
+            gr = gr + wd * p32
+        m.mul_(beta1).add_(gr, alpha=1 - beta1)
+        v.mul_(beta2).addcmul_(gr, gr, value=1 - beta2)
+        bc1, bc2 = 1 - beta1 ** step, 1 - beta2 ** step
+        upd = (m / bc1) / ((v / bc2).sqrt() + eps)
+        if adamw:
+            upd = upd + wd * p32
+        p32.add_(upd, alpha=-lr)
+        if p_lp is not None:
+            p_lp.copy_(p32.to(p_lp.dtype))
+        return
+    _call("b2_adam", _p(p32), _p(m), _p(v), _p(g), _p(p_lp), p32.numel(), float(lr), float(beta1), float(beta2),
+          float(eps), float(wd), int(step), int(adamw), float(grad_scale), _p(sumsq), float(max_norm), _p(found_inf),
+          _dt(g), _dt(p_lp) if p_lp is not None else DT_FP32, _st())
+
+
+def adadelta_(p32, sq, acc, g, *, lr, rho, eps, wd=0.0):
+    if not p32.is_cuda:
+        gr = g + wd * p32
+        sq.mul_(rho).addcmul_(gr, gr, value=1 - rho)
+        d = (acc + eps).sqrt() / (sq + eps).sqrt() * gr
+        acc.mul_(rho).addcmul_(d, d, value=1 - rho)
+        p32.add_(d, alpha=-lr)
+        return
+    _call("b2_adadelta", _p(p32), _p(sq), _p(acc), _p(g), p32.numel(), float(lr), float(rho), float(eps), float(wd), _st())
+
+
+def sgd_(p32, mom, g, *, lr, momentum=0.0, wd=0.0, grad_scale=1.0, first_step=False):
+    if not p32.is_cuda:
+        gr = g * grad_scale + wd * p32
+        if first_step:
+            mom.copy_(gr)
+        else:
+            mom.mul_(momentum).add_(gr)
+        p32.add_(mom if momentum != 0 else gr, alpha=-lr)
+        return
+    _call("b2_sgd", _p(p32), _p(mom), _p(g), p32.numel(), float(lr), float(momentum), float(wd), float(grad_scale),
+          int(first_step), _st())
+
+
+_sumsq_ws = {}
+
+
+def sumsq(x: torch.Tensor, out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+    """out[0] (+)= sum(x^2) as an fp32 device scalar (no host sync)."""
+    if out is None:
+        out = torch.zeros(1, dtype=torch.float32, device=x.device)
+        accumulate = False
+    if not x.is_cuda:
+        val = x.float().pow(2).sum()
+        if accumulate:
+            out.add_(val)
+        else:
+            out.fill_(val)
+        return out
+    key = (x.device.index, torch.cuda.current_stream().cuda_stream)
+    if key not in _sumsq_ws:
+        n = lib().b2_sumsq_scratch_floats()
+        _sumsq_ws[key] = (torch.empty(n, dtype=torch.float32, device=x.device),
+                          torch.zeros(1, dtype=torch.int32, device=x.device))
+    scratch, counter = _sumsq_ws[key]
+    _call("b2_sumsq", _p(x), x.numel(), _p(scratch), _p(counter), _p(out), int(accumulate), _dt(x), _st())
+    return out
+
+
+def scale_check_(x32: torch.Tensor, scale: float, found_inf: torch.Tensor):
+    if not x32.is_cuda:
+        x32.mul_(scale)
+        if not torch.isfinite(x32).all():
+            found_inf.fill_(1.0)
+        return
+    _call("b2_scale_check", _p(x32), x32.numel(), float(scale), _p(found_inf), _st())
+
+
+# =============================================================================================
+# embedding
+# =============================================================================================
+def embedding_fwd(tok, pos, wte, wpe, vocab_start: int = 0):
+    """tok/pos: int64 [tokens]; returns [tokens, H]"""
+    tokens, H = tok.numel(), wte.shape[1]
+    if not wte.is_cuda:
+        idx = tok - vocab_start
+        ok = (idx >= 0) & (idx < wte.shape[0])
+        out = torch.where(ok[:, None], wte.float()[idx.clamp(0, wte.shape[0] - 1)], torch.zeros(1))
+        if wpe is not None:
+            out = out + wpe.float()[pos]
+        return out.to(wte.dtype)
+    out = torch.empty(tokens, H, dtype=wte.dtype, device=wte.device)
+    _call("b2_embedding_fwd", _p(tok), _p(pos), _p(wte), _p(wpe), _p(out), tokens, H, vocab_start, wte.shape[0],
+          _dt(wte), _st())
+    return out
+
+
+def embedding_bwd_(dy2, tok, pos, dwte32, dwpe32, vocab_start: int = 0):
+    tokens, H = dy2.shape
+    if not dy2.is_cuda:
+        idx = tok - vocab_start
+        ok = (idx >= 0) & (idx < dwte32.shape[0])
+        dwte32.index_add_(0, idx[ok], dy2.float()[ok])
+        if dwpe32 is not None:
+            dwpe32.index_add_(0, pos, dy2.float())
+        return
+    _call("b2_embedding_bwd", _p(dy2), _p(tok), _p(pos), _p(dwte32), _p(dwpe32), tokens, H, vocab_start,
+          dwte32.shape[0], _dt(dy2), _st())
+
+
+# =============================================================================================
+# attention.  q/k/v/o are 4-D views [seq, batch, heads, D] with D contiguous (any strides otherwise)
+# =============================================================================================
+def _attn_ref(q, k, v, scale, causal):
+    qf, kf, vf = (t.float().permute(1, 2, 0, 3) for t in (q, k, v))  # [b, h, s, d]
+    s = torch.matmul(qf, kf.transpose(-1, -2)) * scale
+    if causal:
+        S = s.shape[-1]
+        mask = torch.ones(S, S, dtype=torch.bool, device=s.device).tril()
+        s = s.masked_fill(~mask, float("-inf"))
+    lse = torch.logsumexp(s, -1)
+    p = torch.exp(s - lse[..., None])
+    o = torch.matmul(p, vf)
+    return o, lse, p
+
+
+def attn_fwd(q, k, v, scale: float, causal: bool, out: Optional[torch.Tensor] = None):
+    """Returns (o [seq, batch, heads, D] contiguous, lse [batch, heads, seq] fp32)."""
+    S, B, Hh, D = q.shape
+    if out is None:
+        out = torch.empty((S, B, Hh, D), dtype=q.dtype, device=q.device)
+    if not q.is_cuda:
+        o, lse, _ = _attn_ref(q, k, v, scale, causal)
+        out.copy_(o.permute(2, 0, 1, 3).to(q.dtype))
+        return out, lse.contiguous()
+    assert q.dtype == torch.bfloat16, "flash attention kernel is bf16"
+    for t in (q, k, v, out):
+        assert t.stride(3) == 1
+    lse = torch.empty((B, Hh, S), dtype=torch.float32, device=q.device)
+    _call("b2_attn_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), S, B, Hh, D,
+          q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+          v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
+          float(scale), int(causal), _st())
+    return out, lse
+
+
+def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor, dk: torch.Tensor, dv: torch.Tensor):
+    """Writes dq/dk/dv (4-D views like q/k/v, typically slices of one packed dQKV buffer)."""
+    S, B, Hh, D = q.shape
+    if not q.is_cuda:
+        _, _, p = _attn_ref(q, k, v, scale, causal)
+        qf, kf, vf, dof = (t.float().permute(1, 2, 0, 3) for t in (q, k, v, dout))
+        of = o.float().permute(1, 2, 0, 3)
+        dvf = torch.matmul(p.transpose(-1, -2), dof)
+        dp = torch.matmul(dof, vf.transpose(-1, -2))
+        delta = (dof * of).sum(-1, keepdim=True)
+        ds = p * (dp - delta) * scale
+        dqf = torch.matmul(ds, kf)
+        dkf = torch.matmul(ds.transpose(-1, -2), qf)
+        dq.copy_(dqf.permute(2, 0, 1, 3).to(dq.dtype))
+        dk.copy_(dkf.permute(2, 0, 1, 3).to(dk.dtype))
+        dv.copy_(dvf.permute(2, 0, 1, 3).to(dv.dtype))
+        return
+    delta = torch.empty((B, Hh, S), dtype=torch.float32, device=q.device)
+    dq32 = torch.zeros((S, B, Hh, D), dtype=torch.float32, device=q.device)
+    _call("b2_attn_bwd", _p(q), _p(k), _p(v), _p(o), _p(dout), _p(lse), _p(delta), _p(dq32), _p(dk), _p(dv), S, B, Hh, D,
+          q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
+          v.stride(0), v.stride(1), v.stride(2), o.stride(0), o.stride(1), o.stride(2),
+          dout.stride(0), dout.stride(1), dout.stride(2), dk.stride(0), dk.stride(1), dk.stride(2),
+          dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), _st())
+    dq.copy_(dq32)
