@@ -110,6 +110,29 @@ int b2_sumsq(const void* x, long long n, float* scratch, unsigned int* counter, 
              void* stream);
 int b2_scale_check(float* x, long long n, float scale, float* found_inf, void* stream);
 
+/* Allocation-free sum of squares: out[0] = (or +=) sum x^2, same result as b2_sumsq, but the caller passes
+ * only the input and the output.  (No counterpart in the reference: this entry point exists for users of
+ * THIS library.)  It is meant for callers that cannot get device memory when they need a norm: a
+ * monitoring thread in a job whose framework allocator already holds almost all of HBM (a new cudaMalloc
+ * may fail there, and cudaMalloc/cudaFree stall all streams of the device), plain C/C++ hosts without a
+ * workspace pool, services that freeze their memory map after start-up.
+ *   - Scratch: a file-scope __device__ array of b2_sumsq_static_scratch_bytes() = 4352 bytes that every GPU
+ *     loading the library holds until the process exits.  This call performs no cudaMalloc/cudaFree and
+ *     calls no allocating library routine.
+ *   - Limit: n <= B2_SUMSQ_STATIC_MAX_ELEMS (2^31 elements; the 1024 partial-sum slots bound the grid and,
+ *     with it, how many values one fp32 lane accumulates).  Larger n is rejected with an error; split the
+ *     buffer and pass accumulate = 1, or use b2_sumsq with your own scratch.
+ *   - The first call on each device (with that device current) looks up the array's device address; make
+ *     that first call before starting any stream capture.
+ *   - All calls on a device share the one array (it keeps the previous call's contents; the ticket word that
+ *     must start at zero is cleared on `stream` by every call).  Two calls whose kernels overlap on the GPU
+ *     (different streams, no ordering between them) race on it: order them.
+ */
+#define B2_SUMSQ_STATIC_MAX_ELEMS (1LL << 31)
+long long b2_sumsq_static_max_elems(void);
+int b2_sumsq_static_scratch_bytes(void);
+int b2_sumsq_static(const void* x, long long n, float* out, int accumulate, int dtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Embedding (vocab-parallel aware).  replaces: Megatron VocabParallelEmbedding (E10/K11), nn.Embedding.
  */
