@@ -175,6 +175,7 @@ def main():
         s.record()
         last = run(n_steps, it, read_loss)
         e.record()
+        timed.host_issue_ms = (time.perf_counter() - t0) * 1e3 / n_steps    # host time to ISSUE a step (no sync)
         torch.cuda.synchronize(); dist.barrier()
         wall = (time.perf_counter() - t0) * 1e3
         ms = torch.tensor([s.elapsed_time(e), wall], device=dev)
@@ -186,6 +187,7 @@ def main():
     sampler = None if (a.no_clocks or rank != 0) else ClockSampler(torch.cuda.current_device())
     l0 = N.launches()
     ms_dev, _, _ = timed(a.steps, dit, False)
+    host_issue = timed.host_issue_ms
     launches = N.launches() - l0
     run(1, hit, True)
     ms_e2e, wall_e2e, last_loss = timed(a.steps, hit, True)
@@ -206,7 +208,7 @@ def main():
                "clocks": clocks,
                "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": nmb * a.micro_batch_size * (a.seq_length + 1) * 8 if is_src else 0,
                        "d2h_bytes_per_step": 4, "ms_per_step": max(ms_e2e, wall_e2e) / a.steps, "last_loss": last_loss},
-               "gpu_launches": launches}
+               "gpu_launches": launches, "host_issue_ms_per_step": host_issue}
         print(json.dumps(out), flush=True)
     dist.barrier()
     dist.destroy_process_group()

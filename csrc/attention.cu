@@ -32,6 +32,13 @@ constexpr int NTHREADS = 256;
 constexpr int SM_WARP0 = 4;
 constexpr float LOG2E = 1.4426950408889634f;
 
+// single MUFU.EX2 (no denormal/range branches): inputs here are <= 0 after max subtraction
+B2_DEVICE float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct AttnParams {
   int seqlen, batch, heads;
   int causal;
@@ -208,29 +215,40 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t tS = tmem_base + lane_off + S_COL + (j & 1) * BLK;
       const int k0 = j * BLK;
       const bool need_mask = (p.causal && j == qb) || (k0 + BLK > p.seqlen);
-      // pass 1: row max
+      // pass 1: row max (mask handling hoisted out of the element loop: only the diagonal / ragged block pays)
       float mx = m_run;
+      if (!need_mask) {
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tS + c * 32, v);
-        tmem_ld_wait();
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(tS + c * 32, v);
+          tmem_ld_wait();
+          float m0 = __uint_as_float(v[0]), m1 = __uint_as_float(v[1]), m2 = __uint_as_float(v[2]), m3 = __uint_as_float(v[3]);
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float s = __uint_as_float(v[i]);
-          if (need_mask) {
-            const int kpos = k0 + c * 32 + i;
-            if ((p.causal && kpos > qpos) || kpos >= p.seqlen) s = -INFINITY;
+          for (int i = 4; i < 32; i += 4) {
+            m0 = fmaxf(m0, __uint_as_float(v[i])); m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+            m2 = fmaxf(m2, __uint_as_float(v[i + 2])); m3 = fmaxf(m3, __uint_as_float(v[i + 3]));
           }
-          mx = fmaxf(mx, s);
+          mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+        }
+      } else {
+        const int lim = min(p.causal ? qpos : 0x7fffffff, p.seqlen - 1) - k0;   // last visible column of this block
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(tS + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i) <= lim ? __uint_as_float(v[i]) : -INFINITY);
         }
       }
       const float m_new = mx;
       const float msc = (m_new == -INFINITY) ? 0.f : m_new * sl2;
-      const float alpha = (m_run == -INFINITY) ? 0.f : exp2f(m_run * sl2 - msc);
+      const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run * sl2 - msc);
       // pass 2: probabilities -> bf16 -> swizzled smem (A operand of P V)
-      float rs = 0.f;
+      float rs0 = 0.f, rs1 = 0.f;
       uint8_t* pbuf = sP + (j & 1) * L::P_BYTES;
+      const int lim2 = need_mask ? (min(p.causal ? qpos : 0x7fffffff, p.seqlen - 1) - k0) : 0x7fffffff;
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t v[32];
@@ -238,17 +256,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tmem_ld_wait();
         if (c == 3) { tc_fence_before(); mbar_arrive(&s_empty[j & 1]); }
         uint32_t pk[16];
+        if (!need_mask) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float s0 = __uint_as_float(v[i]), s1 = __uint_as_float(v[i + 1]);
-          float e0 = exp2f(s0 * sl2 - msc), e1 = exp2f(s1 * sl2 - msc);
-          if (need_mask) {
-            const int kpos = k0 + c * 32 + i;
-            if ((p.causal && kpos > qpos) || kpos >= p.seqlen) e0 = 0.f;
-            if ((p.causal && kpos + 1 > qpos) || kpos + 1 >= p.seqlen) e1 = 0.f;
+          for (int i = 0; i < 32; i += 2) {
+            float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), sl2, -msc));
+            float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), sl2, -msc));
+            rs0 += e0; rs1 += e1;
+            pk[i >> 1] = pack_bf16x2(e0, e1);
           }
-          rs += e0 + e1;
-          pk[i >> 1] = pack_bf16x2(e0, e1);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            float e0 = (c * 32 + i) <= lim2 ? fast_exp2(fmaf(__uint_as_float(v[i]), sl2, -msc)) : 0.f;
+            float e1 = (c * 32 + i + 1) <= lim2 ? fast_exp2(fmaf(__uint_as_float(v[i + 1]), sl2, -msc)) : 0.f;
+            rs0 += e0; rs1 += e1;
+            pk[i >> 1] = pack_bf16x2(e0, e1);
+          }
         }
         // 32 columns = 64 B = four 16-byte chunks of slab (c >> 1), chunk index (c & 1) * 4 + q
         uint8_t* rowp = pbuf + (c >> 1) * (BLK * 128) + r * 128;
@@ -259,6 +282,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
               make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
         }
       }
+      const float rs = rs0 + rs1;
       fence_proxy_async_smem();
       mbar_arrive(&p_full[j & 1]);
       l_run = l_run * alpha + rs;
@@ -523,6 +547,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       mbar_wait(st_full, it & 1);
       tc_fence_after();
       const bool diag = p.causal && qb == kb;
+      const int qmin = diag ? (kpos - qbase) : 0;     // first visible query column of this block (branch-free mask)
       const float* lse_s = sLse + (it & 1) * BLK;
       const float* del_s = sDelta + (it & 1) * BLK;
 #pragma unroll 1
@@ -538,8 +563,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int qi = c * 32 + i + e;
-            float pe = exp2f(__uint_as_float(sv[i + e]) * sl2 - lse_s[qi]);
-            if (diag && (qbase + qi) < kpos) pe = 0.f;
+            float pe = fast_exp2(fmaf(__uint_as_float(sv[i + e]), sl2, -lse_s[qi]));
+            pe = (qi >= qmin) ? pe : 0.f;
             pr[e] = pe;
             ds[e] = pe * (__uint_as_float(dv[i + e]) - del_s[qi]) * p.scale;
           }
