@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--comm-backend", default="native", choices=["native", "nccl"])
     ap.add_argument("--dropout", type=float, default=0.0)
     ap.add_argument("--no-clocks", action="store_true")
+    ap.add_argument("--no-cuda-graph", action="store_true", help="issue every kernel from Python instead of replaying the captured micro-batch graph")
     return ap.parse_args()
 
 
@@ -125,6 +126,8 @@ def main():
             "--comm-backend", a.comm_backend, "--num-workers", "0"]
     if tp > 1:
         argv.append("--sequence-parallel")
+    if not a.no_cuda_graph and a.dropout == 0.0:
+        argv.append("--cuda-graph")
     _stdout = sys.stdout
     sys.stdout = sys.stderr      # keep stdout for the single JSON line
     args = eng.initialize_megatron(argv=argv)
@@ -203,7 +206,7 @@ def main():
                "impl": "ours",
                "config": {"model": f"GPT-2 small {a.num_layers}L h{a.hidden_size} {a.heads} heads (Megatron GPT, CodeParrot-style)", "global_batch": gbs,
                           "seq_len": a.seq_length, "vocab": a.vocab, "micro_batch": a.micro_batch_size, "num_microbatches": nmb,
-                          "parallelism": f"tp{tp}{'+sp' if tp > 1 else ''} dp{dp}", "comm_backend": a.comm_backend, "dropout": a.dropout,
+                          "parallelism": f"tp{tp}{'+sp' if tp > 1 else ''} dp{dp}", "comm_backend": a.comm_backend, "dropout": a.dropout, "cuda_graph": bool(not a.no_cuda_graph and a.dropout == 0.0),
                           "optimizer": "AdamW fp32 master + grad clip 1.0", "l2": "per-step working set (weights+activations, GBs) exceeds the 126 MB L2"},
                "clocks": clocks,
                "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": nmb * a.micro_batch_size * (a.seq_length + 1) * 8 if is_src else 0,

@@ -1,0 +1,186 @@
+// In-kernel collectives over NVLink 5 / NVSwitch (sm_100a): no NCCL on these paths.
+//
+// Every buffer that takes part is allocated as SYMMETRIC memory (same size on every rank, peer-mapped,
+// and - when the switch supports it - bound to one multicast address).  Each symmetric buffer carries its
+// own small control block (B2_CTRL_WORDS uint32 right after the payload): a call counter and one arrival
+// slot per rank, written with system-scope release stores and polled with acquire loads, so consecutive
+// kernels on a buffer (also when replayed from a CUDA graph) stay in lock-step without the host.
+//
+//   b2_allreduce : sum over ranks, scaled, in place:   multimem.ld_reduce (the switch adds) -> * scale ->
+//                  multimem.st (the switch broadcasts); each rank owns 1/world of the vector.  Falls back to
+//                  peer loads/stores when no multicast address exists.
+//                  replaces: NCCL all-reduce of DDP buckets / the Megatron grad buffer + the separate
+//                  div-by-world pass, fused as scale in the same kernel.
+//   b2_allgather_pull / b2_signal_* : building blocks of the fused all-gather->GEMM (see gemm.cu).
+#include "common.cuh"
+#include "b200dist.h"
+
+using namespace b2;
+
+namespace {
+
+constexpr int MAX_RANKS = 8;
+
+struct Peers {
+  void* ptr[MAX_RANKS];        // payload base of every rank (peer-mapped virtual addresses)
+  uint32_t* ctrl[MAX_RANKS];   // control block of every rank
+};
+
+// ctrl layout (uint32): [0..2] see enter(); [16 + r] arrival slot of rank r for phase A, [32 + r] phase B
+constexpr int CTRL_A = 16, CTRL_B = 32;
+
+// All ranks arrive and wait.  One CTA-wide call; `epoch` must be identical on all ranks.
+B2_DEVICE void fabric_barrier(const Peers& P, int rank, int world, uint32_t epoch, int slot_base) {
+  __syncthreads();
+  if (threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(P.ctrl[threadIdx.x] + slot_base + rank, epoch);
+    const uint32_t* mine = P.ctrl[rank] + slot_base + threadIdx.x;
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) { }
+  }
+  __syncthreads();
+}
+
+B2_DEVICE void mm_ld_reduce_f32x4(const void* mc, float& a, float& b, float& c, float& d) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(a), "=f"(b), "=f"(c), "=f"(d) : "l"(mc) : "memory");
+}
+B2_DEVICE void mm_st_f32x4(void* mc, float a, float b, float c, float d) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+B2_DEVICE void mm_ld_reduce_bf16x8(const void* mc, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "l"(mc) : "memory");
+}
+B2_DEVICE void mm_st_b32x4(void* mc, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// ctrl words: [0] gate (epoch published to the CTAs of this grid), [1] epoch of the last COMPLETED call,
+// [2] CTA completion ticket.  Calls on one buffer are stream-ordered, so word [1] is stable at kernel entry.
+B2_DEVICE uint32_t enter(const Peers& P, int rank, int world, uint32_t* my_ctrl) {
+  const uint32_t epoch = my_ctrl[1] + 1;
+  if (blockIdx.x == 0) {
+    fabric_barrier(P, rank, world, epoch, CTRL_A);         // every rank has launched and its input is visible
+    if (threadIdx.x == 0) st_release_gpu(my_ctrl + 0, epoch);
+  } else {
+    if (threadIdx.x == 0) {
+      while (static_cast<int32_t>(ld_acquire_gpu(my_ctrl + 0) - epoch) < 0) { }
+    }
+    __syncthreads();
+  }
+  return epoch;
+}
+
+template <typename T, bool MULTICAST>
+__global__ void __launch_bounds__(512)
+allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int rank, int world) {
+  uint32_t* my_ctrl = P.ctrl[rank];
+  const uint32_t epoch = enter(P, rank, world, my_ctrl);
+  // my slice, in 16-byte vectors
+  constexpr int EPV = 16 / sizeof(T);
+  const long long nvec = n_elems / EPV;
+  const long long per = (nvec + world - 1) / world;
+  const long long v0 = per * rank, v1 = min(nvec, v0 + per);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long v = v0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < v1; v += stride) {
+    if constexpr (MULTICAST) {
+      uint8_t* mc = static_cast<uint8_t*>(mc_base) + v * 16;
+      if constexpr (sizeof(T) == 4) {
+        float a, b, c, d;
+        mm_ld_reduce_f32x4(mc, a, b, c, d);
+        mm_st_f32x4(mc, a * scale, b * scale, c * scale, d * scale);
+      } else {
+        uint32_t a, b, c, d;
+        mm_ld_reduce_bf16x8(mc, a, b, c, d);
+        if (scale != 1.f) {
+          float2 f;
+          f = unpack_bf16x2(a); a = pack_bf16x2(f.x * scale, f.y * scale);
+          f = unpack_bf16x2(b); b = pack_bf16x2(f.x * scale, f.y * scale);
+          f = unpack_bf16x2(c); c = pack_bf16x2(f.x * scale, f.y * scale);
+          f = unpack_bf16x2(d); d = pack_bf16x2(f.x * scale, f.y * scale);
+        }
+        mm_st_b32x4(mc, a, b, c, d);
+      }
+    } else {
+      float acc[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+      for (int r = 0; r < world; ++r) {
+        uint4 q = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(P.ptr[r]) + v * 16);
+        if constexpr (sizeof(T) == 4) {
+          acc[0] += __uint_as_float(q.x); acc[1] += __uint_as_float(q.y); acc[2] += __uint_as_float(q.z); acc[3] += __uint_as_float(q.w);
+        } else {
+          float2 f;
+          f = unpack_bf16x2(q.x); acc[0] += f.x; acc[1] += f.y;
+          f = unpack_bf16x2(q.y); acc[2] += f.x; acc[3] += f.y;
+          f = unpack_bf16x2(q.z); acc[4] += f.x; acc[5] += f.y;
+          f = unpack_bf16x2(q.w); acc[6] += f.x; acc[7] += f.y;
+        }
+      }
+      uint4 o;
+      if constexpr (sizeof(T) == 4) {
+        o = make_uint4(__float_as_uint(acc[0] * scale), __float_as_uint(acc[1] * scale), __float_as_uint(acc[2] * scale), __float_as_uint(acc[3] * scale));
+      } else {
+        o = make_uint4(pack_bf16x2(acc[0] * scale, acc[1] * scale), pack_bf16x2(acc[2] * scale, acc[3] * scale),
+                       pack_bf16x2(acc[4] * scale, acc[5] * scale), pack_bf16x2(acc[6] * scale, acc[7] * scale));
+      }
+      for (int r = 0; r < world; ++r)
+        *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[r]) + v * 16) = o;
+    }
+  }
+  // all CTAs of this grid done -> one cross-GPU barrier -> result complete everywhere
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool last;
+  if (threadIdx.x == 0) {
+    unsigned int t = atomicAdd(my_ctrl + 2, 1u);           // word 2 = CTA completion ticket
+    last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last) {
+    fabric_barrier(P, rank, world, epoch, CTRL_B);
+    if (threadIdx.x == 0) {
+      my_ctrl[2] = 0u;
+      my_ctrl[1] = epoch;                                  // this call is complete (next launch's epoch base)
+      __threadfence();
+    }
+  }
+}
+
+int check(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int b2_ctrl_words(void) { return B2_CTRL_WORDS; }
+
+// ptrs / ctrls: `world` peer-mapped addresses each (host arrays).  mc_ptr: multicast address of the payload or NULL.
+// n_elems * sizeof(dtype) must be a multiple of 16.  In place on every rank's payload.
+extern "C" int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                            int rank, int world, int max_ctas, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (world < 1 || world > MAX_RANKS) { b2host::set_error("allreduce: world size %d unsupported (max %d)", world, MAX_RANKS); return -1; }
+  const int esz = dtype == B2_DTYPE_FP32 ? 4 : 2;
+  if (dtype == B2_DTYPE_FP16) { b2host::set_error("allreduce: fp16 payloads are not supported (use bf16 or fp32)"); return -1; }
+  if ((n_elems * esz) % 16) { b2host::set_error("allreduce: payload must be a multiple of 16 bytes"); return -1; }
+  Peers P;
+  for (int r = 0; r < MAX_RANKS; ++r) { P.ptr[r] = r < world ? ptrs[r] : nullptr; P.ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
+  long long nvec = n_elems * esz / 16;
+  long long per = (nvec + world - 1) / world;
+  int threads = 512;
+  long long want = (per + threads - 1) / threads;
+  int cap = max_ctas > 0 ? max_ctas : 64;
+  int grid = static_cast<int>(want < 1 ? 1 : (want > cap ? cap : want));
+  if (mc_ptr != nullptr) {
+    if (dtype == B2_DTYPE_FP32) allreduce_kernel<float, true><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world);
+    else allreduce_kernel<__nv_bfloat16, true><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world);
+  } else {
+    if (dtype == B2_DTYPE_FP32) allreduce_kernel<float, false><<<grid, threads, 0, st>>>(P, nullptr, n_elems, scale, rank, world);
+    else allreduce_kernel<__nv_bfloat16, false><<<grid, threads, 0, st>>>(P, nullptr, n_elems, scale, rank, world);
+  }
+  return check("allreduce");
+}

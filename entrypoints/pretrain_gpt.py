@@ -42,7 +42,10 @@ def get_batch(data_iterator):
     of the reference (get_ltor_masks_and_position_ids, :83-88) is implicit in the attention kernel."""
     args, tokenizer = get_args(), get_tokenizer()
     data = next(data_iterator) if data_iterator is not None else None
-    data_b = tensor_parallel.broadcast_data(["text"], data, torch.int64)
+    if getattr(args, "_static_batch", False) and data is not None and data["text"].is_cuda:
+        data_b = data        # CUDA-graph mode: the batch already sits in the static device buffer on every TP rank
+    else:
+        data_b = tensor_parallel.broadcast_data(["text"], data, torch.int64)
     tokens_ = data_b["text"].long()
     labels = tokens_[:, 1:].contiguous()
     tokens = tokens_[:, :-1].contiguous()

@@ -142,6 +142,18 @@ int b2_embedding_bwd(const void* dy, const long long* tok, const long long* pos,
                      long long tokens, int H, long long vocab_start, long long vocab_local, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * In-kernel collectives over NVLink / NVSwitch on SYMMETRIC buffers (csrc/comm.cu).  ptrs[r] / ctrls[r] are the
+ * peer-mapped addresses of rank r's payload and of its control block (B2_CTRL_WORDS zero-initialised uint32
+ * owned by that buffer); mc_ptr is the NVSwitch multicast address of the payload or NULL (peer load/store path).
+ * All ranks of the group must launch the same calls on a buffer in the same order.
+ * replaces: NCCL all-reduce + separate scale of DDP buckets / Megatron's grad buffer.
+ */
+#define B2_CTRL_WORDS 64
+int b2_ctrl_words(void);
+int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                 int rank, int world, int max_ctas, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Flash attention (tcgen05), bf16, head_dim 64 or 128 forward / 64 backward.  Strides are in
  * elements for (seq, batch, head); head_dim is contiguous.  lse: fp32 [batch, heads, seqlen].
  * Backward: delta is fp32 scratch [batch, heads, seqlen]; dq_accum is fp32 [seq, batch, heads, D],

@@ -241,15 +241,42 @@ def setup_model_and_optimizer(model_provider_func, no_optimizer=False):
     return model, optimizer, sched
 
 
+_GRAPH = {"runner": None, "tried": False}
+
+
+def get_graph_runner(forward_step_func, model):
+    """Lazily captures the micro-batch forward+backward into a CUDA graph (--cuda-graph; engine/graphed.py)."""
+    args = get_args()
+    if not getattr(args, "cuda_graph", False) or _GRAPH["tried"]:
+        return _GRAPH["runner"]
+    _GRAPH["tried"] = True
+    from . import graphed
+    if not graphed.supported(args) or len(model) != 1:
+        print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, dropout 0, bf16/fp32, no recompute): running eagerly")
+        return None
+    nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    args._static_batch = True
+    r = graphed.GraphedMicrobatch(forward_step_func, model[0], nmb, args.micro_batch_size, args.seq_length, dev)
+    r.capture()
+    _GRAPH["runner"] = r
+    print_rank_0("> captured micro-batch forward+backward into a CUDA graph")
+    return r
+
+
 def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_scheduler):
     args, timers = get_args(), get_timers()
+    runner = get_graph_runner(forward_step_func, model)
     optimizer.zero_grad()
     S = args.seq_length // (args.tensor_model_parallel_size if args.sequence_parallel else 1)
     shape = (S, args.micro_batch_size, args.hidden_size)
     nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
     timers("forward-backward", log_level=1).start(barrier=args.barrier_with_L1_time)
-    losses = pp.forward_backward(forward_step_func, data_iterator, model, nmb, shape, args.params_dtype, forward_only=False,
-                                 grad_scale=optimizer.get_loss_scale(), timers=timers if args.timing_log_level >= 2 else None)
+    if runner is not None:
+        losses = runner.run_step(data_iterator)
+    else:
+        losses = pp.forward_backward(forward_step_func, data_iterator, model, nmb, shape, args.params_dtype, forward_only=False,
+                                     grad_scale=optimizer.get_loss_scale(), timers=timers if args.timing_log_level >= 2 else None)
     timers("forward-backward").stop()
     timers("all-grads-sync", log_level=1).start(barrier=args.barrier_with_L1_time)
     optimizer.reduce_model_grads()

@@ -1,5 +1,103 @@
-"""placeholder replaced below"""
-class _Null:
-    usable = False
-def get_fabric(group=None):
-    return _Null()
+"""NVLink / NVSwitch fabric: symmetric buffers + the fused in-kernel collectives (csrc/comm.cu, gemm.cu).
+
+Bootstrap uses torch.distributed only for plumbing: ``torch.distributed._symmetric_memory`` allocates a
+buffer on every rank of a group, exchanges the handles, maps every peer's copy into this process and - on
+NVSwitch systems - binds them to one multicast address.  From then on all traffic is issued by our own
+kernels through those addresses (peer ld/st, TMA on peer addresses, multimem.ld_reduce / multimem.st);
+NCCL is not involved on these paths.
+
+A symmetric buffer = payload + a 256-byte control block (arrival slots, call epochs) that the kernels use
+to stay in lock-step across GPUs; because the epochs live in device memory, calls can be captured into a
+CUDA graph and replayed.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Dict, List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import native as N
+
+_CTRL_BYTES = 256
+_FABRICS: Dict[int, "Fabric"] = {}
+
+c_p, c_i, c_ll, c_f = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+class SymmBuffer:
+    """payload tensor (this rank's copy) + peer / multicast addresses."""
+
+    def __init__(self, fabric: "Fabric", numel: int, dtype: torch.dtype):
+        import torch.distributed._symmetric_memory as symm_mem
+        esz = torch.empty((), dtype=dtype).element_size()
+        self.payload_bytes = (numel * esz + 255) // 256 * 256
+        total = self.payload_bytes + _CTRL_BYTES
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.raw = symm_mem.empty(total, dtype=torch.uint8, device=dev)
+        self.raw.zero_()
+        self.handle = symm_mem.rendezvous(self.raw, group=fabric.group)
+        self.tensor = self.raw[: numel * esz].view(dtype)
+        self.numel, self.dtype = numel, dtype
+        w = fabric.world
+        base = [int(p) for p in self.handle.buffer_ptrs]
+        self.ptrs = (c_p * w)(*base)
+        self.ctrls = (c_p * w)(*[b + self.payload_bytes for b in base])
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+        self.mc_ptr = mc if (mc and fabric.use_multicast) else 0
+        torch.cuda.synchronize()
+        dist.barrier(group=fabric.group)     # every rank has zeroed its control block before the first kernel
+
+
+class Fabric:
+    def __init__(self, group=None):
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
+        self.usable = False
+        self.use_multicast = True
+        self.error: Optional[str] = None
+        if not torch.cuda.is_available() or self.world < 2 or self.world > 8 or dist.get_backend(self.group) != "nccl":
+            self.error = "needs CUDA, an NCCL-bootstrapped group and 2..8 ranks"
+            return
+        try:
+            L = N.lib()
+            L.b2_allreduce.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p]
+            L.b2_allreduce.restype = c_i
+            probe = SymmBuffer(self, 1024, torch.float32)
+            probe.tensor.fill_(float(self.rank + 1))
+            self.all_reduce_(probe, scale=1.0)
+            torch.cuda.synchronize()
+            want = self.world * (self.world + 1) / 2
+            ok = bool((probe.tensor == want).all().item())
+            flag = torch.tensor([int(ok)], device=probe.tensor.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+            self.usable = bool(flag.item())
+            if not self.usable:
+                self.error = "probe all-reduce returned wrong values"
+        except Exception as e:  # symmetric memory not available on this system -> callers fall back to NCCL
+            self.error = f"{type(e).__name__}: {e}"
+            self.usable = False
+
+    def alloc(self, numel: int, dtype: torch.dtype) -> SymmBuffer:
+        return SymmBuffer(self, numel, dtype)
+
+    def all_reduce_(self, buf: SymmBuffer, scale: float = 1.0, numel: Optional[int] = None, max_ctas: int = 0):
+        """in place: buf <- scale * sum over ranks (fused NVLS reduce + scale + broadcast)."""
+        n = buf.numel if numel is None else numel
+        esz = buf.tensor.element_size()
+        n_pad = (n * esz + 15) // 16 * 16 // esz       # payload is 256-byte padded, so rounding up is safe
+        N._call("b2_allreduce", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n_pad, N._dt(buf.tensor),
+                float(scale), self.rank, self.world, max_ctas, N._st())
+
+
+def get_fabric(group=None) -> Fabric:
+    g = group if group is not None else dist.group.WORLD
+    key = id(g)
+    if key not in _FABRICS:
+        _FABRICS[key] = Fabric(g)
+        if dist.get_rank() == 0:
+            f = _FABRICS[key]
+            print(f"> NVLink fabric for group of {f.world}: {'ready' if f.usable else 'unavailable (' + str(f.error) + ')'}", flush=True)
+    return _FABRICS[key]
