@@ -77,6 +77,59 @@ if which in ("all", "allreduce"):
         busbw = 2 * (world - 1) / world * n * 4 / ms / 1e6
         p0(f"time allreduce+scale {mb:4d} MiB fp32: fused {ms:.3f} ms ({busbw:.0f} GB/s busbw) | nccl div+allreduce {ms_n:.3f} ms")
 
+if which in ("all", "ag"):
+    for (rows, K, Nn, bmn) in [(256, 128, 256, False), (1024, 768, 1152, False), (6144, 768, 1536, False), (1024, 768, 384, True)]:
+        torch.manual_seed(100 + rank)
+        x = torch.randn(rows, K, device=dev, dtype=torch.bfloat16)
+        torch.manual_seed(7)
+        W = (torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16) * 0.05)
+        bias = torch.randn(Nn, device=dev, dtype=torch.bfloat16) if not bmn else None
+        y, xg = F.ag_gemm(x, W, b_mn=bmn, bias=bias, epilogue=N.EPI_BIAS if bias is not None else N.EPI_NONE)
+        torch.cuda.synchronize()
+        xs = [torch.empty_like(x) for _ in range(world)]
+        dist.all_gather(xs, x)
+        xf = torch.cat(xs)
+        ref = xf.float() @ (W.float() if bmn else W.float().t()) + (bias.float() if bias is not None else 0)
+        report(f"ag_gemm gathered rows{rows} K{K}", xg, xf, 0.0)
+        report(f"ag_gemm out rows{rows} K{K} N{Nn} b_mn={int(bmn)}", y, ref, 2e-2)
+        y2, _ = F.ag_gemm(x, W, b_mn=bmn, bias=bias, epilogue=N.EPI_BIAS if bias is not None else N.EPI_NONE)
+        torch.cuda.synchronize()
+        report(f"ag_gemm (2nd call) rows{rows}", y2, ref, 2e-2)
+    rows, K, Nn = 6144, 768, 1536
+    x = torch.randn(rows, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+    xf = torch.empty(rows * world, K, device=dev, dtype=torch.bfloat16)
+    ms = timeit(lambda: F.ag_gemm(x, W))
+    ms_n = timeit(lambda: (dist.all_gather_into_tensor(xf, x), N.gemm(xf, W)))
+    ms_g = timeit(lambda: N.gemm(xf, W))
+    p0(f"time ag_gemm rows/rank {rows} K{K} N{Nn}: fused {ms:.3f} ms | nccl all_gather + gemm {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms")
+
+if which in ("all", "rs"):
+    for (M, K, Nn, bmn) in [(512, 128, 256, False), (2048, 384, 768, False), (12288, 1536, 768, False), (2048, 576, 768, True)]:
+        torch.manual_seed(200 + rank)
+        a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+        W = torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16) * 0.05
+        torch.manual_seed(9)
+        bias = torch.randn(Nn, device=dev, dtype=torch.bfloat16)
+        rows = M // world
+        res = torch.randn(rows, Nn, device=dev, dtype=torch.bfloat16)
+        out = F.gemm_rs(a, W, b_mn=bmn, bias=bias, residual=res)
+        torch.cuda.synchronize()
+        part = a.float() @ (W.float() if bmn else W.float().t())
+        dist.all_reduce(part)
+        ref = part[rank * rows:(rank + 1) * rows] + bias.float() + res.float()
+        report(f"gemm_rs M{M} K{K} N{Nn} b_mn={int(bmn)}", out, ref, 3e-2)
+        out2 = F.gemm_rs(a, W, b_mn=bmn, bias=bias, residual=res)
+        out3 = F.gemm_rs(a, W, b_mn=bmn, bias=bias, residual=res)
+        torch.cuda.synchronize()
+        report(f"gemm_rs (3rd call) M{M}", out3, ref, 3e-2)
+    M, K, Nn = 12288, 1536, 768
+    a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+    o = torch.empty(M // world, Nn, device=dev, dtype=torch.bfloat16)
+    ms = timeit(lambda: F.gemm_rs(a, W))
+    ms_n = timeit(lambda: dist.reduce_scatter_tensor(o, N.gemm(a, W)))
+    ms_g = timeit(lambda: N.gemm(a, W))
+    p0(f"time gemm_rs M{M} K{K} N{Nn}: fused {ms:.3f} ms | gemm + nccl reduce_scatter {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms")
+
 p0("FAILED:" if FAILS else "ALL OK", FAILS)
 dist.barrier()
 dist.destroy_process_group()

@@ -42,7 +42,129 @@ struct GemmParams {
   const void* aux;      // [M, ld_aux] (operand dtype): residual or pre-activation
   long long ld_aux;
   float alpha;
+  // ---- fused collectives (FUSE != 0); M is split into `f_world` contiguous shards of f_bpr 128-row blocks
+  int f_rank, f_world, f_ncomm, f_bpr, f_shard_rows;
+  int m_rot;                       // tile order starts at row-block m_rot (overlap: see ag / rs comments)
+  long long f_row_bytes;           // AG: bytes per row of the gathered operand
+  void* f_peer[8];                 // AG: every rank's shard (symmetric)   RS: unused
+  uint32_t* f_ctrl[8];             // control block of the symmetric buffer on every rank
+  uint8_t* f_xg;                   // AG: local gathered operand [M, K]
+  uint32_t* f_flags;               // AG: local per-row-block ready epochs
+  uint32_t* f_cnt[8];              // RS: per-row-block arrival counters on every rank (symmetric)
+  const CUtensorMap* f_rsmaps;     // RS: device array [2 parity][world] of staging-slot tensor maps
+  const void* f_stage;             // RS: this rank's staging [2][world][shard_rows, N]
+  void* f_out;                     // RS: reduced output shard [shard_rows, N]
+  long long f_ld_out;
+  const void* f_bias;              // RS: bias [N] added once, after the reduction
+  const void* f_res;               // RS: residual shard [shard_rows, f_ld_res]
+  long long f_ld_res;
 };
+
+constexpr int FUSE_NONE = 0, FUSE_AG = 1, FUSE_RS = 2;
+constexpr int FCTRL_A = 16, FCTRL_B = 32;   // arrival slots inside a control block (same layout as comm.cu)
+
+// ---- 1-D bulk copies (TMA without a tensor map) used by the all-gather CTAs
+B2_DEVICE void bulk_g2s(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+B2_DEVICE void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+               ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+
+// All-gather CTA of the fused AG->GEMM kernel: one thread streams 128-row blocks of every rank's shard
+// (own shard first, then rank+1, ...) through a shared-memory ring with bulk async copies - peer memory is
+// read over NVLink exactly once - into the local gathered operand, and publishes each block to the GEMM
+// CTAs of this GPU with a device-scope release of the call epoch.
+B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t epoch) {
+  constexpr int STG = 6, LA = 3;
+  constexpr uint32_t PIECE = 32 * 1024;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STG * PIECE);
+  uint32_t* my_ctrl = p.f_ctrl[p.f_rank];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < STG; ++i) mbar_init(&bars[i], 1);
+    mbar_fence_init();
+    if (c == 0) {                                   // my shard is complete (stream order): tell the peers
+      __threadfence_system();
+      for (int r = 0; r < p.f_world; ++r)
+        if (r != p.f_rank) st_release_sys(p.f_ctrl[r] + FCTRL_A + p.f_rank, epoch);
+    }
+    uint32_t issued = 0, stored = 0;                // running piece counters (ring position + barrier phase)
+    for (int si = 0; si < p.f_world; ++si) {
+      const int src = (p.f_rank + si) % p.f_world;
+      bool ready = (src == p.f_rank);
+      for (int blk = 0; blk < p.f_bpr; ++blk) {
+        if ((si * p.f_bpr + blk) % p.f_ncomm != c) continue;
+        if (!ready) {
+          while (static_cast<int32_t>(ld_acquire_sys(my_ctrl + FCTRL_A + src) - epoch) < 0) { }
+          ready = true;
+        }
+        const int rows = min(128, p.f_shard_rows - blk * 128);
+        const long long bytes = static_cast<long long>(rows) * p.f_row_bytes;
+        const uint8_t* gsrc = static_cast<const uint8_t*>(p.f_peer[src]) + static_cast<long long>(blk) * 128 * p.f_row_bytes;
+        uint8_t* gdst = p.f_xg + (static_cast<long long>(src) * p.f_shard_rows + static_cast<long long>(blk) * 128) * p.f_row_bytes;
+        const int npieces = static_cast<int>((bytes + PIECE - 1) / PIECE);
+        for (int i = 0; i < npieces + LA; ++i) {
+          if (i < npieces) {
+            const uint32_t s = issued % STG;
+            if (issued >= STG) tma_store_wait_read<STG - LA - 1>();   // the store that last used this slot has drained
+            const long long left_i = bytes - static_cast<long long>(i) * PIECE;
+            const uint32_t sz = left_i < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left_i) : PIECE;
+            mbar_expect_tx(&bars[s], sz);
+            bulk_g2s(smem + s * PIECE, gsrc + static_cast<long long>(i) * PIECE, sz, &bars[s]);
+            ++issued;
+          }
+          const int j = i - LA;
+          if (j >= 0) {
+            const uint32_t s = stored % STG;
+            mbar_wait(&bars[s], (stored / STG) & 1);
+            const long long left_j = bytes - static_cast<long long>(j) * PIECE;
+            const uint32_t sz = left_j < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left_j) : PIECE;
+            bulk_s2g(gdst + static_cast<long long>(j) * PIECE, smem + s * PIECE, sz);
+            tma_store_commit();
+            ++stored;
+          }
+        }
+        tma_store_wait_all<0>();
+        fence_proxy_async_all();
+        __threadfence();
+        st_release_gpu(p.f_flags + src * p.f_bpr + blk, epoch);
+      }
+    }
+    // all of this CTA's pulls are done; the last all-gather CTA tells every peer "I no longer read your shard"
+    __threadfence_system();
+    const unsigned int t = atomicAdd(my_ctrl + 3, 1u);
+    if (t == static_cast<unsigned int>(p.f_ncomm - 1)) {
+      my_ctrl[3] = 0u;
+      for (int r = 0; r < p.f_world; ++r)
+        if (r != p.f_rank) st_release_sys(p.f_ctrl[r] + FCTRL_B + p.f_rank, epoch);
+    }
+  }
+}
+
+// Last CTA of a fused launch: wait until no peer still depends on this rank's symmetric data, then mark
+// the call complete (ctrl[1] = epoch) so the next launch on this buffer derives the next epoch.
+B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers_done) {
+  __syncthreads();
+  __shared__ bool last;
+  uint32_t* my_ctrl = p.f_ctrl[p.f_rank];
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = (atomicAdd(my_ctrl + 2, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (last && threadIdx.x == 0) {
+    if (wait_peers_done) {
+      for (int r = 0; r < p.f_world; ++r)
+        if (r != p.f_rank)
+          while (static_cast<int32_t>(ld_acquire_sys(my_ctrl + FCTRL_B + r) - epoch) < 0) { }
+    }
+    my_ctrl[2] = 0u;
+    my_ctrl[1] = epoch;
+    __threadfence();
+  }
+}
 
 B2_DEVICE float gelu_tanh(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
@@ -81,9 +203,10 @@ B2_DEVICE void decode_tile(const GemmParams& p, int t, int& tm, int& tn, int& ks
   int in_g = r - g * group_sz;
   tm = first_m + in_g % gm;
   tn = in_g / gm;
+  if (p.m_rot) { tm += p.m_rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int FUSE = FUSE_NONE>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
@@ -107,6 +230,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+
+  // fused collectives: the call epoch comes from the buffer's control block (stable at kernel entry)
+  uint32_t f_epoch = 0;
+  int nctas = gridDim.x, cta0 = blockIdx.x;
+  if constexpr (FUSE != FUSE_NONE) {
+    f_epoch = p.f_ctrl[p.f_rank][1] + 1;
+    if constexpr (FUSE == FUSE_AG) {
+      nctas = gridDim.x - p.f_ncomm;
+      cta0 = static_cast<int>(blockIdx.x) - p.f_ncomm;
+      if (cta0 < 0) {                                     // all-gather CTAs (lowest block ids: scheduled first);
+        ag_comm_cta(p, smem, blockIdx.x, f_epoch);         // they never touch TMEM / the MMA pipeline
+        fused_finish(p, f_epoch, true);
+        return;
+      }
+    }
+  }
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -138,12 +277,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+      for (int t = cta0; t < total_tiles; t += nctas) {
         int tm, tn, ks;
         decode_tile(p, t, tm, tn, ks);
         const int m0 = tm * BM, n0 = tn * BN;
         const int kb0 = ks * p.kb_per_split;
         const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+        if constexpr (FUSE == FUSE_AG) {   // rows of this tile must have landed in the gathered operand
+          while (static_cast<int32_t>(ld_acquire_gpu(p.f_flags + tm) - f_epoch) < 0) { }
+          fence_proxy_async_all();
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = stage_base + stage * STAGE_BYTES;
@@ -173,7 +316,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    for (int t = cta0; t < total_tiles; t += nctas, ++it) {
       int tm, tn, ks;
       decode_tile(p, t, tm, tn, ks);
       const int kb0 = ks * p.kb_per_split;
@@ -213,7 +356,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int fmt = p.fmt;
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+    [[maybe_unused]] int rs_groups = 0, rs_prev_owner = -1, rs_prev_blk = 0;   // GEMM->RS: deferred arrival signal
+    for (int t = cta0; t < total_tiles; t += nctas, ++it) {
       int tm, tn, ks;
       decode_tile(p, t, tm, tn, ks);
       const int m0 = tm * BM, n0 = tn * BN;
@@ -338,19 +482,85 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           fence_proxy_async_smem();
           named_bar_sync(1, EPI_THREADS);
           if (leader) {
-            tma_store_2d(&tmC, sb0, col0, m0);
-            if (dual) tma_store_2d(&tmC2, sb1, col0, m0);
+            if constexpr (FUSE == FUSE_RS) {
+              // partial tile -> staging slot [epoch parity][this rank] on the OWNER of these rows (TMA store
+              // through the peer mapping: the NVLink transfer overlaps the following tiles' mainloops)
+              const int owner = tm / p.f_bpr;
+              tma_store_2d(p.f_rsmaps + (f_epoch & 1) * p.f_world + owner, sb0, col0, (tm - owner * p.f_bpr) * BM);
+              ++rs_groups;
+            } else {
+              tma_store_2d(&tmC, sb0, col0, m0);
+              if (dual) tma_store_2d(&tmC2, sb1, col0, m0);
+            }
             tma_store_commit();
+          }
+        }
+        if constexpr (FUSE == FUSE_RS) {
+          if (leader) {
+            // signal the PREVIOUS tile (its stores have certainly landed once only this tile's groups are pending)
+            if (rs_prev_owner >= 0) {
+              if (rs_groups == NCH) tma_store_wait_all<NCH>(); else tma_store_wait_all<0>();
+              __threadfence_system();
+              red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
+            }
+            rs_prev_owner = tm / p.f_bpr;
+            rs_prev_blk = tm - rs_prev_owner * p.f_bpr;
+            rs_groups = 0;
           }
         }
       }
     }
     if (leader) tma_store_wait_all<0>();
+    if constexpr (FUSE == FUSE_RS) {
+      if (leader && rs_prev_owner >= 0) {
+        __threadfence_system();
+        red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
+      }
+      // ---- reduce phase: sum the `world` partials of MY rows (local reads), + bias + residual -> output shard
+      const uint32_t expected = f_epoch * static_cast<uint32_t>(p.f_world * p.tiles_n);
+      const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) +
+                              static_cast<long long>(f_epoch & 1) * p.f_world * p.f_shard_rows * p.N;
+      for (int item = blockIdx.x; item < p.f_bpr * p.tiles_n; item += gridDim.x) {
+        const int lblk = item / p.tiles_n, tn = item - lblk * p.tiles_n;
+        if (leader) {
+          const uint32_t* cnt = p.f_cnt[p.f_rank] + lblk;
+          while (static_cast<int32_t>(ld_acquire_sys(cnt) - expected) < 0) { }
+        }
+        named_bar_sync(1, EPI_THREADS);
+        const int row = lblk * BM + et;
+        if (row < p.f_shard_rows) {
+          for (int j = 0; j < BN / 8; ++j) {
+            const int col = tn * BN + j * 8;
+            if (col >= p.N) break;
+            float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            for (int s = 0; s < p.f_world; ++s) {
+              const uint4 q = *reinterpret_cast<const uint4*>(stage + (static_cast<long long>(s) * p.f_shard_rows + row) * p.N + col);
+              float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+              acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += cc.x; acc[5] += cc.y; acc[6] += d.x; acc[7] += d.y;
+            }
+            if (p.f_bias != nullptr) {
+              const uint4 q = __ldg(reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_bias) + col));
+              float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+              acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += cc.x; acc[5] += cc.y; acc[6] += d.x; acc[7] += d.y;
+            }
+            if (p.f_res != nullptr) {
+              const uint4 q = *reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_res) + static_cast<long long>(row) * p.f_ld_res + col);
+              float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+              acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y; acc[4] += cc.x; acc[5] += cc.y; acc[6] += d.x; acc[7] += d.y;
+            }
+            *reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.f_out) + static_cast<long long>(row) * p.f_ld_out + col) =
+                make_uint4(pack2(acc[0], acc[1], fmt), pack2(acc[2], acc[3], fmt), pack2(acc[4], acc[5], fmt), pack2(acc[6], acc[7], fmt));
+          }
+        }
+      }
+    }
   }
 
   tc_fence_before();
   __syncthreads();
   if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+  if constexpr (FUSE == FUSE_AG) fused_finish(p, f_epoch, true);
+  if constexpr (FUSE == FUSE_RS) fused_finish(p, f_epoch, false);
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -413,7 +623,7 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
       }
     }
   }
-  GemmParams p;
+  GemmParams p{};
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = tiles_m; p.tiles_n = tiles_n;
   p.num_kb = num_kb;
@@ -467,4 +677,153 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   if (bn == 256) B2_DISPATCH(256);
   B2_DISPATCH(128);
 #undef B2_DISPATCH
+}
+
+
+// =============================================================================================
+// Fused compute + collective entry points (tensor / sequence parallelism, ZeRO-3 parameter gather)
+// =============================================================================================
+namespace {
+
+template <int BN, bool B_MN, int FUSE>
+int launch_fused(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
+                 const GemmParams& p, int grid, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<BN, false, B_MN, FUSE>;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 + 256;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { b2host::set_error("fused gemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+    configured = true;
+  }
+  kern<<<grid, NUM_THREADS, smem, stream>>>(tA, tB, tC, tC2, p);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { b2host::set_error("fused gemm launch: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+int make_ab_maps(CUtensorMap* tA, CUtensorMap* tB, const void* A, const void* B, int M, int N, int K, long long lda,
+                 long long ldb, int b_mn, int bn, CUtensorMapDataType dt) {
+  uint64_t dims[2], strides[2]; uint32_t box[2];
+  dims[0] = K; dims[1] = M; box[0] = BK; box[1] = BM; strides[0] = 0; strides[1] = static_cast<uint64_t>(lda) * 2;
+  if (b2host::encode_tmap(tA, dt, 2, A, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = bn; }
+  else       { dims[0] = N; dims[1] = K; box[0] = 64; box[1] = BK; }
+  strides[1] = static_cast<uint64_t>(ldb) * 2;
+  return b2host::encode_tmap(tB, dt, 2, B, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
+}  // namespace
+
+// All-gather -> GEMM in ONE kernel.  Every rank holds a [shard_rows, K] shard of A in symmetric memory
+// (shard_ptrs[r], control blocks ctrls[r]); `n_comm` CTAs pull the shards over NVLink into the local gathered
+// operand xg [world*shard_rows, K] (returned to the caller: backward needs it) while the remaining CTAs run
+// the tcgen05 GEMM tile by tile as soon as the rows of a tile have arrived (own shard first).
+//   C[M, N] = epilogue(xg @ op(B)),  M = world * shard_rows.
+// replaces: NCCL all_gather_into_tensor + cuBLAS GEMM of Megatron's ColumnParallelLinear forward and
+//           RowParallelLinear backward under sequence parallelism, and DeepSpeed's
+//           all_gather_coalesced + GEMM when the gathered operand is a ZeRO-3 weight shard (C19).
+extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg, unsigned int* flags, const void* B, void* C,
+                          int shard_rows, int N, int K, long long ldb, long long ldc, int b_mn_major, int dtype, int epilogue,
+                          const void* bias, const void* aux, long long ld_aux, void* C2, long long ldc2, int rank, int world,
+                          int n_comm, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (world < 2 || world > 8) { b2host::set_error("ag_gemm: world size %d unsupported", world); return -1; }
+  if (shard_rows % BM) { b2host::set_error("ag_gemm: rows per rank (%d) must be a multiple of %d", shard_rows, BM); return -1; }
+  if ((K % 8) || (N % 8) || (ldb % 8) || (ldc % 8)) { b2host::set_error("ag_gemm: K, N and leading dimensions must be multiples of 8"); return -1; }
+  const int M = shard_rows * world;
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const int bn = N > 128 ? 256 : 128;
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
+  p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
+  p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.out_fp32 = 0; p.reduce_add = 0;
+  p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = 1.f;
+  p.f_rank = rank; p.f_world = world; p.f_bpr = shard_rows / BM; p.f_shard_rows = shard_rows;
+  const int sms = b2host::num_sms();
+  if (n_comm <= 0) n_comm = 8;
+  if (n_comm > sms / 4) n_comm = sms / 4;
+  p.f_ncomm = n_comm;
+  p.m_rot = rank * p.f_bpr;
+  p.f_row_bytes = static_cast<long long>(K) * 2;
+  for (int r = 0; r < 8; ++r) { p.f_peer[r] = r < world ? shard_ptrs[r] : nullptr; p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
+  p.f_xg = static_cast<uint8_t*>(xg); p.f_flags = flags;
+  CUtensorMap tA, tB, tC, tC2;
+  if (make_ab_maps(&tA, &tB, xg, B, M, N, K, K, ldb, b_mn_major, bn, dt)) return -1;
+  uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(M)}, strides[2] = {0, static_cast<uint64_t>(ldc) * 2};
+  uint32_t box[2] = {64, BM};
+  if (b2host::encode_tmap(&tC, dt, 2, C, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  tC2 = tC;
+  if (epilogue == B2_EPI_BIAS_GELU_DUAL) {
+    if (C2 == nullptr) { b2host::set_error("ag_gemm: dual epilogue needs C2"); return -1; }
+    strides[1] = static_cast<uint64_t>(ldc2) * 2;
+    if (b2host::encode_tmap(&tC2, dt, 2, C2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  }
+  const int grid = sms;     // one CTA per SM: all-gather CTAs and GEMM CTAs must be co-resident
+  if (bn == 256) return b_mn_major ? launch_fused<256, true, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream)
+                                   : launch_fused<256, false, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream);
+  return b_mn_major ? launch_fused<128, true, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream)
+                    : launch_fused<128, false, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream);
+}
+
+// Builds (host) and uploads (synchronously, once per buffer/shape) the 2*world staging-slot tensor maps of
+// the GEMM->reduce-scatter kernel: map[parity*world + owner] = slot [parity][this rank] of rank `owner`'s
+// staging buffer, viewed as [shard_rows, N].
+extern "C" int b2_make_rs_maps(void* dev_out, void* const* stage_ptrs, int world, int rank, int shard_rows, int N, int dtype) {
+  CUtensorMap maps[16];
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  for (int par = 0; par < 2; ++par)
+    for (int o = 0; o < world; ++o) {
+      uint8_t* base = static_cast<uint8_t*>(stage_ptrs[o]) + (static_cast<long long>(par) * world + rank) * shard_rows * N * 2;
+      uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(shard_rows)}, strides[2] = {0, static_cast<uint64_t>(N) * 2};
+      uint32_t box[2] = {64, BM};
+      if (b2host::encode_tmap(&maps[par * world + o], dt, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+    }
+  cudaError_t e = cudaMemcpy(dev_out, maps, sizeof(CUtensorMap) * 2 * world, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { b2host::set_error("make_rs_maps: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+// GEMM -> reduce-scatter in ONE kernel.  Each rank multiplies its K-slice (partial sums for ALL M rows); the
+// epilogue TMA-stores every partial tile straight into the staging slot of the rank that OWNS those rows
+// (remote rows first, so NVLink traffic overlaps the remaining tiles), bumps an arrival counter there, and the
+// same kernel then folds the `world` partials of its own rows with bias and residual into the output shard.
+//   out[shard_rows, N] = residual + bias + sum_ranks (A_r @ op(B_r))[rows of this rank]
+// replaces: cuBLAS GEMM + NCCL reduce_scatter_tensor (+ bias-dropout-add) of RowParallelLinear forward and
+//           ColumnParallelLinear backward under sequence parallelism.
+extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
+                          int dtype, void* const* cnt_ptrs, void* const* ctrls, const void* rsmaps_dev, const void* stage_local,
+                          void* out, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
+                          int world, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (world < 2 || world > 8) { b2host::set_error("gemm_rs: world size %d unsupported", world); return -1; }
+  if (M % (world * BM)) { b2host::set_error("gemm_rs: M (%d) must be a multiple of world * %d", M, BM); return -1; }
+  if ((K % 8) || (N % 8) || (lda % 8) || (ldb % 8) || (ld_out % 8) || (residual && (ld_res % 8))) {
+    b2host::set_error("gemm_rs: K, N and leading dimensions must be multiples of 8"); return -1;
+  }
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const int bn = N > 128 ? 256 : 128;
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
+  p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
+  p.epilogue = B2_EPI_NONE; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.alpha = 1.f;
+  p.f_rank = rank; p.f_world = world; p.f_shard_rows = M / world; p.f_bpr = p.f_shard_rows / BM; p.f_ncomm = 0;
+  p.m_rot = ((rank + 1) % world) * p.f_bpr;
+  for (int r = 0; r < 8; ++r) {
+    p.f_cnt[r] = r < world ? static_cast<uint32_t*>(cnt_ptrs[r]) : nullptr;
+    p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr;
+  }
+  p.f_rsmaps = static_cast<const CUtensorMap*>(rsmaps_dev);
+  p.f_stage = stage_local; p.f_out = out; p.f_ld_out = ld_out; p.f_bias = bias; p.f_res = residual; p.f_ld_res = ld_res;
+  CUtensorMap tA, tB;
+  if (make_ab_maps(&tA, &tB, A, B, M, N, K, lda, ldb, b_mn_major, bn, dt)) return -1;
+  const int sms = b2host::num_sms();
+  const int total = p.tiles_m * p.tiles_n;
+  const int grid = total < sms ? total : sms;
+  if (bn == 256) return b_mn_major ? launch_fused<256, true, FUSE_RS>(tA, tB, tA, tA, p, grid, stream)
+                                   : launch_fused<256, false, FUSE_RS>(tA, tB, tA, tA, p, grid, stream);
+  return b_mn_major ? launch_fused<128, true, FUSE_RS>(tA, tB, tA, tA, p, grid, stream)
+                    : launch_fused<128, false, FUSE_RS>(tA, tB, tA, tA, p, grid, stream);
 }

@@ -153,6 +153,22 @@ int b2_ctrl_words(void);
 int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
                  int rank, int world, int max_ctas, void* stream);
 
+/* Fused compute + collective kernels (csrc/gemm.cu).  A operand is [rows, K] row-major; B as in b2_gemm.
+ *  b2_ag_gemm : all-gather(A shards over the group) -> GEMM, one kernel; xg receives the gathered A.
+ *  b2_gemm_rs : GEMM -> reduce-scatter(+bias+residual), one kernel; b2_make_rs_maps prepares its staging maps.
+ * replaces: NCCL all-gather / reduce-scatter around cuBLAS GEMMs in Megatron's Column/RowParallelLinear with
+ *           sequence parallelism and DeepSpeed ZeRO-3 parameter gathers (C19).
+ */
+int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg, unsigned int* flags, const void* B, void* C,
+               int shard_rows, int N, int K, long long ldb, long long ldc, int b_mn_major, int dtype, int epilogue,
+               const void* bias, const void* aux, long long ld_aux, void* C2, long long ldc2, int rank, int world,
+               int n_comm, void* stream);
+int b2_make_rs_maps(void* dev_out, void* const* stage_ptrs, int world, int rank, int shard_rows, int N, int dtype);
+int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major, int dtype,
+               void* const* cnt_ptrs, void* const* ctrls, const void* rsmaps_dev, const void* stage_local, void* out,
+               long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world,
+               void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Flash attention (tcgen05), bf16, head_dim 64 or 128 forward / 64 backward.  Strides are in
  * elements for (seq, batch, head); head_dim is contiguous.  lse: fp32 [batch, heads, seqlen].

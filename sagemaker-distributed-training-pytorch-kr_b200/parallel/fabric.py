@@ -65,6 +65,13 @@ class Fabric:
             L = N.lib()
             L.b2_allreduce.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p]
             L.b2_allreduce.restype = c_i
+            L.b2_ag_gemm.argtypes = [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_i, c_p, c_p, c_ll, c_p, c_ll, c_i, c_i, c_i, c_p]
+            L.b2_ag_gemm.restype = c_i
+            L.b2_make_rs_maps.argtypes = [c_p, c_p, c_i, c_i, c_i, c_i, c_i]
+            L.b2_make_rs_maps.restype = c_i
+            L.b2_gemm_rs.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
+            L.b2_gemm_rs.restype = c_i
+            self._ag, self._rs = {}, {}
             probe = SymmBuffer(self, 1024, torch.float32)
             probe.tensor.fill_(float(self.rank + 1))
             self.all_reduce_(probe, scale=1.0)
@@ -90,6 +97,70 @@ class Fabric:
         n_pad = (n * esz + 15) // 16 * 16 // esz       # payload is 256-byte padded, so rounding up is safe
         N._call("b2_allreduce", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n_pad, N._dt(buf.tensor),
                 float(scale), self.rank, self.world, max_ctas, N._st())
+
+
+    # ------------------------------------------------------------------ all-gather -> GEMM
+    def _ag_state(self, rows: int, K: int, dtype):
+        key = (rows, K, dtype)
+        st = self._ag.get(key)
+        if st is None:
+            symm = self.alloc(rows * K, dtype)
+            flags = torch.zeros(self.world * (rows // 128), dtype=torch.int32, device=symm.tensor.device)
+            st = self._ag[key] = {"symm": symm, "flags": flags}
+        return st
+
+    def shard_buffer(self, rows: int, K: int, dtype) -> torch.Tensor:
+        """[rows, K] view of the symmetric shard buffer: a producer (e.g. LayerNorm) that writes here saves the
+        staging copy in ag_gemm."""
+        return self._ag_state(rows, K, dtype)["symm"].tensor.view(rows, K)
+
+    def ag_gemm(self, x2: torch.Tensor, W: torch.Tensor, b_mn: bool = False, bias=None, epilogue: int = N.EPI_NONE, aux=None,
+                out2=None, n_comm: int = 0):
+        """y = epilogue(all_gather_rows(x2) @ op(W)); returns (y [world*rows, N], x_full [world*rows, K])."""
+        rows, K = x2.shape
+        if rows % 128:
+            raise ValueError(f"ag_gemm: rows per rank ({rows}) must be a multiple of 128")
+        st = self._ag_state(rows, K, x2.dtype)
+        shard = st["symm"].tensor.view(rows, K)
+        if x2.data_ptr() != shard.data_ptr():
+            shard.copy_(x2)
+        Nn = W.shape[1] if b_mn else W.shape[0]
+        M = rows * self.world
+        xg = torch.empty((M, K), dtype=x2.dtype, device=x2.device)
+        out = torch.empty((M, Nn), dtype=x2.dtype, device=x2.device)
+        N._call("b2_ag_gemm", st["symm"].ptrs, st["symm"].ctrls, N._p(xg), N._p(st["flags"]), N._p(W), N._p(out), rows, Nn, K,
+                W.stride(0), out.stride(0), int(b_mn), N._dt(x2), epilogue, N._p(bias), N._p(aux),
+                aux.stride(0) if aux is not None else 0, N._p(out2), out2.stride(0) if out2 is not None else 0,
+                self.rank, self.world, n_comm, N._st())
+        return out, xg
+
+    # ------------------------------------------------------------------ GEMM -> reduce-scatter
+    def _rs_state(self, rows: int, Nn: int, dtype):
+        key = (rows, Nn, dtype)
+        st = self._rs.get(key)
+        if st is None:
+            stage = self.alloc(2 * self.world * rows * Nn, dtype)
+            cnt = self.alloc(max(rows // 128, 1), torch.int32)
+            maps = torch.empty(2 * self.world * 128, dtype=torch.uint8, device=stage.tensor.device)
+            rc = N.lib().b2_make_rs_maps(N._p(maps), stage.ptrs, self.world, self.rank, rows, Nn, N._dt(stage.tensor))
+            if rc != 0:
+                raise RuntimeError("b2_make_rs_maps: " + N.lib().b2_last_error().decode())
+            st = self._rs[key] = {"stage": stage, "cnt": cnt, "maps": maps}
+        return st
+
+    def gemm_rs(self, a2: torch.Tensor, W: torch.Tensor, b_mn: bool = False, bias=None, residual=None):
+        """out[rows, N] = residual + bias + reduce_scatter_rows(a2 @ op(W)) in one kernel."""
+        M, K = a2.shape
+        if M % (128 * self.world):
+            raise ValueError(f"gemm_rs: M ({M}) must be a multiple of 128 * world")
+        rows = M // self.world
+        Nn = W.shape[1] if b_mn else W.shape[0]
+        st = self._rs_state(rows, Nn, a2.dtype)
+        out = torch.empty((rows, Nn), dtype=a2.dtype, device=a2.device)
+        N._call("b2_gemm_rs", N._p(a2), N._p(W), M, Nn, K, a2.stride(0), W.stride(0), int(b_mn), N._dt(a2), st["cnt"].ptrs,
+                st["stage"].ctrls, N._p(st["maps"]), N._p(st["stage"].tensor), N._p(out), out.stride(0), N._p(bias),
+                N._p(residual), residual.stride(0) if residual is not None else 0, self.rank, self.world, N._st())
+        return out
 
 
 def get_fabric(group=None) -> Fabric:
