@@ -44,6 +44,30 @@ def timeit(fn, iters=20, warm=3):
     return t.item()
 
 
+def graph_time(fn, reps=10, iters=5):
+    """GPU time per call with launch overhead removed: `reps` calls captured in one CUDA graph, replayed `iters` times."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        fn(); fn()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize(); dist.barrier()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    torch.cuda.synchronize(); dist.barrier()
+    g.replay(); torch.cuda.synchronize(); dist.barrier()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(iters):
+        g.replay()
+    b.record(); torch.cuda.synchronize()
+    t = torch.tensor([a.elapsed_time(b) / (iters * reps)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
 F = fb.get_fabric(dist.group.WORLD)
 p0("fabric usable:", F.usable, "error:", F.error)
 if not F.usable:
@@ -101,7 +125,15 @@ if which in ("all", "ag"):
     ms = timeit(lambda: F.ag_gemm(x, W))
     ms_n = timeit(lambda: (dist.all_gather_into_tensor(xf, x), N.gemm(xf, W)))
     ms_g = timeit(lambda: N.gemm(xf, W))
-    p0(f"time ag_gemm rows/rank {rows} K{K} N{Nn}: fused {ms:.3f} ms | nccl all_gather + gemm {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms")
+    p0(f"time ag_gemm rows/rank {rows} K{K} N{Nn}: fused {ms:.3f} ms | nccl all_gather + gemm {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms (host-issue bound)")
+    for (rows, K, Nn, tag) in [(6144, 768, 1152, "qkv"), (6144, 768, 1536, "fc1"), (6144, 768, 16384, "logits")]:
+        x = F.shard_buffer(rows, K, torch.bfloat16); x.normal_()
+        W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+        xf = torch.randn(rows * world, K, device=dev, dtype=torch.bfloat16)
+        gf = graph_time(lambda: F.ag_gemm(x, W))
+        gg = graph_time(lambda: N.gemm(xf, W))
+        roof = max(2.0 * rows * world * Nn * K / 1.39e15, rows * K * 2 * (world - 1) / 770e9) * 1e3
+        p0(f"graph-timed ag_gemm {tag:7s} rows/rank {rows} K{K} N{Nn}: fused {gf*1e3:7.1f} us | plain gemm on gathered input {gg*1e3:7.1f} us | roofline {roof*1e3:6.1f} us -> {roof/gf:.2f} of roofline")
 
 if which in ("all", "rs"):
     for (M, K, Nn, bmn) in [(512, 128, 256, False), (2048, 384, 768, False), (12288, 1536, 768, False), (2048, 576, 768, True)]:
@@ -128,7 +160,13 @@ if which in ("all", "rs"):
     ms = timeit(lambda: F.gemm_rs(a, W))
     ms_n = timeit(lambda: dist.reduce_scatter_tensor(o, N.gemm(a, W)))
     ms_g = timeit(lambda: N.gemm(a, W))
-    p0(f"time gemm_rs M{M} K{K} N{Nn}: fused {ms:.3f} ms | gemm + nccl reduce_scatter {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms")
+    p0(f"time gemm_rs M{M} K{K} N{Nn}: fused {ms:.3f} ms | gemm + nccl reduce_scatter {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms (host-issue bound)")
+    for (M, K, Nn, tag) in [(12288, 384, 768, "proj"), (12288, 1536, 768, "fc2")]:
+        a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+        gf = graph_time(lambda: F.gemm_rs(a, W))
+        gg = graph_time(lambda: N.gemm(a, W))
+        roof = max(2.0 * M * Nn * K / 1.39e15, M * Nn * 2 * (world - 1) / world / 770e9) * 1e3
+        p0(f"graph-timed gemm_rs {tag:5s} M{M} K{K} N{Nn}: fused {gf*1e3:7.1f} us | plain gemm {gg*1e3:7.1f} us | roofline {roof*1e3:6.1f} us -> {roof/gf:.2f} of roofline")
 
 p0("FAILED:" if FAILS else "ALL OK", FAILS)
 dist.barrier()

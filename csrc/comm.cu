@@ -72,9 +72,11 @@ B2_DEVICE uint32_t enter(const Peers& P, int rank, int world, uint32_t* my_ctrl)
   return epoch;
 }
 
-template <typename T, bool MULTICAST>
+// MODE 0: all-reduce in place.  MODE 1: reduce-scatter (rank r's reduced slice -> local `out`, payload untouched).
+// MODE 2: all-gather (rank r's slice of the payload is broadcast into every rank's payload; no arithmetic).
+template <typename T, bool MULTICAST, int MODE>
 __global__ void __launch_bounds__(512)
-allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int rank, int world) {
+allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int rank, int world, void* out) {
   uint32_t* my_ctrl = P.ctrl[rank];
   const uint32_t epoch = enter(P, rank, world, my_ctrl);
   // my slice, in 16-byte vectors
@@ -84,9 +86,27 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
   const long long v0 = per * rank, v1 = min(nvec, v0 + per);
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
   for (long long v = v0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < v1; v += stride) {
-    if constexpr (MULTICAST) {
+    if constexpr (MODE == 2) {
+      const uint4 q = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(P.ptr[rank]) + v * 16);
+      if constexpr (MULTICAST) {
+        mm_st_b32x4(static_cast<uint8_t*>(mc_base) + v * 16, q.x, q.y, q.z, q.w);
+      } else {
+        for (int r = 0; r < world; ++r)
+          if (r != rank) *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[r]) + v * 16) = q;
+      }
+    } else if constexpr (MULTICAST) {
       uint8_t* mc = static_cast<uint8_t*>(mc_base) + v * 16;
-      if constexpr (sizeof(T) == 4) {
+      if constexpr (MODE == 1) {
+        uint4 o;
+        if constexpr (sizeof(T) == 4) {
+          float a, b, c, d;
+          mm_ld_reduce_f32x4(mc, a, b, c, d);
+          o = make_uint4(__float_as_uint(a * scale), __float_as_uint(b * scale), __float_as_uint(c * scale), __float_as_uint(d * scale));
+        } else {
+          mm_ld_reduce_bf16x8(mc, o.x, o.y, o.z, o.w);
+        }
+        *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v - v0) * 16) = o;
+      } else if constexpr (sizeof(T) == 4) {
         float a, b, c, d;
         mm_ld_reduce_f32x4(mc, a, b, c, d);
         mm_st_f32x4(mc, a * scale, b * scale, c * scale, d * scale);
@@ -125,8 +145,12 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
         o = make_uint4(pack_bf16x2(acc[0] * scale, acc[1] * scale), pack_bf16x2(acc[2] * scale, acc[3] * scale),
                        pack_bf16x2(acc[4] * scale, acc[5] * scale), pack_bf16x2(acc[6] * scale, acc[7] * scale));
       }
-      for (int r = 0; r < world; ++r)
-        *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[r]) + v * 16) = o;
+      if constexpr (MODE == 1) {
+        *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v - v0) * 16) = o;
+      } else {
+        for (int r = 0; r < world; ++r)
+          *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[r]) + v * 16) = o;
+      }
     }
   }
   // all CTAs of this grid done -> one cross-GPU barrier -> result complete everywhere
@@ -160,13 +184,12 @@ extern "C" int b2_ctrl_words(void) { return B2_CTRL_WORDS; }
 
 // ptrs / ctrls: `world` peer-mapped addresses each (host arrays).  mc_ptr: multicast address of the payload or NULL.
 // n_elems * sizeof(dtype) must be a multiple of 16.  In place on every rank's payload.
-extern "C" int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
-                            int rank, int world, int max_ctas, void* stream) {
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (world < 1 || world > MAX_RANKS) { b2host::set_error("allreduce: world size %d unsupported (max %d)", world, MAX_RANKS); return -1; }
+static int run_collective(int mode, void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                          int rank, int world, int max_ctas, void* out, cudaStream_t st) {
+  if (world < 1 || world > MAX_RANKS) { b2host::set_error("collective: world size %d unsupported (max %d)", world, MAX_RANKS); return -1; }
   const int esz = dtype == B2_DTYPE_FP32 ? 4 : 2;
-  if (dtype == B2_DTYPE_FP16) { b2host::set_error("allreduce: fp16 payloads are not supported (use bf16 or fp32)"); return -1; }
-  if ((n_elems * esz) % 16) { b2host::set_error("allreduce: payload must be a multiple of 16 bytes"); return -1; }
+  if (dtype == B2_DTYPE_FP16 && mode != 2) { b2host::set_error("collective: fp16 reductions are not supported (use bf16 or fp32)"); return -1; }
+  if ((n_elems * esz) % (16LL * world)) { b2host::set_error("collective: payload must be a multiple of 16 bytes per rank"); return -1; }
   Peers P;
   for (int r = 0; r < MAX_RANKS; ++r) { P.ptr[r] = r < world ? ptrs[r] : nullptr; P.ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
   long long nvec = n_elems * esz / 16;
@@ -175,12 +198,26 @@ extern "C" int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr,
   long long want = (per + threads - 1) / threads;
   int cap = max_ctas > 0 ? max_ctas : 64;
   int grid = static_cast<int>(want < 1 ? 1 : (want > cap ? cap : want));
-  if (mc_ptr != nullptr) {
-    if (dtype == B2_DTYPE_FP32) allreduce_kernel<float, true><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world);
-    else allreduce_kernel<__nv_bfloat16, true><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world);
-  } else {
-    if (dtype == B2_DTYPE_FP32) allreduce_kernel<float, false><<<grid, threads, 0, st>>>(P, nullptr, n_elems, scale, rank, world);
-    else allreduce_kernel<__nv_bfloat16, false><<<grid, threads, 0, st>>>(P, nullptr, n_elems, scale, rank, world);
-  }
-  return check("allreduce");
+#define B2_LAUNCH(T_, MC_, MODE_) allreduce_kernel<T_, MC_, MODE_><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world, out)
+#define B2_BY_MODE(T_, MC_) do { if (mode == 0) B2_LAUNCH(T_, MC_, 0); else if (mode == 1) B2_LAUNCH(T_, MC_, 1); else B2_LAUNCH(T_, MC_, 2); } while (0)
+  if (mc_ptr != nullptr) { if (esz == 4) B2_BY_MODE(float, true); else B2_BY_MODE(__nv_bfloat16, true); }
+  else                   { if (esz == 4) B2_BY_MODE(float, false); else B2_BY_MODE(__nv_bfloat16, false); }
+#undef B2_BY_MODE
+#undef B2_LAUNCH
+  return check("collective");
+}
+
+extern "C" int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                            int rank, int world, int max_ctas, void* stream) {
+  return run_collective(0, ptrs, ctrls, mc_ptr, n_elems, dtype, scale, rank, world, max_ctas, nullptr, static_cast<cudaStream_t>(stream));
+}
+// out (local, n_elems / world elements) = scale * sum over ranks of slice `rank` of the symmetric payload
+extern "C" int b2_reduce_scatter(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                                 int rank, int world, int max_ctas, void* out, void* stream) {
+  return run_collective(1, ptrs, ctrls, mc_ptr, n_elems, dtype, scale, rank, world, max_ctas, out, static_cast<cudaStream_t>(stream));
+}
+// every rank's slice `r` of the symmetric payload (n_elems total) is replicated into all ranks' payloads
+extern "C" int b2_allgather(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
+                            int max_ctas, void* stream) {
+  return run_collective(2, ptrs, ctrls, mc_ptr, n_elems, dtype, 1.f, rank, world, max_ctas, nullptr, static_cast<cudaStream_t>(stream));
 }

@@ -62,7 +62,8 @@ def loss_func(loss_mask, output_tensor):
     loss = torch.sum(losses.view(-1) * loss_mask) / loss_mask.sum()
     # data-parallel average for logging (reference :98); kept on the device, read only at log time
     averaged = loss.detach().clone()
-    if torch.distributed.is_initialized() and mpu.get_data_parallel_world_size() > 1:
+    if (torch.distributed.is_initialized() and mpu.get_data_parallel_world_size() > 1
+            and not getattr(get_args(), "_static_batch", False)):      # CUDA-graph mode averages once per step outside the graph
         torch.distributed.all_reduce(averaged, group=mpu.get_data_parallel_group())
         averaged = averaged / mpu.get_data_parallel_world_size()
     return loss, {"lm loss": averaged}

@@ -152,6 +152,12 @@ int b2_embedding_bwd(const void* dy, const long long* tok, const long long* pos,
 int b2_ctrl_words(void);
 int b2_allreduce(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
                  int rank, int world, int max_ctas, void* stream);
+/* out (local, n_elems/world) = scale * sum over ranks of slice `rank` of the symmetric payload (payload unchanged) */
+int b2_reduce_scatter(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
+                      int rank, int world, int max_ctas, void* out, void* stream);
+/* slice r of rank r's payload is replicated into every rank's payload (multimem.st broadcast / peer stores) */
+int b2_allgather(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
+                 int max_ctas, void* stream);
 
 /* Fused compute + collective kernels (csrc/gemm.cu).  A operand is [rows, K] row-major; B as in b2_gemm.
  *  b2_ag_gemm : all-gather(A shards over the group) -> GEMM, one kernel; xg receives the gathered A.

@@ -33,9 +33,15 @@ class _StaticIter:
         return self.batch
 
 
-def supported(args) -> bool:
-    return (torch.cuda.is_available() and args.pipeline_model_parallel_size == 1 and args.hidden_dropout == 0.0
-            and args.attention_dropout == 0.0 and not args.fp16 and args.recompute_granularity is None)
+def supported(args, model=None) -> bool:
+    ok = (torch.cuda.is_available() and args.pipeline_model_parallel_size == 1 and args.hidden_dropout == 0.0
+          and args.attention_dropout == 0.0 and not args.fp16 and args.recompute_granularity is None)
+    if ok and args.tensor_model_parallel_size > 1:
+        # tensor-parallel collectives inside the captured region must be the fabric kernels (plain launches);
+        # NCCL calls are kept out of captured graphs
+        comm = getattr(model, "comm", None)
+        ok = comm is not None and comm.fabric is not None and comm.sp
+    return ok
 
 
 class GraphedMicrobatch:
@@ -89,4 +95,10 @@ class GraphedMicrobatch:
         for _ in range(self.M):
             self.load_tokens(data_iterator)
             self.graph.replay()
-        return [{k: v.clone() for k, v in self.loss_acc.items()}]
+        out = {k: v.clone() for k, v in self.loss_acc.items()}
+        dp = mpu.get_data_parallel_world_size()
+        if dp > 1:     # data-parallel average of the logged loss: once per step, outside the captured region
+            for v in out.values():
+                dist.all_reduce(v, group=mpu.get_data_parallel_group())
+                v.div_(dp)
+        return [out]

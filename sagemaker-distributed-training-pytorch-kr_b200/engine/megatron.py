@@ -251,8 +251,8 @@ def get_graph_runner(forward_step_func, model):
         return _GRAPH["runner"]
     _GRAPH["tried"] = True
     from . import graphed
-    if not graphed.supported(args) or len(model) != 1:
-        print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, dropout 0, bf16/fp32, no recompute): running eagerly")
+    if len(model) != 1 or not graphed.supported(args, model[0]):
+        print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, dropout 0, bf16/fp32, no recompute, fabric collectives for TP): running eagerly")
         return None
     nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
     dev = torch.device("cuda", torch.cuda.current_device())

@@ -292,13 +292,7 @@ class _LMHeadLossFn(torch.autograd.Function):
         T, V = logits.shape
         lab = labels.t().contiguous().view(-1)
         m, s, t = N.xent_stats(logits, lab, model.vocab_start)
-        if comm.size > 1:
-            gm = m.clone()
-            tp_ops.all_reduce(gm, comm.group, op=torch.distributed.ReduceOp.MAX)
-            s = s * torch.exp(m - gm)
-            st = torch.stack([s, t])
-            tp_ops.all_reduce(st, comm.group)
-            s, t, m = st[0].contiguous(), st[1].contiguous(), gm
+        m, s, t = comm.combine_xent_stats(m, s, t)
         loss = N.xent_finish(m, s, t, lab, model.ignore_index)
         ctx.save_for_backward(logits, h_full, lab, m, s, wte)
         ctx.model, ctx.params, ctx.dims = model, (wte,), (T // B, B)

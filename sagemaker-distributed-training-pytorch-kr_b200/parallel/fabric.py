@@ -71,7 +71,11 @@ class Fabric:
             L.b2_make_rs_maps.restype = c_i
             L.b2_gemm_rs.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
             L.b2_gemm_rs.restype = c_i
-            self._ag, self._rs = {}, {}
+            L.b2_reduce_scatter.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p, c_p]
+            L.b2_reduce_scatter.restype = c_i
+            L.b2_allgather.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_p]
+            L.b2_allgather.restype = c_i
+            self._ag, self._rs, self._coll = {}, {}, {}
             probe = SymmBuffer(self, 1024, torch.float32)
             probe.tensor.fill_(float(self.rank + 1))
             self.all_reduce_(probe, scale=1.0)
@@ -98,6 +102,32 @@ class Fabric:
         N._call("b2_allreduce", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n_pad, N._dt(buf.tensor),
                 float(scale), self.rank, self.world, max_ctas, N._st())
 
+
+    # ------------------------------------------------------------------ standalone row collectives
+    def _coll_buf(self, numel: int, dtype, tag: str) -> SymmBuffer:
+        key = (numel, dtype, tag)
+        if key not in self._coll:
+            self._coll[key] = self.alloc(numel, dtype)
+        return self._coll[key]
+
+    def reduce_scatter_rows(self, x2: torch.Tensor) -> torch.Tensor:
+        """[world*rows, C] partial sums on every rank -> [rows, C] reduced shard (multimem.ld_reduce of my slice)."""
+        n = x2.numel()
+        buf = self._coll_buf(n, x2.dtype, "rs")
+        buf.tensor.view_as(x2).copy_(x2)
+        out = torch.empty((x2.shape[0] // self.world,) + tuple(x2.shape[1:]), dtype=x2.dtype, device=x2.device)
+        N._call("b2_reduce_scatter", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n, N._dt(x2), 1.0, self.rank,
+                self.world, 0, N._p(out), N._st())
+        return out
+
+    def all_gather_rows(self, x2: torch.Tensor) -> torch.Tensor:
+        """[rows, C] shard -> [world*rows, C] (multimem.st broadcast).  Returns a private copy."""
+        n = x2.numel() * self.world
+        buf = self._coll_buf(n, x2.dtype, "ag")
+        full = buf.tensor.view((x2.shape[0] * self.world,) + tuple(x2.shape[1:]))
+        full[self.rank * x2.shape[0]:(self.rank + 1) * x2.shape[0]].copy_(x2)
+        N._call("b2_allgather", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n, N._dt(x2), self.rank, self.world, 0, N._st())
+        return full.clone()
 
     # ------------------------------------------------------------------ all-gather -> GEMM
     def _ag_state(self, rows: int, K: int, dtype):

@@ -125,10 +125,32 @@ class TPComm:
         return da, dy_full
 
     def gather_seq(self, x):
-        return all_gather_first_dim(x, self.group) if self.sp else x
+        if not self.sp:
+            return x
+        if self.fabric is not None and (x.numel() * x.element_size()) % 16 == 0:
+            return self.fabric.all_gather_rows(x)
+        return all_gather_first_dim(x, self.group)
 
     def reduce_scatter_seq(self, x):
+        if self.sp and self.fabric is not None and (x.numel() * x.element_size()) % (16 * self.size) == 0:
+            return self.fabric.reduce_scatter_rows(x)
         return reduce_scatter_first_dim(x, self.group) if self.sp else all_reduce(x, self.group)
+
+    def combine_xent_stats(self, m, s, t):
+        """per-rank (row max, sum-exp relative to it, target logit) of a vocab shard -> global (max, sum-exp, target).
+        One exchange of 3 scalars per row instead of Megatron's three all-reduces over [s, b]."""
+        if self.size == 1:
+            return m, s, t
+        if self.fabric is not None and (m.numel() * 4) % 16 == 0:
+            allst = self.fabric.all_gather_rows(torch.stack([m, s, t]).unsqueeze(0)).view(self.size, 3, -1)
+            gm = allst[:, 0].max(0).values
+            gs = (allst[:, 1] * torch.exp(allst[:, 0] - gm)).sum(0)
+            return gm, gs, allst[:, 2].sum(0)
+        gm = m.clone()
+        all_reduce(gm, self.group, op=dist.ReduceOp.MAX)
+        st = torch.stack([s * torch.exp(m - gm), t])
+        all_reduce(st, self.group)
+        return gm, st[0].contiguous(), st[1].contiguous()
 
 
 # ------------------------------------------------------------------------------------------
