@@ -1,0 +1,291 @@
+"""Autograd-level ops on top of the native kernels (ops/native.py).
+
+These are the building blocks for the models that are not hand-scheduled per layer (Swin-B, OPT, LLaMA, the
+MNIST head): each Function's forward AND backward call the sm_100a kernels on CUDA tensors and the fp32 PyTorch
+restatement on CPU tensors.  Weight gradients are accumulated straight into ``param.main_grad`` (fp32) when the
+parameter has one - the same contract as the GPT layer - otherwise returned to autograd.
+"""
+from __future__ import annotations
+
+import math
+from typing import Optional
+
+import torch
+
+from . import native as N
+
+
+def _lowp(t: torch.Tensor) -> bool:
+    return t.dtype in (torch.bfloat16, torch.float16)
+
+
+def _wgrad(param, dy2, x2):
+    mg = getattr(param, "main_grad", None)
+    if mg is not None:
+        N.gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
+        return None
+    out = torch.zeros(param.shape, dtype=torch.float32, device=param.device)
+    N.gemm(dy2, x2, a_mn=True, b_mn=True, out=out, accumulate=True)
+    return out.to(param.dtype)
+
+
+def _bgrad(param, dy2):
+    if param is None:
+        return None
+    mg = getattr(param, "main_grad", None)
+    acc = mg if mg is not None else torch.zeros(param.shape, dtype=torch.float32, device=param.device)
+    N.colsum_accum(dy2, acc)
+    return None if mg is not None else acc.to(param.dtype)
+
+
+def _vgrad(param, g32):
+    if param is None:
+        return None
+    mg = getattr(param, "main_grad", None)
+    if mg is not None:
+        mg.add_(g32)
+        return None
+    return g32.to(param.dtype)
+
+
+class _Linear(torch.autograd.Function):
+    """y = act(x W^T + b) (+ residual).  act in {None, 'gelu_tanh'}; bias / activation / residual ride in the GEMM epilogue."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, residual, act):
+        shp = x.shape
+        x2 = x.reshape(-1, shp[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        z = None
+        if act == "gelu_tanh":
+            z = torch.empty((x2.shape[0], w.shape[0]), dtype=x.dtype, device=x.device)
+            y = N.gemm(x2, w, bias=b, epilogue=N.EPI_BIAS_GELU_DUAL, out2=z)
+        elif residual is not None:
+            y = N.gemm(x2, w, bias=b, aux=residual.reshape(-1, w.shape[0]), epilogue=N.EPI_BIAS_RESIDUAL)
+        else:
+            y = N.gemm(x2, w, bias=b, epilogue=N.EPI_BIAS if b is not None else N.EPI_NONE)
+        ctx.save_for_backward(x2, w, z)
+        ctx.params, ctx.shp, ctx.has_res, ctx.act = (w, b), shp, residual is not None, act
+        return y.view(*shp[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, z = ctx.saved_tensors
+        wp, bp = ctx.params
+        dy2 = dy.reshape(-1, w.shape[0])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        d_res = dy if ctx.has_res else None
+        if ctx.act == "gelu_tanh":
+            dy2 = N.bias_act_bwd(dy2, z, None, N.ACT_GELU_TANH)      # z already holds x W^T + b
+        gb = _bgrad(bp, dy2)
+        gw = _wgrad(wp, dy2, x2) if wp.requires_grad else None
+        dx = N.gemm(dy2, w, b_mn=True).view(ctx.shp) if ctx.needs_input_grad[0] else None
+        return dx, gw, gb, d_res, None
+
+
+def linear(x, weight, bias=None, residual=None, act: Optional[str] = None):
+    """Low-precision (bf16/fp16) inputs run the tcgen05 GEMM; fp32 inputs (MNIST / fp32 parity runs) use torch."""
+    if not _lowp(x) or x.shape[-1] % 8 or weight.shape[0] % 8:
+        y = torch.nn.functional.linear(x, weight, bias)
+        if act == "gelu_tanh":
+            y = torch.nn.functional.gelu(y, approximate="tanh")
+        return y + residual if residual is not None else y
+    return _Linear.apply(x, weight, bias, residual, act)
+
+
+class _Norm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, eps, rms):
+        xc = x.contiguous()
+        y, mean, rstd = N.norm_fwd(xc, w, b, eps, rms)
+        ctx.save_for_backward(xc, w, mean if mean is not None else rstd, rstd)
+        ctx.params, ctx.rms = (w, b), rms
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, mean, rstd = ctx.saved_tensors
+        dx, dg, db = N.norm_bwd(dy.contiguous(), x, w, None if ctx.rms else mean, rstd, ctx.rms)
+        return dx, _vgrad(ctx.params[0], dg), (_vgrad(ctx.params[1], db) if ctx.params[1] is not None else None), None, None
+
+
+def layer_norm(x, weight, bias, eps: float = 1e-5):
+    if not _lowp(x) or x.shape[-1] % 8:
+        return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)
+    return _Norm.apply(x, weight, bias, eps, False)
+
+
+def rms_norm(x, weight, eps: float = 1e-6):
+    if not _lowp(x) or x.shape[-1] % 8:
+        xf = x.float()
+        return (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps) * weight.float()).to(x.dtype)
+    return _Norm.apply(x, weight, None, eps, True)
+
+
+class _BiasAct(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, b, mode):
+        xc = x.contiguous()
+        ctx.save_for_backward(xc, b)
+        ctx.mode, ctx.bparam = mode, b
+        return N.bias_act_fwd(xc, b, mode)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, b = ctx.saved_tensors
+        dx = N.bias_act_bwd(dy.contiguous(), x, b, ctx.mode)
+        gb = _bgrad(ctx.bparam, dx.reshape(-1, dx.shape[-1])) if b is not None else None
+        return dx, gb, None
+
+
+def bias_act(x, bias, mode: int):
+    """mode: N.ACT_GELU_TANH / ACT_GELU_ERF / ACT_RELU / ACT_SILU"""
+    if not _lowp(x) or x.shape[-1] % 8:
+        z = x + bias if bias is not None else x
+        F = torch.nn.functional
+        return [lambda t: F.gelu(t, approximate="tanh"), F.gelu, F.relu, F.silu][mode](z)
+    return _BiasAct.apply(x, bias, mode)
+
+
+class _SwiGLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, gu):
+        guc = gu.contiguous()
+        ctx.save_for_backward(guc)
+        return N.swiglu_fwd(guc)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (gu,) = ctx.saved_tensors
+        return N.swiglu_bwd(dy.contiguous(), gu)
+
+
+def swiglu(gate_up):
+    """silu(gate) * up on a fused [..., 2F] projection (gate first)."""
+    if not _lowp(gate_up) or (gate_up.shape[-1] // 2) % 8:
+        F_ = gate_up.shape[-1] // 2
+        return torch.nn.functional.silu(gate_up[..., :F_]) * gate_up[..., F_:]
+    return _SwiGLU.apply(gate_up)
+
+
+class _Attention(torch.autograd.Function):
+    """q, k, v: [S, B, H, D] views (D contiguous) -> o [S, B, H, D].  tcgen05 flash attention fwd/bwd."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, scale, causal):
+        o, lse = N.attn_fwd(q, k, v, scale, causal)
+        ctx.save_for_backward(q, k, v, o, lse)
+        ctx.scale, ctx.causal = scale, causal
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        q, k, v, o, lse = ctx.saved_tensors
+        S, B, H, D = q.shape
+        dqkv = torch.empty((S, B, H, 3 * D), dtype=q.dtype, device=q.device)
+        dq, dk, dv = dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:]
+        N.attn_bwd(q, k, v, o, do.contiguous(), lse, ctx.scale, ctx.causal, dq, dk, dv)
+        return dq, dk, dv, None, None
+
+
+def attention(q, k, v, scale: Optional[float] = None, causal: bool = True):
+    """Scaled-dot-product attention on [S, B, H, D] tensors.  head_dim 64 (fwd+bwd) / 128 (fwd) run the tcgen05
+    kernels in bf16; other shapes / dtypes use the PyTorch restatement (same math, autograd backward)."""
+    D = q.shape[-1]
+    scale = 1.0 / math.sqrt(D) if scale is None else scale
+    native_ok = q.is_cuda and q.dtype == torch.bfloat16 and (D == 64 or (D == 128 and not torch.is_grad_enabled()))
+    if native_ok or (not q.is_cuda and D == 64 and not q.requires_grad and False):
+        return _Attention.apply(q, k, v, scale, causal)
+    qf, kf, vf = (t.permute(1, 2, 0, 3) for t in (q, k, v))
+    o = torch.nn.functional.scaled_dot_product_attention(qf, kf, vf, is_causal=causal, scale=scale)
+    return o.permute(2, 0, 1, 3).contiguous()
+
+
+class _CrossEntropy(torch.autograd.Function):
+    """logits [rows, V] (low precision) + labels [rows] -> per-row fp32 loss; backward overwrites logits with dlogits."""
+
+    @staticmethod
+    def forward(ctx, logits, labels, ignore_index):
+        lc = logits if logits.is_contiguous() else logits.contiguous()
+        m, s, t = N.xent_stats(lc, labels)
+        loss = N.xent_finish(m, s, t, labels, ignore_index)
+        ctx.save_for_backward(lc, labels, m, s)
+        ctx.ignore_index = ignore_index
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        lc, labels, m, s = ctx.saved_tensors
+        d = N.xent_bwd_(lc, labels, m, s, dloss.contiguous().float(), 1.0, 0, ctx.ignore_index)
+        return d, None, None
+
+
+def cross_entropy(logits, labels, ignore_index: int = -100, reduction: str = "mean"):
+    V = logits.shape[-1]
+    l2, lab = logits.reshape(-1, V), labels.reshape(-1)
+    if not _lowp(logits) or V % 8:
+        return torch.nn.functional.cross_entropy(l2.float(), lab, ignore_index=ignore_index, reduction=reduction)
+    loss = _CrossEntropy.apply(l2, lab, ignore_index)
+    if reduction == "none":
+        return loss.view(labels.shape)
+    if reduction == "sum":
+        return loss.sum()
+    return loss.sum() / (lab != ignore_index).sum().clamp(min=1)
+
+
+class _Embedding(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, weight):
+        flat = ids.reshape(-1)
+        out = N.embedding_fwd(flat, flat, weight, None, 0)
+        ctx.save_for_backward(flat)
+        ctx.wparam, ctx.shape = weight, ids.shape
+        return out.view(*ids.shape, weight.shape[1])
+
+    @staticmethod
+    def backward(ctx, dy):
+        (flat,) = ctx.saved_tensors
+        w = ctx.wparam
+        mg = getattr(w, "main_grad", None)
+        acc = mg if mg is not None else torch.zeros(w.shape, dtype=torch.float32, device=w.device)
+        N.embedding_bwd_(dy.reshape(-1, w.shape[1]).contiguous(), flat, flat, acc, None, 0)
+        return None, (None if mg is not None else acc.to(w.dtype))
+
+
+def embedding(ids, weight):
+    if not _lowp(weight) or weight.shape[1] % 8:
+        return torch.nn.functional.embedding(ids, weight)
+    return _Embedding.apply(ids, weight)
+
+
+class _Rope(torch.autograd.Function):
+    """In-place rotate-half RoPE on the q and k slices of x [T, nheads*hd] (returns x)."""
+
+    @staticmethod
+    def forward(ctx, x, cos_t, sin_t, pos, nheads, hd):
+        ctx.save_for_backward(cos_t, sin_t, pos)
+        ctx.meta = (nheads, hd, x.stride(0))
+        ctx.mark_dirty(x)
+        N.rope_(x, cos_t, sin_t, pos, nheads, hd, x.stride(0), hd, backward=False)
+        return x
+
+    @staticmethod
+    def backward(ctx, dy):
+        cos_t, sin_t, pos = ctx.saved_tensors
+        nheads, hd, _ = ctx.meta
+        d = dy.contiguous().clone()
+        N.rope_(d, cos_t, sin_t, pos, nheads, hd, d.stride(0), hd, backward=True)
+        return d, None, None, None, None, None
+
+
+def rope(x2, cos_t, sin_t, pos_i32, nheads: int, hd: int):
+    """x2: [tokens, nheads*hd] contiguous rows (may be a column slice of a wider tensor)."""
+    return _Rope.apply(x2, cos_t, sin_t, pos_i32, nheads, hd)
+
+
+def rope_tables(max_pos: int, hd: int, base: float = 10000.0, device=None):
+    inv = 1.0 / (base ** (torch.arange(0, hd, 2, device=device).float() / hd))
+    ang = torch.arange(max_pos, device=device).float()[:, None] * inv[None]
+    return ang.cos().contiguous(), ang.sin().contiguous()

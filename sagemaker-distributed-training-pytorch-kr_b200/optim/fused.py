@@ -26,6 +26,9 @@ def _runs(params: List[torch.Tensor]):
             q = cur[-1]
             ok = (p.dtype == q.dtype == torch.float32 and p.grad.dtype == torch.float32
                   and p.is_contiguous() and p.grad.is_contiguous() and q.is_contiguous() and q.grad.is_contiguous())
+            if ok:   # a run must live inside ONE storage (arena / bucket), not merely be adjacent in the address space
+                ok = (p.untyped_storage().data_ptr() == q.untyped_storage().data_ptr()
+                      and p.grad.untyped_storage().data_ptr() == q.grad.untyped_storage().data_ptr())
             if ok:
                 gap_p = p.data_ptr() - (q.data_ptr() + q.numel() * 4)
                 gap_g = p.grad.data_ptr() - (q.grad.data_ptr() + q.grad.numel() * 4)
