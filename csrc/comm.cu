@@ -172,6 +172,86 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
   }
 }
 
+// ZeRO gradient path: reduce-scatter of a symmetric gradient buffer fused with what follows it.
+//   slice `rank` of sum_r grad_r  * gscale  ->  (+)= fp32 gradient shard `gacc`   (gradient accumulation steps)
+//   and, on the optimizer boundary (ADAM), straight into AdamW on the fp32 master / m / v shard, emitting the
+//   low-precision parameter shard - the reduced gradient never round-trips through memory between the two.
+// replaces: DeepSpeed stage3 reduce_scatter_coalesced + FusedAdam multi_tensor_adam.
+template <typename T, bool MULTICAST, bool ADAM>
+__global__ void __launch_bounds__(512)
+rs_update_kernel(Peers P, void* mc_base, long long n_elems, int rank, int world, float gscale, float* __restrict__ gacc,
+                 int accumulate, float* __restrict__ sumsq, float* __restrict__ p32, float* __restrict__ m,
+                 float* __restrict__ v, __nv_bfloat16* __restrict__ p_lp, float lr, float beta1, float beta2, float eps,
+                 float wd, float bc1, float bc2) {
+  uint32_t* my_ctrl = P.ctrl[rank];
+  const uint32_t epoch = enter(P, rank, world, my_ctrl);
+  constexpr int EPV = 16 / sizeof(T);
+  const long long nvec = n_elems / EPV;
+  const long long per = (nvec + world - 1) / world;
+  const long long v0 = per * rank, v1 = min(nvec, v0 + per);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  float ss = 0.f;
+  for (long long vi = v0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; vi < v1; vi += stride) {
+    float g[EPV];
+    if constexpr (MULTICAST) {
+      uint8_t* mc = static_cast<uint8_t*>(mc_base) + vi * 16;
+      if constexpr (sizeof(T) == 4) {
+        mm_ld_reduce_f32x4(mc, g[0], g[1], g[2], g[3]);
+      } else {
+        uint32_t a, b, c, d;
+        mm_ld_reduce_bf16x8(mc, a, b, c, d);
+        float2 f;
+        f = unpack_bf16x2(a); g[0] = f.x; g[1] = f.y; f = unpack_bf16x2(b); g[2] = f.x; g[3] = f.y;
+        f = unpack_bf16x2(c); g[4] = f.x; g[5] = f.y; f = unpack_bf16x2(d); g[6] = f.x; g[7] = f.y;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < EPV; ++i) g[i] = 0.f;
+      for (int r = 0; r < world; ++r) {
+        const uint4 q = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(P.ptr[r]) + vi * 16);
+        if constexpr (sizeof(T) == 4) {
+          g[0] += __uint_as_float(q.x); g[1] += __uint_as_float(q.y); g[2] += __uint_as_float(q.z); g[3] += __uint_as_float(q.w);
+        } else {
+          float2 f;
+          f = unpack_bf16x2(q.x); g[0] += f.x; g[1] += f.y; f = unpack_bf16x2(q.y); g[2] += f.x; g[3] += f.y;
+          f = unpack_bf16x2(q.z); g[4] += f.x; g[5] += f.y; f = unpack_bf16x2(q.w); g[6] += f.x; g[7] += f.y;
+        }
+      }
+    }
+    const long long e0 = (vi - v0) * EPV;       // element offset inside this rank's shard
+#pragma unroll
+    for (int i = 0; i < EPV; ++i) {
+      float gr = g[i] * gscale;
+      if (gacc != nullptr) {
+        if (accumulate) gr += gacc[e0 + i];
+        gacc[e0 + i] = gr;
+      }
+      ss += gr * gr;
+      if constexpr (ADAM) {
+        float pa = p32[e0 + i], ma = m[e0 + i], va = v[e0 + i];
+        ma = beta1 * ma + (1.f - beta1) * gr;
+        va = beta2 * va + (1.f - beta2) * gr * gr;
+        pa -= lr * ((ma / bc1) / (sqrtf(va / bc2) + eps) + wd * pa);
+        p32[e0 + i] = pa; m[e0 + i] = ma; v[e0 + i] = va;
+        if (p_lp != nullptr) p_lp[e0 + i] = __float2bfloat16(pa);
+      }
+    }
+  }
+  if (sumsq != nullptr) {
+    ss = warp_sum(ss);
+    if ((threadIdx.x & 31) == 0 && ss != 0.f) atomicAdd(sumsq, ss);
+  }
+  __threadfence_system();
+  __syncthreads();
+  __shared__ bool last;
+  if (threadIdx.x == 0) last = (atomicAdd(my_ctrl + 2, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (last) {
+    fabric_barrier(P, rank, world, epoch, CTRL_B);      // nobody may overwrite its gradient buffer before all have read it
+    if (threadIdx.x == 0) { my_ctrl[2] = 0u; my_ctrl[1] = epoch; __threadfence(); }
+  }
+}
+
 int check(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
@@ -220,4 +300,36 @@ extern "C" int b2_reduce_scatter(void* const* ptrs, void* const* ctrls, void* mc
 extern "C" int b2_allgather(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
                             int max_ctas, void* stream) {
   return run_collective(2, ptrs, ctrls, mc_ptr, n_elems, dtype, 1.f, rank, world, max_ctas, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+// ZeRO: reduce-scatter (+ accumulate into the fp32 gradient shard) (+ AdamW on the shard when `adam` != 0).
+// gacc may be NULL when adam != 0 and no accumulation is wanted; sumsq (device, optional) receives += sum g^2.
+extern "C" int b2_rs_update(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
+                            float gscale, float* gacc, int accumulate, float* sumsq, int adam, float* p32, float* m, float* v,
+                            void* p_lp, float lr, float beta1, float beta2, float eps, float wd, int step, int max_ctas, void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (world < 1 || world > MAX_RANKS) { b2host::set_error("rs_update: world size %d unsupported", world); return -1; }
+  if (dtype != B2_DTYPE_FP32 && dtype != B2_DTYPE_BF16) { b2host::set_error("rs_update: gradients must be fp32 or bf16"); return -1; }
+  const int esz = dtype == B2_DTYPE_FP32 ? 4 : 2;
+  if ((n_elems * esz) % (16LL * world)) { b2host::set_error("rs_update: payload must be a multiple of 16 bytes per rank"); return -1; }
+  Peers P;
+  for (int r = 0; r < MAX_RANKS; ++r) { P.ptr[r] = r < world ? ptrs[r] : nullptr; P.ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
+  const long long per = n_elems * esz / 16 / world;
+  const int threads = 512;
+  long long want = (per + threads - 1) / threads;
+  const int cap = max_ctas > 0 ? max_ctas : 96;
+  const int grid = static_cast<int>(want < 1 ? 1 : (want > cap ? cap : want));
+  const float bc1 = 1.f - powf(beta1, static_cast<float>(step > 0 ? step : 1));
+  const float bc2 = 1.f - powf(beta2, static_cast<float>(step > 0 ? step : 1));
+  __nv_bfloat16* lp = static_cast<__nv_bfloat16*>(p_lp);
+#define B2_RS(T_, MC_, AD_) rs_update_kernel<T_, MC_, AD_><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, rank, world, gscale, gacc, accumulate, sumsq, p32, m, v, lp, lr, beta1, beta2, eps, wd, bc1, bc2)
+  if (mc_ptr != nullptr) {
+    if (esz == 4) { if (adam) B2_RS(float, true, true); else B2_RS(float, true, false); }
+    else          { if (adam) B2_RS(__nv_bfloat16, true, true); else B2_RS(__nv_bfloat16, true, false); }
+  } else {
+    if (esz == 4) { if (adam) B2_RS(float, false, true); else B2_RS(float, false, false); }
+    else          { if (adam) B2_RS(__nv_bfloat16, false, true); else B2_RS(__nv_bfloat16, false, false); }
+  }
+#undef B2_RS
+  return check("rs_update");
 }

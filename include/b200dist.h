@@ -159,6 +159,15 @@ int b2_reduce_scatter(void* const* ptrs, void* const* ctrls, void* mc_ptr, long 
 int b2_allgather(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
                  int max_ctas, void* stream);
 
+/* ZeRO gradient path in one kernel: reduce-scatter of the symmetric gradient buffer (multimem.ld_reduce of this
+ * rank's slice) * gscale, accumulated into the fp32 gradient shard `gacc` (may be NULL) and - when adam != 0 -
+ * consumed directly by AdamW on the fp32 master/m/v shard, writing the bf16 parameter shard `p_lp`.
+ * sumsq (device, optional) += sum of squares of the scaled reduced gradient (for global-norm clipping).
+ * replaces: DeepSpeed reduce_scatter_coalesced + FusedAdam. */
+int b2_rs_update(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, int rank, int world,
+                 float gscale, float* gacc, int accumulate, float* sumsq, int adam, float* p32, float* m, float* v,
+                 void* p_lp, float lr, float beta1, float beta2, float eps, float wd, int step, int max_ctas, void* stream);
+
 /* Fused compute + collective kernels (csrc/gemm.cu).  A operand is [rows, K] row-major; B as in b2_gemm.
  *  b2_ag_gemm : all-gather(A shards over the group) -> GEMM, one kernel; xg receives the gathered A.
  *  b2_gemm_rs : GEMM -> reduce-scatter(+bias+residual), one kernel; b2_make_rs_maps prepares its staging maps.

@@ -20,6 +20,12 @@ def _lowp(t: torch.Tensor) -> bool:
 
 
 def _wgrad(param, dy2, x2):
+    gb = getattr(param, "grad_buffer", None)
+    if gb is not None and gb.is_cuda and gb.dtype == dy2.dtype:
+        # ZeRO-3: the weight gradient is written straight into the symmetric gradient workspace
+        N.gemm(dy2, x2, a_mn=True, b_mn=True, out=gb.view(param.shape[0], -1))
+        param._gb_written = True
+        return None
     mg = getattr(param, "main_grad", None)
     if mg is not None:
         N.gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
@@ -261,20 +267,20 @@ def embedding(ids, weight):
 
 
 class _Rope(torch.autograd.Function):
-    """In-place rotate-half RoPE on the q and k slices of x [T, nheads*hd] (returns x)."""
+    """rotate-half RoPE over `nheads` heads of width `hd` of x [T, nheads*hd]; out of place (native kernel on a copy)."""
 
     @staticmethod
     def forward(ctx, x, cos_t, sin_t, pos, nheads, hd):
         ctx.save_for_backward(cos_t, sin_t, pos)
-        ctx.meta = (nheads, hd, x.stride(0))
-        ctx.mark_dirty(x)
-        N.rope_(x, cos_t, sin_t, pos, nheads, hd, x.stride(0), hd, backward=False)
-        return x
+        ctx.meta = (nheads, hd)
+        y = x.contiguous().clone()
+        N.rope_(y, cos_t, sin_t, pos, nheads, hd, y.stride(0), hd, backward=False)
+        return y
 
     @staticmethod
     def backward(ctx, dy):
         cos_t, sin_t, pos = ctx.saved_tensors
-        nheads, hd, _ = ctx.meta
+        nheads, hd = ctx.meta
         d = dy.contiguous().clone()
         N.rope_(d, cos_t, sin_t, pos, nheads, hd, d.stride(0), hd, backward=True)
         return d, None, None, None, None, None

@@ -1,0 +1,365 @@
+"""ZeRO stage 3: parameters, gradients and optimizer state partitioned over the data-parallel group.
+
+Counterpart of DeepSpeed's zero/{partition_parameters,parameter_offload,partitioned_param_coordinator,stage3}.py
+ configured by configs/default_offload_opt_param.json.  B200-first layout:
+
+  * a *unit* (one decoder layer, the embeddings, the head) owns ONE flat low-precision buffer; each rank keeps only
+    its 1/world slice of it (+ fp32 master / exp_avg / exp_avg_sq / fp32 grad-accumulation slices);
+  * two full-size gather workspaces and two gradient workspaces live in SYMMETRIC memory and rotate between units:
+    the parameters of unit L are views into workspace L % 2, so their addresses never change;
+  * fetch   = copy my slice into the workspace + the fabric all-gather kernel (NVSwitch multicast stores) on a
+    side stream, issued one unit ahead (static prefetch order, forward and backward);
+  * release = nothing to free: the workspace is simply overwritten by the next fetch;
+  * reduce  = ONE fused kernel per unit and micro-step (csrc/comm.cu rs_update): multimem.ld_reduce of my slice of
+    the gradient workspace, scaled, accumulated into the fp32 gradient slice; on the optimizer boundary, when no
+    global-norm clipping is requested, the same kernel applies AdamW to the fp32 slice and writes the bf16 slice
+    (gradient reduce-scatter fused with the partitioned Adam update).  With clipping the Adam pass runs after the
+    norm is known, as one flat launch over all slices;
+  * parameters below ``stage3_param_persistence_threshold`` stay replicated (their grads are all-reduced).
+
+On CPU / gloo (tests) the same bookkeeping runs with torch.distributed collectives.
+``offload_param.device = cpu`` keeps the low-precision slices in pinned host memory and stages them H2D before each
+fetch (slow path).
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..ops import native as N
+
+
+def _align(n, a):
+    return (n + a - 1) // a * a
+
+
+class _Unit:
+    def __init__(self, index: int, name: str, module: nn.Module, params: List[nn.Parameter], names: List[str]):
+        self.index, self.name, self.module, self.params, self.names = index, name, module, params, names
+        self.offsets: List[int] = []
+        self.numel = 0          # padded flat size (multiple of world * 128)
+        self.slice = 0
+
+
+class _FetchFn(torch.autograd.Function):
+    """identity on the activation; forward = make sure unit `idx` is gathered (and prefetch the next one);
+    backward = the unit's backward has finished -> reduce-scatter its gradients."""
+
+    @staticmethod
+    def forward(ctx, x, engine, idx):
+        ctx.engine, ctx.idx = engine, idx
+        engine._ensure(idx, forward=True)
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.engine._reduce_unit(ctx.idx)
+        return g, None, None
+
+
+class _PreBackwardFn(torch.autograd.Function):
+    """identity on the unit output; backward = re-gather the unit before its backward runs (prefetch the previous)."""
+
+    @staticmethod
+    def forward(ctx, y, engine, idx):
+        ctx.engine, ctx.idx = engine, idx
+        return y.view_as(y)
+
+    @staticmethod
+    def backward(ctx, g):
+        ctx.engine._ensure(ctx.idx, forward=False)
+        return g, None, None
+
+
+class Zero3Engine:
+    def __init__(self, units: Sequence[nn.Module], unit_names: Optional[Sequence[str]] = None, group=None, *, lr: float = 1e-5,
+                 betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, max_grad_norm: float = 1.0,
+                 gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
+                 offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None):
+        self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+        self.world = dist.get_world_size(self.group) if self.group is not None else 1
+        self.rank = dist.get_rank(self.group) if self.group is not None else 0
+        self.lr, self.betas, self.eps, self.wd, self.max_grad_norm = lr, betas, eps, weight_decay, max_grad_norm
+        self.ga, self.micro = max(1, gradient_accumulation_steps), 0
+        self.step_count = 0
+        self.offload_param = offload_param
+        first = next(p for u in units for p in u.parameters())
+        self.dev, self.dtype = first.device, first.dtype
+        self.grad_dtype = grad_dtype or self.dtype
+        self.fabric = None
+        if comm_backend == "native" and self.world > 1 and self.dev.type == "cuda":
+            from . import fabric
+            fb = fabric.get_fabric(self.group)
+            if fb.usable:
+                self.fabric = fb
+        # ---- units, persistent (replicated) parameters
+        self.units: List[_Unit] = []
+        self.persistent: List[nn.Parameter] = []
+        names = list(unit_names) if unit_names is not None else [f"unit{i}" for i in range(len(units))]
+        seen = set()
+        pad = self.world * 128
+        for i, (m, nm) in enumerate(zip(units, names)):
+            ps, pn = [], []
+            for n, p in m.named_parameters():
+                if id(p) in seen or not p.requires_grad:
+                    continue
+                seen.add(id(p))
+                if p.numel() <= persistence_threshold:
+                    self.persistent.append(p)
+                    continue
+                ps.append(p); pn.append(n)
+            u = _Unit(i, nm, m, ps, pn)
+            off = 0
+            for p in ps:
+                u.offsets.append(off)
+                off += _align(p.numel(), 64)
+            u.numel = _align(max(off, pad), pad)
+            u.slice = u.numel // self.world
+            self.units.append(u)
+        self.num_persistent = sum(p.numel() for p in self.persistent)
+        max_numel = max(u.numel for u in self.units)
+        # ---- rotating workspaces (symmetric when the fabric is up)
+        self._ws_param, self._ws_grad = [], []
+        for k in range(2):
+            if self.fabric is not None:
+                self._ws_param.append(self.fabric.alloc(max_numel, self.dtype))
+                self._ws_grad.append(self.fabric.alloc(max_numel, self.grad_dtype))
+            else:
+                self._ws_param.append(torch.zeros(max_numel, dtype=self.dtype, device=self.dev))
+                self._ws_grad.append(torch.zeros(max_numel, dtype=self.grad_dtype, device=self.dev))
+        # ---- partition: per-unit slices
+        self.lp_slices, self.fp32, self.exp_avg, self.exp_avg_sq, self.gacc = [], [], [], [], []
+        for u in self.units:
+            flat = torch.zeros(u.numel, dtype=self.dtype, device=self.dev)
+            for p, o in zip(u.params, u.offsets):
+                flat[o:o + p.numel()].copy_(p.data.reshape(-1))
+            sl = flat[self.rank * u.slice:(self.rank + 1) * u.slice].clone()
+            if offload_param == "cpu":
+                sl = sl.cpu().pin_memory() if (pin_memory and torch.cuda.is_available()) else sl.cpu()
+            self.lp_slices.append(sl)
+            self.fp32.append(flat[self.rank * u.slice:(self.rank + 1) * u.slice].float())
+            self.exp_avg.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+            self.exp_avg_sq.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+            self.gacc.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+            ws_p, ws_g = self._param_ws(u.index), self._grad_ws(u.index)
+            for p, o in zip(u.params, u.offsets):      # parameters become views of the rotating workspace
+                p.data = ws_p[o:o + p.numel()].view(p.shape)
+                p.grad_buffer = ws_g[o:o + p.numel()].view(p.shape)
+                p.zero3_unit = u.index
+            del flat
+        self.persist_m = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
+        self.persist_v = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
+        self.persist_fp32 = [p.data.float().clone() for p in self.persistent]
+        self._resident = [None, None]          # which unit currently occupies each workspace
+        self._events: Dict[int, torch.cuda.Event] = {}
+        self._stream = torch.cuda.Stream() if self.dev.type == "cuda" else None
+        self.sumsq = torch.zeros(1, dtype=torch.float32, device=self.dev)
+        self.last_grad_norm = 0.0
+        self.param_groups = [{"lr": lr, "weight_decay": weight_decay}]
+        self._reduce_at_end: List[int] = []
+
+    # ------------------------------------------------------------------ workspace helpers
+    def _param_ws(self, idx) -> torch.Tensor:
+        w = self._ws_param[idx % 2]
+        return w.tensor if hasattr(w, "tensor") else w
+
+    def _grad_ws(self, idx) -> torch.Tensor:
+        w = self._ws_grad[idx % 2]
+        return w.tensor if hasattr(w, "tensor") else w
+
+    def total_params(self) -> int:
+        return sum(sum(p.numel() for p in u.params) for u in self.units) + self.num_persistent
+
+    # ------------------------------------------------------------------ fetch / prefetch
+    def _gather(self, idx: int):
+        """all-gather unit idx into workspace idx % 2 (on the current stream)."""
+        u = self.units[idx]
+        ws = self._param_ws(idx)
+        sl = self.lp_slices[idx]
+        mine = ws[self.rank * u.slice:(self.rank + 1) * u.slice]
+        if sl.device != mine.device:
+            sl = sl.to(mine.device, non_blocking=True)          # offload_param=cpu: pinned H2D staging
+        if mine.is_cuda:
+            N.axpby(sl, None, 1.0, 0.0, out=mine)                # raw-pointer copy: no autograd version bump on the workspace
+        else:
+            mine.data.copy_(sl)
+        if self.world > 1:
+            if self.fabric is not None:
+                buf = self._ws_param[idx % 2]
+                N._call("b2_allgather", buf.ptrs, buf.ctrls, buf.mc_ptr or None, u.numel, N._dt(ws), self.rank, self.world, 0, N._st())
+            else:
+                out = ws[:u.numel]
+                dist.all_gather_into_tensor(out.data, mine.data.clone(), group=self.group)
+        self._resident[idx % 2] = idx
+
+    def _ensure(self, idx: int, forward: bool):
+        nxt = idx + 1 if forward else idx - 1
+        if self._stream is None:
+            if self._resident[idx % 2] != idx:
+                self._gather(idx)
+            return
+        cur = torch.cuda.current_stream()
+        if self._resident[idx % 2] != idx:
+            self._stream.wait_stream(cur)
+            with torch.cuda.stream(self._stream):
+                self._gather(idx)
+                ev = torch.cuda.Event(); ev.record()
+                self._events[idx] = ev
+        ev = self._events.pop(idx, None)
+        if ev is not None:
+            cur.wait_event(ev)
+        if 0 <= nxt < len(self.units) and self._resident[nxt % 2] != nxt:
+            # prefetch the next unit into the OTHER workspace while this one computes; the other workspace's
+            # previous occupant has finished (its compute was issued earlier on the current stream)
+            self._stream.wait_stream(cur)
+            with torch.cuda.stream(self._stream):
+                self._gather(nxt)
+                ev = torch.cuda.Event(); ev.record()
+                self._events[nxt] = ev
+
+    def wrap(self, idx: int, fn, x, *args):
+        """run unit idx: y = fn(x, *args) with fetch before forward/backward and gradient reduction after backward."""
+        if torch.is_tensor(x) and x.is_floating_point() and x.requires_grad:
+            x = _FetchFn.apply(x, self, idx)          # its backward runs right after the unit's backward
+        else:
+            self._ensure(idx, forward=True)           # first unit (token ids in): reduced when loss.backward() returns
+            self._reduce_at_end.append(idx)
+        y = fn(x, *args)
+        if torch.is_grad_enabled() and y.requires_grad:
+            y = _PreBackwardFn.apply(y, self, idx)
+        return y
+
+    # ------------------------------------------------------------------ gradient reduction (+ fused Adam)
+    def _reduce_unit(self, idx: int):
+        u = self.units[idx]
+        # gradients that came back through autograd are moved into the (symmetric) gradient workspace; weight
+        # gradients written there directly by the GEMM (ops/functional._wgrad) are already in place
+        for p in u.params:
+            if p.grad is not None:
+                p.grad_buffer.data.copy_(p.grad.to(p.grad_buffer.dtype))
+                p.grad = None
+            elif not getattr(p, "_gb_written", False):
+                p.grad_buffer.data.zero_()
+            p._gb_written = False
+        boundary = (self.micro + 1) % self.ga == 0
+        fuse_adam = boundary and not (self.max_grad_norm and self.max_grad_norm > 0)
+        gscale = 1.0 / (self.world * self.ga)
+        gws = self._grad_ws(idx)
+        acc = self.micro % self.ga != 0
+        lr, wd = self.param_groups[0]["lr"], self.param_groups[0]["weight_decay"]
+        if self.fabric is not None:
+            buf = self._ws_grad[idx % 2]
+            lp = self.lp_slices[idx]
+            N._call("b2_rs_update", buf.ptrs, buf.ctrls, buf.mc_ptr or None, u.numel, N._dt(gws), self.rank, self.world, float(gscale),
+                    N._p(self.gacc[idx]), int(acc), N._p(self.sumsq), int(fuse_adam), N._p(self.fp32[idx]), N._p(self.exp_avg[idx]),
+                    N._p(self.exp_avg_sq[idx]), N._p(lp) if (fuse_adam and lp.is_cuda) else None, float(lr), float(self.betas[0]),
+                    float(self.betas[1]), float(self.eps), float(wd), self.step_count + 1, 0, N._st())
+            if fuse_adam and not lp.is_cuda:
+                lp.copy_(self.fp32[idx].to(lp.dtype), non_blocking=True)
+        else:
+            full = gws[:u.numel].float()
+            if self.world > 1:
+                dist.all_reduce(full, group=self.group)
+            mine = full[self.rank * u.slice:(self.rank + 1) * u.slice] * gscale
+            if acc:
+                self.gacc[idx].add_(mine)
+            else:
+                self.gacc[idx].copy_(mine)
+            self.sumsq.add_(self.gacc[idx].pow(2).sum() if boundary else 0.0)
+            if fuse_adam:
+                self._adam_slice(idx, 1.0)
+
+    def _adam_slice(self, idx, grad_scale):
+        lp = self.lp_slices[idx]
+        lr, wd = self.param_groups[0]["lr"], self.param_groups[0]["weight_decay"]
+        N.adam_(self.fp32[idx], self.exp_avg[idx], self.exp_avg_sq[idx], self.gacc[idx], lp if lp.device == self.fp32[idx].device else None,
+                lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, wd=wd, step=self.step_count + 1, adamw=True, grad_scale=grad_scale)
+        if lp.device != self.fp32[idx].device:
+            lp.copy_(self.fp32[idx].to(lp.dtype), non_blocking=True)
+
+    # ------------------------------------------------------------------ engine API (DeepSpeedEngine.backward / step)
+    def backward(self, loss: torch.Tensor):
+        loss.backward()
+        for idx in self._reduce_at_end:
+            self._reduce_unit(idx)
+        self._reduce_at_end = []
+        self.micro += 1
+
+    def is_gradient_accumulation_boundary(self) -> bool:
+        return self.micro % self.ga == 0 and self.micro > 0
+
+    def step(self):
+        """acts on the gradient-accumulation boundary only (DeepSpeedEngine.step semantics)."""
+        if not self.is_gradient_accumulation_boundary():
+            return False
+        lr, wd = self.param_groups[0]["lr"], self.param_groups[0]["weight_decay"]
+        # persistent (replicated) parameters: all-reduce their grads, include them in the norm
+        for p in self.persistent:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+            if self.world > 1:
+                dist.all_reduce(p.grad, group=self.group)
+            p.grad.div_(self.world * self.ga)
+        clip = self.max_grad_norm and self.max_grad_norm > 0
+        coef = 1.0
+        if clip:
+            tot = self.sumsq.clone()
+            if self.world > 1:
+                dist.all_reduce(tot, group=self.group)
+            for p in self.persistent:
+                tot += p.grad.float().pow(2).sum()
+            norm = float(tot.sqrt())
+            self.last_grad_norm = norm
+            coef = min(1.0, self.max_grad_norm / (norm + 1e-6))
+            for i in range(len(self.units)):
+                self._adam_slice(i, coef)
+        for p, m, v, p32 in zip(self.persistent, self.persist_m, self.persist_v, self.persist_fp32):
+            N.adam_(p32.view(-1), m.view(-1), v.view(-1), p.grad.float().view(-1).contiguous(), None, lr=lr, beta1=self.betas[0], beta2=self.betas[1],
+                    eps=self.eps, wd=0.0, step=self.step_count + 1, adamw=True, grad_scale=coef)
+            p.data.copy_(p32.to(p.dtype))
+            p.grad = None
+        self.step_count += 1
+        self.micro = 0
+        self.sumsq.zero_()
+        self._resident = [None, None]         # parameter slices changed: workspaces are stale
+        self._events.clear()
+        return True
+
+    def zero_grad(self):
+        for p in self.persistent:
+            p.grad = None
+
+    # ------------------------------------------------------------------ checkpoint helpers
+    def gather_full_state_dict(self) -> Dict[str, torch.Tensor]:
+        """stage3_gather_16bit_weights_on_model_save: every unit is gathered in turn; returns CPU tensors."""
+        out = {}
+        for u in self.units:
+            self._resident[u.index % 2] = None
+            self._ensure(u.index, forward=True) if self._stream is None else self._gather(u.index)
+            if self.dev.type == "cuda":
+                torch.cuda.synchronize()
+            for n, p in zip(u.names, u.params):
+                out[f"{u.name}.{n}" if u.name else n] = p.data.detach().cpu().clone()
+        self._resident = [None, None]
+        return out
+
+    def shard_state(self) -> Dict:
+        return {"zero_stage": 3, "partition_count": self.world, "rank": self.rank, "step": self.step_count,
+                "fp32_flat_groups": [t.detach().cpu() for t in self.fp32],
+                "exp_avg": [t.detach().cpu() for t in self.exp_avg], "exp_avg_sq": [t.detach().cpu() for t in self.exp_avg_sq],
+                "unit_names": [u.name for u in self.units], "unit_numel": [u.numel for u in self.units],
+                "param_shapes": [{n: tuple(p.shape) for n, p in zip(u.names, u.params)} for u in self.units],
+                "param_offsets": [dict(zip(u.names, u.offsets)) for u in self.units]}
+
+    def load_shard_state(self, sd: Dict):
+        assert sd["partition_count"] == self.world, "ZeRO-3 checkpoint was written with a different world size"
+        self.step_count = sd["step"]
+        for i in range(len(self.units)):
+            self.fp32[i].copy_(sd["fp32_flat_groups"][i])
+            self.exp_avg[i].copy_(sd["exp_avg"][i])
+            self.exp_avg_sq[i].copy_(sd["exp_avg_sq"][i])
+            self.lp_slices[i].copy_(self.fp32[i].to(self.lp_slices[i].dtype))
+        self._resident = [None, None]
