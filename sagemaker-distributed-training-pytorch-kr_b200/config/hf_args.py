@@ -1,0 +1,124 @@
+"""HF-style dataclass argument system for the Alpaca script (reference: 4_training_alpaca_deepspeed/train.py:72-89,
+210-211 - `HfArgumentParser((ModelArguments, DataArguments, TrainingArguments))`).
+
+Values arrive as `--flag True|False|value` strings because the SageMaker toolkit turns the hyper-parameter dict
+into argv (4_...ipynb:877), so booleans accept both a bare flag and a string.
+"""
+from __future__ import annotations
+
+import argparse
+import dataclasses
+import math
+from dataclasses import dataclass, field, fields
+from typing import Any, Optional, Tuple, get_args, get_origin, Union
+
+
+def _strbool(v):
+    if isinstance(v, bool):
+        return v
+    s = str(v).lower()
+    if s in ("yes", "true", "t", "y", "1"):
+        return True
+    if s in ("no", "false", "f", "n", "0"):
+        return False
+    raise argparse.ArgumentTypeError(f"Truthy value expected: got {v}")
+
+
+@dataclass
+class ModelArguments:
+    model_name_or_path: Optional[str] = field(default="facebook/opt-125m")
+
+
+@dataclass
+class DataArguments:
+    data_path: Optional[str] = field(default=None, metadata={"help": "Path to the training data."})
+
+
+@dataclass
+class TrainingArguments:
+    """The subset of transformers.TrainingArguments the notebook passes or that feeds the DeepSpeed "auto" fields
+    (4_...ipynb:464-485), plus the three fields train.py adds (cache_dir, optim, model_max_length)."""
+    output_dir: str = "./output"
+    cache_dir: Optional[str] = None
+    optim: str = "adamw_torch"
+    model_max_length: int = field(default=512, metadata={"help": "Maximum sequence length. Sequences will be right padded (and possibly truncated)."})
+    bf16: bool = False
+    fp16: bool = False
+    tf32: Optional[bool] = None
+    num_train_epochs: float = 3.0
+    max_steps: int = -1
+    per_device_train_batch_size: int = 8
+    per_device_eval_batch_size: int = 8
+    gradient_accumulation_steps: int = 1
+    evaluation_strategy: str = "no"
+    save_strategy: str = "steps"
+    save_steps: int = 500
+    save_total_limit: Optional[int] = None
+    learning_rate: float = 5e-5
+    weight_decay: float = 0.0
+    adam_beta1: float = 0.9
+    adam_beta2: float = 0.999
+    adam_epsilon: float = 1e-8
+    max_grad_norm: float = 1.0
+    warmup_ratio: float = 0.0
+    warmup_steps: int = 0
+    lr_scheduler_type: str = "linear"
+    logging_steps: int = 500
+    seed: int = 42
+    deepspeed: Optional[str] = None
+    report_to: str = "none"
+    dataloader_num_workers: int = 0
+    local_rank: int = -1
+    gradient_checkpointing: bool = False
+    # additions
+    comm_backend: str = field(default="native", metadata={"help": "native (fabric kernels) | nccl"})
+    synthetic_data: bool = field(default=False, metadata={"help": "fixed-length synthetic instruction batches (BASELINE config 5)"})
+    synthetic_samples: int = 4096
+
+    world_size: int = 1
+
+    def get_warmup_steps(self, num_training_steps: int) -> int:
+        return self.warmup_steps if self.warmup_steps > 0 else math.ceil(num_training_steps * self.warmup_ratio)
+
+    @property
+    def train_batch_size(self) -> int:
+        return self.per_device_train_batch_size
+
+
+def _base_type(tp):
+    if get_origin(tp) is Union:
+        args = [a for a in get_args(tp) if a is not type(None)]
+        return args[0] if args else str
+    return tp
+
+
+class HfArgumentParser(argparse.ArgumentParser):
+    """dataclass types -> argparse; parse_args_into_dataclasses() returns one instance per type."""
+
+    def __init__(self, dataclass_types, **kw):
+        super().__init__(formatter_class=argparse.ArgumentDefaultsHelpFormatter, **kw)
+        self.dataclass_types = list(dataclass_types) if isinstance(dataclass_types, (list, tuple)) else [dataclass_types]
+        for dt in self.dataclass_types:
+            for f in fields(dt):
+                if not f.init:
+                    continue
+                tp = _base_type(f.type if not isinstance(f.type, str) else eval(f.type, vars(__import__("typing")) | {"Optional": Optional}))
+                default = f.default if f.default is not dataclasses.MISSING else None
+                kwargs: dict = {"help": f.metadata.get("help", "")}
+                if tp is bool:
+                    kwargs.update(type=_strbool, nargs="?", const=True, default=default)
+                else:
+                    kwargs.update(type=tp, default=default)
+                self.add_argument("--" + f.name, **kwargs)
+
+    def parse_args_into_dataclasses(self, args=None, return_remaining_strings=False) -> Tuple[Any, ...]:
+        ns, remaining = self.parse_known_args(args)
+        outs = []
+        for dt in self.dataclass_types:
+            keys = {f.name for f in fields(dt) if f.init}
+            outs.append(dt(**{k: v for k, v in vars(ns).items() if k in keys}))
+        if return_remaining_strings:
+            return (*outs, remaining)
+        if remaining:
+            raise ValueError(f"Some specified arguments are not used by the HfArgumentParser: {remaining}")
+        return tuple(outs)

@@ -44,7 +44,7 @@ class LlamaConfig:
 
     @staticmethod
     def tiny(**kw):
-        d = dict(vocab_size=512, hidden_size=128, intermediate_size=352, num_hidden_layers=2, num_attention_heads=2, max_position_embeddings=128)
+        d = dict(vocab_size=512, hidden_size=128, intermediate_size=352, num_hidden_layers=2, num_attention_heads=2, max_position_embeddings=512)
         d.update(kw)
         return LlamaConfig(**d)
 
@@ -68,7 +68,7 @@ class OPTConfig:
 
     @staticmethod
     def tiny(**kw):
-        d = dict(vocab_size=512, hidden_size=128, ffn_dim=512, num_hidden_layers=2, num_attention_heads=2, max_position_embeddings=128)
+        d = dict(vocab_size=512, hidden_size=128, ffn_dim=512, num_hidden_layers=2, num_attention_heads=2, max_position_embeddings=512)
         d.update(kw)
         return OPTConfig(**d)
 

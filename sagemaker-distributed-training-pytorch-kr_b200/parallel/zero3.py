@@ -107,7 +107,7 @@ class Zero3Engine:
                 if id(p) in seen or not p.requires_grad:
                     continue
                 seen.add(id(p))
-                if p.numel() <= persistence_threshold:
+                if p.numel() <= persistence_threshold or getattr(p, "_zero3_persistent", False):
                     self.persistent.append(p)
                     continue
                 ps.append(p); pn.append(n)
