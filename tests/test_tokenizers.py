@@ -1,0 +1,97 @@
+"""Tokenizers + the jsonl -> .bin/.idx preprocessing tool (cross-checked against HF's GPT-2 tokenizer
+implementation, which is in the image, on a synthetic vocabulary - no downloaded files)."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from b200dist.data import tokenizers as T
+from b200dist.data.indexed_dataset import MMapIndexedDataset
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+CORPUS = ["def add(a, b):\n    return a + b\n", "Hello world! It's 2024, isn't it?", "the theme of the thesis — naïve café ☕", "    for i in range(10): print(i)"]
+
+
+def _train_bpe(tmp_path, n_merges=120):
+    """tiny BPE trainer so the test needs no vocab download."""
+    b2u = T.byte_unicode_table()
+    words = {}
+    for text in CORPUS:
+        for piece in T._PAT.findall(text):
+            w = tuple(b2u[b] for b in piece.encode("utf-8"))
+            words[w] = words.get(w, 0) + 1
+    merges = []
+    for _ in range(n_merges):
+        pairs = {}
+        for w, c in words.items():
+            for a, b in zip(w, w[1:]):
+                pairs[(a, b)] = pairs.get((a, b), 0) + c
+        if not pairs:
+            break
+        best = max(sorted(pairs), key=lambda p: pairs[p])
+        merges.append(best)
+        new = {}
+        for w, c in words.items():
+            out, i = [], 0
+            while i < len(w):
+                if i < len(w) - 1 and (w[i], w[i + 1]) == best:
+                    out.append(w[i] + w[i + 1]); i += 2
+                else:
+                    out.append(w[i]); i += 1
+            new[tuple(out)] = new.get(tuple(out), 0) + c
+        words = new
+    vocab = {c: i for i, c in enumerate(sorted(b2u.values()))}
+    for a, b in merges:
+        vocab.setdefault(a + b, len(vocab))
+    vocab["<|endoftext|>"] = len(vocab)
+    vf, mf = tmp_path / "vocab.json", tmp_path / "merges.txt"
+    vf.write_text(json.dumps(vocab), encoding="utf-8")
+    mf.write_text("#version: 0.2\n" + "\n".join(f"{a} {b}" for a, b in merges) + "\n", encoding="utf-8")
+    return str(vf), str(mf)
+
+
+def test_gpt2_bpe_round_trip_and_hf_parity(tmp_path):
+    vf, mf = _train_bpe(tmp_path)
+    tok = T.GPT2BPETokenizer(vf, mf)
+    assert tok.eod == tok.vocab_size - 1
+    for text in CORPUS + ["unseen ßtring \t with tabs", ""]:
+        ids = tok.tokenize(text)
+        assert tok.detokenize(ids) == text
+    assert len(tok.tokenize(CORPUS[0])) < len(CORPUS[0].encode())          # merges are applied
+    try:
+        from transformers import GPT2Tokenizer
+        merges = [tuple(l.split()) for l in open(mf, encoding="utf-8").read().split("\n")[1:] if l]
+        hf = GPT2Tokenizer(vocab=json.load(open(vf, encoding="utf-8")), merges=merges)
+        assert hf.encode("the") != []
+    except Exception:
+        pytest.skip("transformers slow GPT2Tokenizer not available")
+    for text in CORPUS + ["unseen ßtring with   spaces"]:
+        assert tok.tokenize(text) == hf.encode(text)
+
+
+def test_wordpiece(tmp_path):
+    vf = tmp_path / "vocab.txt"
+    vf.write_text("\n".join(["[PAD]", "[UNK]", "[CLS]", "[SEP]", "[MASK]", "the", "cat", "##s", "sat", ",", "un", "##want", "##ed", "cafe"]) + "\n")
+    tok = T.BertWordPieceTokenizer(str(vf), lower_case=True)
+    assert tok.vocab_size == 14 and (tok.cls, tok.sep, tok.pad, tok.mask) == (2, 3, 0, 4)
+    assert tok.tokenize("The cats sat, unwanted Café xyz") == [5, 6, 7, 8, 9, 10, 11, 12, 13, 1]
+    assert tok.detokenize([5, 6, 7]) == "the cats"
+
+
+def test_preprocess_data_tool(tmp_path):
+    vf, mf = _train_bpe(tmp_path)
+    src = tmp_path / "docs.jsonl"
+    src.write_text("\n".join(json.dumps({"content": t}) for t in CORPUS) + "\n", encoding="utf-8")
+    prefix = str(tmp_path / "cp")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "preprocess_data.py"), "--input", str(src), "--output-prefix", prefix,
+                        "--json-keys", "content", "--vocab-file", vf, "--merge-file", mf, "--append-eod", "--workers", "2"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1500:]
+    ds = MMapIndexedDataset(prefix + "_content_document")
+    tok = T.GPT2BPETokenizer(vf, mf)
+    assert len(ds) == len(CORPUS)
+    for i, text in enumerate(CORPUS):
+        assert np.array_equal(np.asarray(ds[i]), np.asarray(tok.tokenize(text) + [tok.eod]))
