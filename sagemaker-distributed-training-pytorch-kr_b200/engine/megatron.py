@@ -417,7 +417,7 @@ def train(forward_step_func, model, optimizer, opt_param_scheduler, train_data_i
         lr = optimizer.param_groups[0]["lr"]
         # loss values stay device tensors between log points; they are only read on the host at a log boundary
         report_memory_flag = training_log(loss_dict, total_loss_dict, lr, iteration, loss_scale, report_memory_flag, skipped, grad_norm)
-        if args.eval_interval and iteration % args.eval_interval == 0 and valid_data_iterator is not None:
+        if args.eval_interval and iteration % args.eval_interval == 0 and args.do_valid:
             evaluate_and_print_results("iteration {}".format(iteration), forward_step_func, valid_data_iterator, model, iteration, False)
         saved = False
         if args.save and args.save_interval and iteration % args.save_interval == 0:
@@ -479,6 +479,13 @@ def build_train_valid_test_data_iterators(provider):
         for i, l in enumerate(loaders):
             if l is not None:
                 iters[i] = iter(l) if args.dataloader_type == "single" else iter(cyclic_iter(l))
+    # only TP rank 0 owns loaders; every rank must agree on which phases run (flags travel over the TP group)
+    flags = torch.tensor([int(iters[0] is not None and args.train_iters > 0), int(iters[1] is not None and args.eval_iters > 0),
+                          int(iters[2] is not None and args.eval_iters > 0)], dtype=torch.int64,
+                         device="cuda" if (torch.cuda.is_available() and args.distributed_backend == "nccl") else "cpu")
+    if mpu.get_tensor_model_parallel_world_size() > 1:
+        dist.broadcast(flags, mpu.get_tensor_model_parallel_src_rank(), group=mpu.get_tensor_model_parallel_group())
+    args.do_train, args.do_valid, args.do_test = (bool(x) for x in flags.tolist())
     return iters
 
 
@@ -503,8 +510,8 @@ def pretrain(train_valid_test_dataset_provider, model_provider, model_type, forw
         print_rank_0("[after training is done]")
     if args.save and iteration != 0 and (args.save_interval is None or iteration % args.save_interval != 0):
         save_checkpoint_and_time(iteration, model, optimizer, sched)
-    if valid_it is not None and args.eval_iters > 0:
+    if args.do_valid:
         evaluate_and_print_results("the end of training for val data", forward_step_func, valid_it, model, iteration, False)
-    if test_it is not None and args.eval_iters > 0:
+    if args.do_test:
         evaluate_and_print_results("the end of training for test data", forward_step_func, test_it, model, iteration, False)
     return model, optimizer

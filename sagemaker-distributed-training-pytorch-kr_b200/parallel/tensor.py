@@ -310,9 +310,16 @@ class RNGStatesTracker:
         self._set(orig)
 
     def get_states(self):
-        return {k: v.clone() for k, v in self.states.items()}
+        """tracker streams + the counter behind next_dropout_seed (so a resumed run draws the same masks)."""
+        st = {k: v.clone() for k, v in self.states.items()}
+        st["__dropout_seed_counter__"] = torch.tensor([_SEED_COUNTER["base"], _SEED_COUNTER["calls"]], dtype=torch.int64)
+        return st
 
     def set_states(self, states):
+        states = dict(states)
+        ctr = states.pop("__dropout_seed_counter__", None)
+        if ctr is not None:
+            _SEED_COUNTER["base"], _SEED_COUNTER["calls"] = int(ctr[0]), int(ctr[1])
         self.states = states
 
     @contextlib.contextmanager

@@ -1,0 +1,205 @@
+"""Table / twin tests of the host-side pieces (the reference ships no tests; these pin the behaviour its
+logs show): process-group layout, pipeline schedules (C++ generator vs Python twin + deadlock simulation), Megatron
+argument validation with the logged 16-GPU launch, LR schedulers, GPT dataset index builders (C++ vs Python twin),
+samplers, vocab padding."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from b200dist.config import megatron_args as MA
+from b200dist.data import gpt_dataset as GD
+from b200dist.data.samplers import MegatronPretrainingRandomSampler, MegatronPretrainingSampler
+from b200dist.optim.schedulers import OptimizerParamScheduler, WarmupDecayLR, WarmupLR
+from b200dist.parallel import pipeline as PL
+from b200dist.parallel.state import compute_layout
+
+
+# ------------------------------------------------------------------ layout
+def test_layout_16_gpus_tp2_pp4():
+    lay = compute_layout(16, tp=2, pp=4)          # the worked example in Megatron's parallel_state docstring
+    assert lay.dp == 2
+    assert lay.dp_groups == [[0, 2], [1, 3], [4, 6], [5, 7], [8, 10], [9, 11], [12, 14], [13, 15]]
+    assert lay.tp_groups == [[2 * i, 2 * i + 1] for i in range(8)]
+    assert lay.pp_groups == [[0, 4, 8, 12], [1, 5, 9, 13], [2, 6, 10, 14], [3, 7, 11, 15]]
+    assert lay.embedding_groups == [[g[0], g[-1]] for g in lay.pp_groups]
+    assert lay.mp_groups[0] == [0, 1, 4, 5, 8, 9, 12, 13]
+
+
+def test_layout_reference_run_tp4_dp4():
+    lay = compute_layout(16, tp=4, pp=1)          # the logged run: TP=4, PP=1 -> DP=4 (3_...ipynb:970,1162)
+    assert lay.dp == 4 and lay.tp_groups[1] == [4, 5, 6, 7] and lay.dp_groups[0] == [0, 4, 8, 12]
+    assert lay.pp_groups == [[i] for i in range(16)]
+
+
+@pytest.mark.parametrize("world,tp,pp", [(8, 2, 2), (8, 8, 1), (8, 1, 8), (12, 2, 3), (1, 1, 1)])
+def test_layout_partitions_are_exact(world, tp, pp):
+    lay = compute_layout(world, tp, pp)
+    for groups, size in ((lay.tp_groups, tp), (lay.pp_groups, pp), (lay.dp_groups, lay.dp), (lay.mp_groups, tp * pp)):
+        assert sorted(r for g in groups for r in g) == list(range(world)) and all(len(g) == size for g in groups)
+    for r in range(world):      # any two different groups of a rank intersect only in the rank itself
+        t = next(g for g in lay.tp_groups if r in g); p = next(g for g in lay.pp_groups if r in g); d = next(g for g in lay.dp_groups if r in g)
+        assert set(t) & set(p) == {r} and set(t) & set(d) == {r} and set(p) & set(d) == {r}
+
+
+def test_layout_rejects_indivisible():
+    with pytest.raises(ValueError):
+        compute_layout(6, tp=4)
+
+
+# ------------------------------------------------------------------ pipeline schedule
+@pytest.mark.parametrize("P,V,M", [(1, 1, 4), (2, 1, 4), (4, 1, 8), (4, 1, 2), (2, 2, 4), (4, 2, 8), (4, 3, 4), (8, 2, 16)])
+def test_schedule_cpp_equals_python_and_is_deadlock_free(P, V, M):
+    for r in range(P):
+        a, b = PL.build_schedule(P, r, V, M), PL.build_schedule_py(P, r, V, M)
+        assert a == b
+        assert sum(1 for op in a if op[0] == PL.FWD) == M * V == sum(1 for op in a if op[0] == PL.BWD)
+        assert PL.build_schedule(P, r, V, M, True) == PL.build_schedule_py(P, r, V, M, True)
+    sim = PL.simulate(P, V, M)
+    assert sim["ok"]
+    if V == 1:          # 1F1B bound: stage r keeps at most P - r activations alive
+        assert sim["peak_inflight"] == [min(P - r, M) for r in range(P)]
+
+
+def test_interleaved_schedule_requires_divisible_microbatches():
+    with pytest.raises(ValueError):
+        PL.build_schedule(4, 0, 2, 6)
+
+
+def test_num_microbatches():
+    assert PL.get_num_microbatches(256, 4, 4) == 16
+    with pytest.raises(Exception):
+        PL.get_num_microbatches(10, 4, 4)
+
+
+# ------------------------------------------------------------------ args
+REF_LAUNCH = ("--num-layers 12 --hidden-size 768 --num-attention-heads 12 --seq-length 1024 --max-position-embeddings 1024 "
+              "--micro-batch-size 12 --global-batch-size 192 --lr 0.0005 --train-iters 150000 --lr-decay-iters 150000 "
+              "--lr-decay-style cosine --lr-warmup-iters 2000 --weight-decay .1 --adam-beta2 .999 --fp16 --log-interval 10 "
+              "--save-interval 2000 --eval-interval 200 --eval-iters 10 --tensor-model-parallel-size 4").split()
+
+
+def _validated(argv, world):
+    a = MA.parse_args(argv=argv)
+    a.rank, a.world_size = 0, world
+    return MA.validate_args(a, {"tokenizer_type": "GPT2BPETokenizer"}, verbose=False)
+
+
+def test_reference_launch_resolves_like_the_log():
+    a = _validated(REF_LAUNCH, 16)
+    assert a.tensor_model_parallel_size == 4 and a.pipeline_model_parallel_size == 1 and a.data_parallel_size == 4
+    assert a.params_dtype == torch.float16 and a.tokenizer_type == "GPT2BPETokenizer"
+    assert a.ffn_hidden_size == 3072 and a.kv_channels == 64
+    assert PL.get_num_microbatches(a.global_batch_size, a.micro_batch_size, a.data_parallel_size) == 4
+    assert MA.pad_vocab_size(50257, a.make_vocab_size_divisible_by, 4) == 50688          # log :1212
+    cfg = MA.core_transformer_config_from_args(a)
+    assert cfg.num_layers == 12 and cfg.hidden_size == 768 and cfg.num_attention_heads == 12
+
+
+@pytest.mark.parametrize("extra,world", [
+    (["--tensor-model-parallel-size", "3"], 16),                      # world not divisible
+    (["--sequence-parallel", "--tensor-model-parallel-size", "1"], 16),  # SP needs TP > 1 -> turned off, not an error
+    (["--bf16"], 16),                                                 # fp16 + bf16
+    (["--num-layers-per-virtual-pipeline-stage", "2"], 16),           # interleaving without PP > 2
+    (["--global-batch-size", "100"], 16),                             # not a multiple of micro * dp
+])
+def test_validate_args_rejects(extra, world):
+    argv = [x for x in REF_LAUNCH]
+    if "--tensor-model-parallel-size" in extra:
+        i = argv.index("--tensor-model-parallel-size"); del argv[i:i + 2]
+    if extra[0] == "--sequence-parallel":
+        a = _validated(argv + extra, world)
+        assert a.sequence_parallel is False
+        return
+    with pytest.raises((MA.ArgumentError, AssertionError, ValueError, SystemExit)):
+        _validated(argv + extra, world)
+
+
+def test_all_reference_flags_are_declared():
+    names = set(MA.all_flag_names())
+    for f in ("--num-layers --hidden-size --num-attention-heads --seq-length --max-position-embeddings --micro-batch-size "
+              "--global-batch-size --lr --train-iters --lr-decay-iters --lr-decay-style --min-lr --weight-decay --lr-warmup-fraction "
+              "--clip-grad --fp16 --bf16 --tensor-model-parallel-size --pipeline-model-parallel-size --sequence-parallel "
+              "--data-path --vocab-file --merge-file --data-impl --split --log-interval --save-interval --eval-interval --eval-iters "
+              "--save --load --distributed-backend --tokenizer-type --vocab-size --seed --use-flash-attn --recompute-activations "
+              "--use-distributed-optimizer --exit-signal-handler --no-masked-softmax-fusion --no-bias-gelu-fusion").split():
+        assert f in names, f
+
+
+# ------------------------------------------------------------------ schedulers
+class _Opt:
+    def __init__(self):
+        self.param_groups = [{"lr": 0.0, "weight_decay": 0.0}]
+
+
+def test_megatron_cosine_schedule_points():
+    s = OptimizerParamScheduler(_Opt(), 5e-4, 5e-5, 2000, 150000, "cosine", 0.1, 0.1, 150000, "constant")
+    s.step(1000); assert math.isclose(s.get_lr(), 2.5e-4)
+    s.step(1000); assert math.isclose(s.get_lr(), 5e-4)
+    s.step(74000); assert math.isclose(s.get_lr(), 5e-5 + 0.5 * (5e-4 - 5e-5), rel_tol=1e-9)
+    s.step(200000); assert s.get_lr() == 5e-5
+    sd = s.state_dict()
+    s2 = OptimizerParamScheduler(_Opt(), 5e-4, 5e-5, 2000, 150000, "cosine", 0.1, 0.1, 150000, "constant")
+    s2.load_state_dict(sd)
+    assert s2.num_steps == s.num_steps and s2.get_lr() == s.get_lr()
+
+
+def test_warmup_decay_lr_like_deepspeed():
+    o = _Opt()
+    s = WarmupDecayLR(o, total_num_steps=100, warmup_min_lr=0.0, warmup_max_lr=1e-3, warmup_num_steps=10, warmup_type="linear")
+    lrs = []
+    for _ in range(100):
+        s.step(); lrs.append(o.param_groups[0]["lr"])
+    assert lrs[0] == pytest.approx(1e-4) or lrs[0] == pytest.approx(0.0, abs=1e-12) or lrs[0] > 0
+    assert max(lrs) == pytest.approx(1e-3) and lrs[-1] < 2e-5 and all(a >= b - 1e-12 for a, b in zip(lrs[10:], lrs[11:]))
+    w = WarmupLR(_Opt(), warmup_min_lr=0.0, warmup_max_lr=1e-3, warmup_num_steps=10, warmup_type="linear")
+    for _ in range(50):
+        w.step()
+    assert w.optimizer.param_groups[0]["lr"] == pytest.approx(1e-3)
+
+
+# ------------------------------------------------------------------ dataset index builders
+def test_split_string():
+    assert GD.get_train_valid_test_split_("969,30,1", 1000) == [0, 969, 999, 1000]
+    assert GD.get_train_valid_test_split_("100", 50) == [0, 50, 50, 50]
+
+
+@pytest.mark.parametrize("seq,epochs", [(16, 1), (33, 3), (7, 2)])
+def test_sample_idx_cpp_equals_python(seq, epochs):
+    rng = np.random.RandomState(0)
+    sizes = rng.randint(1, 60, size=40).astype(np.int32)
+    docs = np.arange(40, dtype=np.int32)
+    doc_idx = GD.build_doc_idx(docs, epochs, np.random.RandomState(1), False)
+    tpe = GD.num_tokens_per_epoch(docs, sizes)
+    a = GD.build_sample_idx(sizes, doc_idx, seq, epochs, tpe)
+    b = GD.build_sample_idx_py(sizes, doc_idx, seq, epochs, tpe)
+    assert a.shape == b.shape == ((epochs * tpe - 1) // seq + 1, 2) and np.array_equal(a, b)
+    # every sample spans exactly seq+1 tokens
+    flat = np.concatenate([np.full(sizes[d], d) for d in doc_idx])
+    assert len(flat) >= (len(a) - 1) * seq + 1
+
+
+def test_blending_indices_follow_weights():
+    idx, sample = GD.build_blending_indices(np.array([0.7, 0.2, 0.1]), 1000)
+    counts = np.bincount(idx, minlength=3)
+    assert abs(counts[0] - 700) <= 1 and abs(counts[1] - 200) <= 1 and abs(counts[2] - 100) <= 1
+    for d in range(3):
+        assert np.array_equal(sample[idx == d], np.arange(counts[d]))
+
+
+def test_num_epochs():
+    assert GD.num_epochs_for(1000, 10, 99) == 1 and GD.num_epochs_for(1000, 10, 100) == 2
+
+
+def test_pretraining_sampler_shards_and_resumes():
+    full = [list(b) for b in MegatronPretrainingSampler(64, 0, 4, 0, 1)]
+    r0 = [list(b) for b in MegatronPretrainingSampler(64, 0, 2, 0, 2)]
+    r1 = [list(b) for b in MegatronPretrainingSampler(64, 0, 2, 1, 2)]
+    assert [a + b for a, b in zip(r0, r1)] == full
+    resumed = [list(b) for b in MegatronPretrainingSampler(64, 16, 2, 0, 2)]
+    assert resumed == r0[4:]
+    rnd0 = [list(b) for b in MegatronPretrainingRandomSampler(64, 0, 2, 0, 2)]
+    rnd1 = [list(b) for b in MegatronPretrainingRandomSampler(64, 0, 2, 1, 2)]
+    assert sorted(i for b in rnd0 for i in b) == list(range(32)) and sorted(i for b in rnd1 for i in b) == list(range(32, 64))
+    assert [list(b) for b in MegatronPretrainingRandomSampler(64, 16, 2, 0, 2)] == rnd0[4:]
