@@ -118,6 +118,20 @@ def check_gemm(quick):
             bt = b if bmn else b.t()
             ms_ref = timeit(lambda: torch.matmul(a.t() if amn else a, bt, out=o), flush=flush)
             print(f"time gemm {tag:12s} M{M} N{Nn} K{K}: {ms:.4f} ms {tf:7.1f} TFLOP/s = {tf / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak | torch.matmul {ms_ref:.4f} ms", flush=True)
+        # fused epilogues on the GPT-2-small shapes (the model's actual fwd / dgrad calls)
+        for (M, Nn, K, bmn, epi, tag) in [(12288, 2304, 768, False, N.EPI_BIAS, "qkv  bias"), (12288, 768, 768, False, N.EPI_BIAS_RESIDUAL, "proj bias+res"),
+                                          (12288, 3072, 768, False, N.EPI_BIAS_GELU_DUAL, "fc1  gelu dual"), (12288, 768, 3072, False, N.EPI_BIAS_RESIDUAL, "fc2  bias+res"),
+                                          (12288, 3072, 768, True, N.EPI_DGELU, "fc2 dgrad dgelu"), (12288, 768, 768, True, N.EPI_NONE, "proj dgrad")]:
+            a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+            b = torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16)
+            o = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
+            o2 = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16) if epi == N.EPI_BIAS_GELU_DUAL else None
+            bias = torch.randn(Nn, device=dev, dtype=torch.bfloat16) if epi in (N.EPI_BIAS, N.EPI_BIAS_RESIDUAL, N.EPI_BIAS_GELU_DUAL) else None
+            aux = torch.randn(M, Nn, device=dev, dtype=torch.bfloat16) if epi in (N.EPI_BIAS_RESIDUAL, N.EPI_DGELU) else None
+            ms = timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o, epilogue=epi, bias=bias, aux=aux, out2=o2), flush=flush)
+            ms0 = timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o), flush=flush)
+            tf = 2.0 * M * Nn * K / ms / 1e9
+            print(f"time gemm+epi {tag:16s} M{M} N{Nn} K{K}: {ms:.4f} ms {tf:7.1f} TFLOP/s (plain epilogue {ms0:.4f} ms)", flush=True)
         for (Mo, No, Kr, tag) in [(2304, 768, 12288, "qkv wgrad"), (768, 768, 12288, "proj wgrad"), (3072, 768, 12288, "fc1 wgrad")]:
             dy = torch.randn(Kr, Mo, device=dev, dtype=torch.bfloat16)
             x = torch.randn(Kr, No, device=dev, dtype=torch.bfloat16)
@@ -142,6 +156,24 @@ def check_norm(quick):
         report(f"norm bwd dgamma rows{rows} H{H}", dg, dgr, 2e-3)
         if not rms:
             report(f"norm bwd dbeta rows{rows} H{H}", db, dbr, 2e-3)
+        # residual-gradient fusion + accumulate into existing fp32 buffers (main_grad path)
+        dres = torch.randn(rows, H, device=dev, dtype=torch.bfloat16)
+        mg_w, mg_b = torch.ones(H, device=dev), (None if rms else torch.ones(H, device=dev))
+        dx2, _, _ = N.norm_bwd(dy, x, g, mean, rstd, rms, dgamma=mg_w, dbeta=mg_b, accumulate=not rms, dres=dres)
+        dx2r, dg2r, db2r = N.norm_bwd(cpu(dy), cpu(x), cpu(g), meanr, rstdr, rms, dres=cpu(dres))
+        report(f"norm bwd +dres dx rows{rows} H{H} rms={int(rms)}", dx2, dx2r, 3e-2)
+        report(f"norm bwd +dres dgamma(acc) rows{rows} H{H}", mg_w, dg2r + (0.0 if rms else 1.0), 2e-3)
+    if not quick:
+        x = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
+        dy = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
+        g = torch.ones(768, device=dev, dtype=torch.bfloat16)
+        b = torch.zeros(768, device=dev, dtype=torch.bfloat16)
+        _, mean, rstd = N.norm_fwd(x, g, b, 1e-5)
+        mg_w, mg_b = torch.zeros(768, device=dev), torch.zeros(768, device=dev)
+        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+        ms = timeit(lambda: N.norm_bwd(dy, x, g, mean, rstd, dgamma=mg_w, dbeta=mg_b, accumulate=True, dres=dy), flush=flush)
+        gb = 4 * x.numel() * 2 / ms / 1e6
+        print(f"time layernorm bwd(+dres, +fold) 12288x768: {ms:.4f} ms {gb:.0f} GB/s = {gb / PEAKS['hbm_gbs']:.3f} of measured copy bw (L2 flushed)")
     if not quick:
         x = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
         g = torch.ones(768, device=dev, dtype=torch.bfloat16)

@@ -325,28 +325,35 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 // ------------------------------------------------------------------------------------------
 // backward preprocess: delta[b,h,s] = sum_d dO * O
 // ------------------------------------------------------------------------------------------
-__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
-                                  float* __restrict__ delta, int seqlen, int batch, int heads, int D,
-                                  long long o_ss, long long o_sb, long long o_sh, long long do_ss, long long do_sb,
-                                  long long do_sh) {
-  // one warp per (s, b, h)
-  const long long gw = (blockIdx.x * (long long)blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+// D / 8 lanes per (s, b, h) row, one 16-byte load of O and of dO per lane (rows of neighbouring heads are
+// contiguous, so a warp reads 512 B runs); memory-level parallelism comes from the resident CTAs.
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
+                  float* __restrict__ delta, int seqlen, int batch, int heads, int D,
+                  long long o_ss, long long o_sb, long long o_sh, long long do_ss, long long do_sb,
+                  long long do_sh) {
+  const int lpr = D >> 3;                                   // lanes per row: 8 (D = 64) or 16 (D = 128)
+  const long long gt = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  const long long row = gt / lpr;
+  const int sub = static_cast<int>(gt % lpr);
   const long long total = static_cast<long long>(seqlen) * batch * heads;
-  if (gw >= total) return;
-  const int h = static_cast<int>(gw % heads);
-  const int b = static_cast<int>((gw / heads) % batch);
-  const int s = static_cast<int>(gw / (static_cast<long long>(heads) * batch));
-  const __nv_bfloat16* op = o + s * o_ss + b * o_sb + h * o_sh;
-  const __nv_bfloat16* dp = dout + s * do_ss + b * do_sb + h * do_sh;
   float acc = 0.f;
-  for (int d = lane * 2; d < D; d += 64) {
-    float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(op + d));
-    float2 g = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(dp + d));
-    acc += a.x * g.x + a.y * g.y;
+  int h = 0, b = 0, s = 0;
+  if (row < total) {
+    h = static_cast<int>(row % heads);
+    b = static_cast<int>((row / heads) % batch);
+    s = static_cast<int>(row / (static_cast<long long>(heads) * batch));
+    const uint4 qa = *reinterpret_cast<const uint4*>(o + s * o_ss + b * o_sb + h * o_sh + sub * 8);
+    const uint4 qg = *reinterpret_cast<const uint4*>(dout + s * do_ss + b * do_sb + h * do_sh + sub * 8);
+    const uint32_t a4[4] = {qa.x, qa.y, qa.z, qa.w}, g4[4] = {qg.x, qg.y, qg.z, qg.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 a = unpack_bf16x2(a4[i]), g = unpack_bf16x2(g4[i]);
+      acc = fmaf(a.x, g.x, fmaf(a.y, g.y, acc));
+    }
   }
-  acc = warp_sum(acc);
-  if (lane == 0) delta[(static_cast<size_t>(b) * heads + h) * seqlen + s] = acc;
+  for (int off = lpr >> 1; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (row < total && sub == 0) delta[(static_cast<size_t>(b) * heads + h) * seqlen + s] = acc;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -683,8 +690,8 @@ extern "C" int b2_attn_bwd(const void* q, const void* k, const void* v, const vo
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (D != 64) { b2host::set_error("attn_bwd: head_dim must be 64 (got %d)", D); return -1; }
   {
-    long long warps = static_cast<long long>(seqlen) * batch * heads;
-    long long blocks = (warps * 32 + 255) / 256;
+    long long rows = static_cast<long long>(seqlen) * batch * heads;
+    long long blocks = (rows * (D / 8) + 255) / 256;
     attn_delta_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(
         static_cast<const __nv_bfloat16*>(o), static_cast<const __nv_bfloat16*>(dout), delta, seqlen, batch, heads, D,
         o_ss, o_sb, o_sh, do_ss, do_sb, do_sh);

@@ -6,9 +6,12 @@
 //   warp 0    : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem ring, mbarrier tx-count)
 //   warp 1    : MMA issuer    (one thread issues tcgen05.mma kind::f16 128xBNx16, commits to mbarriers)
 //   warp 2    : TMEM allocator
-//   warps 4-7 : epilogue      (tcgen05.ld 32x32b -> fused epilogue -> swizzled smem -> TMA store /
-//                              TMA reduce-add); overlapped with the next tile's mainloop through a
-//                              double-buffered TMEM accumulator.
+//   warps 4-11: epilogue      two independent 128-thread teams (warps 4-7 / 8-11) take alternating 64-column
+//                              chunks of the accumulator: tcgen05.ld 32x32b -> fused epilogue -> swizzled smem ->
+//                              TMA store / TMA reduce-add.  Two teams = two warps per SM sub-partition, so one
+//                              team's TMEM / global-load / TMA-store latency hides under the other's math; the
+//                              whole epilogue overlaps the next tile's mainloop through a double-buffered TMEM
+//                              accumulator.
 // Operand majors are expressed purely through the UMMA descriptors, so forward (x W^T), dgrad
 // (dy W) and wgrad (dy^T x) all read the tensors in place - no transposes are materialised.
 //
@@ -25,8 +28,8 @@ namespace {
 constexpr int BM = 128;
 constexpr int BK = 64;          // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int NUM_THREADS = 256;
-constexpr int EPI_THREADS = 128;
+constexpr int NUM_THREADS = 384;
+constexpr int EPI_THREADS = 128;   // per team
 constexpr int EPI_WARP0 = 4;
 constexpr int STAGE_CHUNK_BYTES = 128 * 128;  // 128 rows x 128 B staging tile
 constexpr int SMEM_MAIN_BYTES = 192 * 1024;
@@ -122,7 +125,7 @@ B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t e
   if (threadIdx.x >= 32) {
     // warps 1..7: copy this rank's OWN shard into the gathered operand (needed by backward's wgrad, not by the
     // GEMM of this kernel, which reads own rows in place) - plain coalesced 16-byte copies, off the critical path
-    const int t = threadIdx.x - 32, nt = NUM_THREADS - 32;
+    const int t = threadIdx.x - 32, nt = NUM_THREADS - 32;   // warps 1..11
     const uint4* src = static_cast<const uint4*>(p.f_peer[p.f_rank]);
     uint4* dst = reinterpret_cast<uint4*>(p.f_xg + static_cast<long long>(p.f_rank) * p.f_shard_rows * p.f_row_bytes);
     const long long total = static_cast<long long>(p.f_shard_rows) * p.f_row_bytes / 16;
@@ -236,18 +239,25 @@ B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers
   }
 }
 
+B2_DEVICE float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 B2_DEVICE float gelu_tanh(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   float u = k0 * x * (1.f + k1 * x * x);
-  float t = 1.f - 2.f / (1.f + __expf(2.f * u));  // tanh(u)
-  return 0.5f * x * (1.f + t);
+  float t = tanh_approx(u);                        // one MUFU op; 2^-11 relative error, below bf16/fp16 rounding
+  const float hx = 0.5f * x;
+  return fmaf(hx, t, hx);
 }
 B2_DEVICE float gelu_tanh_grad(float x) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-  float u = k0 * x * (1.f + k1 * x * x);
-  float t = 1.f - 2.f / (1.f + __expf(2.f * u));
-  float du = k0 * (1.f + 3.f * k1 * x * x);
-  return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+  const float x2 = x * x;
+  float u = k0 * x * fmaf(k1, x2, 1.f);
+  float t = tanh_approx(u);
+  float du = fmaf(3.f * k0 * k1, x2, k0);
+  return fmaf(0.5f * x * fmaf(-t, t, 1.f), du, fmaf(0.5f, t, 0.5f));
 }
 B2_DEVICE uint32_t pack2(float lo, float hi, int fmt) {
   if (fmt == 1) return pack_bf16x2(lo, hi);
@@ -286,6 +296,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGES = SMEM_MAIN_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
+  // GEMM->RS keeps one epilogue team: its arrival-counter protocol is per tile and led by one thread
+  constexpr int TEAMS = (FUSE == FUSE_RS) ? 1 : 2;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -330,7 +342,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], EPI_THREADS);
+      mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS);
     }
     mbar_fence_init();
   }
@@ -428,11 +440,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp >= EPI_WARP0) {
+  } else if (warp >= EPI_WARP0 && warp < EPI_WARP0 + 4 * TEAMS) {
     // ===================== epilogue =====================
-    const int et = threadIdx.x - EPI_WARP0 * 32;   // 0..127 == accumulator row
-    const int ew = warp - EPI_WARP0;               // TMEM lane quarter
+    const int team = (warp - EPI_WARP0) >> 2;      // chunks team, team + TEAMS, ... of every tile
+    const int ew = (warp - EPI_WARP0) & 3;         // TMEM lane quarter (a warp may only touch lanes 32*(warp%4)..+31)
+    const int et = ew * 32 + lane;                 // 0..127 == accumulator row
     const bool leader = (et == 0);
+    const int bar_id = 1 + team;
+    uint8_t* team_buf = epi_buf + team * STAGE_CHUNK_BYTES;   // TEAMS == 2: one staging tile per team
     const int fmt = p.fmt;
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
@@ -453,16 +468,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // 32-column chunks of fp32 (128 B rows)
         constexpr int NCH = BN / 32;
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        for (int c = team; c < NCH; c += TEAMS) {
           uint32_t v[32];
           tmem_ld_32x32b_x32(taddr + c * 32, v);
           tmem_ld_wait();
-          if (c == NCH - 1) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
-          if (n0 + c * 32 >= p.N) continue;   // uniform across the CTA
-          uint8_t* sb = epi_buf + (sctr & 1) * STAGE_CHUNK_BYTES;
+          if (c + TEAMS >= NCH) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          if (n0 + c * 32 >= p.N) continue;   // uniform across the team
+          uint8_t* sb = (TEAMS == 2) ? team_buf : epi_buf + (sctr & 1) * STAGE_CHUNK_BYTES;
           ++sctr;
-          if (leader) tma_store_wait_read<1>();
-          named_bar_sync(1, EPI_THREADS);
+          if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          named_bar_sync(bar_id, EPI_THREADS);
           if (p.alpha != 1.f) {
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * p.alpha);
@@ -474,7 +489,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             *reinterpret_cast<uint4*>(rowp + ((j ^ (et & 7)) << 4)) = q;
           }
           fence_proxy_async_smem();
-          named_bar_sync(1, EPI_THREADS);
+          named_bar_sync(bar_id, EPI_THREADS);
           if (leader) {
             if (p.reduce_add) tma_reduce_add_2d(&tmC, sb, n0 + c * 32, m0);
             else              tma_store_2d(&tmC, sb, n0 + c * 32, m0);
@@ -499,18 +514,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               const uint32_t* cnt = p.f_cnt[p.f_rank] + (tm - p.f_rank * p.f_bpr);
               while (static_cast<int32_t>(ld_acquire_sys(cnt) - expected) < 0) { }
             }
-            named_bar_sync(1, EPI_THREADS);
+            named_bar_sync(bar_id, EPI_THREADS);
           }
         }
+        const bool use_aux = (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU);
 #pragma unroll 1
-        for (int c = 0; c < NCH; ++c) {
+        for (int c = team; c < NCH; c += TEAMS) {
+          const int col0 = n0 + c * 64;
+          // this thread's 128 B of the aux tile (residual / pre-activation): requested before the TMEM load so
+          // the global-memory latency runs under it (and under the other team's math)
+          uint4 aq[8];
+          if (use_aux) {
+            const uint4* ap = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.aux) +
+                                                             static_cast<long long>(row) * p.ld_aux + col0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              aq[j] = (row_ok && col0 + j * 8 < p.N) ? __ldg(ap + j) : make_uint4(0u, 0u, 0u, 0u);
+          }
           uint32_t v[64];
           tmem_ld_32x32b_x32(taddr + c * 64, v);
           tmem_ld_32x32b_x32(taddr + c * 64 + 32, v + 32);
           tmem_ld_wait();
-          if (c == NCH - 1) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
-          const int col0 = n0 + c * 64;
-          if (col0 >= p.N) continue;          // uniform across the CTA
+          if (c + TEAMS >= NCH) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          if (col0 >= p.N) continue;          // uniform across the team
           float* f = reinterpret_cast<float*>(v);
           if (p.alpha != 1.f) {
 #pragma unroll
@@ -578,13 +604,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             }
           }
-          uint8_t* sb0 = epi_buf + (dual ? 0 : (sctr & 1)) * STAGE_CHUNK_BYTES;
+          // staging: TEAMS == 2 -> the team's own tile (reused once its previous TMA store has read it);
+          //          TEAMS == 1 -> ring of two tiles
+          uint8_t* sb0 = (TEAMS == 2) ? team_buf : epi_buf + (dual ? 0 : (sctr & 1)) * STAGE_CHUNK_BYTES;
           ++sctr;
-          uint8_t* sb1 = epi_buf + STAGE_CHUNK_BYTES;
-          if (leader) { if (dual) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
-          named_bar_sync(1, EPI_THREADS);
           if (dual) {
-            // pre-activation z -> C2, gelu(z) -> C
+            // pre-activation z -> C2 first, gelu(z) -> C second (through the same staging tile when TEAMS == 2)
+            uint8_t* sb1 = (TEAMS == 2) ? team_buf : epi_buf + STAGE_CHUNK_BYTES;
+            if (leader) tma_store_wait_read<0>();
+            named_bar_sync(bar_id, EPI_THREADS);
             uint8_t* rowp = sb1 + et * 128;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -592,30 +620,37 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                    pack2(f[8 * j + 4], f[8 * j + 5], fmt), pack2(f[8 * j + 6], f[8 * j + 7], fmt));
               *reinterpret_cast<uint4*>(rowp + ((j ^ (et & 7)) << 4)) = q;
             }
+            if (TEAMS == 2) {
+              fence_proxy_async_smem();
+              named_bar_sync(bar_id, EPI_THREADS);
+              if (leader) { tma_store_2d(&tmC2, sb1, col0, m0); tma_store_commit(); }
+            }
 #pragma unroll
-            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
-          } else if (p.epilogue == B2_EPI_BIAS_GELU) {
+            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);       // runs while the TMA engine reads the z tile
+            if (TEAMS == 2) {
+              if (leader) tma_store_wait_read<0>();
+              named_bar_sync(bar_id, EPI_THREADS);
+            }
+          } else {
+            if (p.epilogue == B2_EPI_BIAS_GELU) {
 #pragma unroll
-            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
-          } else if (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU) {
-            const bool is_res = (p.epilogue == B2_EPI_BIAS_RESIDUAL);
-            if (row_ok) {
-              const uint4* ap = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.aux) +
-                                                               static_cast<long long>(row) * p.ld_aux + col0);
+              for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
+            } else if (use_aux) {
+              const bool is_res = (p.epilogue == B2_EPI_BIAS_RESIDUAL);
 #pragma unroll
               for (int j = 0; j < 8; ++j) {
-                if (col0 + j * 8 < p.N) {
-                  uint4 q = __ldg(ap + j);
-                  float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
-                  float z[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, d.x, d.y};
+                const uint4 q = aq[j];
+                float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+                float z[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, d.x, d.y};
 #pragma unroll
-                  for (int e = 0; e < 8; ++e) {
-                    if (is_res) f[8 * j + e] += z[e];
-                    else        f[8 * j + e] *= gelu_tanh_grad(z[e]);
-                  }
+                for (int e = 0; e < 8; ++e) {
+                  if (is_res) f[8 * j + e] += z[e];
+                  else        f[8 * j + e] *= gelu_tanh_grad(z[e]);
                 }
               }
             }
+            if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+            named_bar_sync(bar_id, EPI_THREADS);
           }
           {
             uint8_t* rowp = sb0 + et * 128;
@@ -627,7 +662,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           }
           fence_proxy_async_smem();
-          named_bar_sync(1, EPI_THREADS);
+          named_bar_sync(bar_id, EPI_THREADS);
           if (leader) {
             if constexpr (FUSE == FUSE_RS) {
               // partial tile -> staging slot [epoch parity][this rank] on the OWNER of these rows (TMA store
@@ -638,7 +673,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               ++rs_groups;
             } else {
               tma_store_2d(&tmC, sb0, col0, m0);
-              if (dual) tma_store_2d(&tmC2, sb1, col0, m0);
+              if (dual && TEAMS == 1) tma_store_2d(&tmC2, epi_buf + STAGE_CHUNK_BYTES, col0, m0);
             }
             tma_store_commit();
           }
@@ -721,7 +756,10 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   {
     long long t256 = 1LL * tiles_m * ((N + 255) / 256);
     long long t128 = 1LL * tiles_m * ((N + 127) / 128);
-    if (N <= 128 || (t256 * (split_k > 0 ? split_k : 1) < sms && t128 > t256)) bn = 128;
+    // fp32-accumulate outputs (wgrad) fill the SMs through split-K instead, so they keep the wide tile
+    // (128x256 halves the operand traffic per MMA); everything else drops to 128 when 256 would idle SMs
+    const bool can_split = out_fp32 && accumulate && split_k <= 0;
+    if (N <= 128 || (!can_split && t256 * (split_k > 0 ? split_k : 1) < sms && t128 > t256)) bn = 128;
   }
   const int tiles_n = (N + bn - 1) / bn;
   const int num_kb = (K + BK - 1) / BK;

@@ -115,20 +115,21 @@ norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* _
   }
 }
 
-template <typename T, int TEAM, bool RMS>
-__global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM)
+template <typename T, int TEAM, bool RMS, int NV /* 8-element vectors per thread: TEAM * NV * 8 >= H */>
+__global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM, (TEAM == 32 && NV <= 3) ? 4 : 1)
 norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ gamma,
-                const float* __restrict__ mean_in, const float* __restrict__ rstd_in, T* __restrict__ dx,
-                float* __restrict__ ws /* [gridDim.x, 2, H] */, int rows, int H) {
+                const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
+                const T* __restrict__ dres /* optional: dx = dres + d(norm) (residual branch gradient) */,
+                T* __restrict__ dx, float* __restrict__ ws /* [gridDim.x, 2, H] */, int rows, int H) {
   extern __shared__ float sm[];  // TEAM == 32: [CTA_THREADS/32][2][H]
   __shared__ float red[8];
   constexpr int ROWS_PER_CTA = TEAM == 32 ? CTA_THREADS / 32 : 1;
   const int tid = TEAM == 32 ? (threadIdx.x & 31) : threadIdx.x;
   const int sub = TEAM == 32 ? (threadIdx.x >> 5) : 0;
   const int nvec = H >> 3;
-  float dg[MAXV][8], db[MAXV][8];
+  float dg[NV][8], db[NV][8];
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i)
+  for (int i = 0; i < NV; ++i)
 #pragma unroll
     for (int e = 0; e < 8; ++e) { dg[i][e] = 0.f; db[i][e] = 0.f; }
 
@@ -139,21 +140,31 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
     const T* dyr = dy + static_cast<size_t>(row) * H;
     const float mean = RMS ? 0.f : mean_in[row];
     const float rstd = rstd_in[row];
-    float xh[MAXV][8], gy[MAXV][8];
+    // the row stays in registers in its packed 16-bit form (half the registers of fp32 copies -> more CTAs per SM,
+    // more loads in flight); the second pass re-derives xhat and dy*gamma from it
+    uint4 xq[NV], dq[NV], rq[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      int vi = tid + i * TEAM;
+      if (vi < nvec) {
+        xq[i] = *reinterpret_cast<const uint4*>(xr + vi * 8);
+        dq[i] = *reinterpret_cast<const uint4*>(dyr + vi * 8);
+        if (dres != nullptr) rq[i] = *reinterpret_cast<const uint4*>(dres + static_cast<size_t>(row) * H + vi * 8);
+      }
+    }
     float s1 = 0.f, s2 = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       int vi = tid + i * TEAM;
       if (vi < nvec) {
         float xv[8], dv[8], g[8];
-        load8<T>(xr + vi * 8, xv);
-        load8<T>(dyr + vi * 8, dv);
+        load8<T>(reinterpret_cast<const T*>(&xq[i]), xv);
+        load8<T>(reinterpret_cast<const T*>(&dq[i]), dv);
         load8<T>(gamma + vi * 8, g);
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           float h = (xv[e] - mean) * rstd;
           float t = dv[e] * g[e];
-          xh[i][e] = h; gy[i][e] = t;
           s1 += t; s2 += t * h;
           dg[i][e] += dv[e] * h;
           db[i][e] += dv[e];
@@ -164,12 +175,21 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
     const float m1 = RMS ? 0.f : s1 / H, m2 = s2 / H;
     T* dxr = dx + static_cast<size_t>(row) * H;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       int vi = tid + i * TEAM;
       if (vi < nvec) {
-        float o[8];
+        float xv[8], dv[8], g[8], o[8];
+        load8<T>(reinterpret_cast<const T*>(&xq[i]), xv);
+        load8<T>(reinterpret_cast<const T*>(&dq[i]), dv);
+        load8<T>(gamma + vi * 8, g);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) o[e] = rstd * (gy[i][e] - m1 - xh[i][e] * m2);
+        for (int e = 0; e < 8; ++e) o[e] = rstd * (dv[e] * g[e] - m1 - (xv[e] - mean) * rstd * m2);
+        if (dres != nullptr) {
+          float r[8];
+          load8<T>(reinterpret_cast<const T*>(&rq[i]), r);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) o[e] += r[e];
+        }
         store8<T>(dxr + vi * 8, o);
       }
     }
@@ -179,7 +199,7 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
     // fold the per-warp partials through smem, one workspace row per CTA
     float* mine = sm + sub * 2 * H;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       int vi = tid + i * TEAM;
       if (vi < nvec) {
 #pragma unroll
@@ -195,7 +215,7 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
+    for (int i = 0; i < NV; ++i) {
       int vi = tid + i * TEAM;
       if (vi < nvec) {
 #pragma unroll
@@ -205,16 +225,33 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
   }
 }
 
-// fold workspace rows -> dgamma / dbeta (fp32, optionally accumulated: main_grad semantics)
-__global__ void norm_bwd_fold_kernel(const float* __restrict__ ws, int nparts, int H, float* __restrict__ dgamma,
-                                     float* __restrict__ dbeta, int accumulate) {
-  int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= 2 * H) return;
-  float a = 0.f;
-  for (int p = 0; p < nparts; ++p) a += ws[static_cast<size_t>(p) * 2 * H + j];
-  float* dst = j < H ? (dgamma + j) : (dbeta ? dbeta + (j - H) : nullptr);
-  if (!dst) return;
-  if (accumulate) *dst += a; else *dst = a;
+// fold workspace rows -> dgamma / dbeta (fp32, optionally accumulated: main_grad semantics).
+// One CTA per 32 columns; its 8 warps stride over the workspace rows with 4 independent loads in flight each.
+__global__ void __launch_bounds__(256)
+norm_bwd_fold_kernel(const float* __restrict__ ws, int nparts, int H, float* __restrict__ dgamma,
+                     float* __restrict__ dbeta, int accumulate) {
+  __shared__ float part[8][33];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  if (j < 2 * H) {
+    const float* col = ws + j;
+    const size_t ld = static_cast<size_t>(2) * H;
+    int p = w;
+    for (; p + 24 < nparts; p += 32) {
+      a0 += col[p * ld]; a1 += col[(p + 8) * ld]; a2 += col[(p + 16) * ld]; a3 += col[(p + 24) * ld];
+    }
+    for (; p < nparts; p += 8) a0 += col[p * ld];
+  }
+  part[w][lane] = (a0 + a1) + (a2 + a3);
+  __syncthreads();
+  if (w == 0 && j < 2 * H) {
+    float a = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a += part[k][lane];
+    float* dst = j < H ? (dgamma + j) : (dbeta ? dbeta + (j - H) : nullptr);
+    if (dst) { if (accumulate) *dst += a; else *dst = a; }
+  }
 }
 
 template <typename T, bool RMS>
@@ -236,18 +273,24 @@ int fwd_dispatch(const void* x, const void* g, const void* b, void* y, float* me
 
 int bwd_parts(int rows, int H) {
   int grid = H <= 1024 ? (rows + 3) / 4 : rows;
-  int cap = b2host::num_sms() * 2;
+  int cap = b2host::num_sms() * (H <= 1024 ? 4 : 2);
   return grid < cap ? grid : cap;
 }
 
 template <typename T, bool RMS>
-int bwd_dispatch(const void* dy, const void* x, const void* g, const float* mean, const float* rstd, void* dx,
-                 float* ws, int grid, int rows, int H, cudaStream_t st) {
+int bwd_dispatch(const void* dy, const void* x, const void* g, const float* mean, const float* rstd, const void* dres,
+                 void* dx, float* ws, int grid, int rows, int H, cudaStream_t st) {
   if (H <= 1024) {
     size_t smem = static_cast<size_t>(CTA_THREADS / 32) * 2 * H * sizeof(float);
-    norm_bwd_kernel<T, 32, RMS><<<grid, CTA_THREADS, smem, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (T*)dx, ws, rows, H);
+#define B2_NB(NV_) norm_bwd_kernel<T, 32, RMS, NV_><<<grid, CTA_THREADS, smem, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H)
+    const int nv = (H + 255) / 256;
+    if (nv == 1) B2_NB(1); else if (nv == 2) B2_NB(2); else if (nv == 3) B2_NB(3); else B2_NB(4);
+#undef B2_NB
   } else if (H <= 8192) {
-    norm_bwd_kernel<T, 256, RMS><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (T*)dx, ws, rows, H);
+#define B2_NB(NV_) norm_bwd_kernel<T, 256, RMS, NV_><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H)
+    const int nv = (H + 2047) / 2048;
+    if (nv == 1) B2_NB(1); else if (nv == 2) B2_NB(2); else if (nv == 3) B2_NB(3); else B2_NB(4);
+#undef B2_NB
   } else { b2host::set_error("norm bwd: hidden size %d > 8192 unsupported", H); return -1; }
   return 0;
 }
@@ -278,15 +321,22 @@ extern "C" int b2_layernorm_fwd(const void* x, const void* gamma, const void* be
 extern "C" int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                                 void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype, int rms,
                                 int accumulate, void* stream) {
+  return b2_layernorm_bwd_res(dy, x, gamma, mean, rstd, nullptr, dx, dgamma, dbeta, ws, rows, H, dtype, rms, accumulate, stream);
+}
+
+// same, with the residual-branch gradient folded in: dx = dres + d(norm)   (dres may be NULL; dres may alias dx)
+extern "C" int b2_layernorm_bwd_res(const void* dy, const void* x, const void* gamma, const float* mean,
+                                    const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta, float* ws,
+                                    int rows, int H, int dtype, int rms, int accumulate, void* stream) {
   if (H % 8) { b2host::set_error("norm: hidden size must be a multiple of 8"); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int grid = bwd_parts(rows, H);
   int r;
-  if (dtype == B2_DTYPE_BF16) r = rms ? bwd_dispatch<__nv_bfloat16, true>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st)
-                                      : bwd_dispatch<__nv_bfloat16, false>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st);
-  else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st)
-               : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dx, ws, grid, rows, H, st);
+  if (dtype == B2_DTYPE_BF16) r = rms ? bwd_dispatch<__nv_bfloat16, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st)
+                                      : bwd_dispatch<__nv_bfloat16, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st);
+  else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st)
+               : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st);
   if (r) return r;
-  norm_bwd_fold_kernel<<<(2 * H + 255) / 256, 256, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
+  norm_bwd_fold_kernel<<<(2 * H + 31) / 32, 256, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
   return check("layernorm_bwd");
 }

@@ -58,6 +58,10 @@ int b2_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y
 int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                      void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype, int rms,
                      int accumulate, void* stream);
+/* same, with the gradient of the residual branch folded in: dx = dres + d(norm)/dx (dres may be NULL or alias dx) */
+int b2_layernorm_bwd_res(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                         const void* dres, void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype,
+                         int rms, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused elementwise ops.  replaces: Megatron jit bias_gelu / bias_dropout_add (K16, K17), HF SwiGLU

@@ -52,6 +52,17 @@ def _vgrad(param: Optional[torch.Tensor], g32: torch.Tensor):
     return g32.to(param.dtype)
 
 
+def _norm_bwd(d_out, x, w, mean, rstd, wp, bp, dres):
+    """LayerNorm backward with the residual-branch gradient folded in; dgamma/dbeta go straight into the fp32
+    main_grad buffers when the parameters have them (no zero-fill / add kernels)."""
+    mg_w, mg_b = getattr(wp, "main_grad", None), getattr(bp, "main_grad", None) if bp is not None else None
+    if mg_w is not None and mg_b is not None:
+        dx, _, _ = N.norm_bwd(d_out, x, w, mean, rstd, dgamma=mg_w, dbeta=mg_b, accumulate=True, dres=dres)
+        return dx, None, None
+    dx, dg, db = N.norm_bwd(d_out, x, w, mean, rstd, dres=dres)
+    return dx, _vgrad(wp, dg), _vgrad(bp, db)
+
+
 def _bias_grad(param: Optional[torch.Tensor], dy2: torch.Tensor):
     if param is None:
         return None
@@ -126,9 +137,7 @@ class _LayerFn(torch.autograd.Function):
         g_fc1_b = _bias_grad(fc1_bp, dz)
         g_fc1_w = _wgrad(fc1_wp, dz, ln2_full)
         d_ln2 = comm.column_dgrad(dz, fc1_w)
-        dx1_ln, dg2, db2 = N.norm_bwd(d_ln2, x1, ln2_w, mean2, rstd2)
-        g_ln2_w, g_ln2_b = _vgrad(ln2_wp, dg2), _vgrad(ln2_bp, db2)
-        dx1 = N.axpby(dy2, dx1_ln, 1.0, 1.0)
+        dx1, g_ln2_w, g_ln2_b = _norm_bwd(d_ln2, x1, ln2_w, mean2, rstd2, ln2_wp, ln2_bp, dy2)     # dx1 = dy + dLN2
 
         # ---- attention half backward
         d_att = N.dropout_bwd(dx1, p_h, ctx.seeds[0]) if p_h > 0.0 else dx1
@@ -143,9 +152,7 @@ class _LayerFn(torch.autograd.Function):
         g_qkv_b = _bias_grad(qkv_bp, dqkv)
         g_qkv_w = _wgrad(qkv_wp, dqkv, ln1_full)
         d_ln1 = comm.column_dgrad(dqkv, qkv_w)
-        dx_ln, dg1, db1 = N.norm_bwd(d_ln1, x2, ln1_w, mean1, rstd1)
-        g_ln1_w, g_ln1_b = _vgrad(ln1_wp, dg1), _vgrad(ln1_bp, db1)
-        dx = N.axpby(dx1, dx_ln, 1.0, 1.0)
+        dx, g_ln1_w, g_ln1_b = _norm_bwd(d_ln1, x2, ln1_w, mean1, rstd1, ln1_wp, ln1_bp, dx1)       # dx = dx1 + dLN1
         return (dx.view(-1, B, H), g_ln1_w, g_ln1_b, g_qkv_w, g_qkv_b, g_proj_w, g_proj_b, g_ln2_w, g_ln2_b,
                 g_fc1_w, g_fc1_b, g_fc2_w, g_fc2_b, None)
 

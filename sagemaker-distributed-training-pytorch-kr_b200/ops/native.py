@@ -34,6 +34,7 @@ _SIGS = {
     "b2_norm_bwd_num_parts": [c_i, c_i],
     "b2_layernorm_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_f, c_i, c_i, c_p],
     "b2_layernorm_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_layernorm_bwd_res": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_bias_dropout_add": [c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_ull, c_i, c_p],
     "b2_dropout_bwd": [c_p, c_p, c_ll, c_f, c_ull, c_i, c_p],
     "b2_bias_act_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_p],
@@ -212,16 +213,18 @@ def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor],
 
 
 def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch.Tensor] = None,
-             dbeta: Optional[torch.Tensor] = None, accumulate: bool = False):
-    """Returns (dx, dgamma_fp32, dbeta_fp32).  With ``accumulate`` the fp32 grads are added in place."""
+             dbeta: Optional[torch.Tensor] = None, accumulate: bool = False, dres: Optional[torch.Tensor] = None):
+    """Returns (dx, dgamma_fp32, dbeta_fp32).  With ``accumulate`` the fp32 grads are added in place (main_grad);
+    ``dres`` is the gradient arriving through the residual branch: dx = dres + d(norm)/dx in the same pass."""
     H = x.shape[-1]
     x2, dy2 = x.reshape(-1, H), dy.reshape(-1, H)
     rows = x2.shape[0]
     if dgamma is None:
-        dgamma = torch.zeros(H, dtype=torch.float32, device=x.device)
+        dgamma = torch.empty(H, dtype=torch.float32, device=x.device)
         accumulate = False
     if dbeta is None and not rms:
-        dbeta = torch.zeros(H, dtype=torch.float32, device=x.device)
+        assert not accumulate, "accumulate needs both dgamma and dbeta"
+        dbeta = torch.empty(H, dtype=torch.float32, device=x.device)
     if not x.is_cuda:
         xf, dyf, g = x2.float(), dy2.float(), gamma.float()
         m = 0 if rms else mean[:, None]
@@ -230,6 +233,8 @@ def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch
         m1 = 0 if rms else gy.mean(-1, keepdim=True)
         m2 = (gy * xh).mean(-1, keepdim=True)
         dx = rstd[:, None] * (gy - m1 - xh * m2)
+        if dres is not None:
+            dx = dx + dres.reshape(-1, H).float()
         dg = (dyf * xh).sum(0)
         if accumulate:
             dgamma.add_(dg)
@@ -246,8 +251,11 @@ def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch
     dx = torch.empty_like(x2)
     parts = lib().b2_norm_bwd_num_parts(rows, H)
     ws = torch.empty(parts * 2 * H, dtype=torch.float32, device=x.device)
-    _call("b2_layernorm_bwd", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dgamma), _p(dbeta), _p(ws),
-          rows, H, _dt(x), int(rms), int(accumulate), _st())
+    if dres is not None:
+        dres = dres.reshape(-1, H)
+        assert dres.is_contiguous() and dres.dtype == x.dtype
+    _call("b2_layernorm_bwd_res", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
+          _p(ws), rows, H, _dt(x), int(rms), int(accumulate), _st())
     return dx.view_as(x), dgamma, dbeta
 
 
