@@ -12,8 +12,11 @@ q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]
 if what.startswith("attn"):
     o, lse = N.attn_fwd(q, k, v, 0.125, True)
     do = torch.randn_like(o); dqkv = torch.empty_like(qkv)
-    for _ in range(4):
-        if what == "attn_fwd":
+    for _ in range(2 if what == "attn_both" else 4):
+        if what == "attn_both":
+            N.attn_fwd(q, k, v, 0.125, True, o)
+            N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:])
+        elif what == "attn_fwd":
             N.attn_fwd(q, k, v, 0.125, True, o)
         else:
             N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:])

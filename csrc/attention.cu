@@ -9,9 +9,10 @@
 // [s, b, heads*d] layout the output projection consumes (no permutes / contiguous copies).
 //
 // Forward CTA = 128 query rows of one (batch, head):
-//   warp 0 TMA producer (Q once, K/V ring) | warp 1 MMA issuer | warp 2 TMEM alloc | warps 4-7 softmax.
+//   warp 0 TMA producer (Q once, K/V ring) | warp 1 MMA issuer | warp 2 TMEM alloc | warps 4-11 softmax
+//   (two warps per 32 query rows, each owning half of the score / output columns).
 //   S = Q K^T        tcgen05.mma 128x128x16 (K-major A and B)            -> TMEM  (double buffered)
-//   P = softmax      tcgen05.ld (thread == row: no shuffles), exp2, bf16 -> smem  (128B swizzle, double buffered)
+//   P = softmax      tcgen05.ld (no shuffles; the two half-row maxima meet in smem), exp2, bf16 -> smem (128B swizzle)
 //   O_j = P V        tcgen05.mma 128xDx16 (A K-major from smem, B = V MN-major) -> TMEM (double buffered)
 //   O  = O*alpha + O_j in registers; the MMA warp runs S_{j+1} and P V_{j-1} while softmax works on block j.
 //
@@ -28,7 +29,7 @@ using namespace b2;
 namespace {
 
 constexpr int BLK = 128;        // query rows / key rows per tile
-constexpr int NTHREADS = 256;
+constexpr int NTHREADS = 384;   // warps 0-3: TMA / MMA / TMEM alloc / idle, warps 4-11: softmax (two per row)
 constexpr int SM_WARP0 = 4;
 constexpr float LOG2E = 1.4426950408889634f;
 
@@ -59,8 +60,14 @@ struct FwdSmem {
   static constexpr int OFF_Q = 0;
   static constexpr int OFF_KV = TILE;
   static constexpr int OFF_P = OFF_KV + KV_STAGES * 2 * TILE;
-  static constexpr int OFF_BAR = OFF_P + 2 * P_BYTES;
-  static constexpr int TOTAL = OFF_BAR + 256 + 1024;
+  static constexpr int OFF_XCH = OFF_P + 2 * P_BYTES;    // float [2 parity][2 halves][128]: row max / row sum exchange
+  static constexpr int OFF_BAR = OFF_XCH + 2 * 2 * BLK * 4;
+  // + up to 1 KB of slack for the manual 1024 B round-up of the base.  The dynamic array is declared
+  // __align__(1024), which the toolchain honours (the round-up is then a no-op), so the D = 128 layout may trim the
+  // slack to stay inside the 227 KB per-CTA limit.
+  static constexpr int MAX_SMEM = 227 * 1024;
+  static constexpr int TOTAL = (OFF_BAR + 256 + 1024) < MAX_SMEM ? (OFF_BAR + 256 + 1024) : MAX_SMEM;
+  static_assert(OFF_BAR + 256 <= MAX_SMEM, "attention forward tile does not fit in shared memory");
 };
 
 template <int D>
@@ -80,6 +87,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sQ = smem + L::OFF_Q;
   uint8_t* sKV = smem + L::OFF_KV;
   uint8_t* sP = smem + L::OFF_P;
+  float* sXch = reinterpret_cast<float*>(smem + L::OFF_XCH);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::OFF_BAR);
   uint64_t* q_full = bars;                   // 1
   uint64_t* kv_full = bars + 1;              // KV_STAGES
@@ -105,8 +113,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     mbar_init(q_full, 1);
     for (int i = 0; i < KV_STAGES; ++i) { mbar_init(&kv_full[i], 1); mbar_init(&kv_empty[i], 1); }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 128); mbar_init(&p_full[i], 128);
-      mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 128);
+      mbar_init(&s_full[i], 1); mbar_init(&s_empty[i], 256); mbar_init(&p_full[i], 256);
+      mbar_init(&o_full[i], 1); mbar_init(&o_empty[i], 256);
     }
     mbar_fence_init();
   }
@@ -183,24 +191,29 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       issue_PV(j);
     }
   } else if (warp >= SM_WARP0) {
-    // ---- softmax / accumulate / epilogue: thread == query row ----
-    const int r = threadIdx.x - SM_WARP0 * 32;
-    const int ew = warp - SM_WARP0;
+    // ---- softmax / accumulate / epilogue: two warps per query row (column halves) ----
+    // Warps 4-7 (g = 0) own score columns 0-63 and output columns 0..D/2-1 of their 32 rows, warps 8-11 (g = 1) the
+    // other halves: two softmax warps per SM sub-partition hide each other's TMEM / MUFU latency, and each thread
+    // keeps its 64 scores in registers between the max and the exp pass (one TMEM read of S instead of two).
+    const int g = (warp - SM_WARP0) >> 2;
+    const int ew = (warp - SM_WARP0) & 3;
+    const int r = ew * 32 + lane;                         // query row inside the tile
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int qpos = q0 + r;
     const float sl2 = p.scale * LOG2E;
-    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;
-    float o_acc[D];
+    constexpr int DH = D / 2;                             // output columns per thread
+    float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;   // l_run: partial sum over this thread's columns
+    float o_acc[DH];
 #pragma unroll
-    for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
+    for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
 
     auto absorb_O = [&](int j, float alpha) {
       mbar_wait(&o_full[j & 1], (j >> 1) & 1);
       tc_fence_after();
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
+      for (int c = 0; c < DH / 32; ++c) {
         uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + lane_off + O_COL + (j & 1) * D + c * 32, v);
+        tmem_ld_32x32b_x32(tmem_base + lane_off + O_COL + (j & 1) * D + g * DH + c * 32, v);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = o_acc[c * 32 + i] * alpha + __uint_as_float(v[i]);
@@ -212,105 +225,82 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(&s_full[j & 1], (j >> 1) & 1);
       tc_fence_after();
-      const uint32_t tS = tmem_base + lane_off + S_COL + (j & 1) * BLK;
+      const uint32_t tS = tmem_base + lane_off + S_COL + (j & 1) * BLK + g * 64;
       const int k0 = j * BLK;
       const bool need_mask = (p.causal && j == qb) || (k0 + BLK > p.seqlen);
-      // pass 1: row max (mask handling hoisted out of the element loop: only the diagonal / ragged block pays)
-      float mx = m_run;
-      if (!need_mask) {
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(tS + c * 32, v);
-          tmem_ld_wait();
-          float m0 = __uint_as_float(v[0]), m1 = __uint_as_float(v[1]), m2 = __uint_as_float(v[2]), m3 = __uint_as_float(v[3]);
+      uint32_t v[64];
+      tmem_ld_32x32b_x32(tS, v);
+      tmem_ld_32x32b_x32(tS + 32, v + 32);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_empty[j & 1]);                       // scores are in registers: S_{j+2} may overwrite the buffer
+      if (need_mask) {
+        // last visible column of this block, relative to this thread's first column
+        const int lim = min(p.causal ? qpos : 0x7fffffff, p.seqlen - 1) - k0 - g * 64;
 #pragma unroll
-          for (int i = 4; i < 32; i += 4) {
-            m0 = fmaxf(m0, __uint_as_float(v[i])); m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
-            m2 = fmaxf(m2, __uint_as_float(v[i + 2])); m3 = fmaxf(m3, __uint_as_float(v[i + 3]));
-          }
-          mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
-        }
-      } else {
-        const int lim = min(p.causal ? qpos : 0x7fffffff, p.seqlen - 1) - k0;   // last visible column of this block
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(tS + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, (c * 32 + i) <= lim ? __uint_as_float(v[i]) : -INFINITY);
-        }
+        for (int i = 0; i < 64; ++i) v[i] = (i <= lim) ? v[i] : 0xff800000u;     // -inf
       }
-      const float m_new = mx;
+      float m0 = __uint_as_float(v[0]), m1 = __uint_as_float(v[1]), m2 = __uint_as_float(v[2]), m3 = __uint_as_float(v[3]);
+#pragma unroll
+      for (int i = 4; i < 64; i += 4) {
+        m0 = fmaxf(m0, __uint_as_float(v[i])); m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+        m2 = fmaxf(m2, __uint_as_float(v[i + 2])); m3 = fmaxf(m3, __uint_as_float(v[i + 3]));
+      }
+      // combine the two column halves of the row through shared memory (parity-buffered per block)
+      float* xch = sXch + (j & 1) * 2 * BLK;
+      xch[g * BLK + r] = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+      named_bar_sync(2, 256);
+      const float m_new = fmaxf(m_run, fmaxf(xch[r], xch[BLK + r]));
       const float msc = (m_new == -INFINITY) ? 0.f : m_new * sl2;
       const float alpha = (m_run == -INFINITY) ? 0.f : fast_exp2(m_run * sl2 - msc);
-      // pass 2: probabilities -> bf16 -> swizzled smem (A operand of P V)
+      // probabilities -> bf16 -> swizzled smem (A operand of P V); masked entries are exp2(-inf) = 0
       float rs0 = 0.f, rs1 = 0.f;
-      uint8_t* pbuf = sP + (j & 1) * L::P_BYTES;
-      const int lim2 = need_mask ? (min(p.causal ? qpos : 0x7fffffff, p.seqlen - 1) - k0) : 0x7fffffff;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tS + c * 32, v);
-        tmem_ld_wait();
-        if (c == 3) { tc_fence_before(); mbar_arrive(&s_empty[j & 1]); }
-        uint32_t pk[16];
-        if (!need_mask) {
+      uint8_t* rowp = sP + (j & 1) * L::P_BYTES + g * (BLK * 128) + r * 128;     // 64 columns = one 128 B slab row
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float e0 = fast_exp2(fmaf(__uint_as_float(v[i]), sl2, -msc));
-            float e1 = fast_exp2(fmaf(__uint_as_float(v[i + 1]), sl2, -msc));
-            rs0 += e0; rs1 += e1;
-            pk[i >> 1] = pack_bf16x2(e0, e1);
-          }
-        } else {
+      for (int q = 0; q < 8; ++q) {
+        uint32_t pk[4];
 #pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            float e0 = (c * 32 + i) <= lim2 ? fast_exp2(fmaf(__uint_as_float(v[i]), sl2, -msc)) : 0.f;
-            float e1 = (c * 32 + i + 1) <= lim2 ? fast_exp2(fmaf(__uint_as_float(v[i + 1]), sl2, -msc)) : 0.f;
-            rs0 += e0; rs1 += e1;
-            pk[i >> 1] = pack_bf16x2(e0, e1);
-          }
+        for (int e = 0; e < 4; ++e) {
+          const float e0 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e]), sl2, -msc));
+          const float e1 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e + 1]), sl2, -msc));
+          rs0 += e0; rs1 += e1;
+          pk[e] = pack_bf16x2(e0, e1);
         }
-        // 32 columns = 64 B = four 16-byte chunks of slab (c >> 1), chunk index (c & 1) * 4 + q
-        uint8_t* rowp = pbuf + (c >> 1) * (BLK * 128) + r * 128;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int chunk = (c & 1) * 4 + q;
-          *reinterpret_cast<uint4*>(rowp + ((chunk ^ (r & 7)) << 4)) =
-              make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-        }
+        *reinterpret_cast<uint4*>(rowp + ((q ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       }
-      const float rs = rs0 + rs1;
       fence_proxy_async_smem();
       mbar_arrive(&p_full[j & 1]);
-      l_run = l_run * alpha + rs;
+      l_run = l_run * alpha + (rs0 + rs1);
       m_run = m_new;
       if (j > 0) absorb_O(j - 1, alpha_prev);
       alpha_prev = alpha;
     }
     absorb_O(nkv - 1, alpha_prev);
 
-    // ---- epilogue: normalise, stage through the (dead) Q tile, TMA store; write LSE ----
-    const float inv_l = l_run > 0.f ? 1.f / l_run : 0.f;
-    if (qpos < p.seqlen && p.lse != nullptr)
+    // ---- epilogue: row sum across the two halves, normalise, stage through the (dead) Q tile, TMA store; LSE ----
+    float* xch = sXch + (nkv & 1) * 2 * BLK;
+    xch[g * BLK + r] = l_run;
+    named_bar_sync(2, 256);
+    const float l_tot = xch[r] + xch[BLK + r];
+    const float inv_l = l_tot > 0.f ? 1.f / l_tot : 0.f;
+    if (g == 0 && qpos < p.seqlen && p.lse != nullptr)
       p.lse[(static_cast<size_t>(bat) * p.heads + head) * p.seqlen + qpos] =
-          (m_run == -INFINITY) ? -INFINITY : (m_run * p.scale + __logf(l_run));
+          (m_run == -INFINITY) ? -INFINITY : (m_run * p.scale + __logf(l_tot));
+    {
+      const int col0 = g * DH;                                       // first output column of this thread
+      uint8_t* rowp = sQ + (col0 >> 6) * (BLK * 128) + r * 128;
+      const int chunk0 = (col0 & 63) >> 3;
 #pragma unroll
-    for (int s = 0; s < SLABS; ++s) {
-      uint8_t* rowp = sQ + s * (BLK * 128) + r * 128;
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float* o = o_acc + s * 64 + q * 8;
-        *reinterpret_cast<uint4*>(rowp + ((q ^ (r & 7)) << 4)) =
+      for (int q = 0; q < DH / 8; ++q) {
+        const float* o = o_acc + q * 8;
+        *reinterpret_cast<uint4*>(rowp + (((chunk0 + q) ^ (r & 7)) << 4)) =
             make_uint4(pack_bf16x2(o[0] * inv_l, o[1] * inv_l), pack_bf16x2(o[2] * inv_l, o[3] * inv_l),
                        pack_bf16x2(o[4] * inv_l, o[5] * inv_l), pack_bf16x2(o[6] * inv_l, o[7] * inv_l));
       }
     }
     fence_proxy_async_smem();
-    named_bar_sync(1, 128);
-    if (r == 0) {
+    named_bar_sync(1, 256);
+    if (g == 0 && r == 0) {
 #pragma unroll
       for (int s = 0; s < SLABS; ++s) tma_store_4d(&tmO, sQ + s * (BLK * 128), s * 64, head, bat, q0);
       tma_store_commit();
@@ -423,7 +413,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   if (warp == 1 && lane == 0) {
     mbar_init(kv_full, 1);
     for (int i = 0; i < 2; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
-    mbar_init(st_full, 1); mbar_init(pds_full, 128); mbar_init(dq_full, 1); mbar_init(dq_empty, 128);
+    mbar_init(st_full, 1); mbar_init(pds_full, 256); mbar_init(dq_full, 1); mbar_init(dq_empty, 256);
     mbar_init(acc_full, 1);
     mbar_fence_init();
   }
@@ -507,8 +497,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (it + 1 < niter) issue_scores(it + 1);
     }
   } else if (warp >= SM_WARP0) {
-    const int r = threadIdx.x - SM_WARP0 * 32;     // key row for S^T / dP^T, query row for dQ
-    const int ew = warp - SM_WARP0;
+    // two warps per key row: group g owns query columns [64g, 64g+64) of S^T / dP^T, dQ columns [32g, 32g+32)
+    // and one of the two final accumulators (g = 0: dV, g = 1: dK)
+    const int g = (warp - SM_WARP0) >> 2;
+    const int ew = (warp - SM_WARP0) & 3;
+    const int r = ew * 32 + lane;                  // key row for S^T / dP^T, query row for dQ
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int kpos = k0 + r;
     const float sl2 = p.scale * LOG2E;
@@ -518,26 +511,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // dQ_i (TMEM, fp32) -> swizzled fp32 staging -> TMA reduce-add
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
+      {
         uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + lane_off + DQ_COL + c * 32, v);
+        tmem_ld_32x32b_x32(tmem_base + lane_off + DQ_COL + g * 32, v);
         tmem_ld_wait();
-        uint8_t* rowp = sDQ + c * (BLK * 128) + r * 128;
+        uint8_t* rowp = sDQ + g * (BLK * 128) + r * 128;
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           *reinterpret_cast<uint4*>(rowp + ((q ^ (r & 7)) << 4)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
       }
       tc_fence_before();
       fence_proxy_async_smem();
-      named_bar_sync(1, 128);
-      if (r == 0) {
+      named_bar_sync(1, 256);
+      if (g == 0 && r == 0) {
 #pragma unroll
         for (int c = 0; c < D / 32; ++c) tma_reduce_add_4d(&tmDQ, sDQ + c * (BLK * 128), c * 32, head, bat, (qb_first + it) * BLK);
         tma_store_commit();
         tma_store_wait_read<0>();
       }
-      named_bar_sync(1, 128);
+      named_bar_sync(1, 256);
       mbar_arrive(dq_empty);
     };
 
@@ -545,12 +537,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const int qb = qb_first + it;
       const int qbase = qb * BLK;
       // stage lse / delta of this query block (parity buffer: the previous iteration may still be read)
-      {
+      if (g == 0) {
         const int qp = qbase + r;
         sLse[(it & 1) * BLK + r] = qp < p.seqlen ? p.lse[stat_base + qp] * LOG2E : INFINITY;
         sDelta[(it & 1) * BLK + r] = qp < p.seqlen ? p.delta[stat_base + qp] : 0.f;
       }
-      named_bar_sync(2, 128);
+      named_bar_sync(2, 256);
       mbar_wait(st_full, it & 1);
       tc_fence_after();
       const bool diag = p.causal && qb == kb;
@@ -558,7 +550,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float* lse_s = sLse + (it & 1) * BLK;
       const float* del_s = sDelta + (it & 1) * BLK;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = g * 2 + cc;
         uint32_t sv[32], dv[32];
         tmem_ld_32x32b_x32(tmem_base + lane_off + ST_COL + c * 32, sv);
         tmem_ld_32x32b_x32(tmem_base + lane_off + DPT_COL + c * 32, dv);
@@ -578,10 +571,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           pk[i >> 1] = pack_bf16x2(pr[0], pr[1]);
           dk[i >> 1] = pack_bf16x2(ds[0], ds[1]);
         }
-        const int slab_off = (c >> 1) * (BLK * 128) + r * 128;
+        const int slab_off = g * (BLK * 128) + r * 128;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const int chunk = ((c & 1) * 4 + q) ^ (r & 7);
+          const int chunk = (cc * 4 + q) ^ (r & 7);
           *reinterpret_cast<uint4*>(sPT + slab_off + (chunk << 4)) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
           *reinterpret_cast<uint4*>(sDST + slab_off + (chunk << 4)) = make_uint4(dk[4 * q], dk[4 * q + 1], dk[4 * q + 2], dk[4 * q + 3]);
         }
@@ -595,10 +588,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // ---- final dK / dV: TMEM -> bf16 -> smem (P^T / dS^T buffers are dead) -> TMA store ----
     mbar_wait(acc_full, 0);
     tc_fence_after();
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
-      uint8_t* stg = which == 0 ? sPT : sDST;
-      const uint32_t col = which == 0 ? DV_COL : DK_COL;
+    {
+      uint8_t* stg = g == 0 ? sPT : sDST;
+      const uint32_t col = g == 0 ? DV_COL : DK_COL;
 #pragma unroll
       for (int c = 0; c < D / 32; ++c) {
         uint32_t v[32];
@@ -618,8 +610,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     }
     tc_fence_before();
     fence_proxy_async_smem();
-    named_bar_sync(1, 128);
-    if (r == 0) {
+    named_bar_sync(1, 256);
+    if (g == 0 && r == 0) {
       tma_store_4d(&tmDV, sPT, 0, head, bat, k0);
       tma_store_4d(&tmDK, sDST, 0, head, bat, k0);
       tma_store_commit();

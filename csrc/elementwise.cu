@@ -3,6 +3,7 @@
 // replaces: Megatron's torch.jit (NVFuser) bias_gelu / bias_dropout_add fusions,
 // HF LLaMA's unfused SwiGLU and rotate_half RoPE (K24), ATen relu/max_pool/log_softmax glue of the
 // MNIST model (K2), and the bias-gradient column reductions autograd runs after every Linear.
+#include <type_traits>
 #include "common.cuh"
 #include "b200dist.h"
 
@@ -262,6 +263,31 @@ __global__ void cast_from_fp32_kernel(T* __restrict__ dst, const float* __restri
     dst[i] = static_cast<T>(src[i]);
 }
 
+// dst[r, 0:cols] (T, row stride ld_dst) = src[r, 0:cols] (fp32, contiguous); cols % 8 == 0, 16-byte aligned rows.
+// Used to drop an fp32 accumulator (attention dQ) into a slice of a packed 16-bit buffer.
+template <typename T>
+__global__ void cast_rows_from_fp32_kernel(T* __restrict__ dst, long long ld_dst, const float* __restrict__ src,
+                                           long long rows, int cols) {
+  const int vpr = cols >> 3;
+  const long long total = rows * vpr;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / vpr;
+    const int c = static_cast<int>(i - r * vpr) * 8;
+    const float4 lo = *reinterpret_cast<const float4*>(src + r * cols + c);
+    const float4 hi = *reinterpret_cast<const float4*>(src + r * cols + c + 4);
+    uint4 q;
+    if constexpr (sizeof(T) == 2 && std::is_same<T, __nv_bfloat16>::value) {
+      q = make_uint4(pack_bf16x2(lo.x, lo.y), pack_bf16x2(lo.z, lo.w), pack_bf16x2(hi.x, hi.y), pack_bf16x2(hi.z, hi.w));
+    } else {
+      __half2 h0 = __floats2half2_rn(lo.x, lo.y), h1 = __floats2half2_rn(lo.z, lo.w), h2 = __floats2half2_rn(hi.x, hi.y),
+              h3 = __floats2half2_rn(hi.z, hi.w);
+      q = make_uint4(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1), *reinterpret_cast<uint32_t*>(&h2),
+                     *reinterpret_cast<uint32_t*>(&h3));
+    }
+    *reinterpret_cast<uint4*>(dst + r * ld_dst + c) = q;
+  }
+}
+
 int grid_for(long long work, int threads) {
   long long g = (work + threads - 1) / threads;
   long long cap = static_cast<long long>(b2host::num_sms()) * 16;
@@ -349,6 +375,13 @@ extern "C" int b2_accum_fp32(float* dst, const void* src, long long n, int dtype
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DISPATCH_T(dtype, (accum_fp32_kernel<T><<<grid_for(n, 256), 256, 0, st>>>(dst, (const T*)src, n)));
   return check("accum_fp32");
+}
+extern "C" int b2_cast_rows_from_fp32(void* dst, long long ld_dst, const float* src, long long rows, int cols, int dtype,
+                                      void* stream) {
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if ((cols % 8) || (ld_dst % 8)) { b2host::set_error("cast_rows_from_fp32: cols and ld_dst must be multiples of 8"); return -1; }
+  DISPATCH_T(dtype, (cast_rows_from_fp32_kernel<T><<<grid_for(rows * (cols / 8), 256), 256, 0, st>>>((T*)dst, ld_dst, src, rows, cols)));
+  return check("cast_rows_from_fp32");
 }
 extern "C" int b2_cast_from_fp32(void* dst, const float* src, long long n, int dtype, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -226,31 +226,33 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
 }
 
 // fold workspace rows -> dgamma / dbeta (fp32, optionally accumulated: main_grad semantics).
-// One CTA per 32 columns; its 8 warps stride over the workspace rows with 4 independent loads in flight each.
-__global__ void __launch_bounds__(256)
+// One 1024-thread CTA per 32 columns: warp w sums parts w, w+32, ... with 8 independent loads in flight (the loop is
+// latency-bound: a few MB spread over many short strided reads), then the 32 warps fold through shared memory.
+__global__ void __launch_bounds__(1024)
 norm_bwd_fold_kernel(const float* __restrict__ ws, int nparts, int H, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, int accumulate) {
-  __shared__ float part[8][33];
+  __shared__ float part[32][33];
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int j = blockIdx.x * 32 + lane;
-  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (j < 2 * H) {
     const float* col = ws + j;
     const size_t ld = static_cast<size_t>(2) * H;
     int p = w;
-    for (; p + 24 < nparts; p += 32) {
-      a0 += col[p * ld]; a1 += col[(p + 8) * ld]; a2 += col[(p + 16) * ld]; a3 += col[(p + 24) * ld];
+    for (; p + 7 * 32 < nparts; p += 8 * 32) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) a[u] += col[(p + u * 32) * ld];
     }
-    for (; p < nparts; p += 8) a0 += col[p * ld];
+    for (; p < nparts; p += 32) a[0] += col[p * ld];
   }
-  part[w][lane] = (a0 + a1) + (a2 + a3);
+  part[w][lane] = ((a[0] + a[1]) + (a[2] + a[3])) + ((a[4] + a[5]) + (a[6] + a[7]));
   __syncthreads();
   if (w == 0 && j < 2 * H) {
-    float a = 0.f;
+    float t = 0.f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) a += part[k][lane];
+    for (int k = 0; k < 32; ++k) t += part[k][lane];
     float* dst = j < H ? (dgamma + j) : (dbeta ? dbeta + (j - H) : nullptr);
-    if (dst) { if (accumulate) *dst += a; else *dst = a; }
+    if (dst) { if (accumulate) *dst += t; else *dst = t; }
   }
 }
 
@@ -337,6 +339,6 @@ extern "C" int b2_layernorm_bwd_res(const void* dy, const void* x, const void* g
   else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st)
                : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st);
   if (r) return r;
-  norm_bwd_fold_kernel<<<(2 * H + 31) / 32, 256, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
+  norm_bwd_fold_kernel<<<(2 * H + 31) / 32, 1024, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
   return check("layernorm_bwd");
 }

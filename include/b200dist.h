@@ -81,6 +81,8 @@ int b2_rope(void* x, const float* cos_t, const float* sin_t, const int* pos, lon
 int b2_axpby(const void* a, const void* b, void* out, long long n, float alpha, float beta, int dtype, void* stream);
 int b2_accum_fp32(float* dst, const void* src, long long n, int dtype, void* stream);
 int b2_cast_from_fp32(void* dst, const float* src, long long n, int dtype, void* stream);
+/* dst[r, 0:cols] (dtype, row stride ld_dst elements) = src[r, 0:cols] (fp32, contiguous); cols, ld_dst % 8 == 0 */
+int b2_cast_rows_from_fp32(void* dst, long long ld_dst, const float* src, long long rows, int cols, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Softmax cross-entropy on (vocab-sharded) logits - see csrc/xent.cu for the 4-step protocol.

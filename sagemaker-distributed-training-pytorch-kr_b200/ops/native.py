@@ -34,6 +34,7 @@ _SIGS = {
     "b2_norm_bwd_num_parts": [c_i, c_i],
     "b2_layernorm_fwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_f, c_i, c_i, c_p],
     "b2_layernorm_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_cast_rows_from_fp32": [c_p, c_ll, c_p, c_ll, c_i, c_i, c_p],
     "b2_layernorm_bwd_res": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_bias_dropout_add": [c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_ull, c_i, c_p],
     "b2_dropout_bwd": [c_p, c_p, c_ll, c_f, c_ull, c_i, c_p],
@@ -638,4 +639,8 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
           v.stride(0), v.stride(1), v.stride(2), o.stride(0), o.stride(1), o.stride(2),
           dout.stride(0), dout.stride(1), dout.stride(2), dk.stride(0), dk.stride(1), dk.stride(2),
           dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), _st())
-    dq.copy_(dq32)
+    # fp32 dQ accumulator -> the (usually strided) 16-bit dq slice
+    if dq.stride(3) == 1 and dq.stride(1) == Hh * dq.stride(2) and dq.stride(0) == B * dq.stride(1) and dq.stride(2) % 8 == 0 and D % 8 == 0:
+        _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
+    else:
+        dq.copy_(dq32)
