@@ -1,0 +1,83 @@
+"""torchrun worker (>= 2 GPUs): ZeRO-3 with the native fabric kernels (in-kernel all-gather of the parameter shards,
+fused reduce-scatter + AdamW) against the same engine over NCCL collectives, plus the row collectives of the fabric."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from b200dist.launch import env as launch_env
+
+info = launch_env.init_distributed("nccl")
+rank, world = info.rank, info.world_size
+dev = torch.device("cuda", torch.cuda.current_device())
+FAILS = []
+
+
+def check(name, ok, detail=""):
+    t = torch.tensor([int(not ok)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"{'FAIL' if t.item() else 'ok  '} {name} {detail}", flush=True)
+    if t.item():
+        FAILS.append(name)
+
+
+def run(backend, model_name, steps, ga, clip, dtype):
+    from b200dist.engine.hf_trainer import Zero3CausalLM
+    from b200dist.models.llama import build_causal_lm
+    torch.manual_seed(0)
+    model = build_causal_lm(model_name, device=dev, dtype=dtype)
+    zm = Zero3CausalLM(model, lr=1e-2, weight_decay=0.01, max_grad_norm=clip, gradient_accumulation_steps=ga,
+                       persistence_threshold=200, comm_backend=backend)
+    g = torch.Generator().manual_seed(3)
+    data = torch.randint(0, 512, (steps * ga, world, 2, 64), generator=g)
+    losses = []
+    for i in range(steps * ga):
+        ids = data[i, rank].to(dev)
+        loss = zm(ids, labels=ids)
+        zm.engine.backward(loss)
+        zm.engine.step()
+        losses.append(float(loss))
+    sd = zm.engine.gather_full_state_dict()
+    used_fabric = zm.engine.fabric is not None
+    return losses, {k: v.float().cpu() for k, v in sd.items()}, used_fabric
+
+
+# ---- fabric row collectives against NCCL
+from b200dist.parallel import fabric as fb
+F = fb.get_fabric(dist.group.WORLD)
+check("fabric usable", F.usable, str(F.error))
+if F.usable:
+    rows, H = 256, 768
+    x = torch.randn(world * rows, H, device=dev, dtype=torch.bfloat16)
+    ref = torch.empty(rows, H, device=dev, dtype=torch.bfloat16)
+    dist.reduce_scatter_tensor(ref, x.clone())
+    got = F.reduce_scatter_rows(x)
+    check("reduce_scatter_rows", torch.allclose(got.float(), ref.float(), atol=6e-2, rtol=2e-2),
+          f"max_err={(got.float() - ref.float()).abs().max().item():.3e}")
+    got2 = F.reduce_scatter_rows(x)            # second call on the same symmetric buffer (epoch flags)
+    check("reduce_scatter_rows (2nd call)", torch.equal(got, got2))
+    shard = torch.randn(rows, H, device=dev, dtype=torch.bfloat16)
+    refg = torch.empty(world * rows, H, device=dev, dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(refg, shard)
+    check("all_gather_rows", torch.equal(F.all_gather_rows(shard), refg))
+    check("all_gather_rows (2nd call)", torch.equal(F.all_gather_rows(shard), refg))
+
+# ---- ZeRO-3 engine: native fabric vs NCCL collectives
+for (name, ga, clip) in [("llama-tiny", 1, 0.0), ("llama-tiny", 2, 1.0), ("opt-tiny", 1, 1.0)]:
+    l_nat, sd_nat, used = run("native", name, 3, ga, clip, torch.bfloat16)
+    l_ref, sd_ref, _ = run("nccl", name, 3, ga, clip, torch.bfloat16)
+    check(f"zero3 {name} ga={ga} clip={clip}: native path used the fabric", used)
+    err = max(abs(a - b) for a, b in zip(l_nat, l_ref))
+    check(f"zero3 {name} ga={ga} clip={clip}: losses native vs nccl", err < 3e-2, f"max |dloss|={err:.3e} first={l_nat[0]:.4f} last={l_nat[-1]:.4f}")
+    check(f"zero3 {name} ga={ga} clip={clip}: loss decreases", l_nat[-1] < l_nat[0])
+    werr = max((sd_nat[k] - sd_ref[k]).abs().max().item() for k in sd_nat)
+    check(f"zero3 {name} ga={ga} clip={clip}: weights native vs nccl", werr < 5e-2, f"max |dw|={werr:.3e}")
+
+if rank == 0:
+    print("FAILED: " + str(FAILS) if FAILS else "ALL OK", flush=True)
+dist.barrier()
+dist.destroy_process_group()
+sys.exit(1 if FAILS else 0)
