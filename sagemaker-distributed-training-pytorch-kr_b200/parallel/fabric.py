@@ -75,6 +75,9 @@ class Fabric:
             L.b2_reduce_scatter.restype = c_i
             L.b2_allgather.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_p]
             L.b2_allgather.restype = c_i
+            L.b2_rs_update.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_f, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p,
+                                       c_f, c_f, c_f, c_f, c_f, c_i, c_i, c_p]
+            L.b2_rs_update.restype = c_i
             self._ag, self._rs, self._coll = {}, {}, {}
             probe = SymmBuffer(self, 1024, torch.float32)
             probe.tensor.fill_(float(self.rank + 1))
@@ -98,7 +101,8 @@ class Fabric:
         """in place: buf <- scale * sum over ranks (fused NVLS reduce + scale + broadcast)."""
         n = buf.numel if numel is None else numel
         esz = buf.tensor.element_size()
-        n_pad = (n * esz + 15) // 16 * 16 // esz       # payload is 256-byte padded, so rounding up is safe
+        q = 16 * self.world                             # every rank reduces a 16-byte aligned slice
+        n_pad = (n * esz + q - 1) // q * q // esz       # payload is 256-byte padded, so rounding up is safe
         N._call("b2_allreduce", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n_pad, N._dt(buf.tensor),
                 float(scale), self.rank, self.world, max_ctas, N._st())
 
