@@ -6,8 +6,9 @@ gradient reduction, clipping, AdamW) in bf16 on synthetic tokens and random-init
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus 8 --steps 10 --warmup 3
 
-Weak scaling: 24 sequences x 1024 tokens per GPU per step (micro-batch 12, as in the reference run); at 8 GPUs
-this is the reference's global batch 192 with TP=2 (+SP) x DP=4.  N=1 runs TP=1.
+Weak scaling: 24 sequences x 1024 tokens per GPU per step, 12 x 1024 tokens per GPU per micro-batch (the reference
+run's micro-batch 12 at TP=1; a TP=2 group shares micro-batches of 24 sequences); at 8 GPUs this is the reference's
+global batch 192 with TP=2 (+SP) x DP=4.  N=1 runs TP=1.
 Prints ONE JSON line on rank 0 (see README / DESIGN.md for the field contract).
 
 --impl reference : the reference's GPT path needs Megatron-LM + apex, which are neither vendored in
@@ -38,7 +39,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "eager"])
-    ap.add_argument("--micro-batch-size", type=int, default=12)
+    ap.add_argument("--micro-batch-size", type=int, default=0, help="0 = 12 x tp: 12 sequences (12288 tokens) per GPU per micro-batch, as in the reference run")
     ap.add_argument("--seqs-per-gpu", type=int, default=24)
     ap.add_argument("--num-layers", type=int, default=12)
     ap.add_argument("--hidden-size", type=int, default=768)
@@ -107,6 +108,8 @@ def main():
     tp = a.tp or min(2, a.gpus)
     dp = a.gpus // tp
     gbs = a.seqs_per_gpu * a.gpus
+    if a.micro_batch_size <= 0:
+        a.micro_batch_size = 12 * tp        # a TP group shares its micro-batch: per-GPU tokens per micro-batch stay at 12 x 1024
     assert gbs % (a.micro_batch_size * dp) == 0
     if a.impl == "eager":
         from baseline.eager_gpt import run_eager

@@ -296,8 +296,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGES = SMEM_MAIN_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
-  // GEMM->RS keeps one epilogue team: its arrival-counter protocol is per tile and led by one thread
-  constexpr int TEAMS = (FUSE == FUSE_RS) ? 1 : 2;
+  // two epilogue teams everywhere; in GEMM->RS each team leader signals its own half of every tile, so a row block
+  // is complete once (world - 1) * tiles_n * TEAMS arrivals have been counted
+  constexpr int TEAMS = 2;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -510,14 +511,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
                 rs_prev_owner = -1;
               }
-              const uint32_t expected = f_epoch * static_cast<uint32_t>((p.f_world - 1) * p.tiles_n);
+              const uint32_t expected = f_epoch * static_cast<uint32_t>((p.f_world - 1) * p.tiles_n * TEAMS);
               const uint32_t* cnt = p.f_cnt[p.f_rank] + (tm - p.f_rank * p.f_bpr);
               while (static_cast<int32_t>(ld_acquire_sys(cnt) - expected) < 0) { }
             }
             named_bar_sync(bar_id, EPI_THREADS);
           }
         }
-        const bool use_aux = (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU);
+        // (GEMM->RS applies bias / residual after the reduction, on the owner: no per-tile aux there)
+        const bool use_aux = (FUSE != FUSE_RS) && (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU);
 #pragma unroll 1
         for (int c = team; c < NCH; c += TEAMS) {
           const int col0 = n0 + c * 64;
@@ -564,42 +566,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               if (lrow < p.f_shard_rows) {
                 const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) +
                                         static_cast<long long>(f_epoch & 1) * p.f_world * p.f_shard_rows * p.N;
+                // all global loads of this chunk are issued back to back (independent), then consumed
+                uint4 rq[8];
+                const bool has_res = p.f_res != nullptr, has_bias = p.f_bias != nullptr;
+                if (has_res) {
+                  const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_res) + static_cast<long long>(lrow) * p.f_ld_res + col0);
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) rq[j] = (col0 + j * 8 < p.N) ? __ldg(rp + j) : make_uint4(0u, 0u, 0u, 0u);
+                }
+                auto add8 = [&](const uint4 (&q8)[8]) {
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) {
+                    const uint4 q = q8[j];
+                    float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+                    f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
+                    f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
+                  }
+                };
                 for (int s = 0; s < p.f_world; ++s) {
                   if (s == p.f_rank) continue;
                   const uint4* sp = reinterpret_cast<const uint4*>(stage + (static_cast<long long>(s) * p.f_shard_rows + lrow) * p.N + col0);
+                  uint4 sq[8];
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    if (col0 + j * 8 < p.N) {
-                      const uint4 q = sp[j];
-                      float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
-                      f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
-                      f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
-                    }
-                  }
+                  for (int j = 0; j < 8; ++j) sq[j] = (col0 + j * 8 < p.N) ? sp[j] : make_uint4(0u, 0u, 0u, 0u);
+                  add8(sq);
                 }
-                if (p.f_bias != nullptr) {
+                if (has_res) add8(rq);
+                if (has_bias) {           // same 128 bytes for every row: L1 hits, no need to hold them across the waits
                   const uint4* bp2 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_bias) + col0);
+                  uint4 bq[8];
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    if (col0 + j * 8 < p.N) {
-                      const uint4 q = __ldg(bp2 + j);
-                      float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
-                      f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
-                      f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
-                    }
-                  }
-                }
-                if (p.f_res != nullptr) {
-                  const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_res) + static_cast<long long>(lrow) * p.f_ld_res + col0);
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    if (col0 + j * 8 < p.N) {
-                      const uint4 q = __ldg(rp + j);
-                      float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
-                      f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
-                      f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
-                    }
-                  }
+                  for (int j = 0; j < 8; ++j) bq[j] = (col0 + j * 8 < p.N) ? __ldg(bp2 + j) : make_uint4(0u, 0u, 0u, 0u);
+                  add8(bq);
                 }
               }
             }
@@ -682,7 +680,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (leader) {
             // signal the PREVIOUS tile (its stores have certainly landed once only this tile's groups are pending)
             if (rs_prev_owner >= 0) {
-              if (rs_groups == NCH) tma_store_wait_all<NCH>(); else tma_store_wait_all<0>();
+              if (rs_groups == NCH / TEAMS) tma_store_wait_all<NCH / TEAMS>(); else tma_store_wait_all<0>();
               __threadfence_system();
               red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
             }
