@@ -51,7 +51,7 @@ class EagerGPT(nn.Module):
         return F.cross_entropy(logits.float().view(-1, logits.shape[-1]), labels.reshape(-1))
 
 
-def run_eager(a, tp, dp, gbs, ClockSampler):
+def run_eager(a, tp, dp, gbs, ClockSampler, emit=print):
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     lr_ = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(lr_)
@@ -102,7 +102,7 @@ def run_eager(a, tp, dp, gbs, ClockSampler):
     clocks = sampler.stop() if sampler else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
     tokens = gbs * a.seq_length
     if rank == 0:
-        print(json.dumps({"metric": "GPT tok/s (Megatron TP/PP)", "value": tokens * a.steps / (ms_dev / 1e3), "unit": "tokens/s", "n_gpus": world,
+        emit(json.dumps({"metric": "GPT tok/s (Megatron TP/PP)", "value": tokens * a.steps / (ms_dev / 1e3), "unit": "tokens/s", "n_gpus": world,
                           "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "weak",
                           "vs_baseline": None, "dtype": "bf16 autocast", "data": "synthetic tokens, random-init weights", "impl": "eager-library-baseline",
                           "config": {"model": "GPT-2 small (stock PyTorch ops)", "global_batch": gbs, "seq_len": a.seq_length, "vocab": a.vocab,

@@ -95,11 +95,29 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+_REAL_STDOUT_FD = None
+
+
+def emit(line: str):
+    """write the result line to the process's original stdout"""
+    sys.stdout.flush()
+    if _REAL_STDOUT_FD is not None:
+        os.write(_REAL_STDOUT_FD, (line + "\n").encode())
+    else:
+        print(line, flush=True)
+
+
 def main():
     a = parse()
     if a.impl == "reference":
         print(json.dumps({"impl": "reference", "unavailable": "reference GPT path = Megatron-LM + apex (cloned by its notebook, not vendored in /root/reference; no wheel in /opt/wheelhouse, no network); `pip install /root/reference` has nothing to build (no setup.py/pyproject)"}))
         return 0
+    # stdout carries exactly ONE JSON line: everything else that writes to fd 1 (NCCL's version banner is printed from
+    # C, below Python's sys.stdout) is sent to stderr until the result is ready
+    sys.stdout.flush()
+    global _REAL_STDOUT_FD
+    _REAL_STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
 
@@ -113,7 +131,7 @@ def main():
     assert gbs % (a.micro_batch_size * dp) == 0
     if a.impl == "eager":
         from baseline.eager_gpt import run_eager
-        return run_eager(a, tp, dp, gbs, ClockSampler)
+        return run_eager(a, tp, dp, gbs, ClockSampler, emit)
 
     import pretrain_gpt as entry
     from b200dist.engine import megatron as eng
@@ -215,7 +233,7 @@ def main():
                "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": nmb * a.micro_batch_size * (a.seq_length + 1) * 8 if is_src else 0,
                        "d2h_bytes_per_step": 4, "ms_per_step": max(ms_e2e, wall_e2e) / a.steps, "last_loss": last_loss},
                "gpu_launches": launches, "host_issue_ms_per_step": host_issue}
-        print(json.dumps(out), flush=True)
+        emit(json.dumps(out))
     dist.barrier()
     dist.destroy_process_group()
     return 0
