@@ -17,6 +17,8 @@ from __future__ import annotations
 from typing import Callable, Dict, List, Optional
 
 import torch
+
+from ..ops import native as N
 import torch.distributed as dist
 
 from ..parallel import state as mpu
@@ -76,8 +78,10 @@ class GraphedMicrobatch:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
+        n0 = N.launches()
         with torch.cuda.graph(self.graph):
             self._one()
+        self.kernels_per_replay = N.launches() - n0     # libb200dist kernel nodes in the captured micro-batch
         torch.cuda.synchronize()
 
     def load_tokens(self, data_iterator):
@@ -95,6 +99,7 @@ class GraphedMicrobatch:
         for _ in range(self.M):
             self.load_tokens(data_iterator)
             self.graph.replay()
+            N.count_launches(self.kernels_per_replay)      # replayed kernels are launches too (bench.py reports the total)
         out = {k: v.clone() for k, v in self.loss_acc.items()}
         dp = mpu.get_data_parallel_world_size()
         if dp > 1:     # data-parallel average of the logged loss: once per step, outside the captured region
