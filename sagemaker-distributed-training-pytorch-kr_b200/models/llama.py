@@ -229,7 +229,7 @@ class OPTForCausalLM(nn.Module):
         return self.head_loss(h, labels)
 
 
-def build_causal_lm(name_or_config, device=None, dtype=torch.float32):
+def build_causal_lm(name_or_config, device=None, dtype=torch.float32, **config_overrides):
     """`--model_name_or_path` resolution without network access: a known name -> config with random init; a local
     directory with config.json (+ weights) -> ckpt.hf loader."""
     import os
@@ -245,5 +245,5 @@ def build_causal_lm(name_or_config, device=None, dtype=torch.float32):
                  "llama-tiny": LlamaConfig.tiny}
         if n not in table:
             raise ValueError(f"unknown model {name_or_config!r}: pass a local HF directory or one of {sorted(table)}")
-        cfg = table[n]()
+        cfg = table[n](**config_overrides)
     return (LlamaForCausalLM if cfg.model_type == "llama" else OPTForCausalLM)(cfg, device=device, dtype=dtype)
