@@ -40,6 +40,30 @@ def report(name, got, ref, tol):
         FAILS.append(name)
 
 
+def graph_timeit(fn, reps=20, iters=5):
+    """GPU time per call without host launch cost: `reps` back-to-back calls captured in one CUDA graph."""
+    st = torch.cuda.Stream()
+    st.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(st):
+        fn(); fn()
+    torch.cuda.current_stream().wait_stream(st)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            fn()
+    torch.cuda.synchronize()
+    g.replay(); torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record(); g.replay(); e.record()
+        torch.cuda.synchronize()
+        ts.append(s.elapsed_time(e) / reps)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
 def timeit(fn, iters=20, warm=5, flush=None):
     for _ in range(warm):
         fn()
@@ -58,7 +82,7 @@ def timeit(fn, iters=20, warm=5, flush=None):
     return ts[len(ts) // 2]
 
 
-def check_gemm(quick):
+def _gemm_numerics(tag):
     cases = [
         # M, N, K, a_mn, b_mn
         (256, 256, 128, False, False), (128, 128, 64, False, False), (384, 512, 320, False, False),
@@ -71,7 +95,7 @@ def check_gemm(quick):
         b = torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16)
         got = N.gemm(a, b, a_mn=amn, b_mn=bmn)
         ref = N.gemm(cpu(a), cpu(b), a_mn=amn, b_mn=bmn, out=torch.empty(M, Nn))
-        report(f"gemm M{M} N{Nn} K{K} a_mn={int(amn)} b_mn={int(bmn)}", got, ref, 2e-2)
+        report(f"gemm[{tag}] M{M} N{Nn} K{K} a_mn={int(amn)} b_mn={int(bmn)}", got, ref, 2e-2)
     # epilogues
     M, Nn, K = 384, 512, 256
     a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
@@ -83,13 +107,13 @@ def check_gemm(quick):
         ax = aux if epi in (N.EPI_BIAS_RESIDUAL, N.EPI_DGELU) else None
         got = N.gemm(a, b, epilogue=epi, bias=bb, aux=ax)
         ref = N.gemm(cpu(a), cpu(b), epilogue=epi, bias=cpu(bb), aux=cpu(ax), out=torch.empty(M, Nn))
-        report(f"gemm epilogue {nm}", got, ref, 2e-2)
+        report(f"gemm[{tag}] epilogue {nm}", got, ref, 2e-2)
     z = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
     got = N.gemm(a, b, epilogue=N.EPI_BIAS_GELU_DUAL, bias=bias, out2=z)
     zr = torch.empty(M, Nn)
     ref = N.gemm(cpu(a), cpu(b), epilogue=N.EPI_BIAS_GELU_DUAL, bias=cpu(bias), out2=zr, out=torch.empty(M, Nn))
-    report("gemm epilogue gelu_dual (act)", got, ref, 2e-2)
-    report("gemm epilogue gelu_dual (pre)", z, zr, 2e-2)
+    report(f"gemm[{tag}] epilogue gelu_dual (act)", got, ref, 2e-2)
+    report(f"gemm[{tag}] epilogue gelu_dual (pre)", z, zr, 2e-2)
     # fp32 accumulate + split-K (wgrad)
     Mo, No, Kr = 768, 768, 4096
     dy = torch.randn(Kr, Mo, device=dev, dtype=torch.bfloat16)
@@ -97,12 +121,20 @@ def check_gemm(quick):
     acc = torch.ones(Mo, No, device=dev, dtype=torch.float32)
     N.gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True)
     ref = 1.0 + dy.float().t() @ x.float()
-    report("gemm wgrad fp32 accumulate auto split-K", acc, ref, 5e-3)
+    report(f"gemm[{tag}] wgrad fp32 accumulate auto split-K", acc, ref, 5e-3)
     acc2 = torch.zeros(Mo, No, device=dev, dtype=torch.float32)
     N.gemm(dy, x, a_mn=True, b_mn=True, out=acc2, accumulate=True, split_k=1)
-    report("gemm wgrad fp32 accumulate split_k=1", acc2, ref - 1.0, 5e-3)
+    report(f"gemm[{tag}] wgrad fp32 accumulate split_k=1", acc2, ref - 1.0, 5e-3)
     out32 = N.gemm(a, b, out_fp32=True)
-    report("gemm fp32 out (no accumulate)", out32, a.float() @ b.float().t(), 5e-3)
+    report(f"gemm[{tag}] fp32 out (no accumulate)", out32, a.float() @ b.float().t(), 5e-3)
+
+
+def check_gemm(quick):
+    for mode, tag in ((0, "1cta"), (2, "pair")):       # single-CTA tiles, then cta_group::2 pairs wherever the shape allows
+        N.set_gemm_pair_mode(mode)
+        _gemm_numerics(tag)
+    N.set_gemm_pair_mode(1)
+    print("co-resident CTA pairs of the GEMM kernel:", N.lib().b2_gemm_resident_pairs(), "on", torch.cuda.get_device_properties(0).multi_processor_count, "SMs", flush=True)
     # timing on the GPT-2-small / 1.5B / LLaMA shapes
     if not quick:
         flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
@@ -113,11 +145,15 @@ def check_gemm(quick):
             a = torch.randn((K, M) if amn else (M, K), device=dev, dtype=torch.bfloat16)
             b = torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16)
             o = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
-            ms = timeit(lambda: N.gemm(a, b, a_mn=amn, b_mn=bmn, out=o), flush=flush)
+            N.set_gemm_pair_mode(0)
+            ms1 = graph_timeit(lambda: N.gemm(a, b, a_mn=amn, b_mn=bmn, out=o))
+            N.set_gemm_pair_mode(2)
+            ms = graph_timeit(lambda: N.gemm(a, b, a_mn=amn, b_mn=bmn, out=o))
+            N.set_gemm_pair_mode(1)
             tf = 2.0 * M * Nn * K / ms / 1e9
             bt = b if bmn else b.t()
-            ms_ref = timeit(lambda: torch.matmul(a.t() if amn else a, bt, out=o), flush=flush)
-            print(f"time gemm {tag:12s} M{M} N{Nn} K{K}: {ms:.4f} ms {tf:7.1f} TFLOP/s = {tf / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak | torch.matmul {ms_ref:.4f} ms", flush=True)
+            ms_ref = graph_timeit(lambda: torch.matmul(a.t() if amn else a, bt, out=o))
+            print(f"time gemm {tag:12s} M{M} N{Nn} K{K}: pair {ms:.4f} ms {tf:7.1f} TFLOP/s = {tf / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak | 1-CTA {ms1:.4f} ms | torch.matmul {ms_ref:.4f} ms  (graph-timed, back to back)", flush=True)
         # fused epilogues on the GPT-2-small shapes (the model's actual fwd / dgrad calls)
         for (M, Nn, K, bmn, epi, tag) in [(12288, 2304, 768, False, N.EPI_BIAS, "qkv  bias"), (12288, 768, 768, False, N.EPI_BIAS_RESIDUAL, "proj bias+res"),
                                           (12288, 3072, 768, False, N.EPI_BIAS_GELU_DUAL, "fc1  gelu dual"), (12288, 768, 3072, False, N.EPI_BIAS_RESIDUAL, "fc2  bias+res"),
@@ -128,17 +164,25 @@ def check_gemm(quick):
             o2 = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16) if epi == N.EPI_BIAS_GELU_DUAL else None
             bias = torch.randn(Nn, device=dev, dtype=torch.bfloat16) if epi in (N.EPI_BIAS, N.EPI_BIAS_RESIDUAL, N.EPI_BIAS_GELU_DUAL) else None
             aux = torch.randn(M, Nn, device=dev, dtype=torch.bfloat16) if epi in (N.EPI_BIAS_RESIDUAL, N.EPI_DGELU) else None
-            ms = timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o, epilogue=epi, bias=bias, aux=aux, out2=o2), flush=flush)
-            ms0 = timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o), flush=flush)
+            N.set_gemm_pair_mode(0)
+            ms1 = graph_timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o, epilogue=epi, bias=bias, aux=aux, out2=o2))
+            N.set_gemm_pair_mode(2)
+            ms = graph_timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o, epilogue=epi, bias=bias, aux=aux, out2=o2))
+            ms0 = graph_timeit(lambda: N.gemm(a, b, b_mn=bmn, out=o))
+            N.set_gemm_pair_mode(1)
             tf = 2.0 * M * Nn * K / ms / 1e9
-            print(f"time gemm+epi {tag:16s} M{M} N{Nn} K{K}: {ms:.4f} ms {tf:7.1f} TFLOP/s (plain epilogue {ms0:.4f} ms)", flush=True)
+            print(f"time gemm+epi {tag:16s} M{M} N{Nn} K{K}: pair {ms:.4f} ms {tf:7.1f} TFLOP/s | 1-CTA {ms1:.4f} ms | pair, plain epilogue {ms0:.4f} ms  (graph-timed)", flush=True)
         for (Mo, No, Kr, tag) in [(2304, 768, 12288, "qkv wgrad"), (768, 768, 12288, "proj wgrad"), (3072, 768, 12288, "fc1 wgrad")]:
             dy = torch.randn(Kr, Mo, device=dev, dtype=torch.bfloat16)
             x = torch.randn(Kr, No, device=dev, dtype=torch.bfloat16)
             acc = torch.zeros(Mo, No, device=dev, dtype=torch.float32)
-            ms = timeit(lambda: N.gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True), flush=flush)
+            N.set_gemm_pair_mode(0)
+            ms1 = graph_timeit(lambda: N.gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True))
+            N.set_gemm_pair_mode(2)
+            ms = graph_timeit(lambda: N.gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True))
+            N.set_gemm_pair_mode(1)
             tf = 2.0 * Mo * No * Kr / ms / 1e9
-            print(f"time gemm {tag:12s} M{Mo} N{No} K{Kr}: {ms:.4f} ms {tf:7.1f} TFLOP/s = {tf / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak", flush=True)
+            print(f"time gemm {tag:12s} M{Mo} N{No} K{Kr}: pair {ms:.4f} ms {tf:7.1f} TFLOP/s = {tf / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak | 1-CTA {ms1:.4f} ms  (graph-timed)", flush=True)
 
 
 def check_norm(quick):

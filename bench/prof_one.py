@@ -20,7 +20,8 @@ if what.startswith("attn"):
             N.attn_fwd(q, k, v, 0.125, True, o)
         else:
             N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:])
-elif what == "gemm":
+elif what in ("gemm", "gemm_pair", "gemm_1cta"):
+    N.set_gemm_pair_mode(2 if what == "gemm_pair" else 0)
     a = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16); b = torch.randn(3072, 768, device=dev, dtype=torch.bfloat16)
     out = torch.empty(12288, 3072, device=dev, dtype=torch.bfloat16)
     for _ in range(4):

@@ -286,13 +286,19 @@ B2_DEVICE void decode_tile(const GemmParams& p, int t, int& tm, int& tn, int& ks
   if (p.m_rot) { tm += p.m_rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
 }
 
-template <int BN, bool A_MN, bool B_MN, int FUSE = FUSE_NONE>
+// CTA2: two CTAs of a cluster (one TPC) work on one 256 x BN tile with tcgen05.mma.cta_group::2: each CTA stages its own
+// 128 rows of A and HALF of the B tile (the pair shares B, so operand traffic per MMA halves and the smem ring gets
+// six stages instead of four), the leader CTA issues the MMAs for both, every CTA runs the epilogue of its own rows.
+template <int BN, bool A_MN, bool B_MN, int FUSE = FUSE_NONE, bool CTA2 = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
                     const GemmParams p, const __grid_constant__ CUtensorMap tmA2 /* AG: this rank's own shard */) {
+  static_assert(!CTA2 || FUSE == FUSE_NONE, "the fused collectives run single-CTA tiles");
+  constexpr int BN_LOAD = CTA2 ? BN / 2 : BN;     // B rows staged by this CTA
+  constexpr int BM_TILE = CTA2 ? 2 * BM : BM;     // rows per scheduled tile
   constexpr int A_BYTES = BM * BK * 2;
-  constexpr int B_BYTES = BN * BK * 2;
+  constexpr int B_BYTES = BN_LOAD * BK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr int STAGES = SMEM_MAIN_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
@@ -313,10 +319,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = CTA2 ? cluster_ctarank() : 0u;     // 0 = leader of the pair
 
   // fused collectives: the call epoch comes from the buffer's control block (stable at kernel entry)
   uint32_t f_epoch = 0;
-  int nctas = gridDim.x, cta0 = blockIdx.x;
+  int nctas = CTA2 ? gridDim.x / 2 : gridDim.x, cta0 = CTA2 ? blockIdx.x / 2 : blockIdx.x;   // tile-loop stride / start
   if constexpr (FUSE != FUSE_NONE) {
     f_epoch = p.f_ctrl[p.f_rank][1] + 1;
     if constexpr (FUSE == FUSE_AG) {
@@ -338,18 +345,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < STAGES; ++i) {
-      mbar_init(&full_bar[i], 1);
+      mbar_init(&full_bar[i], CTA2 ? 2 : 1);      // pair: the leader's expect_tx arrive + the peer's remote arrive
       mbar_init(&empty_bar[i], 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS);
+      mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS * (CTA2 ? 2 : 1));   // pair: both CTAs' epilogue threads (leader's copy)
     }
     mbar_fence_init();
   }
-  if (warp == 2) tmem_alloc<TMEM_COLS>(tmem_slot);
+  if (warp == 2) { if constexpr (CTA2) tmem_alloc_2sm<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CTA2) cluster_sync(); else __syncthreads();     // pair: barriers of both CTAs are live before any remote arrive
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   if constexpr (FUSE != FUSE_NONE) { if (threadIdx.x == 0) dbg_stamp(p, 0); }
@@ -364,7 +371,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int t = cta0; t < total_tiles; t += nctas) {
         int tm, tn, ks;
         decode_tile(p, t, tm, tn, ks);
-        const int m0 = tm * BM, n0 = tn * BN;
+        const int m0 = tm * BM_TILE + static_cast<int>(cta_rank) * BM, n0 = tn * BN + static_cast<int>(cta_rank) * (CTA2 ? BN_LOAD : 0);
         const int kb0 = ks * p.kb_per_split;
         const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
         [[maybe_unused]] bool a_local = false;
@@ -379,6 +386,24 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sA = stage_base + stage * STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
+          if constexpr (CTA2) {
+            // both CTAs' bytes complete on the LEADER's barrier (the leader issues the MMAs for the pair)
+            const uint32_t lbar = mapa_u32(smem_u32(&full_bar[stage]), 0);
+            if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
+            else               mbar_arrive_cluster(lbar);
+            if constexpr (!A_MN) {
+              tma_load_2d_2sm(sA, &tmA, lbar, kb * BK, m0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j) tma_load_2d_2sm(sA + j * (BK * 128), &tmA, lbar, m0 + j * 64, kb * BK);
+            }
+            if constexpr (!B_MN) {
+              tma_load_2d_2sm(sB, &tmB, lbar, kb * BK, n0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN_LOAD / 64; ++j) tma_load_2d_2sm(sB + j * (BK * 128), &tmB, lbar, n0 + j * 64, kb * BK);
+            }
+          } else {
           mbar_expect_tx(&full_bar[stage], STAGE_BYTES);
           if constexpr (!A_MN) {
             if constexpr (FUSE == FUSE_AG) {
@@ -399,13 +424,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int j = 0; j < BN / 64; ++j)
               tma_load_2d(sB + j * (BK * 128), &tmB, &full_bar[stage], n0 + j * 64, kb * BK);
           }
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    const uint32_t idesc = make_idesc_f16(BM, BN, p.fmt, A_MN ? 1 : 0, B_MN ? 1 : 0);
+  } else if (warp == 1 && cta_rank == 0) {
+    // ===================== MMA issuer (pair: the leader CTA only) =====================
+    const uint32_t idesc = make_idesc_f16(BM_TILE, BN, p.fmt, A_MN ? 1 : 0, B_MN ? 1 : 0);
     int stage = 0;
     uint32_t phase = 0;
     int it = 0;
@@ -432,10 +458,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             else                 adesc = make_smem_desc(sA + k * 2048, BK * 128, 1024);
             if constexpr (!B_MN) bdesc = make_smem_desc(sB + k * 32, 16, 1024);
             else                 bdesc = make_smem_desc(sB + k * 2048, BK * 128, 1024);
-            umma_f16_ss(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            if constexpr (CTA2) umma_f16_ss_2sm(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            else                umma_f16_ss(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          umma_commit(&empty_bar[stage]);
-          if (kb == kb1 - 1) umma_commit(&tmem_full[buf]);
+          if constexpr (CTA2) {           // frees the stage in BOTH CTAs / hands the accumulator to BOTH epilogues
+            umma_commit_2sm(&empty_bar[stage], 3);
+            if (kb == kb1 - 1) umma_commit_2sm(&tmem_full[buf], 3);
+          } else {
+            umma_commit(&empty_bar[stage]);
+            if (kb == kb1 - 1) umma_commit(&tmem_full[buf]);
+          }
         }
         __syncwarp();
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
@@ -453,10 +485,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
     [[maybe_unused]] int rs_groups = 0, rs_prev_owner = -1, rs_prev_blk = 0;   // GEMM->RS: deferred arrival signal
+    // accumulator buffer drained: tell the MMA issuer (pair: the leader CTA's barrier, from both CTAs)
+    auto acc_release = [&](uint64_t* bar) {
+      if constexpr (CTA2) mbar_arrive_cluster(mapa_u32(smem_u32(bar), 0));
+      else                mbar_arrive(bar);
+    };
     for (int t = cta0; t < total_tiles; t += nctas, ++it) {
       int tm, tn, ks;
       decode_tile(p, t, tm, tn, ks);
-      const int m0 = tm * BM, n0 = tn * BN;
+      const int m0 = tm * BM_TILE + static_cast<int>(cta_rank) * BM, n0 = tn * BN;
       const int buf = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1;
       mbar_wait(&tmem_full[buf], acc_phase);
@@ -473,7 +510,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint32_t v[32];
           tmem_ld_32x32b_x32(taddr + c * 32, v);
           tmem_ld_wait();
-          if (c + TEAMS >= NCH) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          if (c + TEAMS >= NCH) { tc_fence_before(); acc_release(&tmem_empty[buf]); }
           if (n0 + c * 32 >= p.N) continue;   // uniform across the team
           uint8_t* sb = (TEAMS == 2) ? team_buf : epi_buf + (sctr & 1) * STAGE_CHUNK_BYTES;
           ++sctr;
@@ -537,7 +574,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tmem_ld_32x32b_x32(taddr + c * 64, v);
           tmem_ld_32x32b_x32(taddr + c * 64 + 32, v + 32);
           tmem_ld_wait();
-          if (c + TEAMS >= NCH) { tc_fence_before(); mbar_arrive(&tmem_empty[buf]); }
+          if (c + TEAMS >= NCH) { tc_fence_before(); acc_release(&tmem_empty[buf]); }
           if (col0 >= p.N) continue;          // uniform across the team
           float* f = reinterpret_cast<float*>(v);
           if (p.alpha != 1.f) {
@@ -703,9 +740,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   }
 
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CTA2) cluster_sync(); else __syncthreads();     // pair: neither CTA may free TMEM / exit while the other still uses it
   if constexpr (FUSE != FUSE_NONE) { if (threadIdx.x == 0) dbg_stamp(p, 4); }
-  if (warp == 2) tmem_dealloc<TMEM_COLS>(tmem_base);
+  if (warp == 2) { if constexpr (CTA2) tmem_dealloc_2sm<TMEM_COLS>(tmem_base); else tmem_dealloc<TMEM_COLS>(tmem_base); }
   if constexpr (FUSE == FUSE_AG) fused_finish(p, f_epoch, true);
   if constexpr (FUSE == FUSE_RS) fused_finish(p, f_epoch, false);
 }
@@ -729,7 +766,57 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, 
   return 0;
 }
 
+int g_resident_pairs = 0;
+
+// CTA-pair launch: grid = 2 x (number of 256 x BN tiles, capped at SMs / 2 clusters), cluster dimension (2, 1, 1)
+template <int BN, bool A_MN, bool B_MN>
+int launch_pair(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
+                const GemmParams& p, int max_ctas, cudaStream_t stream) {
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, true>;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { b2host::set_error("gemm(pair): cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
+    configured = true;
+  }
+  const int total = p.tiles_m * p.tiles_n * p.split_k;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  // the kernel is persistent: launch exactly as many pairs as can be CO-RESIDENT (a pair needs both SMs of one TPC;
+  // parts with an odd number of enabled SMs in some GPCs host fewer than SMs/2 pairs), never a second wave
+  static int resident_pairs = 0;
+  if (resident_pairs == 0) {
+    cfg.gridDim = dim3(2 * (b2host::num_sms() / 2), 1, 1);
+    int n = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+    if (e != cudaSuccess || n <= 0) { b2host::set_error("gemm(pair): cudaOccupancyMaxActiveClusters: %s (n=%d)", cudaGetErrorString(e), n); return -1; }
+    resident_pairs = n;
+    g_resident_pairs = n;
+  }
+  int max_clusters = max_ctas / 2 > 0 ? max_ctas / 2 : 1;
+  if (max_clusters > resident_pairs) max_clusters = resident_pairs;
+  const int clusters = total < max_clusters ? total : max_clusters;
+  cfg.gridDim = dim3(2 * clusters, 1, 1);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tA, tB, tC, tC2, p, tA);
+  if (e != cudaSuccess) { b2host::set_error("gemm(pair) launch: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+// 0 = never, 1 = heuristic (default), 2 = whenever the shape allows; set through b2_gemm_set_pair_mode (tuning / A-B tests)
+int g_pair_mode = 1;
+
 }  // namespace
+
+extern "C" void b2_gemm_set_pair_mode(int mode) { g_pair_mode = mode; }
+// number of CTA pairs of the GEMM kernel that can be co-resident on this GPU (0 before the first pair launch)
+extern "C" int b2_gemm_resident_pairs(void) { return g_resident_pairs; }
 
 extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
                        long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
@@ -761,21 +848,29 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   }
   const int tiles_n = (N + bn - 1) / bn;
   const int num_kb = (K + BK - 1) / BK;
+  // CTA pairs (cta_group::2, 256 x bn tiles): when there are enough 256-row tiles to keep every pair busy
+  bool pair = false;
+  if (g_pair_mode > 0 && M >= 256 && bn >= 128) {
+    const long long t2 = 1LL * ((M + 255) / 256) * tiles_n;
+    pair = g_pair_mode == 2 || t2 * (out_fp32 && accumulate && split_k <= 0 ? 4 : 1) >= sms / 2;
+  }
+  const int tiles_m_eff = pair ? (M + 255) / 256 : tiles_m;
 
   if (split_k <= 0) {  // auto: only meaningful for fp32 accumulate outputs
     split_k = 1;
     if (out_fp32 && accumulate) {
-      int tiles = tiles_m * tiles_n;
-      while (tiles * split_k * 2 <= sms && num_kb / (split_k * 2) >= 4) split_k *= 2;
-      if (tiles * split_k < sms && num_kb / (split_k + 1) >= 4) {
-        int want = (sms + tiles - 1) / tiles;
+      int tiles = tiles_m_eff * tiles_n;
+      const int slots = pair ? sms / 2 : sms;
+      while (tiles * split_k * 2 <= slots && num_kb / (split_k * 2) >= 4) split_k *= 2;
+      if (tiles * split_k < slots && num_kb / (split_k + 1) >= 4) {
+        int want = (slots + tiles - 1) / tiles;
         if (num_kb / want >= 4) split_k = want;
       }
     }
   }
   GemmParams p{};
   p.M = M; p.N = N; p.K = K;
-  p.tiles_m = tiles_m; p.tiles_n = tiles_n;
+  p.tiles_m = tiles_m_eff; p.tiles_n = tiles_n;
   p.num_kb = num_kb;
   p.kb_per_split = (num_kb + split_k - 1) / split_k;
   p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
@@ -796,7 +891,7 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
     else             { dims[0] = M; dims[1] = K; box[0] = 64; box[1] = BK; }
     strides[0] = 0; strides[1] = static_cast<uint64_t>(lda) * 2;
     if (b2host::encode_tmap(&tA, dt, 2, A, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
-    if (!b_mn_major) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = bn; }
+    if (!b_mn_major) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = pair ? bn / 2 : bn; }   // pair: each CTA stages half of B
     else             { dims[0] = N; dims[1] = K; box[0] = 64; box[1] = BK; }
     strides[1] = static_cast<uint64_t>(ldb) * 2;
     if (b2host::encode_tmap(&tB, dt, 2, B, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
@@ -824,6 +919,18 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
     if (a_mn_major && b_mn_major) return launch<BN_, true, true>(tA, tB, tC, tC2, p, mc, stream);     \
     return launch<BN_, true, false>(tA, tB, tC, tC2, p, mc, stream);                                  \
   } while (0)
+#define B2_DISPATCH_PAIR(BN_)                                                                         \
+  do {                                                                                                \
+    if (!a_mn_major && !b_mn_major) return launch_pair<BN_, false, false>(tA, tB, tC, tC2, p, mc, stream); \
+    if (!a_mn_major && b_mn_major) return launch_pair<BN_, false, true>(tA, tB, tC, tC2, p, mc, stream);   \
+    if (a_mn_major && b_mn_major) return launch_pair<BN_, true, true>(tA, tB, tC, tC2, p, mc, stream);     \
+    return launch_pair<BN_, true, false>(tA, tB, tC, tC2, p, mc, stream);                                  \
+  } while (0)
+  if (pair) {
+    if (bn == 256) B2_DISPATCH_PAIR(256);
+    B2_DISPATCH_PAIR(128);
+  }
+#undef B2_DISPATCH_PAIR
   if (bn == 256) B2_DISPATCH(256);
   B2_DISPATCH(128);
 #undef B2_DISPATCH

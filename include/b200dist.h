@@ -45,6 +45,9 @@ int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long lon
             long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
             const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
             int split_k, float alpha, int max_ctas, void* stream);
+/* CTA-pair (tcgen05 cta_group::2, 256-row tiles) selection for b2_gemm: 0 never, 1 heuristic (default), 2 whenever the shape allows */
+void b2_gemm_set_pair_mode(int mode);
+int b2_gemm_resident_pairs(void);   /* CTA pairs of the GEMM kernel that can be co-resident (0 before the first pair launch) */
 
 /* ------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].

@@ -89,7 +89,19 @@ def lib():
             fn.argtypes = sig
             fn.restype = c_i
         _lib = L
+        if os.environ.get("B2_GEMM_PAIR_MODE"):       # A/B switch: 0 = single-CTA tiles only, 2 = CTA pairs wherever possible
+            L.b2_gemm_set_pair_mode.argtypes = [ctypes.c_int]
+            L.b2_gemm_set_pair_mode.restype = None
+            L.b2_gemm_set_pair_mode(int(os.environ["B2_GEMM_PAIR_MODE"]))
     return _lib
+
+
+def set_gemm_pair_mode(mode: int) -> None:
+    """CTA-pair (cta_group::2) tile selection of `gemm`: 0 never, 1 heuristic (default), 2 whenever the shape allows."""
+    L = lib()
+    L.b2_gemm_set_pair_mode.argtypes = [ctypes.c_int]
+    L.b2_gemm_set_pair_mode.restype = None
+    L.b2_gemm_set_pair_mode(int(mode))
 
 
 def launches() -> int:
