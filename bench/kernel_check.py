@@ -340,7 +340,8 @@ def check_embedding(quick):
 
 def check_attn(quick):
     for (S, B, Hh, D, causal) in [(128, 1, 1, 64, True), (256, 2, 3, 64, True), (384, 1, 2, 64, False), (200, 1, 2, 64, True),
-                                  (1024, 2, 4, 64, True), (256, 1, 2, 128, True)]:
+                                  (1024, 2, 4, 64, True), (256, 1, 2, 128, True), (512, 2, 3, 128, True), (384, 1, 2, 128, False),
+                                  (200, 1, 2, 128, True)]:
         qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
         q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]
         scale = D ** -0.5
@@ -349,15 +350,15 @@ def check_attn(quick):
         orf, lser = N.attn_fwd(qc, kc, vc, scale, causal)
         report(f"attn fwd S{S} B{B} H{Hh} D{D} causal={int(causal)}", o, orf, 2e-2)
         report(f"attn lse S{S} B{B} H{Hh} D{D}", lse, lser, 2e-3)
-        if D == 64:
+        if D in (64, 128):
             do = torch.randn(S, B, Hh, D, device=dev, dtype=torch.bfloat16)
             dqkv = torch.zeros_like(qkv)
             N.attn_bwd(q, k, v, o, do, lse, scale, causal, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:])
             dref = torch.zeros(S, B, Hh, 3 * D)
             N.attn_bwd(qc, kc, vc, orf, cpu(do), lser, scale, causal, dref[..., :D], dref[..., D:2 * D], dref[..., 2 * D:])
-            report(f"attn bwd dq S{S} B{B} H{Hh}", dqkv[..., :D], dref[..., :D], 4e-2)
-            report(f"attn bwd dk S{S} B{B} H{Hh}", dqkv[..., D:2 * D], dref[..., D:2 * D], 4e-2)
-            report(f"attn bwd dv S{S} B{B} H{Hh}", dqkv[..., 2 * D:], dref[..., 2 * D:], 4e-2)
+            report(f"attn bwd dq S{S} B{B} H{Hh} D{D}", dqkv[..., :D], dref[..., :D], 4e-2)
+            report(f"attn bwd dk S{S} B{B} H{Hh} D{D}", dqkv[..., D:2 * D], dref[..., D:2 * D], 4e-2)
+            report(f"attn bwd dv S{S} B{B} H{Hh} D{D}", dqkv[..., 2 * D:], dref[..., 2 * D:], 4e-2)
     if not quick:
         S, B, Hh, D = 1024, 12, 12, 64
         qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
@@ -371,6 +372,17 @@ def check_attn(quick):
         dqkv = torch.empty_like(qkv)
         ms = timeit(lambda: N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:]))
         print(f"time attn bwd S1024 B12 H12 D64 causal: {ms:.4f} ms {2.5 * fl / ms / 1e9:.1f} TFLOP/s = {2.5 * fl / ms / 1e9 / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak")
+        S, B, Hh, D = 512, 16, 32, 128                  # LLaMA-7B attention at the ZeRO-3 benchmark shape
+        qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
+        q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]
+        fl = 4.0 * S * S * D * B * Hh / 2
+        o, lse = N.attn_fwd(q, k, v, D ** -0.5, True)
+        ms = timeit(lambda: N.attn_fwd(q, k, v, D ** -0.5, True, o))
+        print(f"time attn fwd S512 B16 H32 D128 causal: {ms:.4f} ms {fl / ms / 1e9:.1f} TFLOP/s")
+        do = torch.randn_like(o)
+        dqkv = torch.empty_like(qkv)
+        ms = timeit(lambda: N.attn_bwd(q, k, v, o, do, lse, D ** -0.5, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:]))
+        print(f"time attn bwd S512 B16 H32 D128 causal: {ms:.4f} ms {2.5 * fl / ms / 1e9:.1f} TFLOP/s")
         try:
             from flash_attn import flash_attn_func
             qb, kb, vb = (t.permute(1, 0, 2, 3).contiguous() for t in (q, k, v))

@@ -347,21 +347,31 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
 }
 
 // ------------------------------------------------------------------------------------------
-// backward main (head_dim 64)
+// backward main (head_dim 64 or 128)
 // ------------------------------------------------------------------------------------------
+// D = 64 : Q/dO double-buffered, dQ has its own TMEM columns and smem staging (scores of block i+1 overlap the dQ drain).
+// D = 128: 512 TMEM columns and 227 KB of smem force sharing - Q/dO single-buffered, the dQ accumulator aliases the
+//          dP^T columns and its fp32 staging aliases the P^T / dS^T tiles, so one query block is processed strictly
+//          after the previous one (attention is a few % of a LLaMA-7B step at seq 512; correctness first).
 template <int D>
 struct BwdSmem {
-  static constexpr int TILE = BLK * D * 2;             // 16 KB at D = 64
+  static constexpr int SLABS = D / 64;
+  static constexpr int TILE = BLK * D * 2;             // one K/V/Q/dO tile: 16 KB (D = 64) / 32 KB (D = 128)
+  static constexpr int QST = D == 64 ? 2 : 1;          // Q / dO stages
+  static constexpr bool DQ_ALIAS = D != 64;
+  static constexpr int PT_BYTES = BLK * BLK * 2;       // 32 KB
   static constexpr int OFF_K = 0;
   static constexpr int OFF_V = TILE;
-  static constexpr int OFF_Q = 2 * TILE;               // 2 stages
-  static constexpr int OFF_DO = 4 * TILE;              // 2 stages
-  static constexpr int OFF_PT = 6 * TILE;              // 32 KB
-  static constexpr int OFF_DST = OFF_PT + BLK * BLK * 2;
-  static constexpr int OFF_DQ = OFF_DST + BLK * BLK * 2;   // fp32 staging: 128 x D x 4
-  static constexpr int OFF_STAT = OFF_DQ + BLK * D * 4;    // lse[2][128], delta[2][128]
+  static constexpr int OFF_Q = 2 * TILE;
+  static constexpr int OFF_DO = OFF_Q + QST * TILE;
+  static constexpr int OFF_PT = OFF_DO + QST * TILE;
+  static constexpr int OFF_DST = OFF_PT + PT_BYTES;
+  static constexpr int OFF_DQ = DQ_ALIAS ? OFF_PT : OFF_DST + PT_BYTES;          // fp32 staging: 128 x D x 4
+  static constexpr int OFF_STAT = DQ_ALIAS ? OFF_DST + PT_BYTES : OFF_DQ + BLK * D * 4;   // lse[2][128], delta[2][128]
   static constexpr int OFF_BAR = OFF_STAT + 4 * BLK * 4;
   static constexpr int TOTAL = OFF_BAR + 256 + 1024;
+  static_assert(!DQ_ALIAS || BLK * D * 4 <= 2 * PT_BYTES, "dQ staging must fit in the P^T + dS^T tiles");
+  static_assert(TOTAL <= 227 * 1024, "attention backward tile does not fit in shared memory");
 };
 
 template <int D>
@@ -371,10 +381,15 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 const __grid_constant__ CUtensorMap tmDQ /* fp32, box {32,1,1,128} */,
                 const __grid_constant__ CUtensorMap tmDK, const __grid_constant__ CUtensorMap tmDV,
                 const AttnParams p) {
-  static_assert(D == 64, "backward currently specialised for head_dim 64");
+  static_assert(D == 64 || D == 128, "head_dim 64 or 128");
   using L = BwdSmem<D>;
+  constexpr int SLABS = L::SLABS;
+  constexpr int QST = L::QST;
+  constexpr bool DQ_ALIAS = L::DQ_ALIAS;
   constexpr uint32_t TMEM_COLS = 512;
-  constexpr uint32_t ST_COL = 0, DPT_COL = 128, DV_COL = 256, DK_COL = 256 + D, DQ_COL = 256 + 2 * D;
+  constexpr uint32_t ST_COL = 0, DPT_COL = 128, DV_COL = 256, DK_COL = 256 + D;
+  constexpr uint32_t DQ_COL = DQ_ALIAS ? DPT_COL : 256 + 2 * D;
+  static_assert(DK_COL + D <= 512 && (DQ_ALIAS || DQ_COL + D <= 512), "TMEM budget");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -392,9 +407,9 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t* q_full = bars + 1;       // 2
   uint64_t* q_empty = bars + 3;      // 2
   uint64_t* st_full = bars + 5;      // 1   S^T and dP^T ready
-  uint64_t* pds_full = bars + 6;     // 1   P^T / dS^T written to smem (128 arrivals)
+  uint64_t* pds_full = bars + 6;     // 1   P^T / dS^T written to smem (256 arrivals)
   uint64_t* dq_full = bars + 7;      // 1   dQ_i in TMEM (also: dV/dK MMAs of this iteration done)
-  uint64_t* dq_empty = bars + 8;     // 1   dQ TMEM drained + staging free (128 arrivals)
+  uint64_t* dq_empty = bars + 8;     // 1   dQ TMEM drained + staging free (256 arrivals)
   uint64_t* acc_full = bars + 9;     // 1   final dK/dV
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
@@ -426,14 +441,20 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   if (warp == 0) {
     if (lane == 0) {
       mbar_expect_tx(kv_full, 2 * L::TILE);
-      tma_load_4d(sK, &tmK, kv_full, 0, head, bat, k0);
-      tma_load_4d(sV, &tmV, kv_full, 0, head, bat, k0);
+#pragma unroll
+      for (int s = 0; s < SLABS; ++s) {
+        tma_load_4d(sK + s * (BLK * 128), &tmK, kv_full, s * 64, head, bat, k0);
+        tma_load_4d(sV + s * (BLK * 128), &tmV, kv_full, s * 64, head, bat, k0);
+      }
       for (int it = 0; it < niter; ++it) {
-        const int st = it & 1;
-        mbar_wait(&q_empty[st], ((it >> 1) & 1) ^ 1);
+        const int st = it % QST;
+        mbar_wait(&q_empty[st], ((it / QST) & 1) ^ 1);
         mbar_expect_tx(&q_full[st], 2 * L::TILE);
-        tma_load_4d(sQ + st * L::TILE, &tmQ, &q_full[st], 0, head, bat, (qb_first + it) * BLK);
-        tma_load_4d(sDO + st * L::TILE, &tmDO, &q_full[st], 0, head, bat, (qb_first + it) * BLK);
+#pragma unroll
+        for (int s = 0; s < SLABS; ++s) {
+          tma_load_4d(sQ + st * L::TILE + s * (BLK * 128), &tmQ, &q_full[st], s * 64, head, bat, (qb_first + it) * BLK);
+          tma_load_4d(sDO + st * L::TILE + s * (BLK * 128), &tmDO, &q_full[st], s * 64, head, bat, (qb_first + it) * BLK);
+        }
       }
     }
   } else if (warp == 1) {
@@ -443,20 +464,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     mbar_wait(kv_full, 0);
     const uint32_t aK = smem_u32(sK), aV = smem_u32(sV), aPT = smem_u32(sPT), aDST = smem_u32(sDST);
     auto issue_scores = [&](int it) {
-      const int st = it & 1;
-      mbar_wait(&q_full[st], (it >> 1) & 1);
+      const int st = it % QST;
+      mbar_wait(&q_full[st], (it / QST) & 1);
+      if (DQ_ALIAS && it > 0) mbar_wait(dq_empty, (it - 1) & 1);   // dP^T columns still hold dQ of the previous block
       tc_fence_after();
       if (lane == 0) {
         const uint32_t aQ = smem_u32(sQ + st * L::TILE), aDO = smem_u32(sDO + st * L::TILE);
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
-          umma_f16_ss(tmem_base + ST_COL, make_smem_desc(aK + kk * 32, 16, 1024), make_smem_desc(aQ + kk * 32, 16, 1024),
+          const uint32_t off = (kk >> 2) * (BLK * 128) + (kk & 3) * 32;
+          umma_f16_ss(tmem_base + ST_COL, make_smem_desc(aK + off, 16, 1024), make_smem_desc(aQ + off, 16, 1024),
                       id_kk, kk > 0 ? 1u : 0u);
         }
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
-          umma_f16_ss(tmem_base + DPT_COL, make_smem_desc(aV + kk * 32, 16, 1024),
-                      make_smem_desc(aDO + kk * 32, 16, 1024), id_kk, kk > 0 ? 1u : 0u);
+          const uint32_t off = (kk >> 2) * (BLK * 128) + (kk & 3) * 32;
+          umma_f16_ss(tmem_base + DPT_COL, make_smem_desc(aV + off, 16, 1024), make_smem_desc(aDO + off, 16, 1024),
+                      id_kk, kk > 0 ? 1u : 0u);
         }
         umma_commit(st_full);
       }
@@ -464,7 +488,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     issue_scores(0);
     for (int it = 0; it < niter; ++it) {
-      const int st = it & 1;
+      const int st = it % QST;
       mbar_wait(pds_full, it & 1);
       mbar_wait(dq_empty, (it & 1) ^ 1);
       tc_fence_after();
@@ -497,7 +521,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (it + 1 < niter) issue_scores(it + 1);
     }
   } else if (warp >= SM_WARP0) {
-    // two warps per key row: group g owns query columns [64g, 64g+64) of S^T / dP^T, dQ columns [32g, 32g+32)
+    // two warps per key row: group g owns query columns [64g, 64g+64) of S^T / dP^T, half of the dQ columns
     // and one of the two final accumulators (g = 0: dV, g = 1: dK)
     const int g = (warp - SM_WARP0) >> 2;
     const int ew = (warp - SM_WARP0) & 3;
@@ -508,14 +532,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const size_t stat_base = (static_cast<size_t>(bat) * p.heads + head) * p.seqlen;
 
     auto drain_dq = [&](int it) {
-      // dQ_i (TMEM, fp32) -> swizzled fp32 staging -> TMA reduce-add
+      // dQ_i (TMEM, fp32) -> swizzled fp32 staging (one 128 B-row slab per 32 columns) -> TMA reduce-add
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-      {
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c) {
+        const int cc = g * (D / 64) + c;             // 32-column chunk of dQ handled by this thread
         uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + lane_off + DQ_COL + g * 32, v);
+        tmem_ld_32x32b_x32(tmem_base + lane_off + DQ_COL + cc * 32, v);
         tmem_ld_wait();
-        uint8_t* rowp = sDQ + g * (BLK * 128) + r * 128;
+        uint8_t* rowp = sDQ + cc * (BLK * 128) + r * 128;
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           *reinterpret_cast<uint4*>(rowp + ((q ^ (r & 7)) << 4)) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
@@ -585,7 +611,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       drain_dq(it);
     }
 
-    // ---- final dK / dV: TMEM -> bf16 -> smem (P^T / dS^T buffers are dead) -> TMA store ----
+    // ---- final dK / dV: TMEM -> bf16 -> smem (P^T / dS^T tiles are dead) -> TMA store ----
     mbar_wait(acc_full, 0);
     tc_fence_after();
     {
@@ -596,10 +622,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t v[32];
         tmem_ld_32x32b_x32(tmem_base + lane_off + col + c * 32, v);
         tmem_ld_wait();
-        uint8_t* rowp = stg + r * 128;
+        uint8_t* rowp = stg + (c >> 1) * (BLK * 128) + r * 128;       // 64 bf16 columns per 128 B-row slab
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          const int chunk = (c * 4 + q) ^ (r & 7);
+          const int chunk = ((c & 1) * 4 + q) ^ (r & 7);
           *reinterpret_cast<uint4*>(rowp + (chunk << 4)) =
               make_uint4(pack_bf16x2(__uint_as_float(v[8 * q]), __uint_as_float(v[8 * q + 1])),
                          pack_bf16x2(__uint_as_float(v[8 * q + 2]), __uint_as_float(v[8 * q + 3])),
@@ -612,8 +638,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     fence_proxy_async_smem();
     named_bar_sync(1, 256);
     if (g == 0 && r == 0) {
-      tma_store_4d(&tmDV, sPT, 0, head, bat, k0);
-      tma_store_4d(&tmDK, sDST, 0, head, bat, k0);
+#pragma unroll
+      for (int s = 0; s < SLABS; ++s) {
+        tma_store_4d(&tmDV, sPT + s * (BLK * 128), s * 64, head, bat, k0);
+        tma_store_4d(&tmDK, sDST + s * (BLK * 128), s * 64, head, bat, k0);
+      }
       tma_store_commit();
       tma_store_wait_all<0>();
     }
@@ -680,7 +709,7 @@ extern "C" int b2_attn_bwd(const void* q, const void* k, const void* v, const vo
                            long long do_sh, long long dk_ss, long long dk_sb, long long dk_sh, long long dv_ss,
                            long long dv_sb, long long dv_sh, float scale, int causal, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (D != 64) { b2host::set_error("attn_bwd: head_dim must be 64 (got %d)", D); return -1; }
+  if (D != 64 && D != 128) { b2host::set_error("attn_bwd: head_dim must be 64 or 128 (got %d)", D); return -1; }
   {
     long long rows = static_cast<long long>(seqlen) * batch * heads;
     long long blocks = (rows * (D / 8) + 255) / 256;
@@ -702,9 +731,16 @@ extern "C" int b2_attn_bwd(const void* q, const void* k, const void* v, const vo
   p.seqlen = seqlen; p.batch = batch; p.heads = heads; p.causal = causal; p.scale = scale;
   p.lse = const_cast<float*>(lse); p.delta = delta;
   dim3 grid((seqlen + BLK - 1) / BLK, heads, batch);
-  auto kern = attn_bwd_kernel<64>;
-  static bool cfg = false;
-  if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<64>::TOTAL); cfg = true; }
-  kern<<<grid, NTHREADS, BwdSmem<64>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);
+  if (D == 64) {
+    auto kern = attn_bwd_kernel<64>;
+    static bool cfg = false;
+    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<64>::TOTAL); cfg = true; }
+    kern<<<grid, NTHREADS, BwdSmem<64>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);
+  } else {
+    auto kern = attn_bwd_kernel<128>;
+    static bool cfg = false;
+    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<128>::TOTAL); cfg = true; }
+    kern<<<grid, NTHREADS, BwdSmem<128>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);
+  }
   return check("attn_bwd");
 }

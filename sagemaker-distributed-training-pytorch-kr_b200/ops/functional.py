@@ -197,11 +197,11 @@ class _Attention(torch.autograd.Function):
 
 
 def attention(q, k, v, scale: Optional[float] = None, causal: bool = True):
-    """Scaled-dot-product attention on [S, B, H, D] tensors.  head_dim 64 (fwd+bwd) / 128 (fwd) run the tcgen05
-    kernels in bf16; other shapes / dtypes use the PyTorch restatement (same math, autograd backward)."""
+    """Scaled-dot-product attention on [S, B, H, D] tensors.  head_dim 64 and 128 run the tcgen05 kernels
+    (forward and backward) in bf16; other shapes / dtypes use the PyTorch restatement (same math, autograd backward)."""
     D = q.shape[-1]
     scale = 1.0 / math.sqrt(D) if scale is None else scale
-    native_ok = q.is_cuda and q.dtype == torch.bfloat16 and (D == 64 or (D == 128 and not torch.is_grad_enabled()))
+    native_ok = q.is_cuda and q.dtype == torch.bfloat16 and D in (64, 128)
     if native_ok or (not q.is_cuda and D == 64 and not q.requires_grad and False):
         return _Attention.apply(q, k, v, scale, causal)
     qf, kf, vf = (t.permute(1, 2, 0, 3) for t in (q, k, v))
