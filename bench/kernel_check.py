@@ -359,6 +359,25 @@ def check_attn(quick):
             report(f"attn bwd dq S{S} B{B} H{Hh} D{D}", dqkv[..., :D], dref[..., :D], 4e-2)
             report(f"attn bwd dk S{S} B{B} H{Hh} D{D}", dqkv[..., D:2 * D], dref[..., D:2 * D], 4e-2)
             report(f"attn bwd dv S{S} B{B} H{Hh} D{D}", dqkv[..., 2 * D:], dref[..., 2 * D:], 4e-2)
+    # attention dropout: the kernels' counter-based mask is restated in ops/native.py, so fwd and bwd are checked exactly
+    for (S, B, Hh, D, pd) in [(256, 2, 3, 64, 0.1), (384, 1, 2, 128, 0.25), (200, 1, 2, 64, 0.5)]:
+        qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
+        q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]
+        scale, seed = D ** -0.5, 0x1234567 + S
+        o, lse = N.attn_fwd(q, k, v, scale, True, p_drop=pd, seed=seed)
+        qc, kc, vc = cpu(q), cpu(k), cpu(v)
+        orf, lser = N.attn_fwd(qc, kc, vc, scale, True, p_drop=pd, seed=seed)
+        report(f"attn fwd dropout {pd} S{S} D{D}", o, orf, 2e-2)
+        report(f"attn lse dropout {pd} S{S} D{D}", lse, lser, 2e-3)
+        keep = N.attn_dropout_mask(B, Hh, S, pd, seed).ne(0).float().mean().item()
+        print(f"{'ok  ' if abs(keep - (1 - pd)) < 0.01 else 'FAIL'} attn dropout keep fraction {keep:.4f} (want {1 - pd})")
+        do = torch.randn(S, B, Hh, D, device=dev, dtype=torch.bfloat16)
+        dqkv = torch.zeros_like(qkv)
+        N.attn_bwd(q, k, v, o, do, lse, scale, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:], p_drop=pd, seed=seed)
+        dref = torch.zeros(S, B, Hh, 3 * D)
+        N.attn_bwd(qc, kc, vc, orf, cpu(do), lser, scale, True, dref[..., :D], dref[..., D:2 * D], dref[..., 2 * D:], p_drop=pd, seed=seed)
+        for nm, sl in (("dq", slice(0, D)), ("dk", slice(D, 2 * D)), ("dv", slice(2 * D, 3 * D))):
+            report(f"attn bwd {nm} dropout {pd} S{S} D{D}", dqkv[..., sl], dref[..., sl], 4e-2)
     if not quick:
         S, B, Hh, D = 1024, 12, 12, 64
         qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
@@ -372,6 +391,10 @@ def check_attn(quick):
         dqkv = torch.empty_like(qkv)
         ms = timeit(lambda: N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:]))
         print(f"time attn bwd S1024 B12 H12 D64 causal: {ms:.4f} ms {2.5 * fl / ms / 1e9:.1f} TFLOP/s = {2.5 * fl / ms / 1e9 / PEAKS['bf16_tflops']:.3f} of measured cuBLAS peak")
+        ms = timeit(lambda: N.attn_fwd(q, k, v, 0.125, True, out, p_drop=0.1, seed=7))
+        print(f"time attn fwd S1024 B12 H12 D64 causal dropout 0.1: {ms:.4f} ms")
+        ms = timeit(lambda: N.attn_bwd(q, k, v, o, do, lse, 0.125, True, dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:], p_drop=0.1, seed=7))
+        print(f"time attn bwd S1024 B12 H12 D64 causal dropout 0.1: {ms:.4f} ms")
         S, B, Hh, D = 512, 16, 32, 128                  # LLaMA-7B attention at the ZeRO-3 benchmark shape
         qkv = torch.randn(S, B, Hh, 3 * D, device=dev, dtype=torch.bfloat16)
         q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]

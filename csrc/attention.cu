@@ -46,7 +46,20 @@ struct AttnParams {
   float scale;          // softmax scale (1/sqrt(d))
   float* lse;           // [batch, heads, seqlen] (natural log units)
   const float* delta;   // bwd: [batch, heads, seqlen]
+  // attention dropout (DROP kernels): element (b, h, q, k) is kept iff drop_hash(...) >= drop_thresh; kept values are
+  // scaled by inv_keep.  The row sum / LSE use the un-dropped probabilities (dropout acts on softmax output).
+  uint32_t drop_thresh;  // p * 2^32
+  uint32_t drop_seed;
+  float inv_keep;        // 1 / (1 - p)
 };
+
+// counter-based dropout decision shared by forward and backward (and restated in ops/native.py for the CPU oracle):
+// lowbias32 integer hash of a linear combination of the element's coordinates
+constexpr uint32_t DROP_CQ = 0x9E3779B1u, DROP_CK = 0x85EBCA77u, DROP_CB = 0xC2B2AE3Du;
+B2_DEVICE uint32_t drop_mix(uint32_t x) {
+  x ^= x >> 16; x *= 0x7FEB352Du; x ^= x >> 15; x *= 0x846CA68Bu; x ^= x >> 16;
+  return x;
+}
 
 // ------------------------------------------------------------------------------------------
 // forward
@@ -70,7 +83,7 @@ struct FwdSmem {
   static_assert(OFF_BAR + 256 <= MAX_SMEM, "attention forward tile does not fit in shared memory");
 };
 
-template <int D>
+template <int D, bool DROP>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -201,6 +214,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int qpos = q0 + r;
     const float sl2 = p.scale * LOG2E;
+    [[maybe_unused]] const uint32_t drop_base = p.drop_seed + static_cast<uint32_t>(qpos) * DROP_CQ +
+                                                static_cast<uint32_t>(bat * p.heads + head) * DROP_CB;
     constexpr int DH = D / 2;                             // output columns per thread
     float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;   // l_run: partial sum over this thread's columns
     float o_acc[DH];
@@ -256,14 +271,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       // probabilities -> bf16 -> swizzled smem (A operand of P V); masked entries are exp2(-inf) = 0
       float rs0 = 0.f, rs1 = 0.f;
       uint8_t* rowp = sP + (j & 1) * L::P_BYTES + g * (BLK * 128) + r * 128;     // 64 columns = one 128 B slab row
+      // dropout hash input of this thread's first column; + DROP_CK per column
+      [[maybe_unused]] uint32_t hx = drop_base + static_cast<uint32_t>(k0 + g * 64) * DROP_CK;
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         uint32_t pk[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const float e0 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e]), sl2, -msc));
-          const float e1 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e + 1]), sl2, -msc));
+          float e0 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e]), sl2, -msc));
+          float e1 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e + 1]), sl2, -msc));
           rs0 += e0; rs1 += e1;
+          if constexpr (DROP) {
+            e0 = drop_mix(hx) >= p.drop_thresh ? e0 * p.inv_keep : 0.f;
+            e1 = drop_mix(hx + DROP_CK) >= p.drop_thresh ? e1 * p.inv_keep : 0.f;
+            hx += 2 * DROP_CK;
+          }
           pk[e] = pack_bf16x2(e0, e1);
         }
         *reinterpret_cast<uint4*>(rowp + ((q ^ (r & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
@@ -374,7 +396,7 @@ struct BwdSmem {
   static_assert(TOTAL <= 227 * 1024, "attention backward tile does not fit in shared memory");
 };
 
-template <int D>
+template <int D, bool DROP>
 __global__ void __launch_bounds__(NTHREADS, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                 const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
@@ -529,6 +551,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int kpos = k0 + r;
     const float sl2 = p.scale * LOG2E;
+    [[maybe_unused]] const uint32_t drop_base = p.drop_seed + static_cast<uint32_t>(kpos) * DROP_CK +
+                                                static_cast<uint32_t>(bat * p.heads + head) * DROP_CB;
     const size_t stat_base = (static_cast<size_t>(bat) * p.heads + head) * p.seqlen;
 
     auto drain_dq = [&](int it) {
@@ -591,8 +615,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const int qi = c * 32 + i + e;
             float pe = fast_exp2(fmaf(__uint_as_float(sv[i + e]), sl2, -lse_s[qi]));
             pe = (qi >= qmin) ? pe : 0.f;
-            pr[e] = pe;
-            ds[e] = pe * (__uint_as_float(dv[i + e]) - del_s[qi]) * p.scale;
+            float dp = __uint_as_float(dv[i + e]);
+            if constexpr (DROP) {
+              // same decision as the forward made for element (query qbase + qi, key kpos)
+              const float mk = drop_mix(drop_base + static_cast<uint32_t>(qbase + qi) * DROP_CQ) >= p.drop_thresh ? p.inv_keep : 0.f;
+              pr[e] = pe * mk;                       // dropped probabilities feed dV = P~^T dO
+              dp *= mk;                              // dP = dP~ * mask / keep
+            } else {
+              pr[e] = pe;
+            }
+            ds[e] = pe * (dp - del_s[qi]) * p.scale;
           }
           pk[i >> 1] = pack_bf16x2(pr[0], pr[1]);
           dk[i >> 1] = pack_bf16x2(ds[0], ds[1]);
@@ -667,14 +699,22 @@ int check(const char* what) {
   if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
   return 0;
 }
+void set_dropout(AttnParams& p, float p_drop, unsigned long long seed) {
+  const double t = static_cast<double>(p_drop) * 4294967296.0;
+  p.drop_thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
+  p.drop_seed = static_cast<uint32_t>(seed ^ (seed >> 32));
+  p.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
+}
 }  // namespace
 
 // strides are in ELEMENTS: (seq, batch, head); head_dim contiguous.  bf16 only.
 extern "C" int b2_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int seqlen, int batch,
                            int heads, int D, long long q_ss, long long q_sb, long long q_sh, long long k_ss,
                            long long k_sb, long long k_sh, long long v_ss, long long v_sb, long long v_sh,
-                           long long o_ss, long long o_sb, long long o_sh, float scale, int causal, void* stream) {
+                           long long o_ss, long long o_sb, long long o_sh, float scale, int causal, float p_drop,
+                           unsigned long long seed, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p_drop < 0.f || p_drop >= 1.f) { b2host::set_error("attn_fwd: dropout probability must be in [0, 1)"); return -1; }
   if (D != 64 && D != 128) { b2host::set_error("attn_fwd: head_dim must be 64 or 128 (got %d)", D); return -1; }
   CUtensorMap mq, mk, mv, mo;
   const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
@@ -684,18 +724,19 @@ extern "C" int b2_attn_fwd(const void* q, const void* k, const void* v, void* o,
   if (make_map4(&mo, dt, 2, o, D, heads, batch, seqlen, o_ss, o_sb, o_sh, 64)) return -1;
   AttnParams p;
   p.seqlen = seqlen; p.batch = batch; p.heads = heads; p.causal = causal; p.scale = scale; p.lse = lse; p.delta = nullptr;
+  set_dropout(p, p_drop, seed);
+  const bool drop = p_drop > 0.f;
   dim3 grid((seqlen + BLK - 1) / BLK, heads, batch);
-  if (D == 64) {
-    auto kern = attn_fwd_kernel<64>;
-    static bool cfg = false;
-    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem<64>::TOTAL); cfg = true; }
-    kern<<<grid, NTHREADS, FwdSmem<64>::TOTAL, st>>>(mq, mk, mv, mo, p);
-  } else {
-    auto kern = attn_fwd_kernel<128>;
-    static bool cfg = false;
-    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem<128>::TOTAL); cfg = true; }
-    kern<<<grid, NTHREADS, FwdSmem<128>::TOTAL, st>>>(mq, mk, mv, mo, p);
-  }
+#define B2_ATTN_FWD(D_, DROP_)                                                                                     \
+  do {                                                                                                            \
+    auto kern = attn_fwd_kernel<D_, DROP_>;                                                                       \
+    static bool cfg = false;                                                                                      \
+    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem<D_>::TOTAL); cfg = true; } \
+    kern<<<grid, NTHREADS, FwdSmem<D_>::TOTAL, st>>>(mq, mk, mv, mo, p);                                          \
+  } while (0)
+  if (D == 64) { if (drop) B2_ATTN_FWD(64, true); else B2_ATTN_FWD(64, false); }
+  else         { if (drop) B2_ATTN_FWD(128, true); else B2_ATTN_FWD(128, false); }
+#undef B2_ATTN_FWD
   return check("attn_fwd");
 }
 
@@ -707,8 +748,10 @@ extern "C" int b2_attn_bwd(const void* q, const void* k, const void* v, const vo
                            long long k_sb, long long k_sh, long long v_ss, long long v_sb, long long v_sh,
                            long long o_ss, long long o_sb, long long o_sh, long long do_ss, long long do_sb,
                            long long do_sh, long long dk_ss, long long dk_sb, long long dk_sh, long long dv_ss,
-                           long long dv_sb, long long dv_sh, float scale, int causal, void* stream) {
+                           long long dv_sb, long long dv_sh, float scale, int causal, float p_drop,
+                           unsigned long long seed, void* stream) {
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (p_drop < 0.f || p_drop >= 1.f) { b2host::set_error("attn_bwd: dropout probability must be in [0, 1)"); return -1; }
   if (D != 64 && D != 128) { b2host::set_error("attn_bwd: head_dim must be 64 or 128 (got %d)", D); return -1; }
   {
     long long rows = static_cast<long long>(seqlen) * batch * heads;
@@ -730,17 +773,18 @@ extern "C" int b2_attn_bwd(const void* q, const void* k, const void* v, const vo
   AttnParams p;
   p.seqlen = seqlen; p.batch = batch; p.heads = heads; p.causal = causal; p.scale = scale;
   p.lse = const_cast<float*>(lse); p.delta = delta;
+  set_dropout(p, p_drop, seed);
+  const bool drop = p_drop > 0.f;
   dim3 grid((seqlen + BLK - 1) / BLK, heads, batch);
-  if (D == 64) {
-    auto kern = attn_bwd_kernel<64>;
-    static bool cfg = false;
-    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<64>::TOTAL); cfg = true; }
-    kern<<<grid, NTHREADS, BwdSmem<64>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);
-  } else {
-    auto kern = attn_bwd_kernel<128>;
-    static bool cfg = false;
-    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<128>::TOTAL); cfg = true; }
-    kern<<<grid, NTHREADS, BwdSmem<128>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);
-  }
+#define B2_ATTN_BWD(D_, DROP_)                                                                                     \
+  do {                                                                                                            \
+    auto kern = attn_bwd_kernel<D_, DROP_>;                                                                       \
+    static bool cfg = false;                                                                                      \
+    if (!cfg) { cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem<D_>::TOTAL); cfg = true; } \
+    kern<<<grid, NTHREADS, BwdSmem<D_>::TOTAL, st>>>(mq, mk, mv, mdo, mdq, mdk, mdv, p);                          \
+  } while (0)
+  if (D == 64) { if (drop) B2_ATTN_BWD(64, true); else B2_ATTN_BWD(64, false); }
+  else         { if (drop) B2_ATTN_BWD(128, true); else B2_ATTN_BWD(128, false); }
+#undef B2_ATTN_BWD
   return check("attn_bwd");
 }

@@ -194,24 +194,26 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* stream);
 
 /* ------------------------------------------------------------------------------------------
- * Flash attention (tcgen05), bf16, head_dim 64 or 128 forward / 64 backward.  Strides are in
+ * Flash attention (tcgen05), bf16, head_dim 64 or 128.  Strides are in
  * elements for (seq, batch, head); head_dim is contiguous.  lse: fp32 [batch, heads, seqlen].
  * Backward: delta is fp32 scratch [batch, heads, seqlen]; dq_accum is fp32 [seq, batch, heads, D],
  * contiguous and ZERO on entry (dQ tiles are TMA reduce-added into it).
+ * p_drop > 0 applies attention dropout to the softmax output: element (b, h, q, k) is kept iff a counter-based
+ * hash of (seed, b*heads+h, q, k) >= p_drop * 2^32 (pass the same p_drop / seed to the backward).
  * replaces: Megatron CoreAttention baddbmm/bmm + scaled_upper_triang_masked_softmax_cuda (E17/E19,
  *           K14/K15), HF eager attention (K24).
  */
 int b2_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int seqlen, int batch, int heads,
                 int D, long long q_ss, long long q_sb, long long q_sh, long long k_ss, long long k_sb,
                 long long k_sh, long long v_ss, long long v_sb, long long v_sh, long long o_ss, long long o_sb,
-                long long o_sh, float scale, int causal, void* stream);
+                long long o_sh, float scale, int causal, float p_drop, unsigned long long seed, void* stream);
 int b2_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* dout, const float* lse,
                 float* delta, float* dq_accum, void* dk, void* dv, int seqlen, int batch, int heads, int D,
                 long long q_ss, long long q_sb, long long q_sh, long long k_ss, long long k_sb, long long k_sh,
                 long long v_ss, long long v_sb, long long v_sh, long long o_ss, long long o_sb, long long o_sh,
                 long long do_ss, long long do_sb, long long do_sh, long long dk_ss, long long dk_sb,
-                long long dk_sh, long long dv_ss, long long dv_sb, long long dv_sh, float scale, int causal,
-                void* stream);
+                long long dk_sh, long long dv_ss, long long dv_sb, long long dv_sh, float scale, int causal, float p_drop,
+                unsigned long long seed, void* stream);
 
 #ifdef __cplusplus
 }

@@ -92,7 +92,10 @@ class _LayerFn(torch.autograd.Function):
         S = T // B
         nh, hd = layer.heads_local, layer.head_dim
         qkv4 = qkv.view(S, B, nh, 3 * hd)
-        ctx_t, lse = N.attn_fwd(qkv4[..., :hd], qkv4[..., hd:2 * hd], qkv4[..., 2 * hd:], layer.softmax_scale, True)
+        p_a = cfg.attention_dropout if layer.training else 0.0
+        seed_a = tp_ops.next_dropout_seed(True) if p_a > 0.0 else 0      # heads are split over TP ranks: per-rank stream
+        ctx_t, lse = N.attn_fwd(qkv4[..., :hd], qkv4[..., hd:2 * hd], qkv4[..., 2 * hd:], layer.softmax_scale, True,
+                                p_drop=p_a, seed=seed_a)
         ctx2 = ctx_t.view(T, nh * hd)
         seed1 = seed2 = 0
         if p_h > 0.0:
@@ -110,7 +113,7 @@ class _LayerFn(torch.autograd.Function):
             y2 = N.bias_dropout_add(mlp_out, fc2_b, x1, p_h, seed2)
         else:
             y2 = comm.row_fwd(a, fc2_w, bias=fc2_b, residual=x1)
-        ctx.layer, ctx.p_h, ctx.seeds, ctx.dims = layer, p_h, (seed1, seed2), (S, B, T)
+        ctx.layer, ctx.p_h, ctx.seeds, ctx.dims, ctx.attn_drop = layer, p_h, (seed1, seed2), (S, B, T), (p_a, seed_a)
         ctx.save_for_backward(x2, mean1, rstd1, ln1_full, qkv, ctx_t, lse, x1, mean2, rstd2, ln2_full, z, a,
                               ln1_w, qkv_w, proj_w, ln2_w, fc1_w, fc2_w)
         ctx.params = (ln1_w, ln1_b, qkv_w, qkv_b, proj_w, proj_b, ln2_w, ln2_b, fc1_w, fc1_b, fc2_w, fc2_b)
@@ -148,7 +151,8 @@ class _LayerFn(torch.autograd.Function):
         dqkv = torch.empty_like(qkv)
         dqkv4 = dqkv.view(S, B, nh, 3 * hd)
         N.attn_bwd(qkv4[..., :hd], qkv4[..., hd:2 * hd], qkv4[..., 2 * hd:], ctx_t, d_ctx.view(S, B, nh, hd), lse,
-                   layer.softmax_scale, True, dqkv4[..., :hd], dqkv4[..., hd:2 * hd], dqkv4[..., 2 * hd:])
+                   layer.softmax_scale, True, dqkv4[..., :hd], dqkv4[..., hd:2 * hd], dqkv4[..., 2 * hd:],
+                   p_drop=ctx.attn_drop[0], seed=ctx.attn_drop[1])
         g_qkv_b = _bias_grad(qkv_bp, dqkv)
         g_qkv_w = _wgrad(qkv_wp, dqkv, ln1_full)
         d_ln1 = comm.column_dgrad(dqkv, qkv_w)

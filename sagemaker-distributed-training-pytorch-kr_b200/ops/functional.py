@@ -180,10 +180,10 @@ class _Attention(torch.autograd.Function):
     """q, k, v: [S, B, H, D] views (D contiguous) -> o [S, B, H, D].  tcgen05 flash attention fwd/bwd."""
 
     @staticmethod
-    def forward(ctx, q, k, v, scale, causal):
-        o, lse = N.attn_fwd(q, k, v, scale, causal)
+    def forward(ctx, q, k, v, scale, causal, p_drop=0.0, seed=0):
+        o, lse = N.attn_fwd(q, k, v, scale, causal, p_drop=p_drop, seed=seed)
         ctx.save_for_backward(q, k, v, o, lse)
-        ctx.scale, ctx.causal = scale, causal
+        ctx.scale, ctx.causal, ctx.drop = scale, causal, (p_drop, seed)
         return o
 
     @staticmethod
@@ -192,20 +192,20 @@ class _Attention(torch.autograd.Function):
         S, B, H, D = q.shape
         dqkv = torch.empty((S, B, H, 3 * D), dtype=q.dtype, device=q.device)
         dq, dk, dv = dqkv[..., :D], dqkv[..., D:2 * D], dqkv[..., 2 * D:]
-        N.attn_bwd(q, k, v, o, do.contiguous(), lse, ctx.scale, ctx.causal, dq, dk, dv)
-        return dq, dk, dv, None, None
+        N.attn_bwd(q, k, v, o, do.contiguous(), lse, ctx.scale, ctx.causal, dq, dk, dv, p_drop=ctx.drop[0], seed=ctx.drop[1])
+        return dq, dk, dv, None, None, None, None
 
 
-def attention(q, k, v, scale: Optional[float] = None, causal: bool = True):
+def attention(q, k, v, scale: Optional[float] = None, causal: bool = True, dropout_p: float = 0.0, seed: int = 0):
     """Scaled-dot-product attention on [S, B, H, D] tensors.  head_dim 64 and 128 run the tcgen05 kernels
     (forward and backward) in bf16; other shapes / dtypes use the PyTorch restatement (same math, autograd backward)."""
     D = q.shape[-1]
     scale = 1.0 / math.sqrt(D) if scale is None else scale
     native_ok = q.is_cuda and q.dtype == torch.bfloat16 and D in (64, 128)
-    if native_ok or (not q.is_cuda and D == 64 and not q.requires_grad and False):
-        return _Attention.apply(q, k, v, scale, causal)
+    if native_ok or (dropout_p > 0.0 and not q.is_cuda):      # CPU + dropout: the oracle in ops/native.py draws the kernels' mask
+        return _Attention.apply(q, k, v, scale, causal, dropout_p, seed)
     qf, kf, vf = (t.permute(1, 2, 0, 3) for t in (q, k, v))
-    o = torch.nn.functional.scaled_dot_product_attention(qf, kf, vf, is_causal=causal, scale=scale)
+    o = torch.nn.functional.scaled_dot_product_attention(qf, kf, vf, is_causal=causal, scale=scale, dropout_p=dropout_p)
     return o.permute(2, 0, 1, 3).contiguous()
 
 

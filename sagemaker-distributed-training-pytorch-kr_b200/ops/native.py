@@ -58,8 +58,8 @@ _SIGS = {
     "b2_scale_check": [c_p, c_ll, c_f, c_p, c_p],
     "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
-    "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_p],
-    "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_p],
+    "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
+    "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_num_sms": [],
 }
 
@@ -600,7 +600,23 @@ def embedding_bwd_(dy2, tok, pos, dwte32, dwpe32, vocab_start: int = 0):
 # =============================================================================================
 # attention.  q/k/v/o are 4-D views [seq, batch, heads, D] with D contiguous (any strides otherwise)
 # =============================================================================================
-def _attn_ref(q, k, v, scale, causal):
+def attn_dropout_mask(B: int, Hh: int, S: int, p_drop: float, seed: int, device="cpu") -> torch.Tensor:
+    """[B, H, S(query), S(key)] multiplier (0 or 1/(1-p)) - the decision rule of csrc/attention.cu restated:
+    keep iff lowbias32(seed32 + q*CQ + k*CK + (b*H+h)*CB) >= p * 2^32 (all arithmetic mod 2^32)."""
+    M = 0xFFFFFFFF
+    seed32 = (seed ^ (seed >> 32)) & M
+    q = torch.arange(S, dtype=torch.int64, device=device)[:, None]
+    k = torch.arange(S, dtype=torch.int64, device=device)[None, :]
+    bh = torch.arange(B * Hh, dtype=torch.int64, device=device).view(B, Hh, 1, 1)
+    x = (seed32 + q * 0x9E3779B1 + k * 0x85EBCA77 + bh * 0xC2B2AE3D) & M
+    x = x ^ (x >> 16); x = (x * 0x7FEB352D) & M
+    x = x ^ (x >> 15); x = (x * 0x846CA68B) & M
+    x = x ^ (x >> 16)
+    t = min(int(float(p_drop) * 4294967296.0), M)
+    return (x >= t).float() / (1.0 - p_drop)
+
+
+def _attn_ref(q, k, v, scale, causal, p_drop: float = 0.0, seed: int = 0):
     qf, kf, vf = (t.float().permute(1, 2, 0, 3) for t in (q, k, v))  # [b, h, s, d]
     s = torch.matmul(qf, kf.transpose(-1, -2)) * scale
     if causal:
@@ -609,17 +625,19 @@ def _attn_ref(q, k, v, scale, causal):
         s = s.masked_fill(~mask, float("-inf"))
     lse = torch.logsumexp(s, -1)
     p = torch.exp(s - lse[..., None])
-    o = torch.matmul(p, vf)
-    return o, lse, p
+    mk = attn_dropout_mask(s.shape[0], s.shape[1], s.shape[-1], p_drop, seed, s.device) if p_drop > 0.0 else None
+    o = torch.matmul(p * mk if mk is not None else p, vf)
+    return o, lse, p, mk
 
 
-def attn_fwd(q, k, v, scale: float, causal: bool, out: Optional[torch.Tensor] = None):
-    """Returns (o [seq, batch, heads, D] contiguous, lse [batch, heads, seq] fp32)."""
+def attn_fwd(q, k, v, scale: float, causal: bool, out: Optional[torch.Tensor] = None, p_drop: float = 0.0, seed: int = 0):
+    """Returns (o [seq, batch, heads, D] contiguous, lse [batch, heads, seq] fp32).  p_drop > 0: attention dropout on
+    the softmax output (counter-based mask from `seed`; give the same pair to attn_bwd)."""
     S, B, Hh, D = q.shape
     if out is None:
         out = torch.empty((S, B, Hh, D), dtype=q.dtype, device=q.device)
     if not q.is_cuda:
-        o, lse, _ = _attn_ref(q, k, v, scale, causal)
+        o, lse, _, _ = _attn_ref(q, k, v, scale, causal, p_drop, seed)
         out.copy_(o.permute(2, 0, 1, 3).to(q.dtype))
         return out, lse.contiguous()
     assert q.dtype == torch.bfloat16, "flash attention kernel is bf16"
@@ -629,19 +647,22 @@ def attn_fwd(q, k, v, scale: float, causal: bool, out: Optional[torch.Tensor] = 
     _call("b2_attn_fwd", _p(q), _p(k), _p(v), _p(out), _p(lse), S, B, Hh, D,
           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
           v.stride(0), v.stride(1), v.stride(2), out.stride(0), out.stride(1), out.stride(2),
-          float(scale), int(causal), _st())
+          float(scale), int(causal), float(p_drop), int(seed) & 0xFFFFFFFFFFFFFFFF, _st())
     return out, lse
 
 
-def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor, dk: torch.Tensor, dv: torch.Tensor):
+def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor, dk: torch.Tensor, dv: torch.Tensor,
+             p_drop: float = 0.0, seed: int = 0):
     """Writes dq/dk/dv (4-D views like q/k/v, typically slices of one packed dQKV buffer)."""
     S, B, Hh, D = q.shape
     if not q.is_cuda:
-        _, _, p = _attn_ref(q, k, v, scale, causal)
+        _, _, p, mk = _attn_ref(q, k, v, scale, causal, p_drop, seed)
         qf, kf, vf, dof = (t.float().permute(1, 2, 0, 3) for t in (q, k, v, dout))
         of = o.float().permute(1, 2, 0, 3)
-        dvf = torch.matmul(p.transpose(-1, -2), dof)
+        dvf = torch.matmul((p * mk if mk is not None else p).transpose(-1, -2), dof)
         dp = torch.matmul(dof, vf.transpose(-1, -2))
+        if mk is not None:
+            dp = dp * mk
         delta = (dof * of).sum(-1, keepdim=True)
         ds = p * (dp - delta) * scale
         dqf = torch.matmul(ds, kf)
@@ -656,7 +677,7 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
           q.stride(0), q.stride(1), q.stride(2), k.stride(0), k.stride(1), k.stride(2),
           v.stride(0), v.stride(1), v.stride(2), o.stride(0), o.stride(1), o.stride(2),
           dout.stride(0), dout.stride(1), dout.stride(2), dk.stride(0), dk.stride(1), dk.stride(2),
-          dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), _st())
+          dv.stride(0), dv.stride(1), dv.stride(2), float(scale), int(causal), float(p_drop), int(seed) & 0xFFFFFFFFFFFFFFFF, _st())
     # fp32 dQ accumulator -> the (usually strided) 16-bit dq slice
     if dq.stride(3) == 1 and dq.stride(1) == Hh * dq.stride(2) and dq.stride(0) == B * dq.stride(1) and dq.stride(2) % 8 == 0 and D % 8 == 0:
         _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
