@@ -338,6 +338,41 @@ def check_embedding(quick):
     report("embedding bwd dwpe", dp, dpr, 1e-3)
 
 
+def check_wattn(quick):
+    """Swin window attention (7x7 windows, head_dim 32): fused kernel vs the fp32 PyTorch restatement."""
+    for (Bw, heads, nW) in [(8, 4, 4), (30, 3, 1), (128, 8, 16)]:
+        qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)
+        bias = torch.randn(heads, 49, 49, device=dev)
+        mask = None if nW == 1 else torch.where(torch.rand(nW, 49, 49, device=dev) < 0.3, -100.0, 0.0)
+        scale = 32 ** -0.5
+        out, lse = N.window_attn_fwd(qkv, bias, mask, heads, scale)
+        outr, lser = N.window_attn_fwd(cpu(qkv), cpu(bias), cpu(mask), heads, scale)
+        report(f"wattn fwd Bw{Bw} heads{heads} nW{nW}", out, outr, 2e-2)
+        report(f"wattn lse Bw{Bw} heads{heads} nW{nW}", lse, lser, 2e-3)
+        do = torch.randn_like(out)
+        dqkv, dbias = N.window_attn_bwd(qkv, bias, mask, out, do, lse, heads, scale)
+        dqkvr, dbiasr = N.window_attn_bwd(cpu(qkv), cpu(bias), cpu(mask), outr.to(torch.bfloat16), cpu(do), lser, heads, scale)
+        report(f"wattn bwd dqkv Bw{Bw} heads{heads}", dqkv, dqkvr, 4e-2)
+        report(f"wattn bwd dbias Bw{Bw} heads{heads}", dbias, dbiasr, 2e-2)
+    if not quick:
+        for (Bw, heads, nW, tag) in [(4096, 4, 64, "swin_b stage 1, batch 64"), (256, 16, 4, "swin_b stage 3, batch 64")]:
+            qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)
+            bias = torch.randn(heads, 49, 49, device=dev)
+            mask = torch.zeros(nW, 49, 49, device=dev)
+            out, lse = N.window_attn_fwd(qkv, bias, mask, heads, 32 ** -0.5)
+            do = torch.randn_like(out)
+            ms_f = timeit(lambda: N.window_attn_fwd(qkv, bias, mask, heads, 32 ** -0.5))
+            ms_b = timeit(lambda: N.window_attn_bwd(qkv, bias, mask, out, do, lse, heads, 32 ** -0.5))
+
+            def eager():
+                q, k, v = qkv.view(Bw, 49, 3, heads, 32).permute(2, 0, 3, 1, 4)
+                a = (q * 32 ** -0.5) @ k.transpose(-2, -1) + bias.to(q.dtype)[None]
+                a = (a.view(Bw // nW, nW, heads, 49, 49) + mask.to(a.dtype)[None, :, None]).view(Bw, heads, 49, 49)
+                return (torch.softmax(a.float(), -1).to(v.dtype) @ v).transpose(1, 2).reshape(Bw, 49, heads * 32)
+            ms_e = timeit(eager)
+            print(f"time wattn {tag}: fwd {ms_f:.4f} ms bwd {ms_b:.4f} ms | eager PyTorch chain fwd {ms_e:.4f} ms", flush=True)
+
+
 def check_attn(quick):
     for (S, B, Hh, D, causal) in [(128, 1, 1, 64, True), (256, 2, 3, 64, True), (384, 1, 2, 64, False), (200, 1, 2, 64, True),
                                   (1024, 2, 4, 64, True), (256, 1, 2, 128, True), (512, 2, 3, 128, True), (384, 1, 2, 128, False),
@@ -416,7 +451,7 @@ def check_attn(quick):
 
 
 ALL = {"gemm": check_gemm, "norm": check_norm, "elementwise": check_elementwise, "xent": check_xent,
-       "optim": check_optim, "embedding": check_embedding, "attn": check_attn}
+       "optim": check_optim, "embedding": check_embedding, "attn": check_attn, "wattn": check_wattn}
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()

@@ -601,8 +601,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               // straight to the output shard - no separate reduce pass, no staging round trip of the own partial
               const int lrow = (tm - p.f_rank * p.f_bpr) * BM + et;
               if (lrow < p.f_shard_rows) {
-                const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) +
-                                        static_cast<long long>(f_epoch & 1) * p.f_world * p.f_shard_rows * p.N;
+                // staging slots are chunk-major: [parity][source rank][row block][64-column chunk][128 rows][64]
+                const int ncc = (p.N + 63) >> 6;
+                const long long slot = static_cast<long long>(p.f_shard_rows) * ncc * 64;
+                const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) + static_cast<long long>(f_epoch & 1) * p.f_world * slot +
+                                        ((static_cast<long long>(tm - p.f_rank * p.f_bpr) * ncc + (col0 >> 6)) * BM + et) * 64;
                 // all global loads of this chunk are issued back to back (independent), then consumed
                 uint4 rq[8];
                 const bool has_res = p.f_res != nullptr, has_bias = p.f_bias != nullptr;
@@ -622,7 +625,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 };
                 for (int s = 0; s < p.f_world; ++s) {
                   if (s == p.f_rank) continue;
-                  const uint4* sp = reinterpret_cast<const uint4*>(stage + (static_cast<long long>(s) * p.f_shard_rows + lrow) * p.N + col0);
+                  const uint4* sp = reinterpret_cast<const uint4*>(stage + static_cast<long long>(s) * slot);
                   uint4 sq[8];
 #pragma unroll
                   for (int j = 0; j < 8; ++j) sq[j] = (col0 + j * 8 < p.N) ? sp[j] : make_uint4(0u, 0u, 0u, 0u);
@@ -704,7 +707,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               // through the peer mapping: the NVLink transfer overlaps the following tiles' mainloops)
               const int owner = tm / p.f_bpr;
               if (rs_own) tma_store_2d(&tmC, sb0, col0, (tm - owner * p.f_bpr) * BM);          // final rows of this rank
-              else tma_store_2d(p.f_rsmaps + (f_epoch & 1) * p.f_world + owner, sb0, col0, (tm - owner * p.f_bpr) * BM);
+              else        // one contiguous 16 KB chunk of the owner's staging slot (full-width NVLink writes)
+                tma_store_2d(p.f_rsmaps + (f_epoch & 1) * p.f_world + owner, sb0, 0,
+                             ((tm - owner * p.f_bpr) * ((p.N + 63) >> 6) + (col0 >> 6)) * BM);
               ++rs_groups;
             } else {
               tma_store_2d(&tmC, sb0, col0, m0);
@@ -1036,14 +1041,17 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
 
 // Builds (host) and uploads (synchronously, once per buffer/shape) the 2*world staging-slot tensor maps of
 // the GEMM->reduce-scatter kernel: map[parity*world + owner] = slot [parity][this rank] of rank `owner`'s
-// staging buffer, viewed as [shard_rows, N].
+// staging buffer.  A slot is chunk-major - [row block][64-column chunk][128 rows][64 columns] - so every partial tile
+// chunk the GEMM epilogue pushes is ONE contiguous 16 KB write over NVLink instead of 128 strided 128-byte rows; the
+// map describes the slot as a tall [blocks * chunks * 128, 64] matrix.  Slot size: shard_rows * ceil(N/64) * 64 elements.
 extern "C" int b2_make_rs_maps(void* dev_out, void* const* stage_ptrs, int world, int rank, int shard_rows, int N, int dtype) {
   CUtensorMap maps[16];
   const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   for (int par = 0; par < 2; ++par)
     for (int o = 0; o < world; ++o) {
-      uint8_t* base = static_cast<uint8_t*>(stage_ptrs[o]) + (static_cast<long long>(par) * world + rank) * shard_rows * N * 2;
-      uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(shard_rows)}, strides[2] = {0, static_cast<uint64_t>(N) * 2};
+      const long long ncc = (N + 63) / 64;
+      uint8_t* base = static_cast<uint8_t*>(stage_ptrs[o]) + (static_cast<long long>(par) * world + rank) * shard_rows * ncc * 64 * 2;
+      uint64_t dims[2] = {64, static_cast<uint64_t>(shard_rows * ncc)}, strides[2] = {0, 128};
       uint32_t box[2] = {64, BM};
       if (b2host::encode_tmap(&maps[par * world + o], dt, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
     }

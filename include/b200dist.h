@@ -50,6 +50,19 @@ void b2_gemm_set_pair_mode(int mode);
 int b2_gemm_resident_pairs(void);   /* CTA pairs of the GEMM kernel that can be co-resident (0 before the first pair launch) */
 
 /* ------------------------------------------------------------------------------------------
+ * Swin shifted-window attention (7x7 windows = 49 tokens, head_dim 32), fused forward / backward.
+ * qkv [Bw, 49, 3, heads, 32] (Bw = batch * nW windows) -> out [Bw, 49, heads*32]; bias fp32 [heads, 49, 49]
+ * (relative-position bias gathered from its table), mask fp32 [nW, 49, 49] or NULL (shifted windows; window w uses
+ * mask[w % nW]); lse fp32 [Bw, heads, 49].  Backward writes dqkv (layout of qkv) and ACCUMULATES d(bias) into dbias.
+ * replaces: torchvision ShiftedWindowAttention's matmul / +bias / +mask / softmax / matmul chain.
+ */
+int b2_window_attn_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW,
+                       int heads, int tokens, int head_dim, float scale, int dtype, void* stream);
+int b2_window_attn_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout,
+                       const float* lse, void* dqkv, float* dbias, long long Bw, int nW, int heads, int tokens, int head_dim,
+                       float scale, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].
  * Backward needs an fp32 workspace of b2_norm_bwd_num_parts(rows,H) * 2 * H floats (every element is
  * written before it is read); dgamma/dbeta are fp32 and are accumulated when accumulate != 0.

@@ -77,10 +77,8 @@ class ShiftedWindowAttention(nn.Module):
             x = torch.roll(x, shifts=(-shift[0], -shift[1]), dims=(1, 2))
         nW = (pH // ws) * (pW // ws)
         x = x.view(B, pH // ws, ws, pW // ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B * nW, ws * ws, C)
-        qkv = self.qkv(x).reshape(B * nW, ws * ws, 3, self.heads, C // self.heads).permute(2, 0, 3, 1, 4)
-        q, k, v = qkv[0], qkv[1], qkv[2]
-        attn = (q * (C // self.heads) ** -0.5) @ k.transpose(-2, -1)
-        attn = attn + self._bias().to(attn.dtype)
+        qkv = self.qkv(x)                                   # [B*nW, ws*ws, 3C], last dim = [3][heads][head_dim]
+        mask = None
         if sum(shift) > 0:
             mask = x.new_zeros((pH, pW))
             hs = ((0, -ws), (-ws, -shift[0]), (-shift[0], None))
@@ -92,11 +90,9 @@ class ShiftedWindowAttention(nn.Module):
                     c += 1
             mask = mask.view(pH // ws, ws, pW // ws, ws).permute(0, 2, 1, 3).reshape(nW, ws * ws)
             mask = mask.unsqueeze(1) - mask.unsqueeze(2)
-            mask = mask.masked_fill(mask != 0, float(-100.0)).masked_fill(mask == 0, float(0.0))
-            attn = attn.view(B, nW, self.heads, ws * ws, ws * ws) + mask.to(attn.dtype).unsqueeze(1).unsqueeze(0)
-            attn = attn.view(-1, self.heads, ws * ws, ws * ws)
-        attn = F.softmax(attn.float(), dim=-1).to(v.dtype)
-        x = (attn @ v).transpose(1, 2).reshape(B * nW, ws * ws, C)
+            mask = mask.masked_fill(mask != 0, float(-100.0)).masked_fill(mask == 0, float(0.0))      # [nW, T, T]
+        # scores + relative-position bias + shift mask + softmax + PV in one fused kernel (ops/functional.window_attention)
+        x = OF.window_attention(qkv, self._bias()[0], mask, self.heads, (C // self.heads) ** -0.5)
         x = self.proj(x)
         x = x.view(B, pH // ws, pW // ws, ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B, pH, pW, C)
         if sum(shift) > 0:

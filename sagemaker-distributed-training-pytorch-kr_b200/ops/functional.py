@@ -295,3 +295,40 @@ def rope_tables(max_pos: int, hd: int, base: float = 10000.0, device=None):
     inv = 1.0 / (base ** (torch.arange(0, hd, 2, device=device).float() / hd))
     ang = torch.arange(max_pos, device=device).float()[:, None] * inv[None]
     return ang.cos().contiguous(), ang.sin().contiguous()
+
+
+class _WindowAttention(torch.autograd.Function):
+    """Swin window attention on the fused projection output: qkv [Bw, T, 3C] -> [Bw, T, C]."""
+
+    @staticmethod
+    def forward(ctx, qkv, bias, mask, heads, scale):
+        qkv = qkv.contiguous()
+        bias32 = bias.float().contiguous()
+        mask32 = mask.float().contiguous() if mask is not None else None
+        out, lse = N.window_attn_fwd(qkv, bias32, mask32, heads, scale)
+        ctx.save_for_backward(qkv, bias32, out, lse)
+        ctx.mask, ctx.heads, ctx.scale, ctx.bias_dtype = mask32, heads, scale, bias.dtype
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, bias32, out, lse = ctx.saved_tensors
+        dqkv, dbias = N.window_attn_bwd(qkv, bias32, ctx.mask, out, dout, lse, ctx.heads, ctx.scale)
+        return dqkv, dbias.to(ctx.bias_dtype), None, None, None
+
+
+def window_attention(qkv, bias, mask, heads: int, scale: float):
+    """qkv [Bw, T, 3*C] with the last dim laid out [3][heads][head_dim]; bias [heads, T, T]; mask [nW, T, T] or None.
+    7x7 windows with head_dim 32 in bf16/fp16 on the GPU run the fused kernel; everything else the same math in PyTorch
+    (autograd)."""
+    Bw, T, C3 = qkv.shape
+    hd = C3 // 3 // heads
+    if T == 49 and hd == 32 and (not qkv.is_cuda or _lowp(qkv)):
+        return _WindowAttention.apply(qkv, bias, mask, heads, scale)
+    q, k, v = qkv.view(Bw, T, 3, heads, hd).permute(2, 0, 3, 1, 4)
+    attn = (q * scale) @ k.transpose(-2, -1) + bias.to(q.dtype)[None]
+    if mask is not None:
+        nW = mask.shape[0]
+        attn = (attn.view(Bw // nW, nW, heads, T, T) + mask.to(attn.dtype)[None, :, None]).view(Bw, heads, T, T)
+    attn = torch.softmax(attn.float(), dim=-1).to(v.dtype)
+    return (attn @ v).transpose(1, 2).reshape(Bw, T, C3 // 3)

@@ -58,6 +58,8 @@ _SIGS = {
     "b2_scale_check": [c_p, c_ll, c_f, c_p, c_p],
     "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
+    "b2_window_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
+    "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_num_sms": [],
@@ -683,3 +685,58 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
         _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
     else:
         dq.copy_(dq32)
+
+
+# =============================================================================================
+# Swin window attention.  qkv [Bw, T, 3*C] (last dim = [3][heads][hd]), bias fp32 [heads, T, T], mask fp32 [nW, T, T] | None
+# =============================================================================================
+def _wattn_ref(qkv, bias, mask, heads, scale):
+    Bw, T, C3 = qkv.shape
+    hd = C3 // 3 // heads
+    q, k, v = qkv.float().view(Bw, T, 3, heads, hd).permute(2, 0, 3, 1, 4)          # [Bw, heads, T, hd]
+    s = torch.matmul(q * scale, k.transpose(-1, -2)) + bias.float()[None]
+    if mask is not None:
+        nW = mask.shape[0]
+        s = (s.view(Bw // nW, nW, heads, T, T) + mask.float()[None, :, None]).view(Bw, heads, T, T)
+    lse = torch.logsumexp(s, -1)
+    p = torch.exp(s - lse[..., None])
+    return q, k, v, p, lse
+
+
+def window_attn_fwd(qkv, bias, mask, heads: int, scale: float):
+    """Returns (out [Bw, T, C], lse [Bw, heads, T])."""
+    Bw, T, C3 = qkv.shape
+    C = C3 // 3
+    if not qkv.is_cuda:
+        q, k, v, p, lse = _wattn_ref(qkv, bias, mask, heads, scale)
+        o = torch.matmul(p, v).transpose(1, 2).reshape(Bw, T, C)
+        return o.to(qkv.dtype), lse
+    assert qkv.is_contiguous() and bias.dtype == torch.float32 and bias.is_contiguous()
+    out = torch.empty((Bw, T, C), dtype=qkv.dtype, device=qkv.device)
+    lse = torch.empty((Bw, heads, T), dtype=torch.float32, device=qkv.device)
+    nW = mask.shape[0] if mask is not None else 1
+    _call("b2_window_attn_fwd", _p(qkv), _p(bias), _p(mask), _p(out), _p(lse), Bw, nW, heads, T, C // heads, float(scale), _dt(qkv), _st())
+    return out, lse
+
+
+def window_attn_bwd(qkv, bias, mask, out, dout, lse, heads: int, scale: float):
+    """Returns (dqkv like qkv, dbias fp32 [heads, T, T])."""
+    Bw, T, C3 = qkv.shape
+    C = C3 // 3
+    if not qkv.is_cuda:
+        q, k, v, p, _ = _wattn_ref(qkv, bias, mask, heads, scale)
+        do = dout.float().view(Bw, T, heads, C // heads).transpose(1, 2)
+        of = out.float().view(Bw, T, heads, C // heads).transpose(1, 2)
+        dv = torch.matmul(p.transpose(-1, -2), do)
+        dp = torch.matmul(do, v.transpose(-1, -2))
+        ds = p * (dp - (do * of).sum(-1, keepdim=True))
+        dq = torch.matmul(ds, k) * scale
+        dk = torch.matmul(ds.transpose(-1, -2), q) * scale
+        dqkv = torch.stack([dq, dk, dv], 0).permute(1, 3, 0, 2, 4).reshape(Bw, T, C3)
+        return dqkv.to(qkv.dtype), ds.sum(0)
+    dqkv = torch.empty_like(qkv)
+    dbias = torch.zeros((heads, T, T), dtype=torch.float32, device=qkv.device)
+    nW = mask.shape[0] if mask is not None else 1
+    _call("b2_window_attn_bwd", _p(qkv), _p(bias), _p(mask), _p(out), _p(dout.contiguous()), _p(lse), _p(dqkv), _p(dbias), Bw, nW, heads, T,
+          C // heads, float(scale), _dt(qkv), _st())
+    return dqkv, dbias

@@ -173,7 +173,7 @@ class Fabric:
         key = (rows, Nn, dtype)
         st = self._rs.get(key)
         if st is None:
-            stage = self.alloc(2 * self.world * rows * Nn, dtype)
+            stage = self.alloc(2 * self.world * rows * ((Nn + 63) // 64) * 64, dtype)     # chunk-major slots (see b2_make_rs_maps)
             cnt = self.alloc(max(rows // 128, 1), torch.int32)
             maps = torch.empty(2 * self.world * 128, dtype=torch.uint8, device=stage.tensor.device)
             rc = N.lib().b2_make_rs_maps(N._p(maps), stage.ptrs, self.world, self.rank, rows, Nn, N._dt(stage.tensor))

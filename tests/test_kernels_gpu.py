@@ -20,7 +20,7 @@ def kc():
     return mod
 
 
-@pytest.mark.parametrize("section", ["gemm", "norm", "elementwise", "xent", "optim", "embedding", "attn"])
+@pytest.mark.parametrize("section", ["gemm", "norm", "elementwise", "xent", "optim", "embedding", "attn", "wattn"])
 def test_kernel_section(kc, section):
     from b200dist.ops import native as N
     assert N.available(), "libb200dist.so missing on a GPU box"
