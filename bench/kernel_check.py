@@ -354,6 +354,13 @@ def check_wattn(quick):
         dqkvr, dbiasr = N.window_attn_bwd(cpu(qkv), cpu(bias), cpu(mask), outr.to(torch.bfloat16), cpu(do), lser, heads, scale)
         report(f"wattn bwd dqkv Bw{Bw} heads{heads}", dqkv, dqkvr, 4e-2)
         report(f"wattn bwd dbias Bw{Bw} heads{heads}", dbias, dbiasr, 2e-2)
+    # cyclic shift + window partition and its inverse (one gather pass each) against roll + permute
+    for (B, H, W, C, sh) in [(2, 14, 14, 64, (3, 3)), (3, 28, 56, 128, (3, 0)), (1, 7, 7, 32, (0, 0))]:
+        x = torch.randn(B, H, W, C, device=dev, dtype=torch.bfloat16)
+        xw = N.window_shuffle(x, B, H, W, 7, sh, False)
+        report(f"window partition B{B} {H}x{W} C{C} shift{sh}", xw, N.window_shuffle(cpu(x), B, H, W, 7, sh, False), 0.0)
+        back = N.window_shuffle(xw, B, H, W, 7, sh, True)
+        report(f"window reverse  B{B} {H}x{W} C{C} shift{sh} (round trip)", back, x, 0.0)
     if not quick:
         for (Bw, heads, nW, tag) in [(4096, 4, 64, "swin_b stage 1, batch 64"), (256, 16, 4, "swin_b stage 3, batch 64")]:
             qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)

@@ -65,13 +65,13 @@ B2_DEVICE void stage_tile(const T* base, long long row_stride, float* dst, int t
   }
 }
 B2_DEVICE float dot32(const float* a, const float* s /* smem, warp-uniform address */) {
-  float acc = 0.f;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;       // four independent chains: the FMA latency, not the count, bounds this
 #pragma unroll
   for (int d = 0; d < WD; d += 4) {
     const float4 k = *reinterpret_cast<const float4*>(s + d);
-    acc = fmaf(a[d], k.x, acc); acc = fmaf(a[d + 1], k.y, acc); acc = fmaf(a[d + 2], k.z, acc); acc = fmaf(a[d + 3], k.w, acc);
+    a0 = fmaf(a[d], k.x, a0); a1 = fmaf(a[d + 1], k.y, a1); a2 = fmaf(a[d + 2], k.z, a2); a3 = fmaf(a[d + 3], k.w, a3);
   }
-  return acc;
+  return (a0 + a1) + (a2 + a3);
 }
 
 // ------------------------------------------------------------------------------------------ forward
@@ -271,4 +271,58 @@ extern "C" int b2_window_attn_bwd(const void* qkv, const float* bias, const floa
     wattn_bwd_kernel<__half><<<grid, WG, BWD_SMEM, st>>>((const __half*)qkv, bias, mask, (const __half*)out, (const __half*)dout, lse, (__half*)dqkv,
                                                          dbias, Bw, nW > 0 ? nW : 1, heads, scale);
   return wcheck("window_attn_bwd");
+}
+
+// ------------------------------------------------------------------------------------------
+// cyclic shift + window partition (and its inverse) in one pass.
+//   partition: out[b, wy, wx, ty, tx, :] = in[b, (wy*ws + ty + sh) % H, (wx*ws + tx + sw) % W, :]     (= roll(-s) then partition)
+//   reverse  : out[b, y, x, :]           = in[b, wy, wx, ty, tx, :]  with (y', x') = ((y - sh) % H, (x - sw) % W)   (= unpartition then roll(+s))
+// replaces: torch.roll + view/permute/reshape copies around every Swin attention (two passes over the activations each way);
+// the two maps are inverse permutations, so each is the other's backward.
+// ------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256)
+window_shuffle_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int B, int H, int W, int vecC, int ws, int sh, int sw,
+                      int reverse) {
+  const int nwx = W / ws, nwy = H / ws;
+  const long long total = static_cast<long long>(B) * H * W * vecC;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(idx % vecC);
+    long long row = idx / vecC;                       // OUTPUT row
+    long long src;
+    if (!reverse) {
+      const int tx = static_cast<int>(row % ws); row /= ws;
+      const int ty = static_cast<int>(row % ws); row /= ws;
+      const int wx = static_cast<int>(row % nwx); row /= nwx;
+      const int wy = static_cast<int>(row % nwy); row /= nwy;      // row = b
+      int y = wy * ws + ty + sh; if (y >= H) y -= H;
+      int x = wx * ws + tx + sw; if (x >= W) x -= W;
+      src = (row * H + y) * W + x;
+    } else {
+      const int x = static_cast<int>(row % W); row /= W;
+      const int y = static_cast<int>(row % H); row /= H;           // row = b
+      int yp = y - sh; if (yp < 0) yp += H;
+      int xp = x - sw; if (xp < 0) xp += W;
+      src = (((row * nwy + yp / ws) * nwx + xp / ws) * ws + yp % ws) * ws + xp % ws;
+    }
+    out[idx] = in[src * vecC + v];
+  }
+}
+}  // namespace
+
+// in / out: 16-bit elements, C % 8 == 0, H and W multiples of ws, 0 <= shift < ws
+extern "C" int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int ws, int shift_h, int shift_w, int reverse,
+                                 void* stream) {
+  if ((C % 8) || ws <= 0 || (H % ws) || (W % ws) || shift_h < 0 || shift_w < 0 || shift_h >= H || shift_w >= W) {
+    b2host::set_error("window_shuffle: need C %% 8 == 0, H and W multiples of the window size, 0 <= shift < extent"); return -1;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(b2host::num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
+  window_shuffle_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(static_cast<const uint4*>(in), static_cast<uint4*>(out), B, H, W, C / 8,
+                                                                        ws, shift_h, shift_w, reverse);
+  return wcheck("window_shuffle");
 }

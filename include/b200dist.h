@@ -61,6 +61,10 @@ int b2_window_attn_fwd(const void* qkv, const float* bias, const float* mask, vo
 int b2_window_attn_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout,
                        const float* lse, void* dqkv, float* dbias, long long Bw, int nW, int heads, int tokens, int head_dim,
                        float scale, int dtype, void* stream);
+/* cyclic shift + window partition in one pass (reverse != 0: the inverse, un-partition + shift back); 16-bit elements,
+ * in [B, H, W, C] <-> out [B * (H/ws) * (W/ws), ws*ws, C].  replaces torch.roll + permute copies. */
+int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int ws, int shift_h, int shift_w, int reverse,
+                      void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].

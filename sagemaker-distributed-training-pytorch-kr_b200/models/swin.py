@@ -73,10 +73,8 @@ class ShiftedWindowAttention(nn.Module):
         x = F.pad(x, (0, 0, 0, pad_r, 0, pad_b))
         _, pH, pW, _ = x.shape
         shift = [self.shift if ws < pH else 0, self.shift if ws < pW else 0]
-        if sum(shift) > 0:
-            x = torch.roll(x, shifts=(-shift[0], -shift[1]), dims=(1, 2))
         nW = (pH // ws) * (pW // ws)
-        x = x.view(B, pH // ws, ws, pW // ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B * nW, ws * ws, C)
+        x = OF.window_partition(x, ws, shift)               # cyclic shift + partition in one pass: [B*nW, ws*ws, C]
         qkv = self.qkv(x)                                   # [B*nW, ws*ws, 3C], last dim = [3][heads][head_dim]
         mask = None
         if sum(shift) > 0:
@@ -94,10 +92,8 @@ class ShiftedWindowAttention(nn.Module):
         # scores + relative-position bias + shift mask + softmax + PV in one fused kernel (ops/functional.window_attention)
         x = OF.window_attention(qkv, self._bias()[0], mask, self.heads, (C // self.heads) ** -0.5)
         x = self.proj(x)
-        x = x.view(B, pH // ws, pW // ws, ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B, pH, pW, C)
-        if sum(shift) > 0:
-            x = torch.roll(x, shifts=(shift[0], shift[1]), dims=(1, 2))
-        return x[:, :H, :W, :].contiguous()
+        x = OF.window_reverse(x, B, pH, pW, ws, shift)      # un-partition + shift back in one pass
+        return x if (pH == H and pW == W) else x[:, :H, :W, :].contiguous()
 
 
 class MLP(nn.Module):

@@ -332,3 +332,28 @@ def window_attention(qkv, bias, mask, heads: int, scale: float):
         attn = (attn.view(Bw // nW, nW, heads, T, T) + mask.to(attn.dtype)[None, :, None]).view(Bw, heads, T, T)
     attn = torch.softmax(attn.float(), dim=-1).to(v.dtype)
     return (attn @ v).transpose(1, 2).reshape(Bw, T, C3 // 3)
+
+
+class _WindowShuffle(torch.autograd.Function):
+    """cyclic shift + window partition (or its inverse) as ONE gather pass; the two maps are each other's backward."""
+
+    @staticmethod
+    def forward(ctx, x, B, H, W, ws, shift, reverse):
+        ctx.cfg = (B, H, W, ws, shift, reverse)
+        return N.window_shuffle(x, B, H, W, ws, shift, reverse)
+
+    @staticmethod
+    def backward(ctx, g):
+        B, H, W, ws, shift, reverse = ctx.cfg
+        return N.window_shuffle(g, B, H, W, ws, shift, not reverse), None, None, None, None, None, None
+
+
+def window_partition(x, ws: int, shift=(0, 0)):
+    """[B, H, W, C] -> [B * nW, ws*ws, C] after rolling by -shift (H, W multiples of ws)."""
+    B, H, W, _ = x.shape
+    return _WindowShuffle.apply(x, B, H, W, ws, (int(shift[0]), int(shift[1])), False)
+
+
+def window_reverse(xw, B: int, H: int, W: int, ws: int, shift=(0, 0)):
+    """inverse of window_partition: [B * nW, ws*ws, C] -> [B, H, W, C], rolled back by +shift."""
+    return _WindowShuffle.apply(xw, B, H, W, ws, (int(shift[0]), int(shift[1])), True)

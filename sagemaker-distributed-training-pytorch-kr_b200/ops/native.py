@@ -58,6 +58,7 @@ _SIGS = {
     "b2_scale_check": [c_p, c_ll, c_f, c_p, c_p],
     "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
+    "b2_window_shuffle": [c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_window_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
@@ -740,3 +741,23 @@ def window_attn_bwd(qkv, bias, mask, out, dout, lse, heads: int, scale: float):
     _call("b2_window_attn_bwd", _p(qkv), _p(bias), _p(mask), _p(out), _p(dout.contiguous()), _p(lse), _p(dqkv), _p(dbias), Bw, nW, heads, T,
           C // heads, float(scale), _dt(qkv), _st())
     return dqkv, dbias
+
+
+def window_shuffle(x, B: int, H: int, W: int, ws: int, shift, reverse: bool):
+    """reverse=False: x [B, H, W, C] -> [B*nW, ws*ws, C] (roll by -shift, then window partition);
+    reverse=True : x [B*nW, ws*ws, C] -> [B, H, W, C] (un-partition, then roll by +shift)."""
+    C = x.shape[-1]
+    sh, sw = int(shift[0]), int(shift[1])
+    if x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and C % 8 == 0:
+        x = x.contiguous()
+        out = torch.empty((B * (H // ws) * (W // ws), ws * ws, C) if not reverse else (B, H, W, C), dtype=x.dtype, device=x.device)
+        _call("b2_window_shuffle", _p(x), _p(out), B, H, W, C, ws, sh, sw, int(reverse), _st())
+        return out
+    if not reverse:
+        if sh or sw:
+            x = torch.roll(x, shifts=(-sh, -sw), dims=(1, 2))
+        return x.reshape(B, H // ws, ws, W // ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(-1, ws * ws, C)
+    x = x.reshape(B, H // ws, W // ws, ws, ws, C).permute(0, 1, 3, 2, 4, 5).reshape(B, H, W, C)
+    if sh or sw:
+        x = torch.roll(x, shifts=(sh, sw), dims=(1, 2))
+    return x
