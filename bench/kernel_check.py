@@ -108,6 +108,12 @@ def _gemm_numerics(tag):
         got = N.gemm(a, b, epilogue=epi, bias=bb, aux=ax)
         ref = N.gemm(cpu(a), cpu(b), epilogue=epi, bias=cpu(bb), aux=cpu(ax), out=torch.empty(M, Nn))
         report(f"gemm[{tag}] epilogue {nm}", got, ref, 2e-2)
+    for epi, nm in [(N.EPI_BIAS_GELU | N.EPI_ERF, "bias_gelu(erf)"), (N.EPI_DGELU | N.EPI_ERF, "dgelu(erf)")]:
+        bb = None if (epi & 0xFF) == N.EPI_DGELU else bias
+        ax = aux if (epi & 0xFF) == N.EPI_DGELU else None
+        got = N.gemm(a, b, epilogue=epi, bias=bb, aux=ax)
+        ref = N.gemm(cpu(a), cpu(b), epilogue=epi, bias=cpu(bb), aux=cpu(ax), out=torch.empty(M, Nn))
+        report(f"gemm[{tag}] epilogue {nm}", got, ref, 2e-2)
     z = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
     got = N.gemm(a, b, epilogue=N.EPI_BIAS_GELU_DUAL, bias=bias, out2=z)
     zr = torch.empty(M, Nn)

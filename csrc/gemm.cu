@@ -38,6 +38,7 @@ struct GemmParams {
   int M, N, K;
   int tiles_m, tiles_n, split_k, kb_per_split, num_kb;
   int epilogue;
+  int act_erf;      // GELU epilogues: 0 = tanh approximation (Megatron / GPT-2), 1 = exact erf form (Swin, torch default)
   int fmt;          // 0 fp16, 1 bf16
   int out_fp32;
   int reduce_add;   // fp32 output accumulated with TMA reduce-add
@@ -258,6 +259,10 @@ B2_DEVICE float gelu_tanh_grad(float x) {
   float t = tanh_approx(u);
   float du = fmaf(3.f * k0 * k1, x2, k0);
   return fmaf(0.5f * x * fmaf(-t, t, 1.f), du, fmaf(0.5f, t, 0.5f));
+}
+B2_DEVICE float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.7071067811865476f)); }
+B2_DEVICE float gelu_erf_grad(float x) {
+  return fmaf(x * 0.3989422804014327f, __expf(-0.5f * x * x), 0.5f * (1.f + erff(x * 0.7071067811865476f)));
 }
 B2_DEVICE uint32_t pack2(float lo, float hi, int fmt) {
   if (fmt == 1) return pack_bf16x2(lo, hi);
@@ -663,16 +668,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               named_bar_sync(bar_id, EPI_THREADS);
               if (leader) { tma_store_2d(&tmC2, sb1, col0, m0); tma_store_commit(); }
             }
+            if (p.act_erf) {
 #pragma unroll
-            for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);       // runs while the TMA engine reads the z tile
+              for (int i = 0; i < 64; ++i) f[i] = gelu_erf(f[i]);
+            } else {
+#pragma unroll
+              for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);     // runs while the TMA engine reads the z tile
+            }
             if (TEAMS == 2) {
               if (leader) tma_store_wait_read<0>();
               named_bar_sync(bar_id, EPI_THREADS);
             }
           } else {
             if (p.epilogue == B2_EPI_BIAS_GELU) {
+              if (p.act_erf) {
 #pragma unroll
-              for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
+                for (int i = 0; i < 64; ++i) f[i] = gelu_erf(f[i]);
+              } else {
+#pragma unroll
+                for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);
+              }
             } else if (use_aux) {
               const bool is_res = (p.epilogue == B2_EPI_BIAS_RESIDUAL);
 #pragma unroll
@@ -682,8 +697,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float z[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, d.x, d.y};
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
-                  if (is_res) f[8 * j + e] += z[e];
-                  else        f[8 * j + e] *= gelu_tanh_grad(z[e]);
+                  if (is_res)         f[8 * j + e] += z[e];
+                  else if (p.act_erf) f[8 * j + e] *= gelu_erf_grad(z[e]);
+                  else                f[8 * j + e] *= gelu_tanh_grad(z[e]);
                 }
               }
             }
@@ -828,6 +844,8 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
                        const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
                        int split_k, float alpha, int max_ctas, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int act_erf = (epilogue & B2_EPI_ERF) ? 1 : 0;
+  epilogue &= ~B2_EPI_ERF;
   if (M <= 0 || N <= 0 || K <= 0) { b2host::set_error("gemm: empty problem"); return -1; }
   if ((lda % 8) || (ldb % 8) || (out_fp32 ? (ldc % 4) : (ldc % 8)) || (N % 8)) {
     b2host::set_error("gemm: leading dimensions / N must keep 16-byte alignment (lda=%lld ldb=%lld ldc=%lld N=%d)", lda,
@@ -879,7 +897,7 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   p.num_kb = num_kb;
   p.kb_per_split = (num_kb + split_k - 1) / split_k;
   p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
-  p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0;
+  p.epilogue = epilogue; p.act_erf = act_erf; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0;
   p.out_fp32 = out_fp32; p.reduce_add = accumulate;
   p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = alpha;
   if ((epilogue == B2_EPI_BIAS_RESIDUAL || epilogue == B2_EPI_DGELU) && (aux == nullptr || (ld_aux % 8))) {
@@ -1004,6 +1022,8 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
   p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
+  p.act_erf = (epilogue & B2_EPI_ERF) ? 1 : 0;
+  epilogue &= ~B2_EPI_ERF;
   p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.out_fp32 = 0; p.reduce_add = 0;
   p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = 1.f;
   p.f_rank = rank; p.f_world = world; p.f_bpr = shard_rows / BM; p.f_shard_rows = shard_rows;

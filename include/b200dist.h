@@ -27,6 +27,7 @@ extern "C" {
 #define B2_EPI_BIAS_GELU_DUAL 3  /* C2 = acc + bias[n];  C = gelu_tanh(C2)              */
 #define B2_EPI_BIAS_RESIDUAL 4   /* C = aux[m,n] + acc + bias[n]                        */
 #define B2_EPI_DGELU 5           /* C = acc * gelu_tanh'(aux[m,n])                      */
+#define B2_EPI_ERF 0x100         /* OR into a GELU epilogue: exact erf GELU instead of the tanh approximation */
 
 const char* b2_last_error(void);
 int b2_num_sms(void);

@@ -106,9 +106,7 @@ class MLP(nn.Module):
 
     def forward(self, x):
         fc1, fc2 = getattr(self, "0"), getattr(self, "3")
-        h = OF.linear(x, fc1.weight, None)
-        h = OF.bias_act(h, fc1.bias, N.ACT_GELU_ERF)
-        return fc2(h)
+        return OF.mlp(x, fc1.weight, fc1.bias, fc2.weight, fc2.bias, "gelu_erf")     # bias + GELU / GELU' fused in GEMM epilogues
 
 
 def stochastic_depth(x, p: float, training: bool):

@@ -91,6 +91,48 @@ class _Linear(torch.autograd.Function):
         return dx, gw, gb, d_res, None
 
 
+class _MLP(torch.autograd.Function):
+    """y = fc2(gelu(fc1(x))) as one autograd node: bias + GELU ride in the fc1 GEMM epilogue (both z and gelu(z) are
+    written), and gelu'(z) is applied in the epilogue of the fc2 data-gradient GEMM - no standalone activation kernels."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w2, b2, erf):
+        shp = x.shape
+        x2 = x.reshape(-1, shp[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        flag = N.EPI_ERF if erf else 0
+        z = torch.empty((x2.shape[0], w1.shape[0]), dtype=x.dtype, device=x.device)
+        a = N.gemm(x2, w1, bias=b1, epilogue=N.EPI_BIAS_GELU_DUAL | flag, out2=z)
+        y = N.gemm(a, w2, bias=b2, epilogue=N.EPI_BIAS if b2 is not None else N.EPI_NONE)
+        ctx.save_for_backward(x2, w1, w2, z, a)
+        ctx.params, ctx.shp, ctx.flag = (w1, b1, w2, b2), shp, flag
+        return y.view(*shp[:-1], w2.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w1, w2, z, a = ctx.saved_tensors
+        w1p, b1p, w2p, b2p = ctx.params
+        dy2 = dy.reshape(-1, w2.shape[0])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        gb2 = _bgrad(b2p, dy2)
+        gw2 = _wgrad(w2p, dy2, a) if w2p.requires_grad else None
+        dz = N.gemm(dy2, w2, b_mn=True, epilogue=N.EPI_DGELU | ctx.flag, aux=z)       # (dy W2) * gelu'(z)
+        gb1 = _bgrad(b1p, dz)
+        gw1 = _wgrad(w1p, dz, x2) if w1p.requires_grad else None
+        dx = N.gemm(dz, w1, b_mn=True).view(ctx.shp) if ctx.needs_input_grad[0] else None
+        return dx, gw1, gb1, gw2, gb2, None
+
+
+def mlp(x, w1, b1, w2, b2, act: str = "gelu_erf"):
+    """Two-layer GELU MLP (Swin / ViT / OPT-style).  act: 'gelu_erf' (exact) or 'gelu_tanh'."""
+    if not _lowp(x) or x.shape[-1] % 8 or w1.shape[0] % 8 or w2.shape[0] % 8:
+        h = torch.nn.functional.gelu(torch.nn.functional.linear(x, w1, b1), approximate="tanh" if act == "gelu_tanh" else "none")
+        return torch.nn.functional.linear(h, w2, b2)
+    return _MLP.apply(x, w1, b1, w2, b2, act == "gelu_erf")
+
+
 def linear(x, weight, bias=None, residual=None, act: Optional[str] = None):
     """Low-precision (bf16/fp16) inputs run the tcgen05 GEMM; fp32 inputs (MNIST / fp32 parity runs) use torch."""
     if not _lowp(x) or x.shape[-1] % 8 or weight.shape[0] % 8:

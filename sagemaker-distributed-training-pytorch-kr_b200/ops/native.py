@@ -25,6 +25,7 @@ _launches = 0  # kernels launched through this module (bench.py reports it)
 
 DT_FP16, DT_BF16, DT_FP32 = 0, 1, 2
 EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_BIAS_GELU_DUAL, EPI_BIAS_RESIDUAL, EPI_DGELU = 0, 1, 2, 3, 4, 5
+EPI_ERF = 0x100      # OR into a GELU epilogue: exact erf GELU (Swin / torch default) instead of the tanh approximation
 ACT_GELU_TANH, ACT_GELU_ERF, ACT_RELU, ACT_SILU = 0, 1, 2, 3
 
 c_p, c_i, c_ll, c_f, c_ull = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_ulonglong
@@ -184,15 +185,19 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         c = alpha * (A @ Bm)
         if bias is not None:
             c = c + bias.float()
-        if epilogue == EPI_BIAS_GELU:
-            c = gelu_tanh_ref(c)
-        elif epilogue == EPI_BIAS_GELU_DUAL:
+        erf, epi = bool(epilogue & EPI_ERF), epilogue & ~EPI_ERF
+        act = (lambda t: F.gelu(t)) if erf else gelu_tanh_ref
+        if epi == EPI_BIAS_GELU:
+            c = act(c)
+        elif epi == EPI_BIAS_GELU_DUAL:
             out2.copy_(c.to(out2.dtype))
-            c = gelu_tanh_ref(c)
-        elif epilogue == EPI_BIAS_RESIDUAL:
+            c = act(c)
+        elif epi == EPI_BIAS_RESIDUAL:
             c = c + aux.float()
-        elif epilogue == EPI_DGELU:
-            c = c * gelu_tanh_grad_ref(aux.float())
+        elif epi == EPI_DGELU:
+            z = aux.float()
+            c = c * ((0.5 * (1 + torch.erf(z * 0.7071067811865476)) + z * torch.exp(-0.5 * z * z) * 0.3989422804014327) if erf
+                     else gelu_tanh_grad_ref(z))
         if accumulate:
             out.add_(c.to(out.dtype))
         else:

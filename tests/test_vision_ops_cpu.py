@@ -1,0 +1,68 @@
+"""Swin-specific ops on CPU (the oracles the GPU kernels are checked against): fused window attention autograd vs the eager
+chain, shift+partition / reverse as inverse permutations, the fused GELU MLP node, and torchvision forward parity."""
+import pytest
+import torch
+
+from b200dist.ops import functional as OF
+
+
+def test_window_attention_matches_eager_chain():
+    torch.manual_seed(0)
+    Bw, T, heads = 8, 49, 3
+    qkv = torch.randn(Bw, T, 3 * heads * 32, requires_grad=True)
+    bias = torch.randn(heads, T, T, requires_grad=True)
+    mask = torch.where(torch.rand(4, T, T) < 0.3, -100.0, 0.0)
+    out = OF.window_attention(qkv, bias, mask, heads, 0.2)
+    g = torch.randn_like(out)
+    out.backward(g)
+    g_qkv, g_bias = qkv.grad.clone(), bias.grad.clone()
+    qkv.grad = bias.grad = None
+    q, k, v = qkv.view(Bw, T, 3, heads, 32).permute(2, 0, 3, 1, 4)
+    a = (q * 0.2) @ k.transpose(-2, -1) + bias[None]
+    a = (a.view(2, 4, heads, T, T) + mask[None, :, None]).view(Bw, heads, T, T)
+    ref = (torch.softmax(a, -1) @ v).transpose(1, 2).reshape(Bw, T, heads * 32)
+    ref.backward(g)
+    assert torch.allclose(out, ref, atol=1e-5) and torch.allclose(g_qkv, qkv.grad, atol=1e-5) and torch.allclose(g_bias, bias.grad, atol=1e-4)
+
+
+@pytest.mark.parametrize("shift", [(0, 0), (3, 3), (3, 0)])
+def test_window_partition_reverse_are_inverse(shift):
+    x = torch.randn(2, 14, 21, 8, requires_grad=True)
+    xw = OF.window_partition(x, 7, shift)
+    assert xw.shape == (2 * 2 * 3, 49, 8)
+    ref = torch.roll(x, shifts=(-shift[0], -shift[1]), dims=(1, 2)).view(2, 2, 7, 3, 7, 8).permute(0, 1, 3, 2, 4, 5).reshape(12, 49, 8)
+    assert torch.equal(xw, ref)
+    back = OF.window_reverse(xw, 2, 14, 21, 7, shift)
+    assert torch.equal(back, x)
+    g = torch.randn_like(xw)
+    xw.backward(g)                    # gradient of a permutation = the inverse permutation of the upstream gradient
+    assert torch.equal(x.grad, OF.window_reverse(g, 2, 14, 21, 7, shift))
+
+
+@pytest.mark.parametrize("act", ["gelu_erf", "gelu_tanh"])
+def test_fused_mlp_node_matches_autograd(act):
+    torch.manual_seed(1)
+    t = [torch.randn(s, dtype=torch.bfloat16) for s in ((6, 16), (32, 16), (32,), (16, 32), (16,))]
+    a = [x.clone().requires_grad_() for x in t]
+    y = OF.mlp(*a, act=act)
+    g = torch.randn_like(y)
+    y.backward(g)
+    r = [x.float().requires_grad_() for x in t]
+    h = torch.nn.functional.gelu(torch.nn.functional.linear(r[0], r[1], r[2]), approximate="tanh" if act == "gelu_tanh" else "none")
+    yr = torch.nn.functional.linear(h, r[3], r[4])
+    yr.backward(g.float())
+    for mine, ref in zip([y] + [x.grad for x in a], [yr] + [x.grad for x in r]):
+        scale = ref.abs().max().item() + 1e-6
+        assert (mine.float() - ref).abs().max().item() <= 0.03 * scale
+
+
+def test_swin_t_forward_matches_torchvision():
+    tv = pytest.importorskip("torchvision")
+    from b200dist.models import swin
+    torch.manual_seed(0)
+    m = swin.swin_t(num_classes=10).eval()
+    ref = tv.models.swin_t(weights=None, num_classes=10).eval()
+    ref.load_state_dict(m.state_dict())
+    x = torch.randn(2, 3, 64, 64)
+    with torch.no_grad():
+        assert torch.allclose(m(x), ref(x), atol=1e-5)
