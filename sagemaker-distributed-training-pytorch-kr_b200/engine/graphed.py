@@ -107,3 +107,37 @@ class GraphedMicrobatch:
                 dist.all_reduce(v, group=mpu.get_data_parallel_group())
                 v.div_(dp)
         return [out]
+
+
+class GraphedStep:
+    """Any fixed-shape training closure (zero-grad + forward + backward + fabric gradient reduction) captured once and
+    replayed: used by the DDP workloads, whose ~2000 small launches per step are host-bound when issued from Python.
+    `fn(*static_inputs)` returns a tensor or a tuple of tensors (loss, logits, ...) that live in the graph's memory
+    pool and are overwritten by the next replay; inputs are copied into static buffers before each replay.
+    NCCL collectives must stay outside `fn` (only the fabric kernels are captured)."""
+
+    def __init__(self, fn: Callable, example_inputs):
+        self.fn = fn
+        self.static_in = [torch.empty_like(t) for t in example_inputs]
+        for s, t in zip(self.static_in, example_inputs):
+            s.copy_(t)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                fn(*self.static_in)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = N.launches()
+        with torch.cuda.graph(self.graph):
+            self.static_out = fn(*self.static_in)
+        self.kernels_per_replay = N.launches() - n0
+        torch.cuda.synchronize()
+
+    def __call__(self, *inputs):
+        for s, t in zip(self.static_in, inputs):
+            s.copy_(t, non_blocking=True)
+        self.graph.replay()
+        N.count_launches(self.kernels_per_replay)
+        return self.static_out

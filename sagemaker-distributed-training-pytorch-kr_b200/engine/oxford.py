@@ -61,6 +61,7 @@ def args_fn(argv=None):
     p.add_argument("--max-steps", type=int, default=None)
     p.add_argument("--num-workers", type=int, default=2)
     p.add_argument("--bucket-cap-mb", type=float, default=25.0)
+    p.add_argument("--cuda-graph", action="store_true", help="bf16 path: capture zero-grad + forward + backward + gradient all-reduce once, replay per step")
     return p.parse_args(argv)
 
 
@@ -133,6 +134,17 @@ def train(args):
     logger.info("Processes {}/{} ({:.0f}%) of test data".format(nv, len(test_loader.dataset), 100.0 * nv / len(test_loader.dataset)))
     print(" local_rank : {}, local_batch_size : {}".format(args.local_rank, args.batch_size))
 
+    graphed = None      # built lazily from the first full batch (static shapes: the loader drops nothing, so the last partial batch runs eagerly)
+
+    def eager_step(data, target):
+        optimizer.zero_grad()
+        output = model(data)
+        loss = criterion(output, target)
+        loss.backward()
+        if mixed:
+            optimizer.reduce_model_grads()
+        return loss, output
+
     for epoch in range(1, args.num_epochs + 1):
         batch_time, losses = util.AverageMeter("Time", ":6.3f"), util.AverageMeter("Loss", ":.4e")
         top1, top5 = util.AverageMeter("Acc@1", ":6.2f"), util.AverageMeter("Acc@5", ":6.2f")
@@ -144,12 +156,15 @@ def train(args):
         for batch_idx, (data, target) in enumerate(train_loader):
             data = data.to(dev, non_blocking=True).to(dtype)
             target = target.to(dev, non_blocking=True)
-            optimizer.zero_grad()
-            output = model(data)
-            loss = criterion(output, target)
-            loss.backward()
-            if mixed:
-                optimizer.reduce_model_grads()
+            use_graph = (getattr(args, "cuda_graph", False) and mixed and dev.type == "cuda" and data.size(0) == args.batch_size
+                         and (args.world_size == 1 or getattr(optimizer, "fabric", None) is not None))
+            if use_graph:
+                if graphed is None:
+                    from .graphed import GraphedStep
+                    graphed = GraphedStep(lambda d, t: tuple(x.detach() for x in eager_step(d, t)), (data, target))
+                loss, output = graphed(data, target)
+            else:
+                loss, output = eager_step(data, target)
             optimizer.step()
             since += 1
             if args.rank == 0 and (batch_idx % args.log_interval == args.log_interval - 1 or batch_idx == len(train_loader) - 1):

@@ -15,6 +15,8 @@ from __future__ import annotations
 
 from typing import List, Optional
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -96,6 +98,9 @@ class ShiftedWindowAttention(nn.Module):
         return x if (pH == H and pW == W) else x[:, :H, :W, :].contiguous()
 
 
+_FUSED_MLP = os.environ.get("B2_SWIN_FUSED_MLP", "1") != "0"
+
+
 class MLP(nn.Module):
     """torchvision names: mlp.0 (Linear), mlp.1 GELU, mlp.2 Dropout, mlp.3 (Linear)"""
 
@@ -106,7 +111,10 @@ class MLP(nn.Module):
 
     def forward(self, x):
         fc1, fc2 = getattr(self, "0"), getattr(self, "3")
-        return OF.mlp(x, fc1.weight, fc1.bias, fc2.weight, fc2.bias, "gelu_erf")     # bias + GELU / GELU' fused in GEMM epilogues
+        if _FUSED_MLP:
+            return OF.mlp(x, fc1.weight, fc1.bias, fc2.weight, fc2.bias, "gelu_erf")     # bias + GELU / GELU' fused in GEMM epilogues
+        h = OF.bias_act(OF.linear(x, fc1.weight, None), fc1.bias, N.ACT_GELU_ERF)      # A/B arm: standalone activation kernels
+        return fc2(h)
 
 
 def stochastic_depth(x, p: float, training: bool):
