@@ -294,7 +294,9 @@ B2_DEVICE void decode_tile(const GemmParams& p, int t, int& tm, int& tn, int& ks
 // CTA2: two CTAs of a cluster (one TPC) work on one 256 x BN tile with tcgen05.mma.cta_group::2: each CTA stages its own
 // 128 rows of A and HALF of the B tile (the pair shares B, so operand traffic per MMA halves and the smem ring gets
 // six stages instead of four), the leader CTA issues the MMAs for both, every CTA runs the epilogue of its own rows.
-template <int BN, bool A_MN, bool B_MN, int FUSE = FUSE_NONE, bool CTA2 = false>
+// ERF: the GELU epilogues use the exact erf form (compile-time: a run-time switch inside the unrolled epilogue loops
+// doubled the cost of the tanh path that every GPT layer takes)
+template <int BN, bool A_MN, bool B_MN, int FUSE = FUSE_NONE, bool CTA2 = false, bool ERF = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
@@ -668,7 +670,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               named_bar_sync(bar_id, EPI_THREADS);
               if (leader) { tma_store_2d(&tmC2, sb1, col0, m0); tma_store_commit(); }
             }
-            if (p.act_erf) {
+            if constexpr (ERF) {
 #pragma unroll
               for (int i = 0; i < 64; ++i) f[i] = gelu_erf(f[i]);
             } else {
@@ -681,7 +683,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
           } else {
             if (p.epilogue == B2_EPI_BIAS_GELU) {
-              if (p.act_erf) {
+              if constexpr (ERF) {
 #pragma unroll
                 for (int i = 0; i < 64; ++i) f[i] = gelu_erf(f[i]);
               } else {
@@ -697,9 +699,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 float z[8] = {a.x, a.y, b.x, b.y, cc.x, cc.y, d.x, d.y};
 #pragma unroll
                 for (int e = 0; e < 8; ++e) {
-                  if (is_res)         f[8 * j + e] += z[e];
-                  else if (p.act_erf) f[8 * j + e] *= gelu_erf_grad(z[e]);
-                  else                f[8 * j + e] *= gelu_tanh_grad(z[e]);
+                  if (is_res)            f[8 * j + e] += z[e];
+                  else if constexpr (ERF) f[8 * j + e] *= gelu_erf_grad(z[e]);
+                  else                   f[8 * j + e] *= gelu_tanh_grad(z[e]);
                 }
               }
             }
@@ -768,10 +770,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if constexpr (FUSE == FUSE_RS) fused_finish(p, f_epoch, false);
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool ERF = false>
 int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
            const GemmParams& p, int max_ctas, cudaStream_t stream) {
-  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, false, ERF>;
   const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
   static bool configured = false;
   if (!configured) {
@@ -790,10 +792,10 @@ int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, 
 int g_resident_pairs = 0;
 
 // CTA-pair launch: grid = 2 x (number of 256 x BN tiles, capped at SMs / 2 clusters), cluster dimension (2, 1, 1)
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool ERF = false>
 int launch_pair(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
                 const GemmParams& p, int max_ctas, cudaStream_t stream) {
-  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, true>;
+  auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, true, ERF>;
   const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
   static bool configured = false;
   if (!configured) {
@@ -949,6 +951,19 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
     if (a_mn_major && b_mn_major) return launch_pair<BN_, true, true>(tA, tB, tC, tC2, p, mc, stream);     \
     return launch_pair<BN_, true, false>(tA, tB, tC, tC2, p, mc, stream);                                  \
   } while (0)
+  if (act_erf) {       // exact-erf GELU epilogues: forward / data-gradient layouts only (A K-major)
+    if (a_mn_major) { b2host::set_error("gemm: erf GELU epilogues need a K-major A operand"); return -1; }
+    if (pair) {
+      if (bn == 256) return b_mn_major ? launch_pair<256, false, true, true>(tA, tB, tC, tC2, p, mc, stream)
+                                       : launch_pair<256, false, false, true>(tA, tB, tC, tC2, p, mc, stream);
+      return b_mn_major ? launch_pair<128, false, true, true>(tA, tB, tC, tC2, p, mc, stream)
+                        : launch_pair<128, false, false, true>(tA, tB, tC, tC2, p, mc, stream);
+    }
+    if (bn == 256) return b_mn_major ? launch<256, false, true, true>(tA, tB, tC, tC2, p, mc, stream)
+                                     : launch<256, false, false, true>(tA, tB, tC, tC2, p, mc, stream);
+    return b_mn_major ? launch<128, false, true, true>(tA, tB, tC, tC2, p, mc, stream)
+                      : launch<128, false, false, true>(tA, tB, tC, tC2, p, mc, stream);
+  }
   if (pair) {
     if (bn == 256) B2_DISPATCH_PAIR(256);
     B2_DISPATCH_PAIR(128);
@@ -1022,8 +1037,7 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
   p.M = M; p.N = N; p.K = K;
   p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
   p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
-  p.act_erf = (epilogue & B2_EPI_ERF) ? 1 : 0;
-  epilogue &= ~B2_EPI_ERF;
+  if (epilogue & B2_EPI_ERF) { b2host::set_error("ag_gemm: erf GELU epilogues are not built for the fused kernels"); return -1; }
   p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.out_fp32 = 0; p.reduce_add = 0;
   p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = 1.f;
   p.f_rank = rank; p.f_world = world; p.f_bpr = shard_rows / BM; p.f_shard_rows = shard_rows;
