@@ -307,7 +307,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr int A_BYTES = BM * BK * 2;
   constexpr int B_BYTES = BN_LOAD * BK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  constexpr int STAGES = SMEM_MAIN_BYTES / STAGE_BYTES;
+  // plain / pair kernels give two 16 KB tiles of the operand ring to the epilogue's aux prefetch (residual / pre-activation
+  // tiles arrive by TMA one chunk ahead instead of row-strided global loads); the fused-collective kernels keep the full ring
+  constexpr bool AUX_TMA = (FUSE == FUSE_NONE);
+  constexpr int RING_BYTES = AUX_TMA ? SMEM_MAIN_BYTES - 2 * STAGE_CHUNK_BYTES : SMEM_MAIN_BYTES;
+  constexpr int STAGES = RING_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
   // two epilogue teams everywhere; in GEMM->RS each team leader signals its own half of every tile, so a row block
   // is complete once (world - 1) * tiles_n * TEAMS arrivals have been counted
@@ -316,13 +320,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* stage_base = smem;
-  uint8_t* epi_buf = smem + STAGES * STAGE_BYTES;  // 2 x 16 KB
+  [[maybe_unused]] uint8_t* aux_tiles = smem + RING_BYTES;   // AUX_TMA: 2 x 16 KB (one per epilogue team)
+  uint8_t* epi_buf = smem + SMEM_MAIN_BYTES;       // 2 x 16 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 2 * STAGE_CHUNK_BYTES);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
   uint64_t* tmem_full = bars + 2 * STAGES;
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  [[maybe_unused]] uint64_t* aux_bar = bars + 2 * STAGES + 5;   // [2]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -359,6 +365,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS * (CTA2 ? 2 : 1));   // pair: both CTAs' epilogue threads (leader's copy)
     }
+    if constexpr (AUX_TMA) { mbar_init(&aux_bar[0], 1); mbar_init(&aux_bar[1], 1); }
     mbar_fence_init();
   }
   if (warp == 2) { if constexpr (CTA2) tmem_alloc_2sm<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot); }
@@ -492,6 +499,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
     [[maybe_unused]] int rs_groups = 0, rs_prev_owner = -1, rs_prev_blk = 0;   // GEMM->RS: deferred arrival signal
+    // ---- aux tile prefetch (AUX_TMA): the team leader keeps ONE 16 KB TMA load in flight, for the next chunk this team
+    // will process; (aux_t, aux_c) is that chunk.  The consumer waits on the team's mbarrier, copies its 128-byte row
+    // out of the swizzled tile, and after the team barrier the leader issues the following chunk's load.
+    [[maybe_unused]] const bool aux_on = AUX_TMA && !p.out_fp32 && (p.epilogue == B2_EPI_BIAS_RESIDUAL || p.epilogue == B2_EPI_DGELU);
+    [[maybe_unused]] uint8_t* aux_tile = aux_tiles + team * STAGE_CHUNK_BYTES;
+    [[maybe_unused]] uint32_t aux_phase = 0;
+    [[maybe_unused]] int aux_t = cta0, aux_c = team - TEAMS;
+    [[maybe_unused]] bool aux_more = true;
+    auto aux_issue_next = [&]() {           // leader only
+      if constexpr (AUX_TMA) {
+        while (aux_more) {
+          aux_c += TEAMS;
+          if (aux_c >= BN / 64) { aux_t += nctas; aux_c = team; }
+          if (aux_t >= total_tiles) { aux_more = false; break; }
+          int tm2, tn2, ks2;
+          decode_tile(p, aux_t, tm2, tn2, ks2);
+          const int c0 = tn2 * BN + aux_c * 64;
+          if (c0 >= p.N) { aux_c = BN / 64; continue; }         // rest of this tile is past N: next tile
+          mbar_expect_tx(&aux_bar[team], STAGE_CHUNK_BYTES);
+          tma_load_2d(aux_tile, &tmC2, &aux_bar[team], c0, tm2 * BM_TILE + static_cast<int>(cta_rank) * BM);
+          break;
+        }
+      }
+    };
+    if (aux_on && leader) aux_issue_next();
     // accumulator buffer drained: tell the MMA issuer (pair: the leader CTA's barrier, from both CTAs)
     auto acc_release = [&](uint64_t* bar) {
       if constexpr (CTA2) mbar_arrive_cluster(mapa_u32(smem_u32(bar), 0));
@@ -570,7 +602,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           // this thread's 128 B of the aux tile (residual / pre-activation): requested before the TMEM load so
           // the global-memory latency runs under it (and under the other team's math)
           uint4 aq[8];
-          if (use_aux) {
+          if (use_aux && !aux_on) {
             const uint4* ap = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.aux) +
                                                              static_cast<long long>(row) * p.ld_aux + col0);
 #pragma unroll
@@ -583,6 +615,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tmem_ld_wait();
           if (c + TEAMS >= NCH) { tc_fence_before(); acc_release(&tmem_empty[buf]); }
           if (col0 >= p.N) continue;          // uniform across the team
+          if constexpr (AUX_TMA) {
+            if (aux_on) {                     // the prefetched tile of exactly this chunk (same iteration order as aux_issue_next)
+              mbar_wait(&aux_bar[team], aux_phase);
+              aux_phase ^= 1;
+              const uint8_t* arow = aux_tile + et * 128;
+#pragma unroll
+              for (int j = 0; j < 8; ++j) aq[j] = *reinterpret_cast<const uint4*>(arow + ((j ^ (et & 7)) << 4));
+            }
+          }
           float* f = reinterpret_cast<float*>(v);
           if (p.alpha != 1.f) {
 #pragma unroll
@@ -707,6 +748,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
             named_bar_sync(bar_id, EPI_THREADS);
+            if (aux_on && leader) aux_issue_next();       // every thread of the team has copied its aux row out
           }
           {
             uint8_t* rowp = sb0 + et * 128;
@@ -931,6 +973,10 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
       if (epilogue == B2_EPI_BIAS_GELU_DUAL) {
         strides[1] = static_cast<uint64_t>(ldc2) * 2;
         if (b2host::encode_tmap(&tC2, dt, 2, C2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+      } else if (epilogue == B2_EPI_BIAS_RESIDUAL || epilogue == B2_EPI_DGELU) {
+        // the aux operand (residual / pre-activation) is prefetched tile by tile with TMA through the C2 map slot
+        strides[1] = static_cast<uint64_t>(ld_aux) * 2;
+        if (b2host::encode_tmap(&tC2, dt, 2, aux, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
       } else {
         tC2 = tC;
       }
