@@ -51,6 +51,7 @@ struct AttnParams {
   uint32_t drop_thresh;  // p * 2^32
   uint32_t drop_seed;
   float inv_keep;        // 1 / (1 - p)
+  int dbg_skip;          // profiling hook (b2_attn_set_debug): bit 0 = skip the dQ reduce-add, bit 1 = skip the softmax math
 };
 
 // counter-based dropout decision shared by forward and backward (and restated in ops/native.py for the CPU oracle):
@@ -574,8 +575,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       fence_proxy_async_smem();
       named_bar_sync(1, 256);
       if (g == 0 && r == 0) {
+        if (!(p.dbg_skip & 1)) {
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c) tma_reduce_add_4d(&tmDQ, sDQ + c * (BLK * 128), c * 32, head, bat, (qb_first + it) * BLK);
+          for (int c = 0; c < D / 32; ++c) tma_reduce_add_4d(&tmDQ, sDQ + c * (BLK * 128), c * 32, head, bat, (qb_first + it) * BLK);
+        }
         tma_store_commit();
         tma_store_wait_read<0>();
       }
@@ -600,7 +603,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float* lse_s = sLse + (it & 1) * BLK;
       const float* del_s = sDelta + (it & 1) * BLK;
 #pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) {
+      for (int cc = 0; cc < ((p.dbg_skip & 2) ? 0 : 2); ++cc) {
         const int c = g * 2 + cc;
         uint32_t sv[32], dv[32];
         tmem_ld_32x32b_x32(tmem_base + lane_off + ST_COL + c * 32, sv);
@@ -699,7 +702,9 @@ int check(const char* what) {
   if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
   return 0;
 }
+int g_attn_dbg = 0;
 void set_dropout(AttnParams& p, float p_drop, unsigned long long seed) {
+  p.dbg_skip = g_attn_dbg;
   const double t = static_cast<double>(p_drop) * 4294967296.0;
   p.drop_thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
   p.drop_seed = static_cast<uint32_t>(seed ^ (seed >> 32));
@@ -708,6 +713,9 @@ void set_dropout(AttnParams& p, float p_drop, unsigned long long seed) {
 }  // namespace
 
 // strides are in ELEMENTS: (seq, batch, head); head_dim contiguous.  bf16 only.
+// profiling hook: results are WRONG while a bit is set (timing experiments only)
+extern "C" void b2_attn_set_debug(int bits) { g_attn_dbg = bits; }
+
 extern "C" int b2_attn_fwd(const void* q, const void* k, const void* v, void* o, float* lse, int seqlen, int batch,
                            int heads, int D, long long q_ss, long long q_sb, long long q_sh, long long k_ss,
                            long long k_sb, long long k_sh, long long v_ss, long long v_sb, long long v_sh,
