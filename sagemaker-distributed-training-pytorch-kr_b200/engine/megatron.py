@@ -498,7 +498,17 @@ def pretrain(train_valid_test_dataset_provider, model_provider, model_type, forw
     model, optimizer, sched = setup_model_and_optimizer(model_provider)
     timers("model-and-optimizer-setup").stop()
     timers("train/valid/test-data-iterators-setup", log_level=0).start(barrier=True)
-    train_it, valid_it, test_it = build_train_valid_test_data_iterators(train_valid_test_dataset_provider)
+    if args.virtual_pipeline_model_parallel_size is not None and len(model) > 1:
+        # interleaved schedule: every model chunk draws the SAME micro-batch sequence from its own iterator (first chunk
+        # needs the tokens, last chunk the labels of one and the same batch)
+        train_it, valid_it, test_it = [], [], []
+        for i in range(len(model)):
+            mpu.set_virtual_pipeline_model_parallel_rank(i)
+            t_i, v_i, te_i = build_train_valid_test_data_iterators(train_valid_test_dataset_provider)
+            train_it.append(t_i); valid_it.append(v_i); test_it.append(te_i)
+        mpu.set_virtual_pipeline_model_parallel_rank(0)
+    else:
+        train_it, valid_it, test_it = build_train_valid_test_data_iterators(train_valid_test_dataset_provider)
     timers("train/valid/test-data-iterators-setup").stop()
     print_rank_0("done with setup ...")
     timers.log(["model-and-optimizer-setup", "train/valid/test-data-iterators-setup"], barrier=True)

@@ -83,3 +83,18 @@ def test_swin_b_matches_torchvision_structure():
     a = {k: tuple(v.shape) for k, v in ref.state_dict().items()}
     b = {k: tuple(v.shape) for k, v in ours.state_dict().items()}
     assert a == b and sum(p.numel() for p in ours.parameters()) == 87_768_224
+
+
+def test_gpt_pretrain_tp2_pp2_interleaved_matches_single_process():
+    """4 gloo ranks, TP=2 (+SP) x PP=2 with 2 model chunks per rank: same loss curve as one process (each model chunk draws
+    the same micro-batch sequence from its own data iterator)."""
+    base = [a for a in GPT]
+    base[base.index("--num-layers") + 1] = "8"
+    base[base.index("--global-batch-size") + 1] = "8"
+    base[base.index("--train-iters") + 1] = "3"
+    base += ["--hidden-dropout", "0", "--attention-dropout", "0", "--eval-iters", "0"]
+    single = _losses(_run("pretrain_gpt.py", base))
+    par = _losses(_run("pretrain_gpt.py", base + ["--tensor-model-parallel-size", "2", "--sequence-parallel", "--pipeline-model-parallel-size", "2",
+                                                  "--num-layers-per-virtual-pipeline-stage", "2"], nproc=4, timeout=900))
+    assert sorted(single) == [1, 2, 3] == sorted(par)
+    assert all(abs(float(single[i]) - float(par[i])) < 2e-4 for i in (1, 2, 3)), (single, par)
