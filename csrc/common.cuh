@@ -351,5 +351,6 @@ int encode_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* 
                 const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
 const char* last_error();
 void set_error(const char* fmt, ...);
-int num_sms();
+int num_sms();            // SM count minus the reserve set with set_reserved_sms
+void set_reserved_sms(int n);
 }  // namespace b2host

@@ -18,6 +18,11 @@ void set_error(const char* fmt, ...) {
 }
 const char* last_error() { return g_err; }
 
+static int g_reserved_sms = 0;
+// SMs the persistent kernels leave free (b2_set_reserved_sms): kernels that spin on a peer GPU (fused collectives) occupy
+// every SM they are given; a library kernel the PEER is waiting for (an NCCL send of pipeline parallelism) must still
+// find an SM on this GPU, or the two GPUs wait on each other forever
+void set_reserved_sms(int n) { g_reserved_sms = n < 0 ? 0 : n; }
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;
@@ -28,7 +33,8 @@ int num_sms() {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
     cached[dev] = n;
   }
-  return cached[dev];
+  const int n = cached[dev] - g_reserved_sms;
+  return n < 8 ? 8 : n;
 }
 
 EncodeTiledFn get_encode_fn() {
@@ -76,3 +82,4 @@ int encode_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* 
 
 extern "C" const char* b2_last_error(void) { return b2host::last_error(); }
 extern "C" int b2_num_sms(void) { return b2host::num_sms(); }
+extern "C" void b2_set_reserved_sms(int n) { b2host::set_reserved_sms(n); }

@@ -42,6 +42,10 @@ int b2_num_sms(void);
  *           fused_weight_gradient_mlp_cuda.wgrad_gemm_accum_fp32 (K18); NVFuser bias-GeLU /
  *           bias-dropout-add epilogues (K16, K17).
  */
+/* Persistent kernels size their grids to (SM count - n): leave SMs free for library kernels (NCCL p2p of pipeline
+ * parallelism) that a peer GPU may be waiting for while one of the spin-waiting fused kernels runs here. */
+void b2_set_reserved_sms(int n);
+
 int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
             long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
             const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,

@@ -108,6 +108,14 @@ def set_gemm_pair_mode(mode: int) -> None:
     L.b2_gemm_set_pair_mode(int(mode))
 
 
+def set_reserved_sms(n: int) -> None:
+    """leave `n` SMs free of the persistent kernels (needed when NCCL p2p runs next to the spin-waiting fused kernels)"""
+    L = lib()
+    L.b2_set_reserved_sms.argtypes = [ctypes.c_int]
+    L.b2_set_reserved_sms.restype = None
+    L.b2_set_reserved_sms(int(n))
+
+
 def launches() -> int:
     return _launches
 
