@@ -19,6 +19,8 @@ Design:
 from __future__ import annotations
 
 import contextlib
+import os
+import time
 import ctypes
 from typing import Callable, Dict, Iterator, List, Optional, Tuple, Union
 
@@ -220,8 +222,15 @@ def forward_backward(forward_step_func: Callable, data_iterator, model: Union[to
 
     def reap_sends(block=False):
         keep = []
+        deadline = time.time() + float(os.environ.get("B2_PP_P2P_TIMEOUT_S", "300"))
         for w, t in pending_send:
             if block:
+                # never hang silently: a send that does not complete means the neighbouring stage is stuck
+                while t.is_cuda and not w.is_completed():
+                    if time.time() > deadline:
+                        raise RuntimeError("pipeline p2p send did not complete within B2_PP_P2P_TIMEOUT_S seconds "
+                                           f"(pipeline rank {rank}, {len(pending_send)} sends pending): the neighbouring stage is not receiving")
+                    time.sleep(0.0005)
                 w.wait()
             elif not w.is_completed():
                 keep.append((w, t))
