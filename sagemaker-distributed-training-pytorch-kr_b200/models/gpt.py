@@ -222,6 +222,44 @@ class ParallelTransformerLayer(nn.Module):
                               m.dense_4h_to_h.weight, m.dense_4h_to_h.bias, self)
 
 
+class _RecomputeFn(torch.autograd.Function):
+    """`--recompute-granularity full` (Megatron's checkpointed transformer layer): the forward runs without recording
+    a graph and saves only the layer input; the backward re-runs the layer with the dropout-seed counter (and torch RNG
+    state) of the first run, then back-propagates through the re-run.  `selective` needs no code here: the only
+    activations it drops in the reference are the attention scores, which the flash-attention kernel never stores."""
+
+    @staticmethod
+    def forward(ctx, x, layer):
+        ctx.layer = layer
+        ctx.seed_state = tp_ops.dropout_seed_state()
+        ctx.cpu_rng = torch.get_rng_state()
+        ctx.cuda_rng = torch.cuda.get_rng_state() if x.is_cuda else None
+        ctx.save_for_backward(x)
+        with torch.no_grad():
+            return layer(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        now_seed, now_cpu = tp_ops.dropout_seed_state(), torch.get_rng_state()
+        now_cuda = torch.cuda.get_rng_state() if x.is_cuda else None
+        tp_ops.set_dropout_seed_state(ctx.seed_state)
+        torch.set_rng_state(ctx.cpu_rng)
+        if ctx.cuda_rng is not None:
+            torch.cuda.set_rng_state(ctx.cuda_rng)
+        try:
+            xin = x.detach().requires_grad_(True)
+            with torch.enable_grad():
+                y = ctx.layer(xin)
+            torch.autograd.backward(y, dy)
+        finally:
+            tp_ops.set_dropout_seed_state(now_seed)
+            torch.set_rng_state(now_cpu)
+            if now_cuda is not None:
+                torch.cuda.set_rng_state(now_cuda)
+        return xin.grad, None
+
+
 class _Lin(nn.Module):
     """parameter holder (weight, bias) so state_dict keys read `<name>.weight` / `<name>.bias`."""
     weight: nn.Parameter
@@ -396,7 +434,7 @@ class GPTModel(nn.Module):
             h = self.input_tensor
         for layer in lm.encoder.layers:
             if self.cfg.recompute_granularity == "full" and self.training:
-                h = torch.utils.checkpoint.checkpoint(layer, h, use_reentrant=False)
+                h = _RecomputeFn.apply(h, layer)      # keep only the layer input; the layer is re-run in backward
             else:
                 h = layer(h)
         if not self.post_process:

@@ -355,6 +355,16 @@ def model_parallel_cuda_manual_seed(seed: int):
     _SEED_COUNTER["base"], _SEED_COUNTER["calls"] = seed, 0
 
 
+def dropout_seed_state():
+    """(base, calls) of the counter behind next_dropout_seed - saved by activation recomputation so the re-run of a
+    layer draws the masks of its first run."""
+    return _SEED_COUNTER["base"], _SEED_COUNTER["calls"]
+
+
+def set_dropout_seed_state(state) -> None:
+    _SEED_COUNTER["base"], _SEED_COUNTER["calls"] = int(state[0]), int(state[1])
+
+
 def next_dropout_seed(tensor_parallel_region: bool) -> int:
     """Counter-based seeds for the Philox dropout kernels: deterministic per call site order; inside TP
     regions the seed differs per TP rank (the tracker's contract), outside it is shared."""

@@ -98,3 +98,12 @@ def test_gpt_pretrain_tp2_pp2_interleaved_matches_single_process():
                                                   "--num-layers-per-virtual-pipeline-stage", "2"], nproc=4, timeout=900))
     assert sorted(single) == [1, 2, 3] == sorted(par)
     assert all(abs(float(single[i]) - float(par[i])) < 2e-4 for i in (1, 2, 3)), (single, par)
+
+
+def test_gpt_full_recompute_is_bit_identical_with_dropout():
+    """--recompute-granularity full re-runs each layer in backward with the dropout seeds of its first run."""
+    base = [a for a in GPT]
+    base[base.index("--train-iters") + 1] = "4"
+    plain = _losses(_run("pretrain_gpt.py", base))
+    rec = _losses(_run("pretrain_gpt.py", base + ["--recompute-granularity", "full"]))
+    assert sorted(plain) == [1, 2, 3, 4] and plain == rec
