@@ -95,6 +95,10 @@ def get_rng_state():
 def save_checkpoint(iteration, model: List[torch.nn.Module], optimizer, opt_param_scheduler, args):
     _p0("saving checkpoint at iteration {:7d} to {}".format(iteration, args.save))
     name = get_checkpoint_name(args.save, iteration)
+    if getattr(args, "use_distributed_optimizer", False) and optimizer is not None and not args.no_save_optim:
+        # optimizer state is sharded over DP: every DP rank writes its own slice next to the model file
+        os.makedirs(os.path.dirname(name), exist_ok=True)
+        torch.save(optimizer.state_dict(), os.path.join(os.path.dirname(name), "distrib_optim_dp{:03d}.pt".format(mpu.get_data_parallel_rank())))
     if mpu.get_data_parallel_rank() == 0:
         sd = {"args": args, "checkpoint_version": 3.0, "iteration": iteration}
         if len(model) == 1:
@@ -103,7 +107,7 @@ def save_checkpoint(iteration, model: List[torch.nn.Module], optimizer, opt_para
             for i, m in enumerate(model):
                 sd["model%d" % i] = model_state_dict_nested(m)
         if not args.no_save_optim:
-            if optimizer is not None:
+            if optimizer is not None and not getattr(args, "use_distributed_optimizer", False):
                 sd["optimizer"] = optimizer.state_dict()
             if opt_param_scheduler is not None:
                 sd["opt_param_scheduler"] = opt_param_scheduler.state_dict()
@@ -164,7 +168,10 @@ def load_checkpoint(model: List[torch.nn.Module], optimizer, opt_param_scheduler
         for i, m in enumerate(model):
             load_nested_state_dict(m, sd["model%d" % i], strict)
     if not release and not args.finetune and not args.no_load_optim:
-        if optimizer is not None and "optimizer" in sd:
+        shard_file = os.path.join(os.path.dirname(name), "distrib_optim_dp{:03d}.pt".format(mpu.get_data_parallel_rank()))
+        if optimizer is not None and getattr(args, "use_distributed_optimizer", False) and os.path.isfile(shard_file):
+            optimizer.load_state_dict(torch.load(shard_file, map_location="cpu", weights_only=False))
+        elif optimizer is not None and "optimizer" in sd:
             optimizer.load_state_dict(sd["optimizer"])
         if opt_param_scheduler is not None and "opt_param_scheduler" in sd:
             opt_param_scheduler.load_state_dict(sd["opt_param_scheduler"])

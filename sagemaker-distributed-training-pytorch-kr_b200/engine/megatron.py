@@ -230,7 +230,11 @@ def get_megatron_optimizer(model: List[torch.nn.Module]) -> MixedPrecisionOptimi
     if args.fp16:
         scaler = ConstantGradScaler(args.loss_scale) if args.loss_scale else DynamicGradScaler(
             args.initial_loss_scale, args.min_loss_scale, 2.0, 0.5, args.loss_scale_window, args.hysteresis)
-    return MixedPrecisionOptimizer(model, lr=args.lr, weight_decay=args.weight_decay, betas=(args.adam_beta1, args.adam_beta2), eps=args.adam_eps,
+    cls = MixedPrecisionOptimizer
+    if args.use_distributed_optimizer:
+        from ..optim.distributed import DistributedOptimizer
+        cls = DistributedOptimizer
+    return cls(model, lr=args.lr, weight_decay=args.weight_decay, betas=(args.adam_beta1, args.adam_beta2), eps=args.adam_eps,
                                    clip_grad=args.clip_grad, optimizer=args.optimizer, sgd_momentum=args.sgd_momentum, grad_scaler=scaler,
                                    dp_group=mpu.get_data_parallel_group(), tp_group=mpu.get_tensor_model_parallel_group(),
                                    mp_group=mpu.get_model_parallel_group(),

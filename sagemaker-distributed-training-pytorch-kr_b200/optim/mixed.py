@@ -87,7 +87,7 @@ class MixedPrecisionOptimizer:
                  clip_grad: float = 1.0, optimizer: str = "adam", sgd_momentum: float = 0.9, grad_scaler: Optional[ConstantGradScaler] = None,
                  dp_group=None, tp_group=None, mp_group=None, embedding_group=None, comm_backend: str = "nccl",
                  no_wd_fn: Callable[[str, torch.Tensor], bool] = default_no_weight_decay, log_num_zeros: bool = False,
-                 overlap_grad_reduce: bool = False):
+                 overlap_grad_reduce: bool = False, arena_multiple: int = 1):
         self.chunks = list(model_chunks)
         self.lr, self.wd, self.betas, self.eps, self.clip_grad = lr, weight_decay, betas, eps, clip_grad
         self.kind, self.sgd_momentum = optimizer, sgd_momentum
@@ -126,7 +126,8 @@ class MixedPrecisionOptimizer:
         for p in self.params:
             self.offsets.append(off)
             off += _align(p.numel())
-        self.total = off
+        m = 64 * max(1, int(arena_multiple))        # (distributed optimizer: arena length divisible by the DP size)
+        self.total = (off + m - 1) // m * m
         self.n_wd = sum(_align(p.numel()) for p, w in zip(self.params, self.is_wd) if w)
         # ---- arenas
         self.fabric = None

@@ -107,3 +107,21 @@ def test_gpt_full_recompute_is_bit_identical_with_dropout():
     plain = _losses(_run("pretrain_gpt.py", base))
     rec = _losses(_run("pretrain_gpt.py", base + ["--recompute-granularity", "full"]))
     assert sorted(plain) == [1, 2, 3, 4] and plain == rec
+
+
+def test_gpt_distributed_optimizer_matches_replicated_and_resumes(tmp_path):
+    """--use-distributed-optimizer (optimizer state sharded over DP=2): same losses as the replicated optimizer, one
+    optimizer shard file per DP rank, bit-exact resume."""
+    base = [a for a in GPT]
+    base[base.index("--global-batch-size") + 1] = "8"
+    base += ["--hidden-dropout", "0", "--attention-dropout", "0"]
+    plain = _losses(_run("pretrain_gpt.py", base, nproc=2))
+    ck = str(tmp_path / "ck")
+    dist_run = _losses(_run("pretrain_gpt.py", base + ["--use-distributed-optimizer", "--save", ck, "--save-interval", "3"], nproc=2))
+    assert plain == dist_run and sorted(plain) == [1, 2, 3, 4, 5, 6]
+    d = os.path.join(ck, "iter_0000003", "mp_rank_00")
+    assert sorted(os.listdir(d)) == ["distrib_optim_dp000.pt", "distrib_optim_dp001.pt", "model_optim_rng.pt"]
+    with open(os.path.join(ck, "latest_checkpointed_iteration.txt"), "w") as f:
+        f.write("3")
+    resumed = _losses(_run("pretrain_gpt.py", base + ["--use-distributed-optimizer", "--load", ck], nproc=2))
+    assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == plain[i] for i in (4, 5, 6))
