@@ -49,7 +49,25 @@ def export_torch_env(info: Optional[RankInfo] = None) -> RankInfo:
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29500")
     os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "1")
+    install_hang_dump()
     return info
+
+
+def install_hang_dump() -> None:
+    """B2_HANG_DUMP_S=<seconds>: every rank prints the Python stack of all its threads to stderr every <seconds> (and on
+    SIGUSR1), so a stalled multi-rank run shows WHERE each rank is waiting before an outer `timeout` kills it."""
+    s = os.environ.get("B2_HANG_DUMP_S")
+    if not s:
+        return
+    import faulthandler
+    import signal
+    import sys
+    try:
+        faulthandler.enable(file=sys.stderr)
+        faulthandler.dump_traceback_later(float(s), repeat=True, file=sys.stderr)
+        faulthandler.register(signal.SIGUSR1, file=sys.stderr, all_threads=True)
+    except (ValueError, OSError, AttributeError):
+        pass
 
 
 def sagemaker_dirs(env=None) -> dict:
