@@ -413,7 +413,12 @@ def validate_args(args, defaults: Optional[dict] = None, verbose: bool = True):
     # ---- non-goals: accepted on the command line, rejected when enabled
     _require(not (args.fp8_e4m3 or args.fp8_hybrid) and args.transformer_impl == "local", "TransformerEngine / fp8 paths are not part of this framework")
     _require(not args.retro_add_retriever, "retro is not part of this framework")
-    _require(args.num_experts is None, "--num-experts (Switch MLP) is not supported")
+    if args.num_experts is not None:
+        _require(args.num_experts > 1, "--num-experts must be greater than 1")
+    if args.group_query_attention:
+        _require(args.num_attention_heads % args.num_query_groups == 0, "num-attention-heads must be a multiple of num-query-groups")
+        _require(args.num_query_groups % args.tensor_model_parallel_size == 0, "num-query-groups must be divisible by the tensor parallel size")
+    _require(sum(bool(x) for x in (args.swiglu, args.squared_relu, args.openai_gelu)) <= 1, "choose one of --swiglu, --squared-relu, --openai-gelu")
     if args.use_rotary_position_embeddings:
         args.position_embedding_type = "rope"
     if not args.add_position_embedding and args.position_embedding_type != "rope":
@@ -455,6 +460,15 @@ class TransformerConfig:
     params_dtype: torch.dtype = torch.float32
     add_bias_linear: bool = True
     swiglu: bool = False
+    squared_relu: bool = False
+    openai_gelu: bool = False
+    bias_gelu_fusion: bool = True
+    num_query_groups: Optional[int] = None          # None / == num_attention_heads: multi-head attention
+    apply_layernorm_1p: bool = False
+    apply_residual_connection_post_layernorm: bool = False
+    num_experts: Optional[int] = None
+    rotary_percent: float = 1.0
+    rotary_seq_len_interpolation_factor: Optional[int] = None
     position_embedding_type: str = "learned_absolute"
     untie_embeddings_and_output_weights: bool = False
     apply_query_key_layer_scaling: bool = True
@@ -483,6 +497,8 @@ def core_transformer_config_from_args(args) -> TransformerConfig:
         if hasattr(args, f) and getattr(args, f) is not None:
             kw[f] = getattr(args, f)
     cfg = TransformerConfig(**kw)
+    if not getattr(args, "group_query_attention", False):
+        cfg.num_query_groups = None                 # the flag, not the group count, switches GQA on (arguments.py:566-567)
     cfg.pipeline_dtype = args.params_dtype
     cfg.batch_p2p_comm = not args.overlap_p2p_comm
     cfg.deallocate_pipeline_outputs = True

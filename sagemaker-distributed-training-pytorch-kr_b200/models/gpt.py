@@ -393,8 +393,11 @@ class GPTModel(nn.Module):
                 _init_normal((cfg.max_position_embeddings, H), cfg.init_method_std, seed * 100003 + 11, device, dt))
             lm.embedding.position_embeddings.weight.tensor_model_parallel = False
         lm.encoder = nn.Module()
+        from .gpt_flex import FlexTransformerLayer, needs_flex_layer
+        # GPT-2 shaped layers run the hand-scheduled single-node layer; GQA / RoPE / SwiGLU / Switch-MLP ... the modular one
+        layer_cls = FlexTransformerLayer if (needs_flex_layer(cfg) or getattr(cfg, "force_flex_layer", False)) else ParallelTransformerLayer
         lm.encoder.layers = nn.ModuleList(
-            [ParallelTransformerLayer(cfg, layer_offset + i + 1, self.comm, device, seed) for i in range(num_layers_here)])
+            [layer_cls(cfg, layer_offset + i + 1, self.comm, device, seed) for i in range(num_layers_here)])
         if post_process:
             lm.encoder.final_layernorm = _LN(H, device, dt)
             for p in lm.encoder.final_layernorm.parameters():

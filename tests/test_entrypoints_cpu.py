@@ -125,3 +125,18 @@ def test_gpt_distributed_optimizer_matches_replicated_and_resumes(tmp_path):
         f.write("3")
     resumed = _losses(_run("pretrain_gpt.py", base + ["--use-distributed-optimizer", "--load", ck], nproc=2))
     assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == plain[i] for i in (4, 5, 6))
+
+
+def test_gpt_pretrain_llama_style_flags_and_switch_mlp_resume(tmp_path):
+    """--swiglu / RoPE / GQA / --disable-bias-linear / --num-experts go through the modular layer; checkpoints resume bit-exactly"""
+    ck = str(tmp_path / "ck")
+    extra = ["--swiglu", "--use-rotary-position-embeddings", "--group-query-attention", "--num-query-groups", "2",
+             "--disable-bias-linear", "--untie-embeddings-and-output-weights", "--num-experts", "2"]
+    out = _run("pretrain_gpt.py", GPT + extra + ["--save", ck, "--save-interval", "3"])
+    full = _losses(out)
+    assert sorted(full) == [1, 2, 3, 4, 5, 6]
+    assert float(full[6]) < float(full[1])
+    with open(os.path.join(ck, "latest_checkpointed_iteration.txt"), "w") as f:
+        f.write("3")
+    resumed = _losses(_run("pretrain_gpt.py", GPT + extra + ["--load", ck]))
+    assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == full[i] for i in (4, 5, 6))
