@@ -115,6 +115,128 @@ def simulate(P: int, V: int, M: int) -> Dict[str, object]:
 
 
 # ------------------------------------------------------------------------------------------
+# batched p2p plan: ONE fused send+recv group per schedule step on one communicator per pipeline group
+# ------------------------------------------------------------------------------------------
+def outgoing_messages(P: int, V: int, M: int, src: int, forward_only: bool = False, sched=None):
+    """Per schedule step of rank `src`: None, or (dst rank, key at dst) for the tensor that step produces for a neighbour.
+    key = (op, chunk, microbatch) of the step that CONSUMES it on the destination."""
+    last = P * V - 1
+    out = []
+    for op, c, m in (sched if sched is not None else build_schedule_py(P, src, V, M, forward_only)):
+        vs = virtual_stage(src, c, P)
+        if op == FWD and vs < last:
+            out.append(((src + 1) % P, (FWD, (vs + 1) // P, m)))
+        elif op == BWD and vs > 0:
+            out.append(((src - 1) % P, (BWD, (vs - 1) // P, m)))
+        else:
+            out.append(None)
+    return out
+
+
+def group_boundaries(sched, V: int):
+    """Steps after which a communication group is issued.  Plain 1F1B: after every step.  Interleaved: after every step
+    of the warm-up and cool-down phases, and after each (forward, backward) PAIR of the steady state - the sends of both
+    steps and the receives for the next pair travel in one group, like the reference's
+    send_forward_backward_recv_forward_backward (schedules.py, interleaved 1F1B).  A group after the forward of a pair
+    would couple that forward's send to the backward's receive and can deadlock on an in-order transport."""
+    n = len(sched)
+    lead = next((i for i, st in enumerate(sched) if st[0] == BWD), n)      # leading forwards
+    total_f = sum(1 for st in sched if st[0] == FWD)
+    if V == 1 or lead == total_f:           # plain 1F1B, forward-only, or "all warm-up" (num_microbatches == pipeline size)
+        return set(range(n))
+    # F^warm (F B)^(total - warm) B^warm: the forward of each steady-state pair is not a boundary
+    return {i for i in range(n) if not (i >= lead - 1 and sched[i][0] == FWD and i + 1 < n and sched[i + 1][0] == BWD)}
+
+
+def plan_batched(P: int, V: int, M: int, rank: int, forward_only: bool = False, sched=None):
+    """Communication plan of `rank` for the batched mode: a list of (after_step, [send dst, ...], [(src, key), ...]) groups;
+    after_step = -1 runs before the first step.  A group carries the tensors produced since the previous group (in
+    order) and the receives that must have completed before the steps up to the next group.
+
+    On one communicator, sends and receives between a pair of ranks match in ORDER (NCCL has no tags).  With P = 2 and
+    interleaving, activations and gradients for the same neighbour share that order, and the receiver may need them in
+    a different order than the sender produces them; so receives are always posted in the SENDER's order, up to the one
+    needed, and tensors that arrive early wait in a dictionary.  This adds no dependency: waiting for a tensor implies
+    the sender has already issued everything it sends before it."""
+    sched = sched if sched is not None else build_schedule_py(P, rank, V, M, forward_only)
+    last = P * V - 1
+    inq, ptr = {}, {}
+    for s in {(rank - 1) % P, (rank + 1) % P}:
+        inq[s] = [o[1] for o in outgoing_messages(P, V, M, s, forward_only) if o is not None and o[0] == rank]
+        ptr[s] = 0
+    outs = outgoing_messages(P, V, M, rank, forward_only, sched)
+    bnd = sorted(group_boundaries(sched, V))
+
+    def recvs_for(steps):
+        r = []
+        for step in steps:
+            op, c, m = sched[step]
+            vs = virtual_stage(rank, c, P)
+            if op == FWD and vs > 0:
+                s = (rank - 1) % P
+            elif op == BWD and vs < last:
+                s = (rank + 1) % P
+            else:
+                continue
+            q = inq[s]
+            if (op, c, m) not in q[ptr[s]:]:
+                continue                   # came in early with a previous group
+            idx = q.index((op, c, m), ptr[s])
+            r += [(s, q[n]) for n in range(ptr[s], idx + 1)]
+            ptr[s] = idx + 1
+        return r
+
+    first = bnd[0] if bnd else len(sched) - 1
+    groups = [(-1, [], recvs_for(range(0, first + 1)))]
+    prev = -1
+    for j, b in enumerate(bnd):
+        nxt = bnd[j + 1] if j + 1 < len(bnd) else len(sched) - 1
+        sends = [(i, outs[i][0]) for i in range(prev + 1, b + 1) if outs[i] is not None]
+        groups.append((b, sends, recvs_for(range(b + 1, nxt + 1))))
+        prev = b
+    return groups
+
+
+def simulate_batched(P: int, V: int, M: int, forward_only: bool = False) -> bool:
+    """Deadlock check of the batched plan under the STRICTEST transport model: a group is one blocking kernel in a
+    single in-order queue per rank (CUDA_DEVICE_MAX_CONNECTIONS=1), and a send completes only once the matching receive
+    has started (rendezvous, no eager buffering).  True = every rank runs to completion."""
+    plans = [plan_batched(P, V, M, r, forward_only) for r in range(P)]
+    nsend = [dict() for _ in range(P)]
+    nrecv = [dict() for _ in range(P)]
+    ks = []
+    for r in range(P):                     # number the messages of each directed pair
+        kr = []
+        for _, snd, recvs in plans[r]:
+            sends = []
+            for _, dst in snd:
+                n = nsend[r].get(dst, 0); nsend[r][dst] = n + 1
+                sends.append((r, dst, n))
+            rr = []
+            for s, _ in recvs:
+                n = nrecv[r].get(s, 0); nrecv[r][s] = n + 1
+                rr.append((s, r, n))
+            kr.append((sends, rr))
+        ks.append(kr)
+    started_send, started_recv = set(), set()
+    cur, active = [0] * P, [False] * P
+    progressed = True
+    while progressed:
+        progressed = False
+        for r in range(P):
+            if cur[r] >= len(ks[r]):
+                continue
+            sends, recvs = ks[r][cur[r]]
+            if not active[r]:
+                active[r] = True
+                started_send.update(sends); started_recv.update(recvs)
+                progressed = True
+            if all(x in started_recv for x in sends) and all(x in started_send for x in recvs):
+                cur[r] += 1; active[r] = False; progressed = True
+    return all(cur[r] == len(ks[r]) for r in range(P))
+
+
+# ------------------------------------------------------------------------------------------
 # directed p2p links
 # ------------------------------------------------------------------------------------------
 class P2PLinks:
@@ -144,6 +266,18 @@ class P2PLinks:
 
 
 _LINKS: Optional[P2PLinks] = None
+
+
+def p2p_mode() -> str:
+    """`batched` (default): per schedule step ONE fused group of sends and receives (torch batch_isend_irecv = one NCCL group
+    kernel) on the pipeline group's communicator, proven deadlock-free by `simulate_batched` even when every kernel of a
+    rank shares one in-order hardware queue.  `links`: the unbatched dataflow mode over directed 2-rank groups with
+    receives posted one step ahead; it needs a transport where a pending receive never blocks other work (gloo, or NCCL
+    with enough hardware queues - with CUDA_DEVICE_MAX_CONNECTIONS=1 a receive queued ahead of the compute that feeds the
+    peer stalls both ranks)."""
+    m = os.environ.get("B2_PP_P2P", "batched")
+    assert m in ("batched", "links"), f"B2_PP_P2P={m}: expected batched or links"
+    return m
 
 
 def get_links() -> P2PLinks:
@@ -181,7 +315,8 @@ def forward_backward(forward_step_func: Callable, data_iterator, model: Union[to
     rank = mpu.get_pipeline_model_parallel_rank()
     M = num_microbatches
     sched = build_schedule(P, rank, V, M, forward_only)
-    links = get_links() if P > 1 else None
+    batched = P > 1 and p2p_mode() == "batched"
+    links = get_links() if (P > 1 and not batched) else None
     last_vs = P * V - 1
     dev = next(models[0].parameters()).device
     iters = data_iterator if isinstance(data_iterator, (list, tuple)) else [data_iterator] * V
@@ -236,10 +371,56 @@ def forward_backward(forward_step_func: Callable, data_iterator, model: Union[to
                 keep.append((w, t))
         pending_send[:] = [] if block else keep
 
+    # ---- batched mode: one fused send+recv group per boundary on the pipeline group's communicator
+    arrived: Dict[Tuple[int, int, int], torch.Tensor] = {}
+    produced: Dict[int, torch.Tensor] = {}
+    groups_after: Dict[int, Tuple[list, list]] = {}
+    send_works: List[Tuple[object, torch.Tensor]] = []
+    if batched:
+        pg = mpu.get_pipeline_model_parallel_group()
+        pg_ranks = dist.get_process_group_ranks(pg)
+        for after, snd, rcv in plan_batched(P, V, M, rank, forward_only, sched):
+            groups_after[after] = (snd, rcv)
+
+    def run_group(after):
+        snd, rcv = groups_after.get(after, ((), ()))
+        if not snd and not rcv:
+            return
+        for w, _ in send_works:            # the previous group's sends (complete by construction: see simulate_batched)
+            w.wait()
+        send_works.clear()
+        ops, bufs, sent = [], [], []
+        for step, dst in snd:
+            t = produced.pop(step)
+            ops.append(dist.P2POp(dist.isend, t, pg_ranks[dst], group=pg))
+            sent.append(t)
+        for src, key in rcv:
+            buf = torch.empty(tensor_shape, dtype=dtype, device=dev)
+            ops.append(dist.P2POp(dist.irecv, buf, pg_ranks[src], group=pg))
+            bufs.append((key, buf))
+        works = dist.batch_isend_irecv(ops)
+        if len(works) == len(ops):         # one request per op (gloo): block on the receives, reap the sends later
+            for w, t in zip(works[:len(sent)], sent):
+                send_works.append((w, t))
+            for w in works[len(sent):]:
+                w.wait()
+        else:                              # NCCL: one coalesced request = one fused kernel; wait() orders the compute stream after it
+            for w in works:
+                w.wait()
+        for key, buf in bufs:
+            arrived[key] = buf
+
+    if batched:
+        take_recv = lambda op, c, m: arrived.pop((op, c, m))                      # noqa: E731
+        send = lambda op, tensor: produced.__setitem__(_step[0], tensor.contiguous())   # noqa: E731
+        post_recv = lambda *a: None                                               # noqa: E731
+        run_group(-1)
+    _step = [0]
     if P > 1 and sched:
         post_recv(*sched[0])
     for i, (op, c, m) in enumerate(sched):
-        # prefetch the receive of the NEXT step so the transfer overlaps this step's compute
+        _step[0] = i
+        # (links mode) prefetch the receive of the NEXT step so the transfer overlaps this step's compute
         if P > 1 and i + 1 < len(sched):
             post_recv(*sched[i + 1])
         vs = virtual_stage(rank, c, P)
@@ -292,8 +473,13 @@ def forward_backward(forward_step_func: Callable, data_iterator, model: Union[to
                 timers("backward-compute").stop()
             if vs > 0:
                 send(BWD, x.grad)
+        if batched:
+            run_group(i)
         reap_sends()
     reap_sends(block=True)
+    for w, _ in send_works:
+        w.wait()
+    assert not arrived and not produced, "pipeline plan left tensors undelivered"
     if V > 1:
         mpu.set_virtual_pipeline_model_parallel_rank(0)
     return losses

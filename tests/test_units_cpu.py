@@ -203,3 +203,43 @@ def test_pretraining_sampler_shards_and_resumes():
     rnd1 = [list(b) for b in MegatronPretrainingRandomSampler(64, 0, 2, 1, 2)]
     assert sorted(i for b in rnd0 for i in b) == list(range(32)) and sorted(i for b in rnd1 for i in b) == list(range(32, 64))
     assert [list(b) for b in MegatronPretrainingRandomSampler(64, 16, 2, 0, 2)] == rnd0[4:]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# batched pipeline p2p plan
+# ---------------------------------------------------------------------------------------------------------------
+def test_batched_p2p_plan_is_deadlock_free_on_an_in_order_rendezvous_transport():
+    """every (P, V, M): one blocking kernel per group, one queue per rank, sends complete only against a started receive"""
+    from b200dist.parallel import pipeline as pp
+    n = 0
+    for P in (2, 3, 4, 8):
+        for V in (1, 2, 3, 4):
+            for M in range(1, 25):
+                if V > 1 and M % P:
+                    continue
+                for fo in (False, True):
+                    assert pp.simulate_batched(P, V, M, fo), (P, V, M, fo)
+                    n += 1
+    assert n > 300
+
+
+def test_batched_p2p_plan_delivers_every_tensor_once_and_in_sender_order():
+    from b200dist.parallel import pipeline as pp
+    for P, V, M in ((2, 1, 4), (2, 2, 4), (4, 2, 8), (3, 3, 6), (2, 3, 2)):
+        plans = [pp.plan_batched(P, V, M, r) for r in range(P)]
+        for r in range(P):
+            sched = pp.build_schedule_py(P, r, V, M)
+            need = [(op, c, m) for (op, c, m) in sched
+                    if (op == pp.FWD and pp.virtual_stage(r, c, P) > 0) or (op == pp.BWD and pp.virtual_stage(r, c, P) < P * V - 1)]
+            got = [key for _, _, rcv in plans[r] for _, key in rcv]
+            assert sorted(got) == sorted(need)
+            # a tensor is received in a group that runs before the step that consumes it
+            pos = {st: i for i, st in enumerate(sched)}
+            for after, _, rcv in plans[r]:
+                for _, key in rcv:
+                    assert pos[key] > after
+            # per source, receive order == that source's send order
+            for src in {(r - 1) % P, (r + 1) % P}:
+                sent = [o[1] for o in pp.outgoing_messages(P, V, M, src) if o is not None and o[0] == r]
+                recv = [key for _, _, rcv in plans[r] for s, key in rcv if s == src]
+                assert recv == sent
