@@ -51,7 +51,8 @@ class _HeadUnit(nn.Module):
 
 class Zero3CausalLM(nn.Module):
     def __init__(self, model: nn.Module, *, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0,
-                 gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None):
+                 gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None,
+                 offload_optimizer="none"):
         super().__init__()
         self.model = model
         self.tied = getattr(model, "lm_head", None) is None
@@ -61,7 +62,7 @@ class Zero3CausalLM(nn.Module):
         names = ["embed"] + [f"layers.{i}" for i in range(len(model.layers))] + ["head"]
         self.engine = Zero3Engine(units, names, group, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, max_grad_norm=max_grad_norm,
                                   gradient_accumulation_steps=gradient_accumulation_steps, persistence_threshold=persistence_threshold,
-                                  comm_backend=comm_backend, offload_param=offload_param)
+                                  comm_backend=comm_backend, offload_param=offload_param, offload_optimizer=offload_optimizer)
         self._units = units
 
     def forward(self, input_ids, attention_mask=None, labels=None):
@@ -125,13 +126,15 @@ class Trainer:
         if self.ds.zero.stage != 3:
             raise ValueError("this trainer implements ZeRO stage 3 (the reference config); got stage %d" % self.ds.zero.stage)
         if self.ds.zero.offload_optimizer_device == "cpu" and self.rank == 0:
-            print("[zero3] offload_optimizer.device=cpu requested: optimizer state is kept on the GPU here (180 GB HBM3e per B200)")
+            print("[zero3] offload_optimizer.device=cpu: fp32 master weights and Adam moments in pinned host memory, step on the CPU "
+                  "(csrc/host/cpu_adam.cpp); a B200 holds them in HBM comfortably - configs/zero3_b200_resident.json keeps them there")
         op = self.ds.optimizer_params           # the JSON optimizer block wins over --optim
         self.zmodel = Zero3CausalLM(self.raw_model, lr=op.get("lr", a.learning_rate), betas=tuple(op.get("betas", (a.adam_beta1, a.adam_beta2))),
                                     eps=op.get("eps", a.adam_epsilon), weight_decay=op.get("weight_decay", a.weight_decay),
                                     max_grad_norm=self.ds.gradient_clipping, gradient_accumulation_steps=self.ds.gradient_accumulation_steps,
                                     persistence_threshold=self.ds.zero.stage3_param_persistence_threshold, comm_backend=a.comm_backend,
-                                    offload_param=self.ds.zero.offload_param_device)
+                                    offload_param=self.ds.zero.offload_param_device,
+                                    offload_optimizer=self.ds.zero.offload_optimizer_device)
         eng = self.zmodel.engine
         sp = self.ds.scheduler_params
         if self.ds.scheduler_type == "WarmupDecayLR":

@@ -78,7 +78,8 @@ class Zero3Engine:
     def __init__(self, units: Sequence[nn.Module], unit_names: Optional[Sequence[str]] = None, group=None, *, lr: float = 1e-5,
                  betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, max_grad_norm: float = 1.0,
                  gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
-                 offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None):
+                 offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None,
+                 offload_optimizer: str = "none"):
         self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         self.world = dist.get_world_size(self.group) if self.group is not None else 1
         self.rank = dist.get_rank(self.group) if self.group is not None else 0
@@ -86,6 +87,10 @@ class Zero3Engine:
         self.ga, self.micro = max(1, gradient_accumulation_steps), 0
         self.step_count = 0
         self.offload_param = offload_param
+        # offload_optimizer = cpu (configs/default_offload_opt_param-original.json:24-27): fp32 master shard and both Adam
+        # moments live in pinned host memory and the step runs in csrc/host/cpu_adam.cpp (ZeRO-Offload); per step one D2H
+        # of the reduced gradient slice and one H2D of the updated low-precision slice per unit
+        self.offload_optimizer = offload_optimizer == "cpu"
         first = next(p for u in units for p in u.parameters())
         self.dev, self.dtype = first.device, first.dtype
         self.grad_dtype = grad_dtype or self.dtype
@@ -132,6 +137,7 @@ class Zero3Engine:
                 self._ws_grad.append(torch.zeros(max_numel, dtype=self.grad_dtype, device=self.dev))
         # ---- partition: per-unit slices
         self.lp_slices, self.fp32, self.exp_avg, self.exp_avg_sq, self.gacc = [], [], [], [], []
+        self._gacc_host, self._lp_host = [], []
         for u in self.units:
             flat = torch.zeros(u.numel, dtype=self.dtype, device=self.dev)
             for p, o in zip(u.params, u.offsets):
@@ -140,9 +146,17 @@ class Zero3Engine:
             if offload_param == "cpu":
                 sl = sl.cpu().pin_memory() if (pin_memory and torch.cuda.is_available()) else sl.cpu()
             self.lp_slices.append(sl)
-            self.fp32.append(flat[self.rank * u.slice:(self.rank + 1) * u.slice].float())
-            self.exp_avg.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
-            self.exp_avg_sq.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+            if self.offload_optimizer:
+                pin = (lambda t: t.pin_memory()) if (pin_memory and torch.cuda.is_available()) else (lambda t: t)
+                self.fp32.append(pin(flat[self.rank * u.slice:(self.rank + 1) * u.slice].float().cpu()))
+                self.exp_avg.append(pin(torch.zeros(u.slice, dtype=torch.float32)))
+                self.exp_avg_sq.append(pin(torch.zeros(u.slice, dtype=torch.float32)))
+                self._gacc_host.append(pin(torch.zeros(u.slice, dtype=torch.float32)))
+                self._lp_host.append(sl if sl.device.type == "cpu" else pin(torch.zeros(u.slice, dtype=self.dtype)))
+            else:
+                self.fp32.append(flat[self.rank * u.slice:(self.rank + 1) * u.slice].float())
+                self.exp_avg.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+                self.exp_avg_sq.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
             self.gacc.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
             ws_p, ws_g = self._param_ws(u.index), self._grad_ws(u.index)
             for p, o in zip(u.params, u.offsets):      # parameters become views of the rotating workspace
@@ -245,7 +259,7 @@ class Zero3Engine:
                 p.grad_buffer.data.zero_()
             p._gb_written = False
         boundary = (self.micro + 1) % self.ga == 0
-        fuse_adam = boundary and not (self.max_grad_norm and self.max_grad_norm > 0)
+        fuse_adam = boundary and not (self.max_grad_norm and self.max_grad_norm > 0) and not self.offload_optimizer
         gscale = 1.0 / (self.world * self.ga)
         gws = self._grad_ws(idx)
         acc = self.micro % self.ga != 0
@@ -271,10 +285,23 @@ class Zero3Engine:
             self.sumsq.add_(self.gacc[idx].pow(2).sum() if boundary else 0.0)
             if fuse_adam:
                 self._adam_slice(idx, 1.0)
+        if boundary and self.offload_optimizer:
+            self._gacc_host[idx].copy_(self.gacc[idx], non_blocking=True)      # D2H of the reduced slice, overlaps the rest of backward
 
     def _adam_slice(self, idx, grad_scale):
         lp = self.lp_slices[idx]
         lr, wd = self.param_groups[0]["lr"], self.param_groups[0]["weight_decay"]
+        if self.offload_optimizer:
+            from ..optim.cpu_adam import cpu_adam_
+            lph = self._lp_host[idx]
+            lowp = lph.dtype in (torch.bfloat16, torch.float16)
+            cpu_adam_(self.fp32[idx], self.exp_avg[idx], self.exp_avg_sq[idx], self._gacc_host[idx], lph if lowp else None, lr=lr,
+                      beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, wd=wd, step=self.step_count + 1, adamw=True, grad_scale=grad_scale)
+            if not lowp:
+                lp.copy_(self.fp32[idx], non_blocking=True)       # fp32 model (parity runs): the master shard is the parameter shard
+            elif lph is not lp:
+                lp.copy_(lph, non_blocking=True)
+            return
         N.adam_(self.fp32[idx], self.exp_avg[idx], self.exp_avg_sq[idx], self.gacc[idx], lp if lp.device == self.fp32[idx].device else None,
                 lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, wd=wd, step=self.step_count + 1, adamw=True, grad_scale=grad_scale)
         if lp.device != self.fp32[idx].device:
@@ -314,6 +341,9 @@ class Zero3Engine:
             norm = float(tot.sqrt())
             self.last_grad_norm = norm
             coef = min(1.0, self.max_grad_norm / (norm + 1e-6))
+        if self.offload_optimizer and self.dev.type == "cuda":
+            torch.cuda.current_stream().synchronize()        # the gradient slices' D2H copies have landed
+        if clip or self.offload_optimizer:
             for i in range(len(self.units)):
                 self._adam_slice(i, coef)
         for p, m, v, p32 in zip(self.persistent, self.persist_m, self.persist_v, self.persist_fp32):

@@ -138,3 +138,15 @@ def test_train_entrypoint_gathered_save(tmp_path):
     assert losses[-1] < losses[0]
     model = hf_ckpt.load_pretrained(str(out))
     assert torch.isfinite(model(torch.randint(0, 256, (1, 8)))).all()
+
+
+def test_train_entrypoint_original_config_offloads_the_optimizer_to_the_cpu(tmp_path):
+    """configs/default_offload_opt_param-original.json (offload_optimizer.device = cpu): ZeRO-Offload with the C++ CPU Adam;
+    same loss curve as the config that keeps the optimizer on the device"""
+    out, losses = _run_train(tmp_path, 2, ["--deepspeed", os.path.join(ROOT, "configs", "default_offload_opt_param-original.json")])
+    assert len(losses) == 5 and losses[-1] < losses[0]
+    (tmp_path / "b").mkdir()
+    _, ref = _run_train(tmp_path / "b", 2, ["--deepspeed", os.path.join(ROOT, "configs", "default_offload_opt_param.json")])
+    assert all(abs(a - b) < 5e-3 for a, b in zip(losses, ref)), (losses, ref)
+    sd = ds_ckpt.zero_to_fp32(str(out))
+    assert all(torch.isfinite(v).all() for v in sd.values())

@@ -243,3 +243,50 @@ def test_batched_p2p_plan_delivers_every_tensor_once_and_in_sender_order():
                 sent = [o[1] for o in pp.outgoing_messages(P, V, M, src) if o is not None and o[0] == r]
                 recv = [key for _, _, rcv in plans[r] for s, key in rcv if s == src]
                 assert recv == sent
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# sentence / block sample mappings (helpers.cpp build_mapping, build_blocks_mapping)
+# ---------------------------------------------------------------------------------------------------------------
+def _sentence_corpus(seed=0, n_docs=40):
+    rs = np.random.RandomState(seed)
+    counts = rs.randint(1, 9, size=n_docs)
+    docs = np.concatenate([[0], np.cumsum(counts)]).astype(np.int64)
+    sizes = rs.randint(3, 60, size=int(docs[-1])).astype(np.int32)
+    sizes[int(docs[5])] = 600                     # a document with an over-long sentence is skipped
+    return docs, sizes
+
+
+def test_build_mapping_matches_python_twin_and_is_a_seeded_permutation():
+    from b200dist.data import dataset_utils as du
+    docs, sizes = _sentence_corpus()
+    for prob in (0.0, 0.1, 0.5):
+        raw = du.build_mapping(docs, sizes, 3, 10 ** 6, 128, prob, 1234, shuffle=False)
+        twin = du.build_mapping_py(docs, sizes, 3, 10 ** 6, 128, prob, 1234)
+        assert raw.shape == twin.shape and (raw == twin).all()
+        sh = du.build_mapping(docs, sizes, 3, 10 ** 6, 128, prob, 1234)
+        assert sorted(map(tuple, sh)) == sorted(map(tuple, raw)) and not (sh == raw).all()
+        assert (sh == du.build_mapping(docs, sizes, 3, 10 ** 6, 128, prob, 1234)).all()       # deterministic per seed
+    for a, b, t in raw:
+        d = np.searchsorted(docs, a, side="right") - 1
+        assert docs[d] <= a < b <= docs[d + 1] and d != 5 and 2 <= t <= 128
+    # the epoch loop stops once max_num_samples is reached
+    one = du.build_mapping(docs, sizes, 1, 10 ** 6, 128, 0.0, 1, shuffle=False)
+    capped = du.build_mapping(docs, sizes, 5, len(one), 128, 0.0, 1, shuffle=False)
+    assert len(capped) == len(one)
+
+
+def test_build_blocks_mapping_matches_python_twin():
+    from b200dist.data import dataset_utils as du
+    docs, sizes = _sentence_corpus(1)
+    titles = np.random.RandomState(2).randint(2, 12, size=len(docs) - 1).astype(np.int32)
+    for one_sent in (False, True):
+        raw = du.build_blocks_mapping(docs, sizes, titles, 2, 10 ** 6, 96, 7, one_sent, shuffle=False)
+        twin = du.build_blocks_mapping_py(docs, sizes, titles, 2, 10 ** 6, 96, 7, one_sent)
+        assert raw.shape == twin.shape and (raw == twin).all()
+        sh = du.build_blocks_mapping(docs, sizes, titles, 2, 10 ** 6, 96, 7, one_sent)
+        assert sorted(map(tuple, sh)) == sorted(map(tuple, raw))
+    half = len(raw) // 2
+    assert (raw[:half, 3] == np.arange(half)).all() and raw[half, 3] == 0                   # block ids restart every epoch
+    for a, b, d, _ in raw:
+        assert docs[d] <= a < b <= docs[d + 1]

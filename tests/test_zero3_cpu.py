@@ -11,10 +11,11 @@ def _build(seed=0):
     return LlamaForCausalLM(LlamaConfig.tiny())
 
 
-def _run_engine(rank, world, steps, ga, clip):
+def _run_engine(rank, world, steps, ga, clip, offload_optimizer="none"):
     from b200dist.engine.hf_trainer import Zero3CausalLM
     model = _build()
-    zm = Zero3CausalLM(model, lr=1e-2, weight_decay=0.0, max_grad_norm=clip, gradient_accumulation_steps=ga, persistence_threshold=200, comm_backend="nccl")
+    zm = Zero3CausalLM(model, lr=1e-2, weight_decay=0.0, max_grad_norm=clip, gradient_accumulation_steps=ga, persistence_threshold=200, comm_backend="nccl",
+                       offload_optimizer=offload_optimizer)
     torch.manual_seed(3)
     data = torch.randint(0, 512, (steps * ga, world, 2, 16))
     losses = []
@@ -23,7 +24,7 @@ def _run_engine(rank, world, steps, ga, clip):
         loss = zm(ids, labels=ids)
         zm.engine.backward(loss)
         zm.engine.step()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     sd = zm.engine.gather_full_state_dict()
     key = sorted(sd)[3]
     return losses, sd[key].float().sum().item(), zm.engine.total_params()
@@ -69,3 +70,51 @@ def test_zero3_fused_adam_path_without_clipping():
     for r in range(world):
         want = [ref_losses[i][r] for i in range(steps * ga)]
         assert np.allclose(outs[r][0], want, rtol=2e-4, atol=2e-4)
+
+
+def test_zero3_cpu_offloaded_optimizer_matches_adamw():
+    """offload_optimizer.device = cpu (the reference's `-original` config): host fp32 shards + the C++ CPU Adam"""
+    world, steps, ga, clip = 2, 3, 2, 1.0
+    outs = run_distributed(_run_engine, world, steps, ga, clip, "cpu")
+    ref_losses, _ = _run_reference(world, steps, ga, clip)
+    for r in range(world):
+        want = [ref_losses[i][r] for i in range(steps * ga)]
+        assert np.allclose(outs[r][0], want, rtol=2e-4, atol=2e-4), (r, outs[r][0], want)
+
+
+def test_cpu_adam_kernel_matches_torch_both_code_paths():
+    from b200dist.optim.cpu_adam import CPUAdam, cpu_adam_, cpu_sumsq, simd_width
+    assert simd_width() in (8, 16)
+    torch.manual_seed(0)
+    n = 3 * 16384 + 37                      # several tiles + a ragged tail
+    for adamw, wd in ((True, 0.1), (False, 0.05), (True, 0.0)):
+        for generic in (False, True):
+            p0 = torch.randn(n)
+            ref = p0.clone().requires_grad_()
+            opt = (torch.optim.AdamW if adamw else torch.optim.Adam)([ref], lr=3e-3, betas=(0.9, 0.95), eps=1e-8, weight_decay=wd)
+            p, m, v = p0.clone(), torch.zeros(n), torch.zeros(n)
+            lp = torch.empty(n, dtype=torch.bfloat16)
+            lp16 = torch.empty(n, dtype=torch.float16)
+            for step in range(1, 4):
+                g = torch.randn(n)
+                ref.grad = g.clone() * 0.5
+                opt.step()
+                cpu_adam_(p, m, v, g, lp if step < 3 else lp16, lr=3e-3, beta1=0.9, beta2=0.95, eps=1e-8, wd=wd, step=step, adamw=adamw,
+                          grad_scale=0.5, threads=3, force_generic=generic)
+            assert torch.allclose(p, ref.detach(), rtol=1e-5, atol=1e-6), (adamw, wd, generic, (p - ref.detach()).abs().max())
+            assert torch.equal(lp16, p.to(torch.float16))
+            assert abs(cpu_sumsq(g) - float(g.double().pow(2).sum())) < 1e-6 * n
+    # bf16 copy is round-to-nearest-even of the fp32 result
+    p, m, v, g = torch.randn(n), torch.zeros(n), torch.zeros(n), torch.randn(n)
+    lp = torch.empty(n, dtype=torch.bfloat16)
+    cpu_adam_(p, m, v, g, lp, lr=1e-2, step=1)
+    assert torch.equal(lp, p.to(torch.bfloat16))
+    # optimizer wrapper
+    w = torch.nn.Parameter(torch.randn(1000))
+    w2 = torch.nn.Parameter(w.detach().clone())
+    a, b = CPUAdam([w], lr=1e-2, weight_decay=0.01), torch.optim.AdamW([w2], lr=1e-2, weight_decay=0.01)
+    for _ in range(3):
+        gr = torch.randn(1000)
+        w.grad, w2.grad = gr.clone(), gr.clone()
+        a.step(); b.step()
+    assert torch.allclose(w, w2, rtol=1e-5, atol=1e-6)
