@@ -30,8 +30,8 @@ int b2h_reducer_ready_order(void* h, int32_t* out);
 /* ------------------------------------------------------------------------------------------
  * Pipeline schedule generator (csrc/host/pipeline_schedule.cpp).  replaces: the control flow of
  * megatron.core.pipeline_parallel.schedules (1F1B and interleaved 1F1B).
- * ops: int32 [cap, 3] rows (op 0 = forward / 1 = backward, model chunk, micro-batch).  Returns the row count, -1 on an
- * invalid request (interleaving needs M % P == 0), -2 if cap is too small.
+ * ops: int32 [cap, 3] rows (op 0 = forward / 1 = backward, model chunk, micro-batch).  Returns the row count (rows beyond
+ * `cap` are counted but not written), -1 on an invalid request (interleaving needs M % P == 0).
  */
 int b2h_pp_schedule(int32_t P, int32_t rank, int32_t V, int32_t M, int32_t forward_only, int32_t* ops, int32_t cap);
 
