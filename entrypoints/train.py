@@ -65,7 +65,8 @@ def train(argv=None):
         sft.smart_tokenizer_and_embedding_resize(special, tokenizer, model)
     data_module = sft.make_supervised_data_module(tokenizer, data_args, training_args, vocab_size=model.config.vocab_size)
     trainer = Trainer(model=model, tokenizer=tokenizer, args=training_args, **data_module)
-    metrics = trainer.train()
+    resume = training_args.resume_from_checkpoint
+    metrics = trainer.train(resume_from_checkpoint=(True if str(resume).lower() == "true" else resume) if resume else None)
     trainer.save_state()
     trainer.save_model(output_dir=training_args.output_dir)
     if torch.distributed.is_initialized():

@@ -43,6 +43,7 @@ def save_zero3_checkpoint(engine, out_dir: str, step: int, ds_config: Dict, sche
         "zero_stage": 3, "partition_count": engine.world, "fp32_flat_groups": st["fp32_flat_groups"],
         "optimizer_state_dict": {"state": {i: {"exp_avg": st["exp_avg"][i], "exp_avg_sq": st["exp_avg_sq"][i], "step": st["step"]}
                                            for i in range(len(st["fp32_flat_groups"]))}},
+        "persistent_state": {k: st.get(k) for k in ("persist_fp32", "persist_m", "persist_v")},
         "rank": engine.rank}, "ds_config": ds_config, "ds_version": DS_VERSION}
     torch.save(model_states, os.path.join(d, mfile))
     torch.save(optim_states, os.path.join(d, ofile))
@@ -65,7 +66,7 @@ def load_zero3_checkpoint(engine, ckpt_dir: str, tag: Optional[str] = None, sche
     st = os_["optimizer_state_dict"]["state"]
     engine.load_shard_state({"partition_count": os_["partition_count"], "step": st[0]["step"] if st else 0,
                              "fp32_flat_groups": os_["fp32_flat_groups"], "exp_avg": [st[i]["exp_avg"] for i in range(len(st))],
-                             "exp_avg_sq": [st[i]["exp_avg_sq"] for i in range(len(st))]})
+                             "exp_avg_sq": [st[i]["exp_avg_sq"] for i in range(len(st))], **(os_.get("persistent_state") or {})})
     if scheduler is not None and ms.get("lr_scheduler"):
         scheduler.load_state_dict(ms["lr_scheduler"])
     return ms.get("global_steps", step)

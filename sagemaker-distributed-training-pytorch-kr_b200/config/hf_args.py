@@ -51,6 +51,8 @@ class TrainingArguments:
     per_device_eval_batch_size: int = 8
     gradient_accumulation_steps: int = 1
     evaluation_strategy: str = "no"
+    eval_steps: Optional[int] = None
+    resume_from_checkpoint: Optional[str] = None
     save_strategy: str = "steps"
     save_steps: int = 500
     save_total_limit: Optional[int] = None

@@ -149,6 +149,8 @@ GROUPS: Dict[str, List[Flag]] = {
         _f("--tokenizer-model", type=str), _f("--data-impl", type=str, default="infer", choices=["mmap", "infer"]),
         _f("--reset-position-ids", action=T), _f("--reset-attention-mask", action=T), _f("--eod-mask-loss", action=T),
         _f("--mock-data", action=T, help="(addition) synthetic token stream of the configured shape"),
+        _f("--metrics-jsonl", type=str, help="(addition) append one JSON record per log point: loss, lr, step ms, tokens/s, MFU"),
+        _f("--inject-fault", type=str, help="(addition) RANK:ITERATION - raise on that rank after that iteration (recovery tests)"),
     ],
     "autoresume": [_f("--adlr-autoresume", action=T), _f("--adlr-autoresume-interval", type=int, default=1000)],
     "biencoder": [

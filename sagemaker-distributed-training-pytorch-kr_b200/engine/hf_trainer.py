@@ -93,7 +93,7 @@ class TrainerState:
 class Trainer:
     def __init__(self, model: nn.Module, tokenizer=None, args=None, train_dataset=None, eval_dataset=None, data_collator=None):
         self.raw_model, self.tokenizer, self.args = model, tokenizer, args
-        self.train_dataset, self.data_collator = train_dataset, data_collator
+        self.train_dataset, self.eval_dataset, self.data_collator = train_dataset, eval_dataset, data_collator
         self.world = dist.get_world_size() if dist.is_initialized() else 1
         self.rank = dist.get_rank() if dist.is_initialized() else 0
         args.world_size = self.world
@@ -165,21 +165,41 @@ class Trainer:
         self.zmodel.engine.backward(loss)
         return loss.detach()
 
-    def train(self):
+    def train(self, resume_from_checkpoint=None):
+        """`resume_from_checkpoint`: a `checkpoint-N` directory, or True for the newest one under output_dir (the
+        transformers.Trainer contract; the reference never passes it, train.py:244, but its save_steps/save_total_limit
+        settings - 4_...ipynb:474-476 - exist for exactly this)."""
+        from ..utils.metrics import JsonlSink
         torch.manual_seed(self.args.seed)
         self._setup()
         a, eng = self.args, self.zmodel.engine
         loader, sampler = self._loader()
         total = self.state.max_steps
         steps_per_epoch = max(1, len(loader) // a.gradient_accumulation_steps)
+        sink = JsonlSink(rank=self.rank)
+        skip_batches, epoch = 0, 0
+        if resume_from_checkpoint:
+            ck = self._latest_checkpoint() if resume_from_checkpoint is True else str(resume_from_checkpoint)
+            if ck is None:
+                raise ValueError(f"no checkpoint-* directory under {a.output_dir} to resume from")
+            self._load_checkpoint(ck)
+            consumed = self.state.global_step * a.gradient_accumulation_steps
+            epoch, skip_batches = consumed // max(1, len(loader)), consumed % max(1, len(loader))
+            if self.rank == 0:
+                print(f"[trainer] resumed from {ck}: global step {self.state.global_step}, epoch {epoch}, skipping {skip_batches} batches", flush=True)
         t0 = time.time()
         tr_loss = torch.zeros((), device=eng.dev)
-        logged_loss, samples, epoch = 0.0, 0, 0
-        done = False
+        logged_loss, samples = 0.0, 0
+        done = self.state.global_step >= total
         while not done:
             if sampler is not None:
                 sampler.set_epoch(epoch)
+            else:
+                torch.manual_seed(a.seed + epoch)          # single process: the shuffle order is a function of the epoch (resumable)
             for i, batch in enumerate(loader):
+                if skip_batches > 0:
+                    skip_batches -= 1
+                    continue
                 tr_loss += self.training_step(batch) / a.gradient_accumulation_steps
                 samples += batch["input_ids"].shape[0] * self.world
                 if eng.step():
@@ -195,8 +215,15 @@ class Trainer:
                         self.state.log_history.append({**log, "step": self.state.global_step})
                         if self.rank == 0:
                             print(log, flush=True)
+                            sink.write(workload="sft", step=self.state.global_step, **log)
+                    ev = a.evaluation_strategy
+                    if self.eval_dataset is not None and ((ev == "steps" and self.state.global_step % (a.eval_steps or a.logging_steps) == 0)
+                                                          or (ev == "epoch" and self.state.global_step % steps_per_epoch == 0)):
+                        self.evaluate()
                     if a.save_strategy == "steps" and a.save_steps and self.state.global_step % a.save_steps == 0:
-                        self.save_model(os.path.join(a.output_dir, f"checkpoint-{self.state.global_step}"))
+                        self._save_checkpoint()
+                    elif a.save_strategy == "epoch" and self.state.global_step % steps_per_epoch == 0:
+                        self._save_checkpoint()
                     if self.state.global_step >= total:
                         done = True
                         break
@@ -212,7 +239,80 @@ class Trainer:
             print(metrics, flush=True)
         return metrics
 
+    # ------------------------------------------------------------------ evaluation
+    def evaluate(self, eval_dataset=None) -> dict:
+        """mean per-token loss over the (rank-sharded) evaluation set; logs {'eval_loss': ...} like transformers.Trainer"""
+        ds = eval_dataset if eval_dataset is not None else self.eval_dataset
+        if ds is None:
+            return {}
+        a, eng = self.args, self.zmodel.engine
+        sampler = torch.utils.data.distributed.DistributedSampler(ds, self.world, self.rank, shuffle=False) if self.world > 1 else None
+        loader = torch.utils.data.DataLoader(ds, batch_size=a.per_device_eval_batch_size, sampler=sampler, shuffle=False,
+                                             collate_fn=self.data_collator, drop_last=self.world > 1)
+        tot = torch.zeros(2, dtype=torch.float64, device=eng.dev)
+        was_training = self.zmodel.training
+        self.zmodel.eval()
+        t0 = time.time()
+        with torch.no_grad():
+            for batch in loader:
+                ids, labels = batch["input_ids"].to(eng.dev), batch["labels"].to(eng.dev)
+                n = (labels[:, 1:] != -100).sum()
+                tot[0] += self.zmodel(ids, attention_mask=None, labels=labels).double() * n
+                tot[1] += n
+        if self.world > 1:
+            t32 = tot.float()
+            dist.all_reduce(t32)
+            tot = t32.double()
+        self.zmodel.train(was_training)
+        metrics = {"eval_loss": float(tot[0] / tot[1].clamp(min=1)), "eval_runtime": round(time.time() - t0, 4), "epoch": round(self.state.epoch, 2)}
+        self.state.log_history.append({**metrics, "step": self.state.global_step})
+        if self.rank == 0:
+            print(metrics, flush=True)
+        return metrics
+
     # ------------------------------------------------------------------ persistence
+    def _checkpoints(self):
+        out = self.args.output_dir
+        if not os.path.isdir(out):
+            return []
+        found = []
+        for n in os.listdir(out):
+            if n.startswith("checkpoint-") and n[len("checkpoint-"):].isdigit() and os.path.isfile(os.path.join(out, n, "latest")):
+                found.append((int(n[len("checkpoint-"):]), os.path.join(out, n)))
+        return [p for _, p in sorted(found)]
+
+    def _latest_checkpoint(self):
+        c = self._checkpoints()
+        return c[-1] if c else None
+
+    def _save_checkpoint(self):
+        """resumable intermediate checkpoint: ZeRO-3 shards of every rank (fp32 master + Adam moments + scheduler) in
+        `output_dir/checkpoint-N/`, trainer_state.json next to them; `save_total_limit` keeps the newest N"""
+        import shutil
+        from ..ckpt import deepspeed as ds_ckpt
+        d = os.path.join(self.args.output_dir, f"checkpoint-{self.state.global_step}")
+        os.makedirs(d, exist_ok=True)
+        ds_ckpt.save_zero3_checkpoint(self.zmodel.engine, d, self.state.global_step, self.ds.raw if self.ds else {},
+                                      scheduler=self.scheduler, persistent=self._persistent_named())
+        if self.rank == 0:
+            with open(os.path.join(d, "trainer_state.json"), "w") as f:
+                json.dump(self.state.to_json(), f, indent=2)
+            limit = self.args.save_total_limit
+            if limit is not None and limit > 0:
+                for old in self._checkpoints()[:-limit]:
+                    shutil.rmtree(old, ignore_errors=True)
+        if dist.is_initialized():
+            dist.barrier()
+
+    def _load_checkpoint(self, ck: str):
+        from ..ckpt import deepspeed as ds_ckpt
+        step = ds_ckpt.load_zero3_checkpoint(self.zmodel.engine, ck, scheduler=self.scheduler)
+        self.state.global_step = int(step)
+        ts = os.path.join(ck, "trainer_state.json")
+        if os.path.isfile(ts):
+            with open(ts) as f:
+                self.state.log_history = json.load(f).get("log_history", [])
+
     def save_state(self):
         if self.rank == 0:
             os.makedirs(self.args.output_dir, exist_ok=True)

@@ -27,7 +27,8 @@ from ..parallel import state as mpu
 from ..parallel import tensor as tp_ops
 from ..utils.timers import Timers
 
-_GLOBAL = {"args": None, "timers": None, "tokenizer": None, "signal": None, "start_time": time.time()}
+_GLOBAL = {"args": None, "timers": None, "tokenizer": None, "signal": None, "start_time": time.time(), "sink": None, "tb": None,
+           "optimizer": None}
 
 
 def get_args():
@@ -146,6 +147,12 @@ def initialize_megatron(extra_args_provider=None, args_defaults=None, ignore_unk
     np.random.seed(seed)
     tp_ops.model_parallel_cuda_manual_seed(seed)
     _GLOBAL["tokenizer"] = build_tokenizer(args)
+    from ..utils import metrics as _metrics
+    last = args.world_size - 1                       # the rank that prints the training log also owns the structured sinks
+    _GLOBAL["sink"] = _metrics.JsonlSink(args.metrics_jsonl, rank=0 if args.rank == last else 1)
+    _GLOBAL["tb"] = _metrics.ScalarWriter(args.tensorboard_dir, rank=0 if args.rank == last else 1, queue_size=args.tensorboard_queue_size)
+    if args.profile:
+        _metrics.enable_nvtx(True)                   # timers double as NVTX ranges inside the cudaProfilerStart/Stop window
     if args.exit_signal_handler:
         _GLOBAL["signal"] = _SignalHandler()
     # native code: dataset helpers + kernels are prebuilt in-tree; build them here if a fresh checkout
@@ -239,7 +246,7 @@ def get_megatron_optimizer(model: List[torch.nn.Module]) -> MixedPrecisionOptimi
                                    dp_group=mpu.get_data_parallel_group(), tp_group=mpu.get_tensor_model_parallel_group(),
                                    mp_group=mpu.get_model_parallel_group(),
                                    embedding_group=mpu.get_embedding_group() if mpu.is_rank_in_embedding_group(ignore_virtual=True) and mpu.get_pipeline_model_parallel_world_size() > 1 else None,
-                                   comm_backend=args.comm_backend)
+                                   comm_backend=args.comm_backend, log_num_zeros=bool(args.log_num_zeros_in_grad))
 
 
 def setup_model_and_optimizer(model_provider_func, no_optimizer=False):
@@ -314,7 +321,8 @@ def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_sch
     return loss_reduced, skipped, grad_norm, num_zeros
 
 
-def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scale, report_memory_flag, skipped_iter, grad_norm):
+def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scale, report_memory_flag, skipped_iter, grad_norm,
+                 params_norm=None, num_zeros_in_grad=None):
     """'iteration N/ M | consumed samples: ... | elapsed time per iteration (ms): ... | learning rate: ... |
     global batch size: ... | lm loss: ... | loss scale: ... | grad norm: ... | number of skipped iterations: ... |
     number of nan iterations: ... |'  (format of 3_...ipynb:4347)."""
@@ -331,6 +339,7 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
         elapsed = timers("interval-time").elapsed(barrier=True)
         per_iter = elapsed / (total_loss_dict[adv] + total_loss_dict[skp])
         s = " iteration {:8d}/{:8d} |".format(iteration, args.train_iters)
+        logged = {}
         s += " consumed samples: {:12d} |".format(args.consumed_train_samples)
         s += " elapsed time per iteration (ms): {:.1f} |".format(per_iter * 1000.0)
         s += " learning rate: {:.3E} |".format(learning_rate)
@@ -342,15 +351,42 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
             avg = float(v) / float(max(1, total_loss_dict[adv]))
             if avg > 0.0:
                 s += " {}: {:.6E} |".format(k, avg)
+                logged[k] = avg
             total_loss_dict[k] = 0.0
         s += " loss scale: {:.1f} |".format(loss_scale)
+        rec = {"iteration": iteration, "consumed_samples": args.consumed_train_samples, "ms_per_iteration": per_iter * 1000.0,
+               "learning_rate": learning_rate, "global_batch_size": args.global_batch_size, "loss_scale": loss_scale,
+               "skipped_iterations": total_loss_dict[skp], **{k.replace(" ", "_"): v for k, v in logged.items()}}
         if grad_norm is not None:
             gn = math.sqrt(float(grad_norm)) if torch.is_tensor(grad_norm) else float(grad_norm)
             s += " grad norm: {:.3f} |".format(gn)
+            rec["grad_norm"] = gn
+        if num_zeros_in_grad is not None:
+            s += " num zeros: {:.1f} |".format(float(num_zeros_in_grad))
+            rec["num_zeros_in_grad"] = float(num_zeros_in_grad)
+        if params_norm is not None:
+            s += " params norm: {:.3f} |".format(params_norm)
+            rec["params_norm"] = params_norm
         s += " number of skipped iterations: {:3d} |".format(total_loss_dict[skp])
         s += " number of nan iterations: {:3d} |".format(total_loss_dict[nan])
         tokens_per_s = args.global_batch_size * args.seq_length / max(per_iter, 1e-9)
         s += " tokens/s: {:.0f} |".format(tokens_per_s)
+        sink, tb = _GLOBAL["sink"], _GLOBAL["tb"]
+        if (sink is not None and sink.enabled) or (tb is not None and tb.enabled):
+            from ..utils import metrics as _metrics
+            fpt = _metrics.model_flops_per_token(args.num_layers, args.hidden_size, args.ffn_hidden_size, args.padded_vocab_size, args.seq_length,
+                                                 swiglu=bool(args.swiglu), kv_ratio=(args.num_query_groups / args.num_attention_heads)
+                                                 if args.group_query_attention else 1.0)
+            rec.update(tokens_per_s=tokens_per_s, mfu=_metrics.mfu(tokens_per_s / max(1, args.world_size), fpt), world_size=args.world_size)
+            if sink is not None:
+                sink.write(**rec)
+            if tb is not None and tb.enabled and iteration % args.tensorboard_log_interval == 0:
+                for k, v in rec.items():
+                    if k not in ("iteration", "time") and isinstance(v, (int, float)):
+                        tb.add_scalar(k.replace("_", "-"), v, iteration)
+                        if k.endswith("loss"):
+                            tb.add_scalar(k.replace("_", "-") + " vs samples", v, args.consumed_train_samples)
+                tb.flush()
         total_loss_dict[adv] = total_loss_dict[skp] = total_loss_dict[nan] = 0
         print_rank_last(s)
         if report_memory_flag and learning_rate > 0.0 and torch.cuda.is_available():
@@ -427,13 +463,15 @@ def train(forward_step_func, model, optimizer, opt_param_scheduler, train_data_i
             if iteration == args.profile_step_end and prof_on:
                 torch.cuda.cudart().cudaProfilerStop(); prof_on = False
         args.curr_iteration = iteration
-        loss_dict, skipped, grad_norm, _ = train_step(forward_step_func, train_data_iterator, model, optimizer, opt_param_scheduler)
+        loss_dict, skipped, grad_norm, num_zeros = train_step(forward_step_func, train_data_iterator, model, optimizer, opt_param_scheduler)
         iteration += 1
         args.consumed_train_samples += args.global_batch_size
         loss_scale = optimizer.get_loss_scale()
         lr = optimizer.param_groups[0]["lr"]
         # loss values stay device tensors between log points; they are only read on the host at a log boundary
-        report_memory_flag = training_log(loss_dict, total_loss_dict, lr, iteration, loss_scale, report_memory_flag, skipped, grad_norm)
+        params_norm = optimizer.params_norm() if (args.log_params_norm and iteration % args.log_interval == 0 and hasattr(optimizer, "params_norm")) else None
+        report_memory_flag = training_log(loss_dict, total_loss_dict, lr, iteration, loss_scale, report_memory_flag, skipped, grad_norm,
+                                          params_norm, num_zeros)
         if args.eval_interval and iteration % args.eval_interval == 0 and args.do_valid:
             evaluate_and_print_results("iteration {}".format(iteration), forward_step_func, valid_data_iterator, model, iteration, False)
         saved = False
@@ -457,7 +495,7 @@ def train(forward_step_func, model, optimizer, opt_param_scheduler, train_data_i
                 save_checkpoint_and_time(iteration, model, optimizer, opt_param_scheduler)
             print_rank_0("exiting program at iteration {}".format(iteration))
             sys.exit()
-        inj = os.environ.get("B200DIST_INJECT_FAULT")     # "rank:iteration" test hook
+        inj = args.inject_fault or os.environ.get("B200DIST_INJECT_FAULT")     # "rank:iteration" test hook
         if inj:
             r, it = (int(x) for x in inj.split(":"))
             if (dist.get_rank() if dist.is_initialized() else 0) == r and iteration == it:

@@ -52,6 +52,17 @@ def check_sagemaker(args):
     return args
 
 
+_SINK = []
+
+
+def _sink():
+    """JSONL metrics sink (env B200DIST_METRICS_JSONL), created on first use by the logging rank"""
+    if not _SINK:
+        from ..utils.metrics import JsonlSink
+        _SINK.append(JsonlSink())
+    return _SINK[0]
+
+
 def train(args, model, device, train_loader, optimizer, epoch):
     model.train()
     for batch_idx, (data, target) in enumerate(train_loader):
@@ -65,6 +76,7 @@ def train(args, model, device, train_loader, optimizer, epoch):
             print("Train Epoch: {} [{}/{} ({:.0f}%)]\tLoss: {:.6f}".format(
                 epoch, batch_idx * len(data) * args.world_size, len(train_loader.dataset),
                 100.0 * batch_idx / len(train_loader), loss.item()), flush=True)
+            _sink().write(workload="mnist", epoch=epoch, batch_idx=batch_idx, loss=loss.item())
         if args.verbose:
             print("Batch", batch_idx, "from rank", args.rank)
         if args.max_steps is not None and batch_idx + 1 >= args.max_steps:

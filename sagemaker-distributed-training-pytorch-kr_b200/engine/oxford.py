@@ -102,6 +102,17 @@ class _Criterion(nn.Module):
         return OF.cross_entropy(output, target)
 
 
+_SINK = []
+
+
+def _sink():
+    """JSONL metrics sink (env B200DIST_METRICS_JSONL), created on first use by the logging rank"""
+    if not _SINK:
+        from ..utils.metrics import JsonlSink
+        _SINK.append(JsonlSink())
+    return _SINK[0]
+
+
 def train(args):
     best_acc1 = -1.0
     model_history = util.init_modelhistory({})
@@ -183,6 +194,8 @@ def train(args):
                           args.world_size * args.batch_size / batch_time.avg, bt=batch_time, loss=losses, top1=top1, top5=top5), flush=True)
                 for k, v in (("epoch", epoch), ("batch_idx", batch_idx), ("batch_time", batch_time.val), ("losses", losses.val), ("top1", top1.val), ("top5", top5.val)):
                     model_history[k].append(v)
+                _sink().write(workload="oxford", epoch=epoch, batch_idx=batch_idx, step_ms=batch_time.val * 1000.0,
+                              images_per_s=args.world_size * args.batch_size / batch_time.val, loss=losses.val, top1=top1.val, top5=top5.val)
             if args.max_steps is not None and batch_idx + 1 >= args.max_steps:
                 break
         acc1 = validate(test_loader, model, criterion, epoch, model_history, args, dtype)

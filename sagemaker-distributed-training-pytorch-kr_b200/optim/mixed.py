@@ -98,6 +98,7 @@ class MixedPrecisionOptimizer:
         self.tp_rank = dist.get_rank(tp_group) if self.tp_size > 1 else 0
         self.step_count = 0
         self.comm_backend = comm_backend
+        self.log_num_zeros = log_num_zeros
         # ---- collect parameters, sort into segments: (weight-decay?, de-dup class)
         named = []
         seen = set()
@@ -228,6 +229,14 @@ class MixedPrecisionOptimizer:
                 self.skipped_last = True
                 return False, None, None
         self.skipped_last = False
+        num_zeros = None
+        if self.log_num_zeros:          # --log-num-zeros-in-grad: zeros of the (unscaled) gradient, TP-duplicated parameters counted once
+            nz = torch.zeros(1, dtype=torch.float32, device=self.main_grad.device)
+            for (a, b) in self._norm_spans:
+                nz += (self.main_grad[a:b] == 0).sum()
+            if self.mp_group is not None and dist.get_world_size(self.mp_group) > 1:
+                dist.all_reduce(nz, group=self.mp_group)
+            num_zeros = nz
         ss = None
         if self.clip_grad and self.clip_grad > 0:
             first = True
@@ -258,7 +267,16 @@ class MixedPrecisionOptimizer:
                        grad_scale=coef, first_step=self.step_count == 1)
                 if plp is not None:
                     N.cast_from_fp32_(plp, self.main_param[a:b])
-        return True, self.last_grad_norm, None
+        return True, self.last_grad_norm, num_zeros
+
+    def params_norm(self) -> float:
+        """L2 norm of the fp32 master parameters over the model-parallel group (--log-params-norm)"""
+        tot = torch.zeros(1, dtype=torch.float32, device=self.main_param.device)
+        for (a, b) in self._norm_spans:
+            N.sumsq(self.main_param[a:b], tot, accumulate=True)
+        if self.mp_group is not None and dist.get_world_size(self.mp_group) > 1:
+            dist.all_reduce(tot, group=self.mp_group)
+        return math.sqrt(float(tot))
 
     def grad_norm_value(self) -> float:
         return math.sqrt(float(self.last_grad_norm)) if self.last_grad_norm is not None else 0.0

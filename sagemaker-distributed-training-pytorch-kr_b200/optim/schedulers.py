@@ -136,6 +136,7 @@ class WarmupLR:
 
     def load_state_dict(self, sd):
         self.last_batch_iteration = sd["last_batch_iteration"]
+        self._apply(self.get_lr())
 
 
 class WarmupDecayLR(WarmupLR):

@@ -60,13 +60,77 @@ class _Bucket:
         self.symm = None
 
 
+class GradBucket:
+    """what a communication hook sees of one bucket (torch.distributed.GradBucket)"""
+
+    def __init__(self, b: _Bucket, last: bool):
+        self._b, self._last = b, last
+
+    def index(self) -> int:
+        return self._b.index
+
+    def buffer(self) -> torch.Tensor:
+        return self._b.flat
+
+    def gradients(self) -> List[torch.Tensor]:
+        return list(self._b.views)
+
+    def parameters(self) -> List[nn.Parameter]:
+        return list(self._b.params)
+
+    def is_last(self) -> bool:
+        return self._last
+
+    def set_buffer(self, t: torch.Tensor):
+        self._b.flat.copy_(t.view_as(self._b.flat))
+
+
+class _HookWork:
+    def __init__(self, out, flat):
+        self.out, self.flat = out, flat
+
+    def wait(self):
+        r = self.out
+        if hasattr(r, "wait") and not torch.is_tensor(r):       # torch.futures.Future / torch._C.Future / Work
+            r = r.wait()
+            if isinstance(r, (list, tuple)):
+                r = r[0]
+        if r is not None and r.data_ptr() != self.flat.data_ptr():
+            self.flat.copy_(r.view_as(self.flat))
+
+
+def allreduce_hook(process_group, bucket: GradBucket):
+    """default hook: average over the group (torch ddp_comm_hooks.default_hooks.allreduce_hook)"""
+    g = process_group if process_group is not None else dist.group.WORLD
+    t = bucket.buffer()
+    t.div_(dist.get_world_size(g))
+    return dist.all_reduce(t, group=g, async_op=True).get_future().then(lambda f: f.value()[0])
+
+
+def _compress_hook(dtype):
+    def hook(process_group, bucket: GradBucket):
+        g = process_group if process_group is not None else dist.group.WORLD
+        buf = bucket.buffer()
+        c = buf.to(dtype).div_(dist.get_world_size(g))
+        fut = dist.all_reduce(c, group=g, async_op=True).get_future()
+        return fut.then(lambda f: buf.copy_(f.value()[0]))
+    return hook
+
+
+fp16_compress_hook = _compress_hook(torch.float16)     # torch ddp_comm_hooks.default_hooks.fp16_compress_hook
+bf16_compress_hook = _compress_hook(torch.bfloat16)
+
+
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, process_group=None,
                  bucket_cap_mb: float = 25, first_bucket_cap_mb: float = 1, broadcast_buffers: bool = True,
                  find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True,
-                 comm_backend: str = "auto", skip_constant_buffers: bool = True, rebuild_buckets: bool = True):
+                 comm_backend: str = "auto", skip_constant_buffers: bool = True, rebuild_buckets: bool = True,
+                 static_graph: bool = False):
         super().__init__()
         self.module = module
+        self.static_graph = static_graph        # accepted for API parity: the bucket plan is static after the first rebuild anyway
+        self._comm_hook = None
         self.process_group = process_group if process_group is not None else dist.group.WORLD
         self.world_size = dist.get_world_size(self.process_group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(self.process_group) if dist.is_initialized() else 0
@@ -201,6 +265,11 @@ class DistributedDataParallel(nn.Module):
 
     def _launch(self, b: _Bucket):
         self._launched += 1
+        if self._comm_hook is not None:
+            state, hook = self._comm_hook
+            out = hook(state, GradBucket(b, b.index == len(self.buckets) - 1))
+            b.work = _HookWork(out, b.flat)
+            return
         if self.comm_backend == "native":
             ev = torch.cuda.Event()
             ev.record()
@@ -228,7 +297,9 @@ class DistributedDataParallel(nn.Module):
         for b in self.buckets:
             if b.work is None:
                 continue
-            if isinstance(b.work, torch.cuda.Stream):
+            if isinstance(b.work, _HookWork):
+                b.work.wait()
+            elif isinstance(b.work, torch.cuda.Stream):
                 if not waited_stream:
                     torch.cuda.current_stream().wait_stream(b.work)
                     waited_stream = True
@@ -248,6 +319,16 @@ class DistributedDataParallel(nn.Module):
         L.b2h_reducer_reset(ctypes.c_void_p(self._core))
 
     # ------------------------------------------------------------------ public API
+    def register_comm_hook(self, state, hook):
+        """torch DDP's communication-hook contract (default_comm_hooks.cpp / ddp_comm_hooks):
+        `hook(state, bucket: GradBucket) -> Future[Tensor] | Tensor`; the returned tensor replaces the bucket's gradients
+        (it must already be averaged).  Registering a hook bypasses the fused NVLS kernel for the buckets."""
+        if self._comm_hook is not None:
+            raise RuntimeError("register_comm_hook: a communication hook is already registered")
+        if not callable(hook):
+            raise TypeError("communication hook must be callable")
+        self._comm_hook = (state, hook)
+
     @contextlib.contextmanager
     def no_sync(self):
         old = self.require_backward_grad_sync

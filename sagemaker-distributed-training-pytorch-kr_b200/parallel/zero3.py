@@ -240,7 +240,8 @@ class Zero3Engine:
             x = _FetchFn.apply(x, self, idx)          # its backward runs right after the unit's backward
         else:
             self._ensure(idx, forward=True)           # first unit (token ids in): reduced when loss.backward() returns
-            self._reduce_at_end.append(idx)
+            if torch.is_grad_enabled():
+                self._reduce_at_end.append(idx)
         y = fn(x, *args)
         if torch.is_grad_enabled() and y.requires_grad:
             y = _PreBackwardFn.apply(y, self, idx)
@@ -382,7 +383,10 @@ class Zero3Engine:
                 "exp_avg": [t.detach().cpu() for t in self.exp_avg], "exp_avg_sq": [t.detach().cpu() for t in self.exp_avg_sq],
                 "unit_names": [u.name for u in self.units], "unit_numel": [u.numel for u in self.units],
                 "param_shapes": [{n: tuple(p.shape) for n, p in zip(u.names, u.params)} for u in self.units],
-                "param_offsets": [dict(zip(u.names, u.offsets)) for u in self.units]}
+                "param_offsets": [dict(zip(u.names, u.offsets)) for u in self.units],
+                # replicated (persistent) parameters: master copy and moments, identical on every rank
+                "persist_fp32": [t.detach().cpu() for t in self.persist_fp32], "persist_m": [t.detach().cpu() for t in self.persist_m],
+                "persist_v": [t.detach().cpu() for t in self.persist_v]}
 
     def load_shard_state(self, sd: Dict):
         assert sd["partition_count"] == self.world, "ZeRO-3 checkpoint was written with a different world size"
@@ -392,4 +396,9 @@ class Zero3Engine:
             self.exp_avg[i].copy_(sd["exp_avg"][i])
             self.exp_avg_sq[i].copy_(sd["exp_avg_sq"][i])
             self.lp_slices[i].copy_(self.fp32[i].to(self.lp_slices[i].dtype))
+        if sd.get("persist_fp32") is not None and len(sd["persist_fp32"]) == len(self.persistent):
+            for p, p32, m, v, s32, sm, sv in zip(self.persistent, self.persist_fp32, self.persist_m, self.persist_v,
+                                                 sd["persist_fp32"], sd["persist_m"], sd["persist_v"]):
+                p32.copy_(s32); m.copy_(sm); v.copy_(sv)
+                p.data.copy_(p32.to(p.dtype))
         self._resident = [None, None]

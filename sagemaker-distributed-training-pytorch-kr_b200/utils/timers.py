@@ -9,6 +9,8 @@ from typing import Dict, List, Optional
 import torch
 import torch.distributed as dist
 
+from .metrics import nvtx_pop, nvtx_push
+
 
 class _Dummy:
     def start(self, barrier=False): pass
@@ -32,9 +34,11 @@ class _Timer:
         assert not self._started, f"timer {self.name} has already been started"
         self._sync(barrier)
         self._t0, self._started = time.time(), True
+        nvtx_push(self.name)          # visible in nsys / ncu timelines when --profile (or B200DIST_NVTX=1) is on
 
     def stop(self, barrier=False):
         assert self._started, f"timer {self.name} is not started"
+        nvtx_pop()
         self._sync(barrier)
         self._elapsed += time.time() - self._t0
         self._started = False

@@ -150,3 +150,32 @@ def test_train_entrypoint_original_config_offloads_the_optimizer_to_the_cpu(tmp_
     assert all(abs(a - b) < 5e-3 for a, b in zip(losses, ref)), (losses, ref)
     sd = ds_ckpt.zero_to_fp32(str(out))
     assert all(torch.isfinite(v).all() for v in sd.values())
+
+
+def test_trainer_checkpoint_rotation_resume_and_evaluation(tmp_path):
+    """save_steps / save_total_limit (4_...ipynb:474-476) produce resumable checkpoints; --resume_from_checkpoint continues
+    with the losses of the uninterrupted run; evaluation_strategy=steps reports eval_loss"""
+    out, losses = _run_train(tmp_path, 2, ["--max_steps", "6", "--save_steps", "2", "--save_total_limit", "2", "--weight_decay", "0.01"])
+    assert len(losses) == 6
+    assert sorted(n for n in os.listdir(out) if n.startswith("checkpoint-")) == ["checkpoint-4", "checkpoint-6"]
+    assert json.load(open(out / "checkpoint-4" / "trainer_state.json"))["global_step"] == 4
+    import shutil
+    shutil.rmtree(out / "checkpoint-6")
+    out2, resumed = _run_train(tmp_path, 2, ["--max_steps", "6", "--save_steps", "2", "--save_total_limit", "2", "--weight_decay", "0.01",
+                                            "--resume_from_checkpoint", "True"])
+    assert len(resumed) == 2 and all(abs(a - b) < 2e-4 for a, b in zip(resumed, losses[4:])), (resumed, losses)
+    # evaluation in-process (single rank)
+    from b200dist.config.hf_args import DataArguments, TrainingArguments
+    from b200dist.data import sft
+    from b200dist.engine.hf_trainer import Trainer
+    targs = TrainingArguments(output_dir=str(tmp_path / "ev"), max_steps=4, per_device_train_batch_size=2, logging_steps=2, evaluation_strategy="steps",
+                              eval_steps=2, save_strategy="no", learning_rate=1e-3, synthetic_data=True, synthetic_samples=16, model_max_length=32,
+                              comm_backend="nccl")
+    model = build_causal_lm("opt-tiny")
+    tok = sft.ByteTokenizer(model_max_length=32)
+    dm = sft.make_supervised_data_module(tok, DataArguments(data_path=None), targs, vocab_size=model.config.vocab_size)
+    dm["eval_dataset"] = dm["train_dataset"]
+    tr = Trainer(model=model, tokenizer=tok, args=targs, **dm)
+    tr.train()
+    evals = [h["eval_loss"] for h in tr.state.log_history if "eval_loss" in h]
+    assert len(evals) == 2 and evals[1] < evals[0]

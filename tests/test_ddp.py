@@ -150,3 +150,57 @@ def test_distributed_sampler_matches_torch():
         a = DistributedSampler(103, 4, rank, shuffle=True, seed=0); a.set_epoch(3)
         b = TS(ds, 4, rank, shuffle=True, seed=0); b.set_epoch(3)
         assert list(a) == list(b)
+
+
+def _hook_worker(rank, world, which):
+    """communication hooks (torch DDP register_comm_hook contract) and find_unused_parameters"""
+    import torch.distributed as dist
+    from b200dist.parallel import ddp as D
+    torch.manual_seed(0)
+    model = _Tiny()
+    extra = nn.Linear(16, 4)                      # never used in forward
+    model.add_module("unused_branch", extra)
+    ddp = D.DistributedDataParallel(model, bucket_cap_mb=0.004, first_bucket_cap_mb=0.001, find_unused_parameters=True)
+    seen = []
+    if which == "allreduce":
+        ddp.register_comm_hook(None, lambda st, b: (seen.append((b.index(), b.is_last(), len(b.parameters()))), D.allreduce_hook(st, b))[1])
+    elif which == "bf16":
+        ddp.register_comm_hook(None, D.bf16_compress_hook)
+    elif which == "custom":
+        def hook(state, bucket):               # synchronous hook returning a tensor
+            t = bucket.buffer().clone()
+            dist.all_reduce(t)
+            return t / world
+        ddp.register_comm_hook(None, hook)
+    torch.manual_seed(100 + rank)
+    x = torch.randn(4, 16)
+    ddp(x).sum().backward()
+    g = torch.cat([p.grad.reshape(-1) for n, p in model.named_parameters() if "unused_branch" not in n])
+    unused_zero = all(float(p.grad.abs().max()) == 0 for p in extra.parameters())
+    torch.manual_seed(0)
+    ref = _Tiny()
+    tot = None
+    for r in range(world):
+        torch.manual_seed(100 + r)
+        a = torch.randn(4, 16)
+        ref.zero_grad()
+        ref(a).sum().backward()
+        gr = torch.cat([p.grad.reshape(-1) for p in ref.parameters()])
+        tot = gr if tot is None else tot + gr
+    tol = 2e-2 if which == "bf16" else 1e-5
+    ok = torch.allclose(g, tot / world, atol=tol, rtol=tol)
+    try:
+        ddp.register_comm_hook(None, D.allreduce_hook)
+        twice = which == "none"
+    except RuntimeError:
+        twice = True
+    return ok, unused_zero, twice, len(seen)
+
+
+def test_ddp_comm_hooks_and_unused_parameters():
+    for which in ("none", "allreduce", "bf16", "custom"):
+        outs = run_distributed(_hook_worker, 2, which)
+        for ok, unused_zero, twice, nseen in outs:
+            assert ok and unused_zero and twice, (which, ok, unused_zero, twice)
+            if which == "allreduce":
+                assert nseen >= 2

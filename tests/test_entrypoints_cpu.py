@@ -140,3 +140,26 @@ def test_gpt_pretrain_llama_style_flags_and_switch_mlp_resume(tmp_path):
         f.write("3")
     resumed = _losses(_run("pretrain_gpt.py", GPT + extra + ["--load", ck]))
     assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == full[i] for i in (4, 5, 6))
+
+
+def test_gpt_pretrain_structured_metrics_and_fault_injection_recovery(tmp_path):
+    """JSONL + scalar sinks, --log-params-norm / --log-num-zeros-in-grad, and the recovery story
+    (a rank dies after a checkpoint -> relaunch with --load resumes from the latest checkpoint with identical losses)"""
+    import json
+    ck, mj, tb = str(tmp_path / "ck"), str(tmp_path / "m" / "metrics.jsonl"), str(tmp_path / "tb")
+    obs = ["--metrics-jsonl", mj, "--tensorboard-dir", tb, "--log-params-norm", "--log-num-zeros-in-grad", "--timing-log-level", "1"]
+    full = _losses(_run("pretrain_gpt.py", GPT + obs))
+    recs = [json.loads(l) for l in open(mj)]
+    assert [r["iteration"] for r in recs] == [1, 2, 3, 4, 5, 6]
+    for r in recs:
+        assert r["tokens_per_s"] > 0 and 0 < r["mfu"] < 1 and r["params_norm"] > 0 and r["num_zeros_in_grad"] >= 0 and "lm_loss" in r
+        assert abs(r["lm_loss"] - float(full[r["iteration"]])) < 1e-5
+    assert os.listdir(tb)
+    # a fault after iteration 4 (checkpoint at 3): the job fails ...
+    cmd = [sys.executable, os.path.join(ROOT, "entrypoints", "pretrain_gpt.py"), *GPT, "--save", ck, "--save-interval", "3", "--inject-fault", "0:4"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode != 0 and "injected fault on rank 0 at iteration 4" in r.stderr
+    assert open(os.path.join(ck, "latest_checkpointed_iteration.txt")).read().strip() == "3"
+    # ... and the relaunch picks up at iteration 4 with the losses of the uninterrupted run
+    resumed = _losses(_run("pretrain_gpt.py", GPT + ["--load", ck, "--save", ck, "--save-interval", "3"]))
+    assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == full[i] for i in (4, 5, 6))
