@@ -216,6 +216,17 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Stand-alone scale + mask + softmax over attention scores (the unfused attention path).  x, y: [rows, sk] with
+ * rows = batches * heads * sq; mask: uint8 [mask_batches, 1, sq, sk] (non-zero = masked, filled with -10000 after
+ * scaling; mask_batches == batches or 1) or NULL; causal != 0 hides keys j > i + (sk - sq).  sk <= 16384.
+ * Backward: dx = scale * y * (dy - sum_j dy_j y_j).  dtype: B2_DTYPE_{FP16,BF16,FP32}.
+ * replaces: Megatron scaled_upper_triang_masked_softmax_cuda / scaled_masked_softmax_cuda / scaled_softmax_cuda (E19).
+ */
+int b2_softmax_fwd(const void* x, const unsigned char* mask, void* y, long long rows, int sq, int sk, int heads,
+                   int mask_batches, float scale, int causal, int dtype, void* stream);
+int b2_softmax_bwd(const void* dy, const void* y, void* dx, long long rows, int sk, float scale, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Flash attention (tcgen05), bf16, head_dim 64 or 128.  Strides are in
  * elements for (seq, batch, head); head_dim is contiguous.  lse: fp32 [batch, heads, seqlen].
  * Backward: delta is fp32 scratch [batch, heads, seqlen]; dq_accum is fp32 [seq, batch, heads, D],

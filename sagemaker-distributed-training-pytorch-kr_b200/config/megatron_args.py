@@ -149,6 +149,9 @@ GROUPS: Dict[str, List[Flag]] = {
         _f("--tokenizer-model", type=str), _f("--data-impl", type=str, default="infer", choices=["mmap", "infer"]),
         _f("--reset-position-ids", action=T), _f("--reset-attention-mask", action=T), _f("--eod-mask-loss", action=T),
         _f("--mock-data", action=T, help="(addition) synthetic token stream of the configured shape"),
+        _f("--attention-impl", type=str, default="flash", choices=["flash", "unfused"],
+           help="(addition) flash = tcgen05 flash attention (default, what --use-flash-attn selects); unfused = the reference's CoreAttention: "
+                "batched GEMM, scale+mask+softmax kernel, dropout, batched GEMM"),
         _f("--metrics-jsonl", type=str, help="(addition) append one JSON record per log point: loss, lr, step ms, tokens/s, MFU"),
         _f("--inject-fault", type=str, help="(addition) RANK:ITERATION - raise on that rank after that iteration (recovery tests)"),
     ],
@@ -472,6 +475,8 @@ class TransformerConfig:
     rotary_percent: float = 1.0
     rotary_seq_len_interpolation_factor: Optional[int] = None
     position_embedding_type: str = "learned_absolute"
+    attention_impl: str = "flash"                   # "unfused": scores -> scale/mask/softmax kernel -> context (CoreAttention)
+    masked_softmax_fusion: bool = True
     untie_embeddings_and_output_weights: bool = False
     apply_query_key_layer_scaling: bool = True
     tensor_model_parallel_size: int = 1

@@ -27,7 +27,7 @@ from ..parallel.tensor import TPComm
 
 def needs_flex_layer(cfg: TransformerConfig) -> bool:
     ng = cfg.num_query_groups
-    return bool(cfg.swiglu or cfg.squared_relu or cfg.position_embedding_type == "rope" or cfg.apply_layernorm_1p
+    return bool(cfg.attention_impl == "unfused" or cfg.swiglu or cfg.squared_relu or cfg.position_embedding_type == "rope" or cfg.apply_layernorm_1p
                 or cfg.num_experts or cfg.apply_residual_connection_post_layernorm
                 or (ng is not None and ng != cfg.num_attention_heads)
                 or _activation_name(cfg) != "gelu_tanh")
@@ -364,8 +364,11 @@ class FlexTransformerLayer(nn.Module):
         if nq > 1:                                      # grouped-query: every K/V head serves nq query heads
             k4 = k4.unsqueeze(3).expand(S, B, ng, nq, hd).reshape(S, B, nh, hd)
             v4 = v4.unsqueeze(3).expand(S, B, ng, nq, hd).reshape(S, B, nh, hd)
-        seed_a = tp_ops.next_dropout_seed(True) if p_a > 0.0 else 0
-        ctx4 = Fn.attention(q4.contiguous(), k4.contiguous(), v4.contiguous(), self.softmax_scale, True, p_a, seed_a)
+        if cfg.attention_impl == "unfused":
+            ctx4 = core_attention(self, q4, k4, v4, p_a)
+        else:
+            seed_a = tp_ops.next_dropout_seed(True) if p_a > 0.0 else 0
+            ctx4 = Fn.attention(q4.contiguous(), k4.contiguous(), v4.contiguous(), self.softmax_scale, True, p_a, seed_a)
         ctx2 = ctx4.reshape(T, nh * hd)
         res1 = ln1 if cfg.apply_residual_connection_post_layernorm else x2      # both are [T_local, H]
         if p_h > 0.0:
@@ -379,6 +382,28 @@ class FlexTransformerLayer(nn.Module):
         seed2 = tp_ops.next_dropout_seed(False) if p_h > 0.0 else 0
         y2 = self.mlp(ln2, res2, p_h, seed2)
         return y2.view(S_loc, B, H)
+
+
+def core_attention(self, q4, k4, v4, p_drop):
+    """megatron CoreAttention (transformer.py): [s, b, h, d] -> scores [b, h, sq, sk] by batched GEMM, scale + causal mask +
+    softmax in one kernel (csrc/softmax.cu; torch.softmax when --no-masked-softmax-fusion), dropout under the
+    tensor-parallel RNG stream, context by batched GEMM."""
+    S, B, nh, hd = q4.shape
+    q = q4.permute(1, 2, 0, 3).reshape(B * nh, S, hd)
+    k = k4.permute(1, 2, 3, 0).reshape(B * nh, hd, S)
+    scores = torch.bmm(q, k).view(B, nh, S, S)
+    if self.cfg.masked_softmax_fusion:
+        probs = Fn.scaled_upper_triang_masked_softmax(scores, self.softmax_scale)
+    else:
+        keep = torch.ones(S, S, dtype=torch.bool, device=scores.device).tril()
+        probs = torch.softmax((scores.float() * self.softmax_scale).masked_fill(~keep, float("-inf")), dim=-1).to(scores.dtype)
+    if p_drop > 0.0:
+        with tp_ops.get_cuda_rng_tracker().fork():
+            probs = torch.nn.functional.dropout(probs, p_drop, training=True)
+    v = v4.permute(1, 2, 0, 3).reshape(B * nh, S, hd)
+    ctx = torch.bmm(probs.view(B * nh, S, S), v).view(B, nh, S, hd)
+    return ctx.permute(2, 0, 1, 3).contiguous()
+
 
 
 class _LNp(nn.Module):

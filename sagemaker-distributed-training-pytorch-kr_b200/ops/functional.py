@@ -399,3 +399,66 @@ def window_partition(x, ws: int, shift=(0, 0)):
 def window_reverse(xw, B: int, H: int, W: int, ws: int, shift=(0, 0)):
     """inverse of window_partition: [B * nW, ws*ws, C] -> [B, H, W, C], rolled back by +shift."""
     return _WindowShuffle.apply(xw, B, H, W, ws, (int(shift[0]), int(shift[1])), True)
+
+
+# =============================================================================================
+# scale + mask + softmax over materialised attention scores (the unfused attention path)
+# =============================================================================================
+class _ScaledMaskedSoftmax(torch.autograd.Function):
+    """x [b, h, sq, sk] -> softmax(scale * x, masked) ; native kernel on CUDA (csrc/softmax.cu), fp32 restatement on CPU."""
+
+    @staticmethod
+    def forward(ctx, x, mask, scale, causal):
+        y = N.softmax_fwd(x, mask, scale, causal)
+        ctx.save_for_backward(y)
+        ctx.scale = scale
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return N.softmax_bwd(dy, y, ctx.scale), None, None, None
+
+
+def scaled_masked_softmax(x, mask=None, scale: float = 1.0):
+    """reference: ScaledMaskedSoftmax / ScaledSoftmax (megatron/model/fused_softmax.py); mask True = masked."""
+    return _ScaledMaskedSoftmax.apply(x, mask, float(scale), False)
+
+
+def scaled_upper_triang_masked_softmax(x, scale: float = 1.0):
+    """reference: ScaledUpperTriangMaskedSoftmax (causal); x [b, h, sq, sk] (the reference folds b and h into one dim)."""
+    return _ScaledMaskedSoftmax.apply(x, None, float(scale), True)
+
+
+class FusedScaleMaskSoftmax(torch.nn.Module):
+    """megatron.model.fused_softmax.FusedScaleMaskSoftmax: picks the fused kernel when it applies, else scale -> mask_func ->
+    torch.softmax.  The native kernel has none of the reference's shape limits (16 < sk <= 4096, sq % 4, batches % 4) - only
+    sk <= 16384 - so `is_kernel_available` is true for every 16-bit input when fusion is on."""
+
+    def __init__(self, input_in_fp16: bool = False, input_in_bf16: bool = True, attn_mask_type: str = "causal", scaled_masked_softmax_fusion: bool = True,
+                 mask_func=None, softmax_in_fp32: bool = True, scale: Optional[float] = None):
+        super().__init__()
+        assert not (input_in_fp16 and input_in_bf16), "both fp16 and bf16 flags cannot be active at the same time."
+        self.input_in_float16 = input_in_fp16 or input_in_bf16
+        self.attn_mask_type, self.fusion, self.mask_func, self.softmax_in_fp32, self.scale = attn_mask_type, scaled_masked_softmax_fusion, mask_func, softmax_in_fp32, scale
+        assert self.scale is None or softmax_in_fp32, "softmax should be in fp32 when scaled"
+
+    def is_kernel_available(self, mask, b, np_, sq, sk) -> bool:
+        return bool(self.fusion and self.input_in_float16 and sk <= 16384)
+
+    def forward(self, x, mask=None):
+        assert x.dim() == 4
+        scale = self.scale if self.scale is not None else 1.0
+        if self.is_kernel_available(mask, *x.shape):
+            if self.attn_mask_type == "causal":
+                return scaled_upper_triang_masked_softmax(x, scale)
+            return scaled_masked_softmax(x, mask, scale)
+        xf = x.float() if (self.input_in_float16 and self.softmax_in_fp32) else x
+        xf = xf * scale if self.scale is not None else xf
+        if self.attn_mask_type == "causal" and mask is None:
+            sq, sk = x.shape[-2:]
+            mask = ~torch.ones(sq, sk, dtype=torch.bool, device=x.device).tril(diagonal=sk - sq)
+        if mask is not None:
+            xf = self.mask_func(xf, mask) if self.mask_func is not None else xf.masked_fill(mask, -10000.0)
+        p = torch.softmax(xf, dim=-1)
+        return p.to(x.dtype) if (self.input_in_float16 and self.softmax_in_fp32) else p

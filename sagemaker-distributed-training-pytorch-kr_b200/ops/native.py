@@ -64,6 +64,8 @@ _SIGS = {
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_f, c_ull, c_p],
+    "b2_softmax_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_p],
+    "b2_softmax_bwd": [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_p],
     "b2_num_sms": [],
 }
 
@@ -699,6 +701,48 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
         _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
     else:
         dq.copy_(dq32)
+
+
+# =============================================================================================
+# Stand-alone scale + mask + softmax (unfused attention path; Megatron fused_kernels scaled_*_softmax)
+# =============================================================================================
+def softmax_ref(x, mask, scale: float, causal: bool):
+    """fp32 restatement: x [b, h, sq, sk]; mask bool/uint8 [b | 1, 1, sq, sk] (True = masked -> -10000 after scaling)."""
+    s = x.float() * scale
+    if mask is not None:
+        s = s.masked_fill(mask.bool(), -10000.0)
+    if causal:
+        sq, sk = x.shape[-2], x.shape[-1]
+        keep = torch.ones(sq, sk, dtype=torch.bool, device=x.device).tril(diagonal=sk - sq)
+        s = s.masked_fill(~keep, float("-inf"))
+    return torch.softmax(s, dim=-1)
+
+
+def softmax_fwd(x: torch.Tensor, mask: Optional[torch.Tensor], scale: float, causal: bool) -> torch.Tensor:
+    """x: [b, h, sq, sk] contiguous scores -> probabilities (same dtype)."""
+    assert x.dim() == 4
+    if not x.is_cuda:
+        return softmax_ref(x, mask, scale, causal).to(x.dtype)
+    x = x.contiguous()
+    b, h, sq, sk = x.shape
+    m8 = None
+    if mask is not None:
+        assert mask.shape[-2:] == (sq, sk) and mask.shape[1] == 1 and mask.shape[0] in (1, b)
+        m8 = mask.to(torch.uint8).contiguous()
+    y = torch.empty_like(x)
+    _call("b2_softmax_fwd", _p(x), _p(m8), _p(y), b * h * sq, sq, sk, h, m8.shape[0] if m8 is not None else 1, float(scale), int(causal),
+          _dt(x), _st())
+    return y
+
+
+def softmax_bwd(dy: torch.Tensor, y: torch.Tensor, scale: float) -> torch.Tensor:
+    if not y.is_cuda:
+        yf, df = y.float(), dy.float()
+        return (scale * yf * (df - (df * yf).sum(-1, keepdim=True))).to(y.dtype)
+    dy, y = dy.contiguous(), y.contiguous()
+    dx = torch.empty_like(y)
+    _call("b2_softmax_bwd", _p(dy), _p(y), _p(dx), y.numel() // y.shape[-1], y.shape[-1], float(scale), _dt(y), _st())
+    return dx
 
 
 # =============================================================================================

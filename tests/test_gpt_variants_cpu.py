@@ -285,3 +285,43 @@ def test_parallel_layers_and_label_smoothed_loss(world, sp):
         assert np.allclose(loss, ref_loss.numpy(), rtol=1e-4, atol=1e-5)
         for k in ref_g:
             assert np.allclose(g[k], ref_g[k].numpy(), rtol=1e-3, atol=1e-5), (k, np.abs(g[k] - ref_g[k].numpy()).max())
+
+
+def test_unfused_core_attention_matches_flash_path():
+    """--attention-impl unfused (the reference's CoreAttention) against the default attention on the same weights"""
+    from b200dist.models.gpt import GPTModel
+    tokens, labels = torch.randint(0, 128, (2, 16)), torch.randint(0, 128, (2, 16))
+    a = GPTModel(_cfg(position_embedding_type="rope"), device="cpu", layer_offset=0, num_layers_here=2)
+    for fusion in (True, False):
+        b = GPTModel(_cfg(position_embedding_type="rope", attention_impl="unfused", masked_softmax_fusion=fusion), device="cpu", layer_offset=0, num_layers_here=2)
+        b.load_state_dict(a.state_dict())
+        a.zero_grad()
+        la, lb = a(tokens, labels=labels), b(tokens, labels=labels)
+        assert torch.allclose(la, lb, rtol=1e-5, atol=1e-5)
+        la.sum().backward(); lb.sum().backward()
+        for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+            assert torch.allclose(p.grad, q.grad, rtol=1e-3, atol=1e-5), n
+
+
+def test_scale_mask_softmax_op_and_module():
+    from b200dist.ops import functional as Fn
+    torch.manual_seed(0)
+    x = torch.randn(2, 3, 8, 12, requires_grad=True)
+    mask = torch.rand(2, 1, 8, 12) > 0.7
+    y = Fn.scaled_masked_softmax(x, mask, 0.5)
+    ref = torch.softmax((x * 0.5).masked_fill(mask, -10000.0), -1)
+    assert torch.allclose(y, ref, atol=1e-6)
+    g = torch.randn_like(y)
+    (gx,) = torch.autograd.grad(y, x, g)
+    (gr,) = torch.autograd.grad(ref, x, g)
+    assert torch.allclose(gx, gr, atol=1e-6)
+    yc = Fn.scaled_upper_triang_masked_softmax(x, 2.0)           # sq < sk: keys j <= i + (sk - sq) visible
+    keep = torch.ones(8, 12, dtype=torch.bool).tril(diagonal=4)
+    refc = torch.softmax((x * 2.0).masked_fill(~keep, float("-inf")), -1)
+    assert torch.allclose(yc, refc, atol=1e-6) and float(yc[..., 0, 5:].abs().max()) == 0.0
+    m = Fn.FusedScaleMaskSoftmax(input_in_bf16=True, attn_mask_type="padding", scale=0.5)
+    xb = x.detach().to(torch.bfloat16)
+    assert m.is_kernel_available(mask, *xb.shape)
+    assert torch.allclose(m(xb, mask).float(), ref.detach(), atol=2e-2)
+    m2 = Fn.FusedScaleMaskSoftmax(input_in_bf16=False, attn_mask_type="causal", scaled_masked_softmax_fusion=False, scale=2.0)
+    assert torch.allclose(m2(x.detach()), refc.detach(), atol=1e-6)
