@@ -216,6 +216,25 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * fp32 kernels of the MNIST CNN (csrc/conv.cu): valid stride-1 convolution with K x K filters (K <= 5), NCHW.
+ * fwd: y = relu?(conv(x, w) + bias).  bwd: g = dy * (yact > 0) when relu (yact = the forward output); dx (may be NULL),
+ * dw / db (may be NULL; accumulate != 0 adds into them).  One input / gradient image must fit in shared memory
+ * (<= 200 KB: e.g. 32 x 26 x 26 fp32).  maxpool2: 2 x 2, stride 2, idx = winning tap (uint8) for the backward.
+ * log_softmax_nll: C <= 32 classes; loss[row] = -logp[row, target[row]]; bwd adds the NLL gradient
+ * (gloss[row] (or 1) * gscalar) to dlogp (may be NULL) and applies the log-softmax Jacobian.
+ * replaces: cuDNN convolution fwd/bwd, ATen max_pool2d, log_softmax, nll_loss (model_def.py:22-45; K1, K2).
+ */
+int b2_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout, int K,
+                  int relu, void* stream);
+int b2_conv2d_bwd(const float* dy, const float* yact, const float* x, const float* w, float* dx, float* dw, float* db, int B,
+                  int Cin, int H, int W, int Cout, int K, int relu, int accumulate, void* stream);
+int b2_maxpool2_fwd(const float* x, float* y, unsigned char* idx, long long planes, int H, int W, void* stream);
+int b2_maxpool2_bwd(const float* dy, const unsigned char* idx, float* dx, long long planes, int H, int W, void* stream);
+int b2_log_softmax_nll_fwd(const float* x, const long long* target, float* logp, float* loss, long long rows, int C, void* stream);
+int b2_log_softmax_nll_bwd(const float* logp, const float* dlogp, const long long* target, const float* gloss, float gscalar,
+                           float* dx, long long rows, int C, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Stand-alone scale + mask + softmax over attention scores (the unfused attention path).  x, y: [rows, sk] with
  * rows = batches * heads * sq; mask: uint8 [mask_batches, 1, sq, sk] (non-zero = masked, filled with -10000 after
  * scaling; mask_batches == batches or 1) or NULL; causal != 0 hides keys j > i + (sk - sq).  sk <= 16384.

@@ -13,8 +13,12 @@ import torch.nn.functional as F
 
 
 class Net(nn.Module):
-    def __init__(self):
+    """`native_ops=True` (entry points: --native-ops): on a CUDA device the two conv + bias + ReLU stages, the max-pool and
+    the log-softmax run the fp32 kernels of csrc/conv.cu instead of cuDNN / ATen (same parameters, same state_dict)."""
+
+    def __init__(self, native_ops: bool = False):
         super().__init__()
+        self.native_ops = native_ops
         self.conv1 = nn.Conv2d(1, 32, 3, 1)
         self.conv2 = nn.Conv2d(32, 64, 3, 1)
         self.dropout1 = nn.Dropout2d(0.25)
@@ -23,6 +27,16 @@ class Net(nn.Module):
         self.fc2 = nn.Linear(128, 10)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.native_ops and x.dtype == torch.float32:
+            from ..ops import functional as Fn
+            x = Fn.conv2d_bias_relu(x, self.conv1.weight, self.conv1.bias)
+            x = Fn.conv2d_bias_relu(x, self.conv2.weight, self.conv2.bias)
+            x = Fn.max_pool2x2(x)
+            x = self.dropout1(x)
+            x = torch.flatten(x, 1)
+            x = F.relu(self.fc1(x))
+            x = self.dropout2(x)
+            return Fn.log_softmax_small(self.fc2(x))
         x = F.relu(self.conv1(x))
         x = F.relu(self.conv2(x))
         x = F.max_pool2d(x, 2)

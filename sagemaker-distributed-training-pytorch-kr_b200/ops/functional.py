@@ -462,3 +462,62 @@ class FusedScaleMaskSoftmax(torch.nn.Module):
             xf = self.mask_func(xf, mask) if self.mask_func is not None else xf.masked_fill(mask, -10000.0)
         p = torch.softmax(xf, dim=-1)
         return p.to(x.dtype) if (self.input_in_float16 and self.softmax_in_fp32) else p
+
+
+# =============================================================================================
+# fp32 MNIST ops (conv + bias + ReLU, max-pool, log-softmax): csrc/conv.cu on CUDA, ATen on CPU
+# =============================================================================================
+class _ConvBiasReLU(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, relu):
+        y = N.conv2d_fwd(x, w, b, relu)
+        ctx.save_for_backward(x, w, y)
+        ctx.relu, ctx.has_bias = relu, b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y = ctx.saved_tensors
+        dx, dw, db = N.conv2d_bwd(dy, y, x, w, ctx.relu, ctx.needs_input_grad[0], ctx.has_bias)
+        return dx, dw, db, None
+
+
+def conv2d_bias_relu(x, weight, bias=None, relu: bool = True):
+    """valid stride-1 convolution + bias + ReLU in one kernel (fp32)"""
+    return _ConvBiasReLU.apply(x, weight, bias, relu)
+
+
+class _MaxPool2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y, idx = N.maxpool2_fwd(x)
+        ctx.save_for_backward(idx)
+        ctx.in_shape = tuple(x.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        return N.maxpool2_bwd(dy, idx, ctx.in_shape)
+
+
+def max_pool2x2(x):
+    return _MaxPool2.apply(x)
+
+
+class _LogSoftmax(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        lp, _ = N.log_softmax_nll_fwd(x, None)
+        ctx.save_for_backward(lp)
+        return lp
+
+    @staticmethod
+    def backward(ctx, d):
+        (lp,) = ctx.saved_tensors
+        return N.log_softmax_nll_bwd(lp, d.contiguous())
+
+
+def log_softmax_small(x):
+    """log_softmax over dim 1 for <= 32 classes (one warp per row)"""
+    return _LogSoftmax.apply(x)

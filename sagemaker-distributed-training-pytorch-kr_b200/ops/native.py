@@ -64,6 +64,12 @@ _SIGS = {
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_f, c_ull, c_p],
+    "b2_conv2d_fwd": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_conv2d_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_maxpool2_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_p],
+    "b2_maxpool2_bwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_p],
+    "b2_log_softmax_nll_fwd": [c_p, c_p, c_p, c_p, c_ll, c_i, c_p],
+    "b2_log_softmax_nll_bwd": [c_p, c_p, c_p, c_p, c_f, c_p, c_ll, c_i, c_p],
     "b2_softmax_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_p],
     "b2_softmax_bwd": [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_p],
     "b2_num_sms": [],
@@ -701,6 +707,94 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
         _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
     else:
         dq.copy_(dq32)
+
+
+# =============================================================================================
+# fp32 MNIST kernels: valid 3x3 convolution (+bias+ReLU), 2x2 max-pool, log-softmax + NLL   (csrc/conv.cu)
+# =============================================================================================
+def conv2d_fwd(x, w, bias, relu: bool):
+    """x [B, Cin, H, W] fp32, w [Cout, Cin, K, K] -> relu?(conv(x, w) + bias), valid, stride 1"""
+    if not x.is_cuda:
+        y = F.conv2d(x, w, bias)
+        return F.relu(y) if relu else y
+    x, w = x.contiguous(), w.contiguous()
+    B, Cin, H, W = x.shape
+    Cout, _, K, _ = w.shape
+    y = torch.empty((B, Cout, H - K + 1, W - K + 1), dtype=torch.float32, device=x.device)
+    _call("b2_conv2d_fwd", _p(x), _p(w), _p(bias), _p(y), B, Cin, H, W, Cout, K, int(relu), _st())
+    return y
+
+
+def conv2d_bwd(dy, y, x, w, relu: bool, need_dx: bool, has_bias: bool = True):
+    """-> (dx | None, dw, db | None); y is the forward output (ReLU mask)"""
+    if not x.is_cuda:
+        g = dy * (y > 0) if relu else dy
+        dx = torch.nn.grad.conv2d_input(x.shape, w, g) if need_dx else None
+        dw = torch.nn.grad.conv2d_weight(x, w.shape, g)
+        return dx, dw, (g.sum((0, 2, 3)) if has_bias else None)
+    dy, y, x, w = dy.contiguous(), y.contiguous(), x.contiguous(), w.contiguous()
+    B, Cin, H, W = x.shape
+    Cout, _, K, _ = w.shape
+    dx = torch.empty_like(x) if need_dx else None
+    dw = torch.empty_like(w)
+    db = torch.empty(Cout, dtype=torch.float32, device=x.device) if has_bias else None
+    _call("b2_conv2d_bwd", _p(dy), _p(y), _p(x), _p(w), _p(dx), _p(dw), _p(db), B, Cin, H, W, Cout, K, int(relu), 0, _st())
+    return dx, dw, db
+
+
+def maxpool2_fwd(x):
+    """x [..., H, W] fp32 -> (y [..., H//2, W//2], idx uint8 same shape as y)"""
+    H, W = x.shape[-2:]
+    if not x.is_cuda:
+        y, ind = F.max_pool2d(x.reshape(-1, 1, H, W), 2, return_indices=True)
+        iy, ix = (ind // W) % 2, (ind % W) % 2
+        return y.view(*x.shape[:-2], H // 2, W // 2), (iy * 2 + ix).to(torch.uint8).view(*x.shape[:-2], H // 2, W // 2)
+    x = x.contiguous()
+    y = torch.empty((*x.shape[:-2], H // 2, W // 2), dtype=torch.float32, device=x.device)
+    idx = torch.empty(y.shape, dtype=torch.uint8, device=x.device)
+    _call("b2_maxpool2_fwd", _p(x), _p(y), _p(idx), x.numel() // (H * W), H, W, _st())
+    return y, idx
+
+
+def maxpool2_bwd(dy, idx, in_shape):
+    H, W = in_shape[-2:]
+    if not dy.is_cuda:
+        dx = torch.zeros(in_shape, dtype=dy.dtype)
+        Ho, Wo = H // 2, W // 2
+        v = dx[..., :2 * Ho, :2 * Wo].reshape(*in_shape[:-2], Ho, 2, Wo, 2).permute(*range(len(in_shape) - 2), -4, -2, -3, -1)
+        oh = torch.nn.functional.one_hot(idx.long(), 4).view(*idx.shape, 2, 2).to(dy.dtype)
+        v.copy_(oh * dy[..., None, None])
+        return dx
+    dy = dy.contiguous()
+    dx = torch.empty(in_shape, dtype=torch.float32, device=dy.device)
+    _call("b2_maxpool2_bwd", _p(dy), _p(idx), _p(dx), dx.numel() // (H * W), H, W, _st())
+    return dx
+
+
+def log_softmax_nll_fwd(x, target=None):
+    """x [rows, C <= 32] fp32 -> (logp, loss[rows] | None)"""
+    if not x.is_cuda:
+        lp = F.log_softmax(x, dim=1)
+        return lp, (F.nll_loss(lp, target, reduction="none") if target is not None else None)
+    x = x.contiguous()
+    lp = torch.empty_like(x)
+    loss = torch.empty(x.shape[0], dtype=torch.float32, device=x.device) if target is not None else None
+    _call("b2_log_softmax_nll_fwd", _p(x), _p(target), _p(lp), _p(loss), x.shape[0], x.shape[1], _st())
+    return lp, loss
+
+
+def log_softmax_nll_bwd(logp, dlogp=None, target=None, gloss=None, gscalar: float = 1.0):
+    """gradient wrt the logits of  sum(dlogp * logp) + sum(gloss * gscalar * nll(logp, target))"""
+    if not logp.is_cuda:
+        d = dlogp.clone() if dlogp is not None else torch.zeros_like(logp)
+        if target is not None:
+            g = (gloss if gloss is not None else torch.ones(logp.shape[0])) * gscalar
+            d[torch.arange(logp.shape[0]), target] -= g
+        return d - logp.exp() * d.sum(1, keepdim=True)
+    dx = torch.empty_like(logp)
+    _call("b2_log_softmax_nll_bwd", _p(logp), _p(dlogp.contiguous() if dlogp is not None else None), _p(target),
+          _p(gloss.contiguous() if gloss is not None else None), float(gscalar), _p(dx), logp.shape[0], logp.shape[1], _st())
+    return dx
 
 
 # =============================================================================================

@@ -66,3 +66,45 @@ def test_swin_t_forward_matches_torchvision():
     x = torch.randn(2, 3, 64, 64)
     with torch.no_grad():
         assert torch.allclose(m(x), ref(x), atol=1e-5)
+
+
+def test_mnist_native_op_layer_matches_aten_on_cpu():
+    """the autograd wrappers around csrc/conv.cu (CPU: their restatements) against plain ATen ops, and the MNIST model with
+    native_ops on / off (same parameters, eval mode so dropout is inert)"""
+    import torch
+    import torch.nn.functional as F
+    from b200dist.models.mnist import Net
+    from b200dist.ops import functional as Fn
+    from b200dist.ops import native as N
+    torch.manual_seed(0)
+    x = torch.randn(3, 2, 9, 9, requires_grad=True)
+    w = torch.randn(5, 2, 3, 3, requires_grad=True)
+    b = torch.randn(5, requires_grad=True)
+    y = Fn.max_pool2x2(Fn.conv2d_bias_relu(x, w, b))
+    ref = F.max_pool2d(F.relu(F.conv2d(x, w, b)), 2)
+    assert torch.allclose(y, ref, atol=1e-6)
+    g = torch.randn_like(y)
+    got = torch.autograd.grad(y, (x, w, b), g)
+    want = torch.autograd.grad(ref, (x, w, b), g)
+    for a_, b_ in zip(got, want):
+        assert torch.allclose(a_, b_, atol=1e-5)
+    z = torch.randn(7, 10, requires_grad=True)
+    lp = Fn.log_softmax_small(z)
+    t = torch.randint(0, 10, (7,))
+    (gz,) = torch.autograd.grad(F.nll_loss(lp, t), z)
+    (gr,) = torch.autograd.grad(F.nll_loss(F.log_softmax(z, 1), t), z)
+    assert torch.allclose(gz, gr, atol=1e-6)
+    # fused loss form of the kernel pair
+    lp2, loss = N.log_softmax_nll_fwd(z.detach(), t)
+    assert torch.allclose(loss, F.nll_loss(F.log_softmax(z.detach(), 1), t, reduction="none"), atol=1e-6)
+    assert torch.allclose(N.log_softmax_nll_bwd(lp2, None, t, None, 1.0 / 7), gr, atol=1e-6)
+    # odd spatial size: the last row / column is dropped by the pool and receives zero gradient
+    xo = torch.randn(2, 3, 7, 5, requires_grad=True)
+    yo = Fn.max_pool2x2(xo)
+    ro = F.max_pool2d(xo, 2)
+    assert torch.equal(yo, ro)
+    assert torch.equal(torch.autograd.grad(yo.sum(), xo)[0], torch.autograd.grad(ro.sum(), xo)[0])
+    m1, m2 = Net().eval(), Net(native_ops=True).eval()
+    m2.load_state_dict(m1.state_dict())
+    img = torch.randn(4, 1, 28, 28)
+    assert torch.allclose(m1(img), m2(img), atol=1e-5)
