@@ -487,6 +487,7 @@ class TransformerConfig:
     recompute_granularity: Optional[str] = None
     recompute_method: Optional[str] = None
     recompute_num_layers: int = 1
+    distribute_saved_activations: bool = False
     fp16: bool = False
     bf16: bool = False
     fp32_residual_connection: bool = False

@@ -20,6 +20,7 @@ import math
 from typing import List, Optional
 
 import torch
+import torch.distributed as dist
 import torch.nn as nn
 
 from ..config.megatron_args import TransformerConfig
@@ -223,24 +224,38 @@ class ParallelTransformerLayer(nn.Module):
 
 
 class _RecomputeFn(torch.autograd.Function):
-    """`--recompute-granularity full` (Megatron's checkpointed transformer layer): the forward runs without recording
-    a graph and saves only the layer input; the backward re-runs the layer with the dropout-seed counter (and torch RNG
-    state) of the first run, then back-propagates through the re-run.  `selective` needs no code here: the only
-    activations it drops in the reference are the attention scores, which the flash-attention kernel never stores."""
+    """`--recompute-granularity full` (Megatron's checkpointed transformer layers, tensor_parallel.random.checkpoint): the
+    forward runs without recording a graph and saves only the input of a GROUP of layers; the backward re-runs the group
+    with the dropout-seed counter (and torch RNG state) of the first run, then back-propagates through the re-run.
+    `--distribute-saved-activations`: the saved input is split over the tensor-parallel ranks (each keeps 1/t of it) and
+    all-gathered before the re-run.  `selective` needs no code here: the only activations it drops in the reference are
+    the attention scores, which the flash-attention kernel never stores."""
 
     @staticmethod
-    def forward(ctx, x, layer):
-        ctx.layer = layer
+    def forward(ctx, x, layers, distribute_group):
+        ctx.layers = layers
         ctx.seed_state = tp_ops.dropout_seed_state()
         ctx.cpu_rng = torch.get_rng_state()
         ctx.cuda_rng = torch.cuda.get_rng_state() if x.is_cuda else None
-        ctx.save_for_backward(x)
+        ctx.dist_group, ctx.shape = distribute_group, x.shape
+        if distribute_group is not None:
+            t, r = dist.get_world_size(distribute_group), dist.get_rank(distribute_group)
+            flat = x.detach().reshape(-1)
+            assert flat.numel() % t == 0, "--distribute-saved-activations: activation size must divide by the tensor-parallel size"
+            ctx.save_for_backward(flat.chunk(t)[r].clone())
+        else:
+            ctx.save_for_backward(x)
         with torch.no_grad():
-            return layer(x)
+            h = x
+            for layer in layers:
+                h = layer(h)
+            return h
 
     @staticmethod
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
+        if ctx.dist_group is not None:
+            x = tp_ops.all_gather_first_dim(x, ctx.dist_group).view(ctx.shape)
         now_seed, now_cpu = tp_ops.dropout_seed_state(), torch.get_rng_state()
         now_cuda = torch.cuda.get_rng_state() if x.is_cuda else None
         tp_ops.set_dropout_seed_state(ctx.seed_state)
@@ -250,14 +265,31 @@ class _RecomputeFn(torch.autograd.Function):
         try:
             xin = x.detach().requires_grad_(True)
             with torch.enable_grad():
-                y = ctx.layer(xin)
+                y = xin
+                for layer in ctx.layers:
+                    y = layer(y)
             torch.autograd.backward(y, dy)
         finally:
             tp_ops.set_dropout_seed_state(now_seed)
             torch.set_rng_state(now_cpu)
             if now_cuda is not None:
                 torch.cuda.set_rng_state(now_cuda)
-        return xin.grad, None
+        return xin.grad, None, None
+
+
+def recompute_plan(num_layers: int, method: Optional[str], group: int):
+    """[(first layer, one past last, recompute?)] for the layers of one model chunk (reference: ParallelTransformer.
+    _checkpointed_forward, transformer.py).  `uniform`: consecutive groups of `group` layers, each re-run as a unit from its
+    saved input; `block`: the first `group` layers are recomputed one by one, the rest keep their activations; no method
+    given: every layer on its own (uniform with groups of one)."""
+    group = max(1, int(group or 1))
+    if method == "block":
+        return [(i, i + 1, i < group) for i in range(num_layers)]
+    if method not in (None, "uniform"):
+        raise ValueError("Invalid activation recompute method.")
+    if method is None:
+        group = 1
+    return [(i, min(i + group, num_layers), True) for i in range(0, num_layers, group)]
 
 
 class _Lin(nn.Module):
@@ -435,10 +467,19 @@ class GPTModel(nn.Module):
                 h = _DropoutFn.apply(h, p, tp_ops.next_dropout_seed(self.comm.sp))
         else:
             h = self.input_tensor
-        for layer in lm.encoder.layers:
-            if self.cfg.recompute_granularity == "full" and self.training:
-                h = _RecomputeFn.apply(h, layer)      # keep only the layer input; the layer is re-run in backward
-            else:
+        if self.cfg.recompute_granularity == "full" and self.training:
+            dgroup = None
+            if self.cfg.distribute_saved_activations and self.comm.size > 1 and not self.comm.sp:
+                dgroup = self.comm.group          # under sequence parallelism the activation is already 1/t per rank
+            layers = list(lm.encoder.layers)
+            for a, b, re in recompute_plan(len(layers), self.cfg.recompute_method, self.cfg.recompute_num_layers):
+                if re:
+                    h = _RecomputeFn.apply(h, layers[a:b], dgroup)      # keep only the group's input; re-run in backward
+                else:
+                    for layer in layers[a:b]:
+                        h = layer(h)
+        else:
+            for layer in lm.encoder.layers:
                 h = layer(h)
         if not self.post_process:
             return h

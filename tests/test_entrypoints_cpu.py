@@ -107,6 +107,23 @@ def test_gpt_full_recompute_is_bit_identical_with_dropout():
     plain = _losses(_run("pretrain_gpt.py", base))
     rec = _losses(_run("pretrain_gpt.py", base + ["--recompute-granularity", "full"]))
     assert sorted(plain) == [1, 2, 3, 4] and plain == rec
+    # the reference's recompute methods: uniform groups of 2 layers, and block (first layer only)
+    l4 = [a for a in base]
+    l4[l4.index("--num-layers") + 1] = "4"
+    plain4 = _losses(_run("pretrain_gpt.py", l4))
+    for extra in (["--recompute-method", "uniform", "--recompute-num-layers", "2"], ["--recompute-method", "block", "--recompute-num-layers", "1"]):
+        assert _losses(_run("pretrain_gpt.py", l4 + ["--recompute-granularity", "full"] + extra)) == plain4, extra
+
+
+def test_gpt_distributed_saved_activations_tp2():
+    """--distribute-saved-activations: the checkpointed layer input is kept as 1/t slices and re-gathered in backward"""
+    base = [a for a in GPT]
+    base[base.index("--train-iters") + 1] = "3"
+    tp = ["--tensor-model-parallel-size", "2", "--hidden-dropout", "0", "--attention-dropout", "0"]
+    plain = _losses(_run("pretrain_gpt.py", base + tp, nproc=2))
+    rec = _losses(_run("pretrain_gpt.py", base + tp + ["--recompute-granularity", "full", "--recompute-method", "uniform",
+                                                        "--distribute-saved-activations"], nproc=2))
+    assert sorted(plain) == [1, 2, 3] and plain == rec
 
 
 def test_gpt_distributed_optimizer_matches_replicated_and_resumes(tmp_path):

@@ -290,3 +290,12 @@ def test_build_blocks_mapping_matches_python_twin():
     assert (raw[:half, 3] == np.arange(half)).all() and raw[half, 3] == 0                   # block ids restart every epoch
     for a, b, d, _ in raw:
         assert docs[d] <= a < b <= docs[d + 1]
+
+
+def test_recompute_plan_methods():
+    from b200dist.models.gpt import recompute_plan
+    assert recompute_plan(5, None, 3) == [(0, 1, True), (1, 2, True), (2, 3, True), (3, 4, True), (4, 5, True)]
+    assert recompute_plan(5, "uniform", 2) == [(0, 2, True), (2, 4, True), (4, 5, True)]
+    assert recompute_plan(4, "block", 1) == [(0, 1, True), (1, 2, False), (2, 3, False), (3, 4, False)]
+    with pytest.raises(ValueError):
+        recompute_plan(4, "other", 1)
