@@ -23,6 +23,7 @@ from ..launch import env as launch_env
 from ..optim.mixed import ConstantGradScaler, DynamicGradScaler, MixedPrecisionOptimizer
 from ..optim.schedulers import OptimizerParamScheduler
 from ..parallel import pipeline as pp
+from ..utils import microbatches as mb
 from ..parallel import state as mpu
 from ..parallel import tensor as tp_ops
 from ..utils.timers import Timers
@@ -113,6 +114,7 @@ def initialize_megatron(extra_args_provider=None, args_defaults=None, ignore_unk
     args.rank, args.world_size = info.rank, info.world_size
     args = megatron_args.validate_args(args, args_defaults or {}, verbose=True)
     _GLOBAL["args"] = args
+    mb.build_num_microbatches_calculator(args)
     _GLOBAL["timers"] = Timers(args.timing_log_level, args.timing_log_option)
     backend = args.distributed_backend if torch.cuda.is_available() else "gloo"
     if args.rank == 0:
@@ -225,9 +227,20 @@ def get_optimizer_param_scheduler(optimizer):
 
 
 def update_train_iters(args):
+    """sample-based training: the iteration count, including the shorter iterations of a batch-size ramp-up (training.py)"""
     if args.train_iters:
         return
-    args.train_iters = args.train_samples // args.global_batch_size
+    if args.rampup_batch_size is None:
+        args.train_iters = args.train_samples // args.global_batch_size
+    else:
+        iterations, consumed = 0, 0
+        while consumed <= int(args.rampup_batch_size[2]):
+            mb.update_num_microbatches(consumed, consistency_check=False)
+            consumed += mb.get_current_global_batch_size()
+            iterations += 1
+        mb.update_num_microbatches(0, consistency_check=False)
+        iterations += (args.train_samples - consumed) // args.global_batch_size
+        args.train_iters = iterations
     print_rank_0("setting training iterations to {}".format(args.train_iters))
 
 
@@ -278,7 +291,10 @@ def get_graph_runner(forward_step_func, model):
     if len(model) != 1 or not graphed.supported(args, model[0]):
         print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, dropout 0, bf16/fp32, no recompute, fabric collectives for TP): running eagerly")
         return None
-    nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
+    if args.rampup_batch_size is not None:
+        print_rank_0("> --cuda-graph replays a fixed number of micro-batches: not used with --rampup-batch-size")
+        return None
+    nmb = mb.get_num_microbatches()
     dev = torch.device("cuda", torch.cuda.current_device())
     args._static_batch = True
     r = graphed.GraphedMicrobatch(forward_step_func, model[0], nmb, args.micro_batch_size, args.seq_length, dev)
@@ -294,7 +310,7 @@ def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_sch
     optimizer.zero_grad()
     S = args.seq_length // (args.tensor_model_parallel_size if args.sequence_parallel else 1)
     shape = (S, args.micro_batch_size, args.hidden_size)
-    nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
+    nmb = mb.get_num_microbatches()
     timers("forward-backward", log_level=1).start(barrier=args.barrier_with_L1_time)
     if runner is not None:
         losses = runner.run_step(data_iterator)
@@ -343,7 +359,8 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
         s += " consumed samples: {:12d} |".format(args.consumed_train_samples)
         s += " elapsed time per iteration (ms): {:.1f} |".format(per_iter * 1000.0)
         s += " learning rate: {:.3E} |".format(learning_rate)
-        s += " global batch size: {:5d} |".format(args.global_batch_size)
+        batch_size = mb.get_current_global_batch_size()
+        s += " global batch size: {:5d} |".format(batch_size)
         for k in list(total_loss_dict.keys()):
             if k in (adv, skp, nan):
                 continue
@@ -355,7 +372,7 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
             total_loss_dict[k] = 0.0
         s += " loss scale: {:.1f} |".format(loss_scale)
         rec = {"iteration": iteration, "consumed_samples": args.consumed_train_samples, "ms_per_iteration": per_iter * 1000.0,
-               "learning_rate": learning_rate, "global_batch_size": args.global_batch_size, "loss_scale": loss_scale,
+               "learning_rate": learning_rate, "global_batch_size": batch_size, "loss_scale": loss_scale,
                "skipped_iterations": total_loss_dict[skp], **{k.replace(" ", "_"): v for k, v in logged.items()}}
         if grad_norm is not None:
             gn = math.sqrt(float(grad_norm)) if torch.is_tensor(grad_norm) else float(grad_norm)
@@ -369,7 +386,7 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
             rec["params_norm"] = params_norm
         s += " number of skipped iterations: {:3d} |".format(total_loss_dict[skp])
         s += " number of nan iterations: {:3d} |".format(total_loss_dict[nan])
-        tokens_per_s = args.global_batch_size * args.seq_length / max(per_iter, 1e-9)
+        tokens_per_s = batch_size * args.seq_length / max(per_iter, 1e-9)
         s += " tokens/s: {:.0f} |".format(tokens_per_s)
         sink, tb = _GLOBAL["sink"], _GLOBAL["tb"]
         if (sink is not None and sink.enabled) or (tb is not None and tb.enabled):
@@ -390,10 +407,10 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
         total_loss_dict[adv] = total_loss_dict[skp] = total_loss_dict[nan] = 0
         print_rank_last(s)
         if report_memory_flag and learning_rate > 0.0 and torch.cuda.is_available():
-            mb = 1024.0 * 1024.0
+            mib = 1024.0 * 1024.0
             print("[Rank {}] (after {} iterations) memory (MB) | allocated: {} | max allocated: {} | reserved: {} | max reserved: {}".format(
-                dist.get_rank() if dist.is_initialized() else 0, iteration, torch.cuda.memory_allocated() / mb, torch.cuda.max_memory_allocated() / mb,
-                torch.cuda.memory_reserved() / mb, torch.cuda.max_memory_reserved() / mb), flush=True)
+                dist.get_rank() if dist.is_initialized() else 0, iteration, torch.cuda.memory_allocated() / mib, torch.cuda.max_memory_allocated() / mib,
+                torch.cuda.memory_reserved() / mib, torch.cuda.max_memory_reserved() / mib), flush=True)
             report_memory_flag = False
         names = ["forward-backward", "forward-compute", "backward-compute", "batch-generator", "all-grads-sync", "optimizer"]
         timers.log(names, normalizer=args.log_interval)
@@ -407,7 +424,7 @@ def evaluate(forward_step_func, data_iterator, model, verbose=False):
     total = {}
     S = args.seq_length // (args.tensor_model_parallel_size if args.sequence_parallel else 1)
     shape = (S, args.micro_batch_size, args.hidden_size)
-    nmb = pp.get_num_microbatches(args.global_batch_size, args.micro_batch_size, args.data_parallel_size)
+    nmb = mb.get_num_microbatches()
     with torch.no_grad():
         for it in range(args.eval_iters):
             if verbose and (it + 1) % args.log_interval == 0:
@@ -417,7 +434,7 @@ def evaluate(forward_step_func, data_iterator, model, verbose=False):
                 for d in losses:
                     for k, v in d.items():
                         total[k] = total.get(k, 0.0) + v
-            args.consumed_valid_samples += args.global_batch_size
+            args.consumed_valid_samples += mb.get_current_global_batch_size()
     for m in model:
         m.train()
     for k in total:
@@ -463,9 +480,10 @@ def train(forward_step_func, model, optimizer, opt_param_scheduler, train_data_i
             if iteration == args.profile_step_end and prof_on:
                 torch.cuda.cudart().cudaProfilerStop(); prof_on = False
         args.curr_iteration = iteration
+        mb.update_num_microbatches(args.consumed_train_samples)
         loss_dict, skipped, grad_norm, num_zeros = train_step(forward_step_func, train_data_iterator, model, optimizer, opt_param_scheduler)
         iteration += 1
-        args.consumed_train_samples += args.global_batch_size
+        args.consumed_train_samples += mb.get_current_global_batch_size()
         loss_scale = optimizer.get_loss_scale()
         lr = optimizer.param_groups[0]["lr"]
         # loss values stay device tensors between log points; they are only read on the host at a log boundary

@@ -180,3 +180,20 @@ def test_gpt_pretrain_structured_metrics_and_fault_injection_recovery(tmp_path):
     # ... and the relaunch picks up at iteration 4 with the losses of the uninterrupted run
     resumed = _losses(_run("pretrain_gpt.py", GPT + ["--load", ck, "--save", ck, "--save-interval", "3"]))
     assert sorted(resumed) == [4, 5, 6] and all(resumed[i] == full[i] for i in (4, 5, 6))
+
+
+def test_gpt_sample_based_training_with_batch_size_rampup():
+    """--train-samples + --rampup-batch-size 2 2 8: global batch 2 -> 4 over the first 8 samples (megatron/microbatches.py)"""
+    argv = [a for a in GPT]
+    for flag in ("--train-iters", "--lr-decay-iters", "--lr-warmup-iters"):
+        i = argv.index(flag)
+        del argv[i:i + 2]
+    argv[argv.index("--micro-batch-size") + 1] = "1"
+    out = _run("pretrain_gpt.py", argv + ["--train-samples", "20", "--lr-decay-samples", "20", "--lr-warmup-samples", "4", "--rampup-batch-size", "2", "2", "8"])
+    rows = re.findall(r"iteration\s+(\d+)/\s*(\d+) \| consumed samples:\s+(\d+) .*? global batch size:\s+(\d+) ", out)
+    assert rows, out[-2000:]
+    sizes = [int(r[3]) for r in rows]
+    consumed = [int(r[2]) for r in rows]
+    assert sizes[0] == 2 and sizes[-1] == 4 and sorted(sizes) == sizes
+    assert all(consumed[i] - (consumed[i - 1] if i else 0) == sizes[i] for i in range(len(rows)))
+    assert int(rows[0][1]) == len(rows) and consumed[-1] <= 20

@@ -299,3 +299,23 @@ def test_recompute_plan_methods():
     assert recompute_plan(4, "block", 1) == [(0, 1, True), (1, 2, False), (2, 3, False), (3, 4, False)]
     with pytest.raises(ValueError):
         recompute_plan(4, "other", 1)
+
+
+def test_microbatch_calculators_constant_and_rampup():
+    from types import SimpleNamespace
+    from b200dist.utils import microbatches as mb
+    a = SimpleNamespace(rampup_batch_size=None, global_batch_size=192, micro_batch_size=12, data_parallel_size=4, rank=1)
+    mb.build_num_microbatches_calculator(a)
+    assert mb.get_num_microbatches() == 4 and mb.get_current_global_batch_size() == 192
+    a.rampup_batch_size = ["32", "32", "1000"]          # 32 -> 192 in 5 increments of 32 over 1000 samples (200 samples each)
+    a.micro_batch_size, a.data_parallel_size = 4, 2
+    mb.build_num_microbatches_calculator(a)
+    seen = []
+    for consumed in (0, 199, 200, 450, 999, 1000, 1001, 5000):
+        mb.update_num_microbatches(consumed)
+        seen.append((mb.get_current_global_batch_size(), mb.get_num_microbatches()))
+    assert seen == [(32, 4), (32, 4), (64, 8), (96, 12), (160, 20), (192, 24), (192, 24), (192, 24)]
+    a.micro_batch_size = 5                               # 32 is not a multiple of 5 * 2: caught by the consistency check
+    mb.build_num_microbatches_calculator(a)
+    with pytest.raises(AssertionError):
+        mb.update_num_microbatches(0, consistency_check=True)
