@@ -16,6 +16,14 @@ from b200dist.config.hf_args import DataArguments, HfArgumentParser, ModelArgume
 from b200dist.data import sft
 from b200dist.models.llama import build_causal_lm
 
+
+def _free_port():
+    import socket
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        return so.getsockname()[1]
+
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
@@ -110,7 +118,7 @@ def _run_train(tmp_path, nproc, extra):
                                 {"instruction": "Name a color.", "input": "", "output": "blue"}, {"instruction": "Double it.", "input": "4", "output": "8"}]))
     out = tmp_path / "out"
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
-           "--master-port", str(29600 + os.getpid() % 300), os.path.join(ROOT, "entrypoints", "train.py"),
+           "--master-port", str(_free_port()), os.path.join(ROOT, "entrypoints", "train.py"),
            "--model_name_or_path", "opt-tiny", "--data_path", str(data), "--output_dir", str(out), "--max_steps", "5",
            "--per_device_train_batch_size", "1", "--gradient_accumulation_steps", "2", "--learning_rate", "1e-3", "--logging_steps", "1",
            "--model_max_length", "512", "--bf16", "True", *extra]

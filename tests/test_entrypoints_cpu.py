@@ -8,6 +8,14 @@ import sys
 
 import pytest
 
+
+def _free_port():
+    import socket
+    with socket.socket() as so:
+        so.bind(("127.0.0.1", 0))
+        return so.getsockname()[1]
+
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GPT = ("--num-layers 2 --hidden-size 64 --num-attention-heads 4 --seq-length 32 --max-position-embeddings 32 --micro-batch-size 2 "
        "--global-batch-size 4 --lr 1e-3 --lr-decay-style cosine --lr-warmup-iters 2 --weight-decay 0.1 --log-interval 1 "
@@ -18,7 +26,7 @@ GPT = ("--num-layers 2 --hidden-size 64 --num-attention-heads 4 --seq-length 32 
 def _run(script, argv, nproc=0, timeout=600):
     if nproc:
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
-               "--master-port", str(29900 + os.getpid() % 90), os.path.join(ROOT, "entrypoints", script), *argv]
+               "--master-port", str(_free_port()), os.path.join(ROOT, "entrypoints", script), *argv]
     else:
         cmd = [sys.executable, os.path.join(ROOT, "entrypoints", script), *argv]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env={**os.environ, "OMP_NUM_THREADS": "2"})
