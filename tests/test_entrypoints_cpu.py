@@ -205,3 +205,36 @@ def test_gpt_sample_based_training_with_batch_size_rampup():
     assert sizes[0] == 2 and sizes[-1] == 4 and sorted(sizes) == sizes
     assert all(consumed[i] - (consumed[i - 1] if i else 0) == sizes[i] for i in range(len(rows)))
     assert int(rows[0][1]) == len(rows) and consumed[-1] <= 20
+
+
+def test_checkpoint_util_reshards_tp_and_pp(tmp_path):
+    """tools/checkpoint_util.py: a TP=2 checkpoint (SwiGLU + GQA, so the packed layouts are exercised) evaluated under TP=2, then
+    re-sharded to TP=1 and to TP=1 x PP=2 - the validation loss of the re-loaded model is the same in every layout"""
+    def val_loss(out):
+        m = re.search(r"validation loss at the end of training for val data \| lm loss value: ([0-9.E+-]+)", out)
+        assert m, out[-3000:]
+        return float(m.group(1))
+
+    ck = str(tmp_path / "tp2")
+    argv = [a for a in GPT]
+    argv[argv.index("--train-iters") + 1] = "2"
+    argv[argv.index("--num-layers") + 1] = "4"
+    argv += ["--swiglu", "--group-query-attention", "--num-query-groups", "2", "--hidden-dropout", "0", "--attention-dropout", "0"]
+    _run("pretrain_gpt.py", argv + ["--tensor-model-parallel-size", "2", "--save", ck, "--save-interval", "2"], nproc=2)
+    ev = ["--finetune", "--skip-train"]
+    ref = val_loss(_run("pretrain_gpt.py", argv + ["--tensor-model-parallel-size", "2", "--load", ck] + ev, nproc=2))
+    tool = os.path.join(ROOT, "tools", "checkpoint_util.py")
+    for tp, pp in ((1, 1), (1, 2)):
+        out_dir = str(tmp_path / f"tp{tp}pp{pp}")
+        r = subprocess.run([sys.executable, tool, "--load-dir", ck, "--save-dir", out_dir, "--target-tensor-parallel-size", str(tp),
+                            "--target-pipeline-parallel-size", str(pp)], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stdout + r.stderr
+        extra = ["--tensor-model-parallel-size", str(tp), "--pipeline-model-parallel-size", str(pp), "--load", out_dir] + ev
+        got = val_loss(_run("pretrain_gpt.py", argv + extra, nproc=tp * pp if tp * pp > 1 else 0))
+        assert abs(got - ref) < 2e-4 * max(1.0, abs(ref)), (tp, pp, got, ref)
+    # and back up: TP=1 -> TP=2 x PP=2 file layout
+    out_dir = str(tmp_path / "tp2pp2")
+    r = subprocess.run([sys.executable, tool, "--load-dir", str(tmp_path / "tp1pp1"), "--save-dir", out_dir, "--target-tensor-parallel-size", "2",
+                        "--target-pipeline-parallel-size", "2"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert sorted(os.listdir(os.path.join(out_dir, "iter_0000002"))) == ["mp_rank_00_000", "mp_rank_00_001", "mp_rank_01_000", "mp_rank_01_001"]
