@@ -52,7 +52,7 @@ class _HeadUnit(nn.Module):
 class Zero3CausalLM(nn.Module):
     def __init__(self, model: nn.Module, *, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0,
                  gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None,
-                 offload_optimizer="none"):
+                 offload_optimizer="none", gradient_checkpointing=False):
         super().__init__()
         self.model = model
         self.tied = getattr(model, "lm_head", None) is None
@@ -62,7 +62,8 @@ class Zero3CausalLM(nn.Module):
         names = ["embed"] + [f"layers.{i}" for i in range(len(model.layers))] + ["head"]
         self.engine = Zero3Engine(units, names, group, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, max_grad_norm=max_grad_norm,
                                   gradient_accumulation_steps=gradient_accumulation_steps, persistence_threshold=persistence_threshold,
-                                  comm_backend=comm_backend, offload_param=offload_param, offload_optimizer=offload_optimizer)
+                                  comm_backend=comm_backend, offload_param=offload_param, offload_optimizer=offload_optimizer,
+                                  checkpoint_units=range(1, len(units) - 1) if gradient_checkpointing else ())      # the decoder layers
         self._units = units
 
     def forward(self, input_ids, attention_mask=None, labels=None):
@@ -134,7 +135,8 @@ class Trainer:
                                     max_grad_norm=self.ds.gradient_clipping, gradient_accumulation_steps=self.ds.gradient_accumulation_steps,
                                     persistence_threshold=self.ds.zero.stage3_param_persistence_threshold, comm_backend=a.comm_backend,
                                     offload_param=self.ds.zero.offload_param_device,
-                                    offload_optimizer=self.ds.zero.offload_optimizer_device)
+                                    offload_optimizer=self.ds.zero.offload_optimizer_device,
+                                    gradient_checkpointing=bool(a.gradient_checkpointing))
         eng = self.zmodel.engine
         sp = self.ds.scheduler_params
         if self.ds.scheduler_type == "WarmupDecayLR":

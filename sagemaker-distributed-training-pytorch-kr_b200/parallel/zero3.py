@@ -74,12 +74,48 @@ class _PreBackwardFn(torch.autograd.Function):
         return g, None, None
 
 
+class _CheckpointFn(torch.autograd.Function):
+    """activation checkpointing of one gather unit (HF `--gradient_checkpointing`): the forward runs without a graph and
+    keeps only the unit's input; the backward - which autograd runs between `_PreBackwardFn.backward` (unit re-gathered)
+    and `_FetchFn.backward` (unit's gradients reduced) - re-runs the unit with a graph and back-propagates through it, so
+    parameter gradients land exactly where the un-checkpointed path puts them."""
+
+    @staticmethod
+    def forward(ctx, x, fn, args):
+        ctx.fn, ctx.args = fn, args
+        ctx.save_for_backward(x)
+        ctx.cpu_rng = torch.get_rng_state()
+        ctx.cuda_rng = torch.cuda.get_rng_state() if x.is_cuda else None
+        with torch.no_grad():
+            return fn(x, *args)
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        now_cpu = torch.get_rng_state()
+        now_cuda = torch.cuda.get_rng_state() if x.is_cuda else None
+        torch.set_rng_state(ctx.cpu_rng)
+        if ctx.cuda_rng is not None:
+            torch.cuda.set_rng_state(ctx.cuda_rng)
+        try:
+            xin = x.detach().requires_grad_(True)
+            with torch.enable_grad():
+                y = ctx.fn(xin, *ctx.args)
+            torch.autograd.backward(y, g)
+        finally:
+            torch.set_rng_state(now_cpu)
+            if now_cuda is not None:
+                torch.cuda.set_rng_state(now_cuda)
+        return xin.grad, None, None
+
+
 class Zero3Engine:
     def __init__(self, units: Sequence[nn.Module], unit_names: Optional[Sequence[str]] = None, group=None, *, lr: float = 1e-5,
                  betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, max_grad_norm: float = 1.0,
                  gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
                  offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None,
-                 offload_optimizer: str = "none"):
+                 offload_optimizer: str = "none", checkpoint_units: Sequence[int] = ()):
+        self.checkpoint_units = set(checkpoint_units)      # unit indices whose activations are recomputed in backward
         self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         self.world = dist.get_world_size(self.group) if self.group is not None else 1
         self.rank = dist.get_rank(self.group) if self.group is not None else 0
@@ -242,7 +278,10 @@ class Zero3Engine:
             self._ensure(idx, forward=True)           # first unit (token ids in): reduced when loss.backward() returns
             if torch.is_grad_enabled():
                 self._reduce_at_end.append(idx)
-        y = fn(x, *args)
+        if idx in self.checkpoint_units and torch.is_grad_enabled() and torch.is_tensor(x) and x.requires_grad:
+            y = _CheckpointFn.apply(x, fn, args)
+        else:
+            y = fn(x, *args)
         if torch.is_grad_enabled() and y.requires_grad:
             y = _PreBackwardFn.apply(y, self, idx)
         return y

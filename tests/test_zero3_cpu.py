@@ -11,11 +11,11 @@ def _build(seed=0):
     return LlamaForCausalLM(LlamaConfig.tiny())
 
 
-def _run_engine(rank, world, steps, ga, clip, offload_optimizer="none"):
+def _run_engine(rank, world, steps, ga, clip, offload_optimizer="none", gradient_checkpointing=False):
     from b200dist.engine.hf_trainer import Zero3CausalLM
     model = _build()
     zm = Zero3CausalLM(model, lr=1e-2, weight_decay=0.0, max_grad_norm=clip, gradient_accumulation_steps=ga, persistence_threshold=200, comm_backend="nccl",
-                       offload_optimizer=offload_optimizer)
+                       offload_optimizer=offload_optimizer, gradient_checkpointing=gradient_checkpointing)
     torch.manual_seed(3)
     data = torch.randint(0, 512, (steps * ga, world, 2, 16))
     losses = []
@@ -118,3 +118,13 @@ def test_cpu_adam_kernel_matches_torch_both_code_paths():
         w.grad, w2.grad = gr.clone(), gr.clone()
         a.step(); b.step()
     assert torch.allclose(w, w2, rtol=1e-5, atol=1e-6)
+
+
+def test_zero3_gradient_checkpointing_is_loss_identical():
+    """--gradient_checkpointing True: decoder layers keep only their input and are re-run in backward"""
+    world, steps, ga, clip = 2, 3, 2, 1.0
+    plain = run_distributed(_run_engine, world, steps, ga, clip)
+    ckpt = run_distributed(_run_engine, world, steps, ga, clip, "none", True)
+    for r in range(world):
+        assert plain[r][0] == ckpt[r][0], (plain[r][0], ckpt[r][0])
+        assert plain[r][1] == ckpt[r][1]
