@@ -1,0 +1,54 @@
+"""Cross-load with the REAL Hugging Face implementation: a checkpoint written by `transformers` loads
+into our LLaMA / OPT models and produces the same logits, and a checkpoint written by ckpt/hf.py loads into `transformers`
+(sharded safetensors + index, and the legacy .bin format)."""
+import os
+
+import pytest
+import torch
+
+transformers = pytest.importorskip("transformers")
+
+
+def _hf_tiny(kind):
+    if kind == "llama":
+        cfg = transformers.LlamaConfig(vocab_size=512, hidden_size=128, intermediate_size=352, num_hidden_layers=2, num_attention_heads=2,
+                                       num_key_value_heads=2, max_position_embeddings=512, rms_norm_eps=1e-6, tie_word_embeddings=False,
+                                       attention_bias=False, mlp_bias=False)
+        return transformers.LlamaForCausalLM(cfg)
+    cfg = transformers.OPTConfig(vocab_size=512, hidden_size=128, ffn_dim=512, num_hidden_layers=2, num_attention_heads=2, max_position_embeddings=512,
+                                 word_embed_proj_dim=128, do_layer_norm_before=True, dropout=0.0, attention_dropout=0.0, activation_function="relu")
+    return transformers.OPTForCausalLM(cfg)
+
+
+@pytest.mark.parametrize("kind", ["llama", "opt"])
+def test_checkpoint_written_by_transformers_loads_here(tmp_path, kind):
+    from b200dist.ckpt import hf as hf_ckpt
+    torch.manual_seed(0)
+    ref = _hf_tiny(kind).eval()
+    ref.save_pretrained(str(tmp_path), safe_serialization=True, max_shard_size="300KB")        # forces several shards + index.json
+    assert any(f.endswith(".index.json") for f in os.listdir(tmp_path))
+    ours = hf_ckpt.load_pretrained(str(tmp_path)).eval()
+    ids = torch.randint(2, 512, (2, 24))
+    with torch.no_grad():
+        want = ref(input_ids=ids).logits
+        got = ours(ids)
+    assert got.shape == want.shape and torch.allclose(got, want, atol=2e-4, rtol=1e-3), (got - want).abs().max()
+    # loss with label shifting and ignore_index, as the Trainer uses it
+    labels = ids.clone()
+    labels[:, :5] = -100
+    with torch.no_grad():
+        assert abs(float(ours(ids, labels=labels)) - float(ref(input_ids=ids, labels=labels).loss)) < 2e-4
+
+
+@pytest.mark.parametrize("kind,safe", [("llama", True), ("llama", False), ("opt", True)])
+def test_checkpoint_written_here_loads_in_transformers(tmp_path, kind, safe):
+    from b200dist.ckpt import hf as hf_ckpt
+    from b200dist.models.llama import build_causal_lm
+    torch.manual_seed(1)
+    ours = build_causal_lm(f"{kind}-tiny").eval()
+    hf_ckpt.save_pretrained(ours, str(tmp_path), max_shard_size=300 * 1024, safe_serialization=safe)
+    cls = transformers.LlamaForCausalLM if kind == "llama" else transformers.OPTForCausalLM
+    ref = cls.from_pretrained(str(tmp_path), torch_dtype=torch.float32).eval()
+    ids = torch.randint(2, 512, (2, 24))
+    with torch.no_grad():
+        assert torch.allclose(ours(ids), ref(input_ids=ids).logits, atol=2e-4, rtol=1e-3)
