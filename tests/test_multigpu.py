@@ -49,3 +49,27 @@ def test_gpt_tp2_sp_native_matches_nccl_backend():
         curves[backend] = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
     assert len(curves["native"]) == 4 == len(curves["nccl"])
     assert max(abs(a - b) for a, b in zip(curves["native"], curves["nccl"])) < 5e-2, curves
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+@pytest.mark.xfail(reason="batched pipeline p2p (fused send+recv groups) has not run on NCCL yet: it was written after the round's last GPU session", strict=False)
+def test_gpt_pp2_batched_p2p_matches_single_gpu():
+    """PP=2 (1F1B, then interleaved) over NCCL with the batched p2p transport against the same model on one GPU; every
+    launch sits inside `timeout`, and B2_HANG_DUMP_S prints where each rank waits if it stalls"""
+    import re
+    base = ["--num-layers", "4", "--hidden-size", "256", "--num-attention-heads", "4", "--seq-length", "256", "--max-position-embeddings", "256",
+            "--micro-batch-size", "2", "--global-batch-size", "8", "--lr", "1e-3", "--train-iters", "3", "--lr-decay-iters", "3", "--lr-warmup-iters", "1",
+            "--log-interval", "1", "--eval-interval", "100", "--eval-iters", "0", "--tokenizer-type", "NullTokenizer", "--vocab-size", "1023", "--mock-data",
+            "--bf16", "--seed", "11", "--hidden-dropout", "0", "--attention-dropout", "0"]
+    os.environ["B2_HANG_DUMP_S"] = "60"
+    try:
+        rc, out = _torchrun("entrypoints/pretrain_gpt.py", 1, 240, *base)
+        assert rc == 0, out[-4000:]
+        ref = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+        for extra in ([], ["--num-layers-per-virtual-pipeline-stage", "1"]):
+            rc, out = _torchrun("entrypoints/pretrain_gpt.py", 2, 240, *base, "--pipeline-model-parallel-size", "2", *extra)
+            assert rc == 0, out[-6000:]
+            got = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+            assert len(got) == 3 == len(ref) and max(abs(a - b) for a, b in zip(got, ref)) < 5e-2, (extra, got, ref)
+    finally:
+        os.environ.pop("B2_HANG_DUMP_S", None)
