@@ -94,6 +94,45 @@ def _base_type(tp):
     return tp
 
 
+# transformers.TrainingArguments fields (4.28 .. 5.x) that this trainer does not act on: accepted on the command line with a
+# one-line notice, so launch lines written for the reference keep working.  Fields the trainer honours are
+# dataclass fields above; anything in neither set is an error, as in transformers.
+HF_ACCEPTED_IGNORED = frozenset("""
+overwrite_output_dir do_train do_eval do_predict prediction_loss_only per_gpu_train_batch_size per_gpu_eval_batch_size eval_accumulation_steps
+eval_delay torch_empty_cache_steps lr_scheduler_kwargs log_level log_level_replica log_on_each_node logging_dir logging_strategy
+logging_first_step logging_nan_inf_filter save_safetensors save_on_each_node save_only_model restore_callback_states_from_checkpoint no_cuda
+use_cpu use_mps_device data_seed jit_mode_eval use_ipex bf16_full_eval fp16_full_eval fp16_opt_level half_precision_backend ddp_backend
+tpu_num_cores tpu_metrics_debug debug dataloader_drop_last dataloader_prefetch_factor dataloader_pin_memory dataloader_persistent_workers past_index
+run_name disable_tqdm remove_unused_columns label_names load_best_model_at_end metric_for_best_model greater_is_better ignore_data_skip sharded_ddp
+fsdp fsdp_min_num_params fsdp_config fsdp_transformer_layer_cls_to_wrap accelerator_config parallelism_config label_smoothing_factor optim_args
+adafactor group_by_length length_column_name ddp_find_unused_parameters ddp_bucket_cap_mb ddp_broadcast_buffers ddp_timeout skip_memory_metrics
+use_legacy_prediction_loop push_to_hub hub_model_id hub_strategy hub_token hub_private_repo hub_always_push hub_revision gradient_checkpointing_kwargs
+include_inputs_for_metrics include_for_metrics eval_do_concat_batches eval_use_gather_object batch_eval_metrics eval_on_start auto_find_batch_size
+full_determinism torchdynamo ray_scope torch_compile torch_compile_backend torch_compile_mode dispatch_batches split_batches include_tokens_per_second
+include_num_input_tokens_seen neftune_noise_alpha optim_target_modules use_liger_kernel liger_kernel_config use_cache average_tokens_across_devices
+project trackio_space_id enable_jit_checkpoint train_sampling_strategy mp_parameters xpu_backend push_to_hub_model_id push_to_hub_organization
+push_to_hub_token
+""".split())
+HF_ALIASES = {"eval_strategy": "evaluation_strategy"}          # renamed upstream in 4.41
+
+
+def _strip_accepted(remaining):
+    """drop `--known_hf_flag [value]` pairs from the unparsed tokens; returns (still unknown, names that were ignored)"""
+    out, ignored, i = [], [], 0
+    while i < len(remaining):
+        tok = remaining[i]
+        name = tok[2:].split("=", 1)[0] if tok.startswith("--") else None
+        if name in HF_ACCEPTED_IGNORED:
+            ignored.append(name)
+            i += 1
+            if "=" not in tok and i < len(remaining) and not remaining[i].startswith("--"):
+                i += 1
+            continue
+        out.append(tok)
+        i += 1
+    return out, ignored
+
+
 class HfArgumentParser(argparse.ArgumentParser):
     """dataclass types -> argparse; parse_args_into_dataclasses() returns one instance per type."""
 
@@ -114,7 +153,18 @@ class HfArgumentParser(argparse.ArgumentParser):
                 self.add_argument("--" + f.name, **kwargs)
 
     def parse_args_into_dataclasses(self, args=None, return_remaining_strings=False) -> Tuple[Any, ...]:
+        import sys as _sys
+        args = list(_sys.argv[1:] if args is None else args)
+        for i, tok in enumerate(args):                       # renamed upstream flags
+            if tok.startswith("--"):
+                name, eq, val = tok[2:].partition("=")
+                if name in HF_ALIASES:
+                    args[i] = "--" + HF_ALIASES[name] + (eq + val if eq else "")
         ns, remaining = self.parse_known_args(args)
+        remaining, ignored = _strip_accepted(remaining)
+        if ignored:
+            print("[args] accepted for transformers.TrainingArguments compatibility, not used by this trainer: " + ", ".join(sorted(set(ignored))),
+                  flush=True)
         outs = []
         for dt in self.dataclass_types:
             keys = {f.name for f in fields(dt) if f.init}

@@ -187,3 +187,15 @@ def test_trainer_checkpoint_rotation_resume_and_evaluation(tmp_path):
     tr.train()
     evals = [h["eval_loss"] for h in tr.state.log_history if "eval_loss" in h]
     assert len(evals) == 2 and evals[1] < evals[0]
+
+
+def test_hf_training_arguments_compatibility_flags(capsys):
+    """flags of transformers.TrainingArguments that the trainer does not act on are accepted with a notice; unknown flags fail"""
+    p = HfArgumentParser((ModelArguments, DataArguments, TrainingArguments))
+    m, d, t = p.parse_args_into_dataclasses(["--model_name_or_path", "x", "--output_dir", "o", "--logging_dir", "l", "--fsdp", "full_shard auto_wrap",
+                                             "--eval_strategy", "steps", "--overwrite_output_dir", "--do_train", "True", "--report_to", "none",
+                                             "--gradient_checkpointing", "True", "--ddp_timeout=1800"])
+    assert t.evaluation_strategy == "steps" and t.gradient_checkpointing is True and t.output_dir == "o"
+    assert "fsdp" in capsys.readouterr().out
+    with pytest.raises(ValueError):
+        p.parse_args_into_dataclasses(["--output_dir", "o", "--definitely_not_a_flag", "1"])
