@@ -37,7 +37,8 @@ class _StaticIter:
 
 def supported(args, model=None) -> bool:
     ok = (torch.cuda.is_available() and args.pipeline_model_parallel_size == 1 and args.hidden_dropout == 0.0
-          and args.attention_dropout == 0.0 and not args.fp16 and args.recompute_granularity is None)
+          and args.attention_dropout == 0.0 and not args.fp16 and args.recompute_granularity is None
+          and getattr(args, "num_experts", None) is None)          # Switch-MLP routing (`nonzero`) is data dependent: not capturable
     if ok and args.tensor_model_parallel_size > 1:
         # tensor-parallel collectives inside the captured region must be the fabric kernels (plain launches);
         # NCCL calls are kept out of captured graphs
