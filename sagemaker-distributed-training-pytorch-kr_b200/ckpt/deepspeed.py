@@ -50,6 +50,11 @@ def save_zero3_checkpoint(engine, out_dir: str, step: int, ds_config: Dict, sche
     if engine.rank == 0:
         with open(os.path.join(out_dir, "latest"), "w") as f:
             f.write(tag)
+        # DeepSpeed leaves its consolidation script next to the shards; so do we (tools/zero_to_fp32.py, torch only)
+        src = os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "tools", "zero_to_fp32.py")
+        if os.path.isfile(src):
+            import shutil
+            shutil.copyfile(src, os.path.join(out_dir, "zero_to_fp32.py"))
     if dist.is_initialized():
         dist.barrier()
 

@@ -138,6 +138,12 @@ def test_train_entrypoint_zero3_shards_and_consolidation(tmp_path):
     model = build_causal_lm("opt-tiny")
     n_model = sum(p.numel() for p in model.parameters())
     assert sum(v.numel() for v in sd.values()) == n_model
+    # the consolidation script dropped next to the shards works stand-alone (torch only)
+    assert (out / "zero_to_fp32.py").exists()
+    r = subprocess.run([sys.executable, str(out / "zero_to_fp32.py"), str(out), str(out / "fp32.pt"), "--strip-unit-prefix"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    flat = torch.load(out / "fp32.pt")
+    assert sum(v.numel() for v in flat.values()) == n_model and all(torch.equal(flat[k], v) for k, v in hf_ckpt.rename_unit_keys(sd).items() if k in flat)
     assert all(v.dtype == torch.float32 and torch.isfinite(v).all() for v in sd.values())
 
 
