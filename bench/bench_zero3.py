@@ -30,6 +30,9 @@ def main():
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (0 = the model's own)")
     ap.add_argument("--comm-backend", default="native")
     ap.add_argument("--clip", type=float, default=1.0)
+    ap.add_argument("--offload-optimizer", default="none", choices=["none", "cpu"], help="cpu = the reference's -original config (C++ CPU Adam)")
+    ap.add_argument("--offload-param", default="none", choices=["none", "cpu"], help="cpu = the reference's shipped config (pinned host shards)")
+    ap.add_argument("--gradient-checkpointing", action="store_true")
     a = ap.parse_args()
     real_fd = os.dup(1)
     os.dup2(2, 1)
@@ -45,7 +48,8 @@ def main():
     model = build_causal_lm(a.model, device=dev, dtype=torch.bfloat16, **kw)
     nparams = sum(p.numel() for p in model.parameters())
     zm = Zero3CausalLM(model, lr=2e-5, weight_decay=0.0, max_grad_norm=a.clip, gradient_accumulation_steps=1,
-                       persistence_threshold=10 * model.config.hidden_size, comm_backend=a.comm_backend if world > 1 else "nccl")
+                       persistence_threshold=10 * model.config.hidden_size, comm_backend=a.comm_backend if world > 1 else "nccl",
+                       offload_optimizer=a.offload_optimizer, offload_param=a.offload_param, gradient_checkpointing=a.gradient_checkpointing)
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     V = model.config.vocab_size
@@ -88,7 +92,8 @@ def main():
                "dtype": "bf16", "data": "synthetic instruction batches (pinned host -> device every step), random-init weights",
                "config": {"model": a.model, "layers": model.config.num_hidden_layers, "params": nparams, "seq_len": a.seq, "micro_batch_per_gpu": a.micro_batch,
                           "global_batch": world * a.micro_batch, "parallelism": f"zero3 dp{world}", "comm_backend": a.comm_backend,
-                          "fabric": zm.engine.fabric is not None, "optimizer": f"AdamW fp32 partitioned, clip {a.clip}"},
+                          "fabric": zm.engine.fabric is not None, "optimizer": f"AdamW fp32 partitioned, clip {a.clip}",
+                          "offload_optimizer": a.offload_optimizer, "offload_param": a.offload_param, "gradient_checkpointing": a.gradient_checkpointing},
                "model_tflops_per_gpu": flops / (ms / 1e3) / 1e12, "peak_mem_gib": mem, "setup_s": setup_s, "last_loss": last_loss,
                "gpu_launches": N.launches() - l0}
         os.write(real_fd, (json.dumps(out) + "\n").encode())
