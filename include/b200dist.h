@@ -216,6 +216,25 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * BatchNorm2d over NCHW tensors (csrc/batchnorm.cu), fp32 / bf16 / fp16 activations, fp32 statistics.  Training forward =
+ * b2_bn_reduce (sums[C][2] double, zero on entry) -> [all-reduce sums and count over the group for SyncBatchNorm] ->
+ * b2_bn_finalize (mean, rstd, scale, shift, running statistics) -> b2_bn_apply (y = x*scale + shift, optional ReLU).
+ * Inference = b2_bn_eval_coeffs -> b2_bn_apply.  Backward = b2_bn_bwd_reduce (sum g, sum g*xhat) -> [all-reduce] ->
+ * b2_bn_bwd_apply; dbeta[c] = sums[c][0], dgamma[c] = sums[c][1].
+ * replaces: cuDNN / ATen batch_norm (torchvision ResNet under pytorch_oxford_ddp.py), apex syncbn (E25).
+ */
+int b2_bn_reduce(const void* x, double* sums, int N, int C, int HW, int dtype, void* stream);
+int b2_bn_finalize(const double* sums, double count, const float* gamma, const float* beta, float eps, float momentum,
+                   float* running_mean, float* running_var, float* mean, float* rstd, float* scale, float* shift, int C, void* stream);
+int b2_bn_eval_coeffs(const float* running_mean, const float* running_var, const float* gamma, const float* beta, float eps,
+                      float* scale, float* shift, int C, void* stream);
+int b2_bn_apply(const void* x, const float* scale, const float* shift, void* y, int N, int C, int HW, int relu, int dtype, void* stream);
+int b2_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, double* sums, int N, int C,
+                     int HW, int relu, int dtype, void* stream);
+int b2_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const float* gamma,
+                    const double* sums, double count, void* dx, int N, int C, int HW, int relu, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * fp32 kernels of the MNIST CNN (csrc/conv.cu): valid stride-1 convolution with K x K filters (K <= 5), NCHW.
  * fwd: y = relu?(conv(x, w) + bias).  bwd: g = dy * (yact > 0) when relu (yact = the forward output); dx (may be NULL),
  * dw / db (may be NULL; accumulate != 0 adds into them).  One input / gradient image must fit in shared memory

@@ -42,6 +42,9 @@ def args_fn(argv=None):
     p.add_argument("--channels-last", type=_strbool, default=True)
     p.add_argument("--seed", type=int, default=1, metavar="S", help="random seed (default: 1)")
     p.add_argument("-p", "--print-freq", default=10, type=int, metavar="N", help="print frequency (default: 10)")
+    p.add_argument("--native-bn", action="store_true", default=False,
+                   help="models with BatchNorm2d (resnet*): run it on the kernels of csrc/batchnorm.cu instead of cuDNN / ATen")
+    p.add_argument("--sync-bn", action="store_true", default=False, help="with --native-bn: batch statistics over all ranks (SyncBatchNorm)")
     p.add_argument("--model_name", type=str, default="resnet50")
     p.add_argument("--height", type=int, default=224)
     p.add_argument("--width", type=int, default=224)
@@ -119,6 +122,9 @@ def train(args):
     dev = args.device
     dtype = torch.bfloat16 if (args.bf16 and dev.type == "cuda") else torch.float32
     model = util.torch_model(args.model_name, num_classes=args.num_classes, pretrained=not args.no_pretrained, local_rank=args.local_rank).to(dev)
+    if args.native_bn:
+        from ..ops.functional import convert_batchnorm
+        model = convert_batchnorm(model, dist.group.WORLD if (args.sync_bn and dist.is_initialized() and args.world_size > 1) else None)
     criterion = _Criterion()
     if dtype != torch.float32:
         from ..optim.mixed import MixedPrecisionOptimizer

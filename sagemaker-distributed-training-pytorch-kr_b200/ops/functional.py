@@ -521,3 +521,68 @@ class _LogSoftmax(torch.autograd.Function):
 def log_softmax_small(x):
     """log_softmax over dim 1 for <= 32 classes (one warp per row)"""
     return _LogSoftmax.apply(x)
+
+
+# =============================================================================================
+# BatchNorm2d / SyncBatchNorm with optional fused ReLU (csrc/batchnorm.cu)
+# =============================================================================================
+class _BatchNormTrain(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, eps, momentum, relu, group):
+        y, mean, rstd, count = N.bn_train_fwd(x, gamma, beta, running_mean, running_var, eps, momentum, relu, group)
+        ctx.save_for_backward(x, y if relu else x, gamma, mean, rstd)
+        ctx.meta = (count, relu, group, gamma is not None, beta is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, gamma, mean, rstd = ctx.saved_tensors
+        count, relu, group, has_g, has_b = ctx.meta
+        dx, dgamma, dbeta = N.bn_bwd(dy, x, y if relu else None, gamma, mean, rstd, count, relu, group)
+        return (dx, dgamma.to(gamma.dtype) if has_g else None, dbeta.to(gamma.dtype if has_g else dbeta.dtype) if has_b else None,
+                None, None, None, None, None, None)
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, training: bool, momentum: float = 0.1, eps: float = 1e-5, relu: bool = False, group=None):
+    if training:
+        return _BatchNormTrain.apply(x, gamma, beta, running_mean, running_var, float(eps), float(momentum), bool(relu), group)
+    return N.bn_eval_fwd(x, gamma, beta, running_mean, running_var, eps, relu)
+
+
+class BatchNorm2d(torch.nn.BatchNorm2d):
+    """Drop-in nn.BatchNorm2d (same parameters / buffers / state_dict) on the native kernels; `process_group` turns it into a
+    SyncBatchNorm (statistics over the group); `fuse_relu` applies ReLU in the same pass."""
+
+    def __init__(self, num_features, eps=1e-5, momentum=0.1, affine=True, track_running_stats=True, process_group=None, fuse_relu=False, **kw):
+        super().__init__(num_features, eps, momentum, affine, track_running_stats, **kw)
+        self.process_group, self.fuse_relu = process_group, fuse_relu
+
+    def forward(self, x):
+        if x.dim() != 4 or (x.is_cuda and not x.is_contiguous()):
+            y = super().forward(x)
+            return torch.relu(y) if self.fuse_relu else y
+        use_batch = self.training or not self.track_running_stats
+        if use_batch and self.track_running_stats and self.num_batches_tracked is not None:
+            self.num_batches_tracked.add_(1)
+        mom = self.momentum if self.momentum is not None else 1.0 / max(1, int(self.num_batches_tracked)) if use_batch else 0.0
+        return batch_norm(x, self.weight, self.bias, self.running_mean if self.track_running_stats else None,
+                          self.running_var if self.track_running_stats else None, use_batch, mom, self.eps, self.fuse_relu,
+                          self.process_group if use_batch else None)
+
+
+def convert_batchnorm(module: torch.nn.Module, process_group=None) -> torch.nn.Module:
+    """replace every nn.BatchNorm2d in `module` by the native one, keeping parameters and buffers (the way
+    torch.nn.SyncBatchNorm.convert_sync_batchnorm does); with `process_group` the layers synchronise their statistics"""
+    out = module
+    if isinstance(module, torch.nn.BatchNorm2d) and not isinstance(module, BatchNorm2d):
+        out = BatchNorm2d(module.num_features, module.eps, module.momentum, module.affine, module.track_running_stats, process_group)
+        if module.affine:
+            out.weight, out.bias = module.weight, module.bias
+        if module.track_running_stats:
+            out.running_mean, out.running_var, out.num_batches_tracked = module.running_mean, module.running_var, module.num_batches_tracked
+        out.train(module.training)
+    for name, child in list(module.named_children()):
+        new = convert_batchnorm(child, process_group)
+        if new is not child:
+            setattr(out, name, new)
+    return out

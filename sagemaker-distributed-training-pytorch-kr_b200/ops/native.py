@@ -64,6 +64,12 @@ _SIGS = {
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
     "b2_attn_bwd": [c_p] * 10 + [c_i, c_i, c_i, c_i] + [c_ll] * 21 + [c_f, c_i, c_f, c_ull, c_p],
+    "b2_bn_reduce": [c_p, c_p, c_i, c_i, c_i, c_i, c_p],
+    "b2_bn_finalize": [c_p, ctypes.c_double, c_p, c_p, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_p],
+    "b2_bn_eval_coeffs": [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i, c_p],
+    "b2_bn_apply": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_bn_bwd_reduce": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_bn_bwd_apply": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, ctypes.c_double, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_conv2d_fwd": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_conv2d_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_maxpool2_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_p],
@@ -707,6 +713,97 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
         _call("b2_cast_rows_from_fp32", _p(dq), dq.stride(2), _p(dq32), S * B * Hh, D, _dt(dq), _st())
     else:
         dq.copy_(dq32)
+
+
+# =============================================================================================
+# BatchNorm2d (NCHW), optional fused ReLU, optional cross-rank statistics (SyncBatchNorm)     (csrc/batchnorm.cu)
+# =============================================================================================
+def _bn_sync(t: torch.Tensor, group):
+    if group is not None and torch.distributed.is_initialized() and torch.distributed.get_world_size(group) > 1:
+        torch.distributed.all_reduce(t, group=group)
+    return t
+
+
+def bn_train_fwd(x, gamma, beta, running_mean, running_var, eps: float, momentum: float, relu: bool = False, group=None):
+    """x [N, C, H, W] -> (y, mean[C], rstd[C], count): batch statistics over N*H*W (x the group's ranks when `group` is given);
+    running statistics are updated in place like torch (unbiased variance)."""
+    Nn, C, H, W = x.shape
+    HW = H * W
+    if not x.is_cuda:
+        xf = x.float()
+        sums = torch.stack([xf.sum((0, 2, 3)), (xf * xf).sum((0, 2, 3))], 1).double()
+        cnt = torch.tensor([float(Nn * HW)], dtype=torch.float64)
+        _bn_sync(sums, group); _bn_sync(cnt, group)
+        count = float(cnt)
+        mean = (sums[:, 0] / count)
+        var = (sums[:, 1] / count - mean * mean).clamp_(min=0)
+        rstd = torch.rsqrt(var.float() + eps)
+        mean = mean.float()
+        g = gamma.float() if gamma is not None else torch.ones(C)
+        b = beta.float() if beta is not None else torch.zeros(C)
+        y = (xf - mean[None, :, None, None]) * (rstd * g)[None, :, None, None] + b[None, :, None, None]
+        if relu:
+            y = torch.relu(y)
+        if running_mean is not None:
+            unb = var.float() * (count / (count - 1)) if count > 1 else var.float()
+            running_mean.mul_(1 - momentum).add_(momentum * mean)
+            running_var.mul_(1 - momentum).add_(momentum * unb)
+        return y.to(x.dtype), mean, rstd, count
+    x = x.contiguous()
+    dev = x.device
+    sums = torch.zeros(C, 2, dtype=torch.float64, device=dev)
+    _call("b2_bn_reduce", _p(x), _p(sums), Nn, C, HW, _dt(x), _st())
+    count = float(Nn * HW)
+    if group is not None and torch.distributed.is_initialized() and torch.distributed.get_world_size(group) > 1:
+        _bn_sync(sums, group)
+        count *= torch.distributed.get_world_size(group)          # equal per-rank batch shapes (DDP)
+    mean, rstd = torch.empty(C, dtype=torch.float32, device=dev), torch.empty(C, dtype=torch.float32, device=dev)
+    scale, shift = torch.empty_like(mean), torch.empty_like(mean)
+    _call("b2_bn_finalize", _p(sums), count, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var), _p(mean), _p(rstd),
+          _p(scale), _p(shift), C, _st())
+    y = torch.empty_like(x)
+    _call("b2_bn_apply", _p(x), _p(scale), _p(shift), _p(y), Nn, C, HW, int(relu), _dt(x), _st())
+    return y, mean, rstd, count
+
+
+def bn_eval_fwd(x, gamma, beta, running_mean, running_var, eps: float, relu: bool = False):
+    Nn, C, H, W = x.shape
+    if not x.is_cuda:
+        y = F.batch_norm(x.float(), running_mean, running_var, gamma.float() if gamma is not None else None, beta.float() if beta is not None else None,
+                         False, 0.0, eps)
+        return (torch.relu(y) if relu else y).to(x.dtype)
+    x = x.contiguous()
+    scale, shift = torch.empty(C, dtype=torch.float32, device=x.device), torch.empty(C, dtype=torch.float32, device=x.device)
+    _call("b2_bn_eval_coeffs", _p(running_mean), _p(running_var), _p(gamma), _p(beta), float(eps), _p(scale), _p(shift), C, _st())
+    y = torch.empty_like(x)
+    _call("b2_bn_apply", _p(x), _p(scale), _p(shift), _p(y), Nn, C, H * W, int(relu), _dt(x), _st())
+    return y
+
+
+def bn_bwd(dy, x, y, gamma, mean, rstd, count: float, relu: bool = False, group=None):
+    """-> (dx, dgamma[C] fp32, dbeta[C] fp32); `count` = elements per channel over the whole group (from bn_train_fwd)"""
+    Nn, C, H, W = x.shape
+    HW = H * W
+    if not x.is_cuda:
+        g = dy.float()
+        if relu:
+            g = g * (y > 0)
+        xhat = (x.float() - mean[None, :, None, None]) * rstd[None, :, None, None]
+        sums = torch.stack([g.sum((0, 2, 3)), (g * xhat).sum((0, 2, 3))], 1).double()
+        dbeta, dgamma = sums[:, 0].float().clone(), sums[:, 1].float().clone()      # local sums: DDP averages parameter gradients
+        _bn_sync(sums, group)
+        mg, mgx = (sums[:, 0] / count).float(), (sums[:, 1] / count).float()
+        gm = gamma.float() if gamma is not None else torch.ones(C)
+        dx = (gm * rstd)[None, :, None, None] * (g - mg[None, :, None, None] - xhat * mgx[None, :, None, None])
+        return dx.to(x.dtype), dgamma, dbeta
+    dy, x = dy.contiguous(), x.contiguous()
+    sums = torch.zeros(C, 2, dtype=torch.float64, device=x.device)
+    _call("b2_bn_bwd_reduce", _p(dy), _p(x), _p(y), _p(mean), _p(rstd), _p(sums), Nn, C, HW, int(relu), _dt(x), _st())
+    dbeta, dgamma = sums[:, 0].float(), sums[:, 1].float()
+    _bn_sync(sums, group)
+    dx = torch.empty_like(x)
+    _call("b2_bn_bwd_apply", _p(dy), _p(x), _p(y), _p(mean), _p(rstd), _p(gamma), _p(sums), float(count), _p(dx), Nn, C, HW, int(relu), _dt(x), _st())
+    return dx, dgamma, dbeta
 
 
 # =============================================================================================

@@ -131,8 +131,47 @@ def unfused_attention_layer():
         assert torch.isfinite(ga).all() and (ga - gb).norm() <= 0.08 * ga.norm() + 1e-4, n
 
 
+def batchnorm_kernels():
+    from b200dist.ops import functional as Fn
+    from b200dist.ops import native as N
+    torch.manual_seed(0)
+    for dtype, tol in ((torch.float32, 2e-5), (torch.bfloat16, 3e-2)):
+        for shape in ((64, 64, 56, 56), (8, 2048, 7, 7), (3, 5, 7, 9)):
+            x = (torch.randn(*shape, device="cuda") * 2 + 3).to(dtype).requires_grad_()
+            ref = torch.nn.BatchNorm2d(shape[1]).cuda()
+            with torch.no_grad():
+                ref.weight.uniform_(0.5, 1.5); ref.bias.normal_()
+            for relu in (False, True):
+                ours = Fn.BatchNorm2d(shape[1], fuse_relu=relu).cuda()
+                ours.load_state_dict(ref.state_dict())
+                ref_t = torch.nn.BatchNorm2d(shape[1]).cuda()
+                ref_t.load_state_dict(ref.state_dict())
+                before = N.launches()
+                y = ours(x)
+                r = ref_t(x.float())
+                r = torch.relu(r) if relu else r
+                assert N.launches() >= before + 3, "native batch-norm kernels did not run"
+                assert torch.allclose(y.float(), r, atol=tol, rtol=tol), (dtype, shape, relu, (y.float() - r).abs().max())
+                g = torch.randn_like(r)
+                got = torch.autograd.grad(y, (x, ours.weight, ours.bias), g.to(dtype))
+                want = torch.autograd.grad(r, (x, ref_t.weight, ref_t.bias), g)
+                scale = max(1.0, float(want[1].abs().max()))
+                assert torch.allclose(got[0].float(), want[0].float(), atol=tol * 2, rtol=tol * 2), (dtype, shape, relu, "dx")
+                assert torch.allclose(got[1].float(), want[1], atol=tol * 4 * scale, rtol=tol * 4), (dtype, shape, relu, "dgamma")
+                assert torch.allclose(got[2].float(), want[2], atol=tol * 4 * scale, rtol=tol * 4), (dtype, shape, relu, "dbeta")
+                assert torch.allclose(ours.running_mean, ref_t.running_mean, atol=tol) and torch.allclose(ours.running_var, ref_t.running_var, atol=tol * 4, rtol=tol * 4)
+                ours.eval(); ref_t.eval()
+                re = ref_t(x.detach().float())
+                assert torch.allclose(ours(x.detach()).float(), torch.relu(re) if relu else re, atol=tol, rtol=tol)
+    import torchvision
+    net = torchvision.models.resnet50(weights=None, num_classes=37).cuda()
+    twin = Fn.convert_batchnorm(__import__("copy").deepcopy(net))
+    img = torch.randn(8, 3, 128, 128, device="cuda")
+    assert torch.allclose(net(img), twin(img), atol=2e-3, rtol=2e-3)
+
+
 CHECKS = {"conv_kernels": conv_kernels, "pool_and_log_softmax": pool_and_log_softmax, "mnist_step": mnist_step,
-          "softmax_kernels": softmax_kernels, "unfused_attention_layer": unfused_attention_layer}
+          "batchnorm_kernels": batchnorm_kernels, "softmax_kernels": softmax_kernels, "unfused_attention_layer": unfused_attention_layer}
 
 if __name__ == "__main__":
     CHECKS[sys.argv[1]]()

@@ -238,3 +238,17 @@ def test_checkpoint_util_reshards_tp_and_pp(tmp_path):
                         "--target-pipeline-parallel-size", "2"], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert sorted(os.listdir(os.path.join(out_dir, "iter_0000002"))) == ["mp_rank_00_000", "mp_rank_00_001", "mp_rank_01_000", "mp_rank_01_001"]
+
+
+def test_oxford_resnet_script_with_native_sync_batchnorm(tmp_path):
+    """the script's default model family (--model_name resnet*, pytorch_oxford_ddp.py:123) with the head really replaced
+    and every BatchNorm2d on the native SyncBatchNorm path"""
+    out = _run("pytorch_oxford_ddp.py", ["--model_name", "resnet18", "--num-classes", "37", "--num-epochs", "1", "--batch-size", "4",
+                                         "--test-batch-size", "2", "--synthetic", "--synthetic-train-size", "16", "--synthetic-val-size", "4",
+                                         "--height", "64", "--width", "64", "--backend", "gloo", "--no-pretrained", "--num-workers", "0",
+                                         "--model-dir", str(tmp_path), "--print-freq", "1", "--max-steps", "2", "--native-bn", "--sync-bn"], nproc=2, timeout=900)
+    assert "Test_Prec@1=" in out and "Test_Loss=" in out
+    import torch
+    ck = torch.load(os.path.join(tmp_path, "checkpoint.pth"), map_location="cpu", weights_only=False)
+    keys = list(ck["state_dict"])
+    assert any(k.endswith("bn1.running_mean") for k in keys) and any(k.endswith("fc.weight") and ck["state_dict"][k].shape[0] == 37 for k in keys)

@@ -108,3 +108,80 @@ def test_mnist_native_op_layer_matches_aten_on_cpu():
     m2.load_state_dict(m1.state_dict())
     img = torch.randn(4, 1, 28, 28)
     assert torch.allclose(m1(img), m2(img), atol=1e-5)
+
+
+def test_native_batchnorm_matches_torch_and_converts_resnet():
+    import torch
+    from b200dist.ops import functional as Fn
+    torch.manual_seed(0)
+    x = (torch.randn(6, 5, 7, 9) * 2 + 3).requires_grad_()
+    ref = torch.nn.BatchNorm2d(5)
+    ours = Fn.BatchNorm2d(5)
+    with torch.no_grad():
+        ref.weight.uniform_(0.5, 1.5); ref.bias.normal_()
+    ours.load_state_dict(ref.state_dict())
+    for step in range(2):                      # two training steps: running statistics evolve identically
+        y, r = ours(x), ref(x)
+        assert torch.allclose(y, r, atol=1e-5)
+        g = torch.randn_like(r)
+        got = torch.autograd.grad(y, (x, ours.weight, ours.bias), g)
+        want = torch.autograd.grad(r, (x, ref.weight, ref.bias), g)
+        for a, b in zip(got, want):
+            assert torch.allclose(a, b, atol=2e-5), (a - b).abs().max()
+    assert torch.allclose(ours.running_mean, ref.running_mean, atol=1e-6) and torch.allclose(ours.running_var, ref.running_var, atol=1e-5)
+    assert int(ours.num_batches_tracked) == 2
+    ours.eval(); ref.eval()
+    assert torch.allclose(ours(x), ref(x), atol=1e-5)
+    # fused ReLU, forward and backward
+    fr = Fn.BatchNorm2d(5, fuse_relu=True)
+    fr.load_state_dict(ref.state_dict()); fr.train(); ref.train()
+    y, r = fr(x), torch.relu(ref(x))
+    assert torch.allclose(y, r, atol=1e-5)
+    g = torch.randn_like(r)
+    for a, b in zip(torch.autograd.grad(y, (x, fr.weight, fr.bias), g), torch.autograd.grad(r, (x, ref.weight, ref.bias), g)):
+        assert torch.allclose(a, b, atol=2e-5)
+    # torchvision ResNet with every BatchNorm2d swapped for the native module
+    import torchvision
+    net = torchvision.models.resnet18(weights=None, num_classes=7)
+    twin = Fn.convert_batchnorm(__import__("copy").deepcopy(net))
+    assert sum(isinstance(m, Fn.BatchNorm2d) for m in twin.modules()) == 20 and list(twin.state_dict()) == list(net.state_dict())
+    img = torch.randn(4, 3, 64, 64)
+    a, b = net(img), twin(img)
+    assert torch.allclose(a, b, atol=1e-4)
+    a.square().mean().backward(); b.square().mean().backward()
+    ga, gb = net.layer2[0].conv1.weight.grad, twin.layer2[0].conv1.weight.grad
+    assert torch.allclose(ga, gb, atol=1e-5, rtol=1e-3)
+
+
+def _syncbn_worker(rank, world):
+    import torch
+    from b200dist.ops import functional as Fn
+    torch.manual_seed(0)
+    x = torch.randn(8, 3, 5, 5) * 1.5 + 0.5
+    g = torch.randn(8, 3, 5, 5)
+    bn = Fn.BatchNorm2d(3, process_group=torch.distributed.group.WORLD)
+    with torch.no_grad():
+        bn.weight.copy_(torch.tensor([0.5, 1.0, 1.5])); bn.bias.copy_(torch.tensor([0.1, -0.2, 0.3]))
+    xs = x.chunk(world)[rank].clone().requires_grad_()
+    y = bn(xs)
+    dx, dw, db = torch.autograd.grad(y, (xs, bn.weight, bn.bias), g.chunk(world)[rank])
+    return y.detach(), dx, dw, db, bn.running_mean.clone(), bn.running_var.clone()
+
+
+def test_sync_batchnorm_over_two_ranks_equals_full_batch():
+    import numpy as np
+    import torch
+    from tests._dist_util import run_distributed
+    outs = run_distributed(_syncbn_worker, 2)
+    torch.manual_seed(0)
+    x = (torch.randn(8, 3, 5, 5) * 1.5 + 0.5).requires_grad_()
+    g = torch.randn(8, 3, 5, 5)
+    ref = torch.nn.BatchNorm2d(3)
+    with torch.no_grad():
+        ref.weight.copy_(torch.tensor([0.5, 1.0, 1.5])); ref.bias.copy_(torch.tensor([0.1, -0.2, 0.3]))
+    y = ref(x)
+    dx, dw, db = torch.autograd.grad(y, (x, ref.weight, ref.bias), g)
+    assert np.allclose(np.concatenate([outs[0][0], outs[1][0]]), y.detach().numpy(), atol=1e-5)
+    assert np.allclose(np.concatenate([outs[0][1], outs[1][1]]), dx.numpy(), atol=2e-5)
+    assert np.allclose(outs[0][2] + outs[1][2], dw.numpy(), atol=2e-5) and np.allclose(outs[0][3] + outs[1][3], db.numpy(), atol=2e-5)
+    assert np.allclose(outs[0][4], ref.running_mean.numpy(), atol=1e-6) and np.allclose(outs[1][5], ref.running_var.numpy(), atol=1e-5)

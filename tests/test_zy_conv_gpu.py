@@ -17,6 +17,6 @@ def _run(name):
     assert r.returncode == 0 and ("ok " + name) in r.stdout, (r.stdout[-2000:] + r.stderr[-4000:])
 
 
-@pytest.mark.parametrize("name", ["conv_kernels", "pool_and_log_softmax", "mnist_step"])
+@pytest.mark.parametrize("name", ["conv_kernels", "pool_and_log_softmax", "mnist_step", "batchnorm_kernels"])
 def test_conv_tier(name):
     _run(name)
