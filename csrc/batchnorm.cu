@@ -50,14 +50,15 @@ B2_DEVICE void block_sum2_atomic(float a, float b, double* out2) {
 }
 
 // element e of channel c, e in [0, N*HW): n = e / HW, p = e % HW  ->  offset (n*C + c)*HW + p
-template <typename T>
+// I = unsigned (tensors below 2^31 elements: 32-bit index arithmetic, no software 64-bit division) or long long
+template <typename T, typename I>
 __global__ void __launch_bounds__(kThreads) bn_reduce_kernel(const T* __restrict__ x, double* __restrict__ sums, int N, int C, int HW) {
-  const int c = blockIdx.x;
-  const long long M = static_cast<long long>(N) * HW;
+  const I c = blockIdx.x;
+  const I M = static_cast<I>(N) * static_cast<I>(HW);
   float s = 0.f, q = 0.f;
-  for (long long e = static_cast<long long>(blockIdx.y) * kThreads + threadIdx.x; e < M; e += static_cast<long long>(gridDim.y) * kThreads) {
-    const long long n = e / HW, p = e % HW;
-    const float v = ldf<T>(x, (n * C + c) * HW + p);
+  for (I e = static_cast<I>(blockIdx.y) * kThreads + threadIdx.x; e < M; e += static_cast<I>(gridDim.y) * kThreads) {
+    const I n = e / static_cast<I>(HW), p = e - n * static_cast<I>(HW);
+    const float v = ldf<T>(x, static_cast<long long>((n * static_cast<I>(C) + c) * static_cast<I>(HW) + p));
     s += v;
     q = fmaf(v, v, q);
   }
@@ -96,27 +97,29 @@ __global__ void bn_eval_coeffs_kernel(const float* __restrict__ running_mean, co
   shift[c] = b - running_mean[c] * g * r;
 }
 
-template <typename T>
+template <typename T, typename I>
 __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                                                            T* __restrict__ y, long long total, int C, int HW, int relu) {
-  for (long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * kThreads) {
-    const int c = static_cast<int>((i / HW) % C);
+                                                            T* __restrict__ y, long long total_ll, int C, int HW, int relu) {
+  const I total = static_cast<I>(total_ll);
+  for (I i = static_cast<I>(blockIdx.x) * kThreads + threadIdx.x; i < total; i += static_cast<I>(gridDim.x) * kThreads) {
+    const int c = static_cast<int>((i / static_cast<I>(HW)) % static_cast<I>(C));
     float v = fmaf(ldf<T>(x, i), scale[c], shift[c]);
     if (relu) v = fmaxf(v, 0.f);
     stf<T>(y, i, v);
   }
 }
 
-template <typename T>
+template <typename T, typename I>
 __global__ void __launch_bounds__(kThreads) bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ y,
                                                                  const float* __restrict__ mean, const float* __restrict__ rstd,
                                                                  double* __restrict__ sums, int N, int C, int HW, int relu) {
-  const int c = blockIdx.x;
-  const long long M = static_cast<long long>(N) * HW;
+  const I c = blockIdx.x;
+  const I M = static_cast<I>(N) * static_cast<I>(HW);
   const float mu = mean[c], r = rstd[c];
   float sg = 0.f, sgx = 0.f;
-  for (long long e = static_cast<long long>(blockIdx.y) * kThreads + threadIdx.x; e < M; e += static_cast<long long>(gridDim.y) * kThreads) {
-    const long long n = e / HW, p = e % HW, off = (n * C + c) * HW + p;
+  for (I e = static_cast<I>(blockIdx.y) * kThreads + threadIdx.x; e < M; e += static_cast<I>(gridDim.y) * kThreads) {
+    const I n = e / static_cast<I>(HW), p = e - n * static_cast<I>(HW);
+    const long long off = static_cast<long long>((n * static_cast<I>(C) + c) * static_cast<I>(HW) + p);
     float g = ldf<T>(dy, off);
     if (relu && !(ldf<T>(y, off) > 0.f)) g = 0.f;
     sg += g;
@@ -126,17 +129,18 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_reduce_kernel(const T* __rest
 }
 
 // sums: GLOBAL sum(g), sum(g*xhat) over `count` elements per channel
-template <typename T>
+template <typename T, typename I>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ y,
                                                                 const float* __restrict__ mean, const float* __restrict__ rstd,
-                                                                const float* __restrict__ gamma, const double* __restrict__ sums, double count,
-                                                                T* __restrict__ dx, long long total, int C, int HW, int relu) {
-  for (long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * kThreads) {
-    const int c = static_cast<int>((i / HW) % C);
+                                                                const float* __restrict__ gamma, const double* __restrict__ sums, double inv_count,
+                                                                T* __restrict__ dx, long long total_ll, int C, int HW, int relu) {
+  const I total = static_cast<I>(total_ll);
+  for (I i = static_cast<I>(blockIdx.x) * kThreads + threadIdx.x; i < total; i += static_cast<I>(gridDim.x) * kThreads) {
+    const int c = static_cast<int>((i / static_cast<I>(HW)) % static_cast<I>(C));
     float g = ldf<T>(dy, i);
     if (relu && !(ldf<T>(y, i) > 0.f)) g = 0.f;
     const float r = rstd[c], xhat = (ldf<T>(x, i) - mean[c]) * r;
-    const float mg = static_cast<float>(sums[2 * c] / count), mgx = static_cast<float>(sums[2 * c + 1] / count);
+    const float mg = static_cast<float>(sums[2 * c] * inv_count), mgx = static_cast<float>(sums[2 * c + 1] * inv_count);
     stf<T>(dx, i, (gamma ? gamma[c] : 1.f) * r * (g - mg - xhat * mgx));
   }
 }
@@ -160,11 +164,20 @@ int grid1d(long long n) {
   return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
-#define BN_DISPATCH(dtype, CALL)                                                     \
-  do {                                                                               \
-    if ((dtype) == B2_DTYPE_BF16) { using T = __nv_bfloat16; CALL; }                 \
-    else if ((dtype) == B2_DTYPE_FP16) { using T = __half; CALL; }                   \
-    else { using T = float; CALL; }                                                  \
+// T from the dtype code, I = unsigned when every element offset (plus one grid stride) fits in 32 bits
+#define BN_DISPATCH(dtype, total, CALL)                                                              \
+  do {                                                                                               \
+    if ((total) < (1LL << 31)) {                                                                     \
+      using I = unsigned;                                                                            \
+      if ((dtype) == B2_DTYPE_BF16) { using T = __nv_bfloat16; CALL; }                               \
+      else if ((dtype) == B2_DTYPE_FP16) { using T = __half; CALL; }                                 \
+      else { using T = float; CALL; }                                                                \
+    } else {                                                                                         \
+      using I = long long;                                                                           \
+      if ((dtype) == B2_DTYPE_BF16) { using T = __nv_bfloat16; CALL; }                               \
+      else if ((dtype) == B2_DTYPE_FP16) { using T = __half; CALL; }                                 \
+      else { using T = float; CALL; }                                                                \
+    }                                                                                                \
   } while (0)
 
 }  // namespace
@@ -173,7 +186,8 @@ int grid1d(long long n) {
 extern "C" int b2_bn_reduce(const void* x, double* sums, int N, int C, int HW, int dtype, void* stream) {
   if (N <= 0 || C <= 0 || HW <= 0) { b2host::set_error("bn_reduce: empty tensor"); return -1; }
   dim3 grid(C, splits_for(C, static_cast<long long>(N) * HW));
-  BN_DISPATCH(dtype, (bn_reduce_kernel<T><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(x), sums, N, C, HW)));
+  BN_DISPATCH(dtype, static_cast<long long>(N) * C * HW,
+              (bn_reduce_kernel<T, I><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(x), sums, N, C, HW)));
   return check("bn_reduce");
 }
 
@@ -198,8 +212,8 @@ extern "C" int b2_bn_eval_coeffs(const float* running_mean, const float* running
 extern "C" int b2_bn_apply(const void* x, const float* scale, const float* shift, void* y, int N, int C, int HW, int relu, int dtype, void* stream) {
   const long long total = static_cast<long long>(N) * C * HW;
   if (total <= 0) { b2host::set_error("bn_apply: empty tensor"); return -1; }
-  BN_DISPATCH(dtype, (bn_apply_kernel<T><<<grid1d(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const T*>(x), scale, shift,
-                                                                                                          static_cast<T*>(y), total, C, HW, relu)));
+  BN_DISPATCH(dtype, total, (bn_apply_kernel<T, I><<<grid1d(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+                                static_cast<const T*>(x), scale, shift, static_cast<T*>(y), total, C, HW, relu)));
   return check("bn_apply");
 }
 
@@ -209,7 +223,7 @@ extern "C" int b2_bn_bwd_reduce(const void* dy, const void* x, const void* y, co
   if (N <= 0 || C <= 0 || HW <= 0) { b2host::set_error("bn_bwd_reduce: empty tensor"); return -1; }
   if (relu && !y) { b2host::set_error("bn_bwd_reduce: fused ReLU backward needs the forward output"); return -1; }
   dim3 grid(C, splits_for(C, static_cast<long long>(N) * HW));
-  BN_DISPATCH(dtype, (bn_bwd_reduce_kernel<T><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+  BN_DISPATCH(dtype, static_cast<long long>(N) * C * HW, (bn_bwd_reduce_kernel<T, I><<<grid, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
                          static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, sums, N, C, HW, relu)));
   return check("bn_bwd_reduce");
 }
@@ -219,8 +233,8 @@ extern "C" int b2_bn_bwd_apply(const void* dy, const void* x, const void* y, con
                                const double* sums, double count, void* dx, int N, int C, int HW, int relu, int dtype, void* stream) {
   const long long total = static_cast<long long>(N) * C * HW;
   if (total <= 0 || count <= 0) { b2host::set_error("bn_bwd_apply: empty tensor"); return -1; }
-  BN_DISPATCH(dtype, (bn_bwd_apply_kernel<T><<<grid1d(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-                         static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, gamma, sums, count,
+  BN_DISPATCH(dtype, total, (bn_bwd_apply_kernel<T, I><<<grid1d(total), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+                         static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, gamma, sums, 1.0 / count,
                          static_cast<T*>(dx), total, C, HW, relu)));
   return check("bn_bwd_apply");
 }
