@@ -144,6 +144,9 @@ class Trainer:
                                            sp.get("warmup_num_steps", 0), sp.get("warmup_type", "log"))
         elif self.ds.scheduler_type == "WarmupLR":
             self.scheduler = WarmupLR(eng, sp.get("warmup_min_lr", 0), sp.get("warmup_max_lr", a.learning_rate), sp.get("warmup_num_steps", 0))
+        elif self.ds.scheduler_type is None:      # no scheduler block in the JSON: the HF Trainer's own schedule (--lr_scheduler_type)
+            from ..optim.schedulers import HFScheduler
+            self.scheduler = HFScheduler(eng, a.lr_scheduler_type, a.get_warmup_steps(total), total)
         if self.rank == 0:
             n_persist = eng.num_persistent
             print(f"[zero3] partitioned {eng.total_params() - n_persist} parameters in {len(eng.units)} units over {self.world} ranks; "

@@ -150,3 +150,50 @@ class WarmupDecayLR(WarmupLR):
         if self.last_batch_iteration < self.warmup_num_steps:
             return super()._gamma()
         return max(0.0, (self.total_num_steps - self.last_batch_iteration) / max(1.0, self.total_num_steps - self.warmup_num_steps))
+
+
+class HFScheduler:
+    """transformers.get_scheduler(name, optimizer, num_warmup_steps, num_training_steps) for the case the DeepSpeed JSON has no
+    `scheduler` block (then the HF Trainer builds its own from --lr_scheduler_type / --warmup_ratio / --warmup_steps):
+    linear | cosine | constant | constant_with_warmup | polynomial (power 1 = linear) | inverse_sqrt.  Multiplies the base
+    learning rate of every param group; step() after each optimizer step."""
+
+    def __init__(self, optimizer, name: str, num_warmup_steps: int, num_training_steps: int, last_step: int = 0):
+        assert name in ("linear", "cosine", "constant", "constant_with_warmup", "polynomial", "inverse_sqrt"), f"unsupported lr_scheduler_type {name}"
+        self.optimizer, self.name, self.warmup, self.total = optimizer, name, int(num_warmup_steps), int(num_training_steps)
+        self.base_lrs = [g["lr"] for g in optimizer.param_groups]
+        self.last_step = last_step
+        self._apply()
+
+    def factor(self, step: int) -> float:
+        w, t = self.warmup, self.total
+        if self.name != "constant" and step < w:
+            return step / max(1, w)
+        if self.name in ("constant", "constant_with_warmup"):
+            return 1.0
+        if self.name in ("linear", "polynomial"):
+            return max(0.0, (t - step) / max(1, t - w))
+        if self.name == "cosine":
+            prog = (step - w) / max(1, t - w)
+            return max(0.0, 0.5 * (1.0 + math.cos(math.pi * prog)))
+        shift = max(w, 1)                                   # inverse_sqrt
+        return math.sqrt(shift) / math.sqrt(max(step, shift))
+
+    def _apply(self):
+        f = self.factor(self.last_step)
+        for g, b in zip(self.optimizer.param_groups, self.base_lrs):
+            g["lr"] = b * f
+
+    def step(self):
+        self.last_step += 1
+        self._apply()
+
+    def get_last_lr(self):
+        return [g["lr"] for g in self.optimizer.param_groups]
+
+    def state_dict(self):
+        return {"last_step": self.last_step, "base_lrs": list(self.base_lrs)}
+
+    def load_state_dict(self, sd):
+        self.last_step, self.base_lrs = sd["last_step"], list(sd["base_lrs"])
+        self._apply()

@@ -319,3 +319,22 @@ def test_microbatch_calculators_constant_and_rampup():
     mb.build_num_microbatches_calculator(a)
     with pytest.raises(AssertionError):
         mb.update_num_microbatches(0, consistency_check=True)
+
+
+def test_hf_schedulers_match_transformers():
+    transformers = pytest.importorskip("transformers")
+    from b200dist.optim.schedulers import HFScheduler
+    for name in ("linear", "cosine", "constant", "constant_with_warmup", "inverse_sqrt"):
+        w = torch.nn.Parameter(torch.zeros(1))
+        ref_opt = torch.optim.SGD([w], lr=0.5)
+        ref = transformers.get_scheduler(name, ref_opt, num_warmup_steps=3, num_training_steps=20)
+        class Opt:
+            param_groups = [{"lr": 0.5}]
+        ours = HFScheduler(Opt, name, 3, 20)
+        for _ in range(20):
+            assert abs(Opt.param_groups[0]["lr"] - ref_opt.param_groups[0]["lr"]) < 1e-9, (name, ours.last_step)
+            ref_opt.step(); ref.step(); ours.step()
+        sd = ours.state_dict()
+        again = HFScheduler(Opt, name, 3, 20)
+        again.load_state_dict(sd)
+        assert again.get_last_lr() == ours.get_last_lr()
