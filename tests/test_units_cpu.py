@@ -338,3 +338,25 @@ def test_hf_schedulers_match_transformers():
         again = HFScheduler(Opt, name, 3, 20)
         again.load_state_dict(sd)
         assert again.get_last_lr() == ours.get_last_lr()
+
+
+def test_prepare_oxford_pet_split(tmp_path):
+    import importlib.util
+    import os
+    from PIL import Image
+    spec = importlib.util.spec_from_file_location("prep", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "prepare_oxford_pet.py"))
+    prep = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(prep)
+    src = tmp_path / "images"
+    src.mkdir()
+    for cls in ("Abyssinian", "american_bulldog"):
+        for i in range(1, 21):
+            Image.new("RGB", (8, 8), (i * 10, 0, 0)).save(src / f"{cls}_{i}.jpg")
+    (src / "american_bulldog_99.jpg").write_bytes(b"not a jpeg")                 # undecodable -> dropped
+    r = prep.prepare(str(src), str(tmp_path / "out"))
+    assert r["classes"] == 2 and r["train"] == 15 + 16 and r["val"] == 1 + 2 and r["test"] == 3 + 2 and "american_bulldog_99.jpg" in r["dropped"]
+    assert "Abyssinian_5.jpg" in r["dropped"]                                    # the notebook's list of corrupt files
+    assert sorted(os.listdir(tmp_path / "out")) == ["test", "train", "val"]
+    assert sorted(os.listdir(tmp_path / "out" / "train")) == ["Abyssinian", "american_bulldog"]
+    again = prep.prepare(str(src), str(tmp_path / "out2"))
+    assert sorted(os.listdir(tmp_path / "out" / "val" / "Abyssinian")) == sorted(os.listdir(tmp_path / "out2" / "val" / "Abyssinian"))
