@@ -718,6 +718,10 @@ def attn_bwd(q, k, v, o, dout, lse, scale: float, causal: bool, dq: torch.Tensor
 # =============================================================================================
 # BatchNorm2d (NCHW), optional fused ReLU, optional cross-rank statistics (SyncBatchNorm)     (csrc/batchnorm.cu)
 # =============================================================================================
+def _f32(t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    return t if (t is None or t.dtype == torch.float32) else t.float()
+
+
 def _bn_sync(t: torch.Tensor, group):
     if group is not None and torch.distributed.is_initialized() and torch.distributed.get_world_size(group) > 1:
         torch.distributed.all_reduce(t, group=group)
@@ -751,6 +755,10 @@ def bn_train_fwd(x, gamma, beta, running_mean, running_var, eps: float, momentum
         return y.to(x.dtype), mean, rstd, count
     x = x.contiguous()
     dev = x.device
+    # the kernels take fp32 parameters and statistics; a model cast to bf16 carries 16-bit ones: widen, and narrow back after
+    rm_in, rv_in = running_mean, running_var
+    gamma, beta = _f32(gamma), _f32(beta)
+    running_mean, running_var = _f32(running_mean), _f32(running_var)
     sums = torch.zeros(C, 2, dtype=torch.float64, device=dev)
     _call("b2_bn_reduce", _p(x), _p(sums), Nn, C, HW, _dt(x), _st())
     count = float(Nn * HW)
@@ -761,6 +769,8 @@ def bn_train_fwd(x, gamma, beta, running_mean, running_var, eps: float, momentum
     scale, shift = torch.empty_like(mean), torch.empty_like(mean)
     _call("b2_bn_finalize", _p(sums), count, _p(gamma), _p(beta), float(eps), float(momentum), _p(running_mean), _p(running_var), _p(mean), _p(rstd),
           _p(scale), _p(shift), C, _st())
+    if rm_in is not None and rm_in.dtype != torch.float32:
+        rm_in.copy_(running_mean); rv_in.copy_(running_var)
     y = torch.empty_like(x)
     _call("b2_bn_apply", _p(x), _p(scale), _p(shift), _p(y), Nn, C, HW, int(relu), _dt(x), _st())
     return y, mean, rstd, count
@@ -773,6 +783,7 @@ def bn_eval_fwd(x, gamma, beta, running_mean, running_var, eps: float, relu: boo
                          False, 0.0, eps)
         return (torch.relu(y) if relu else y).to(x.dtype)
     x = x.contiguous()
+    gamma, beta, running_mean, running_var = _f32(gamma), _f32(beta), _f32(running_mean), _f32(running_var)
     scale, shift = torch.empty(C, dtype=torch.float32, device=x.device), torch.empty(C, dtype=torch.float32, device=x.device)
     _call("b2_bn_eval_coeffs", _p(running_mean), _p(running_var), _p(gamma), _p(beta), float(eps), _p(scale), _p(shift), C, _st())
     y = torch.empty_like(x)
@@ -797,6 +808,9 @@ def bn_bwd(dy, x, y, gamma, mean, rstd, count: float, relu: bool = False, group=
         dx = (gm * rstd)[None, :, None, None] * (g - mg[None, :, None, None] - xhat * mgx[None, :, None, None])
         return dx.to(x.dtype), dgamma, dbeta
     dy, x = dy.contiguous(), x.contiguous()
+    gamma = _f32(gamma)
+    if dy.dtype != x.dtype:
+        dy = dy.to(x.dtype)
     sums = torch.zeros(C, 2, dtype=torch.float64, device=x.device)
     _call("b2_bn_bwd_reduce", _p(dy), _p(x), _p(y), _p(mean), _p(rstd), _p(sums), Nn, C, HW, int(relu), _dt(x), _st())
     dbeta, dgamma = sums[:, 0].float(), sums[:, 1].float()
@@ -814,6 +828,7 @@ def conv2d_fwd(x, w, bias, relu: bool):
     if not x.is_cuda:
         y = F.conv2d(x, w, bias)
         return F.relu(y) if relu else y
+    assert x.dtype == torch.float32 and w.dtype == torch.float32 and (bias is None or bias.dtype == torch.float32), "conv kernels are fp32"
     x, w = x.contiguous(), w.contiguous()
     B, Cin, H, W = x.shape
     Cout, _, K, _ = w.shape
@@ -829,6 +844,7 @@ def conv2d_bwd(dy, y, x, w, relu: bool, need_dx: bool, has_bias: bool = True):
         dx = torch.nn.grad.conv2d_input(x.shape, w, g) if need_dx else None
         dw = torch.nn.grad.conv2d_weight(x, w.shape, g)
         return dx, dw, (g.sum((0, 2, 3)) if has_bias else None)
+    assert dy.dtype == torch.float32 and x.dtype == torch.float32 and w.dtype == torch.float32, "conv kernels are fp32"
     dy, y, x, w = dy.contiguous(), y.contiguous(), x.contiguous(), w.contiguous()
     B, Cin, H, W = x.shape
     Cout, _, K, _ = w.shape
@@ -846,6 +862,7 @@ def maxpool2_fwd(x):
         y, ind = F.max_pool2d(x.reshape(-1, 1, H, W), 2, return_indices=True)
         iy, ix = (ind // W) % 2, (ind % W) % 2
         return y.view(*x.shape[:-2], H // 2, W // 2), (iy * 2 + ix).to(torch.uint8).view(*x.shape[:-2], H // 2, W // 2)
+    assert x.dtype == torch.float32, "max-pool kernel is fp32"
     x = x.contiguous()
     y = torch.empty((*x.shape[:-2], H // 2, W // 2), dtype=torch.float32, device=x.device)
     idx = torch.empty(y.shape, dtype=torch.uint8, device=x.device)
@@ -873,6 +890,7 @@ def log_softmax_nll_fwd(x, target=None):
     if not x.is_cuda:
         lp = F.log_softmax(x, dim=1)
         return lp, (F.nll_loss(lp, target, reduction="none") if target is not None else None)
+    assert x.dtype == torch.float32 and x.dim() == 2 and x.shape[1] <= 32, "log-softmax kernel: fp32, at most 32 classes"
     x = x.contiguous()
     lp = torch.empty_like(x)
     loss = torch.empty(x.shape[0], dtype=torch.float32, device=x.device) if target is not None else None
