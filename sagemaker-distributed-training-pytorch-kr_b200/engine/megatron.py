@@ -514,7 +514,7 @@ def train(forward_step_func, model, optimizer, opt_param_scheduler, train_data_i
             print_rank_0("exiting program at iteration {}".format(iteration))
             sys.exit()
         inj = args.inject_fault or os.environ.get("B200DIST_INJECT_FAULT")     # "rank:iteration" test hook
-        if inj:
+        if inj and os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") == "0":      # only in the first attempt of an elastic job
             r, it = (int(x) for x in inj.split(":"))
             if (dist.get_rank() if dist.is_initialized() else 0) == r and iteration == it:
                 raise RuntimeError(f"injected fault on rank {r} at iteration {it}")

@@ -98,8 +98,15 @@ def init_distributed(backend: str = "nccl", timeout_minutes: int = 10) -> RankIn
         kw = {}
         if be == "nccl" and torch.cuda.is_available():
             kw["device_id"] = torch.device("cuda", torch.cuda.current_device())
-        dist.init_process_group(backend=be, rank=info.rank, world_size=info.world_size,
-                                timeout=datetime.timedelta(minutes=timeout_minutes), **kw)
+        timeout = datetime.timedelta(minutes=timeout_minutes)
+        restart = os.environ.get("TORCHELASTIC_RESTART_COUNT")
+        if restart is not None and os.environ.get("TORCHELASTIC_USE_AGENT_STORE") == "True":
+            # elastic restarts (`torchrun --max-restarts N`): the agent's TCPStore outlives the failed attempt, and with it the
+            # transport addresses the dead workers published; a rank of the new attempt that reads them before its peers have
+            # overwritten them connects to a closed port.  Give every attempt its own key space.
+            store = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]), info.world_size, False, timeout)
+            kw["store"] = dist.PrefixStore(f"/b200dist/attempt_{restart}", store)
+        dist.init_process_group(backend=be, rank=info.rank, world_size=info.world_size, timeout=timeout, **kw)
     return info
 
 

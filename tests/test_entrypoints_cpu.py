@@ -252,3 +252,21 @@ def test_oxford_resnet_script_with_native_sync_batchnorm(tmp_path):
     ck = torch.load(os.path.join(tmp_path, "checkpoint.pth"), map_location="cpu", weights_only=False)
     keys = list(ck["state_dict"])
     assert any(k.endswith("bn1.running_mean") for k in keys) and any(k.endswith("fc.weight") and ck["state_dict"][k].shape[0] == 37 for k in keys)
+
+
+def test_elastic_restart_resumes_from_latest_checkpoint(tmp_path):
+    """the recovery story of SURVEY 5.3 end to end: `torchrun --max-restarts 1`; rank 0 dies after iteration 4 of the first attempt,
+    the agent restarts the workers, `--load` picks up the iteration-3 checkpoint and the job finishes with the uninterrupted losses"""
+    ck = str(tmp_path / "ck")
+    full = _losses(_run("pretrain_gpt.py", GPT, nproc=2))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--standalone", "--local-addr", "127.0.0.1", "--nnodes=1", "--nproc-per-node=2", "--max-restarts=1",
+           os.path.join(ROOT, "entrypoints", "pretrain_gpt.py"), *GPT, "--save", ck, "--save-interval", "3",
+           "--load", ck, "--inject-fault", "0:4"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env={**os.environ, "OMP_NUM_THREADS": "2"})
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-4000:]
+    assert "injected fault on rank 0 at iteration 4" in out
+    its = [int(m.group(1)) for m in re.finditer(r"iteration\s+(\d+)/", out)]
+    assert its[:4] == [1, 2, 3, 4] and its[-3:] == [4, 5, 6]                 # second attempt starts after the iteration-3 checkpoint
+    final = {int(m.group(1)): m.group(2) for m in re.finditer(r"iteration\s+(\d+)/\s*\d+ \|.*?lm loss: ([0-9.E+-]+)", out)}
+    assert all(final[i] == full[i] for i in (4, 5, 6)), (final, full)          # same 2-rank job, uninterrupted
