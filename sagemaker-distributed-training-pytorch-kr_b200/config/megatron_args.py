@@ -428,6 +428,25 @@ def validate_args(args, defaults: Optional[dict] = None, verbose: bool = True):
         args.position_embedding_type = "rope"
     if not args.add_position_embedding and args.position_embedding_type != "rope":
         raise ArgumentError("--no-position-embedding is deprecated, use --position-embedding-type")
+    # ---- flags that parse but do not change what runs here: say so once instead of silently ignoring them
+    inert = []
+    if args.fp32_residual_connection:
+        inert.append("--fp32-residual-connection (the residual stream stays in the parameter dtype; LayerNorm / softmax / loss accumulate in fp32)")
+    if not args.apply_query_key_layer_scaling:
+        inert.append("--no-query-key-layer-scaling (scores are scaled by 1/sqrt(d) inside the attention kernel with an fp32 softmax: the layer-number trick is unnecessary)")
+    if getattr(args, "overlap_p2p_comm", False):
+        inert.append("--overlap-p2p-communication (pipeline p2p is one fused send+recv group per schedule boundary; B2_PP_P2P=links posts receives ahead)")
+    if not getattr(args, "scatter_gather_tensors_in_pipeline", True):
+        inert.append("--no-scatter-gather-tensors-in-pipeline (stage-to-stage tensors are sent whole; under sequence parallelism they already are 1/t)")
+    if getattr(args, "use_ring_exchange_p2p", False):
+        inert.append("--use-ring-exchange-p2p")
+    if not getattr(args, "bias_dropout_fusion", True):
+        inert.append("--no-bias-dropout-fusion (bias + dropout + residual is always one kernel or a GEMM epilogue)")
+    if getattr(args, "attention_impl", "flash") == "flash" and not args.masked_softmax_fusion:
+        inert.append("--no-masked-softmax-fusion (only affects --attention-impl unfused)")
+    args.inert_flags = inert
+    if inert and args.rank == 0:
+        print("> accepted for CLI compatibility, no effect in this runtime:\n    " + "\n    ".join(inert), flush=True)
     if verbose:
         print_args("arguments", args)
     return args
