@@ -61,6 +61,7 @@ def args_fn(argv=None):
     p.add_argument("--synthetic-val-size", type=int, default=734)
     p.add_argument("--bf16", type=_strbool, nargs="?", const=True, default=False)
     p.add_argument("--no-pretrained", action="store_true")
+    p.add_argument("--pretrained-path", type=str, default=None, help="torchvision-format state_dict file to start from (no download here)")
     p.add_argument("--max-steps", type=int, default=None)
     p.add_argument("--num-workers", type=int, default=2)
     p.add_argument("--bucket-cap-mb", type=float, default=25.0)
@@ -121,7 +122,8 @@ def train(args):
     model_history = util.init_modelhistory({})
     dev = args.device
     dtype = torch.bfloat16 if (args.bf16 and dev.type == "cuda") else torch.float32
-    model = util.torch_model(args.model_name, num_classes=args.num_classes, pretrained=not args.no_pretrained, local_rank=args.local_rank).to(dev)
+    model = util.torch_model(args.model_name, num_classes=args.num_classes, pretrained=not args.no_pretrained and not args.pretrained_path, local_rank=args.local_rank,
+                             pretrained_path=args.pretrained_path).to(dev)
     if args.native_bn:
         from ..ops.functional import convert_batchnorm
         model = convert_batchnorm(model, dist.group.WORLD if (args.sync_bn and dist.is_initialized() and args.world_size > 1) else None)

@@ -8,12 +8,13 @@ import json
 import os
 import shutil
 import subprocess
-from typing import Dict, List, Sequence
+from typing import Optional, Dict, List, Sequence
 
 import torch
 
 
-def torch_model(model_name: str, num_classes: int = 0, pretrained: bool = True, local_rank: int = 0, model_type: str = "custom", dtype=None):
+def torch_model(model_name: str, num_classes: int = 0, pretrained: bool = True, local_rank: int = 0, model_type: str = "custom", dtype=None,
+                pretrained_path: Optional[str] = None):
     """Model factory (util.py:34-66).  `pretrained` weights are used when torchvision has them cached locally;
     this box has no network, so the default is random init.  Unlike the reference (Q5) the classification head is
     really resized to `num_classes`."""
@@ -36,6 +37,18 @@ def torch_model(model_name: str, num_classes: int = 0, pretrained: bool = True, 
         model = torchvision.models.__dict__[model_name](weights=None)
         if num_classes > 0:
             swin.replace_head(model, num_classes)
+    if pretrained_path:
+        # a torchvision-format state_dict file (`torch.save(torchvision.models.swin_b(weights=...).state_dict(), path)`); the
+        # classifier rows are skipped when their shape differs from the replaced head
+        sd = torch.load(pretrained_path, map_location="cpu", weights_only=True)
+        sd = sd.get("state_dict", sd)
+        own = model.state_dict()
+        keep = {k.removeprefix("module."): v for k, v in sd.items()}
+        keep = {k: v for k, v in keep.items() if k in own and own[k].shape == v.shape}
+        missing = [k for k in own if k not in keep]
+        model.load_state_dict(keep, strict=False)
+        if local_rank == 0:
+            print(f"[torch_model] loaded {len(keep)} tensors from {pretrained_path}; left at their initial values: {missing[:6]}{'...' if len(missing) > 6 else ''}")
     if dtype is not None:
         model = model.to(dtype)
     return model
