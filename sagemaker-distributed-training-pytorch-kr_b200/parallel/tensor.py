@@ -373,3 +373,65 @@ def next_dropout_seed(tensor_parallel_region: bool) -> int:
     if tensor_parallel_region:
         s = s * 31 + 2718 + mpu.get_tensor_model_parallel_rank()
     return s
+
+
+# ------------------------------------------------------------------------------------------
+# activation checkpointing with RNG restore (megatron.core.tensor_parallel.random.checkpoint)
+# ------------------------------------------------------------------------------------------
+class _CheckpointFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, run_function, distribute_saved_activations, *args):
+        ctx.run_function, ctx.distribute = run_function, bool(distribute_saved_activations)
+        ctx.cpu_rng = torch.get_rng_state()
+        ctx.cuda_rng = torch.cuda.get_rng_state() if torch.cuda.is_available() else None
+        ctx.tracker = get_cuda_rng_tracker().get_states()
+        with torch.no_grad():
+            outputs = run_function(*args)
+        ctx.first_shape = None
+        saved = list(args)
+        if ctx.distribute and torch.is_tensor(args[0]) and _ws(mpu.get_tensor_model_parallel_group()) > 1:
+            # keep only this TP rank's 1/t slice of the first argument (the hidden states); re-gathered in backward
+            g = mpu.get_tensor_model_parallel_group()
+            t, r = _ws(g), dist.get_rank(g)
+            ctx.first_shape = args[0].shape
+            saved[0] = args[0].detach().reshape(-1).chunk(t)[r].clone()
+        ctx.tensor_idx = [i for i, a in enumerate(saved) if torch.is_tensor(a)]
+        ctx.others = [None if torch.is_tensor(a) else a for a in saved]
+        ctx.save_for_backward(*[saved[i] for i in ctx.tensor_idx])
+        return outputs
+
+    @staticmethod
+    def backward(ctx, *grads):
+        if not torch.autograd._is_checkpoint_valid():
+            raise RuntimeError("Checkpointing is not compatible with .grad(), please use .backward() if possible")
+        args = list(ctx.others)
+        for i, t in zip(ctx.tensor_idx, ctx.saved_tensors):
+            args[i] = t
+        if ctx.first_shape is not None:
+            args[0] = all_gather_first_dim(args[0], mpu.get_tensor_model_parallel_group()).view(ctx.first_shape)
+        now_cpu, now_tracker = torch.get_rng_state(), get_cuda_rng_tracker().get_states()
+        now_cuda = torch.cuda.get_rng_state() if torch.cuda.is_available() else None
+        torch.set_rng_state(ctx.cpu_rng)
+        if ctx.cuda_rng is not None:
+            torch.cuda.set_rng_state(ctx.cuda_rng)
+        get_cuda_rng_tracker().set_states(ctx.tracker)
+        try:
+            detached = [a.detach().requires_grad_(a.requires_grad) if torch.is_tensor(a) else a for a in args]
+            with torch.enable_grad():
+                outputs = ctx.run_function(*detached)
+        finally:
+            torch.set_rng_state(now_cpu)
+            if now_cuda is not None:
+                torch.cuda.set_rng_state(now_cuda)
+            get_cuda_rng_tracker().set_states(now_tracker)
+        outputs = (outputs,) if torch.is_tensor(outputs) else tuple(outputs)
+        pairs = [(o, g) for o, g in zip(outputs, grads) if torch.is_tensor(o) and o.requires_grad and g is not None]
+        torch.autograd.backward([o for o, _ in pairs], [g for _, g in pairs])
+        return (None, None) + tuple(a.grad if torch.is_tensor(a) else None for a in detached)
+
+
+def checkpoint(function, distribute_saved_activations, *args):
+    """Run `function(*args)` without keeping its intermediate activations; the backward pass re-runs it under the RNG states
+    (default generator, CUDA generator, tracker streams and the dropout-seed counter) of the first run, so dropout masks
+    repeat.  Same signature as the reference's tensor_parallel.checkpoint."""
+    return _CheckpointFunction.apply(function, distribute_saved_activations, *args)

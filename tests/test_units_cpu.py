@@ -360,3 +360,29 @@ def test_prepare_oxford_pet_split(tmp_path):
     assert sorted(os.listdir(tmp_path / "out" / "train")) == ["Abyssinian", "american_bulldog"]
     again = prep.prepare(str(src), str(tmp_path / "out2"))
     assert sorted(os.listdir(tmp_path / "out" / "val" / "Abyssinian")) == sorted(os.listdir(tmp_path / "out2" / "val" / "Abyssinian"))
+
+
+def test_tensor_parallel_checkpoint_repeats_dropout_masks():
+    from b200dist.parallel import tensor as tpo
+    torch.manual_seed(0)
+    tpo.get_cuda_rng_tracker().reset()
+    tpo.get_cuda_rng_tracker().add("model-parallel-rng", 4321)
+    lin = torch.nn.Linear(16, 16)
+
+    def block(x, scale):
+        h = torch.nn.functional.dropout(lin(x), 0.5, training=True)            # default stream
+        with tpo.get_cuda_rng_tracker().fork():
+            h = torch.nn.functional.dropout(h, 0.3, training=True)             # tracker stream
+        return h * scale
+
+    x = torch.randn(4, 16, requires_grad=True)
+    st_cpu, st_tr = torch.get_rng_state(), tpo.get_cuda_rng_tracker().get_states()
+    y = block(x, 2.0)
+    y.sum().backward()
+    want = (y.detach().clone(), x.grad.clone(), lin.weight.grad.clone())
+    x.grad = None; lin.zero_grad()
+    torch.set_rng_state(st_cpu); tpo.get_cuda_rng_tracker().set_states(st_tr)
+    y2 = tpo.checkpoint(block, False, x, 2.0)
+    torch.nn.functional.dropout(torch.ones(8), 0.5, training=True)           # RNG use between forward and backward must not matter
+    y2.sum().backward()
+    assert torch.equal(y2, want[0]) and torch.equal(x.grad, want[1]) and torch.equal(lin.weight.grad, want[2])
