@@ -208,3 +208,73 @@ def is_rank_in_embedding_group(ignore_virtual: bool = False) -> bool:
 
 def is_rank_in_position_embedding_group() -> bool:
     return _S.rank in _ranks("position_embedding")
+
+
+# ------------------------------------------------------------------------------------------
+# remaining pieces of megatron.core.parallel_state
+# ------------------------------------------------------------------------------------------
+def get_data_parallel_group_gloo():
+    """CPU (gloo) twin of the data-parallel group, used for host-side exchanges of the distributed optimizer.  Created on first
+    use; like every `new_group` this is collective over the world: all ranks must make the first call together."""
+    if not _S.initialized:
+        return None
+    if "dp_gloo" not in _S.groups:
+        mine = None
+        if dist.is_initialized() and dist.get_world_size() > 1:
+            for ranks in _S.layout.dp_groups:
+                g = dist.new_group(ranks, backend="gloo")
+                if _S.rank in ranks:
+                    mine = g
+        _S.groups["dp_gloo"], _S.group_ranks["dp_gloo"] = mine, _S.group_ranks["dp"]
+    return _S.groups["dp_gloo"]
+
+
+def get_pipeline_model_parallel_split_rank() -> Optional[int]:
+    return _S.split_rank
+
+
+def is_pipeline_stage_before_split(rank: Optional[int] = None) -> bool:
+    """encoder side of an encoder-decoder pipeline (`--pipeline-model-parallel-split-rank`); everything counts as "before" without a split"""
+    if get_pipeline_model_parallel_world_size() == 1 or _S.split_rank is None:
+        return True
+    r = get_pipeline_model_parallel_rank() if rank is None else rank
+    return r < _S.split_rank
+
+
+def is_pipeline_stage_after_split(rank: Optional[int] = None) -> bool:
+    if get_pipeline_model_parallel_world_size() == 1 or _S.split_rank is None:
+        return True
+    r = get_pipeline_model_parallel_rank() if rank is None else rank
+    return r >= _S.split_rank
+
+
+def is_pipeline_stage_at_split() -> bool:
+    r = get_pipeline_model_parallel_rank()
+    return is_pipeline_stage_before_split(r) and is_pipeline_stage_after_split(r + 1)
+
+
+class GlobalMemoryBuffer:
+    """Named, growing scratch tensors reused across calls (megatron.core.utils.GlobalMemoryBuffer): `get_tensor(shape, dtype, name)`
+    returns a view of a buffer that is reallocated only when a larger request arrives."""
+
+    def __init__(self):
+        self.buffer = {}
+
+    def get_tensor(self, tensor_shape, dtype, name, device=None):
+        import math
+        import torch
+        need = math.prod(tensor_shape)
+        key = (name, dtype)
+        buf = self.buffer.get(key)
+        if buf is None or buf.numel() < need or (device is not None and buf.device != torch.device(device)):
+            dev = device if device is not None else (torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else "cpu")
+            buf = torch.empty(need, dtype=dtype, device=dev, requires_grad=False)
+            self.buffer[key] = buf
+        return buf[:need].view(*tensor_shape)
+
+
+_GLOBAL_MEMORY_BUFFER = GlobalMemoryBuffer()
+
+
+def get_global_memory_buffer() -> GlobalMemoryBuffer:
+    return _GLOBAL_MEMORY_BUFFER

@@ -386,3 +386,23 @@ def test_tensor_parallel_checkpoint_repeats_dropout_masks():
     torch.nn.functional.dropout(torch.ones(8), 0.5, training=True)           # RNG use between forward and backward must not matter
     y2.sum().backward()
     assert torch.equal(y2, want[0]) and torch.equal(x.grad, want[1]) and torch.equal(lin.weight.grad, want[2])
+
+
+def _state_extras_worker(rank, world):
+    import torch.distributed as dist
+    from b200dist.parallel import state as mpu
+    mpu.initialize_model_parallel(1, 2, None, 1)                  # PP=2 with the split after stage 0; DP groups are singletons at world 2
+    g = mpu.get_data_parallel_group_gloo()
+    before, after, at = mpu.is_pipeline_stage_before_split(), mpu.is_pipeline_stage_after_split(), mpu.is_pipeline_stage_at_split()
+    buf = mpu.get_global_memory_buffer()
+    a = buf.get_tensor((4, 8), torch.float32, "mpu", device="cpu")
+    b = buf.get_tensor((2, 8), torch.float32, "mpu", device="cpu")
+    c = buf.get_tensor((8, 8), torch.float32, "mpu", device="cpu")
+    return (g is not None, before, after, at, a.data_ptr() == b.data_ptr(), tuple(c.shape), mpu.get_pipeline_model_parallel_split_rank())
+
+
+def test_parallel_state_split_rank_gloo_group_and_memory_buffer():
+    from tests._dist_util import run_distributed
+    outs = run_distributed(_state_extras_worker, 2)
+    assert outs[0][1:4] == (True, False, True) and outs[1][1:4] == (False, True, False)
+    assert all(o[0] and o[4] and o[5] == (8, 8) and o[6] == 1 for o in outs)
