@@ -12,7 +12,12 @@
 //   bn_bwd_apply   dx = scale * (g - mean_g - xhat * mean_gx);  dgamma = sum(g*xhat), dbeta = sum(g)
 // Partial sums are fp32 per thread (a few thousand elements at most), combined in double across the CTA and across CTAs,
 // so E[x^2] - mean^2 keeps its digits for activations with a large mean.
+#ifdef B2_EMU                      // CPU emulation of the CUDA execution model (tests/emu/cuda_emu.h): kernels only
+#include "cuda_emu.h"
+namespace b2 {}
+#else
 #include "common.cuh"
+#endif
 #include "b200dist.h"
 
 using namespace b2;
@@ -145,6 +150,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const T* __restr
   }
 }
 
+#ifndef B2_EMU
 int check(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
@@ -180,8 +186,10 @@ int grid1d(long long n) {
     }                                                                                                \
   } while (0)
 
+#endif  // !B2_EMU
 }  // namespace
 
+#ifndef B2_EMU
 // phase 1 of the training forward: sums[C][2] (double, ZERO on entry) += per-channel sum(x), sum(x^2)
 extern "C" int b2_bn_reduce(const void* x, double* sums, int N, int C, int HW, int dtype, void* stream) {
   if (N <= 0 || C <= 0 || HW <= 0) { b2host::set_error("bn_reduce: empty tensor"); return -1; }
@@ -238,3 +246,4 @@ extern "C" int b2_bn_bwd_apply(const void* dy, const void* x, const void* y, con
                          static_cast<T*>(dx), total, C, HW, relu)));
   return check("bn_bwd_apply");
 }
+#endif  // !B2_EMU

@@ -13,6 +13,8 @@
 #include <stdint.h>
 
 #define B2_DEVICE __device__ __forceinline__
+// dynamic shared memory of a kernel (a macro so the CPU emulation in tests/emu can substitute a per-block allocation)
+#define B2_DYN_SMEM(type, name) extern __shared__ type name[]
 
 namespace b2 {
 

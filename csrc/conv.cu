@@ -11,7 +11,12 @@
 //   * conv2d_wgrad : dw, db                                 grid (Cout, Cin): each CTA reduces its 9 taps over batch x pixels
 //   * maxpool2x2 fwd (+ argmax byte) / bwd, log_softmax + NLL fwd / bwd for <= 32 classes (one warp per row)
 // Layout NCHW, stride 1, no padding, square kernels up to 5x5 (one instantiation per size: the tap loops are unrolled).
+#ifdef B2_EMU                      // CPU emulation of the CUDA execution model (tests/emu/cuda_emu.h): kernels only
+#include "cuda_emu.h"
+namespace b2 {}
+#else
 #include "common.cuh"
+#endif
 #include "b200dist.h"
 
 using namespace b2;
@@ -22,18 +27,20 @@ constexpr int kThreads = 256;
 constexpr int kCoTile = 8;       // output channels per CTA in fwd, input channels per CTA in dgrad
 constexpr int kMaxK = 5;
 
+#ifndef B2_EMU
 int check(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { b2host::set_error("%s: %s", what, cudaGetErrorString(e)); return -1; }
   return 0;
 }
+#endif  // !B2_EMU
 
 // x [B, Cin, H, W], w [Cout, Cin, K, K], bias [Cout] | NULL, y [B, Cout, Ho, Wo]  (Ho = H - K + 1)
 template <int K>
 __global__ void __launch_bounds__(kThreads) conv2d_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                               const float* __restrict__ bias, float* __restrict__ y, int Cin,
                                                               int H, int W, int Cout, int relu) {
-  extern __shared__ float sm[];
+  B2_DYN_SMEM(float, sm);
   constexpr int KK = K * K;
   const int Ho = H - K + 1, Wo = W - K + 1;
   float* sx = sm;                                    // [Cin][H][W]
@@ -80,7 +87,7 @@ template <int K>
 __global__ void __launch_bounds__(kThreads) conv2d_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ yact,
                                                                 const float* __restrict__ w, float* __restrict__ dx, int Cin,
                                                                 int H, int W, int Cout, int relu) {
-  extern __shared__ float sm[];
+  B2_DYN_SMEM(float, sm);
   constexpr int KK = K * K;
   const int Ho = H - K + 1, Wo = W - K + 1;
   float* sg = sm;                                    // [Cout][Ho][Wo]
@@ -252,6 +259,7 @@ __global__ void log_softmax_nll_bwd_kernel(const float* __restrict__ logp, const
   if (lane < C) dx[row * C + lane] = d - __expf(logp[row * C + lane]) * s;
 }
 
+#ifndef B2_EMU
 int grid1d(long long n, int threads) {
   long long g = (n + threads - 1) / threads, cap = static_cast<long long>(b2host::num_sms()) * 16;
   return static_cast<int>(g < 1 ? 1 : (g > cap ? cap : g));
@@ -265,8 +273,10 @@ bool conv_args_ok(const char* what, int B, int Cin, int H, int W, int Cout, int 
   return true;
 }
 
+#endif  // !B2_EMU
 }  // namespace
 
+#ifndef B2_EMU
 extern "C" int b2_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout, int K,
                              int relu, void* stream) {
   if (!conv_args_ok("conv2d_fwd", B, Cin, H, W, Cout, K)) return -1;
@@ -341,3 +351,4 @@ extern "C" int b2_log_softmax_nll_bwd(const float* logp, const float* dlogp, con
                                                                                                                     dx, rows, C);
   return check("log_softmax_nll_bwd");
 }
+#endif  // !B2_EMU

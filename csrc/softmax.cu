@@ -11,7 +11,12 @@
 //   y[j] = softmax_j( scale * x[j]  with  x[j] := -10000 where mask[b, 0, i, j] != 0,  and  j > i + (sk - sq) excluded )
 // exactly the conventions of the reference kernels (masked positions are filled with -10000 AFTER scaling; the causal
 // variant gives future positions probability 0).  Backward: dx = scale * y * (dy - sum_j dy[j] y[j]).
+#ifdef B2_EMU                      // CPU emulation of the CUDA execution model (tests/emu/cuda_emu.h): kernels only
+#include "cuda_emu.h"
+namespace b2 {}
+#else
 #include "common.cuh"
+#endif
 #include "b200dist.h"
 
 using namespace b2;
@@ -51,7 +56,7 @@ template <typename T>
 __global__ void __launch_bounds__(kThreads) softmax_fwd_kernel(const T* __restrict__ x, const uint8_t* __restrict__ mask,
                                                                T* __restrict__ y, long long rows, int sq, int sk, int heads,
                                                                int mask_batches, float scale, int causal) {
-  extern __shared__ float row[];         // [sk]
+  B2_DYN_SMEM(float, row);               // [sk]
   __shared__ float red[kThreads / 32];
   for (long long r = blockIdx.x; r < rows; r += gridDim.x) {
     const int i = static_cast<int>(r % sq);
@@ -102,6 +107,7 @@ __global__ void __launch_bounds__(kThreads) softmax_bwd_kernel(const T* __restri
   }
 }
 
+#ifndef B2_EMU
 int grid_rows(long long rows) {
   long long cap = static_cast<long long>(b2host::num_sms()) * 8;
   return static_cast<int>(rows < cap ? (rows < 1 ? 1 : rows) : cap);
@@ -113,8 +119,10 @@ int check(const char* what) {
   return 0;
 }
 
+#endif  // !B2_EMU
 }  // namespace
 
+#ifndef B2_EMU
 extern "C" int b2_softmax_fwd(const void* x, const unsigned char* mask, void* y, long long rows, int sq, int sk, int heads,
                               int mask_batches, float scale, int causal, int dtype, void* stream) {
   if (rows <= 0 || sq <= 0 || sk <= 0 || heads <= 0 || sk > kMaxSk) {
@@ -156,3 +164,4 @@ extern "C" int b2_softmax_bwd(const void* dy, const void* y, void* dx, long long
                                                          sk, scale);
   return check("softmax_bwd");
 }
+#endif  // !B2_EMU

@@ -1,0 +1,137 @@
+// Driver that runs the SIMT kernels of csrc/{softmax,conv,batchnorm}.cu under the CPU emulation in cuda_emu.h.
+// Built by tests/test_kernel_emulation_cpu.py with g++ (no nvcc, no GPU); each entry point mirrors the launch of the
+// corresponding extern "C" host wrapper in the .cu file (same grid shape rules, smaller caps).
+#define B2_EMU 1
+#include "cuda_emu.h"
+#include "b200dist.h"
+
+namespace k_softmax {
+#include "softmax.cu"
+}
+namespace k_conv {
+#include "conv.cu"
+}
+namespace k_bn {
+#include "batchnorm.cu"
+}
+
+namespace {
+template <typename F>
+void with_dtype(int dtype, F f) {            // 0 fp16, 1 bf16, 2 fp32 (B2_DTYPE_*)
+  if (dtype == 1) f(static_cast<__nv_bfloat16*>(nullptr));
+  else if (dtype == 0) f(static_cast<__half*>(nullptr));
+  else f(static_cast<float*>(nullptr));
+}
+}  // namespace
+
+extern "C" {
+
+void emu_softmax_fwd(const void* x, const unsigned char* mask, void* y, long long rows, int sq, int sk, int heads, int mask_batches,
+                     float scale, int causal, int dtype, int grid) {
+  with_dtype(dtype, [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    emu::launch(dim3(grid), dim3(128), sizeof(float) * sk, [&] {
+      k_softmax::softmax_fwd_kernel<T>(static_cast<const T*>(x), mask, static_cast<T*>(y), rows, sq, sk, heads, mask_batches, scale, causal);
+    });
+  });
+}
+
+void emu_softmax_bwd(const void* dy, const void* y, void* dx, long long rows, int sk, float scale, int dtype, int grid) {
+  with_dtype(dtype, [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    emu::launch(dim3(grid), dim3(128), 0, [&] {
+      k_softmax::softmax_bwd_kernel<T>(static_cast<const T*>(dy), static_cast<const T*>(y), static_cast<T*>(dx), rows, sk, scale);
+    });
+  });
+}
+
+#define EMU_K_SWITCH(K, BODY)                                             \
+  switch (K) {                                                            \
+    case 1: { constexpr int KV = 1; BODY; break; }                        \
+    case 2: { constexpr int KV = 2; BODY; break; }                        \
+    case 3: { constexpr int KV = 3; BODY; break; }                        \
+    case 4: { constexpr int KV = 4; BODY; break; }                        \
+    default: { constexpr int KV = 5; BODY; break; }                       \
+  }
+
+void emu_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout, int K, int relu) {
+  const size_t smem = (static_cast<size_t>(Cin) * H * W + 8u * Cin * K * K) * sizeof(float);
+  dim3 grid(B, (Cout + 7) / 8);
+  EMU_K_SWITCH(K, emu::launch(grid, dim3(256), smem, [&] { k_conv::conv2d_fwd_kernel<KV>(x, w, bias, y, Cin, H, W, Cout, relu); }));
+}
+
+void emu_conv2d_bwd(const float* dy, const float* yact, const float* x, const float* w, float* dx, float* dw, float* db, int B, int Cin, int H,
+                    int W, int Cout, int K, int relu, int accumulate) {
+  const int Ho = H - K + 1, Wo = W - K + 1;
+  if (dx) {
+    const size_t smem = (static_cast<size_t>(Cout) * Ho * Wo + static_cast<size_t>(Cout) * 8 * K * K) * sizeof(float);
+    dim3 grid(B, (Cin + 7) / 8);
+    EMU_K_SWITCH(K, emu::launch(grid, dim3(256), smem, [&] { k_conv::conv2d_dgrad_kernel<KV>(dy, yact, w, dx, Cin, H, W, Cout, relu); }));
+  }
+  if (dw) {
+    dim3 grid(Cout, Cin);
+    EMU_K_SWITCH(K, emu::launch(grid, dim3(256), 0, [&] { k_conv::conv2d_wgrad_kernel<KV>(dy, yact, x, dw, db, B, Cin, H, W, Cout, relu, accumulate); }));
+  }
+}
+
+void emu_maxpool2_fwd(const float* x, float* y, unsigned char* idx, long long planes, int H, int W, int grid) {
+  emu::launch(dim3(grid), dim3(256), 0, [&] { k_conv::maxpool2_fwd_kernel(x, y, idx, planes, H, W); });
+}
+
+void emu_maxpool2_bwd(const float* dy, const unsigned char* idx, float* dx, long long planes, int H, int W, int grid) {
+  emu::launch(dim3(grid), dim3(256), 0, [&] { k_conv::maxpool2_bwd_kernel(dy, idx, dx, planes, H, W); });
+}
+
+void emu_log_softmax_nll_fwd(const float* x, const long long* target, float* logp, float* loss, long long rows, int C) {
+  emu::launch(dim3(static_cast<unsigned>((rows * 32 + 255) / 256)), dim3(256), 0,
+              [&] { k_conv::log_softmax_nll_fwd_kernel(x, target, logp, loss, rows, C); });
+}
+
+void emu_log_softmax_nll_bwd(const float* logp, const float* dlogp, const long long* target, const float* gloss, float gscalar, float* dx,
+                             long long rows, int C) {
+  emu::launch(dim3(static_cast<unsigned>((rows * 32 + 255) / 256)), dim3(256), 0,
+              [&] { k_conv::log_softmax_nll_bwd_kernel(logp, dlogp, target, gloss, gscalar, dx, rows, C); });
+}
+
+// BatchNorm: `wide` != 0 instantiates the 64-bit index variants (used on the GPU only for tensors of >= 2^31 elements)
+void emu_bn_train_fwd(const void* x, const float* gamma, const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                      float* mean, float* rstd, void* y, double* sums, int N, int C, int HW, int relu, int dtype, int splits, int wide) {
+  const long long total = static_cast<long long>(N) * C * HW;
+  std::vector<float> scale(C), shift(C);
+  with_dtype(dtype, [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    auto run = [&](auto idx_tag) {
+      using I = decltype(idx_tag);
+      emu::launch(dim3(C, splits), dim3(256), 0, [&] { k_bn::bn_reduce_kernel<T, I>(static_cast<const T*>(x), sums, N, C, HW); });
+      emu::launch(dim3((C + 127) / 128), dim3(128), 0, [&] {
+        k_bn::bn_finalize_kernel(sums, static_cast<double>(N) * HW, gamma, beta, eps, momentum, running_mean, running_var, mean, rstd, scale.data(),
+                                 shift.data(), C);
+      });
+      emu::launch(dim3(3), dim3(256), 0, [&] {
+        k_bn::bn_apply_kernel<T, I>(static_cast<const T*>(x), scale.data(), shift.data(), static_cast<T*>(y), total, C, HW, relu);
+      });
+    };
+    if (wide) run(static_cast<long long>(0)); else run(0u);
+  });
+}
+
+void emu_bn_bwd(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const float* gamma, double* sums, void* dx,
+                int N, int C, int HW, int relu, int dtype, int splits, int wide) {
+  const long long total = static_cast<long long>(N) * C * HW;
+  with_dtype(dtype, [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    auto run = [&](auto idx_tag) {
+      using I = decltype(idx_tag);
+      emu::launch(dim3(C, splits), dim3(256), 0, [&] {
+        k_bn::bn_bwd_reduce_kernel<T, I>(static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, sums, N, C, HW, relu);
+      });
+      emu::launch(dim3(3), dim3(256), 0, [&] {
+        k_bn::bn_bwd_apply_kernel<T, I>(static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, gamma, sums,
+                                        1.0 / (static_cast<double>(N) * HW), static_cast<T*>(dx), total, C, HW, relu);
+      });
+    };
+    if (wide) run(static_cast<long long>(0)); else run(0u);
+  });
+}
+
+}  // extern "C"

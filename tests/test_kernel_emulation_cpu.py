@@ -1,0 +1,152 @@
+"""The SIMT kernels of csrc/softmax.cu, csrc/conv.cu and csrc/batchnorm.cu executed on the CPU under an emulation of the CUDA
+execution model (tests/emu/cuda_emu.h: one OS thread per CUDA thread, barriers for __syncthreads, slot exchange for warp
+shuffles, poisoned dynamic shared memory) and compared with the PyTorch oracles.  These kernels were written after the round's
+GPU budget was spent; this is the strongest check of their indexing / reduction / barrier logic available without hardware.
+The kernel source is compiled unchanged (the .cu files switch headers on B2_EMU and hide only their host-side launch code)."""
+import ctypes
+import os
+import subprocess
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SO = os.path.join(ROOT, "build", "libb2_emu.so")
+DT = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
+
+
+@pytest.fixture(scope="module")
+def emu():
+    srcs = [os.path.join(ROOT, "tests", "emu", f) for f in ("emu_kernels.cpp", "cuda_emu.h")] + \
+           [os.path.join(ROOT, "csrc", f) for f in ("softmax.cu", "conv.cu", "batchnorm.cu")]
+    if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(s) for s in srcs):
+        os.makedirs(os.path.dirname(SO), exist_ok=True)
+        r = subprocess.run(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-mf16c", "-mavx2", "-I" + os.path.join(ROOT, "tests", "emu"),
+                            "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "csrc"), srcs[0], "-o", SO], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-3000:]
+    return ctypes.CDLL(SO)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+c_i, c_ll, c_f = ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("shape,causal,masked", [((2, 3, 8, 8), True, False), ((2, 2, 5, 37), False, True), ((1, 2, 6, 150), True, False),
+                                                  ((1, 1, 3, 300), False, False)])
+def test_softmax_kernels_under_emulation(emu, dtype, shape, causal, masked):
+    from b200dist.ops import native as N
+    torch.manual_seed(0)
+    b, h, sq, sk = shape
+    x = (torch.randn(shape) * 3).to(dtype)
+    mask = (torch.rand(b, 1, sq, sk) > 0.7) if masked else None
+    m8 = mask.to(torch.uint8).contiguous() if masked else None
+    y = torch.empty_like(x)
+    rows = b * h * sq
+    emu.emu_softmax_fwd(_p(x), _p(m8), _p(y), c_ll(rows), sq, sk, h, b if masked else 1, c_f(0.37), int(causal), DT[dtype], 3)   # grid 3 < rows: row loop
+    ref = N.softmax_ref(x, mask, 0.37, causal)
+    tol = 1e-6 if dtype == torch.float32 else 8e-3
+    assert torch.allclose(y.float(), ref, atol=tol, rtol=tol), (y.float() - ref).abs().max()
+    dy = torch.randn(shape).to(dtype)
+    dx = torch.empty_like(x)
+    emu.emu_softmax_bwd(_p(dy), _p(y), _p(dx), c_ll(rows), sk, c_f(0.37), DT[dtype], 2)
+    yf, df = y.float(), dy.float()
+    want = 0.37 * yf * (df - (df * yf).sum(-1, keepdim=True))
+    assert torch.allclose(dx.float(), want, atol=tol * 4, rtol=tol * 4), (dx.float() - want).abs().max()
+    if masked:                                  # mask broadcast over the batch
+        y1 = torch.empty_like(x)
+        emu.emu_softmax_fwd(_p(x), _p(m8[:1].contiguous()), _p(y1), c_ll(rows), sq, sk, h, 1, c_f(0.37), int(causal), DT[dtype], 4)
+        assert torch.allclose(y1.float(), N.softmax_ref(x, mask[:1], 0.37, causal), atol=tol, rtol=tol)
+
+
+@pytest.mark.parametrize("shape", [(2, 1, 9, 9, 5, 3), (2, 5, 8, 7, 13, 3), (1, 3, 7, 7, 4, 5), (2, 9, 5, 6, 3, 1), (1, 2, 6, 6, 9, 2), (1, 3, 7, 8, 2, 4)])
+@pytest.mark.parametrize("relu", [True, False])
+def test_conv_kernels_under_emulation(emu, shape, relu):
+    B, Cin, H, W, Cout, K = shape
+    torch.manual_seed(1)
+    x = torch.randn(B, Cin, H, W, requires_grad=True)
+    w = (torch.randn(Cout, Cin, K, K) / (Cin * K * K) ** 0.5).requires_grad_()
+    b = torch.randn(Cout, requires_grad=True)
+    y = torch.empty(B, Cout, H - K + 1, W - K + 1)
+    emu.emu_conv2d_fwd(_p(x.detach()), _p(w.detach()), _p(b.detach()), _p(y), B, Cin, H, W, Cout, K, int(relu))
+    ref = F.conv2d(x, w, b)
+    ref = F.relu(ref) if relu else ref
+    assert torch.allclose(y, ref, atol=1e-5), (y - ref).abs().max()
+    dy = torch.randn_like(ref)
+    dx, dw, db = torch.empty_like(x), torch.empty_like(w), torch.empty_like(b)
+    emu.emu_conv2d_bwd(_p(dy), _p(y), _p(x.detach()), _p(w.detach()), _p(dx), _p(dw), _p(db), B, Cin, H, W, Cout, K, int(relu), 0)
+    rx, rw, rb = torch.autograd.grad(ref, (x, w, b), dy)
+    assert torch.allclose(dx, rx, atol=1e-5) and torch.allclose(dw, rw, atol=1e-4) and torch.allclose(db, rb, atol=1e-4)
+    dw2, db2 = dw.clone(), db.clone()           # accumulate = 1 adds into dw / db; dx may be NULL
+    emu.emu_conv2d_bwd(_p(dy), _p(y), _p(x.detach()), _p(w.detach()), None, _p(dw2), _p(db2), B, Cin, H, W, Cout, K, int(relu), 1)
+    assert torch.allclose(dw2, 2 * rw, atol=2e-4) and torch.allclose(db2, 2 * rb, atol=2e-4)
+
+
+def test_pool_and_log_softmax_kernels_under_emulation(emu):
+    torch.manual_seed(2)
+    for shape in ((2, 3, 6, 8), (1, 2, 7, 5)):
+        x = torch.randn(*shape, requires_grad=True)
+        H, W = shape[-2:]
+        y = torch.empty(*shape[:-2], H // 2, W // 2)
+        idx = torch.empty(y.shape, dtype=torch.uint8)
+        planes = shape[0] * shape[1]
+        emu.emu_maxpool2_fwd(_p(x.detach()), _p(y), _p(idx), c_ll(planes), H, W, 2)
+        ref = F.max_pool2d(x, 2)
+        assert torch.equal(y, ref)
+        g = torch.randn_like(ref)
+        dx = torch.empty_like(x)
+        emu.emu_maxpool2_bwd(_p(g), _p(idx), _p(dx), c_ll(planes), H, W, 2)
+        assert torch.equal(dx, torch.autograd.grad(ref, x, g)[0])
+    for rows, C in ((19, 10), (5, 32), (9, 1)):
+        z = torch.randn(rows, C, requires_grad=True)
+        t = torch.randint(0, C, (rows,))
+        lp, loss = torch.empty(rows, C), torch.empty(rows)
+        emu.emu_log_softmax_nll_fwd(_p(z.detach()), _p(t), _p(lp), _p(loss), c_ll(rows), C)
+        rlp = F.log_softmax(z, 1)
+        assert torch.allclose(lp, rlp, atol=1e-6) and torch.allclose(loss, F.nll_loss(rlp, t, reduction="none"), atol=1e-6)
+        d, gl = torch.randn(rows, C), torch.rand(rows)
+        dx = torch.empty(rows, C)
+        emu.emu_log_softmax_nll_bwd(_p(lp), _p(d), _p(t), _p(gl), c_f(0.5), _p(dx), c_ll(rows), C)
+        (want,) = torch.autograd.grad((rlp * d).sum() + (F.nll_loss(rlp, t, reduction="none") * gl * 0.5).sum(), z)
+        assert torch.allclose(dx, want, atol=1e-5)
+        emu.emu_log_softmax_nll_bwd(_p(lp), None, _p(t), None, c_f(1.0 / rows), _p(dx), c_ll(rows), C)      # plain mean NLL
+        (want,) = torch.autograd.grad(F.nll_loss(F.log_softmax(z, 1), t), z)
+        assert torch.allclose(dx, want, atol=1e-6)
+
+
+@pytest.mark.parametrize("dtype,wide", [(torch.float32, 0), (torch.bfloat16, 0), (torch.float16, 0), (torch.float32, 1)])
+@pytest.mark.parametrize("relu", [False, True])
+def test_batchnorm_kernels_under_emulation(emu, dtype, wide, relu):
+    torch.manual_seed(3)
+    N_, C, H, W = 3, 5, 4, 7
+    x = (torch.randn(N_, C, H, W) * 2 + 3).to(dtype)
+    gamma, beta = torch.rand(C) + 0.5, torch.randn(C)
+    rm, rv = torch.zeros(C), torch.ones(C)
+    mean, rstd = torch.empty(C), torch.empty(C)
+    y = torch.empty_like(x)
+    sums = torch.zeros(C, 2, dtype=torch.float64)
+    emu.emu_bn_train_fwd(_p(x), _p(gamma), _p(beta), c_f(1e-5), c_f(0.1), _p(rm), _p(rv), _p(mean), _p(rstd), _p(y), _p(sums), N_, C, H * W, int(relu),
+                         DT[dtype], 2, wide)
+    xr = x.float().requires_grad_()
+    g_, b_ = gamma.clone().requires_grad_(), beta.clone().requires_grad_()
+    rm2, rv2 = torch.zeros(C), torch.ones(C)
+    ref = F.batch_norm(xr, rm2, rv2, g_, b_, True, 0.1, 1e-5)
+    ref = torch.relu(ref) if relu else ref
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    assert torch.allclose(y.float(), ref, atol=tol, rtol=tol), (y.float() - ref).abs().max()
+    assert torch.allclose(rm, rm2, atol=1e-5) and torch.allclose(rv, rv2, atol=1e-4)
+    assert torch.allclose(mean, x.float().mean((0, 2, 3)), atol=1e-5)
+    dy = torch.randn(N_, C, H, W).to(dtype)
+    dx = torch.empty_like(x)
+    sums.zero_()
+    emu.emu_bn_bwd(_p(dy), _p(x), _p(y), _p(mean), _p(rstd), _p(gamma), _p(sums), _p(dx), N_, C, H * W, int(relu), DT[dtype], 3, wide)
+    # the oracle masks with the kernel's own (rounded) forward output, like the kernel does
+    gy = dy.float() * (y.float() > 0) if relu else dy.float()
+    pre = F.batch_norm(xr, None, None, g_, b_, True, 0.0, 1e-5)
+    wx, wg, wb = torch.autograd.grad(pre, (xr, g_, b_), gy)
+    assert torch.allclose(dx.float(), wx, atol=tol * 2, rtol=tol * 2), (dx.float() - wx).abs().max()
+    assert torch.allclose(sums[:, 1].float(), wg, atol=tol * 8, rtol=tol * 4) and torch.allclose(sums[:, 0].float(), wb, atol=tol * 8, rtol=tol * 4)
