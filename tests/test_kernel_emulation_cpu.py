@@ -150,3 +150,19 @@ def test_batchnorm_kernels_under_emulation(emu, dtype, wide, relu):
     wx, wg, wb = torch.autograd.grad(pre, (xr, g_, b_), gy)
     assert torch.allclose(dx.float(), wx, atol=tol * 2, rtol=tol * 2), (dx.float() - wx).abs().max()
     assert torch.allclose(sums[:, 1].float(), wg, atol=tol * 8, rtol=tol * 4) and torch.allclose(sums[:, 0].float(), wb, atol=tol * 8, rtol=tol * 4)
+
+
+def test_emulated_kernels_are_race_free_under_thread_sanitizer(tmp_path):
+    """the same kernels under -fsanitize=thread: a __shared__ access that a barrier should have ordered is reported as a data race"""
+    exe = str(tmp_path / "emu_tsan")
+    r = subprocess.run(["g++", "-std=c++17", "-fsanitize=thread", "-O1", "-g", "-pthread", "-mf16c", "-mavx2", "-I" + os.path.join(ROOT, "tests", "emu"),
+                        "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "csrc"), os.path.join(ROOT, "tests", "emu", "tsan_main.cpp"),
+                        os.path.join(ROOT, "tests", "emu", "emu_kernels.cpp"), "-o", exe], capture_output=True, text=True)
+    if r.returncode != 0 and "tsan" in r.stderr.lower():
+        pytest.skip("libtsan not available")
+    assert r.returncode == 0, r.stderr[-3000:]
+    run = subprocess.run([exe], capture_output=True, text=True, timeout=900)
+    out = run.stdout + run.stderr
+    if "FATAL: ThreadSanitizer" in out and "unexpected memory mapping" in out:
+        pytest.skip("ThreadSanitizer cannot run in this container (memory layout)")
+    assert run.returncode == 0 and "tsan pass done" in out and "data race" not in out, out[-4000:]
