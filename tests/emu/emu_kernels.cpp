@@ -135,3 +135,84 @@ void emu_bn_bwd(const void* dy, const void* x, const void* y, const float* mean,
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The same entry-point NAMES and SIGNATURES as include/b200dist.h, so that the Python bindings (ops/native.py: argument
+// order, ctypes signature table) can be exercised end to end against the emulated kernels.  `stream` is ignored.
+// ---------------------------------------------------------------------------------------------------------------------
+extern "C" {
+
+int b2_softmax_fwd(const void* x, const unsigned char* mask, void* y, long long rows, int sq, int sk, int heads, int mask_batches, float scale,
+                   int causal, int dtype, void*) {
+  if (rows <= 0 || sk <= 0 || rows % (static_cast<long long>(sq) * heads) != 0) return -1;
+  emu_softmax_fwd(x, mask, y, rows, sq, sk, heads, mask_batches, scale, causal, dtype, static_cast<int>(std::min<long long>(rows, 3)));
+  return 0;
+}
+int b2_softmax_bwd(const void* dy, const void* y, void* dx, long long rows, int sk, float scale, int dtype, void*) {
+  emu_softmax_bwd(dy, y, dx, rows, sk, scale, dtype, static_cast<int>(std::min<long long>(rows, 3)));
+  return 0;
+}
+int b2_conv2d_fwd(const float* x, const float* w, const float* bias, float* y, int B, int Cin, int H, int W, int Cout, int K, int relu, void*) {
+  emu_conv2d_fwd(x, w, bias, y, B, Cin, H, W, Cout, K, relu);
+  return 0;
+}
+int b2_conv2d_bwd(const float* dy, const float* yact, const float* x, const float* w, float* dx, float* dw, float* db, int B, int Cin, int H, int W,
+                  int Cout, int K, int relu, int accumulate, void*) {
+  emu_conv2d_bwd(dy, yact, x, w, dx, dw, db, B, Cin, H, W, Cout, K, relu, accumulate);
+  return 0;
+}
+int b2_maxpool2_fwd(const float* x, float* y, unsigned char* idx, long long planes, int H, int W, void*) { emu_maxpool2_fwd(x, y, idx, planes, H, W, 2); return 0; }
+int b2_maxpool2_bwd(const float* dy, const unsigned char* idx, float* dx, long long planes, int H, int W, void*) { emu_maxpool2_bwd(dy, idx, dx, planes, H, W, 2); return 0; }
+int b2_log_softmax_nll_fwd(const float* x, const long long* target, float* logp, float* loss, long long rows, int C, void*) {
+  emu_log_softmax_nll_fwd(x, target, logp, loss, rows, C);
+  return 0;
+}
+int b2_log_softmax_nll_bwd(const float* logp, const float* dlogp, const long long* target, const float* gloss, float gscalar, float* dx, long long rows,
+                           int C, void*) {
+  emu_log_softmax_nll_bwd(logp, dlogp, target, gloss, gscalar, dx, rows, C);
+  return 0;
+}
+
+#define EMU_BN(dtype, BODY)                                                                         \
+  with_dtype(dtype, [&](auto* tag) { using T = std::remove_pointer_t<decltype(tag)>; using I = unsigned; BODY; })
+
+int b2_bn_reduce(const void* x, double* sums, int N, int C, int HW, int dtype, void*) {
+  EMU_BN(dtype, emu::launch(dim3(C, 2), dim3(256), 0, [&] { k_bn::bn_reduce_kernel<T, I>(static_cast<const T*>(x), sums, N, C, HW); }));
+  return 0;
+}
+int b2_bn_finalize(const double* sums, double count, const float* gamma, const float* beta, float eps, float momentum, float* running_mean,
+                   float* running_var, float* mean, float* rstd, float* scale, float* shift, int C, void*) {
+  emu::launch(dim3((C + 127) / 128), dim3(128), 0, [&] {
+    k_bn::bn_finalize_kernel(sums, count, gamma, beta, eps, momentum, running_mean, running_var, mean, rstd, scale, shift, C);
+  });
+  return 0;
+}
+int b2_bn_eval_coeffs(const float* running_mean, const float* running_var, const float* gamma, const float* beta, float eps, float* scale, float* shift,
+                      int C, void*) {
+  emu::launch(dim3((C + 127) / 128), dim3(128), 0, [&] { k_bn::bn_eval_coeffs_kernel(running_mean, running_var, gamma, beta, eps, scale, shift, C); });
+  return 0;
+}
+int b2_bn_apply(const void* x, const float* scale, const float* shift, void* y, int N, int C, int HW, int relu, int dtype, void*) {
+  const long long total = static_cast<long long>(N) * C * HW;
+  EMU_BN(dtype, emu::launch(dim3(3), dim3(256), 0, [&] { k_bn::bn_apply_kernel<T, I>(static_cast<const T*>(x), scale, shift, static_cast<T*>(y), total, C, HW, relu); }));
+  return 0;
+}
+int b2_bn_bwd_reduce(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, double* sums, int N, int C, int HW, int relu,
+                     int dtype, void*) {
+  if (relu && !y) return -1;
+  EMU_BN(dtype, emu::launch(dim3(C, 2), dim3(256), 0, [&] {
+           k_bn::bn_bwd_reduce_kernel<T, I>(static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, sums, N, C, HW, relu);
+         }));
+  return 0;
+}
+int b2_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* mean, const float* rstd, const float* gamma, const double* sums,
+                    double count, void* dx, int N, int C, int HW, int relu, int dtype, void*) {
+  const long long total = static_cast<long long>(N) * C * HW;
+  EMU_BN(dtype, emu::launch(dim3(3), dim3(256), 0, [&] {
+           k_bn::bn_bwd_apply_kernel<T, I>(static_cast<const T*>(dy), static_cast<const T*>(x), static_cast<const T*>(y), mean, rstd, gamma, sums, 1.0 / count,
+                                           static_cast<T*>(dx), total, C, HW, relu);
+         }));
+  return 0;
+}
+
+}  // extern "C"

@@ -166,3 +166,83 @@ def test_emulated_kernels_are_race_free_under_thread_sanitizer(tmp_path):
     if "FATAL: ThreadSanitizer" in out and "unexpected memory mapping" in out:
         pytest.skip("ThreadSanitizer cannot run in this container (memory layout)")
     assert run.returncode == 0 and "tsan pass done" in out and "data race" not in out, out[-4000:]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Python bindings end to end: ops/native.py's CUDA branches (argument order, ctypes signature table, scratch handling) driven
+# against the emulated kernels through entry points with the names and signatures of include/b200dist.h
+# ---------------------------------------------------------------------------------------------------------------------
+class _FakeCuda(torch.Tensor):
+    """a CPU tensor that answers `is_cuda` with True, so the wrappers take their native branch"""
+    is_cuda = True
+
+
+def _fc(t):
+    return t.detach().as_subclass(_FakeCuda)
+
+
+@pytest.fixture()
+def native_on_emu(emu, monkeypatch):
+    from b200dist.ops import native as N
+
+    def call(name, *args):
+        fn = getattr(emu, name)
+        fn.argtypes, fn.restype = N._SIGS[name], ctypes.c_int
+        rc = fn(*args)
+        assert rc == 0, f"{name} returned {rc}"
+
+    monkeypatch.setattr(N, "_call", call)
+    monkeypatch.setattr(N, "_st", lambda: None)
+    return N
+
+
+def test_python_bindings_drive_the_emulated_kernels(native_on_emu):
+    N = native_on_emu
+    from b200dist.ops import functional as Fn
+    torch.manual_seed(4)
+    # softmax (causal + padding mask) through the autograd op
+    x = torch.randn(2, 2, 6, 10)
+    mask = torch.rand(2, 1, 6, 10) > 0.7
+    xs = _fc(x).requires_grad_()
+    y = Fn.scaled_masked_softmax(xs, mask, 0.5)
+    xr = x.clone().requires_grad_()
+    ref = torch.softmax((xr * 0.5).masked_fill(mask, -10000.0), -1)
+    assert torch.allclose(torch.Tensor(y), ref, atol=1e-6)
+    g = torch.randn_like(ref)
+    y.backward(_fc(g)); ref.backward(g)
+    assert torch.allclose(torch.Tensor(xs.grad), xr.grad, atol=1e-6)
+    yc = N.softmax_fwd(_fc(x), None, 2.0, True)
+    assert torch.allclose(torch.Tensor(yc), N.softmax_ref(x, None, 2.0, True), atol=1e-6)
+    # batch norm module: training (running statistics), fused ReLU, backward, inference
+    xb = torch.randn(4, 3, 5, 6) * 2 + 1
+    ours, ref_bn = Fn.BatchNorm2d(3, fuse_relu=True), torch.nn.BatchNorm2d(3)
+    with torch.no_grad():
+        ref_bn.weight.uniform_(0.5, 1.5); ref_bn.bias.normal_()
+    ours.load_state_dict(ref_bn.state_dict())
+    xo, xr = _fc(xb).requires_grad_(), xb.clone().requires_grad_()
+    yo, yr = ours(xo), torch.relu(ref_bn(xr))
+    assert torch.allclose(torch.Tensor(yo), yr, atol=1e-5)
+    g = torch.randn_like(yr)
+    yo.backward(_fc(g)); yr.backward(g)
+    assert torch.allclose(torch.Tensor(xo.grad), xr.grad, atol=2e-5)
+    assert torch.allclose(ours.weight.grad, ref_bn.weight.grad, atol=2e-5) and torch.allclose(ours.bias.grad, ref_bn.bias.grad, atol=2e-5)
+    assert torch.allclose(ours.running_mean, ref_bn.running_mean, atol=1e-6) and torch.allclose(ours.running_var, ref_bn.running_var, atol=1e-5)
+    ours.eval(); ref_bn.eval()
+    assert torch.allclose(torch.Tensor(ours(_fc(xb))), torch.relu(ref_bn(xb)), atol=1e-5)
+
+
+def test_mnist_model_on_the_emulated_native_ops(native_on_emu):
+    """the whole MNIST network with --native-ops: conv + bias + ReLU x2, max-pool, log-softmax through bindings + emulated
+    kernels (fc layers on ATen) against the ATen model: loss and every parameter gradient"""
+    from b200dist.models.mnist import Net
+    torch.manual_seed(5)
+    a, b = Net().eval(), Net(native_ops=True).eval()
+    b.load_state_dict(a.state_dict())
+    x = torch.randn(2, 1, 28, 28)
+    t = torch.randint(0, 10, (2,))
+    la = F.nll_loss(a(x), t)
+    lb = F.nll_loss(torch.Tensor(b(_fc(x))), t)
+    assert torch.allclose(la, lb, atol=1e-5)
+    la.backward(); lb.backward()
+    for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-4, rtol=1e-3), (n, (p.grad - q.grad).abs().max())
