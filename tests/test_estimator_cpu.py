@@ -67,3 +67,11 @@ def test_environment_contract_and_fail_stop(tmp_path):
     assert time.time() - t0 < 30          # the sleeping rank was taken down, not waited for
     with pytest.raises(ValueError):
         LocalEstimator(entry_point=str(script), instance_count=2)
+
+
+def test_example_script_of_notebook_1_runs(tmp_path):
+    import subprocess
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "1_mnist_ddp.py"), "--processes", "2", "--output", str(tmp_path)],
+                       capture_output=True, text=True, timeout=600, cwd=os.path.join(ROOT, "examples"))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "'test:Accuracy'" in r.stdout and "model:" in r.stdout
