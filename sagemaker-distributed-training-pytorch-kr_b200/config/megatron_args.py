@@ -146,7 +146,7 @@ GROUPS: Dict[str, List[Flag]] = {
         _f("--short-seq-prob", type=float, default=0.1), _f("--mmap-warmup", action=T), _f("--num-workers", type=int, default=2),
         _f("--tokenizer-type", type=str, choices=["BertWordPieceLowerCase", "BertWordPieceCase", "GPT2BPETokenizer", "SentencePieceTokenizer",
                                                   "GPTSentencePieceTokenizer", "NullTokenizer"]),
-        _f("--tokenizer-model", type=str), _f("--data-impl", type=str, default="infer", choices=["mmap", "infer"]),
+        _f("--tokenizer-model", type=str), _f("--data-impl", type=str, default="infer", choices=["lazy", "cached", "mmap", "infer"]),
         _f("--reset-position-ids", action=T), _f("--reset-attention-mask", action=T), _f("--eod-mask-loss", action=T),
         _f("--mock-data", action=T, help="(addition) synthetic token stream of the configured shape"),
         _f("--attention-impl", type=str, default="flash", choices=["flash", "unfused"],

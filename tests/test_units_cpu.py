@@ -406,3 +406,37 @@ def test_parallel_state_split_rank_gloo_group_and_memory_buffer():
     outs = run_distributed(_state_extras_worker, 2)
     assert outs[0][1:4] == (True, False, True) and outs[1][1:4] == (False, True, False)
     assert all(o[0] and o[4] and o[5] == (8, 8) and o[6] == 1 for o in outs)
+
+
+def test_indexed_dataset_formats_mmap_lazy_cached_infer(tmp_path):
+    from b200dist.data import indexed_dataset as idx
+    rs = np.random.RandomState(0)
+    docs = [[rs.randint(0, 1000, size=rs.randint(1, 20)) for _ in range(rs.randint(1, 4))] for _ in range(12)]
+    for impl in ("mmap", "cached"):
+        prefix = str(tmp_path / impl)
+        b = idx.make_builder(idx.data_file_path(prefix), impl, dtype=np.uint16)
+        for d in docs:
+            for sent in d:
+                b.add_item(sent)
+            b.end_document()
+        b.finalize(idx.index_file_path(prefix))
+        assert idx.infer_dataset_impl(prefix) == impl
+    flat = [s for d in docs for s in d]
+    views = {"mmap": idx.make_dataset(str(tmp_path / "mmap"), "mmap"), "infer-mmap": idx.make_dataset(str(tmp_path / "mmap"), "infer"),
+             "lazy": idx.make_dataset(str(tmp_path / "cached"), "lazy"), "cached": idx.make_dataset(str(tmp_path / "cached"), "infer")}
+    assert isinstance(views["cached"], idx.IndexedCachedDataset) and isinstance(views["infer-mmap"], idx.MMapIndexedDataset)
+    views["cached"].prefetch(range(0, len(flat), 2))
+    for name, ds in views.items():
+        assert len(ds) == len(flat) and list(ds.sizes) == [len(s) for s in flat], name
+        assert list(ds.doc_idx) == list(np.cumsum([0] + [len(d) for d in docs])), name
+        for i, s in enumerate(flat):
+            assert (ds[i] == s).all() and (ds.get(i, 0, 1) == s[:1]).all(), (name, i)
+            if len(s) > 2:
+                assert (ds.get(i, 1, len(s) - 2) == s[1:-1]).all()
+    # the GPT dataset builds the same samples from either format
+    from b200dist.data.gpt_dataset import build_train_valid_test_datasets
+    out = []
+    for impl, pref in (("mmap", "mmap"), ("lazy", "cached")):
+        tr, va, te = build_train_valid_test_datasets([str(tmp_path / pref)], impl, "8,1,1", [20, 4, 4], 16, 1234, True)
+        out.append([tr[i]["text"].tolist() for i in range(5)])
+    assert out[0] == out[1]

@@ -58,12 +58,12 @@ def main(argv=None):
     p.add_argument("--append-eod", action="store_true")
     p.add_argument("--workers", type=int, default=1)
     p.add_argument("--log-interval", type=int, default=10000)
-    p.add_argument("--dataset-impl", default="mmap", choices=["mmap"])
+    p.add_argument("--dataset-impl", default="mmap", choices=["mmap", "lazy", "cached"])
     a = p.parse_args(argv)
-    from b200dist.data.indexed_dataset import MMapIndexedDatasetBuilder, data_file_path, index_file_path
+    from b200dist.data.indexed_dataset import data_file_path, index_file_path, make_builder
     tok = _build_tok(a)
     dtype = np.uint16 if tok.vocab_size < 65500 else np.int32
-    builders = {k: MMapIndexedDatasetBuilder(data_file_path(f"{a.output_prefix}_{k}_document"), dtype=dtype) for k in a.json_keys}
+    builders = {k: make_builder(data_file_path(f"{a.output_prefix}_{k}_document"), a.dataset_impl, dtype=dtype) for k in a.json_keys}
     t0, nbytes, ndocs = time.time(), 0, 0
     with open(a.input, encoding="utf-8") as fin:
         if a.workers > 1:
