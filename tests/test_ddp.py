@@ -204,3 +204,33 @@ def test_ddp_comm_hooks_and_unused_parameters():
             assert ok and unused_zero and twice, (which, ok, unused_zero, twice)
             if which == "allreduce":
                 assert nseen >= 2
+
+
+def _vs_torch_ddp_worker(rank, world, steps):
+    """our wrapper and torch.nn.parallel.DistributedDataParallel side by side: same init, same per-rank data, same optimizer"""
+    import copy
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    from b200dist.parallel.ddp import DistributedDataParallel as DDP
+    torch.manual_seed(1234 + rank)
+    base = _Tiny()
+    ours = DDP(copy.deepcopy(base), bucket_cap_mb=0.004, first_bucket_cap_mb=0.001)
+    theirs = TorchDDP(copy.deepcopy(base), bucket_cap_mb=0.004)
+    o1 = torch.optim.SGD(ours.parameters(), lr=0.1, momentum=0.9)
+    o2 = torch.optim.SGD(theirs.parameters(), lr=0.1, momentum=0.9)
+    torch.manual_seed(7)
+    X, Y = torch.randn(steps, 8, 16), torch.randint(0, 4, (steps, 8))
+    for s in range(steps):
+        xs, ys = X[s].chunk(world)[rank], Y[s].chunk(world)[rank]
+        for m, o in ((ours, o1), (theirs, o2)):
+            o.zero_grad()
+            nn.functional.cross_entropy(m(xs), ys).backward()
+            o.step()
+    a = torch.cat([p.detach().reshape(-1) for p in ours.module.parameters()])
+    b = torch.cat([p.detach().reshape(-1) for p in theirs.module.parameters()])
+    keys_equal = list(ours.state_dict()) == list(theirs.state_dict())
+    return float((a - b).abs().max()), keys_equal
+
+
+def test_ddp_wrapper_tracks_torch_ddp():
+    for err, keys_equal in run_distributed(_vs_torch_ddp_worker, 2, 5):
+        assert err < 1e-6 and keys_equal
