@@ -83,3 +83,32 @@ def test_cpu_adam_matches_reference_formula(n, adamw, wd, step):
     cpu_adam_(p, m, v, gr, lp, lr=lr, beta1=b1, beta2=b2, eps=eps, wd=wd, step=step, adamw=adamw, threads=2)
     assert torch.allclose(p.double(), want, rtol=2e-5, atol=2e-6)
     assert torch.equal(lp, p.to(torch.bfloat16))
+
+
+@settings(max_examples=12, deadline=None)
+@given(st.sampled_from(["adam", "adamw", "sgd", "sgd_momentum", "adadelta"]), st.floats(0.0, 0.1), st.integers(0, 10 ** 6))
+def test_fused_optimizers_track_torch_optim(kind, wd, seed):
+    """the flat-arena optimizers of optim/fused.py (CPU: the fp32 restatement of the multi-tensor kernels) against torch.optim over
+    several parameter tensors of odd sizes and 4 steps, plus StepLR"""
+    from b200dist.optim import fused
+    g = torch.Generator().manual_seed(seed)
+    shapes = [(7, 5), (13,), (3, 4, 2), (1,)]
+    ps = [torch.randn(*s, generator=g) for s in shapes]
+    a = [torch.nn.Parameter(p.clone()) for p in ps]
+    b = [torch.nn.Parameter(p.clone()) for p in ps]
+    mk = {"adam": (lambda q: fused.Adam(q, lr=1e-2, weight_decay=wd), lambda q: torch.optim.Adam(q, lr=1e-2, weight_decay=wd)),
+          "adamw": (lambda q: fused.AdamW(q, lr=1e-2, weight_decay=wd), lambda q: torch.optim.AdamW(q, lr=1e-2, weight_decay=wd)),
+          "sgd": (lambda q: fused.SGD(q, lr=0.1, weight_decay=wd), lambda q: torch.optim.SGD(q, lr=0.1, weight_decay=wd)),
+          "sgd_momentum": (lambda q: fused.SGD(q, lr=0.1, momentum=0.9, weight_decay=wd), lambda q: torch.optim.SGD(q, lr=0.1, momentum=0.9, weight_decay=wd)),
+          "adadelta": (lambda q: fused.Adadelta(q, lr=1.0, weight_decay=wd), lambda q: torch.optim.Adadelta(q, lr=1.0, weight_decay=wd))}[kind]
+    oa, ob = mk[0](a), mk[1](b)
+    sa, sb = fused.StepLR(oa, 1, 0.7), torch.optim.lr_scheduler.StepLR(ob, 1, 0.7)
+    for _ in range(4):
+        for x, y in zip(a, b):
+            gr = torch.randn(x.shape, generator=g)
+            x.grad, y.grad = gr.clone(), gr.clone()
+        oa.step(); ob.step()
+        sa.step(); sb.step()
+        assert abs(sa.get_last_lr()[0] - sb.get_last_lr()[0]) < 1e-12
+    for x, y in zip(a, b):
+        assert torch.allclose(x, y, rtol=2e-5, atol=2e-6), (kind, (x - y).abs().max())
