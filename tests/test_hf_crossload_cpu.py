@@ -86,3 +86,24 @@ def test_zero3_training_loss_curve_matches_eager_transformers(tmp_path, kind):
         b.append(float(l2.detach()))
     assert all(abs(x - y) < 3e-4 * max(1.0, abs(x)) for x, y in zip(a, b)), (a, b)
     assert len(set(round(x, 4) for x in b)) == 5          # the weights moved: five different batches, five different losses
+
+
+def test_greedy_generation_matches_transformers_generate(tmp_path):
+    """utils/generate.py (prefix re-run, no KV cache) produces the tokens of transformers' cached greedy decoding on the same weights"""
+    from b200dist.ckpt import hf as hf_ckpt
+    from b200dist.utils.generate import generate, sample_next
+    torch.manual_seed(0)
+    ref = _hf_tiny("llama").eval()
+    ref.save_pretrained(str(tmp_path), safe_serialization=True)
+    ours = hf_ckpt.load_pretrained(str(tmp_path)).eval()
+    prompt = torch.randint(3, 512, (2, 5))
+    want = ref.generate(prompt, max_new_tokens=8, do_sample=False, pad_token_id=0)
+    got = generate(ours, prompt, max_new_tokens=8)
+    assert torch.equal(got, want[:, :got.shape[1]])
+    # sampling filters: top-k keeps k candidates, top-p keeps the smallest prefix reaching p
+    lg = torch.tensor([[2.0, 1.0, 0.5, -1.0, -3.0]])
+    g = torch.Generator().manual_seed(1)
+    draws = {int(sample_next(lg, 1.0, top_k=2, generator=g)) for _ in range(50)}
+    assert draws <= {0, 1} and len(draws) == 2
+    draws = {int(sample_next(lg, 1.0, top_p=0.5, generator=g)) for _ in range(50)}
+    assert draws == {0}
