@@ -440,3 +440,32 @@ def test_indexed_dataset_formats_mmap_lazy_cached_infer(tmp_path):
         tr, va, te = build_train_valid_test_datasets([str(tmp_path / pref)], impl, "8,1,1", [20, 4, 4], 16, 1234, True)
         out.append([tr[i]["text"].tolist() for i in range(5)])
     assert out[0] == out[1]
+
+
+def test_dynamic_loss_scale_reproduces_the_reference_trace():
+    """3_training_megatron-lm.ipynb:4347-4348: initial scale 2^32, hysteresis 2; iterations 1-10 all overflow -> the log shows
+    8388608 (2^23) at iteration 10; 8 more skipped iterations by iteration 20 -> 32768 (2^15); then growth after `window` clean steps"""
+    from b200dist.optim.mixed import DynamicGradScaler
+    s = DynamicGradScaler(initial_scale=2.0 ** 32, min_scale=1.0, growth_factor=2.0, backoff_factor=0.5, growth_interval=1000, hysteresis=2)
+    for _ in range(10):
+        s.update(True)
+    assert s.scale == 8388608.0
+    for _ in range(8):
+        s.update(True)
+    assert s.scale == 32768.0
+    s.update(False); s.update(False)
+    assert s.scale == 32768.0
+    sd = s.state_dict()
+    t = DynamicGradScaler(initial_scale=1.0, growth_interval=1000, hysteresis=2)
+    t.load_state_dict(sd)
+    for _ in range(998):
+        t.update(False)
+    assert t.scale == 65536.0                       # 1000 clean steps in total: one growth step
+    t.update(True)                                  # hysteresis was re-armed by the growth: the first overflow does not back off
+    assert t.scale == 65536.0
+    t.update(True)
+    assert t.scale == 32768.0
+    m = DynamicGradScaler(initial_scale=4.0, min_scale=2.0, hysteresis=1)
+    for _ in range(5):
+        m.update(True)
+    assert m.scale == 2.0                           # floor at --min-loss-scale
