@@ -270,3 +270,23 @@ def test_elastic_restart_resumes_from_latest_checkpoint(tmp_path):
     assert its[:4] == [1, 2, 3, 4] and its[-3:] == [4, 5, 6]                 # second attempt starts after the iteration-3 checkpoint
     final = {int(m.group(1)): m.group(2) for m in re.finditer(r"iteration\s+(\d+)/\s*\d+ \|.*?lm loss: ([0-9.E+-]+)", out)}
     assert all(final[i] == full[i] for i in (4, 5, 6)), (final, full)          # same 2-rank job, uninterrupted
+
+
+def test_gpt_fp16_dynamic_loss_scale_skips_then_trains():
+    """--fp16 true (the notebook's spelling, Q10) with a too-large initial loss scale: overflowing iterations are skipped (no lm loss
+    in the line, scheduler not advanced, scale halved), then training proceeds at a scale that fits - the shape of 3_...ipynb:4347-4348"""
+    argv = [a for a in GPT]
+    argv[argv.index("--train-iters") + 1] = "10"
+    argv[argv.index("--lr-decay-iters") + 1] = "10"
+    out = _run("pretrain_gpt.py", argv + ["--fp16", "true", "--initial-loss-scale", "16777216", "--hysteresis", "1"])
+    rows = []
+    for line in out.splitlines():
+        m = re.search(r"iteration\s+(\d+)/.*?learning rate: ([0-9.E+-]+) .*?loss scale: ([0-9.]+) .*?number of skipped iterations:\s+(\d+)", line)
+        if m:
+            rows.append((int(m.group(1)), float(m.group(2)), float(m.group(3)), int(m.group(4)), "lm loss:" in line))
+    assert len(rows) == 10
+    assert rows[0][3] == 1 and not rows[0][4] and rows[0][1] == 0.0 and rows[0][2] == 8388608.0        # skipped: no loss, lr not advanced, scale halved
+    assert rows[-1][3] == 0 and rows[-1][4] and rows[-1][2] < 8388608.0 and rows[-1][1] > 0.0
+    scales = [r[2] for r in rows]
+    assert scales == sorted(scales, reverse=True)
+    assert sum(r[3] for r in rows) >= 3
