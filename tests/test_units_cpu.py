@@ -469,3 +469,30 @@ def test_dynamic_loss_scale_reproduces_the_reference_trace():
     for _ in range(5):
         m.update(True)
     assert m.scale == 2.0                           # floor at --min-loss-scale
+
+
+def test_merge_datasets_tool(tmp_path):
+    import importlib.util
+    import os
+    from b200dist.data import indexed_dataset as idx
+    spec = importlib.util.spec_from_file_location("merge_datasets", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "merge_datasets.py"))
+    tool = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tool)
+    rs = np.random.RandomState(1)
+    all_docs = []
+    for k, impl in enumerate(("mmap", "cached")):
+        prefix = str(tmp_path / f"part{k}")
+        b = idx.make_builder(idx.data_file_path(prefix), impl, dtype=np.uint16)
+        for _ in range(5):
+            doc = [rs.randint(0, 500, size=rs.randint(1, 9)) for _ in range(rs.randint(1, 3))]
+            for s in doc:
+                b.add_item(s)
+            b.end_document()
+            all_docs.append(doc)
+        b.finalize(idx.index_file_path(prefix))
+    n_items, n_docs = tool.merge([str(tmp_path / "part0"), str(tmp_path / "part1")], str(tmp_path / "merged"))
+    ds = idx.make_dataset(str(tmp_path / "merged"), "infer")
+    flat = [s for d in all_docs for s in d]
+    assert n_docs == 10 and n_items == len(flat) == len(ds) and ds[0].dtype == np.uint16
+    assert all((ds[i] == s).all() for i, s in enumerate(flat))
+    assert list(ds.doc_idx) == list(np.cumsum([0] + [len(d) for d in all_docs]))
