@@ -131,7 +131,8 @@ def test_gpt_distributed_saved_activations_tp2():
     plain = _losses(_run("pretrain_gpt.py", base + tp, nproc=2))
     rec = _losses(_run("pretrain_gpt.py", base + tp + ["--recompute-granularity", "full", "--recompute-method", "uniform",
                                                         "--distribute-saved-activations"], nproc=2))
-    assert sorted(plain) == [1, 2, 3] and plain == rec
+    # two separate 2-rank runs: multi-threaded CPU GEMMs are not bit-reproducible across processes, so compare to rounding
+    assert sorted(plain) == [1, 2, 3] == sorted(rec) and all(abs(float(plain[i]) - float(rec[i])) < 2e-5 for i in plain), (plain, rec)
 
 
 def test_gpt_distributed_optimizer_matches_replicated_and_resumes(tmp_path):
@@ -269,7 +270,7 @@ def test_elastic_restart_resumes_from_latest_checkpoint(tmp_path):
     its = [int(m.group(1)) for m in re.finditer(r"iteration\s+(\d+)/", out)]
     assert its[:4] == [1, 2, 3, 4] and its[-3:] == [4, 5, 6]                 # second attempt starts after the iteration-3 checkpoint
     final = {int(m.group(1)): m.group(2) for m in re.finditer(r"iteration\s+(\d+)/\s*\d+ \|.*?lm loss: ([0-9.E+-]+)", out)}
-    assert all(final[i] == full[i] for i in (4, 5, 6)), (final, full)          # same 2-rank job, uninterrupted
+    assert all(abs(float(final[i]) - float(full[i])) < 2e-5 for i in (4, 5, 6)), (final, full)          # same 2-rank job, uninterrupted
 
 
 def test_gpt_fp16_dynamic_loss_scale_skips_then_trains():
