@@ -94,3 +94,8 @@ def train_valid_test_datasets_provider(train_val_test_num_samples):
 if __name__ == "__main__":
     pretrain(train_valid_test_datasets_provider, model_provider, "encoder_or_decoder", forward_step,
              args_defaults={"tokenizer_type": "GPT2BPETokenizer"})
+    # orderly teardown: leaving the process with live communicator threads can abort at interpreter exit
+    # ("terminate called without an active exception") when the peers are already gone
+    if torch.distributed.is_initialized():
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
