@@ -318,7 +318,7 @@ def test_scale_mask_softmax_op_and_module():
     yc = Fn.scaled_upper_triang_masked_softmax(x, 2.0)           # sq < sk: keys j <= i + (sk - sq) visible
     keep = torch.ones(8, 12, dtype=torch.bool).tril(diagonal=4)
     refc = torch.softmax((x * 2.0).masked_fill(~keep, float("-inf")), -1)
-    assert torch.allclose(yc, refc, atol=1e-6) and float(yc[..., 0, 5:].abs().max()) == 0.0
+    assert torch.allclose(yc, refc, atol=1e-6) and float(yc.detach()[..., 0, 5:].abs().max()) == 0.0
     m = Fn.FusedScaleMaskSoftmax(input_in_bf16=True, attn_mask_type="padding", scale=0.5)
     xb = x.detach().to(torch.bfloat16)
     assert m.is_kernel_available(mask, *xb.shape)
