@@ -1,6 +1,6 @@
-"""Bodies of the GPU checks for kernels that were added after the last GPU session of round 1 (csrc/conv.cu, csrc/softmax.cu and
-the modular GPT layer on the GPU).  tests/test_zy_*_gpu.py runs each of them in a CHILD process: a fault in a kernel that has
-never run on hardware must not poison the CUDA context of the pytest process (and with it every test collected later).
+"""Bodies of the GPU checks for csrc/conv.cu, csrc/batchnorm.cu, csrc/softmax.cu and the modular GPT layer on the GPU.
+tests/test_zy_*_gpu.py runs each of them in a CHILD process: a fault in one kernel tier must not poison the CUDA context of the
+pytest process (and with it every test collected later).
 
     python -m tests._zy_checks <name>
 """
@@ -38,7 +38,7 @@ def _conv_one(shape, relu):
     assert torch.allclose(dx, rx, atol=1e-4, rtol=1e-3), (dx - rx).abs().max()
     assert torch.allclose(dw, rw, atol=2e-3, rtol=2e-3), (dw - rw).abs().max()
     assert torch.allclose(db, rb, atol=2e-3, rtol=2e-3), (db - rb).abs().max()
-    assert N.launches() >= before + 3
+    assert N.launches() >= before + 2, "the native conv kernels did not run"     # one C call forward, one backward (dgrad + wgrad)
 
 
 def pool_and_log_softmax():
@@ -148,15 +148,24 @@ def batchnorm_kernels():
                 ref_t.load_state_dict(ref.state_dict())
                 before = N.launches()
                 y = ours(x)
-                r = ref_t(x.float())
-                r = torch.relu(r) if relu else r
+                pre = ref_t(x.float())
+                # fused ReLU: an activation that rounds to +-1e-7 may land on either side of zero in two fp32 implementations; the
+                # oracle takes OUR mask where the pre-activation is within rounding of zero, so one flipped element (whose
+                # gradient is O(1)) cannot fail the comparison, and the mask itself is checked everywhere else
+                if relu:
+                    mask = (y.float() > 0)
+                    sure = pre.detach().abs() > 1e-4 * max(1.0, float(pre.detach().abs().max()))
+                    assert torch.equal(mask[sure], (pre.detach() > 0)[sure]), (dtype, shape, "relu mask")
+                    r = pre * mask
+                else:
+                    r = pre
                 assert N.launches() >= before + 3, "native batch-norm kernels did not run"
                 assert torch.allclose(y.float(), r, atol=tol, rtol=tol), (dtype, shape, relu, (y.float() - r).abs().max())
                 g = torch.randn_like(r)
                 got = torch.autograd.grad(y, (x, ours.weight, ours.bias), g.to(dtype))
-                want = torch.autograd.grad(r, (x, ref_t.weight, ref_t.bias), g)
-                scale = max(1.0, float(want[1].abs().max()))
-                assert torch.allclose(got[0].float(), want[0].float(), atol=tol * 2, rtol=tol * 2), (dtype, shape, relu, "dx")
+                want = torch.autograd.grad(r, (x, ref_t.weight, ref_t.bias), g.to(dtype).float())
+                scale = max(1.0, float(want[1].abs().max()), float(want[2].abs().max()))
+                assert torch.allclose(got[0].float(), want[0].float(), atol=tol * 2, rtol=tol * 2), (dtype, shape, relu, "dx", (got[0].float() - want[0].float()).abs().max())
                 assert torch.allclose(got[1].float(), want[1], atol=tol * 4 * scale, rtol=tol * 4), (dtype, shape, relu, "dgamma")
                 assert torch.allclose(got[2].float(), want[2], atol=tol * 4 * scale, rtol=tol * 4), (dtype, shape, relu, "dbeta")
                 assert torch.allclose(ours.running_mean, ref_t.running_mean, atol=tol) and torch.allclose(ours.running_var, ref_t.running_var, atol=tol * 4, rtol=tol * 4)
