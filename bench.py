@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--comm-backend", default="native", choices=["native", "nccl"])
     ap.add_argument("--dropout", type=float, default=0.0)
     ap.add_argument("--no-clocks", action="store_true")
+    ap.add_argument("--kernel-profile", default="", help="after the timed runs, trace 2 more steps with torch.profiler (CUPTI) on rank 0 and write a per-kernel table here (diagnostic: never a bench value)")
     ap.add_argument("--no-cuda-graph", action="store_true", help="issue every kernel from Python instead of replaying the captured micro-batch graph")
     return ap.parse_args()
 
@@ -216,6 +217,24 @@ def main():
     run(1, hit, True)
     ms_e2e, wall_e2e, last_loss = timed(a.steps, hit, True)
     clocks = sampler.stop() if sampler is not None else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+    if a.kernel_profile:
+        from torch.profiler import profile, ProfilerActivity
+        dist.barrier(); torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            run(2, dit, False)
+            torch.cuda.synchronize()
+        if rank == 0:
+            rows = {}
+            for ev in prof.events():
+                if ev.device_type is not None and "cuda" in str(ev.device_type).lower():
+                    r = rows.setdefault(ev.name, [0, 0.0])
+                    r[0] += 1; r[1] += ev.device_time if hasattr(ev, "device_time") else ev.cuda_time
+            tot = sum(v[1] for v in rows.values())
+            with open(a.kernel_profile, "w") as f:
+                f.write(f"# per-kernel device time over 2 steps (torch.profiler / CUPTI, rank 0): total {tot / 2e3:.3f} ms per step of kernel time\n")
+                for name, (cnt, us) in sorted(rows.items(), key=lambda kv: -kv[1][1]):
+                    f.write(f"{us / 2e3:9.3f} ms/step {100 * us / tot:5.1f}%  x{cnt // 2:5d}  avg {us / cnt:8.1f} us  {name[:150]}\n")
+        dist.barrier()
     sys.stdout = _stdout
     tokens = gbs * a.seq_length
     value = tokens * a.steps / (ms_dev / 1e3)

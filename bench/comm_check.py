@@ -126,7 +126,7 @@ if which in ("all", "ag"):
     ms_n = timeit(lambda: (dist.all_gather_into_tensor(xf, x), N.gemm(xf, W)))
     ms_g = timeit(lambda: N.gemm(xf, W))
     p0(f"time ag_gemm rows/rank {rows} K{K} N{Nn}: fused {ms:.3f} ms | nccl all_gather + gemm {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms (host-issue bound)")
-    for (rows, K, Nn, tag) in [(6144, 768, 1152, "qkv"), (6144, 768, 1536, "fc1"), (6144, 768, 16384, "logits")]:
+    for (rows, K, Nn, tag) in [(6144, 768, 1152, "qkv"), (6144, 768, 1536, "fc1"), (6144, 768, 16384, "logits"), (12288, 768, 1152, "qkv"), (12288, 768, 1536, "fc1")]:
         x = F.shard_buffer(rows, K, torch.bfloat16); x.normal_()
         W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
         xf = torch.randn(rows * world, K, device=dev, dtype=torch.bfloat16)
@@ -154,6 +154,21 @@ if which in ("all", "rs"):
         out3 = F.gemm_rs(a, W, b_mn=bmn, bias=bias, residual=res)
         torch.cuda.synchronize()
         report(f"gemm_rs (3rd call) M{M}", out3, ref, 3e-2)
+    # back-to-back calls with fresh inputs every time (a signal that overtook its data would show up as a stale partial)
+    M, K, Nn = 12288, 384, 768
+    W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16) * 0.05
+    outs, refs = [], []
+    for it in range(24):
+        torch.manual_seed(1000 + 17 * it + rank)
+        a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+        outs.append(F.gemm_rs(a, W))
+        part = a.float() @ W.float().t()
+        dist.all_reduce(part)
+        refs.append(part[rank * (M // world):(rank + 1) * (M // world)])
+    torch.cuda.synchronize()
+    worst = max((o.float() - r).abs().max().item() for o, r in zip(outs, refs))
+    report("gemm_rs 24 back-to-back calls, fresh data (worst)", torch.full((1,), worst, device=dev), torch.zeros(1, device=dev), 8e-2)
+    del outs, refs
     M, K, Nn = 12288, 1536, 768
     a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
     o = torch.empty(M // world, Nn, device=dev, dtype=torch.bfloat16)
@@ -161,7 +176,7 @@ if which in ("all", "rs"):
     ms_n = timeit(lambda: dist.reduce_scatter_tensor(o, N.gemm(a, W)))
     ms_g = timeit(lambda: N.gemm(a, W))
     p0(f"time gemm_rs M{M} K{K} N{Nn}: fused {ms:.3f} ms | gemm + nccl reduce_scatter {ms_n:.3f} ms | gemm alone {ms_g:.3f} ms (host-issue bound)")
-    for (M, K, Nn, tag) in [(12288, 384, 768, "proj"), (12288, 1536, 768, "fc2")]:
+    for (M, K, Nn, tag) in [(12288, 384, 768, "proj"), (12288, 1536, 768, "fc2"), (24576, 384, 768, "proj"), (24576, 1536, 768, "fc2")]:
         a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
         gf = graph_time(lambda: F.gemm_rs(a, W))
         gg = graph_time(lambda: N.gemm(a, W))

@@ -28,27 +28,38 @@ def show(tag, ncomm=0):
             print("  comm CTAs: start", summ(0, cr), "| first peer ready", summ(1, cr), "| pulls done", summ(2, cr))
             print("  gemm CTAs: start", summ(0, gr), "| tiles done", summ(1, gr), "| exit", summ(4, gr))
         else:
-            print("  start", summ(0, allr), "| gemm tiles done", summ(1, allr), "| last signal sent", summ(2, allr))
-            print("  first reduce item ready", summ(3, allr), "| reduce done/exit", summ(4, allr))
+            print("  start", summ(0, allr), "| owed signal sent before own tile", summ(7, allr), "| own-tile wait begins", summ(3, allr), "| own-tile wait ends", summ(6, allr))
+            print("  tile loop done", summ(1, allr), "| last signal sent", summ(2, allr), "| CTA exit", summ(4, allr))
         print("  kernel complete (last CTA)", summ(5, allr))
 
-rows, K, Nn = 6144, 768, 1536
-x = F.shard_buffer(rows, K, torch.bfloat16); x.normal_()
-W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
-for i in range(3):
-    F.ag_gemm(x, W)
-torch.cuda.synchronize(); dist.barrier()
-L.b2_fused_set_debug(N.c_p(dbg.data_ptr()))
-dbg.zero_(); F.ag_gemm(x, W); torch.cuda.synchronize(); dist.barrier()
-show("ag_gemm fc1 rows/rank 6144 K768 N1536", ncomm=24)
-M, K, Nn = 12288, 1536, 768
-a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
-L.b2_fused_set_debug(None)
-for i in range(3):
-    F.gemm_rs(a, W)
-torch.cuda.synchronize(); dist.barrier()
-L.b2_fused_set_debug(N.c_p(dbg.data_ptr()))
-dbg.zero_(); F.gemm_rs(a, W); torch.cuda.synchronize(); dist.barrier()
-show("gemm_rs fc2 M12288 K1536 N768")
-L.b2_fused_set_debug(None)
+def trace_ag(rows, K, Nn, tag):
+    x = F.shard_buffer(rows, K, torch.bfloat16); x.normal_()
+    W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+    L.b2_fused_set_debug(None)
+    for i in range(3):
+        F.ag_gemm(x, W)
+    torch.cuda.synchronize(); dist.barrier()
+    L.b2_fused_set_debug(N.c_p(dbg.data_ptr()))
+    dbg.zero_(); F.ag_gemm(x, W); torch.cuda.synchronize(); dist.barrier()
+    show(f"ag_gemm {tag} rows/rank {rows} K{K} N{Nn}", ncomm=int(os.environ.get("B2_FUSED_NCOMM", "16")))
+    L.b2_fused_set_debug(None)
+
+
+def trace_rs(M, K, Nn, tag):
+    a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+    L.b2_fused_set_debug(None)
+    for i in range(3):
+        F.gemm_rs(a, W)
+    torch.cuda.synchronize(); dist.barrier()
+    L.b2_fused_set_debug(N.c_p(dbg.data_ptr()))
+    dbg.zero_(); F.gemm_rs(a, W); torch.cuda.synchronize(); dist.barrier()
+    show(f"gemm_rs {tag} M{M} K{K} N{Nn}")
+    L.b2_fused_set_debug(None)
+
+
+trace_ag(6144, 768, 1536, "fc1")
+trace_ag(12288, 768, 1536, "fc1")
+trace_rs(12288, 384, 768, "proj")
+trace_rs(24576, 384, 768, "proj")
+trace_rs(24576, 1536, 768, "fc2")
 dist.barrier(); dist.destroy_process_group()

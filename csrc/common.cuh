@@ -318,6 +318,50 @@ B2_DEVICE void red_release_sys_add(uint32_t* p, uint32_t v) {
   asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+B2_DEVICE void red_release_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+B2_DEVICE void red_relaxed_gpu_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+B2_DEVICE void red_relaxed_sys_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+B2_DEVICE unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory");
+  return t;
+}
+// Every wait on a flag that ANOTHER GPU (or another CTA of a co-resident grid) writes is bounded: a peer that faulted or was
+// never launched must not hang this GPU.  After B2_SPIN_TIMEOUT_NS the waiter records where it gave up and traps, which
+// surfaces as a launch failure on the host instead of a stuck device.
+#ifndef B2_SPIN_TIMEOUT_NS
+#define B2_SPIN_TIMEOUT_NS 4000000000ull
+#endif
+static __device__ unsigned int g_b2_spin_timeout_site;      // last site id that timed out in this translation unit (0 = none)
+B2_DEVICE void spin_timeout(unsigned int site) {
+  g_b2_spin_timeout_site = site;
+  __threadfence_system();
+  __trap();
+}
+// wait until (int32)(*p - target) >= 0 with system-scope acquire loads
+B2_DEVICE void wait_ge_sys(const uint32_t* p, uint32_t target, unsigned int site) {
+  if (static_cast<int32_t>(ld_acquire_sys(p) - target) >= 0) return;
+  const unsigned long long t0 = globaltimer_ns();
+  uint32_t polls = 0;
+  while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
+    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > B2_SPIN_TIMEOUT_NS) spin_timeout(site);
+  }
+}
+B2_DEVICE void wait_ge_gpu(const uint32_t* p, uint32_t target, unsigned int site) {
+  if (static_cast<int32_t>(ld_acquire_gpu(p) - target) >= 0) return;
+  const unsigned long long t0 = globaltimer_ns();
+  uint32_t polls = 0;
+  while (static_cast<int32_t>(ld_acquire_gpu(p) - target) < 0) {
+    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > B2_SPIN_TIMEOUT_NS) spin_timeout(site);
+  }
+}
+
 B2_DEVICE uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);

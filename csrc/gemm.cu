@@ -53,9 +53,10 @@ struct GemmParams {
   void* f_peer[8];                 // AG: every rank's shard (symmetric)   RS: unused
   uint32_t* f_ctrl[8];             // control block of the symmetric buffer on every rank
   uint8_t* f_xg;                   // AG: local gathered operand [M, K]
-  uint32_t* f_flags;               // AG: local per-row-block ready epochs
+  uint32_t* f_flags;               // AG: local per-row-block arrival counters (pieces landed, cumulative over calls)
+  int f_npb;                       // AG: 32 KB pieces per 128-row block
   uint32_t* f_cnt[8];              // RS: per-row-block arrival counters on every rank (symmetric)
-  const CUtensorMap* f_rsmaps;     // RS: device array [2 parity][world] of staging-slot tensor maps
+  uint8_t* f_stage_peer[8];        // RS: every rank's staging buffer (symmetric): [2 parity][world sources][slot]
   const void* f_stage;             // RS: this rank's staging [2][world][shard_rows, N]
   void* f_out;                     // RS: reduced output shard [shard_rows, N]
   long long f_ld_out;
@@ -68,7 +69,7 @@ struct GemmParams {
 B2_DEVICE void dbg_stamp(const GemmParams& p, int k) {
   if (p.f_dbg != nullptr) {
     unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory");
     p.f_dbg[blockIdx.x * 8 + k] = t;
   }
 }
@@ -86,59 +87,21 @@ B2_DEVICE void bulk_s2g(void* gdst, const void* smem_src, uint32_t bytes) {
                ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
 }
 
-// All-gather CTA of the fused AG->GEMM kernel: one thread streams 128-row blocks of every rank's shard
-// (own shard first, then rank+1, ...) through a shared-memory ring with bulk async copies - peer memory is
-// read over NVLink exactly once - into the local gathered operand, and publishes each block to the GEMM
-// CTAs of this GPU with a device-scope release of the call epoch.
-// cursor over the (source rank, 128-row block, 32 KB piece) sequence one all-gather CTA is responsible for:
-// remote shards first (rank+1, rank+2, ...), the local shard last (GEMM CTAs read local rows in place)
-struct AgCursor {
-  int si, blk, piece, npieces;
-  long long bytes;
-  B2_DEVICE void seek(const GemmParams& p, int c) {       // advance (si, blk) to the next block owned by CTA c
-    while (si <= p.f_world - 1) {
-      if (si == p.f_world - 1) return;                    // exhausted (only the world-1 REMOTE shards are pulled)
-      if (blk < p.f_bpr && (si * p.f_bpr + blk) % p.f_ncomm == c) break;
-      if (++blk >= p.f_bpr) { blk = 0; ++si; }
-    }
-    const int rows = min(128, p.f_shard_rows - blk * 128);
-    bytes = static_cast<long long>(rows) * p.f_row_bytes;
-    npieces = static_cast<int>((bytes + 32767) / 32768);
-    piece = 0;
-  }
-  B2_DEVICE bool done(const GemmParams& p) const { return si >= p.f_world - 1; }
-  B2_DEVICE int src(const GemmParams& p) const { return (p.f_rank + 1 + si) % p.f_world; }
-  B2_DEVICE void next(const GemmParams& p, int c) {
-    if (++piece >= npieces) { if (++blk >= p.f_bpr) { blk = 0; ++si; } seek(p, c); }
-  }
-};
-
-// All-gather CTA of the fused AG->GEMM kernel: one thread streams 128-row blocks of every rank's shard through
-// a shared-memory ring with bulk async copies - peer memory is read over NVLink exactly once - into the local
-// gathered operand, and publishes each block to the GEMM CTAs of this GPU with a device-scope release of the
-// call epoch.  Loads run LA pieces ahead of stores in one continuous pipeline across blocks; a block's flag is
-// published as soon as its last store group has completed (checked two groups later, so nothing drains).
+// All-gather CTAs of the fused AG->GEMM kernel.  The remote shards are cut into 32 KB pieces that are dealt round-robin
+// over the `f_ncomm` all-gather CTAs IN ROW ORDER (piece g goes to CTA g % f_ncomm), so the 128-row blocks of the gathered
+// operand complete one after the other, in exactly the order in which the GEMM CTAs consume them - not in f_ncomm-wide
+// waves.  One thread per CTA drives a 7-stage ring: 1-D bulk copy peer shard -> shared memory (NVLink is read exactly
+// once), bulk copy shared memory -> local gathered operand; a piece that has landed adds 1 to its block's arrival counter
+// (release, device scope); a GEMM CTA may load a block once its counter has reached epoch * pieces-per-block.
+// This rank's OWN shard reaches the gathered operand (the backward's wgrad reads it there; this kernel's GEMM reads own
+// rows in place) through the two otherwise idle warps of every GEMM CTA - a slow background copy spread over the whole
+// kernel, so its HBM traffic never competes with the NVLink stream in bursts (copying it from the all-gather CTAs cut the
+// pull rate from ~600 to ~470 GB/s; copying it after the pulls left a 20-30 us tail).
 B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t epoch) {
-  constexpr int STG = 7, LA = 5;
+  constexpr int STG = 7, LA = 6, PUB = 3;
   constexpr uint32_t PIECE = 32 * 1024;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STG * PIECE);
   uint32_t* my_ctrl = p.f_ctrl[p.f_rank];
-  if (threadIdx.x >= 32) {
-    // warps 1..7: copy this rank's OWN shard into the gathered operand (needed by backward's wgrad, not by the
-    // GEMM of this kernel, which reads own rows in place) - plain coalesced 16-byte copies, off the critical path
-    const int t = threadIdx.x - 32, nt = NUM_THREADS - 32;   // warps 1..11
-    const uint4* src = static_cast<const uint4*>(p.f_peer[p.f_rank]);
-    uint4* dst = reinterpret_cast<uint4*>(p.f_xg + static_cast<long long>(p.f_rank) * p.f_shard_rows * p.f_row_bytes);
-    const long long total = static_cast<long long>(p.f_shard_rows) * p.f_row_bytes / 16;
-    const long long per = (total + p.f_ncomm - 1) / p.f_ncomm;
-    const long long v0 = per * c, v1 = v0 + per < total ? v0 + per : total;
-    long long v = v0 + t;
-    for (; v + 3LL * nt < v1; v += 4LL * nt) {
-      const uint4 q0 = src[v], q1 = src[v + nt], q2 = src[v + 2LL * nt], q3 = src[v + 3LL * nt];
-      dst[v] = q0; dst[v + nt] = q1; dst[v + 2LL * nt] = q2; dst[v + 3LL * nt] = q3;
-    }
-    for (; v < v1; v += nt) dst[v] = src[v];
-  }
   if (threadIdx.x == 0) {
     for (int i = 0; i < STG; ++i) mbar_init(&bars[i], 1);
     mbar_fence_init();
@@ -148,62 +111,63 @@ B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t e
         if (r != p.f_rank) st_release_sys(p.f_ctrl[r] + FCTRL_A + p.f_rank, epoch);
     }
     dbg_stamp(p, 0);
-    AgCursor ld{0, 0, 0, 0, 0}, st{0, 0, 0, 0, 0};
-    ld.seek(p, c); st.seek(p, c);
-    uint32_t issued = 0, stored = 0;
-    int ready_src = -1;
-    uint32_t* pend_flag = nullptr; uint32_t pend_mark = 0;
-    while (!st.done(p)) {
-      // ---- issue loads up to LA pieces ahead of the store cursor
-      while (!ld.done(p) && issued - stored < LA) {
-        const int src = ld.src(p);
-        if (src != p.f_rank && src != ready_src) {
-          while (static_cast<int32_t>(ld_acquire_sys(my_ctrl + FCTRL_A + src) - epoch) < 0) { }
-          if (ready_src < 0) dbg_stamp(p, 1);
-          ready_src = src;
+    const long long blk_bytes = 128LL * p.f_row_bytes;
+    const int npb = p.f_npb;
+    const long long total = static_cast<long long>(p.f_world - 1) * p.f_bpr * npb;     // pieces of all remote shards
+    const long long mine = total > c ? (total - c + p.f_ncomm - 1) / p.f_ncomm : 0;    // pieces c, c + ncomm, ...
+    long long issued = 0, stored = 0, published = 0;
+    int ready_upto = 0;                              // sources (rank+1 ... rank+ready_upto) known to be complete
+    uint32_t* pub[PUB];
+    auto locate = [&](long long k, int& src, long long& off, uint32_t& sz, uint32_t*& flag) {
+      const long long g = c + k * p.f_ncomm;
+      const long long bi = g / npb;
+      const int pc = static_cast<int>(g - bi * npb);
+      const int si = static_cast<int>(bi / p.f_bpr), blk = static_cast<int>(bi - static_cast<long long>(si) * p.f_bpr);
+      src = (p.f_rank + 1 + si) % p.f_world;
+      off = blk * blk_bytes + static_cast<long long>(pc) * PIECE;
+      const long long left = blk_bytes - static_cast<long long>(pc) * PIECE;
+      sz = left < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left) : PIECE;
+      flag = p.f_flags + src * p.f_bpr + blk;
+    };
+    // the piece's bulk store has COMPLETED (cp.async.bulk.wait_group, not .read): its bytes are in L2, which is where the GEMM
+    // CTAs' TMA loads read them.  A relaxed add is enough - a release here costs a MEMBAR that also waits for this thread's
+    // outstanding NVLink loads (measured: 2.7 us per piece, pull rate 196 GB/s instead of ~460)
+    auto publish = [&](uint32_t* flag) { red_relaxed_gpu_add(flag, 1u); };
+    while (stored < mine) {
+      while (issued < mine && issued - stored < LA) {
+        int src; long long off; uint32_t sz; uint32_t* flag;
+        locate(issued, src, off, sz, flag);
+        const int si = (src - p.f_rank - 1 + p.f_world) % p.f_world;
+        while (ready_upto <= si) {                   // the source's shard must be complete before the first pull from it
+          const int r = (p.f_rank + 1 + ready_upto) % p.f_world;
+          wait_ge_sys(my_ctrl + FCTRL_A + r, epoch, 0x101);
+          if (ready_upto == 0) dbg_stamp(p, 1);
+          ++ready_upto;
         }
-        const uint32_t s = issued % STG;
-        if (issued >= STG) tma_store_wait_read<STG - LA - 1>();     // the store that last used this slot has drained
-        const long long left = ld.bytes - static_cast<long long>(ld.piece) * PIECE;
-        const uint32_t sz = left < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left) : PIECE;
-        const uint8_t* gsrc = static_cast<const uint8_t*>(p.f_peer[src]) + static_cast<long long>(ld.blk) * 128 * p.f_row_bytes +
-                              static_cast<long long>(ld.piece) * PIECE;
+        const uint32_t s = static_cast<uint32_t>(issued % STG);
+        if (issued >= STG) tma_store_wait_read<STG - LA - 1>();     // the store that last used this slot has been read out
         mbar_expect_tx(&bars[s], sz);
-        bulk_g2s(smem + s * PIECE, gsrc, sz, &bars[s]);
+        bulk_g2s(smem + s * PIECE, static_cast<const uint8_t*>(p.f_peer[src]) + off, sz, &bars[s]);
         ++issued;
-        ld.next(p, c);
       }
-      // ---- store one piece
       {
-        const int src = st.src(p);
-        const uint32_t s = stored % STG;
-        mbar_wait(&bars[s], (stored / STG) & 1);
-        const long long left = st.bytes - static_cast<long long>(st.piece) * PIECE;
-        const uint32_t sz = left < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left) : PIECE;
-        uint8_t* gdst = p.f_xg + (static_cast<long long>(src) * p.f_shard_rows + static_cast<long long>(st.blk) * 128) * p.f_row_bytes +
-                        static_cast<long long>(st.piece) * PIECE;
-        bulk_s2g(gdst, smem + s * PIECE, sz);
+        int src; long long off; uint32_t sz; uint32_t* flag;
+        locate(stored, src, off, sz, flag);
+        const uint32_t s = static_cast<uint32_t>(stored % STG);
+        mbar_wait(&bars[s], static_cast<uint32_t>(stored / STG) & 1);
+        bulk_s2g(p.f_xg + static_cast<long long>(src) * p.f_shard_rows * p.f_row_bytes + off, smem + s * PIECE, sz);
         tma_store_commit();
+        pub[stored % PUB] = flag;
         ++stored;
-        const bool last_piece = (st.piece == st.npieces - 1);
-        uint32_t* this_flag = p.f_flags + src * p.f_bpr + st.blk;
-        if (pend_flag != nullptr && (last_piece || stored - pend_mark >= 2)) {
-          if (stored - pend_mark >= 2) tma_store_wait_all<2>(); else tma_store_wait_all<0>();
-          fence_proxy_async_all();
-          __threadfence();
-          st_release_gpu(pend_flag, epoch);
-          pend_flag = nullptr;
+        if (stored - published >= PUB) {             // the store issued PUB - 1 groups ago has certainly completed
+          tma_store_wait_all<PUB - 1>();
+          publish(pub[published % PUB]);
+          ++published;
         }
-        if (last_piece) { pend_flag = this_flag; pend_mark = stored; }
-        st.next(p, c);
       }
     }
     tma_store_wait_all<0>();
-    if (pend_flag != nullptr) {
-      fence_proxy_async_all();
-      __threadfence();
-      st_release_gpu(pend_flag, epoch);
-    }
+    for (; published < stored; ++published) publish(pub[published % PUB]);
     // all of this CTA's pulls are done; the last all-gather CTA tells every peer "I no longer read your shard"
     dbg_stamp(p, 2);
     __threadfence_system();
@@ -231,7 +195,7 @@ B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers
     if (wait_peers_done) {
       for (int r = 0; r < p.f_world; ++r)
         if (r != p.f_rank)
-          while (static_cast<int32_t>(ld_acquire_sys(my_ctrl + FCTRL_B + r) - epoch) < 0) { }
+          wait_ge_sys(my_ctrl + FCTRL_B + r, epoch, 0x102);
     }
     my_ctrl[2] = 0u;
     my_ctrl[1] = epoch;
@@ -301,16 +265,17 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmC2,
                     const GemmParams p, const __grid_constant__ CUtensorMap tmA2 /* AG: this rank's own shard */) {
-  static_assert(!CTA2 || FUSE == FUSE_NONE, "the fused collectives run single-CTA tiles");
   constexpr int BN_LOAD = CTA2 ? BN / 2 : BN;     // B rows staged by this CTA
   constexpr int BM_TILE = CTA2 ? 2 * BM : BM;     // rows per scheduled tile
   constexpr int A_BYTES = BM * BK * 2;
   constexpr int B_BYTES = BN_LOAD * BK * 2;
   constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  // plain / pair kernels give two 16 KB tiles of the operand ring to the epilogue's aux prefetch (residual / pre-activation
-  // tiles arrive by TMA one chunk ahead instead of row-strided global loads); the fused-collective kernels keep the full ring
-  constexpr bool AUX_TMA = (FUSE == FUSE_NONE);
-  constexpr int RING_BYTES = AUX_TMA ? SMEM_MAIN_BYTES - 2 * STAGE_CHUNK_BYTES : SMEM_MAIN_BYTES;
+  // two 16 KB tiles of the operand ring go to the epilogue's aux prefetch (residual / pre-activation tiles arrive by TMA
+  // one chunk ahead instead of row-strided global loads); GEMM->RS adds its residual after the reduction and keeps the full ring
+  constexpr bool AUX_TMA = (FUSE != FUSE_RS);
+  // GEMM->RS: four 16 KB push buffers (two per epilogue team) between the epilogue and the push warp come out of the ring
+  constexpr int RS_PUSH_BUFS = 4;
+  constexpr int RING_BYTES = AUX_TMA ? SMEM_MAIN_BYTES - 2 * STAGE_CHUNK_BYTES : SMEM_MAIN_BYTES - RS_PUSH_BUFS * STAGE_CHUNK_BYTES;
   constexpr int STAGES = RING_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
   // two epilogue teams everywhere; in GEMM->RS each team leader signals its own half of every tile, so a row block
@@ -329,6 +294,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tmem_empty = bars + 2 * STAGES + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   [[maybe_unused]] uint64_t* aux_bar = bars + 2 * STAGES + 5;   // [2]
+  // GEMM->RS push queue: epilogue team T fills push buffer 2T + (its push count & 1), the push warp sends it over NVLink
+  [[maybe_unused]] uint8_t* push_bufs = smem + RING_BYTES;
+  [[maybe_unused]] uint64_t* pfull = bars + 2 * STAGES + 7;      // [RS_PUSH_BUFS]
+  [[maybe_unused]] uint64_t* pempty = pfull + RS_PUSH_BUFS;      // [RS_PUSH_BUFS]
+  struct PushMeta { uint8_t* dst; uint32_t* cnt; };
+  [[maybe_unused]] PushMeta* pmeta = reinterpret_cast<PushMeta*>(pempty + RS_PUSH_BUFS);   // [RS_PUSH_BUFS]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -340,9 +311,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if constexpr (FUSE != FUSE_NONE) {
     f_epoch = p.f_ctrl[p.f_rank][1] + 1;
     if constexpr (FUSE == FUSE_AG) {
-      nctas = gridDim.x - p.f_ncomm;
-      cta0 = static_cast<int>(blockIdx.x) - p.f_ncomm;
-      if (cta0 < 0) {                                     // all-gather CTAs (lowest block ids: scheduled first);
+      // pair kernels: f_ncomm is even, so a cluster is either two all-gather CTAs or one GEMM pair
+      nctas = (static_cast<int>(gridDim.x) - p.f_ncomm) / (CTA2 ? 2 : 1);
+      cta0 = (static_cast<int>(blockIdx.x) - p.f_ncomm) / (CTA2 ? 2 : 1);
+      if (static_cast<int>(blockIdx.x) < p.f_ncomm) {     // all-gather CTAs (lowest block ids: scheduled first);
         ag_comm_cta(p, smem, blockIdx.x, f_epoch);         // they never touch TMEM / the MMA pipeline
         fused_finish(p, f_epoch, true);
         return;
@@ -366,6 +338,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS * (CTA2 ? 2 : 1));   // pair: both CTAs' epilogue threads (leader's copy)
     }
     if constexpr (AUX_TMA) { mbar_init(&aux_bar[0], 1); mbar_init(&aux_bar[1], 1); }
+    if constexpr (FUSE == FUSE_RS) { for (int i = 0; i < RS_PUSH_BUFS; ++i) { mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1); } }
     mbar_fence_init();
   }
   if (warp == 2) { if constexpr (CTA2) tmem_alloc_2sm<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot); }
@@ -390,9 +363,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int kb1 = min(p.num_kb, kb0 + p.kb_per_split);
         [[maybe_unused]] bool a_local = false;
         if constexpr (FUSE == FUSE_AG) {
-          a_local = (tm / p.f_bpr == p.f_rank);          // own rows: read in place from the shard, no waiting
+          const int rb = m0 / BM;                        // the 128-row block this CTA stages (pair: each CTA its own half)
+          a_local = (rb / p.f_bpr == p.f_rank);          // own rows: read in place from the shard, no waiting
           if (!a_local) {                                // remote rows must have landed in the gathered operand
-            while (static_cast<int32_t>(ld_acquire_gpu(p.f_flags + tm) - f_epoch) < 0) { }
+            wait_ge_gpu(p.f_flags + rb, f_epoch * static_cast<uint32_t>(p.f_npb), 0x103);
             fence_proxy_async_all();
           }
         }
@@ -406,7 +380,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (cta_rank == 0) mbar_expect_tx(&full_bar[stage], 2 * STAGE_BYTES);
             else               mbar_arrive_cluster(lbar);
             if constexpr (!A_MN) {
-              tma_load_2d_2sm(sA, &tmA, lbar, kb * BK, m0);
+              if constexpr (FUSE == FUSE_AG) {
+                if (a_local) tma_load_2d_2sm(sA, &tmA2, lbar, kb * BK, m0 - p.f_rank * p.f_shard_rows);
+                else         tma_load_2d_2sm(sA, &tmA, lbar, kb * BK, m0);
+              } else {
+                tma_load_2d_2sm(sA, &tmA, lbar, kb * BK, m0);
+              }
             } else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j) tma_load_2d_2sm(sA + j * (BK * 128), &tmA, lbar, m0 + j * 64, kb * BK);
@@ -487,6 +466,65 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
     }
+  } else if (FUSE == FUSE_RS && warp == 3) {
+    // ===================== GEMM->RS push warp =====================
+    // One thread sends the partial-tile chunks that the epilogue teams park in the push buffers to the rank that owns the
+    // rows (ONE 16 KB bulk copy each, the swizzled tile verbatim), keeps at most four in flight, and - as each copy
+    // COMPLETES - adds 1 to the owner's arrival counter of that row block and hands the buffer back.  The epilogue teams
+    // therefore never wait for NVLink, only for a free buffer, and nobody on this GPU ever waits for a peer while a signal
+    // is still owed (the pushes depend on nothing remote).
+    if (lane == 0) {
+      constexpr int NCH = BN / 64;
+      uint32_t q[TEAMS] = {0u, 0u};
+      uint32_t issued = 0, retired = 0;
+      int fifo[4];
+      // the chunk's bulk copy has COMPLETED (cp.async.bulk.wait_group without .read: the write is performed at the owner),
+      // so a relaxed add that is issued afterwards cannot overtake it; a system-scope fence here would also wait for the
+      // copies still in flight and cut the push rate in half (measured)
+      auto retire = [&]() {
+        const int slot = fifo[retired & 3];
+        red_relaxed_sys_add(pmeta[slot].cnt, 1u);
+        mbar_arrive(&pempty[slot]);
+        ++retired;
+      };
+      for (int t = cta0; t < total_tiles; t += nctas) {
+        int tm, tn, ks;
+        decode_tile(p, t, tm, tn, ks);
+        const int rb = (tm * BM_TILE + static_cast<int>(cta_rank) * BM) / BM;
+        if (rb / p.f_bpr == p.f_rank) continue;            // own rows: reduced and stored by the epilogue itself
+        for (int c = 0; c < NCH; ++c) {
+          if (tn * BN + c * 64 >= p.N) break;
+          const int team = c % TEAMS;
+          const int slot = team * 2 + static_cast<int>(q[team] & 1u);
+          mbar_wait(&pfull[slot], (q[team] >> 1) & 1u);
+          ++q[team];
+          bulk_s2g(pmeta[slot].dst, push_bufs + slot * STAGE_CHUNK_BYTES, STAGE_CHUNK_BYTES);
+          tma_store_commit();
+          fifo[issued & 3] = slot;
+          ++issued;
+          if (issued - retired > 3) { tma_store_wait_all<3>(); retire(); }
+        }
+      }
+      tma_store_wait_all<0>();
+      while (retired < issued) retire();
+      dbg_stamp(p, 2);
+    }
+  } else if (FUSE == FUSE_AG && (warp == 2 || warp == 3)) {
+    // ===================== own shard -> gathered operand (background copy, see ag_comm_cta) =====================
+    const long long nthr = static_cast<long long>(gridDim.x - p.f_ncomm) * 64;
+    const long long tid = static_cast<long long>(blockIdx.x - p.f_ncomm) * 64 + (warp - 2) * 32 + lane;
+    const uint4* src = static_cast<const uint4*>(p.f_peer[p.f_rank]);
+    uint4* dst = reinterpret_cast<uint4*>(p.f_xg + static_cast<long long>(p.f_rank) * p.f_shard_rows * p.f_row_bytes);
+    const long long total = static_cast<long long>(p.f_shard_rows) * p.f_row_bytes / 16;
+    long long v = tid;
+    for (; v + 7 * nthr < total; v += 8 * nthr) {
+      uint4 q[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) q[j] = __ldg(src + v + j * nthr);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) dst[v + j * nthr] = q[j];
+    }
+    for (; v < total; v += nthr) dst[v] = __ldg(src + v);
   } else if (warp >= EPI_WARP0 && warp < EPI_WARP0 + 4 * TEAMS) {
     // ===================== epilogue =====================
     const int team = (warp - EPI_WARP0) >> 2;      // chunks team, team + TEAMS, ... of every tile
@@ -498,7 +536,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int fmt = p.fmt;
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
-    [[maybe_unused]] int rs_groups = 0, rs_prev_owner = -1, rs_prev_blk = 0;   // GEMM->RS: deferred arrival signal
+    [[maybe_unused]] uint32_t rs_pq = 0;       // GEMM->RS: chunks this team has handed to the push warp
     // ---- aux tile prefetch (AUX_TMA): the team leader keeps ONE 16 KB TMA load in flight, for the next chunk this team
     // will process; (aux_t, aux_c) is that chunk.  The consumer waits on the team's mbarrier, copies its 128-byte row
     // out of the swizzled tile, and after the team barrier the leader issues the following chunk's load.
@@ -577,19 +615,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         constexpr int NCH = BN / 64;
         const bool dual = (p.epilogue == B2_EPI_BIAS_GELU_DUAL);
         [[maybe_unused]] bool rs_own = false;
+        [[maybe_unused]] const int rb = m0 / BM;                 // this CTA's 128-row block (pair: its half of the 256-row tile)
+        [[maybe_unused]] const int rs_owner = (FUSE == FUSE_RS) ? rb / p.f_bpr : 0;
+        [[maybe_unused]] const int rs_lblk = (FUSE == FUSE_RS) ? rb - rs_owner * p.f_bpr : 0;
         if constexpr (FUSE == FUSE_RS) {
-          rs_own = (tm / p.f_bpr == p.f_rank);
+          rs_own = (rs_owner == p.f_rank);
           if (rs_own) {          // every peer's partial tiles of this row block must have arrived
             if (leader) {
-              if (rs_prev_owner >= 0) {   // never wait on peers while still owing them a signal (deadlock otherwise)
-                tma_store_wait_all<0>();
-                __threadfence_system();
-                red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
-                rs_prev_owner = -1;
-              }
-              const uint32_t expected = f_epoch * static_cast<uint32_t>((p.f_world - 1) * p.tiles_n * TEAMS);
-              const uint32_t* cnt = p.f_cnt[p.f_rank] + (tm - p.f_rank * p.f_bpr);
-              while (static_cast<int32_t>(ld_acquire_sys(cnt) - expected) < 0) { }
+              // one arrival per 64-column chunk and peer (sent by the peers' push warps, which wait for nothing remote)
+              const uint32_t expected = f_epoch * static_cast<uint32_t>((p.f_world - 1) * ((p.N + 63) >> 6));
+              const uint32_t* cnt = p.f_cnt[p.f_rank] + rs_lblk;
+              if (team == 0) dbg_stamp(p, 3);
+              wait_ge_sys(cnt, expected, 0x104);
+              if (team == 0) dbg_stamp(p, 6);
             }
             named_bar_sync(bar_id, EPI_THREADS);
           }
@@ -647,13 +685,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               // rows owned by this rank are computed LAST: the peers' partial tiles already sit in the local
               // staging slots, so the reduction (+ bias + residual) happens right here and the result goes
               // straight to the output shard - no separate reduce pass, no staging round trip of the own partial
-              const int lrow = (tm - p.f_rank * p.f_bpr) * BM + et;
+              const int lrow = rs_lblk * BM + et;
               if (lrow < p.f_shard_rows) {
-                // staging slots are chunk-major: [parity][source rank][row block][64-column chunk][128 rows][64]
+                // staging slots are chunk-major: [parity][source rank][row block][64-column chunk][128 rows][64], and every
+                // 16 KB chunk is the sender's 128B-SWIZZLED shared-memory tile verbatim (it left there as one 1-D bulk copy):
+                // 16-byte unit j of row r sits at unit j ^ (r & 7)
                 const int ncc = (p.N + 63) >> 6;
                 const long long slot = static_cast<long long>(p.f_shard_rows) * ncc * 64;
                 const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) + static_cast<long long>(f_epoch & 1) * p.f_world * slot +
-                                        ((static_cast<long long>(tm - p.f_rank * p.f_bpr) * ncc + (col0 >> 6)) * BM + et) * 64;
+                                        ((static_cast<long long>(rs_lblk) * ncc + (col0 >> 6)) * BM + et) * 64;
                 // all global loads of this chunk are issued back to back (independent), then consumed
                 uint4 rq[8];
                 const bool has_res = p.f_res != nullptr, has_bias = p.f_bias != nullptr;
@@ -676,7 +716,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                   const uint4* sp = reinterpret_cast<const uint4*>(stage + static_cast<long long>(s) * slot);
                   uint4 sq[8];
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) sq[j] = (col0 + j * 8 < p.N) ? sp[j] : make_uint4(0u, 0u, 0u, 0u);
+                  for (int j = 0; j < 8; ++j) sq[j] = (col0 + j * 8 < p.N) ? sp[j ^ (et & 7)] : make_uint4(0u, 0u, 0u, 0u);
                   add8(sq);
                 }
                 if (has_res) add8(rq);
@@ -746,7 +786,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
               }
             }
-            if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+            [[maybe_unused]] const int pslot = team * 2 + static_cast<int>(rs_pq & 1u);
+            if constexpr (FUSE == FUSE_RS) {
+              if (!rs_own) {                // remote rows: the chunk goes into one of this team's two push buffers
+                if (leader) mbar_wait(&pempty[pslot], ((rs_pq >> 1) & 1u) ^ 1u);
+                sb0 = push_bufs + pslot * STAGE_CHUNK_BYTES;
+              } else if (leader) {
+                tma_store_wait_read<0>();
+              }
+            } else {
+              if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+            }
             named_bar_sync(bar_id, EPI_THREADS);
             if (aux_on && leader) aux_issue_next();       // every thread of the team has copied its aux row out
           }
@@ -763,45 +813,33 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           named_bar_sync(bar_id, EPI_THREADS);
           if (leader) {
             if constexpr (FUSE == FUSE_RS) {
-              // partial tile -> staging slot [epoch parity][this rank] on the OWNER of these rows (TMA store
-              // through the peer mapping: the NVLink transfer overlaps the following tiles' mainloops)
-              const int owner = tm / p.f_bpr;
-              if (rs_own) tma_store_2d(&tmC, sb0, col0, (tm - owner * p.f_bpr) * BM);          // final rows of this rank
-              else        // one contiguous 16 KB chunk of the owner's staging slot (full-width NVLink writes)
-                tma_store_2d(p.f_rsmaps + (f_epoch & 1) * p.f_world + owner, sb0, 0,
-                             ((tm - owner * p.f_bpr) * ((p.N + 63) >> 6) + (col0 >> 6)) * BM);
-              ++rs_groups;
+              // partial tile -> staging slot [epoch parity][this rank] on the OWNER of these rows: the swizzled 16 KB tile
+              // goes out verbatim as ONE 1-D bulk copy through the peer mapping (large NVLink writes; the owner undoes the
+              // swizzle when it reads), and the transfer overlaps the following tiles' mainloops
+              if (rs_own) {
+                tma_store_2d(&tmC, sb0, col0, rs_lblk * BM);          // final rows of this rank
+                tma_store_commit();
+              } else {
+                const int ncc = (p.N + 63) >> 6;
+                const long long slot_bytes = static_cast<long long>(p.f_shard_rows) * ncc * 128;
+                const int pslot = team * 2 + static_cast<int>(rs_pq & 1u);
+                pmeta[pslot].dst = p.f_stage_peer[rs_owner] + (static_cast<long long>(f_epoch & 1) * p.f_world + p.f_rank) * slot_bytes +
+                                   (static_cast<long long>(rs_lblk) * ncc + (col0 >> 6)) * STAGE_CHUNK_BYTES;
+                pmeta[pslot].cnt = p.f_cnt[rs_owner] + rs_lblk;
+                mbar_arrive(&pfull[pslot]);           // release: the push warp sees the meta words and (through the team barrier) the tile
+              }
             } else {
               tma_store_2d(&tmC, sb0, col0, m0);
               if (dual && TEAMS == 1) tma_store_2d(&tmC2, epi_buf + STAGE_CHUNK_BYTES, col0, m0);
+              tma_store_commit();
             }
-            tma_store_commit();
           }
-        }
-        if constexpr (FUSE == FUSE_RS) {
-          if (leader) {
-            // signal the PREVIOUS tile (its stores have certainly landed once only this tile's groups are pending)
-            if (rs_prev_owner >= 0) {
-              if (rs_groups == NCH / TEAMS) tma_store_wait_all<NCH / TEAMS>(); else tma_store_wait_all<0>();
-              __threadfence_system();
-              red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
-            }
-            rs_prev_owner = rs_own ? -1 : tm / p.f_bpr;
-            rs_prev_blk = tm - (tm / p.f_bpr) * p.f_bpr;
-            rs_groups = 0;
-          }
+          if constexpr (FUSE == FUSE_RS) { if (!rs_own) ++rs_pq; }
         }
       }
     }
-    if constexpr (FUSE != FUSE_NONE) { if (leader) dbg_stamp(p, 1); }
+    if constexpr (FUSE != FUSE_NONE) { if (leader && team == 0) dbg_stamp(p, 1); }
     if (leader) tma_store_wait_all<0>();
-    if constexpr (FUSE == FUSE_RS) {
-      if (leader && rs_prev_owner >= 0) {
-        __threadfence_system();
-        red_release_sys_add(p.f_cnt[rs_prev_owner] + rs_prev_blk, 1u);
-      }
-      if (leader) dbg_stamp(p, 2);
-    }
   }
 
   tc_fence_before();
@@ -816,7 +854,7 @@ template <int BN, bool A_MN, bool B_MN, bool ERF = false>
 int launch(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
            const GemmParams& p, int max_ctas, cudaStream_t stream) {
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, false, ERF>;
-  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -838,7 +876,7 @@ template <int BN, bool A_MN, bool B_MN, bool ERF = false>
 int launch_pair(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
                 const GemmParams& p, int max_ctas, cudaStream_t stream) {
   auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, FUSE_NONE, true, ERF>;
-  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 /*align slack*/ + 512 /*barriers*/;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -1030,41 +1068,100 @@ extern "C" void b2_fused_set_debug(void* buf) { g_fused_dbg = static_cast<unsign
 // =============================================================================================
 namespace {
 
-template <int BN, bool B_MN, int FUSE>
+int g_fused_pair_mode = 1;     // 0: single-CTA tiles in the fused kernels, 1: CTA pairs whenever the shard geometry allows
+int g_fused_ncomm = 24;        // default number of all-gather CTAs (even); measured on 2 x B200: 24 CTAs x 6 x 32 KB in flight pull ~630 GB/s, 16 CTAs ~400
+
+// grid: number of CTAs (a multiple of 2 when PAIR); PAIR launches clusters of two
+template <int BN, bool B_MN, int FUSE, bool PAIR>
 int launch_fused(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tC, const CUtensorMap& tC2,
                  const GemmParams& p, int grid, cudaStream_t stream, const CUtensorMap& tA2) {
-  auto kern = gemm_tcgen05_kernel<BN, false, B_MN, FUSE>;
-  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 + 256;
+  auto kern = gemm_tcgen05_kernel<BN, false, B_MN, FUSE, PAIR, false>;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 + 512;
   static bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { b2host::set_error("fused gemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return -1; }
     configured = true;
   }
-  kern<<<grid, NUM_THREADS, smem, stream>>>(tA, tB, tC, tC2, p, tA2);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { b2host::set_error("fused gemm launch: %s", cudaGetErrorString(e)); return -1; }
-  return 0;
+  if constexpr (!PAIR) {
+    kern<<<grid, NUM_THREADS, smem, stream>>>(tA, tB, tC, tC2, p, tA2);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { b2host::set_error("fused gemm launch: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid, 1, 1);
+    cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tA, tB, tC, tC2, p, tA2);
+    if (e != cudaSuccess) { b2host::set_error("fused gemm(pair) launch: %s", cudaGetErrorString(e)); return -1; }
+    return 0;
+  }
+}
+
+// CTA pairs that can be co-resident (every CTA of a fused launch must be: the GEMM CTAs wait for the all-gather CTAs / for
+// peers).  Uses the plain pair kernel's answer - same block size, same dynamic shared memory, same cluster shape.
+int fused_resident_pairs() {
+  static int cached = 0;
+  if (cached > 0) return cached;
+  auto kern = gemm_tcgen05_kernel<256, false, false, FUSE_AG, true, false>;
+  const int smem = SMEM_MAIN_BYTES + 2 * STAGE_CHUNK_BYTES + 1024 + 512;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * (b2host::num_sms() / 2), 1, 1);
+  cfg.blockDim = dim3(NUM_THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  cudaError_t e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+  if (e != cudaSuccess || n <= 0) { cudaGetLastError(); n = 0; }
+  cached = n > 0 ? n : -1;
+  return cached;
 }
 
 int make_ab_maps(CUtensorMap* tA, CUtensorMap* tB, const void* A, const void* B, int M, int N, int K, long long lda,
-                 long long ldb, int b_mn, int bn, CUtensorMapDataType dt) {
+                 long long ldb, int b_mn, int bn_box, CUtensorMapDataType dt) {
   uint64_t dims[2], strides[2]; uint32_t box[2];
   dims[0] = K; dims[1] = M; box[0] = BK; box[1] = BM; strides[0] = 0; strides[1] = static_cast<uint64_t>(lda) * 2;
   if (b2host::encode_tmap(tA, dt, 2, A, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
-  if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = bn; }
+  if (!b_mn) { dims[0] = K; dims[1] = N; box[0] = BK; box[1] = bn_box; }
   else       { dims[0] = N; dims[1] = K; box[0] = 64; box[1] = BK; }
   strides[1] = static_cast<uint64_t>(ldb) * 2;
   return b2host::encode_tmap(tB, dt, 2, B, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+#define B2_FUSED_DISPATCH(FUSE_, PAIR_)                                                                                  \
+  do {                                                                                                                   \
+    if (bn == 256) return b_mn_major ? launch_fused<256, true, FUSE_, PAIR_>(tA, tB, tC, tC2, p, grid, stream, tA2)      \
+                                     : launch_fused<256, false, FUSE_, PAIR_>(tA, tB, tC, tC2, p, grid, stream, tA2);    \
+    return b_mn_major ? launch_fused<128, true, FUSE_, PAIR_>(tA, tB, tC, tC2, p, grid, stream, tA2)                     \
+                      : launch_fused<128, false, FUSE_, PAIR_>(tA, tB, tC, tC2, p, grid, stream, tA2);                   \
+  } while (0)
+
 }  // namespace
+
+// tuning knobs of the fused kernels: pair_mode 0 = single-CTA tiles, 1 = CTA pairs when the geometry allows (default);
+// n_comm = default number of all-gather CTAs (rounded to an even number), <= 0 keeps the current value
+extern "C" void b2_fused_config(int pair_mode, int n_comm) {
+  if (pair_mode >= 0) g_fused_pair_mode = pair_mode;
+  if (n_comm > 0) g_fused_ncomm = (n_comm + 1) & ~1;
+}
 
 // All-gather -> GEMM in ONE kernel.  Every rank holds a [shard_rows, K] shard of A in symmetric memory
 // (shard_ptrs[r], control blocks ctrls[r]); `n_comm` CTAs pull the shards over NVLink into the local gathered
 // operand xg [world*shard_rows, K] (returned to the caller: backward needs it) while the remaining CTAs run
-// the tcgen05 GEMM tile by tile as soon as the rows of a tile have arrived (own shard first).
+// the tcgen05 GEMM (CTA pairs, 256-row tiles) tile by tile as soon as the rows of a tile have arrived (own shard first).
 //   C[M, N] = epilogue(xg @ op(B)),  M = world * shard_rows.
+// flags: world * shard_rows / 128 uint32 arrival counters owned by this (buffer, K) pair; zero before the first call and
+//        never touched by the caller afterwards (they count pieces cumulatively, in step with the buffer's call epoch).
 // replaces: NCCL all_gather_into_tensor + cuBLAS GEMM of Megatron's ColumnParallelLinear forward and
 //           RowParallelLinear backward under sequence parallelism, and DeepSpeed's
 //           all_gather_coalesced + GEMM when the gathered operand is a ZeRO-3 weight shard (C19).
@@ -1079,24 +1176,32 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
   const int M = shard_rows * world;
   const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   const int bn = N > 128 ? 256 : 128;
+  const int sms = b2host::num_sms();
+  if (n_comm <= 0) n_comm = g_fused_ncomm;
+  if (n_comm > sms / 4) n_comm = sms / 4;
+  n_comm = (n_comm + 1) & ~1;
+  // CTA pairs need 256-row tiles that do not straddle two ranks' shards, and every CTA of the grid co-resident
+  const int res_pairs = g_fused_pair_mode ? fused_resident_pairs() : 0;
+  const bool pair = g_fused_pair_mode && (shard_rows % (2 * BM) == 0) && res_pairs > n_comm / 2 + 1;
   GemmParams p{};
   p.M = M; p.N = N; p.K = K;
-  p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
+  p.tiles_m = pair ? M / (2 * BM) : M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
   p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
   if (epilogue & B2_EPI_ERF) { b2host::set_error("ag_gemm: erf GELU epilogues are not built for the fused kernels"); return -1; }
   p.epilogue = epilogue; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.out_fp32 = 0; p.reduce_add = 0;
   p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = 1.f;
+  if ((epilogue == B2_EPI_BIAS_RESIDUAL || epilogue == B2_EPI_DGELU) && (aux == nullptr || (ld_aux % 8))) {
+    b2host::set_error("ag_gemm: epilogue needs a 16-byte aligned aux tensor"); return -1;
+  }
   p.f_rank = rank; p.f_world = world; p.f_bpr = shard_rows / BM; p.f_shard_rows = shard_rows;
-  const int sms = b2host::num_sms();
-  if (n_comm <= 0) n_comm = 24;
-  if (n_comm > sms / 4) n_comm = sms / 4;
   p.f_ncomm = n_comm;
-  p.m_rot = rank * p.f_bpr;
+  p.m_rot = pair ? rank * (p.f_bpr / 2) : rank * p.f_bpr;
   p.f_row_bytes = static_cast<long long>(K) * 2;
+  p.f_npb = static_cast<int>((128LL * p.f_row_bytes + 32767) / 32768);
   for (int r = 0; r < 8; ++r) { p.f_peer[r] = r < world ? shard_ptrs[r] : nullptr; p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
   p.f_xg = static_cast<uint8_t*>(xg); p.f_flags = flags; p.f_dbg = g_fused_dbg;
   CUtensorMap tA, tB, tC, tC2;
-  if (make_ab_maps(&tA, &tB, xg, B, M, N, K, K, ldb, b_mn_major, bn, dt)) return -1;
+  if (make_ab_maps(&tA, &tB, xg, B, M, N, K, K, ldb, b_mn_major, pair ? bn / 2 : bn, dt)) return -1;
   uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(M)}, strides[2] = {0, static_cast<uint64_t>(ldc) * 2};
   uint32_t box[2] = {64, BM};
   if (b2host::encode_tmap(&tC, dt, 2, C, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
@@ -1105,6 +1210,9 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
     if (C2 == nullptr) { b2host::set_error("ag_gemm: dual epilogue needs C2"); return -1; }
     strides[1] = static_cast<uint64_t>(ldc2) * 2;
     if (b2host::encode_tmap(&tC2, dt, 2, C2, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  } else if (epilogue == B2_EPI_BIAS_RESIDUAL || epilogue == B2_EPI_DGELU) {
+    strides[1] = static_cast<uint64_t>(ld_aux) * 2;        // aux tiles are prefetched by TMA through the C2 map slot
+    if (b2host::encode_tmap(&tC2, dt, 2, aux, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
   }
   CUtensorMap tA2;
   {
@@ -1112,43 +1220,29 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
     uint32_t b2[2] = {BK, BM};
     if (b2host::encode_tmap(&tA2, dt, 2, shard_ptrs[rank], d2, s2, b2, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
   }
-  const int grid = sms;     // one CTA per SM: all-gather CTAs and GEMM CTAs must be co-resident
-  if (bn == 256) return b_mn_major ? launch_fused<256, true, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream, tA2)
-                                   : launch_fused<256, false, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream, tA2);
-  return b_mn_major ? launch_fused<128, true, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream, tA2)
-                    : launch_fused<128, false, FUSE_AG>(tA, tB, tC, tC2, p, grid, stream, tA2);
-}
-
-// Builds (host) and uploads (synchronously, once per buffer/shape) the 2*world staging-slot tensor maps of
-// the GEMM->reduce-scatter kernel: map[parity*world + owner] = slot [parity][this rank] of rank `owner`'s
-// staging buffer.  A slot is chunk-major - [row block][64-column chunk][128 rows][64 columns] - so every partial tile
-// chunk the GEMM epilogue pushes is ONE contiguous 16 KB write over NVLink instead of 128 strided 128-byte rows; the
-// map describes the slot as a tall [blocks * chunks * 128, 64] matrix.  Slot size: shard_rows * ceil(N/64) * 64 elements.
-extern "C" int b2_make_rs_maps(void* dev_out, void* const* stage_ptrs, int world, int rank, int shard_rows, int N, int dtype) {
-  CUtensorMap maps[16];
-  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-  for (int par = 0; par < 2; ++par)
-    for (int o = 0; o < world; ++o) {
-      const long long ncc = (N + 63) / 64;
-      uint8_t* base = static_cast<uint8_t*>(stage_ptrs[o]) + (static_cast<long long>(par) * world + rank) * shard_rows * ncc * 64 * 2;
-      uint64_t dims[2] = {64, static_cast<uint64_t>(shard_rows * ncc)}, strides[2] = {0, 128};
-      uint32_t box[2] = {64, BM};
-      if (b2host::encode_tmap(&maps[par * world + o], dt, 2, base, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
-    }
-  cudaError_t e = cudaMemcpy(dev_out, maps, sizeof(CUtensorMap) * 2 * world, cudaMemcpyHostToDevice);
-  if (e != cudaSuccess) { b2host::set_error("make_rs_maps: %s", cudaGetErrorString(e)); return -1; }
-  return 0;
+  // one CTA per SM: all-gather CTAs and GEMM CTAs must be co-resident
+  if (pair) {
+    int pairs = sms / 2 < res_pairs ? sms / 2 : res_pairs;
+    const int grid = 2 * pairs;
+    B2_FUSED_DISPATCH(FUSE_AG, true);
+  }
+  const int grid = sms;
+  B2_FUSED_DISPATCH(FUSE_AG, false);
 }
 
 // GEMM -> reduce-scatter in ONE kernel.  Each rank multiplies its K-slice (partial sums for ALL M rows); the
-// epilogue TMA-stores every partial tile straight into the staging slot of the rank that OWNS those rows
-// (remote rows first, so NVLink traffic overlaps the remaining tiles), bumps an arrival counter there, and the
-// same kernel then folds the `world` partials of its own rows with bias and residual into the output shard.
+// epilogue sends every partial tile straight into the staging slot of the rank that OWNS those rows (remote rows first, so
+// NVLink traffic overlaps the remaining tiles; a tile chunk leaves as one 16 KB bulk copy of the swizzled shared-memory
+// tile), bumps an arrival counter there, and the same kernel then folds the `world` partials of its own rows with bias
+// and residual into the output shard.
 //   out[shard_rows, N] = residual + bias + sum_ranks (A_r @ op(B_r))[rows of this rank]
+// stage_ptrs[r]: rank r's staging buffer (symmetric), 2 * world * shard_rows * ceil(N/64) * 64 elements:
+//                [call parity][source rank][row block][64-column chunk][128 rows x 128 B, swizzled]
+// cnt_ptrs[r]:   rank r's per-row-block arrival counters (symmetric, zero before the first call)
 // replaces: cuBLAS GEMM + NCCL reduce_scatter_tensor (+ bias-dropout-add) of RowParallelLinear forward and
 //           ColumnParallelLinear backward under sequence parallelism.
 extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
-                          int dtype, void* const* cnt_ptrs, void* const* ctrls, const void* rsmaps_dev, const void* stage_local,
+                          int dtype, void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs,
                           void* out, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
                           int world, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -1158,33 +1252,43 @@ extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, lon
     b2host::set_error("gemm_rs: K, N and leading dimensions must be multiples of 8"); return -1;
   }
   const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-  const int bn = N > 128 ? 256 : 128;
+  const int sms = b2host::num_sms();
+  const int shard_rows = M / world;
+  const int res_pairs = g_fused_pair_mode ? fused_resident_pairs() : 0;
+  const bool pair = g_fused_pair_mode && (shard_rows % (2 * BM) == 0) && res_pairs > 0;
+  // the push buffers take 64 KB of the operand ring: single-CTA 128 x 256 tiles (48 KB stages) would be left with two stages
+  const int bn = (N > 128 && pair) ? 256 : 128;
   GemmParams p{};
   p.M = M; p.N = N; p.K = K;
-  p.tiles_m = M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
+  p.tiles_m = pair ? M / (2 * BM) : M / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
   p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
   p.epilogue = B2_EPI_NONE; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.alpha = 1.f;
-  p.f_rank = rank; p.f_world = world; p.f_shard_rows = M / world; p.f_bpr = p.f_shard_rows / BM; p.f_ncomm = 0;
-  p.m_rot = ((rank + 1) % world) * p.f_bpr;
+  p.f_rank = rank; p.f_world = world; p.f_shard_rows = shard_rows; p.f_bpr = shard_rows / BM; p.f_ncomm = 0;
+  p.m_rot = ((rank + 1) % world) * (pair ? p.f_bpr / 2 : p.f_bpr);
   for (int r = 0; r < 8; ++r) {
     p.f_cnt[r] = r < world ? static_cast<uint32_t*>(cnt_ptrs[r]) : nullptr;
     p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr;
+    p.f_stage_peer[r] = r < world ? static_cast<uint8_t*>(stage_ptrs[r]) : nullptr;
   }
-  p.f_rsmaps = static_cast<const CUtensorMap*>(rsmaps_dev);
   p.f_dbg = g_fused_dbg;
-  p.f_stage = stage_local; p.f_out = out; p.f_ld_out = ld_out; p.f_bias = bias; p.f_res = residual; p.f_ld_res = ld_res;
+  p.f_stage = stage_ptrs[rank]; p.f_out = out; p.f_ld_out = ld_out; p.f_bias = bias; p.f_res = residual; p.f_ld_res = ld_res;
   CUtensorMap tA, tB, tC;
-  if (make_ab_maps(&tA, &tB, A, B, M, N, K, lda, ldb, b_mn_major, bn, dt)) return -1;
+  if (make_ab_maps(&tA, &tB, A, B, M, N, K, lda, ldb, b_mn_major, pair ? bn / 2 : bn, dt)) return -1;
   {
     uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(p.f_shard_rows)}, strides[2] = {0, static_cast<uint64_t>(ld_out) * 2};
     uint32_t box[2] = {64, BM};
     if (b2host::encode_tmap(&tC, dt, 2, out, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
   }
-  const int sms = b2host::num_sms();
+  const CUtensorMap& tC2 = tC;
+  const CUtensorMap& tA2 = tA;
   const int total = p.tiles_m * p.tiles_n;
+  if (pair) {
+    int pairs = sms / 2 < res_pairs ? sms / 2 : res_pairs;
+    if (total < pairs) pairs = total;
+    const int grid = 2 * pairs;
+    B2_FUSED_DISPATCH(FUSE_RS, true);
+  }
   const int grid = total < sms ? total : sms;
-  if (bn == 256) return b_mn_major ? launch_fused<256, true, FUSE_RS>(tA, tB, tC, tC, p, grid, stream, tA)
-                                   : launch_fused<256, false, FUSE_RS>(tA, tB, tC, tC, p, grid, stream, tA);
-  return b_mn_major ? launch_fused<128, true, FUSE_RS>(tA, tB, tC, tC, p, grid, stream, tA)
-                    : launch_fused<128, false, FUSE_RS>(tA, tB, tC, tC, p, grid, stream, tA);
+  B2_FUSED_DISPATCH(FUSE_RS, false);
 }
+#undef B2_FUSED_DISPATCH

@@ -200,8 +200,14 @@ int b2_rs_update(void* const* ptrs, void* const* ctrls, void* mc_ptr, long long 
                  void* p_lp, float lr, float beta1, float beta2, float eps, float wd, int step, int max_ctas, void* stream);
 
 /* Fused compute + collective kernels (csrc/gemm.cu).  A operand is [rows, K] row-major; B as in b2_gemm.
- *  b2_ag_gemm : all-gather(A shards over the group) -> GEMM, one kernel; xg receives the gathered A.
- *  b2_gemm_rs : GEMM -> reduce-scatter(+bias+residual), one kernel; b2_make_rs_maps prepares its staging maps.
+ *  b2_ag_gemm : all-gather(A shards over the group) -> GEMM, one kernel; xg receives the gathered A.  `flags` = world *
+ *               shard_rows / 128 uint32 arrival counters that belong to the shard buffer (zero before its first call, owned
+ *               by the kernels afterwards).  n_comm <= 0: the default number of all-gather CTAs.
+ *  b2_gemm_rs : GEMM -> reduce-scatter(+bias+residual), one kernel.  stage_ptrs[r] = rank r's symmetric staging buffer of
+ *               2 * world * shard_rows * ceil(N/64) * 64 elements, cnt_ptrs[r] = rank r's shard_rows / 128 arrival counters.
+ *  b2_fused_config : pair_mode 0/1 (CTA-pair 256-row tiles in the fused kernels, default 1; < 0 keeps), default n_comm (<= 0 keeps).
+ * Every cross-GPU wait in these kernels is bounded (B2_SPIN_TIMEOUT_NS, 4 s): a peer that never arrives turns into a
+ * launch failure (trap), not a hung GPU.
  * replaces: NCCL all-gather / reduce-scatter around cuBLAS GEMMs in Megatron's Column/RowParallelLinear with
  *           sequence parallelism and DeepSpeed ZeRO-3 parameter gathers (C19).
  */
@@ -209,11 +215,11 @@ int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg, unsigned i
                int shard_rows, int N, int K, long long ldb, long long ldc, int b_mn_major, int dtype, int epilogue,
                const void* bias, const void* aux, long long ld_aux, void* C2, long long ldc2, int rank, int world,
                int n_comm, void* stream);
-int b2_make_rs_maps(void* dev_out, void* const* stage_ptrs, int world, int rank, int shard_rows, int N, int dtype);
 int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major, int dtype,
-               void* const* cnt_ptrs, void* const* ctrls, const void* rsmaps_dev, const void* stage_local, void* out,
+               void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, void* out,
                long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world,
                void* stream);
+void b2_fused_config(int pair_mode, int n_comm);
 
 /* ------------------------------------------------------------------------------------------
  * BatchNorm2d over NCHW tensors (csrc/batchnorm.cu), fp32 / bf16 / fp16 activations, fp32 statistics.  Training forward =

@@ -52,7 +52,7 @@ class _HeadUnit(nn.Module):
 class Zero3CausalLM(nn.Module):
     def __init__(self, model: nn.Module, *, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0,
                  gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None,
-                 offload_optimizer="none", gradient_checkpointing=False):
+                 offload_optimizer="none", gradient_checkpointing=False, max_live_parameters=0, prefetch_bucket_size=0, max_reuse_distance=0):
         super().__init__()
         self.model = model
         self.tied = getattr(model, "lm_head", None) is None
@@ -63,7 +63,9 @@ class Zero3CausalLM(nn.Module):
         self.engine = Zero3Engine(units, names, group, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, max_grad_norm=max_grad_norm,
                                   gradient_accumulation_steps=gradient_accumulation_steps, persistence_threshold=persistence_threshold,
                                   comm_backend=comm_backend, offload_param=offload_param, offload_optimizer=offload_optimizer,
-                                  checkpoint_units=range(1, len(units) - 1) if gradient_checkpointing else ())      # the decoder layers
+                                  checkpoint_units=range(1, len(units) - 1) if gradient_checkpointing else (),      # the decoder layers
+                                  max_live_parameters=max_live_parameters, prefetch_bucket_size=prefetch_bucket_size,
+                                  max_reuse_distance=max_reuse_distance)
         self._units = units
 
     def forward(self, input_ids, attention_mask=None, labels=None):
@@ -136,7 +138,10 @@ class Trainer:
                                     persistence_threshold=self.ds.zero.stage3_param_persistence_threshold, comm_backend=a.comm_backend,
                                     offload_param=self.ds.zero.offload_param_device,
                                     offload_optimizer=self.ds.zero.offload_optimizer_device,
-                                    gradient_checkpointing=bool(a.gradient_checkpointing))
+                                    gradient_checkpointing=bool(a.gradient_checkpointing),
+                                    max_live_parameters=self.ds.zero.stage3_max_live_parameters,
+                                    prefetch_bucket_size=self.ds.zero.stage3_prefetch_bucket_size,
+                                    max_reuse_distance=self.ds.zero.stage3_max_reuse_distance)
         eng = self.zmodel.engine
         sp = self.ds.scheduler_params
         if self.ds.scheduler_type == "WarmupDecayLR":

@@ -67,10 +67,10 @@ class Fabric:
             L.b2_allreduce.restype = c_i
             L.b2_ag_gemm.argtypes = [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_i, c_p, c_p, c_ll, c_p, c_ll, c_i, c_i, c_i, c_p]
             L.b2_ag_gemm.restype = c_i
-            L.b2_make_rs_maps.argtypes = [c_p, c_p, c_i, c_i, c_i, c_i, c_i]
-            L.b2_make_rs_maps.restype = c_i
-            L.b2_gemm_rs.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
+            L.b2_gemm_rs.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
             L.b2_gemm_rs.restype = c_i
+            L.b2_fused_config.argtypes = [c_i, c_i]
+            L.b2_fused_config.restype = None
             L.b2_reduce_scatter.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p, c_p]
             L.b2_reduce_scatter.restype = c_i
             L.b2_allgather.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_p]
@@ -78,6 +78,8 @@ class Fabric:
             L.b2_rs_update.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_f, c_p, c_i, c_p, c_i, c_p, c_p, c_p, c_p,
                                        c_f, c_f, c_f, c_f, c_f, c_i, c_i, c_p]
             L.b2_rs_update.restype = c_i
+            import os
+            L.b2_fused_config(int(os.environ.get("B2_FUSED_PAIR", "-1")), int(os.environ.get("B2_FUSED_NCOMM", "0")))     # tuning / A-B runs
             self._ag, self._rs, self._coll = {}, {}, {}
             probe = SymmBuffer(self, 1024, torch.float32)
             probe.tensor.fill_(float(self.rank + 1))
@@ -173,13 +175,9 @@ class Fabric:
         key = (rows, Nn, dtype)
         st = self._rs.get(key)
         if st is None:
-            stage = self.alloc(2 * self.world * rows * ((Nn + 63) // 64) * 64, dtype)     # chunk-major slots (see b2_make_rs_maps)
+            stage = self.alloc(2 * self.world * rows * ((Nn + 63) // 64) * 64, dtype)     # [parity][source][row block][64-col chunk][128 x 128 B]
             cnt = self.alloc(max(rows // 128, 1), torch.int32)
-            maps = torch.empty(2 * self.world * 128, dtype=torch.uint8, device=stage.tensor.device)
-            rc = N.lib().b2_make_rs_maps(N._p(maps), stage.ptrs, self.world, self.rank, rows, Nn, N._dt(stage.tensor))
-            if rc != 0:
-                raise RuntimeError("b2_make_rs_maps: " + N.lib().b2_last_error().decode())
-            st = self._rs[key] = {"stage": stage, "cnt": cnt, "maps": maps}
+            st = self._rs[key] = {"stage": stage, "cnt": cnt}
         return st
 
     def gemm_rs(self, a2: torch.Tensor, W: torch.Tensor, b_mn: bool = False, bias=None, residual=None):
@@ -192,7 +190,7 @@ class Fabric:
         st = self._rs_state(rows, Nn, a2.dtype)
         out = torch.empty((rows, Nn), dtype=a2.dtype, device=a2.device)
         N._call("b2_gemm_rs", N._p(a2), N._p(W), M, Nn, K, a2.stride(0), W.stride(0), int(b_mn), N._dt(a2), st["cnt"].ptrs,
-                st["stage"].ctrls, N._p(st["maps"]), N._p(st["stage"].tensor), N._p(out), out.stride(0), N._p(bias),
+                st["stage"].ctrls, st["stage"].ptrs, N._p(out), out.stride(0), N._p(bias),
                 N._p(residual), residual.stride(0) if residual is not None else 0, self.rank, self.world, N._st())
         return out
 

@@ -6,15 +6,20 @@ Counterpart of DeepSpeed's zero/{partition_parameters,parameter_offload,partitio
   * a *unit* (one decoder layer, the embeddings, the head) owns ONE flat low-precision buffer; each rank keeps only
     its 1/world slice of it (+ fp32 master / exp_avg / exp_avg_sq / fp32 grad-accumulation slices);
   * two full-size gather workspaces and two gradient workspaces live in SYMMETRIC memory and rotate between units:
-    the parameters of unit L are views into workspace L % 2, so their addresses never change;
+    the parameters of unit L are views into workspace L % n_ws, so their addresses never change;
   * fetch   = copy my slice into the workspace + the fabric all-gather kernel (NVSwitch multicast stores) on a
     side stream, issued one unit ahead (static prefetch order, forward and backward);
   * release = nothing to free: the workspace is simply overwritten by the next fetch;
   * reduce  = ONE fused kernel per unit and micro-step (csrc/comm.cu rs_update): multimem.ld_reduce of my slice of
     the gradient workspace, scaled, accumulated into the fp32 gradient slice; on the optimizer boundary, when no
     global-norm clipping is requested, the same kernel applies AdamW to the fp32 slice and writes the bf16 slice
-    (gradient reduce-scatter fused with the partitioned Adam update).  With clipping the Adam pass runs after the
-    norm is known, as one flat launch over all slices;
+    (gradient reduce-scatter fused with the partitioned Adam update).  With clipping the update cannot start before
+    the last unit's gradient is reduced; the reduce kernels leave sum(g^2) in a device scalar, and the Adam pass is ONE
+    launch over the flat arena of all slices that derives the clip coefficient from that scalar on the device (no host
+    round trip between backward and the update; the norm is only read back when somebody logs it);
+  * ``stage3_max_live_parameters`` sizes the ring of gather workspaces (more than two: the last units of the forward are
+    still resident when the backward starts, DeepSpeed's ``stage3_max_reuse_distance`` effect) and
+    ``stage3_prefetch_bucket_size`` the look-ahead depth of the prefetcher;
   * parameters below ``stage3_param_persistence_threshold`` stay replicated (their grads are all-reduced).
 
 On CPU / gloo (tests) the same bookkeeping runs with torch.distributed collectives.
@@ -114,7 +119,8 @@ class Zero3Engine:
                  betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.0, max_grad_norm: float = 1.0,
                  gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
                  offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None,
-                 offload_optimizer: str = "none", checkpoint_units: Sequence[int] = ()):
+                 offload_optimizer: str = "none", checkpoint_units: Sequence[int] = (), max_live_parameters: float = 0,
+                 prefetch_bucket_size: int = 0, max_reuse_distance: float = 0):
         self.checkpoint_units = set(checkpoint_units)      # unit indices whose activations are recomputed in backward
         self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         self.world = dist.get_world_size(self.group) if self.group is not None else 1
@@ -162,18 +168,44 @@ class Zero3Engine:
             self.units.append(u)
         self.num_persistent = sum(p.numel() for p in self.persistent)
         max_numel = max(u.numel for u in self.units)
-        # ---- rotating workspaces (symmetric when the fabric is up)
+        # ---- rotating workspaces (symmetric when the fabric is up).  Gather workspaces form a ring of n_ws >= 2:
+        # stage3_max_live_parameters bounds how many gathered elements may be alive at once (DeepSpeed's meaning), so
+        # n_ws = max_live // largest unit; stage3_max_reuse_distance caps it the same way (a unit that comes back within
+        # that many elements - the last units at the forward/backward turn - is still resident and is not re-gathered).
+        # The prefetcher looks `depth` units ahead: stage3_prefetch_bucket_size elements, at least one unit, at most n_ws - 1.
+        n_units = len(self.units)
+        n_ws = 2
+        if max_live_parameters and max_live_parameters > 0:
+            n_ws = int(max_live_parameters // max_numel)
+            if max_reuse_distance and max_reuse_distance > 0:
+                n_ws = min(n_ws, max(2, int(max_reuse_distance // max_numel)))
+        self.n_ws = max(2, min(n_ws, n_units, 8))
+        depth = 1
+        if prefetch_bucket_size and prefetch_bucket_size > 0:
+            depth = -(-int(prefetch_bucket_size) // max_numel)
+        self.prefetch_depth = max(1, min(depth, self.n_ws - 1))
         self._ws_param, self._ws_grad = [], []
-        for k in range(2):
+        for k in range(self.n_ws):
             if self.fabric is not None:
                 self._ws_param.append(self.fabric.alloc(max_numel, self.dtype))
-                self._ws_grad.append(self.fabric.alloc(max_numel, self.grad_dtype))
             else:
                 self._ws_param.append(torch.zeros(max_numel, dtype=self.dtype, device=self.dev))
+        for k in range(2):
+            if self.fabric is not None:
+                self._ws_grad.append(self.fabric.alloc(max_numel, self.grad_dtype))
+            else:
                 self._ws_grad.append(torch.zeros(max_numel, dtype=self.grad_dtype, device=self.dev))
         # ---- partition: per-unit slices
         self.lp_slices, self.fp32, self.exp_avg, self.exp_avg_sq, self.gacc = [], [], [], [], []
         self._gacc_host, self._lp_host = [], []
+        # every rank-local slice (fp32 master, both moments, fp32 gradient accumulator, low-precision copy) is a view of ONE
+        # flat arena per kind, so the clipped optimizer step is a single launch over the arena
+        tot_slice = sum(u.slice for u in self.units)
+        self._arena = None
+        if not self.offload_optimizer:
+            self._arena = {k: torch.zeros(tot_slice, dtype=torch.float32, device=self.dev) for k in ("fp32", "m", "v", "gacc")}
+            self._arena["lp"] = torch.zeros(tot_slice, dtype=self.dtype, device=self.dev) if offload_param != "cpu" else None
+        a_off = 0
         for u in self.units:
             flat = torch.zeros(u.numel, dtype=self.dtype, device=self.dev)
             for p, o in zip(u.params, u.offsets):
@@ -181,6 +213,10 @@ class Zero3Engine:
             sl = flat[self.rank * u.slice:(self.rank + 1) * u.slice].clone()
             if offload_param == "cpu":
                 sl = sl.cpu().pin_memory() if (pin_memory and torch.cuda.is_available()) else sl.cpu()
+            elif self._arena is not None:
+                v_ = self._arena["lp"][a_off:a_off + u.slice]
+                v_.copy_(sl)
+                sl = v_
             self.lp_slices.append(sl)
             if self.offload_optimizer:
                 pin = (lambda t: t.pin_memory()) if (pin_memory and torch.cuda.is_available()) else (lambda t: t)
@@ -189,11 +225,14 @@ class Zero3Engine:
                 self.exp_avg_sq.append(pin(torch.zeros(u.slice, dtype=torch.float32)))
                 self._gacc_host.append(pin(torch.zeros(u.slice, dtype=torch.float32)))
                 self._lp_host.append(sl if sl.device.type == "cpu" else pin(torch.zeros(u.slice, dtype=self.dtype)))
+                self.gacc.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
             else:
-                self.fp32.append(flat[self.rank * u.slice:(self.rank + 1) * u.slice].float())
-                self.exp_avg.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
-                self.exp_avg_sq.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
-            self.gacc.append(torch.zeros(u.slice, dtype=torch.float32, device=self.dev))
+                self._arena["fp32"][a_off:a_off + u.slice].copy_(flat[self.rank * u.slice:(self.rank + 1) * u.slice])
+                self.fp32.append(self._arena["fp32"][a_off:a_off + u.slice])
+                self.exp_avg.append(self._arena["m"][a_off:a_off + u.slice])
+                self.exp_avg_sq.append(self._arena["v"][a_off:a_off + u.slice])
+                self.gacc.append(self._arena["gacc"][a_off:a_off + u.slice])
+            a_off += u.slice
             ws_p, ws_g = self._param_ws(u.index), self._grad_ws(u.index)
             for p, o in zip(u.params, u.offsets):      # parameters become views of the rotating workspace
                 p.data = ws_p[o:o + p.numel()].view(p.shape)
@@ -203,17 +242,22 @@ class Zero3Engine:
         self.persist_m = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
         self.persist_v = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
         self.persist_fp32 = [p.data.float().clone() for p in self.persistent]
-        self._resident = [None, None]          # which unit currently occupies each workspace
+        self._resident = [None] * self.n_ws    # which unit currently occupies each workspace
         self._events: Dict[int, torch.cuda.Event] = {}
         self._stream = torch.cuda.Stream() if self.dev.type == "cuda" else None
         self.sumsq = torch.zeros(1, dtype=torch.float32, device=self.dev)
-        self.last_grad_norm = 0.0
+        self._norm_sq: Optional[torch.Tensor] = None       # global sum(g^2) of the last step, on the device
         self.param_groups = [{"lr": lr, "weight_decay": weight_decay}]
         self._reduce_at_end: List[int] = []
 
     # ------------------------------------------------------------------ workspace helpers
+    @property
+    def last_grad_norm(self) -> float:
+        """global gradient norm of the last optimizer step (reads the device scalar: synchronises, so log sparingly)"""
+        return float(self._norm_sq.sqrt()) if self._norm_sq is not None else 0.0
+
     def _param_ws(self, idx) -> torch.Tensor:
-        w = self._ws_param[idx % 2]
+        w = self._ws_param[idx % self.n_ws]
         return w.tensor if hasattr(w, "tensor") else w
 
     def _grad_ws(self, idx) -> torch.Tensor:
@@ -225,7 +269,7 @@ class Zero3Engine:
 
     # ------------------------------------------------------------------ fetch / prefetch
     def _gather(self, idx: int):
-        """all-gather unit idx into workspace idx % 2 (on the current stream)."""
+        """all-gather unit idx into workspace idx % n_ws (on the current stream)."""
         u = self.units[idx]
         ws = self._param_ws(idx)
         sl = self.lp_slices[idx]
@@ -238,21 +282,21 @@ class Zero3Engine:
             mine.data.copy_(sl)
         if self.world > 1:
             if self.fabric is not None:
-                buf = self._ws_param[idx % 2]
+                buf = self._ws_param[idx % self.n_ws]
                 N._call("b2_allgather", buf.ptrs, buf.ctrls, buf.mc_ptr or None, u.numel, N._dt(ws), self.rank, self.world, 0, N._st())
             else:
                 out = ws[:u.numel]
                 dist.all_gather_into_tensor(out.data, mine.data.clone(), group=self.group)
-        self._resident[idx % 2] = idx
+        self._resident[idx % self.n_ws] = idx
 
     def _ensure(self, idx: int, forward: bool):
-        nxt = idx + 1 if forward else idx - 1
+        step = 1 if forward else -1
         if self._stream is None:
-            if self._resident[idx % 2] != idx:
+            if self._resident[idx % self.n_ws] != idx:
                 self._gather(idx)
             return
         cur = torch.cuda.current_stream()
-        if self._resident[idx % 2] != idx:
+        if self._resident[idx % self.n_ws] != idx:
             self._stream.wait_stream(cur)
             with torch.cuda.stream(self._stream):
                 self._gather(idx)
@@ -261,14 +305,16 @@ class Zero3Engine:
         ev = self._events.pop(idx, None)
         if ev is not None:
             cur.wait_event(ev)
-        if 0 <= nxt < len(self.units) and self._resident[nxt % 2] != nxt:
-            # prefetch the next unit into the OTHER workspace while this one computes; the other workspace's
-            # previous occupant has finished (its compute was issued earlier on the current stream)
-            self._stream.wait_stream(cur)
-            with torch.cuda.stream(self._stream):
-                self._gather(nxt)
-                ev = torch.cuda.Event(); ev.record()
-                self._events[nxt] = ev
+        for k in range(1, self.prefetch_depth + 1):
+            nxt = idx + step * k
+            if 0 <= nxt < len(self.units) and self._resident[nxt % self.n_ws] != nxt:
+                # prefetch into a workspace whose previous occupant is at least n_ws - depth units behind: its compute was
+                # issued earlier on the current stream, which the side stream waits for
+                self._stream.wait_stream(cur)
+                with torch.cuda.stream(self._stream):
+                    self._gather(nxt)
+                    ev = torch.cuda.Event(); ev.record()
+                    self._events[nxt] = ev
 
     def wrap(self, idx: int, fn, x, *args):
         """run unit idx: y = fn(x, *args) with fetch before forward/backward and gradient reduction after backward."""
@@ -308,7 +354,7 @@ class Zero3Engine:
             buf = self._ws_grad[idx % 2]
             lp = self.lp_slices[idx]
             N._call("b2_rs_update", buf.ptrs, buf.ctrls, buf.mc_ptr or None, u.numel, N._dt(gws), self.rank, self.world, float(gscale),
-                    N._p(self.gacc[idx]), int(acc), N._p(self.sumsq), int(fuse_adam), N._p(self.fp32[idx]), N._p(self.exp_avg[idx]),
+                    N._p(self.gacc[idx]), int(acc), N._p(self.sumsq) if boundary else None, int(fuse_adam), N._p(self.fp32[idx]), N._p(self.exp_avg[idx]),
                     N._p(self.exp_avg_sq[idx]), N._p(lp) if (fuse_adam and lp.is_cuda) else None, float(lr), float(self.betas[0]),
                     float(self.betas[1]), float(self.eps), float(wd), self.step_count + 1, 0, N._st())
             if fuse_adam and not lp.is_cuda:
@@ -370,31 +416,43 @@ class Zero3Engine:
             if self.world > 1:
                 dist.all_reduce(p.grad, group=self.group)
             p.grad.div_(self.world * self.ga)
-        clip = self.max_grad_norm and self.max_grad_norm > 0
-        coef = 1.0
-        if clip:
-            tot = self.sumsq.clone()
-            if self.world > 1:
-                dist.all_reduce(tot, group=self.group)
-            for p in self.persistent:
-                tot += p.grad.float().pow(2).sum()
-            norm = float(tot.sqrt())
-            self.last_grad_norm = norm
-            coef = min(1.0, self.max_grad_norm / (norm + 1e-6))
-        if self.offload_optimizer and self.dev.type == "cuda":
-            torch.cuda.current_stream().synchronize()        # the gradient slices' D2H copies have landed
-        if clip or self.offload_optimizer:
+        clip = bool(self.max_grad_norm and self.max_grad_norm > 0)
+        # global sum(g^2): the reduce kernels accumulated this rank's slices on the boundary micro-step; everything below stays
+        # on the device (the Adam kernels derive the clip coefficient from the scalar themselves)
+        tot = self.sumsq.clone()
+        if self.world > 1:
+            dist.all_reduce(tot, group=self.group)
+        for p in self.persistent:
+            tot += p.grad.float().pow(2).sum()
+        self._norm_sq = tot
+        mx = float(self.max_grad_norm) if clip else 0.0
+        if self.offload_optimizer:
+            coef = 1.0
+            if clip:
+                coef = min(1.0, self.max_grad_norm / (float(tot.sqrt()) + 1e-6))
+            if self.dev.type == "cuda":
+                torch.cuda.current_stream().synchronize()        # the gradient slices' D2H copies have landed
             for i in range(len(self.units)):
                 self._adam_slice(i, coef)
+        elif clip:
+            a = self._arena
+            if a["lp"] is not None:
+                N.adam_(a["fp32"], a["m"], a["v"], a["gacc"], a["lp"], lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, wd=wd,
+                        step=self.step_count + 1, adamw=True, grad_scale=1.0, sumsq=tot, max_norm=mx)
+            else:       # offload_param=cpu: low-precision slices live in pinned host memory
+                N.adam_(a["fp32"], a["m"], a["v"], a["gacc"], None, lr=lr, beta1=self.betas[0], beta2=self.betas[1], eps=self.eps, wd=wd,
+                        step=self.step_count + 1, adamw=True, grad_scale=1.0, sumsq=tot, max_norm=mx)
+                for i, lp in enumerate(self.lp_slices):
+                    lp.copy_(self.fp32[i].to(lp.dtype), non_blocking=True)
         for p, m, v, p32 in zip(self.persistent, self.persist_m, self.persist_v, self.persist_fp32):
             N.adam_(p32.view(-1), m.view(-1), v.view(-1), p.grad.float().view(-1).contiguous(), None, lr=lr, beta1=self.betas[0], beta2=self.betas[1],
-                    eps=self.eps, wd=0.0, step=self.step_count + 1, adamw=True, grad_scale=coef)
+                    eps=self.eps, wd=0.0, step=self.step_count + 1, adamw=True, grad_scale=1.0, sumsq=tot if clip else None, max_norm=mx)
             p.data.copy_(p32.to(p.dtype))
             p.grad = None
         self.step_count += 1
         self.micro = 0
         self.sumsq.zero_()
-        self._resident = [None, None]         # parameter slices changed: workspaces are stale
+        self._resident = [None] * self.n_ws   # parameter slices changed: workspaces are stale
         self._events.clear()
         return True
 
@@ -407,13 +465,13 @@ class Zero3Engine:
         """stage3_gather_16bit_weights_on_model_save: every unit is gathered in turn; returns CPU tensors."""
         out = {}
         for u in self.units:
-            self._resident[u.index % 2] = None
+            self._resident[u.index % self.n_ws] = None
             self._ensure(u.index, forward=True) if self._stream is None else self._gather(u.index)
             if self.dev.type == "cuda":
                 torch.cuda.synchronize()
             for n, p in zip(u.names, u.params):
                 out[f"{u.name}.{n}" if u.name else n] = p.data.detach().cpu().clone()
-        self._resident = [None, None]
+        self._resident = [None] * self.n_ws
         return out
 
     def shard_state(self) -> Dict:
@@ -440,4 +498,4 @@ class Zero3Engine:
                                                  sd["persist_fp32"], sd["persist_m"], sd["persist_v"]):
                 p32.copy_(s32); m.copy_(sm); v.copy_(sv)
                 p.data.copy_(p32.to(p.dtype))
-        self._resident = [None, None]
+        self._resident = [None] * self.n_ws
