@@ -132,7 +132,12 @@ def main():
         return t.item(), last
 
     run(a.warmup, False)
+    sampler = None
+    if cuda and rank == 0:
+        from bench import ClockSampler
+        sampler = ClockSampler(torch.cuda.current_device())
     ms, last = timed(a.steps)
+    clocks = sampler.stop() if sampler is not None else {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
     # the loss lives on the last pipeline stage; share it for the report
     lt = torch.tensor([last if last is not None else -1.0], device=dev)
     dist.all_reduce(lt, op=dist.ReduceOp.MAX)
@@ -144,7 +149,8 @@ def main():
             "metric": "GPT tok/s (Megatron TP/PP)", "value": tokens * a.steps / (ms / 1e3), "unit": "tokens/s", "n_gpus": a.gpus, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16" if cuda else "fp32 (cpu logic check)", "data": "synthetic tokens (pinned host -> device every micro-batch), random-init weights",
-            "impl": "ours", "e2e_included": True, "last_loss": lt.item(),
+            "impl": "ours", "e2e_included": True, "last_loss": lt.item(), "clocks": clocks,
+            "tp_kernels": "fused NVLink kernels" if (args.comm_backend == "native" and a.tp > 1) else "NCCL collectives + tcgen05 GEMMs",
             "config": {"model": f"GPT {a.num_layers}L h{a.hidden_size} {a.heads} heads ({n_params / 1e9:.2f} B parameters)", "global_batch": gbs,
                        "seq_len": a.seq_length, "vocab": a.vocab, "micro_batch": a.micro_batch_size, "num_microbatches": nmb,
                        "parallelism": f"tp{a.tp}{'+sp' if (a.tp > 1 and a.sequence_parallel) else ''} pp{a.pp}"

@@ -300,6 +300,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   [[maybe_unused]] uint64_t* pempty = pfull + RS_PUSH_BUFS;      // [RS_PUSH_BUFS]
   struct PushMeta { uint8_t* dst; uint32_t* cnt; };
   [[maybe_unused]] PushMeta* pmeta = reinterpret_cast<PushMeta*>(pempty + RS_PUSH_BUFS);   // [RS_PUSH_BUFS]
+  // once a CTA has reached its OWN rows nothing is pushed any more: the push buffers become landing tiles for the peers'
+  // staged partials (buffer 2T) and the residual tile (buffer 2T + 1) of team T, filled by TMA and tracked by `sbar`
+  [[maybe_unused]] uint64_t* sbar = reinterpret_cast<uint64_t*>(pmeta + RS_PUSH_BUFS);     // [RS_PUSH_BUFS]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -338,7 +341,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(&tmem_empty[i], EPI_THREADS * TEAMS * (CTA2 ? 2 : 1));   // pair: both CTAs' epilogue threads (leader's copy)
     }
     if constexpr (AUX_TMA) { mbar_init(&aux_bar[0], 1); mbar_init(&aux_bar[1], 1); }
-    if constexpr (FUSE == FUSE_RS) { for (int i = 0; i < RS_PUSH_BUFS; ++i) { mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1); } }
+    if constexpr (FUSE == FUSE_RS) { for (int i = 0; i < RS_PUSH_BUFS; ++i) { mbar_init(&pfull[i], 1); mbar_init(&pempty[i], 1); mbar_init(&sbar[i], 1); } }
     mbar_fence_init();
   }
   if (warp == 2) { if constexpr (CTA2) tmem_alloc_2sm<TMEM_COLS>(tmem_slot); else tmem_alloc<TMEM_COLS>(tmem_slot); }
@@ -537,6 +540,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
     [[maybe_unused]] uint32_t rs_pq = 0;       // GEMM->RS: chunks this team has handed to the push warp
+    [[maybe_unused]] uint32_t rs_phA = 0, rs_phB = 0;     // phases of the two landing-tile barriers
+    [[maybe_unused]] bool rs_landing = false;             // the team's push buffers have been taken over as landing tiles
+    [[maybe_unused]] uint8_t* landA = push_bufs + (team * 2) * STAGE_CHUNK_BYTES;
+    [[maybe_unused]] uint8_t* landB = push_bufs + (team * 2 + 1) * STAGE_CHUNK_BYTES;
+    // leader: start the TMA loads of one own-row chunk: first peer's staged partial -> landA, residual tile -> landB
+    auto rs_issue = [&](int lblk, int col0) {
+      if constexpr (FUSE == FUSE_RS) {
+        const int ncc = (p.N + 63) >> 6;
+        const long long slot_bytes = static_cast<long long>(p.f_shard_rows) * ncc * 128;
+        const int s0 = p.f_rank == 0 ? 1 : 0;
+        const uint8_t* src = static_cast<const uint8_t*>(p.f_stage) + (static_cast<long long>(f_epoch & 1) * p.f_world + s0) * slot_bytes +
+                             (static_cast<long long>(lblk) * ncc + (col0 >> 6)) * STAGE_CHUNK_BYTES;
+        mbar_expect_tx(&sbar[team * 2], STAGE_CHUNK_BYTES);
+        bulk_g2s(landA, src, STAGE_CHUNK_BYTES, &sbar[team * 2]);
+        if (p.f_res != nullptr) {
+          mbar_expect_tx(&sbar[team * 2 + 1], STAGE_CHUNK_BYTES);
+          tma_load_2d(landB, &tmC2, &sbar[team * 2 + 1], col0, lblk * BM);
+        }
+      }
+    };
     // ---- aux tile prefetch (AUX_TMA): the team leader keeps ONE 16 KB TMA load in flight, for the next chunk this team
     // will process; (aux_t, aux_c) is that chunk.  The consumer waits on the team's mbarrier, copies its 128-byte row
     // out of the swizzled tile, and after the team barrier the leader issues the following chunk's load.
@@ -628,7 +651,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               if (team == 0) dbg_stamp(p, 3);
               wait_ge_sys(cnt, expected, 0x104);
               if (team == 0) dbg_stamp(p, 6);
+              if (!rs_landing) {            // both push buffers of this team have been retired by the push warp
+                mbar_wait(&pempty[team * 2 + static_cast<int>(rs_pq & 1u)], ((rs_pq >> 1) & 1u) ^ 1u);
+                mbar_wait(&pempty[team * 2 + static_cast<int>((rs_pq + 1) & 1u)], (((rs_pq + 1) >> 1) & 1u) ^ 1u);
+              }
+              if (n0 + team * 64 < p.N) rs_issue(rs_lblk, n0 + team * 64);
             }
+            rs_landing = true;
             named_bar_sync(bar_id, EPI_THREADS);
           }
         }
@@ -685,47 +714,55 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               // rows owned by this rank are computed LAST: the peers' partial tiles already sit in the local
               // staging slots, so the reduction (+ bias + residual) happens right here and the result goes
               // straight to the output shard - no separate reduce pass, no staging round trip of the own partial
-              const int lrow = rs_lblk * BM + et;
-              if (lrow < p.f_shard_rows) {
-                // staging slots are chunk-major: [parity][source rank][row block][64-column chunk][128 rows][64], and every
-                // 16 KB chunk is the sender's 128B-SWIZZLED shared-memory tile verbatim (it left there as one 1-D bulk copy):
-                // 16-byte unit j of row r sits at unit j ^ (r & 7)
-                const int ncc = (p.N + 63) >> 6;
-                const long long slot = static_cast<long long>(p.f_shard_rows) * ncc * 64;
-                const uint16_t* stage = static_cast<const uint16_t*>(p.f_stage) + static_cast<long long>(f_epoch & 1) * p.f_world * slot +
-                                        ((static_cast<long long>(rs_lblk) * ncc + (col0 >> 6)) * BM + et) * 64;
-                // all global loads of this chunk are issued back to back (independent), then consumed
-                uint4 rq[8];
-                const bool has_res = p.f_res != nullptr, has_bias = p.f_bias != nullptr;
-                if (has_res) {
-                  const uint4* rp = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_res) + static_cast<long long>(lrow) * p.f_ld_res + col0);
+              // staging slots are chunk-major: [parity][source rank][row block][64-column chunk][128 rows][64], and every
+              // 16 KB chunk is the sender's 128B-SWIZZLED shared-memory tile verbatim (it left there as one 1-D bulk copy):
+              // 16-byte unit j of row r sits at unit j ^ (r & 7).  The chunk arrives in the landing tile by ONE bulk copy
+              // (issued a chunk ahead), so every thread reads its 128-byte row from shared memory without bank conflicts.
+              auto add_row = [&](const uint8_t* tile) {
+                const uint8_t* rowp = tile + et * 128;
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) rq[j] = (col0 + j * 8 < p.N) ? __ldg(rp + j) : make_uint4(0u, 0u, 0u, 0u);
-                }
-                auto add8 = [&](const uint4 (&q8)[8]) {
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    const uint4 q = q8[j];
+                for (int j = 0; j < 8; ++j) {
+                  if (col0 + j * 8 < p.N) {
+                    const uint4 q = *reinterpret_cast<const uint4*>(rowp + ((j ^ (et & 7)) << 4));
                     float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
                     f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
                     f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
                   }
-                };
-                for (int s = 0; s < p.f_world; ++s) {
-                  if (s == p.f_rank) continue;
-                  const uint4* sp = reinterpret_cast<const uint4*>(stage + static_cast<long long>(s) * slot);
-                  uint4 sq[8];
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) sq[j] = (col0 + j * 8 < p.N) ? sp[j ^ (et & 7)] : make_uint4(0u, 0u, 0u, 0u);
-                  add8(sq);
                 }
-                if (has_res) add8(rq);
-                if (has_bias) {           // same 128 bytes for every row: L1 hits, no need to hold them across the waits
-                  const uint4* bp2 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_bias) + col0);
-                  uint4 bq[8];
+              };
+              mbar_wait(&sbar[team * 2], rs_phA); rs_phA ^= 1u;
+              add_row(landA);
+              {                                   // further peers (world > 2): one after the other through the same tile
+                const int ncc = (p.N + 63) >> 6;
+                const long long slot_bytes = static_cast<long long>(p.f_shard_rows) * ncc * 128;
+                const int s0 = p.f_rank == 0 ? 1 : 0;
+                for (int sidx = s0 + 1; sidx < p.f_world; ++sidx) {
+                  if (sidx == p.f_rank) continue;
+                  named_bar_sync(bar_id, EPI_THREADS);        // everybody has read the previous partial
+                  if (leader) {
+                    const uint8_t* src = static_cast<const uint8_t*>(p.f_stage) + (static_cast<long long>(f_epoch & 1) * p.f_world + sidx) * slot_bytes +
+                                         (static_cast<long long>(rs_lblk) * ncc + (col0 >> 6)) * STAGE_CHUNK_BYTES;
+                    mbar_expect_tx(&sbar[team * 2], STAGE_CHUNK_BYTES);
+                    bulk_g2s(landA, src, STAGE_CHUNK_BYTES, &sbar[team * 2]);
+                  }
+                  mbar_wait(&sbar[team * 2], rs_phA); rs_phA ^= 1u;
+                  add_row(landA);
+                }
+              }
+              if (p.f_res != nullptr) {
+                mbar_wait(&sbar[team * 2 + 1], rs_phB); rs_phB ^= 1u;
+                add_row(landB);
+              }
+              if (p.f_bias != nullptr) {           // same 128 bytes for every row: L1 hits
+                const uint4* bp2 = reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.f_bias) + col0);
 #pragma unroll
-                  for (int j = 0; j < 8; ++j) bq[j] = (col0 + j * 8 < p.N) ? __ldg(bp2 + j) : make_uint4(0u, 0u, 0u, 0u);
-                  add8(bq);
+                for (int j = 0; j < 8; ++j) {
+                  if (col0 + j * 8 < p.N) {
+                    const uint4 q = __ldg(bp2 + j);
+                    float2 a = unpack2(q.x, fmt), b = unpack2(q.y, fmt), cc = unpack2(q.z, fmt), d = unpack2(q.w, fmt);
+                    f[8 * j + 0] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
+                    f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
+                  }
                 }
               }
             }
@@ -799,6 +836,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             named_bar_sync(bar_id, EPI_THREADS);
             if (aux_on && leader) aux_issue_next();       // every thread of the team has copied its aux row out
+            if constexpr (FUSE == FUSE_RS) {              // ... and its landing-tile rows: fetch this tile's next chunk
+              if (rs_own && leader && c + TEAMS < NCH && col0 + TEAMS * 64 < p.N) rs_issue(rs_lblk, col0 + TEAMS * 64);
+            }
           }
           {
             uint8_t* rowp = sb0 + et * 128;
@@ -1279,7 +1319,12 @@ extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, lon
     uint32_t box[2] = {64, BM};
     if (b2host::encode_tmap(&tC, dt, 2, out, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
   }
-  const CUtensorMap& tC2 = tC;
+  CUtensorMap tC2 = tC;
+  if (residual != nullptr) {       // the owner's reduce epilogue fetches residual tiles by TMA through the C2 map slot
+    uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(p.f_shard_rows)}, strides[2] = {0, static_cast<uint64_t>(ld_res) * 2};
+    uint32_t box[2] = {64, BM};
+    if (b2host::encode_tmap(&tC2, dt, 2, residual, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  }
   const CUtensorMap& tA2 = tA;
   const int total = p.tiles_m * p.tiles_n;
   if (pair) {

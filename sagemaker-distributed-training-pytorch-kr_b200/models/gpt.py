@@ -76,6 +76,13 @@ def _bias_grad(param: Optional[torch.Tensor], dy2: torch.Tensor):
     return acc.to(param.dtype)
 
 
+def _ag_buf(comm, x2):
+    """the fused all-gather->GEMM's input buffer for a LayerNorm output of x2's shape (CUDA + native TP backend), else None"""
+    if not x2.is_cuda or not hasattr(comm, "column_input_buffer"):
+        return None
+    return comm.column_input_buffer(x2.shape[0], x2.shape[1], x2.dtype)
+
+
 class _LayerFn(torch.autograd.Function):
     """x [S_local, B, H] -> y [S_local, B, H] for one transformer layer."""
 
@@ -87,7 +94,7 @@ class _LayerFn(torch.autograd.Function):
         eps = cfg.layernorm_epsilon
         p_h = cfg.hidden_dropout if layer.training else 0.0
         # ---- attention half
-        ln1, mean1, rstd1 = N.norm_fwd(x2, ln1_w, ln1_b, eps)
+        ln1, mean1, rstd1 = N.norm_fwd(x2, ln1_w, ln1_b, eps, out=_ag_buf(comm, x2))
         qkv, ln1_full = comm.column_fwd(ln1, qkv_w, bias=qkv_b, epilogue=N.EPI_BIAS if qkv_b is not None else N.EPI_NONE)
         T = qkv.shape[0]
         S = T // B
@@ -106,7 +113,7 @@ class _LayerFn(torch.autograd.Function):
         else:
             x1 = comm.row_fwd(ctx2, proj_w, bias=proj_b, residual=x2)
         # ---- MLP half
-        ln2, mean2, rstd2 = N.norm_fwd(x1, ln2_w, ln2_b, eps)
+        ln2, mean2, rstd2 = N.norm_fwd(x1, ln2_w, ln2_b, eps, out=_ag_buf(comm, x1))
         z = torch.empty((T, fc1_w.shape[0]), dtype=x.dtype, device=x.device)
         a, ln2_full = comm.column_fwd(ln2, fc1_w, bias=fc1_b, epilogue=N.EPI_BIAS_GELU_DUAL, out2=z)
         if p_h > 0.0:

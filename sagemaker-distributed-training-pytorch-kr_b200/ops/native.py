@@ -236,8 +236,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
 # =============================================================================================
 # LayerNorm / RMSNorm
 # =============================================================================================
-def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor], eps: float, rms: bool = False):
-    """Returns (y, mean, rstd); mean is None for RMSNorm."""
+def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor], eps: float, rms: bool = False,
+             out: Optional[torch.Tensor] = None):
+    """Returns (y, mean, rstd); mean is None for RMSNorm.  ``out`` (CUDA only): a contiguous [rows, H] buffer that receives y
+    (e.g. the symmetric shard buffer the fused all-gather->GEMM reads, which saves its staging copy)."""
     H = x.shape[-1]
     x2 = x.reshape(-1, H)
     rows = x2.shape[0]
@@ -253,7 +255,11 @@ def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor],
             y = (xf - mean[:, None]) * rstd[:, None] * gamma.float() + (beta.float() if beta is not None else 0)
         return y.to(x.dtype).view_as(x), mean, rstd
     assert x2.is_contiguous()
-    y = torch.empty_like(x2)
+    if out is not None:
+        assert out.is_contiguous() and out.shape == x2.shape and out.dtype == x2.dtype
+        y = out
+    else:
+        y = torch.empty_like(x2)
     mean = None if rms else torch.empty(rows, dtype=torch.float32, device=x.device)
     rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
     _call("b2_layernorm_fwd", _p(x2), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, H, float(eps), _dt(x),

@@ -79,6 +79,13 @@ class TPComm:
             if not self.fabric.usable:
                 self.backend, self.fabric = "nccl", None
 
+    def column_input_buffer(self, rows: int, K: int, dtype) -> Optional[torch.Tensor]:
+        """[rows, K] buffer a producer may write the NEXT column_fwd / row_dgrad input into (the symmetric shard buffer of
+        the fused all-gather->GEMM: saves its staging copy), or None when there is none.  Only valid until that call."""
+        if self.sp and self.fabric is not None and rows % 128 == 0:
+            return self.fabric.shard_buffer(rows, K, dtype)
+        return None
+
     # x: [T_local, K] (SP) or [T, K];  W: [N_local, K]  ->  (y [T, N_local], x_full [T, K])
     def column_fwd(self, x2, W, bias=None, epilogue=N.EPI_NONE, out2=None):
         if self.sp:

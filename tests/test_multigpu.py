@@ -72,3 +72,30 @@ def test_gpt_pp2_batched_p2p_matches_single_gpu():
             assert len(got) == 3 == len(ref) and max(abs(a - b) for a, b in zip(got, ref)) < 5e-2, (extra, got, ref)
     finally:
         os.environ.pop("B2_HANG_DUMP_S", None)
+
+
+@pytest.mark.skipif(_ngpu() < 4, reason="needs 4 GPUs")
+def test_gpt_tp2_pp2_interleaved_fused_tp_kernels_match_nccl_tp():
+    """TP=2 (+SP) x PP=2 interleaved on 4 GPUs: the fused AG->GEMM / GEMM->RS kernels next to NCCL pipeline p2p
+    (B2_PP_NATIVE_TP=1: SMs reserved for the NCCL send/recv kernels) give the loss curve of the all-NCCL run"""
+    import re
+    base = ["--num-layers", "4", "--hidden-size", "256", "--num-attention-heads", "4", "--seq-length", "256", "--max-position-embeddings", "256",
+            "--micro-batch-size", "2", "--global-batch-size", "8", "--lr", "1e-3", "--train-iters", "3", "--lr-decay-iters", "3", "--lr-warmup-iters", "1",
+            "--log-interval", "1", "--eval-interval", "100", "--eval-iters", "0", "--tokenizer-type", "NullTokenizer", "--vocab-size", "1023", "--mock-data",
+            "--bf16", "--seed", "11", "--hidden-dropout", "0", "--attention-dropout", "0", "--tensor-model-parallel-size", "2", "--sequence-parallel",
+            "--pipeline-model-parallel-size", "2", "--num-layers-per-virtual-pipeline-stage", "1"]
+    curves = {}
+    os.environ["B2_HANG_DUMP_S"] = "60"
+    try:
+        for native in ("0", "1"):
+            os.environ["B2_PP_NATIVE_TP"] = native
+            rc, out = _torchrun("entrypoints/pretrain_gpt.py", 4, 240, *base, "--comm-backend", "native")
+            assert rc == 0, out[-6000:]
+            if native == "1":
+                assert "reserving SMs for NCCL p2p" in out, out[-3000:]
+            curves[native] = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+    finally:
+        os.environ.pop("B2_PP_NATIVE_TP", None)
+        os.environ.pop("B2_HANG_DUMP_S", None)
+    assert len(curves["0"]) == 3 == len(curves["1"])
+    assert max(abs(a - b) for a, b in zip(curves["0"], curves["1"])) < 5e-2, curves
