@@ -8,7 +8,13 @@ written by data-parallel rank 0 of every (tp, pp) position.  The file is a dict 
 ``optimizer``, ``opt_param_scheduler``, ``rng_state``.  The ``model`` entry nests parameters as
 language_model -> {embedding -> {word_embeddings, position_embeddings}, encoder -> {layers.N....,
 final_layernorm.*}} exactly like Megatron's ``state_dict_for_save_checkpoint`` so files written by the
-reference stack load here and vice versa (flags: arguments.py:922-956)."""
+reference stack load here and vice versa (flags: arguments.py:922-956).
+
+``optimizer``: this framework writes {step, state[name] -> {exp_avg, exp_avg_sq, fp32_param}, grad_scaler, param_groups}; a file
+written by the reference stack carries Megatron's {optimizer: torch-Adam state_dict, grad_scaler, fp32_from_fp16_params}
+instead and is recognised and mapped onto the flat arenas by `MixedPrecisionOptimizer.load_state_dict` (same tensor-parallel
+size required; otherwise load the weights only with --no-load-optim).  Megatron itself cannot read this framework's optimizer
+section or the per-DP-rank `distrib_optim_dpNNN.pt` files: pass --no-load-optim there."""
 from __future__ import annotations
 
 import os
@@ -175,8 +181,6 @@ def load_checkpoint(model: List[torch.nn.Module], optimizer, opt_param_scheduler
             optimizer.load_state_dict(sd["optimizer"])
         if opt_param_scheduler is not None and "opt_param_scheduler" in sd:
             opt_param_scheduler.load_state_dict(sd["opt_param_scheduler"])
-    elif optimizer is not None:
-        optimizer.reload_model_params()
     if not release and not args.finetune and not args.no_load_rng and "rng_state" in sd:
         rs = sd["rng_state"][0]
         random.setstate(rs["random_rng_state"])
@@ -186,8 +190,8 @@ def load_checkpoint(model: List[torch.nn.Module], optimizer, opt_param_scheduler
             torch.cuda.set_rng_state(rs["cuda_rng_state"])
         if rs.get("rng_tracker_states"):
             tp_ops.get_cuda_rng_tracker().set_states(rs["rng_tracker_states"])
-    if optimizer is not None and (args.finetune or args.no_load_optim):
-        optimizer.reload_model_params()
+    if optimizer is not None and (release or args.finetune or args.no_load_optim):
+        optimizer.reload_model_params()        # fp32 master copy <- the freshly loaded model weights
     if dist.is_initialized():
         dist.barrier()
     _p0(f"  successfully loaded checkpoint from {load_dir} at iteration {iteration}")

@@ -172,7 +172,9 @@ def _build_index_mappings(name, data_prefix, documents, sizes, splits_string, nu
         if all(os.path.isfile(os.path.join(pref, f)) for f in fns.values()):
             build, found_prefix = False, pref
             break
-    cache_dir = os.path.dirname(os.path.join(prefixes[0], "x")) if found_prefix is None else found_prefix
+    # no cache found: write to the LAST place looked in - the --data-cache-path when one is given (a read-only data channel
+    # keeps working), else <data dir>/index-cache (reference gpt_dataset.py:345-366)
+    cache_dir = prefixes[-1] if found_prefix is None else found_prefix
     data_cache_success = True
     # every node builds its own cache on its local rank 0 (SageMaker edit, node-local storage)
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -216,6 +218,9 @@ def _build_index_mappings(name, data_prefix, documents, sizes, splits_string, nu
         if counts[0].item() != expect:
             _p0("Data index creation unsuccessful, exiting.")
             raise SystemExit(1)
+    elif not data_cache_success:
+        _p0("Data index creation unsuccessful, exiting.")
+        raise SystemExit(1)
     t0 = time.time()
     doc_idx = np.load(os.path.join(cache_dir, fns["doc"]), allow_pickle=True, mmap_mode="r")
     sample_idx = np.load(os.path.join(cache_dir, fns["sample"]), allow_pickle=True, mmap_mode="r")

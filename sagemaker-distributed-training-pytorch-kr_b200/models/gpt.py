@@ -107,7 +107,9 @@ class _LayerFn(torch.autograd.Function):
         ctx2 = ctx_t.view(T, nh * hd)
         seed1 = seed2 = 0
         if p_h > 0.0:
-            seed1, seed2 = tp_ops.next_dropout_seed(False), tp_ops.next_dropout_seed(False)
+            # under sequence parallelism every TP rank holds a different sequence shard: per-rank stream (Megatron forks the
+            # model-parallel RNG for these dropouts), otherwise the stream that is identical across the TP group
+            seed1, seed2 = tp_ops.next_dropout_seed(comm.sp), tp_ops.next_dropout_seed(comm.sp)
             attn_out = comm.row_fwd(ctx2, proj_w)
             x1 = N.bias_dropout_add(attn_out, proj_b, x2, p_h, seed1)
         else:

@@ -373,13 +373,13 @@ class FlexTransformerLayer(nn.Module):
         res1 = ln1 if cfg.apply_residual_connection_post_layernorm else x2      # both are [T_local, H]
         if p_h > 0.0:
             att = row_parallel_linear(ctx2, sa.dense.weight, None, comm)
-            x1 = _BiasDropoutAdd.apply(att, sa.dense.bias, res1, p_h, tp_ops.next_dropout_seed(False))
+            x1 = _BiasDropoutAdd.apply(att, sa.dense.bias, res1, p_h, tp_ops.next_dropout_seed(comm.sp))
         else:
             x1 = row_parallel_linear(ctx2, sa.dense.weight, sa.dense.bias, comm, res1)
         # ---- MLP half
         ln2 = self.post_attention_layernorm(x1, cfg.layernorm_epsilon)
         res2 = ln2 if cfg.apply_residual_connection_post_layernorm else x1
-        seed2 = tp_ops.next_dropout_seed(False) if p_h > 0.0 else 0
+        seed2 = tp_ops.next_dropout_seed(comm.sp) if p_h > 0.0 else 0
         y2 = self.mlp(ln2, res2, p_h, seed2)
         return y2.view(S_loc, B, H)
 

@@ -116,6 +116,7 @@ class MixedPrecisionOptimizer:
         # order: wd-sharded, wd-replicated, wd-dup, nowd-dup, nowd-replicated, nowd-sharded -> replicated ones adjacent
         keyed.sort(key=lambda k: (k[0], k[1] if k[0] == 0 else -k[1], k[2]))
         self.names = [k[3] for k in keyed]
+        self._module_order = [k[2] for k in keyed]          # position of each entry in module (named_parameters) order
         self.params: List[nn.Parameter] = [k[4] for k in keyed]
         self.is_wd = [k[0] == 0 for k in keyed]
         self.klass = [k[1] for k in keyed]
@@ -299,7 +300,54 @@ class MixedPrecisionOptimizer:
         return {"step": self.step_count, "state": per, "grad_scaler": self.scaler.state_dict() if self.scaler else None,
                 "param_groups": [dict(g) for g in self.param_groups]}
 
+    def _load_reference_layout(self, sd: Dict):
+        """Optimizer section written by the reference stack (Megatron Float16OptimizerWithFloat16Params.state_dict()):
+        {'optimizer': torch Adam state_dict {state: {idx: {exp_avg, exp_avg_sq[, step]}}, param_groups: [{params: [idx..],
+        step?}, ..]}, 'grad_scaler': .., 'fp32_from_fp16_params': [[fp32 tensors of group 0], [group 1]]}.  Megatron builds two
+        groups in module order - weight-decay parameters, then no-weight-decay ones (biases and 1-D tensors) - which is the
+        rule `no_wd_fn` applies here, so the i-th parameter of a group is matched by position and checked by shape."""
+        inner = sd["optimizer"]
+        groups = inner["param_groups"]
+        if len(groups) != 2:
+            raise ValueError(f"reference-layout optimizer state has {len(groups)} parameter groups (expected 2: weight decay / no weight decay); "
+                             "load the model only with --no-load-optim")
+        order = sorted(range(len(self.params)), key=lambda i: self._module_order[i])
+        mine = [[i for i in order if self.is_wd[i]], [i for i in order if not self.is_wd[i]]]
+        fp32 = sd.get("fp32_from_fp16_params")
+        step = None
+        for g, idxs in enumerate(mine):
+            ref_ids = groups[g]["params"]
+            if len(ref_ids) != len(idxs):
+                raise ValueError(f"reference-layout optimizer state: group {g} has {len(ref_ids)} parameters, this model has {len(idxs)}; "
+                                 "load the model only with --no-load-optim")
+            step = groups[g].get("step", step)
+            for k, i in enumerate(idxs):
+                p, o = self.params[i], self.offsets[i]
+                st = inner["state"].get(ref_ids[k])
+                sl = slice(o, o + p.numel())
+                if st is not None:
+                    if tuple(st["exp_avg"].shape) != tuple(p.shape):
+                        raise ValueError(f"reference-layout optimizer state: {self.names[i]} is {tuple(p.shape)} here but {tuple(st['exp_avg'].shape)} in the "
+                                         "checkpoint (different tensor-parallel size?); load the model only with --no-load-optim")
+                    self.exp_avg[sl].copy_(st["exp_avg"].reshape(-1))
+                    if self.exp_avg_sq is not None and st.get("exp_avg_sq") is not None:
+                        self.exp_avg_sq[sl].copy_(st["exp_avg_sq"].reshape(-1))
+                    if st.get("step") is not None:
+                        step = st["step"]
+                if self.low_precision and fp32 is not None:
+                    self.main_param[sl].copy_(fp32[g][k].reshape(-1))
+        if step is not None:
+            self.step_count = int(step)
+        if self.scaler is not None and sd.get("grad_scaler"):
+            gs = sd["grad_scaler"]
+            self.scaler.load_state_dict({"scale": float(gs["scale"]), "growth_tracker": int(gs.get("growth_tracker", 0)),
+                                         "hysteresis_tracker": int(gs.get("hysteresis_tracker", getattr(self.scaler, "hysteresis", 2)))})
+        if not (self.low_precision and fp32 is not None):
+            self.reload_model_params()
+
     def load_state_dict(self, sd: Dict):
+        if "optimizer" in sd and "state" in sd.get("optimizer", {}):       # written by the reference stack
+            return self._load_reference_layout(sd)
         self.step_count = sd["step"]
         for n, p, o in zip(self.names, self.params, self.offsets):
             st = sd["state"].get(n)

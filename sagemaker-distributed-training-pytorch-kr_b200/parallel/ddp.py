@@ -175,9 +175,12 @@ class DistributedDataParallel(nn.Module):
         for r, other in enumerate(gathered):
             if other != sig:
                 raise RuntimeError(f"DDP: parameter shapes differ between rank {self.rank} and rank {r}")
-        src = dist.get_global_rank(self.process_group, 0) if self.process_group is not dist.group.WORLD else 0
         tensors = [p.data for p in self.module.parameters()] + [b for b in self.module.buffers()]
-        self._broadcast_coalesced(tensors, src)
+        self._broadcast_coalesced(tensors, self._src_rank())
+
+    def _src_rank(self) -> int:
+        """global rank of the group's rank 0 (torch.distributed.broadcast takes a GLOBAL source rank)"""
+        return dist.get_global_rank(self.process_group, 0) if self.process_group is not dist.group.WORLD else 0
 
     def _broadcast_coalesced(self, tensors, src, chunk_bytes=250 * _MiB):
         by_dtype = {}
@@ -312,7 +315,18 @@ class DistributedDataParallel(nn.Module):
             m = L.b2h_reducer_ready_order(ctypes.c_void_p(self._core), order)
             self._rebuild_pending = False
             ready = [order[i] for i in range(m)]
-            if ready != [pid for b in self.buckets for pid in b.param_ids]:
+            if self.find_unused_parameters:
+                ready = None       # torch skips the rebuild here: a parameter unused in iteration 1 would have no bucket later
+            else:
+                # every rank must rebuild with the SAME layout (the rebuild allocates symmetric buffers collectively and
+                # same-index buckets are reduced together): rank 0's arrival order wins, as in torch's Reducer
+                seen = set(ready)
+                ready += [i for i in range(len(self._params)) if i not in seen]     # never-ready parameters keep a bucket
+                if self.world_size > 1:
+                    t = torch.tensor(ready, dtype=torch.int32, device=self._params[0].device)
+                    dist.broadcast(t, src=self._src_rank(), group=self.process_group)
+                    ready = [int(v) for v in t.tolist()]
+            if ready is not None and ready != [pid for b in self.buckets for pid in b.param_ids]:
                 self._build_buckets(ready)
                 L.b2h_reducer_reset(ctypes.c_void_p(self._core))
                 return
@@ -344,7 +358,7 @@ class DistributedDataParallel(nn.Module):
         bufs = [b for b in self.module.buffers()
                 if not (self.skip_constant_buffers and not (b.is_floating_point() or b.is_complex()))]
         if bufs:
-            self._broadcast_coalesced(bufs, 0)
+            self._broadcast_coalesced(bufs, self._src_rank())
 
     def forward(self, *args, **kwargs):
         if self.world_size > 1 and self.broadcast_buffers and self.require_backward_grad_sync:

@@ -234,3 +234,50 @@ def _vs_torch_ddp_worker(rank, world, steps):
 def test_ddp_wrapper_tracks_torch_ddp():
     for err, keys_equal in run_distributed(_vs_torch_ddp_worker, 2, 5):
         assert err < 1e-6 and keys_equal
+
+
+class _TwoBranch(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b, self.head = nn.Linear(16, 32), nn.Linear(16, 32), nn.Linear(32, 4)
+
+    def forward(self, x, swap):
+        # the two branches reach autograd in a rank-dependent order, so gradient hooks fire in different orders per rank
+        u, v = (self.b(x), self.a(x)) if swap else (self.a(x), self.b(x))
+        return self.head(torch.relu(u) + torch.relu(v) * 1.0)
+
+
+def _rebuild_order_worker(rank, world):
+    import torch.distributed as dist
+    from b200dist.parallel.ddp import DistributedDataParallel as DDP
+    torch.manual_seed(0)
+    model = _TwoBranch()
+    ddp = DDP(model, bucket_cap_mb=0.002, first_bucket_cap_mb=0.001)
+    torch.manual_seed(50 + rank)
+    xs = [torch.randn(4, 16) for _ in range(3)]
+    for x in xs:
+        ddp.zero_grad()
+        ddp(x, swap=(rank == 1)).sum().backward()
+    layout = [list(b.param_ids) for b in ddp.buckets]
+    objs = [None] * world
+    dist.all_gather_object(objs, layout)
+    g = torch.cat([p.grad.reshape(-1) for p in model.parameters()])
+    # oracle for the last step: mean over ranks of the local gradients
+    torch.manual_seed(0)
+    ref = _TwoBranch()
+    tot = None
+    for r in range(world):
+        torch.manual_seed(50 + r)
+        x = [torch.randn(4, 16) for _ in range(3)][-1]
+        ref.zero_grad()
+        ref(x, swap=(r == 1)).sum().backward()
+        gr = torch.cat([p.grad.reshape(-1) for p in ref.parameters()])
+        tot = gr if tot is None else tot + gr
+    return all(o == objs[0] for o in objs), bool(torch.allclose(g, tot / world, atol=1e-5)), sorted(i for b in layout for i in b) == list(range(6))
+
+
+def test_ddp_bucket_rebuild_uses_rank0_order_on_every_rank():
+    """ranks whose gradients arrive in different orders still rebuild identical buckets (rank 0's order is broadcast), every
+    parameter keeps a bucket, and the reduced gradients are the cross-rank mean"""
+    for same_layout, grads_ok, complete in run_distributed(_rebuild_order_worker, 2):
+        assert same_layout and grads_ok and complete

@@ -178,3 +178,46 @@ def test_dp2_matches_single_on_same_global_batch():
     ref = _single_process_losses(2)
     outs = run_distributed(_train_worker, 2, 1, 1, 0, False, 2)
     assert np.allclose(outs[0], ref, rtol=2e-4, atol=2e-4)
+
+
+def test_optimizer_loads_the_reference_stack_optimizer_layout():
+    """an `optimizer` checkpoint section in Megatron's layout (torch-Adam state_dict + fp32_from_fp16_params, two parameter
+    groups in module order) lands in the flat arenas exactly like this framework's own layout"""
+    import torch
+    from b200dist.config.megatron_args import TransformerConfig
+    from b200dist.models.gpt import GPTModel
+    from b200dist.optim.mixed import MixedPrecisionOptimizer, default_no_weight_decay
+    cfg = TransformerConfig(num_layers=2, hidden_size=32, num_attention_heads=4, ffn_hidden_size=64, kv_channels=8, seq_length=16,
+                            max_position_embeddings=16, padded_vocab_size=64, hidden_dropout=0.0, attention_dropout=0.0,
+                            params_dtype=torch.bfloat16, bf16=True)
+    torch.manual_seed(0)
+    model = GPTModel(cfg, device=torch.device("cpu"), layer_offset=0, num_layers_here=2)
+    a = MixedPrecisionOptimizer([model], lr=1e-3, weight_decay=0.1, clip_grad=1.0)
+    tokens = torch.randint(0, 64, (2, 17))
+    for _ in range(2):
+        a.zero_grad()
+        model(tokens[:, :-1].contiguous(), labels=tokens[:, 1:].contiguous()).mean().backward()
+        a.reduce_model_grads(); a.step()
+    own = a.state_dict()
+    # restate it the way Megatron's Float16OptimizerWithFloat16Params writes it
+    named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
+    groups = [[(n, p) for n, p in named if not default_no_weight_decay(n, p)], [(n, p) for n, p in named if default_no_weight_decay(n, p)]]
+    state, pg, fp32, idx = {}, [], [], 0
+    for g in groups:
+        ids = []
+        for n, p in g:
+            state[idx] = {"exp_avg": own["state"][n]["exp_avg"], "exp_avg_sq": own["state"][n]["exp_avg_sq"]}
+            ids.append(idx); idx += 1
+        pg.append({"params": ids, "step": own["step"], "lr": 1e-3})
+        fp32.append([own["state"][n]["fp32_param"] for n, p in g])
+    ref_layout = {"optimizer": {"state": state, "param_groups": pg}, "grad_scaler": None, "fp32_from_fp16_params": fp32}
+    torch.manual_seed(1)
+    model_b = GPTModel(cfg, device=torch.device("cpu"), layer_offset=0, num_layers_here=2)
+    b = MixedPrecisionOptimizer([model_b], lr=1e-3, weight_decay=0.1, clip_grad=1.0)
+    b.load_state_dict(ref_layout)
+    assert b.step_count == a.step_count
+    assert torch.equal(b.exp_avg, a.exp_avg) and torch.equal(b.exp_avg_sq, a.exp_avg_sq) and torch.equal(b.main_param, a.main_param)
+    bad = {"optimizer": {"state": state, "param_groups": pg[:1]}, "fp32_from_fp16_params": fp32}
+    import pytest
+    with pytest.raises(ValueError, match="--no-load-optim"):
+        b.load_state_dict(bad)

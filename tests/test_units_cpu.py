@@ -496,3 +496,31 @@ def test_merge_datasets_tool(tmp_path):
     assert n_docs == 10 and n_items == len(flat) == len(ds) and ds[0].dtype == np.uint16
     assert all((ds[i] == s).all() for i, s in enumerate(flat))
     assert list(ds.doc_idx) == list(np.cumsum([0] + [len(d) for d in all_docs]))
+
+
+def test_gpt_dataset_index_cache_goes_to_data_cache_path_on_a_read_only_data_dir(tmp_path):
+    """--data-cache-path is where a missing index cache is WRITTEN (reference gpt_dataset.py:345-366): a read-only data
+    channel keeps working; a second build finds the files there and writes nothing"""
+    import os, stat
+    from b200dist.data import indexed_dataset as idx
+    from b200dist.data.gpt_dataset import build_train_valid_test_datasets
+    data = tmp_path / "data"; cache = tmp_path / "cache"
+    data.mkdir()
+    rs = np.random.RandomState(1)
+    b = idx.make_builder(idx.data_file_path(str(data / "corpus")), "mmap", dtype=np.uint16)
+    for _ in range(30):
+        b.add_item(rs.randint(0, 500, size=rs.randint(5, 40))); b.end_document()
+    b.finalize(idx.index_file_path(str(data / "corpus")))
+    os.chmod(data, stat.S_IRUSR | stat.S_IXUSR)          # read-only channel
+    try:
+        tr, va, te = build_train_valid_test_datasets([str(data / "corpus")], "mmap", "8,1,1", [12, 2, 2], 16, 1234, True, data_cache_path=str(cache))
+        assert not (data / "index-cache").exists()
+        files = sorted(os.listdir(cache))
+        assert any(f.endswith("_doc_idx.npy") for f in files) and any(f.endswith(".dsc") for f in files)
+        first = [tr[i]["text"].tolist() for i in range(4)]
+        mtimes = {f: os.path.getmtime(cache / f) for f in files}
+        tr2, _, _ = build_train_valid_test_datasets([str(data / "corpus")], "mmap", "8,1,1", [12, 2, 2], 16, 1234, True, data_cache_path=str(cache))
+        assert sorted(os.listdir(cache)) == files and all(os.path.getmtime(cache / f) == t for f, t in mtimes.items())
+        assert [tr2[i]["text"].tolist() for i in range(4)] == first
+    finally:
+        os.chmod(data, stat.S_IRWXU)
