@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--vocab", type=int, default=32768)
     ap.add_argument("--tp", type=int, default=0, help="0 = min(2, gpus) (the BASELINE config)")
     ap.add_argument("--comm-backend", default="native", choices=["native", "nccl"])
-    ap.add_argument("--dropout", type=float, default=0.0)
+    ap.add_argument("--dropout", type=float, default=0.1, help="hidden AND attention dropout (reference run: 0.1 each, 3_training_megatron-lm.ipynb:985,1056)")
     ap.add_argument("--no-clocks", action="store_true")
     ap.add_argument("--kernel-profile", default="", help="after the timed runs, trace 2 more steps with torch.profiler (CUPTI) on rank 0 and write a per-kernel table here (diagnostic: never a bench value)")
     ap.add_argument("--no-cuda-graph", action="store_true", help="issue every kernel from Python instead of replaying the captured micro-batch graph")
@@ -144,11 +144,11 @@ def main():
             "--global-batch-size", str(gbs), "--tensor-model-parallel-size", str(tp), "--bf16", "--tokenizer-type", "NullTokenizer",
             "--vocab-size", str(a.vocab - 1), "--mock-data", "--train-iters", str(a.steps + a.warmup + 2), "--lr", "3e-4", "--min-lr", "3e-5",
             "--lr-decay-style", "cosine", "--lr-warmup-iters", "2", "--weight-decay", "0.1", "--adam-beta2", "0.95", "--clip-grad", "1.0",
-            "--hidden-dropout", str(a.dropout), "--attention-dropout", "0.0", "--log-interval", "1000000", "--eval-iters", "0",
+            "--hidden-dropout", str(a.dropout), "--attention-dropout", str(a.dropout), "--log-interval", "1000000", "--eval-iters", "0",
             "--comm-backend", a.comm_backend, "--num-workers", "0"]
     if tp > 1:
         argv.append("--sequence-parallel")
-    if not a.no_cuda_graph and a.dropout == 0.0:
+    if not a.no_cuda_graph:
         argv.append("--cuda-graph")
     _stdout = sys.stdout
     sys.stdout = sys.stderr      # keep stdout for the single JSON line
@@ -246,7 +246,7 @@ def main():
                "impl": "ours",
                "config": {"model": f"GPT-2 small {a.num_layers}L h{a.hidden_size} {a.heads} heads (Megatron GPT, CodeParrot-style)", "global_batch": gbs,
                           "seq_len": a.seq_length, "vocab": a.vocab, "micro_batch": a.micro_batch_size, "num_microbatches": nmb,
-                          "parallelism": f"tp{tp}{'+sp' if tp > 1 else ''} dp{dp}", "comm_backend": a.comm_backend, "dropout": a.dropout, "cuda_graph": bool(not a.no_cuda_graph and a.dropout == 0.0),
+                          "parallelism": f"tp{tp}{'+sp' if tp > 1 else ''} dp{dp}", "comm_backend": a.comm_backend, "dropout": a.dropout, "cuda_graph": bool(not a.no_cuda_graph),
                           "optimizer": "AdamW fp32 master + grad clip 1.0", "l2": "per-step working set (weights+activations, GBs) exceeds the 126 MB L2"},
                "clocks": clocks,
                "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": nmb * a.micro_batch_size * (a.seq_length + 1) * 8 if is_src else 0,

@@ -50,6 +50,7 @@ struct AttnParams {
   // scaled by inv_keep.  The row sum / LSE use the un-dropped probabilities (dropout acts on softmax output).
   uint32_t drop_thresh;  // p * 2^32
   uint32_t drop_seed;
+  const unsigned long long* drop_replay;   // device replay counter mixed into drop_seed (NULL = off), see host.cu
   float inv_keep;        // 1 / (1 - p)
   int dbg_skip;          // profiling hook (b2_attn_set_debug): bit 0 = skip the dQ reduce-add, bit 1 = skip the softmax math
 };
@@ -215,7 +216,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int qpos = q0 + r;
     const float sl2 = p.scale * LOG2E;
-    [[maybe_unused]] const uint32_t drop_base = p.drop_seed + static_cast<uint32_t>(qpos) * DROP_CQ +
+    [[maybe_unused]] const uint32_t drop_seed_r = p.drop_replay == nullptr ? p.drop_seed : p.drop_seed ^ static_cast<uint32_t>((*p.drop_replay * 0x9E3779B97F4A7C15ull) >> 32);
+    [[maybe_unused]] const uint32_t drop_base = drop_seed_r + static_cast<uint32_t>(qpos) * DROP_CQ +
                                                 static_cast<uint32_t>(bat * p.heads + head) * DROP_CB;
     constexpr int DH = D / 2;                             // output columns per thread
     float m_run = -INFINITY, l_run = 0.f, alpha_prev = 1.f;   // l_run: partial sum over this thread's columns
@@ -552,7 +554,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t lane_off = static_cast<uint32_t>(ew * 32) << 16;
     const int kpos = k0 + r;
     const float sl2 = p.scale * LOG2E;
-    [[maybe_unused]] const uint32_t drop_base = p.drop_seed + static_cast<uint32_t>(kpos) * DROP_CK +
+    [[maybe_unused]] const uint32_t drop_seed_r = p.drop_replay == nullptr ? p.drop_seed : p.drop_seed ^ static_cast<uint32_t>((*p.drop_replay * 0x9E3779B97F4A7C15ull) >> 32);
+    [[maybe_unused]] const uint32_t drop_base = drop_seed_r + static_cast<uint32_t>(kpos) * DROP_CK +
                                                 static_cast<uint32_t>(bat * p.heads + head) * DROP_CB;
     const size_t stat_base = (static_cast<size_t>(bat) * p.heads + head) * p.seqlen;
 
@@ -708,6 +711,7 @@ void set_dropout(AttnParams& p, float p_drop, unsigned long long seed) {
   const double t = static_cast<double>(p_drop) * 4294967296.0;
   p.drop_thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
   p.drop_seed = static_cast<uint32_t>(seed ^ (seed >> 32));
+  p.drop_replay = p_drop > 0.f ? b2host::dropout_replay_ptr() : nullptr;
   p.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
 }
 }  // namespace

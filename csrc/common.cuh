@@ -371,6 +371,11 @@ B2_DEVICE float2 unpack_bf16x2(uint32_t u) {
   return __bfloat1622float2(v);
 }
 
+// seed of this launch in this graph replay: the host-drawn seed, scrambled with the replay counter when one is installed
+B2_DEVICE unsigned long long replay_seed(unsigned long long seed, const unsigned long long* replay) {
+  return replay == nullptr ? seed : seed ^ (*replay * 0x9E3779B97F4A7C15ull);
+}
+
 B2_DEVICE float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -397,6 +402,7 @@ int encode_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* 
                 const uint64_t* strides_bytes, const uint32_t* box, CUtensorMapSwizzle swz);
 const char* last_error();
 void set_error(const char* fmt, ...);
+const unsigned long long* dropout_replay_ptr();   // device word mixed into dropout seeds (NULL = off), see host.cu
 int num_sms();            // SM count minus the reserve set with set_reserved_sms
 void set_reserved_sms(int n);
 }  // namespace b2host

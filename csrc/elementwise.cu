@@ -78,7 +78,9 @@ B2_DEVICE float gelu_erf_grad(float x) {
 // out = residual + dropout(x + bias)           (training: p > 0 uses the Philox mask)
 template <typename T>
 __global__ void bias_dropout_add_kernel(const T* __restrict__ x, const T* __restrict__ bias, const T* __restrict__ res,
-                                        T* __restrict__ out, long long nvec, int H, float p, uint64_t seed) {
+                                        T* __restrict__ out, long long nvec, int H, float p, uint64_t seed,
+                                        const unsigned long long* __restrict__ replay) {
+  seed = replay_seed(seed, replay);
   const float inv = p > 0.f ? 1.f / (1.f - p) : 1.f;
   for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
     float a[8], b[8], r[8], o[8];
@@ -98,7 +100,9 @@ __global__ void bias_dropout_add_kernel(const T* __restrict__ x, const T* __rest
 }
 // dx = dropout_mask * dy / (1-p)
 template <typename T>
-__global__ void dropout_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, long long nvec, float p, uint64_t seed) {
+__global__ void dropout_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, long long nvec, float p, uint64_t seed,
+                                   const unsigned long long* __restrict__ replay) {
+  seed = replay_seed(seed, replay);
   const float inv = 1.f / (1.f - p);
   for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
     float a[8], o[8];
@@ -313,14 +317,14 @@ extern "C" int b2_bias_dropout_add(const void* x, const void* bias, const void* 
   if (n % 8 || H % 8) { b2host::set_error("bias_dropout_add: sizes must be multiples of 8"); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   long long nvec = n / 8;
-  DISPATCH_T(dtype, (bias_dropout_add_kernel<T><<<grid_for(nvec, 256), 256, 0, st>>>((const T*)x, (const T*)bias, (const T*)residual, (T*)out, nvec, H, p, seed)));
+  DISPATCH_T(dtype, (bias_dropout_add_kernel<T><<<grid_for(nvec, 256), 256, 0, st>>>((const T*)x, (const T*)bias, (const T*)residual, (T*)out, nvec, H, p, seed, b2host::dropout_replay_ptr())));
   return check("bias_dropout_add");
 }
 extern "C" int b2_dropout_bwd(const void* dy, void* dx, long long n, float p, unsigned long long seed, int dtype, void* stream) {
   if (n % 8) { b2host::set_error("dropout_bwd: size must be a multiple of 8"); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   long long nvec = n / 8;
-  DISPATCH_T(dtype, (dropout_bwd_kernel<T><<<grid_for(nvec, 256), 256, 0, st>>>((const T*)dy, (T*)dx, nvec, p, seed)));
+  DISPATCH_T(dtype, (dropout_bwd_kernel<T><<<grid_for(nvec, 256), 256, 0, st>>>((const T*)dy, (T*)dx, nvec, p, seed, b2host::dropout_replay_ptr())));
   return check("dropout_bwd");
 }
 extern "C" int b2_bias_act_fwd(const void* x, const void* bias, void* out, long long n, int H, int mode, int dtype, void* stream) {

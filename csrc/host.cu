@@ -37,6 +37,12 @@ int num_sms() {
   return n < 8 ? 8 : n;
 }
 
+// Device word that every dropout kernel mixes into its seed (NULL = off).  A CUDA graph bakes the seeds that the host drew at
+// capture time into its kernel nodes; a captured one-thread kernel bumps this word at the start of every replay, so each
+// replay draws fresh masks while forward and backward of the same replay still see the same value.
+static const unsigned long long* g_dropout_replay = nullptr;
+const unsigned long long* dropout_replay_ptr() { return g_dropout_replay; }
+
 EncodeTiledFn get_encode_fn() {
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
@@ -80,6 +86,16 @@ int encode_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* 
 
 }  // namespace b2host
 
+namespace {
+__global__ void counter_add_kernel(unsigned long long* p, unsigned long long inc) { *p += inc; }
+}  // namespace
+extern "C" void b2_set_dropout_replay_counter(const void* dev_word) { b2host::g_dropout_replay = static_cast<const unsigned long long*>(dev_word); }
+extern "C" int b2_counter_add(void* dev_word, unsigned long long inc, void* stream) {
+  counter_add_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<unsigned long long*>(dev_word), inc);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { b2host::set_error("counter_add: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
 extern "C" const char* b2_last_error(void) { return b2host::last_error(); }
 extern "C" int b2_num_sms(void) { return b2host::num_sms(); }
 extern "C" void b2_set_reserved_sms(int n) { b2host::set_reserved_sms(n); }

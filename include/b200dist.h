@@ -31,6 +31,13 @@ extern "C" {
 
 const char* b2_last_error(void);
 int b2_num_sms(void);
+/* Dropout under CUDA graphs: a captured kernel node carries the seed the host drew at capture time.  Install a device
+ * word with b2_set_dropout_replay_counter (NULL = off) and capture b2_counter_add(word, 1) at the head of the graph: every
+ * dropout kernel (bias-dropout-add, dropout backward, attention dropout) scrambles its seed with the word, so each replay
+ * draws new masks and forward / backward of one replay agree.  (The reference draws from the CUDA RNG tracker instead:
+ * megatron/arguments.py:687-690 hidden_dropout / attention_dropout 0.1.) */
+void b2_set_dropout_replay_counter(const void* dev_word);
+int b2_counter_add(void* dev_word, unsigned long long inc, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * GEMM (tcgen05 + TMEM + TMA).  C[M,N] (+)= alpha * op(A)[M,K] . op(B)[K,N]

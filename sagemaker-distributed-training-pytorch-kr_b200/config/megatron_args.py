@@ -95,7 +95,7 @@ GROUPS: Dict[str, List[Flag]] = {
         _f("--no-async-tensor-model-parallel-allreduce", action=F_, dest="async_tensor_model_parallel_allreduce"),
         _f("--no-persist-layer-norm", action=T), _f("--sequence-parallel", action=T),
         _f("--no-gradient-accumulation-fusion", action=F_, dest="gradient_accumulation_fusion"),
-        _f("--cuda-graph", action=T, help="(addition) replay the micro-batch forward+backward as a CUDA graph (PP=1, dropout 0)"),
+        _f("--cuda-graph", action=T, help="(addition) replay the micro-batch forward+backward as a CUDA graph (PP=1)"),
     ],
     "initialization": [
         _f("--seed", type=int, default=1234), _f("--data-parallel-random-init", action=T), _f("--init-method-std", type=float, default=0.02),

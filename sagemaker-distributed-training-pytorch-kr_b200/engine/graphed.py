@@ -8,8 +8,10 @@ gradient arena and the token buffer are static - and replayed per micro-batch.  
 between steps (learning rate, Adam bias correction, loss-scale bookkeeping) stays outside the graph in the
 optimizer step, which is only a handful of launches.
 
-Constraints (checked by ``supported``): pipeline size 1, dropout 0 (the Philox seeds advance on the host),
-fixed micro-batch shape.  Collectives inside the captured region (tensor-parallel NCCL or the fused fabric
+Constraints (checked by ``supported``): pipeline size 1, fixed micro-batch shape.  Dropout: the counter-based seeds are
+drawn on the host, so a captured kernel node would repeat its mask on every replay; the graph therefore starts with a
+one-thread kernel that bumps a device-side replay counter which every dropout kernel mixes into its seed
+(``ops.native.dropout_replay_counter``) - forward and backward of one replay agree, successive replays differ.  Collectives inside the captured region (tensor-parallel NCCL or the fused fabric
 kernels, the data-parallel loss average) are captured with it.
 """
 from __future__ import annotations
@@ -36,8 +38,8 @@ class _StaticIter:
 
 
 def supported(args, model=None) -> bool:
-    ok = (torch.cuda.is_available() and args.pipeline_model_parallel_size == 1 and args.hidden_dropout == 0.0
-          and args.attention_dropout == 0.0 and not args.fp16 and args.recompute_granularity is None
+    ok = (torch.cuda.is_available() and args.pipeline_model_parallel_size == 1
+          and not args.fp16 and args.recompute_granularity is None
           and getattr(args, "num_experts", None) is None)          # Switch-MLP routing (`nonzero`) is data dependent: not capturable
     if ok and args.tensor_model_parallel_size > 1:
         # tensor-parallel collectives inside the captured region must be the fabric kernels (plain launches);
@@ -59,8 +61,14 @@ class GraphedMicrobatch:
         self.tp_src = mpu.get_tensor_model_parallel_src_rank()
         self.is_src = mpu.get_tensor_model_parallel_rank() == 0
         self._static_iter = _StaticIter({"text": self.tokens})
+        self.dropout = any(getattr(m, "training", False) for m in [model]) and (
+            getattr(getattr(model, "cfg", None), "hidden_dropout", 0.0) > 0.0 or getattr(getattr(model, "cfg", None), "attention_dropout", 0.0) > 0.0)
+        if self.dropout:
+            N.dropout_replay_counter(device)
 
     def _one(self):
+        if self.dropout:
+            N.bump_dropout_replay_counter()        # first node of the captured graph: new dropout masks per replay
         out, loss_func = self.fwd(self._static_iter, self.model)
         loss, reduced = loss_func(out)
         (loss / self.M).backward()

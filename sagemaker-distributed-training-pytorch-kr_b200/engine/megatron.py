@@ -291,7 +291,7 @@ def get_graph_runner(forward_step_func, model):
     _GRAPH["tried"] = True
     from . import graphed
     if len(model) != 1 or not graphed.supported(args, model[0]):
-        print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, dropout 0, bf16/fp32, no recompute, fabric collectives for TP): running eagerly")
+        print_rank_0("> --cuda-graph requested but not applicable (needs PP=1, bf16/fp32, no recompute, fabric collectives for TP): running eagerly")
         return None
     if args.rampup_batch_size is not None:
         print_rank_0("> --cuda-graph replays a fixed number of micro-batches: not used with --rampup-batch-size")

@@ -79,6 +79,7 @@ _SIGS = {
     "b2_softmax_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_i, c_p],
     "b2_softmax_bwd": [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_p],
     "b2_num_sms": [],
+    "b2_counter_add": [c_p, c_ull, c_p],
 }
 
 
@@ -128,6 +129,27 @@ def set_reserved_sms(n: int) -> None:
     L.b2_set_reserved_sms.argtypes = [ctypes.c_int]
     L.b2_set_reserved_sms.restype = None
     L.b2_set_reserved_sms(int(n))
+
+
+_replay_word: Optional[torch.Tensor] = None
+
+
+def dropout_replay_counter(device=None) -> torch.Tensor:
+    """Installs (once) the device word that every dropout kernel mixes into its seed and returns it.  A CUDA graph that
+    contains dropout captures ``bump_dropout_replay_counter()`` as its first node, so each replay draws new masks."""
+    global _replay_word
+    if _replay_word is None:
+        dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        _replay_word = torch.zeros(1, dtype=torch.int64, device=dev)
+        L = lib()
+        L.b2_set_dropout_replay_counter.argtypes = [ctypes.c_void_p]
+        L.b2_set_dropout_replay_counter.restype = None
+        L.b2_set_dropout_replay_counter(_p(_replay_word))
+    return _replay_word
+
+
+def bump_dropout_replay_counter() -> None:
+    _call("b2_counter_add", _p(dropout_replay_counter()), 1, _st())
 
 
 def launches() -> int:

@@ -60,3 +60,46 @@ def test_smoke_entry():
     sys.path.insert(0, ROOT)
     import __graft_entry__ as ge
     ge.smoke()
+
+
+def test_dropout_masks_change_between_graph_replays_and_agree_within_one():
+    """dropout under a CUDA graph: the captured seed is scrambled with a device-side replay counter that the graph's first
+    node bumps, so (1) two replays draw different masks, (2) forward and backward of one replay use the same mask, for the
+    Philox element-wise dropout and for attention dropout"""
+    import torch
+    from b200dist.ops import native as N
+    dev = torch.device("cuda", 0)
+    x = torch.ones(4096, 256, device=dev, dtype=torch.bfloat16)
+    S, B, H, D = 256, 2, 4, 64
+    torch.manual_seed(0)
+    qkv = torch.randn(S, B, H, 3 * D, device=dev, dtype=torch.bfloat16)
+    q, k, v = qkv[..., :D], qkv[..., D:2 * D], qkv[..., 2 * D:]
+    N.dropout_replay_counter(dev)
+    out = {}
+
+    def step():
+        N.bump_dropout_replay_counter()
+        out["y"] = N.bias_dropout_add(x, None, None, 0.25, 1234)
+        out["dx"] = N.dropout_bwd(x, 0.25, 1234)
+        out["o"], out["lse"] = N.attn_fwd(q, k, v, 0.125, True, p_drop=0.2, seed=77)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        step()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        step()
+    seen = []
+    for _ in range(3):
+        g.replay()
+        torch.cuda.synchronize()
+        y, dx, o = out["y"].float(), out["dx"].float(), out["o"].float().clone()
+        assert torch.equal(y == 0, dx == 0), "forward and backward masks of one replay differ"
+        keep = (y != 0).float().mean().item()
+        assert abs(keep - 0.75) < 0.01, keep
+        seen.append(((y != 0).clone(), o))
+    assert not torch.equal(seen[0][0], seen[1][0]) and not torch.equal(seen[1][0], seen[2][0]), "replays repeated the element-wise mask"
+    assert not torch.equal(seen[0][1], seen[1][1]), "replays repeated the attention-dropout mask"
