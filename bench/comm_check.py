@@ -92,7 +92,17 @@ if which in ("all", "allreduce"):
             F.all_reduce_(buf, scale=1.0 / world)       # second call on the same buffer (epochs advance)
             torch.cuda.synchronize()
             report(f"allreduce {dtype} n={n} (2nd call)", buf.tensor[:n], ref, tol)
-    for mb in (1, 25, 224, 497):
+    # reduce-scatter with a scale factor, fp32 and bf16 (the bf16 multicast branch once dropped it)
+    for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2)):
+        torch.manual_seed(31 + rank)
+        x = torch.randn(world * 512, 384, device=dev).to(dtype)
+        ref = x.clone().float()
+        dist.all_reduce(ref)
+        ref = ref[rank * 512:(rank + 1) * 512] * 0.37
+        got = F.reduce_scatter_rows(x, scale=0.37)
+        torch.cuda.synchronize()
+        report(f"reduce_scatter_rows scale=0.37 {dtype}", got, ref, tol)
+    for mb in (1, 4, 25, 64, 224, 497):
         n = mb * (1 << 20) // 4
         buf = F.alloc(n, torch.float32)
         t = torch.randn(n, device=dev)

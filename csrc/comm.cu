@@ -36,7 +36,7 @@ B2_DEVICE void fabric_barrier(const Peers& P, int rank, int world, uint32_t epoc
     __threadfence_system();
     st_release_sys(P.ctrl[threadIdx.x] + slot_base + rank, epoch);
     const uint32_t* mine = P.ctrl[rank] + slot_base + threadIdx.x;
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) { }
+    wait_ge_sys(mine, epoch, 0x201);
   }
   __syncthreads();
 }
@@ -65,7 +65,7 @@ B2_DEVICE uint32_t enter(const Peers& P, int rank, int world, uint32_t* my_ctrl)
     if (threadIdx.x == 0) st_release_gpu(my_ctrl + 0, epoch);
   } else {
     if (threadIdx.x == 0) {
-      while (static_cast<int32_t>(ld_acquire_gpu(my_ctrl + 0) - epoch) < 0) { }
+      wait_ge_gpu(my_ctrl + 0, epoch, 0x202);
     }
     __syncthreads();
   }
@@ -85,7 +85,82 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
   const long long per = (nvec + world - 1) / world;
   const long long v0 = per * rank, v1 = min(nvec, v0 + per);
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long v = v0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < v1; v += stride) {
+  long long v = v0 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if constexpr (MULTICAST && MODE != 2) {
+    // four independent 16-byte multimem.ld_reduce per thread in flight: the switch round trip (~2-3 us) needs depth, not
+    // more CTAs - one load per iteration left this kernel behind NCCL from 25 MiB up
+    constexpr int U = 4;
+    for (; v + (U - 1) * stride < v1; v += U * stride) {
+      uint32_t r[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint8_t* mc = static_cast<const uint8_t*>(mc_base) + (v + u * stride) * 16;
+        if constexpr (sizeof(T) == 4) {
+          float a, b, c, d;
+          mm_ld_reduce_f32x4(mc, a, b, c, d);
+          r[u][0] = __float_as_uint(a); r[u][1] = __float_as_uint(b); r[u][2] = __float_as_uint(c); r[u][3] = __float_as_uint(d);
+        } else {
+          mm_ld_reduce_bf16x8(mc, r[u][0], r[u][1], r[u][2], r[u][3]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if constexpr (sizeof(T) == 4) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) r[u][i] = __float_as_uint(__uint_as_float(r[u][i]) * scale);
+        } else if (scale != 1.f) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { const float2 f = unpack_bf16x2(r[u][i]); r[u][i] = pack_bf16x2(f.x * scale, f.y * scale); }
+        }
+        if constexpr (MODE == 1) {
+          *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v + u * stride - v0) * 16) = make_uint4(r[u][0], r[u][1], r[u][2], r[u][3]);
+        } else {
+          mm_st_b32x4(static_cast<uint8_t*>(mc_base) + (v + u * stride) * 16, r[u][0], r[u][1], r[u][2], r[u][3]);
+        }
+      }
+    }
+  }
+  if constexpr (!MULTICAST && MODE != 2) {
+    // two ranks: plain peer loads / stores move n bytes per direction where the multicast path moves 1.5 n (the switch
+    // also fetches the requester's own copy); four independent remote loads per thread hide the NVLink round trip
+    if (world == 2) {
+      constexpr int U = 4;
+      const uint8_t* mine = static_cast<const uint8_t*>(P.ptr[rank]);
+      const uint8_t* peer = static_cast<const uint8_t*>(P.ptr[rank ^ 1]);
+      for (; v + (U - 1) * stride < v1; v += U * stride) {
+        uint4 a[U], b[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) b[u] = *reinterpret_cast<const uint4*>(peer + (v + u * stride) * 16);
+#pragma unroll
+        for (int u = 0; u < U; ++u) a[u] = *reinterpret_cast<const uint4*>(mine + (v + u * stride) * 16);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          uint4 o;
+          if constexpr (sizeof(T) == 4) {
+            o = make_uint4(__float_as_uint((__uint_as_float(a[u].x) + __uint_as_float(b[u].x)) * scale), __float_as_uint((__uint_as_float(a[u].y) + __uint_as_float(b[u].y)) * scale),
+                           __float_as_uint((__uint_as_float(a[u].z) + __uint_as_float(b[u].z)) * scale), __float_as_uint((__uint_as_float(a[u].w) + __uint_as_float(b[u].w)) * scale));
+          } else {
+            const uint32_t* pa = reinterpret_cast<const uint32_t*>(&a[u]);
+            const uint32_t* pb = reinterpret_cast<const uint32_t*>(&b[u]);
+            uint32_t po[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const float2 fa = unpack_bf16x2(pa[i]), fb = unpack_bf16x2(pb[i]);
+              po[i] = pack_bf16x2((fa.x + fb.x) * scale, (fa.y + fb.y) * scale);
+            }
+            o = make_uint4(po[0], po[1], po[2], po[3]);
+          }
+          if constexpr (MODE == 1) {
+            *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v + u * stride - v0) * 16) = o;
+          } else {
+            *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[rank]) + (v + u * stride) * 16) = o;
+            *reinterpret_cast<uint4*>(static_cast<uint8_t*>(P.ptr[rank ^ 1]) + (v + u * stride) * 16) = o;
+          }
+        }
+      }
+    }
+  }
+  for (; v < v1; v += stride) {
     if constexpr (MODE == 2) {
       const uint4 q = *reinterpret_cast<const uint4*>(static_cast<const uint8_t*>(P.ptr[rank]) + v * 16);
       if constexpr (MULTICAST) {
@@ -96,22 +171,12 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
       }
     } else if constexpr (MULTICAST) {
       uint8_t* mc = static_cast<uint8_t*>(mc_base) + v * 16;
-      if constexpr (MODE == 1) {
-        uint4 o;
-        if constexpr (sizeof(T) == 4) {
-          float a, b, c, d;
-          mm_ld_reduce_f32x4(mc, a, b, c, d);
-          o = make_uint4(__float_as_uint(a * scale), __float_as_uint(b * scale), __float_as_uint(c * scale), __float_as_uint(d * scale));
-        } else {
-          mm_ld_reduce_bf16x8(mc, o.x, o.y, o.z, o.w);
-        }
-        *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v - v0) * 16) = o;
-      } else if constexpr (sizeof(T) == 4) {
-        float a, b, c, d;
-        mm_ld_reduce_f32x4(mc, a, b, c, d);
-        mm_st_f32x4(mc, a * scale, b * scale, c * scale, d * scale);
+      uint32_t a, b, c, d;
+      if constexpr (sizeof(T) == 4) {
+        float fa, fb, fc, fd;
+        mm_ld_reduce_f32x4(mc, fa, fb, fc, fd);
+        a = __float_as_uint(fa * scale); b = __float_as_uint(fb * scale); c = __float_as_uint(fc * scale); d = __float_as_uint(fd * scale);
       } else {
-        uint32_t a, b, c, d;
         mm_ld_reduce_bf16x8(mc, a, b, c, d);
         if (scale != 1.f) {
           float2 f;
@@ -120,8 +185,9 @@ allreduce_kernel(Peers P, void* mc_base, long long n_elems, float scale, int ran
           f = unpack_bf16x2(c); c = pack_bf16x2(f.x * scale, f.y * scale);
           f = unpack_bf16x2(d); d = pack_bf16x2(f.x * scale, f.y * scale);
         }
-        mm_st_b32x4(mc, a, b, c, d);
       }
+      if constexpr (MODE == 1) *reinterpret_cast<uint4*>(static_cast<uint8_t*>(out) + (v - v0) * 16) = make_uint4(a, b, c, d);
+      else                     mm_st_b32x4(mc, a, b, c, d);
     } else {
       float acc[8];
 #pragma unroll
@@ -264,6 +330,9 @@ extern "C" int b2_ctrl_words(void) { return B2_CTRL_WORDS; }
 
 // ptrs / ctrls: `world` peer-mapped addresses each (host arrays).  mc_ptr: multicast address of the payload or NULL.
 // n_elems * sizeof(dtype) must be a multiple of 16.  In place on every rank's payload.
+static bool g_force_no_mc = false;
+// A/B switch for measurements: 1 = never use the multicast (multimem) instructions, 0 = default selection
+extern "C" void b2_collective_force_peer_path(int on) { g_force_no_mc = on != 0; }
 static int run_collective(int mode, void* const* ptrs, void* const* ctrls, void* mc_ptr, long long n_elems, int dtype, float scale,
                           int rank, int world, int max_ctas, void* out, cudaStream_t st) {
   if (world < 1 || world > MAX_RANKS) { b2host::set_error("collective: world size %d unsupported (max %d)", world, MAX_RANKS); return -1; }
@@ -276,11 +345,18 @@ static int run_collective(int mode, void* const* ptrs, void* const* ctrls, void*
   long long per = (nvec + world - 1) / world;
   int threads = 512;
   long long want = (per + threads - 1) / threads;
-  int cap = max_ctas > 0 ? max_ctas : 64;
+  // every thread keeps 4 vectors in flight: payloads above ~16 MiB per rank get up to 128 CTAs, small ones stay small so
+  // that a bucket reduced on the communication stream takes few SMs from the backward pass it overlaps
+  want = (want + 3) / 4;
+  int cap = max_ctas > 0 ? max_ctas : (per * 16 >= (16LL << 20) ? 128 : 64);
+  if (cap > b2host::num_sms()) cap = b2host::num_sms();
   int grid = static_cast<int>(want < 1 ? 1 : (want > cap ? cap : want));
 #define B2_LAUNCH(T_, MC_, MODE_) allreduce_kernel<T_, MC_, MODE_><<<grid, threads, 0, st>>>(P, mc_ptr, n_elems, scale, rank, world, out)
 #define B2_BY_MODE(T_, MC_) do { if (mode == 0) B2_LAUNCH(T_, MC_, 0); else if (mode == 1) B2_LAUNCH(T_, MC_, 1); else B2_LAUNCH(T_, MC_, 2); } while (0)
-  if (mc_ptr != nullptr) { if (esz == 4) B2_BY_MODE(float, true); else B2_BY_MODE(__nv_bfloat16, true); }
+  // reductions between TWO ranks take the peer load/store path (less NVLink traffic than a round trip through the switch's
+  // multicast unit, see the kernel); the all-gather (mode 2) and larger groups use multimem when it is available
+  const bool use_mc = mc_ptr != nullptr && (world > 2 || mode == 2) && !g_force_no_mc;
+  if (use_mc) { if (esz == 4) B2_BY_MODE(float, true); else B2_BY_MODE(__nv_bfloat16, true); }
   else                   { if (esz == 4) B2_BY_MODE(float, false); else B2_BY_MODE(__nv_bfloat16, false); }
 #undef B2_BY_MODE
 #undef B2_LAUNCH

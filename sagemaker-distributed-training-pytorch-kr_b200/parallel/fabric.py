@@ -116,13 +116,13 @@ class Fabric:
             self._coll[key] = self.alloc(numel, dtype)
         return self._coll[key]
 
-    def reduce_scatter_rows(self, x2: torch.Tensor) -> torch.Tensor:
-        """[world*rows, C] partial sums on every rank -> [rows, C] reduced shard (multimem.ld_reduce of my slice)."""
+    def reduce_scatter_rows(self, x2: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+        """[world*rows, C] partial sums on every rank -> [rows, C] reduced shard * scale (multimem.ld_reduce of my slice)."""
         n = x2.numel()
         buf = self._coll_buf(n, x2.dtype, "rs")
         buf.tensor.view_as(x2).copy_(x2)
         out = torch.empty((x2.shape[0] // self.world,) + tuple(x2.shape[1:]), dtype=x2.dtype, device=x2.device)
-        N._call("b2_reduce_scatter", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n, N._dt(x2), 1.0, self.rank,
+        N._call("b2_reduce_scatter", buf.ptrs, buf.ctrls, c_p(buf.mc_ptr) if buf.mc_ptr else None, n, N._dt(x2), float(scale), self.rank,
                 self.world, 0, N._p(out), N._st())
         return out
 
