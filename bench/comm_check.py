@@ -193,6 +193,35 @@ if which in ("all", "rs"):
         roof = max(2.0 * M * Nn * K / 1.39e15, M * Nn * 2 * (world - 1) / world / 770e9) * 1e3
         p0(f"graph-timed gemm_rs {tag:5s} M{M} K{K} N{Nn}: fused {gf*1e3:7.1f} us | plain gemm {gg*1e3:7.1f} us | roofline {roof*1e3:6.1f} us -> {roof/gf:.2f} of roofline")
 
+if which in ("all", "ar_gemm"):
+    for (M, K, Nn, bmn) in [(512, 128, 256, False), (2048, 384, 768, False), (12288, 1536, 768, False), (2048, 576, 768, True)]:
+        if M % (128 * world):
+            continue
+        torch.manual_seed(300 + rank)
+        a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+        W = torch.randn((K, Nn) if bmn else (Nn, K), device=dev, dtype=torch.bfloat16) * 0.05
+        torch.manual_seed(9)
+        bias = torch.randn(Nn, device=dev, dtype=torch.bfloat16)
+        res = torch.randn(M, Nn, device=dev, dtype=torch.bfloat16)
+        out = F.gemm_ar(a, W, b_mn=bmn, bias=bias, residual=res)
+        torch.cuda.synchronize()
+        part = a.float() @ (W.float() if bmn else W.float().t())
+        dist.all_reduce(part)
+        ref = part + bias.float() + res.float()
+        report(f"gemm_ar M{M} K{K} N{Nn} b_mn={int(bmn)}", out, ref, 3e-2)
+        out2 = F.gemm_ar(a, W, b_mn=bmn, bias=bias, residual=res)
+        out3 = F.gemm_ar(a, W, b_mn=bmn)
+        torch.cuda.synchronize()
+        report(f"gemm_ar (2nd call) M{M}", out2, ref, 3e-2)
+        report(f"gemm_ar (3rd call, no bias / residual) M{M}", out3, part, 3e-2)
+    for (M, K, Nn, tag) in [(12288, 192, 768, "proj tp4"), (12288, 768, 768, "fc2 tp4"), (12288, 384, 768, "proj tp2")]:
+        a = torch.randn(M, K, device=dev, dtype=torch.bfloat16); W = torch.randn(Nn, K, device=dev, dtype=torch.bfloat16)
+        t = torch.empty(M, Nn, device=dev, dtype=torch.bfloat16)
+        gf = graph_time(lambda: F.gemm_ar(a, W))
+        gg = graph_time(lambda: N.gemm(a, W))
+        ms_n = timeit(lambda: dist.all_reduce(N.gemm(a, W)))
+        p0(f"graph-timed gemm_ar {tag:9s} M{M} K{K} N{Nn}: fused {gf*1e3:7.1f} us (incl. the private copy of the result) | plain gemm {gg*1e3:7.1f} us | gemm + nccl all_reduce {ms_n*1e3:7.1f} us (stream-timed)")
+
 p0("FAILED:" if FAILS else "ALL OK", FAILS)
 dist.barrier()
 dist.destroy_process_group()

@@ -63,6 +63,7 @@ struct GemmParams {
   const void* f_bias;              // RS: bias [N] added once, after the reduction
   const void* f_res;               // RS: residual shard [shard_rows, f_ld_res]
   long long f_ld_res;
+  const CUtensorMap* f_armaps;     // GEMM->all-reduce: device array [world] of maps over every rank's full [M, N] output (NULL: reduce-scatter)
   unsigned long long* f_dbg;       // optional [gridDim.x][8] globaltimer stamps (profiling builds of the caller)
 };
 
@@ -182,7 +183,9 @@ B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t e
 
 // Last CTA of a fused launch: wait until no peer still depends on this rank's symmetric data, then mark
 // the call complete (ctrl[1] = epoch) so the next launch on this buffer derives the next epoch.
-B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers_done) {
+// announce: first tell every peer that this rank's stores of the call have all completed (GEMM->all-reduce: together with
+// the wait this is the closing cross-GPU barrier - every rank's broadcast rows have landed everywhere)
+B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers_done, bool announce = false) {
   __syncthreads();
   __shared__ bool last;
   uint32_t* my_ctrl = p.f_ctrl[p.f_rank];
@@ -192,6 +195,11 @@ B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers
   }
   __syncthreads();
   if (last && threadIdx.x == 0) {
+    if (announce) {
+      __threadfence_system();
+      for (int r = 0; r < p.f_world; ++r)
+        if (r != p.f_rank) st_release_sys(p.f_ctrl[r] + FCTRL_B + p.f_rank, epoch);
+    }
     if (wait_peers_done) {
       for (int r = 0; r < p.f_world; ++r)
         if (r != p.f_rank)
@@ -857,7 +865,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               // goes out verbatim as ONE 1-D bulk copy through the peer mapping (large NVLink writes; the owner undoes the
               // swizzle when it reads), and the transfer overlaps the following tiles' mainloops
               if (rs_own) {
-                tma_store_2d(&tmC, sb0, col0, rs_lblk * BM);          // final rows of this rank
+                if (p.f_armaps != nullptr) {      // all-reduce: the reduced rows go to EVERY rank's full output (TMA stores, peers included)
+                  for (int r = 0; r < p.f_world; ++r) tma_store_2d(p.f_armaps + r, sb0, col0, m0);
+                } else {
+                  tma_store_2d(&tmC, sb0, col0, rs_lblk * BM);          // final rows of this rank
+                }
                 tma_store_commit();
               } else {
                 const int ncc = (p.N + 63) >> 6;
@@ -887,7 +899,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if constexpr (FUSE != FUSE_NONE) { if (threadIdx.x == 0) dbg_stamp(p, 4); }
   if (warp == 2) { if constexpr (CTA2) tmem_dealloc_2sm<TMEM_COLS>(tmem_base); else tmem_dealloc<TMEM_COLS>(tmem_base); }
   if constexpr (FUSE == FUSE_AG) fused_finish(p, f_epoch, true);
-  if constexpr (FUSE == FUSE_RS) fused_finish(p, f_epoch, false);
+  if constexpr (FUSE == FUSE_RS) {
+    // (every epilogue leader has waited for the completion of its TMA stores before the CTA-wide barrier above)
+    const bool ar = p.f_armaps != nullptr;
+    fused_finish(p, f_epoch, ar, ar);
+  }
 }
 
 template <int BN, bool A_MN, bool B_MN, bool ERF = false>
@@ -1281,10 +1297,10 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
 // cnt_ptrs[r]:   rank r's per-row-block arrival counters (symmetric, zero before the first call)
 // replaces: cuBLAS GEMM + NCCL reduce_scatter_tensor (+ bias-dropout-add) of RowParallelLinear forward and
 //           ColumnParallelLinear backward under sequence parallelism.
-extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
-                          int dtype, void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs,
-                          void* out, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
-                          int world, void* stream_) {
+static int gemm_rs_impl(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
+                        int dtype, void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs,
+                        void* out, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
+                        int world, const void* armaps_dev, void* stream_) {
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (world < 2 || world > 8) { b2host::set_error("gemm_rs: world size %d unsupported", world); return -1; }
   if (M % (world * BM)) { b2host::set_error("gemm_rs: M (%d) must be a multiple of world * %d", M, BM); return -1; }
@@ -1311,6 +1327,7 @@ extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, lon
     p.f_stage_peer[r] = r < world ? static_cast<uint8_t*>(stage_ptrs[r]) : nullptr;
   }
   p.f_dbg = g_fused_dbg;
+  p.f_armaps = static_cast<const CUtensorMap*>(armaps_dev);
   p.f_stage = stage_ptrs[rank]; p.f_out = out; p.f_ld_out = ld_out; p.f_bias = bias; p.f_res = residual; p.f_ld_res = ld_res;
   CUtensorMap tA, tB, tC;
   if (make_ab_maps(&tA, &tB, A, B, M, N, K, lda, ldb, b_mn_major, pair ? bn / 2 : bn, dt)) return -1;
@@ -1321,6 +1338,8 @@ extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, lon
   }
   CUtensorMap tC2 = tC;
   if (residual != nullptr) {       // the owner's reduce epilogue fetches residual tiles by TMA through the C2 map slot
+    if (armaps_dev != nullptr)     // all-reduce: `residual` is the full [M, N] tensor; this rank reduces rows [rank * shard_rows, ...)
+      residual = static_cast<const uint8_t*>(residual) + static_cast<long long>(rank) * p.f_shard_rows * ld_res * 2;
     uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(p.f_shard_rows)}, strides[2] = {0, static_cast<uint64_t>(ld_res) * 2};
     uint32_t box[2] = {64, BM};
     if (b2host::encode_tmap(&tC2, dt, 2, residual, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
@@ -1337,3 +1356,45 @@ extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, lon
   B2_FUSED_DISPATCH(FUSE_RS, false);
 }
 #undef B2_FUSED_DISPATCH
+
+extern "C" int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
+                          int dtype, void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs,
+                          void* out, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
+                          int world, void* stream_) {
+  return gemm_rs_impl(A, B, M, N, K, lda, ldb, b_mn_major, dtype, cnt_ptrs, ctrls, stage_ptrs, out, ld_out, bias, residual, ld_res, rank,
+                      world, nullptr, stream_);
+}
+
+// Uploads (synchronously, once per output buffer / shape) the `world` tensor maps of the GEMM->all-reduce kernel:
+// map[r] = rank r's full [M, N] output (row stride ld_out elements) in symmetric memory, boxes of 128 rows x 64 columns.
+extern "C" int b2_make_ar_maps(void* dev_out, void* const* out_ptrs, int world, int M, int N, long long ld_out, int dtype) {
+  CUtensorMap maps[8];
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  if (world < 2 || world > 8) { b2host::set_error("make_ar_maps: world size %d unsupported", world); return -1; }
+  for (int r = 0; r < world; ++r) {
+    uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(M)}, strides[2] = {0, static_cast<uint64_t>(ld_out) * 2};
+    uint32_t box[2] = {64, BM};
+    if (b2host::encode_tmap(&maps[r], dt, 2, out_ptrs[r], dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  }
+  cudaError_t e = cudaMemcpy(dev_out, maps, sizeof(CUtensorMap) * world, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) { b2host::set_error("make_ar_maps: %s", cudaGetErrorString(e)); return -1; }
+  return 0;
+}
+
+// GEMM -> all-reduce in ONE kernel (tensor parallelism WITHOUT sequence parallelism: RowParallelLinear forward and
+// ColumnParallelLinear backward all-reduce their [tokens, hidden] result over the TP group).  Same kernel as b2_gemm_rs -
+// partial tiles of rows another rank reduces are pushed to it while later tiles are still being multiplied - except that
+// the rank that has reduced a row block (+ bias + residual) TMA-stores it into EVERY rank's full output, and the launch
+// ends with a cross-GPU barrier, after which out_ptrs[rank] holds all M rows on every rank.
+//   out[M, N] (on all ranks) = residual + bias + sum_ranks (A_r @ op(B_r));   residual: the full [M, N] tensor or NULL
+// armaps_dev: from b2_make_ar_maps for these out_ptrs.  out buffers are symmetric memory.
+// replaces: cuBLAS GEMM + NCCL all_reduce (Megatron `reduce_from_tensor_model_parallel_region`, the logged TP=4 run with
+//           sequence_parallel False, 3_training_megatron-lm.ipynb:1162).
+extern "C" int b2_gemm_ar(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major,
+                          int dtype, void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, const void* armaps_dev,
+                          void* out_local, long long ld_out, const void* bias, const void* residual, long long ld_res, int rank,
+                          int world, void* stream_) {
+  if (armaps_dev == nullptr) { b2host::set_error("gemm_ar: output tensor maps missing (b2_make_ar_maps)"); return -1; }
+  return gemm_rs_impl(A, B, M, N, K, lda, ldb, b_mn_major, dtype, cnt_ptrs, ctrls, stage_ptrs, out_local, ld_out, bias, residual, ld_res,
+                      rank, world, armaps_dev, stream_);
+}

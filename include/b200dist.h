@@ -226,6 +226,15 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, void* out,
                long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world,
                void* stream);
+/* GEMM -> all-reduce (tensor parallelism without sequence parallelism): the b2_gemm_rs kernel whose reducing rank stores
+ * each finished row block into EVERY rank's full [M, N] output and which ends with a cross-GPU barrier.  out buffers are
+ * symmetric; armaps_dev = `world` tensor maps uploaded once by b2_make_ar_maps (a synchronous cudaMemcpy: set-up time only).
+ * residual: full [M, N] or NULL.  replaces: cuBLAS GEMM + NCCL all_reduce of Row/ColumnParallelLinear with
+ * sequence_parallel False (3_training_megatron-lm.ipynb:1162). */
+int b2_make_ar_maps(void* dev_out, void* const* out_ptrs, int world, int M, int N, long long ld_out, int dtype);
+int b2_gemm_ar(const void* A, const void* B, int M, int N, int K, long long lda, long long ldb, int b_mn_major, int dtype,
+               void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, const void* armaps_dev, void* out_local,
+               long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world, void* stream);
 void b2_fused_config(int pair_mode, int n_comm);
 
 /* ------------------------------------------------------------------------------------------

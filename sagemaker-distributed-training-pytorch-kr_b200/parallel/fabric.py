@@ -69,6 +69,10 @@ class Fabric:
             L.b2_ag_gemm.restype = c_i
             L.b2_gemm_rs.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
             L.b2_gemm_rs.restype = c_i
+            L.b2_make_ar_maps.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_i]
+            L.b2_make_ar_maps.restype = c_i
+            L.b2_gemm_ar.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
+            L.b2_gemm_ar.restype = c_i
             L.b2_fused_config.argtypes = [c_i, c_i]
             L.b2_fused_config.restype = None
             L.b2_reduce_scatter.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p, c_p]
@@ -193,6 +197,31 @@ class Fabric:
                 st["stage"].ctrls, st["stage"].ptrs, N._p(out), out.stride(0), N._p(bias),
                 N._p(residual), residual.stride(0) if residual is not None else 0, self.rank, self.world, N._st())
         return out
+
+
+def _gemm_ar(self, a2: torch.Tensor, W: torch.Tensor, b_mn: bool = False, bias=None, residual=None):
+    """out[M, N] = residual + bias + all_reduce(a2 @ op(W)) in one kernel; every rank gets the full result (a private copy)."""
+    M, K = a2.shape
+    if M % (128 * self.world):
+        raise ValueError(f"gemm_ar: M ({M}) must be a multiple of 128 * world")
+    rows = M // self.world
+    Nn = W.shape[1] if b_mn else W.shape[0]
+    st = self._rs_state(rows, Nn, a2.dtype)
+    if "ar_out" not in st:
+        out = self.alloc(M * Nn, a2.dtype)
+        maps = torch.empty(self.world * 128, dtype=torch.uint8, device=a2.device)
+        rc = N.lib().b2_make_ar_maps(N._p(maps), out.ptrs, self.world, M, Nn, Nn, N._dt(a2))
+        if rc != 0:
+            raise RuntimeError("b2_make_ar_maps: " + N.lib().b2_last_error().decode())
+        st["ar_out"], st["ar_maps"] = out, maps
+    out = st["ar_out"]
+    N._call("b2_gemm_ar", N._p(a2), N._p(W), M, Nn, K, a2.stride(0), W.stride(0), int(b_mn), N._dt(a2), st["cnt"].ptrs,
+            st["stage"].ctrls, st["stage"].ptrs, N._p(st["ar_maps"]), N._p(out.tensor), Nn, N._p(bias),
+            N._p(residual), residual.stride(0) if residual is not None else 0, self.rank, self.world, N._st())
+    return out.tensor.view(M, Nn).clone()
+
+
+Fabric.gemm_ar = _gemm_ar
 
 
 def get_fabric(group=None) -> Fabric:

@@ -105,6 +105,8 @@ class TPComm:
             return N.gemm(a2, W, bias=bias, epilogue=N.EPI_BIAS if bias is not None else N.EPI_NONE)
         if self.fabric is not None and self.sp:
             return self.fabric.gemm_rs(a2, W, bias=bias, residual=residual)
+        if self.fabric is not None and a2.shape[0] % (128 * self.size) == 0:       # no SP: GEMM -> all-reduce in one kernel
+            return self.fabric.gemm_ar(a2, W, bias=bias, residual=residual)
         part = N.gemm(a2, W)
         red = reduce_scatter_first_dim(part, self.group) if self.sp else all_reduce(part, self.group)
         if bias is None and residual is None:
@@ -117,6 +119,8 @@ class TPComm:
             return N.gemm(dy2, W, b_mn=True)
         if self.fabric is not None and self.sp:
             return self.fabric.gemm_rs(dy2, W, b_mn=True)
+        if self.fabric is not None and dy2.shape[0] % (128 * self.size) == 0:
+            return self.fabric.gemm_ar(dy2, W, b_mn=True)
         part = N.gemm(dy2, W, b_mn=True)
         return reduce_scatter_first_dim(part, self.group) if self.sp else all_reduce(part, self.group)
 

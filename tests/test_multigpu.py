@@ -52,6 +52,24 @@ def test_gpt_tp2_sp_native_matches_nccl_backend():
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_gpt_tp2_without_sp_gemm_allreduce_kernel_matches_nccl_backend():
+    """TP=2 WITHOUT sequence parallelism (the reference's logged layout): RowParallelLinear forward / ColumnParallelLinear
+    backward run the fused GEMM->all-reduce kernel; same loss curve as GEMM + NCCL all_reduce"""
+    base = ["--num-layers", "2", "--hidden-size", "256", "--num-attention-heads", "4", "--seq-length", "256", "--max-position-embeddings", "256",
+            "--micro-batch-size", "4", "--global-batch-size", "8", "--lr", "1e-3", "--train-iters", "4", "--lr-decay-iters", "4", "--lr-warmup-iters", "1",
+            "--log-interval", "1", "--eval-interval", "100", "--eval-iters", "0", "--tokenizer-type", "NullTokenizer", "--vocab-size", "1023", "--mock-data",
+            "--bf16", "--tensor-model-parallel-size", "2", "--seed", "11", "--hidden-dropout", "0", "--attention-dropout", "0"]
+    import re
+    curves = {}
+    for backend in ("native", "nccl"):
+        rc, out = _torchrun("entrypoints/pretrain_gpt.py", 2, 300, *base, "--comm-backend", backend)
+        assert rc == 0, out[-4000:]
+        curves[backend] = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+    assert len(curves["native"]) == 4 == len(curves["nccl"])
+    assert max(abs(a - b) for a, b in zip(curves["native"], curves["nccl"])) < 5e-2, curves
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
 def test_gpt_pp2_batched_p2p_matches_single_gpu():
     """PP=2 (1F1B, then interleaved) over NCCL with the batched p2p transport against the same model on one GPU; every
     launch sits inside `timeout`, and B2_HANG_DUMP_S prints where each rank waits if it stalls"""
