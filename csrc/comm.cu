@@ -409,3 +409,9 @@ extern "C" int b2_rs_update(void* const* ptrs, void* const* ctrls, void* mc_ptr,
 #undef B2_RS
   return check("rs_update");
 }
+
+namespace b2host {
+int set_spin_timeout_comm(unsigned long long ns) {
+  return cudaMemcpyToSymbol(b2::g_b2_spin_timeout_ns, &ns, sizeof(ns)) == cudaSuccess ? 0 : -1;
+}
+}  // namespace b2host

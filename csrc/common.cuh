@@ -339,6 +339,7 @@ B2_DEVICE unsigned long long globaltimer_ns() {
 #define B2_SPIN_TIMEOUT_NS 4000000000ull
 #endif
 static __device__ unsigned int g_b2_spin_timeout_site;      // last site id that timed out in this translation unit (0 = none)
+static __device__ unsigned long long g_b2_spin_timeout_ns = B2_SPIN_TIMEOUT_NS;   // per translation unit; b2_set_spin_timeout_ms
 B2_DEVICE void spin_timeout(unsigned int site) {
   g_b2_spin_timeout_site = site;
   __threadfence_system();
@@ -350,7 +351,7 @@ B2_DEVICE void wait_ge_sys(const uint32_t* p, uint32_t target, unsigned int site
   const unsigned long long t0 = globaltimer_ns();
   uint32_t polls = 0;
   while (static_cast<int32_t>(ld_acquire_sys(p) - target) < 0) {
-    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > B2_SPIN_TIMEOUT_NS) spin_timeout(site);
+    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > g_b2_spin_timeout_ns) spin_timeout(site);
   }
 }
 B2_DEVICE void wait_ge_gpu(const uint32_t* p, uint32_t target, unsigned int site) {
@@ -358,7 +359,7 @@ B2_DEVICE void wait_ge_gpu(const uint32_t* p, uint32_t target, unsigned int site
   const unsigned long long t0 = globaltimer_ns();
   uint32_t polls = 0;
   while (static_cast<int32_t>(ld_acquire_gpu(p) - target) < 0) {
-    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > B2_SPIN_TIMEOUT_NS) spin_timeout(site);
+    if ((++polls & 1023u) == 0 && globaltimer_ns() - t0 > g_b2_spin_timeout_ns) spin_timeout(site);
   }
 }
 
@@ -404,5 +405,7 @@ const char* last_error();
 void set_error(const char* fmt, ...);
 const unsigned long long* dropout_replay_ptr();   // device word mixed into dropout seeds (NULL = off), see host.cu
 int num_sms();            // SM count minus the reserve set with set_reserved_sms
+int set_spin_timeout_gemm(unsigned long long ns);     // gemm.cu / comm.cu: copy the bound into their translation unit's device word
+int set_spin_timeout_comm(unsigned long long ns);
 void set_reserved_sms(int n);
 }  // namespace b2host

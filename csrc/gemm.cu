@@ -283,7 +283,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   constexpr bool AUX_TMA = (FUSE != FUSE_RS);
   // GEMM->RS: four 16 KB push buffers (two per epilogue team) between the epilogue and the push warp come out of the ring
   constexpr int RS_PUSH_BUFS = 4;
-  constexpr int RING_BYTES = AUX_TMA ? SMEM_MAIN_BYTES - 2 * STAGE_CHUNK_BYTES : SMEM_MAIN_BYTES - RS_PUSH_BUFS * STAGE_CHUNK_BYTES;
+  // pair kernels (except GEMM->RS) double-buffer the epilogue staging: a second 16 KB tile per team, also out of the ring,
+  // so a chunk's shared-memory write never waits for the previous chunk's TMA store to be read out (for K = 768 the
+  // epilogue, not the mainloop, paces the kernel: ncu shows the tensor pipe active 64 % of the time)
+  constexpr bool EPI_DB = CTA2 && (FUSE != FUSE_RS);
+  constexpr int RING_BYTES = AUX_TMA ? SMEM_MAIN_BYTES - (EPI_DB ? 4 : 2) * STAGE_CHUNK_BYTES : SMEM_MAIN_BYTES - RS_PUSH_BUFS * STAGE_CHUNK_BYTES;
   constexpr int STAGES = RING_BYTES / STAGE_BYTES;
   constexpr uint32_t TMEM_COLS = 512;
   // two epilogue teams everywhere; in GEMM->RS each team leader signals its own half of every tile, so a row block
@@ -295,6 +299,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint8_t* stage_base = smem;
   [[maybe_unused]] uint8_t* aux_tiles = smem + RING_BYTES;   // AUX_TMA: 2 x 16 KB (one per epilogue team)
   uint8_t* epi_buf = smem + SMEM_MAIN_BYTES;       // 2 x 16 KB
+  [[maybe_unused]] uint8_t* epi_buf2 = smem + RING_BYTES + 2 * STAGE_CHUNK_BYTES;     // EPI_DB: the teams' second staging tiles
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_buf + 2 * STAGE_CHUNK_BYTES);
   uint64_t* full_bar = bars;
   uint64_t* empty_bar = bars + STAGES;
@@ -543,7 +548,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int et = ew * 32 + lane;                 // 0..127 == accumulator row
     const bool leader = (et == 0);
     const int bar_id = 1 + team;
-    uint8_t* team_buf = epi_buf + team * STAGE_CHUNK_BYTES;   // TEAMS == 2: one staging tile per team
+    uint8_t* team_buf = epi_buf + team * STAGE_CHUNK_BYTES;   // TEAMS == 2: one staging tile per team (two with EPI_DB)
+    [[maybe_unused]] uint8_t* team_buf2 = epi_buf2 + team * STAGE_CHUNK_BYTES;
+    // staging tile of store group number n of this team, and the wait that makes it reusable
+    auto stage_of = [&](int n) -> uint8_t* { return (EPI_DB && (n & 1)) ? team_buf2 : team_buf; };
+    auto stage_wait = [&]() { if constexpr (EPI_DB) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); };
     const int fmt = p.fmt;
     int it = 0;
     int sctr = 0;  // staging-buffer ring counter (one increment per issued TMA store group)
@@ -620,9 +629,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tmem_ld_wait();
           if (c + TEAMS >= NCH) { tc_fence_before(); acc_release(&tmem_empty[buf]); }
           if (n0 + c * 32 >= p.N) continue;   // uniform across the team
-          uint8_t* sb = (TEAMS == 2) ? team_buf : epi_buf + (sctr & 1) * STAGE_CHUNK_BYTES;
+          uint8_t* sb = stage_of(sctr);
           ++sctr;
-          if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+          if (leader) stage_wait();
           named_bar_sync(bar_id, EPI_THREADS);
           if (p.alpha != 1.f) {
 #pragma unroll
@@ -777,12 +786,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
           // staging: TEAMS == 2 -> the team's own tile (reused once its previous TMA store has read it);
           //          TEAMS == 1 -> ring of two tiles
-          uint8_t* sb0 = (TEAMS == 2) ? team_buf : epi_buf + (dual ? 0 : (sctr & 1)) * STAGE_CHUNK_BYTES;
-          ++sctr;
+          uint8_t* sb0 = stage_of(dual ? sctr + 1 : sctr);      // dual: z goes through tile n, gelu(z) through tile n + 1
+          sctr += dual ? 2 : 1;
           if (dual) {
             // pre-activation z -> C2 first, gelu(z) -> C second (through the same staging tile when TEAMS == 2)
-            uint8_t* sb1 = (TEAMS == 2) ? team_buf : epi_buf + STAGE_CHUNK_BYTES;
-            if (leader) tma_store_wait_read<0>();
+            uint8_t* sb1 = stage_of(sctr - 2);
+            if (leader) stage_wait();
             named_bar_sync(bar_id, EPI_THREADS);
             uint8_t* rowp = sb1 + et * 128;
 #pragma unroll
@@ -804,7 +813,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               for (int i = 0; i < 64; ++i) f[i] = gelu_tanh(f[i]);     // runs while the TMA engine reads the z tile
             }
             if (TEAMS == 2) {
-              if (leader) tma_store_wait_read<0>();
+              if (leader) stage_wait();           // EPI_DB: the other tile (last used two groups ago) is free; else wait for the z store
               named_bar_sync(bar_id, EPI_THREADS);
             }
           } else {
@@ -840,7 +849,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tma_store_wait_read<0>();
               }
             } else {
-              if (leader) { if (TEAMS == 2) tma_store_wait_read<0>(); else tma_store_wait_read<1>(); }
+              if (leader) stage_wait();
             }
             named_bar_sync(bar_id, EPI_THREADS);
             if (aux_on && leader) aux_issue_next();       // every thread of the team has copied its aux row out
@@ -882,7 +891,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               }
             } else {
               tma_store_2d(&tmC, sb0, col0, m0);
-              if (dual && TEAMS == 1) tma_store_2d(&tmC2, epi_buf + STAGE_CHUNK_BYTES, col0, m0);
               tma_store_commit();
             }
           }
@@ -1398,3 +1406,9 @@ extern "C" int b2_gemm_ar(const void* A, const void* B, int M, int N, int K, lon
   return gemm_rs_impl(A, B, M, N, K, lda, ldb, b_mn_major, dtype, cnt_ptrs, ctrls, stage_ptrs, out_local, ld_out, bias, residual, ld_res,
                       rank, world, armaps_dev, stream_);
 }
+
+namespace b2host {
+int set_spin_timeout_gemm(unsigned long long ns) {
+  return cudaMemcpyToSymbol(b2::g_b2_spin_timeout_ns, &ns, sizeof(ns)) == cudaSuccess ? 0 : -1;
+}
+}  // namespace b2host

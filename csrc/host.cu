@@ -96,6 +96,13 @@ extern "C" int b2_counter_add(void* dev_word, unsigned long long inc, void* stre
   if (e != cudaSuccess) { b2host::set_error("counter_add: %s", cudaGetErrorString(e)); return -1; }
   return 0;
 }
+// bound of every cross-GPU / cross-CTA flag wait of the fused kernels on the CURRENT device (default 4000 ms; a run under
+// compute-sanitizer, where a peer can be seconds late, wants more)
+extern "C" int b2_set_spin_timeout_ms(long long ms) {
+  const unsigned long long ns = static_cast<unsigned long long>(ms < 1 ? 1 : ms) * 1000000ull;
+  if (b2host::set_spin_timeout_gemm(ns) || b2host::set_spin_timeout_comm(ns)) { b2host::set_error("set_spin_timeout: cudaMemcpyToSymbol failed"); return -1; }
+  return 0;
+}
 extern "C" const char* b2_last_error(void) { return b2host::last_error(); }
 extern "C" int b2_num_sms(void) { return b2host::num_sms(); }
 extern "C" void b2_set_reserved_sms(int n) { b2host::set_reserved_sms(n); }

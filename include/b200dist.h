@@ -236,6 +236,7 @@ int b2_gemm_ar(const void* A, const void* B, int M, int N, int K, long long lda,
                void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, const void* armaps_dev, void* out_local,
                long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world, void* stream);
 void b2_fused_config(int pair_mode, int n_comm);
+int b2_set_spin_timeout_ms(long long ms);   /* bound of the cross-GPU waits on the current device (default 4000 ms) */
 
 /* ------------------------------------------------------------------------------------------
  * BatchNorm2d over NCHW tensors (csrc/batchnorm.cu), fp32 / bf16 / fp16 activations, fp32 statistics.  Training forward =

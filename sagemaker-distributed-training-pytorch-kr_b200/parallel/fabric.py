@@ -84,6 +84,10 @@ class Fabric:
             L.b2_rs_update.restype = c_i
             import os
             L.b2_fused_config(int(os.environ.get("B2_FUSED_PAIR", "-1")), int(os.environ.get("B2_FUSED_NCOMM", "0")))     # tuning / A-B runs
+            if os.environ.get("B2_SPIN_TIMEOUT_MS"):
+                L.b2_set_spin_timeout_ms.argtypes = [c_ll]
+                L.b2_set_spin_timeout_ms.restype = c_i
+                L.b2_set_spin_timeout_ms(int(os.environ["B2_SPIN_TIMEOUT_MS"]))
             self._ag, self._rs, self._coll = {}, {}, {}
             probe = SymmBuffer(self, 1024, torch.float32)
             probe.tensor.fill_(float(self.rank + 1))

@@ -33,16 +33,17 @@ def run(backend, model_name, steps, ga, clip, dtype):
                        persistence_threshold=200, comm_backend=backend)
     g = torch.Generator().manual_seed(3)
     data = torch.randint(0, 512, (1, world, 2, 64), generator=g).expand(steps * ga, world, 2, 64)   # one batch, repeated: loss must fall
-    losses = []
+    losses, norms = [], []
     for i in range(steps * ga):
         ids = data[i, rank].to(dev)
         loss = zm(ids, labels=ids)
         zm.engine.backward(loss)
-        zm.engine.step()
+        if zm.engine.step():
+            norms.append(zm.engine.last_grad_norm)
         losses.append(float(loss))
     sd = zm.engine.gather_full_state_dict()
     used_fabric = zm.engine.fabric is not None
-    return losses, {k: v.float().cpu() for k, v in sd.items()}, used_fabric
+    return losses, {k: v.float().cpu() for k, v in sd.items()}, used_fabric, norms
 
 
 # ---- fabric row collectives against NCCL
@@ -67,8 +68,12 @@ if F.usable:
 
 # ---- ZeRO-3 engine: native fabric vs NCCL collectives
 for (name, ga, clip) in [("llama-tiny", 1, 0.0), ("llama-tiny", 2, 1.0), ("opt-tiny", 1, 1.0)]:
-    l_nat, sd_nat, used = run("native", name, 4, ga, clip, torch.bfloat16)
-    l_ref, sd_ref, _ = run("nccl", name, 4, ga, clip, torch.bfloat16)
+    l_nat, sd_nat, used, n_nat = run("native", name, 4, ga, clip, torch.bfloat16)
+    l_ref, sd_ref, _, n_ref = run("nccl", name, 4, ga, clip, torch.bfloat16)
+    # the global gradient norm (what clipping acts on) must agree too, in particular with gradient accumulation: only the
+    # boundary micro-step contributes ||accumulated gradient||^2
+    nerr = max(abs(a - b) / max(b, 1e-6) for a, b in zip(n_nat, n_ref))
+    check(f"zero3 {name} ga={ga} clip={clip}: grad norm native vs nccl", len(n_nat) == 4 and nerr < 2e-2, f"max rel diff={nerr:.3e} first={n_nat[0]:.4f}")
     check(f"zero3 {name} ga={ga} clip={clip}: native path used the fabric", used)
     err = max(abs(a - b) for a, b in zip(l_nat, l_ref))
     check(f"zero3 {name} ga={ga} clip={clip}: losses native vs nccl", err < 3e-2, f"max |dloss|={err:.3e} first={l_nat[0]:.4f} last={l_nat[-1]:.4f}")
