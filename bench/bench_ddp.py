@@ -94,6 +94,11 @@ def main():
     for i in range(a.warmup):
         step(i)
     torch.cuda.synchronize(); dist.barrier()
+    sampler = None
+    if rank == 0:
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        from bench import ClockSampler
+        sampler = ClockSampler(torch.cuda.current_device())
     l0 = N.launches()
     s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     w0 = time.time()
@@ -107,13 +112,15 @@ def main():
     t = torch.tensor([max(s.elapsed_time(e), wall)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item() / a.steps
+    clocks = sampler.stop() if sampler is not None else None
     if rank == 0:
         out = {"metric": "DDP img/s", "value": world * a.batch_size / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": a.steps,
                "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "dtype": "fp32" if a.fp32 else "bf16",
                "data": "synthetic images (pinned host -> device every step), random-init weights",
                "config": {"model": a.model, "params": nparams, "image": a.size, "batch_per_gpu": a.batch_size, "global_batch": world * a.batch_size,
                           "parallelism": f"dp{world}", "comm_backend": a.comm_backend, "optimizer": "Adam", "cuda_graph": graphed is not None},
-               "last_loss": last, "gpu_launches": N.launches() - l0, "peak_mem_gib": torch.cuda.max_memory_allocated() / 2**30}
+               "last_loss": last, "clocks": clocks, "gpu_launches": N.launches() - l0,
+               "e2e": {"included": True, "h2d_bytes_per_step": a.batch_size * 3 * a.size * a.size * (4 if a.fp32 else 2) + a.batch_size * 8, "d2h_bytes_per_step": 4}, "peak_mem_gib": torch.cuda.max_memory_allocated() / 2**30}
         os.write(real_fd, (json.dumps(out) + "\n").encode())
     dist.barrier()
     dist.destroy_process_group()

@@ -46,9 +46,12 @@ struct AttnParams {
   float scale;          // softmax scale (1/sqrt(d))
   float* lse;           // [batch, heads, seqlen] (natural log units)
   const float* delta;   // bwd: [batch, heads, seqlen]
-  // attention dropout (DROP kernels): element (b, h, q, k) is kept iff drop_hash(...) >= drop_thresh; kept values are
+  // attention dropout (DROP kernels): ONE 32-bit hash decides a PAIR of adjacent keys (k even: low 16 bits, k odd: high 16
+  // bits), each half compared with the 16-bit threshold drop_thresh = round(p * 65536) - the forward, whose threads walk
+  // along k, hashes half as often (the hash cost 60 % of the forward's time per element); element (b, h, q, k) is kept iff
+  // half(lowbias32(seed + q*CQ + (k>>1)*CK + (b*H+h)*CB), k&1) >= drop_thresh; kept values are
   // scaled by inv_keep.  The row sum / LSE use the un-dropped probabilities (dropout acts on softmax output).
-  uint32_t drop_thresh;  // p * 2^32
+  uint32_t drop_thresh;  // round(p * 2^16)
   uint32_t drop_seed;
   const unsigned long long* drop_replay;   // device replay counter mixed into drop_seed (NULL = off), see host.cu
   float inv_keep;        // 1 / (1 - p)
@@ -275,7 +278,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       float rs0 = 0.f, rs1 = 0.f;
       uint8_t* rowp = sP + (j & 1) * L::P_BYTES + g * (BLK * 128) + r * 128;     // 64 columns = one 128 B slab row
       // dropout hash input of this thread's first column; + DROP_CK per column
-      [[maybe_unused]] uint32_t hx = drop_base + static_cast<uint32_t>(k0 + g * 64) * DROP_CK;
+      [[maybe_unused]] uint32_t hx = drop_base + static_cast<uint32_t>((k0 + g * 64) >> 1) * DROP_CK;     // + DROP_CK per key PAIR
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         uint32_t pk[4];
@@ -285,9 +288,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           float e1 = fast_exp2(fmaf(__uint_as_float(v[q * 8 + 2 * e + 1]), sl2, -msc));
           rs0 += e0; rs1 += e1;
           if constexpr (DROP) {
-            e0 = drop_mix(hx) >= p.drop_thresh ? e0 * p.inv_keep : 0.f;
-            e1 = drop_mix(hx + DROP_CK) >= p.drop_thresh ? e1 * p.inv_keep : 0.f;
-            hx += 2 * DROP_CK;
+            const uint32_t hh = drop_mix(hx);
+            e0 = (hh & 0xFFFFu) >= p.drop_thresh ? e0 * p.inv_keep : 0.f;
+            e1 = (hh >> 16) >= p.drop_thresh ? e1 * p.inv_keep : 0.f;
+            hx += DROP_CK;
           }
           pk[e] = pack_bf16x2(e0, e1);
         }
@@ -555,7 +559,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int kpos = k0 + r;
     const float sl2 = p.scale * LOG2E;
     [[maybe_unused]] const uint32_t drop_seed_r = p.drop_replay == nullptr ? p.drop_seed : p.drop_seed ^ static_cast<uint32_t>((*p.drop_replay * 0x9E3779B97F4A7C15ull) >> 32);
-    [[maybe_unused]] const uint32_t drop_base = drop_seed_r + static_cast<uint32_t>(kpos) * DROP_CK +
+    [[maybe_unused]] const uint32_t drop_base = drop_seed_r + static_cast<uint32_t>(kpos >> 1) * DROP_CK +
                                                 static_cast<uint32_t>(bat * p.heads + head) * DROP_CB;
     const size_t stat_base = (static_cast<size_t>(bat) * p.heads + head) * p.seqlen;
 
@@ -624,7 +628,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             float dp = __uint_as_float(dv[i + e]);
             if constexpr (DROP) {
               // same decision as the forward made for element (query qbase + qi, key kpos)
-              const float mk = drop_mix(drop_base + static_cast<uint32_t>(qbase + qi) * DROP_CQ) >= p.drop_thresh ? p.inv_keep : 0.f;
+              const uint32_t hh = drop_mix(drop_base + static_cast<uint32_t>(qbase + qi) * DROP_CQ);
+              const float mk = ((kpos & 1) ? (hh >> 16) : (hh & 0xFFFFu)) >= p.drop_thresh ? p.inv_keep : 0.f;
               pr[e] = pe * mk;                       // dropped probabilities feed dV = P~^T dO
               dp *= mk;                              // dP = dP~ * mask / keep
             } else {
@@ -708,11 +713,13 @@ int check(const char* what) {
 int g_attn_dbg = 0;
 void set_dropout(AttnParams& p, float p_drop, unsigned long long seed) {
   p.dbg_skip = g_attn_dbg;
-  const double t = static_cast<double>(p_drop) * 4294967296.0;
-  p.drop_thresh = t >= 4294967295.0 ? 0xFFFFFFFFu : static_cast<uint32_t>(t);
+  long long t = static_cast<long long>(static_cast<double>(p_drop) * 65536.0 + 0.5);
+  if (t > 65535) t = 65535;
+  if (t < 0) t = 0;
+  p.drop_thresh = static_cast<uint32_t>(t);
   p.drop_seed = static_cast<uint32_t>(seed ^ (seed >> 32));
+  p.inv_keep = 65536.f / static_cast<float>(65536 - t);        // 1 / (realised keep probability): unbiased for every p
   p.drop_replay = p_drop > 0.f ? b2host::dropout_replay_ptr() : nullptr;
-  p.inv_keep = p_drop > 0.f ? 1.f / (1.f - p_drop) : 1.f;
 }
 }  // namespace
 

@@ -659,19 +659,21 @@ def embedding_bwd_(dy2, tok, pos, dwte32, dwpe32, vocab_start: int = 0):
 # attention.  q/k/v/o are 4-D views [seq, batch, heads, D] with D contiguous (any strides otherwise)
 # =============================================================================================
 def attn_dropout_mask(B: int, Hh: int, S: int, p_drop: float, seed: int, device="cpu") -> torch.Tensor:
-    """[B, H, S(query), S(key)] multiplier (0 or 1/(1-p)) - the decision rule of csrc/attention.cu restated:
-    keep iff lowbias32(seed32 + q*CQ + k*CK + (b*H+h)*CB) >= p * 2^32 (all arithmetic mod 2^32)."""
+    """[B, H, S(query), S(key)] multiplier (0 or 1/keep) - the decision rule of csrc/attention.cu restated: one hash per PAIR of
+    adjacent keys, h = lowbias32(seed32 + q*CQ + (k>>1)*CK + (b*H+h)*CB) (mod 2^32); key k is kept iff its 16-bit half of h (low
+    half for even k, high half for odd k) >= round(p * 65536); kept values are scaled by 65536 / (65536 - threshold)."""
     M = 0xFFFFFFFF
     seed32 = (seed ^ (seed >> 32)) & M
     q = torch.arange(S, dtype=torch.int64, device=device)[:, None]
     k = torch.arange(S, dtype=torch.int64, device=device)[None, :]
     bh = torch.arange(B * Hh, dtype=torch.int64, device=device).view(B, Hh, 1, 1)
-    x = (seed32 + q * 0x9E3779B1 + k * 0x85EBCA77 + bh * 0xC2B2AE3D) & M
+    x = (seed32 + q * 0x9E3779B1 + (k >> 1) * 0x85EBCA77 + bh * 0xC2B2AE3D) & M
     x = x ^ (x >> 16); x = (x * 0x7FEB352D) & M
     x = x ^ (x >> 15); x = (x * 0x846CA68B) & M
     x = x ^ (x >> 16)
-    t = min(int(float(p_drop) * 4294967296.0), M)
-    return (x >= t).float() / (1.0 - p_drop)
+    half = torch.where((k & 1) == 1, x >> 16, x & 0xFFFF)
+    t = max(0, min(int(float(p_drop) * 65536.0 + 0.5), 65535))
+    return (half >= t).float() * (65536.0 / (65536 - t))
 
 
 def _attn_ref(q, k, v, scale, causal, p_drop: float = 0.0, seed: int = 0):
