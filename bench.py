@@ -96,6 +96,23 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def library_baseline(n_gpus: int, value: float):
+    """archived same-box comparison arms (profiles/library_baselines.json: this stack over NCCL collectives, and stock PyTorch);
+    never the reference - see BASELINE.md section 3"""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "library_baselines.json")))
+        row = d["tokens_per_s"].get(str(n_gpus))
+        if not row:
+            return None
+        out = {"source": "archived runs on this pool (profiles/library_baselines.json), same config and timing rules; not the reference"}
+        for k in ("nccl_backend", "stock_pytorch"):
+            if row.get(k):
+                out[k] = {"tokens_per_s": row[k], "ours_over_it": value / row[k]}
+        return out
+    except Exception:
+        return None
+
+
 _REAL_STDOUT_FD = None
 
 
@@ -251,7 +268,7 @@ def main():
                "clocks": clocks,
                "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": nmb * a.micro_batch_size * (a.seq_length + 1) * 8 if is_src else 0,
                        "d2h_bytes_per_step": 4, "ms_per_step": max(ms_e2e, wall_e2e) / a.steps, "last_loss": last_loss},
-               "gpu_launches": launches, "host_issue_ms_per_step": host_issue}
+               "gpu_launches": launches, "host_issue_ms_per_step": host_issue, "library_baseline": library_baseline(a.gpus, value)}
         emit(json.dumps(out))
     dist.barrier()
     dist.destroy_process_group()

@@ -36,8 +36,10 @@ def build_parser(ddp: bool = True) -> argparse.ArgumentParser:
         p.add_argument("--backend", type=str, default="nccl", help="backend for distributed operations (nccl | gloo | smddp | native)")
     # additions (not in the reference)
     p.add_argument("--model-dir", type=str, default=None, help="where mnist_cnn.pt is written (default: cwd / SM_MODEL_DIR)")
-    p.add_argument("--native-ops", action="store_true", default=False,
-                   help="run conv+bias+ReLU / max-pool / log-softmax on the fp32 kernels of csrc/conv.cu instead of cuDNN / ATen")
+    p.add_argument("--native-ops", dest="native_ops", action="store_true", default=None,
+                   help="run conv+bias+ReLU / max-pool / log-softmax on the fp32 kernels of csrc/conv.cu instead of cuDNN / ATen "
+                        "(default on a CUDA device: the kernels match cuDNN to rounding on a B200, tests/test_zy_conv_gpu.py)")
+    p.add_argument("--no-native-ops", dest="native_ops", action="store_false", help="keep the convolutions / pooling / log-softmax on cuDNN / ATen")
     p.add_argument("--synthetic", action="store_true", default=False, help="use synthetic MNIST-shaped data")
     p.add_argument("--synthetic-size", type=int, default=None)
     p.add_argument("--max-steps", type=int, default=None, help="stop each epoch after this many steps (smoke tests)")
@@ -124,7 +126,8 @@ def main(argv=None, ddp: bool = True):
         test_ds = MNISTTensors(args.data_path, train=False, synthetic=True if args.synthetic else None,
                                synthetic_size=None if args.synthetic_size is None else max(args.synthetic_size // 6, 1))
         test_loader = TensorBatchLoader(test_ds, args.test_batch_size)
-    model = Net(native_ops=args.native_ops).to(device)
+    native_ops = (device.type == "cuda") if args.native_ops is None else bool(args.native_ops)
+    model = Net(native_ops=native_ops).to(device)
     if ddp and args.world_size > 1:
         model = DDP(model, comm_backend="auto" if args.backend in ("smddp", "native") else ("nccl" if device.type == "cuda" else "gloo"))
     optimizer = Adadelta(model.parameters(), lr=args.lr)
