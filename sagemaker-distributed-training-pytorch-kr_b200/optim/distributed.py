@@ -10,9 +10,11 @@ into), but every DP rank keeps the fp32 master copy and the Adam moments only fo
     AdamW on the slice                fp32 master slice -> bf16 slice of the model arena
     all-gather over DP                every rank has the updated bf16 parameters again
 
-Memory per rank: 2 + 4 (main_grad) + 12 / dp bytes per parameter instead of 18.  The collectives here are
-torch.distributed calls (reduce_scatter_tensor / all_gather_into_tensor on NCCL, all-reduce + slice on gloo); wiring
-the slice update to the fused `b2_rs_update` kernel that ZeRO-3 already uses is the planned next step.
+Memory per rank: 2 + 4 (main_grad) + 12 / dp bytes per parameter instead of 18.  With `--comm-backend native` on GPUs both
+collectives are the fabric kernels of csrc/comm.cu on symmetric arenas - `b2_reduce_scatter` (multimem.ld_reduce of this
+rank's slice, scaled by 1/dp, straight into the fp32 gradient shard) and `b2_allgather` (multimem.st of the updated bf16
+slice into every rank's model arena, in place); otherwise torch.distributed calls (reduce_scatter_tensor /
+all_gather_into_tensor on NCCL, all-reduce + slice on gloo).
 """
 from __future__ import annotations
 
@@ -31,7 +33,7 @@ class DistributedOptimizer(MixedPrecisionOptimizer):
         dp_group = kw.get("dp_group")
         dp = dist.get_world_size(dp_group) if (dp_group is not None and dist.is_initialized()) else 1
         kw["arena_multiple"] = dp
-        kw["comm_backend"] = "nccl" if kw.get("comm_backend") == "native" else kw.get("comm_backend", "nccl")   # plain collectives here
+        kw["symmetric_model_arena"] = True
         super().__init__(model_chunks, **kw)
         self.dp_rank = dist.get_rank(dp_group) if dp > 1 else 0
         self.shard = self.total // dp
@@ -53,7 +55,11 @@ class DistributedOptimizer(MixedPrecisionOptimizer):
         finally:
             self.dp_size = dp
         if dp > 1:
-            if self.main_grad.is_cuda:
+            if self.fabric is not None and self._grad_symm is not None:
+                g = self._grad_symm
+                N._call("b2_reduce_scatter", g.ptrs, g.ctrls, g.mc_ptr or None, self.total, N.DT_FP32, 1.0 / dp, self.dp_rank, dp, 0,
+                        N._p(self.grad_shard), N._st())
+            elif self.main_grad.is_cuda:
                 dist.reduce_scatter_tensor(self.grad_shard, self.main_grad, group=grp)
                 self.grad_shard.div_(dp)
             else:                               # gloo has no reduce-scatter: all-reduce, keep the slice
@@ -112,7 +118,10 @@ class DistributedOptimizer(MixedPrecisionOptimizer):
                 self.model_arena[a:b].copy_(self.main_param[la:lb])
         if self.dp_size > 1:                    # every rank gets the other ranks' updated slices
             mine = self.model_arena[self.lo:self.hi]
-            if self.model_arena.is_cuda:
+            if self._model_symm is not None:
+                m = self._model_symm
+                N._call("b2_allgather", m.ptrs, m.ctrls, m.mc_ptr or None, self.total, N._dt(self.model_arena), self.dp_rank, self.dp_size, 0, N._st())
+            elif self.model_arena.is_cuda:
                 dist.all_gather_into_tensor(self.model_arena, mine, group=self.dp_group)
             else:
                 parts = [torch.empty_like(mine) for _ in range(self.dp_size)]

@@ -87,7 +87,7 @@ class MixedPrecisionOptimizer:
                  clip_grad: float = 1.0, optimizer: str = "adam", sgd_momentum: float = 0.9, grad_scaler: Optional[ConstantGradScaler] = None,
                  dp_group=None, tp_group=None, mp_group=None, embedding_group=None, comm_backend: str = "nccl",
                  no_wd_fn: Callable[[str, torch.Tensor], bool] = default_no_weight_decay, log_num_zeros: bool = False,
-                 overlap_grad_reduce: bool = False, arena_multiple: int = 1):
+                 overlap_grad_reduce: bool = False, arena_multiple: int = 1, symmetric_model_arena: bool = False):
         self.chunks = list(model_chunks)
         self.lr, self.wd, self.betas, self.eps, self.clip_grad = lr, weight_decay, betas, eps, clip_grad
         self.kind, self.sgd_momentum = optimizer, sgd_momentum
@@ -138,7 +138,13 @@ class MixedPrecisionOptimizer:
             fb = fabric.get_fabric(dp_group)
             if fb.usable:
                 self.fabric = fb
-        self.model_arena = torch.zeros(self.total, dtype=self.model_dtype, device=dev)
+        self._model_symm = None
+        if symmetric_model_arena and self.fabric is not None:     # the distributed optimizer all-gathers updated slices in place
+            self._model_symm = self.fabric.alloc(self.total, self.model_dtype)
+            self.model_arena = self._model_symm.tensor
+            self.model_arena.zero_()
+        else:
+            self.model_arena = torch.zeros(self.total, dtype=self.model_dtype, device=dev)
         for p, o in zip(self.params, self.offsets):
             v = self.model_arena[o:o + p.numel()].view_as(p)
             v.copy_(p.data)

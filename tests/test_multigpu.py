@@ -117,3 +117,21 @@ def test_gpt_tp2_pp2_interleaved_fused_tp_kernels_match_nccl_tp():
         os.environ.pop("B2_HANG_DUMP_S", None)
     assert len(curves["0"]) == 3 == len(curves["1"])
     assert max(abs(a - b) for a, b in zip(curves["0"], curves["1"])) < 5e-2, curves
+
+
+@pytest.mark.skipif(_ngpu() < 2, reason="needs 2 GPUs")
+def test_distributed_optimizer_fabric_collectives_match_nccl():
+    """--use-distributed-optimizer on DP=2: gradient reduce-scatter and parameter all-gather on the fabric kernels (symmetric
+    main_grad / model arenas) against reduce_scatter_tensor / all_gather_into_tensor"""
+    import re
+    base = ["--num-layers", "2", "--hidden-size", "256", "--num-attention-heads", "4", "--seq-length", "256", "--max-position-embeddings", "256",
+            "--micro-batch-size", "4", "--global-batch-size", "16", "--lr", "1e-3", "--train-iters", "4", "--lr-decay-iters", "4", "--lr-warmup-iters", "1",
+            "--log-interval", "1", "--eval-interval", "100", "--eval-iters", "0", "--tokenizer-type", "NullTokenizer", "--vocab-size", "1023", "--mock-data",
+            "--bf16", "--seed", "11", "--hidden-dropout", "0", "--attention-dropout", "0", "--use-distributed-optimizer"]
+    curves = {}
+    for backend in ("native", "nccl"):
+        rc, out = _torchrun("entrypoints/pretrain_gpt.py", 2, 300, *base, "--comm-backend", backend)
+        assert rc == 0, out[-4000:]
+        curves[backend] = [float(x) for x in re.findall(r"lm loss: ([0-9.E+-]+)", out)]
+    assert len(curves["native"]) == 4 == len(curves["nccl"])
+    assert max(abs(a - b) for a, b in zip(curves["native"], curves["nccl"])) < 5e-2, curves
