@@ -1,2 +1,3 @@
-timeout 300 python bench/kernel_check.py --only attn > gpurun_out/kc_attn.log 2>&1; echo rc=$?; grep -c "^ok" gpurun_out/kc_attn.log; grep "^FAIL\|^time" gpurun_out/kc_attn.log | head
-timeout 600 python -m pytest tests/test_multigpu.py -q -x -k "distributed_optimizer or zero3" 2>&1 | tail -5
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port"
+timeout 200 $TR 29612 bench/comm_check.py xent > gpurun_out/cc_xent.log 2>&1; echo rc=$? >> gpurun_out/cc_xent.log
+grep "graph-timed\|FAIL\|ALL\|rc=" gpurun_out/cc_xent.log

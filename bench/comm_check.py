@@ -222,6 +222,27 @@ if which in ("all", "ar_gemm"):
         ms_n = timeit(lambda: dist.all_reduce(N.gemm(a, W)))
         p0(f"graph-timed gemm_ar {tag:9s} M{M} K{K} N{Nn}: fused {gf*1e3:7.1f} us (incl. the private copy of the result) | plain gemm {gg*1e3:7.1f} us | gemm + nccl all_reduce {ms_n*1e3:7.1f} us (stream-timed)")
 
+if which in ("all", "xent"):
+    for (rows, V) in [(512, 1024), (3000, 4096), (24576, 16384)]:
+        torch.manual_seed(400 + rank)
+        logits = (torch.randn(rows, V, device=dev) * 3).to(torch.bfloat16)
+        torch.manual_seed(5)
+        labels = torch.randint(0, V * world, (rows,), device=dev)
+        labels[::7] = -100
+        gm, gs, loss = F.xent_vocab_parallel(logits, labels, rank * V, -100)
+        torch.cuda.synchronize()
+        full = [torch.empty_like(logits) for _ in range(world)]
+        dist.all_gather(full, logits)
+        lf = torch.cat(full, dim=1).float()
+        ref = torch.nn.functional.cross_entropy(lf, labels, ignore_index=-100, reduction="none")
+        report(f"xent_vocab_parallel loss rows{rows} V{V}x{world}", loss, ref, 2e-3)
+        report(f"xent_vocab_parallel max rows{rows}", gm, lf.max(-1).values, 1e-6)
+        gm2, gs2, loss2 = F.xent_vocab_parallel(logits, labels, rank * V, -100)      # second call: other parity of the stats buffer
+        torch.cuda.synchronize()
+        report(f"xent_vocab_parallel (2nd call) rows{rows}", loss2, ref, 2e-3)
+    gt = graph_time(lambda: F.xent_vocab_parallel(logits, labels, rank * V, -100))
+    p0(f"graph-timed xent_vocab_parallel rows 24576 V {V} per rank: {gt*1e3:.1f} us ({rows * V * 2 / (gt * 1e-3) / 1e9:.0f} GB/s of logits)")
+
 p0("FAILED:" if FAILS else "ALL OK", FAILS)
 dist.barrier()
 dist.destroy_process_group()

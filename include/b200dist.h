@@ -124,6 +124,12 @@ int b2_xent_stats(const void* logits, const long long* labels, float* rmax, floa
                   long long rows, int V, long long ld, long long vocab_start, int dtype, void* stream);
 int b2_xent_finish(const float* rmax, const float* rsum, const float* rtgt, const long long* labels, float* loss,
                    long long rows, long long ignore_index, void* stream);
+/* Vocab-parallel forward in ONE kernel: row statistics of this rank's shard -> exchange through the symmetric stats buffers
+ * (stats_ptrs[r]: 2 * 3 * rows floats + control block on every rank) -> global max / sum-exp / loss on every rank.
+ * replaces the three NCCL all-reduces of Megatron's _VocabParallelCrossEntropy. */
+int b2_xent_vocab_parallel(const void* logits, const long long* labels, void* const* stats_ptrs, void* const* ctrls, int rank,
+                           int world, float* gmax, float* gsum, float* loss, long long rows, int V, long long ld,
+                           long long vocab_start, long long ignore_index, int dtype, void* stream);
 int b2_xent_bwd(const void* logits, void* dlogits, const long long* labels, const float* gmax, const float* gsum,
                 const float* row_scale, float scalar_scale, long long rows, int V, long long ld,
                 long long vocab_start, long long ignore_index, int dtype, void* stream);

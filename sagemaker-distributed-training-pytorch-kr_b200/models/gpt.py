@@ -381,9 +381,12 @@ class _LMHeadLossFn(torch.autograd.Function):
         logits, h_full = comm.column_fwd(h2, wte)
         T, V = logits.shape
         lab = labels.t().contiguous().view(-1)
-        m, s, t = N.xent_stats(logits, lab, model.vocab_start)
-        m, s, t = comm.combine_xent_stats(m, s, t)
-        loss = N.xent_finish(m, s, t, lab, model.ignore_index)
+        if hasattr(comm, "xent_forward"):
+            m, s, loss = comm.xent_forward(logits, lab, model.vocab_start, model.ignore_index)
+        else:
+            m, s, t = N.xent_stats(logits, lab, model.vocab_start)
+            m, s, t = comm.combine_xent_stats(m, s, t)
+            loss = N.xent_finish(m, s, t, lab, model.ignore_index)
         ctx.save_for_backward(logits, h_full, lab, m, s, wte)
         ctx.model, ctx.params, ctx.dims = model, (wte,), (T // B, B)
         return loss.view(T // B, B).t().contiguous()

@@ -73,6 +73,8 @@ class Fabric:
             L.b2_make_ar_maps.restype = c_i
             L.b2_gemm_ar.argtypes = [c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_p, c_p, c_p, c_p, c_p, c_ll, c_p, c_p, c_ll, c_i, c_i, c_p]
             L.b2_gemm_ar.restype = c_i
+            L.b2_xent_vocab_parallel.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_ll, c_i, c_p]
+            L.b2_xent_vocab_parallel.restype = c_i
             L.b2_fused_config.argtypes = [c_i, c_i]
             L.b2_fused_config.restype = None
             L.b2_reduce_scatter.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p, c_p]
@@ -226,6 +228,20 @@ def _gemm_ar(self, a2: torch.Tensor, W: torch.Tensor, b_mn: bool = False, bias=N
 
 
 Fabric.gemm_ar = _gemm_ar
+
+
+def _xent_vocab_parallel(self, logits2: torch.Tensor, labels: torch.Tensor, vocab_start: int, ignore_index: int = -100):
+    """(global max, global sum-exp, loss) per row of vocab-sharded logits in one kernel (stats -> exchange -> finish)."""
+    rows, V = logits2.shape
+    buf = self._coll_buf(2 * 3 * rows, torch.float32, "xent")
+    gmax = torch.empty(rows, dtype=torch.float32, device=logits2.device)
+    gsum, loss = torch.empty_like(gmax), torch.empty_like(gmax)
+    N._call("b2_xent_vocab_parallel", N._p(logits2), N._p(labels), buf.ptrs, buf.ctrls, self.rank, self.world, N._p(gmax), N._p(gsum),
+            N._p(loss), rows, V, logits2.stride(0), int(vocab_start), int(ignore_index), N._dt(logits2), N._st())
+    return gmax, gsum, loss
+
+
+Fabric.xent_vocab_parallel = _xent_vocab_parallel
 
 
 def get_fabric(group=None) -> Fabric:

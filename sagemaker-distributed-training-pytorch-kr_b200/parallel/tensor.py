@@ -147,6 +147,15 @@ class TPComm:
             return self.fabric.reduce_scatter_rows(x)
         return reduce_scatter_first_dim(x, self.group) if self.sp else all_reduce(x, self.group)
 
+    def xent_forward(self, logits2, labels, vocab_start: int, ignore_index: int = -100):
+        """vocab-parallel cross-entropy forward -> (global row max, global sum-exp, loss).  Native backend on GPUs: ONE kernel
+        (shard statistics, exchange over NVLink, loss); otherwise statistics kernel + collective + finish."""
+        if self.size > 1 and self.fabric is not None and logits2.is_cuda:
+            return self.fabric.xent_vocab_parallel(logits2, labels, vocab_start, ignore_index)
+        m, s, t = N.xent_stats(logits2, labels, vocab_start)
+        m, s, t = self.combine_xent_stats(m, s, t)
+        return m, s, N.xent_finish(m, s, t, labels, ignore_index)
+
     def combine_xent_stats(self, m, s, t):
         """per-rank (row max, sum-exp relative to it, target logit) of a vocab shard -> global (max, sum-exp, target).
         One exchange of 3 scalars per row instead of Megatron's three all-reduces over [s, b]."""
