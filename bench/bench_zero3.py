@@ -34,6 +34,7 @@ def main():
     ap.add_argument("--max-live-parameters", type=float, default=1e9)
     ap.add_argument("--max-reuse-distance", type=float, default=1e9)
     ap.add_argument("--no-clocks", action="store_true")
+    ap.add_argument("--no-fuse-gather-gemm", action="store_true", help="gather the LM head with the stand-alone kernel instead of inside its GEMM")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (0 = the model's own)")
     ap.add_argument("--comm-backend", default="native")
     ap.add_argument("--clip", type=float, default=1.0)
@@ -59,6 +60,8 @@ def main():
                        prefetch_bucket_size=int(0.9 * model.config.hidden_size ** 2),
                        persistence_threshold=10 * model.config.hidden_size, comm_backend=a.comm_backend if world > 1 else "nccl",
                        offload_optimizer=a.offload_optimizer, offload_param=a.offload_param, gradient_checkpointing=a.gradient_checkpointing)
+    if a.no_fuse_gather_gemm:
+        zm.engine._agw_units = set()
     torch.cuda.synchronize()
     setup_s = time.time() - t0
     V = model.config.vocab_size
@@ -108,7 +111,7 @@ def main():
                "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
                "dtype": "bf16", "data": "synthetic instruction batches (pinned host -> device every step), random-init weights",
                "config": {"model": a.model, "layers": model.config.num_hidden_layers, "params": nparams, "seq_len": a.seq, "micro_batch_per_gpu": a.micro_batch, "grad_accum": a.grad_accum,
-                          "global_batch": world * a.micro_batch * a.grad_accum, "gather_workspaces": zm.engine.n_ws, "prefetch_depth": zm.engine.prefetch_depth, "parallelism": f"zero3 dp{world}", "comm_backend": a.comm_backend,
+                          "global_batch": world * a.micro_batch * a.grad_accum, "gather_workspaces": zm.engine.n_ws, "fused_gather_gemm_units": sorted(zm.engine._agw_units), "prefetch_depth": zm.engine.prefetch_depth, "parallelism": f"zero3 dp{world}", "comm_backend": a.comm_backend,
                           "fabric": zm.engine.fabric is not None, "optimizer": f"AdamW fp32 partitioned, clip {a.clip}",
                           "offload_optimizer": a.offload_optimizer, "offload_param": a.offload_param, "gradient_checkpointing": a.gradient_checkpointing},
                "model_tflops_per_gpu": flops / (ms / 1e3) / 1e12, "peak_mem_gib": mem, "setup_s": setup_s, "last_loss": last_loss,

@@ -222,6 +222,30 @@ if which in ("all", "ar_gemm"):
         ms_n = timeit(lambda: dist.all_reduce(N.gemm(a, W)))
         p0(f"graph-timed gemm_ar {tag:9s} M{M} K{K} N{Nn}: fused {gf*1e3:7.1f} us (incl. the private copy of the result) | plain gemm {gg*1e3:7.1f} us | gemm + nccl all_reduce {ms_n*1e3:7.1f} us (stream-timed)")
 
+if which in ("all", "agw"):
+    # all-gather of a row-sharded weight fused into its GEMM (ZeRO-3 head): shard rows need not be a multiple of 128
+    for (M, K, srows) in [(126, 64, 256), (300, 256, 104), (2044, 1024, 4000), (2044, 4096, 4000)]:
+        Nn = srows * world
+        wbuf = F.alloc(Nn * K, torch.bfloat16)
+        torch.manual_seed(500 + rank)
+        mine = (torch.randn(srows, K, device=dev) * 0.05).to(torch.bfloat16)
+        shards = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(shards, mine)
+        wfull = torch.cat(shards)
+        torch.manual_seed(77)
+        x = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+        for call in range(2):
+            wbuf.tensor.zero_()
+            wbuf.tensor.view(Nn, K)[rank * srows:(rank + 1) * srows].copy_(mine)
+            torch.cuda.synchronize(); dist.barrier()
+            y = F.agw_gemm(x, wbuf, 0, srows, K)
+            torch.cuda.synchronize()
+            report(f"agw_gemm out M{M} K{K} shard_rows{srows} (call {call + 1})", y, x.float() @ wfull.float().t(), 2e-2)
+            report(f"agw_gemm gathered weight shard_rows{srows} (call {call + 1})", wbuf.tensor.view(Nn, K), wfull, 0.0)
+    gf = graph_time(lambda: F.agw_gemm(x, wbuf, 0, srows, K))
+    gg = graph_time(lambda: N.gemm(x, wfull))
+    p0(f"graph-timed agw_gemm M{M} K{K} N{Nn}: fused {gf*1e3:.1f} us | plain gemm on the gathered weight {gg*1e3:.1f} us | remote shards {srows * (world - 1) * K * 2 / 1e6:.1f} MB")
+
 if which in ("all", "xent"):
     for (rows, V) in [(512, 1024), (3000, 4096), (24576, 16384)]:
         torch.manual_seed(400 + rank)

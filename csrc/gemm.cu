@@ -55,6 +55,9 @@ struct GemmParams {
   uint8_t* f_xg;                   // AG: local gathered operand [M, K]
   uint32_t* f_flags;               // AG: local per-row-block arrival counters (pieces landed, cumulative over calls)
   int f_npb;                       // AG: 32 KB pieces per 128-row block
+  int f_last_rows, f_npb_last;     // AG: rows / pieces of a shard's LAST block (= 128 / f_npb unless the shard is not a multiple of 128 rows)
+  int f_nmajor, n_rot;             // AGB: tile order is N-major and starts at column tile n_rot (this rank's own rows of B)
+  int f_self_clean;                // AGB: the arrival counters are zeroed at the end of the launch (they count from 0 every call)
   uint32_t* f_cnt[8];              // RS: per-row-block arrival counters on every rank (symmetric)
   uint8_t* f_stage_peer[8];        // RS: every rank's staging buffer (symmetric): [2 parity][world sources][slot]
   const void* f_stage;             // RS: this rank's staging [2][world][shard_rows, N]
@@ -75,7 +78,7 @@ B2_DEVICE void dbg_stamp(const GemmParams& p, int k) {
   }
 }
 
-constexpr int FUSE_NONE = 0, FUSE_AG = 1, FUSE_RS = 2;
+constexpr int FUSE_NONE = 0, FUSE_AG = 1, FUSE_RS = 2, FUSE_AGB = 3;     // AGB: the gathered operand is B (a row-sharded weight)
 constexpr int FCTRL_A = 16, FCTRL_B = 32;   // arrival slots inside a control block (same layout as comm.cu)
 
 // ---- 1-D bulk copies (TMA without a tensor map) used by the all-gather CTAs
@@ -114,19 +117,23 @@ B2_DEVICE void ag_comm_cta(const GemmParams& p, uint8_t* smem, int c, uint32_t e
     dbg_stamp(p, 0);
     const long long blk_bytes = 128LL * p.f_row_bytes;
     const int npb = p.f_npb;
-    const long long total = static_cast<long long>(p.f_world - 1) * p.f_bpr * npb;     // pieces of all remote shards
+    const long long pps = static_cast<long long>(p.f_bpr - 1) * npb + p.f_npb_last;     // pieces per shard
+    const long long total = static_cast<long long>(p.f_world - 1) * pps;               // pieces of all remote shards
     const long long mine = total > c ? (total - c + p.f_ncomm - 1) / p.f_ncomm : 0;    // pieces c, c + ncomm, ...
     long long issued = 0, stored = 0, published = 0;
     int ready_upto = 0;                              // sources (rank+1 ... rank+ready_upto) known to be complete
     uint32_t* pub[PUB];
     auto locate = [&](long long k, int& src, long long& off, uint32_t& sz, uint32_t*& flag) {
       const long long g = c + k * p.f_ncomm;
-      const long long bi = g / npb;
-      const int pc = static_cast<int>(g - bi * npb);
-      const int si = static_cast<int>(bi / p.f_bpr), blk = static_cast<int>(bi - static_cast<long long>(si) * p.f_bpr);
+      const int si = static_cast<int>(g / pps);
+      const long long rem = g - si * pps;
+      int blk = static_cast<int>(rem / npb);
+      if (blk > p.f_bpr - 1) blk = p.f_bpr - 1;
+      const int pc = static_cast<int>(rem - static_cast<long long>(blk) * npb);
       src = (p.f_rank + 1 + si) % p.f_world;
       off = blk * blk_bytes + static_cast<long long>(pc) * PIECE;
-      const long long left = blk_bytes - static_cast<long long>(pc) * PIECE;
+      const long long this_bytes = (blk == p.f_bpr - 1) ? static_cast<long long>(p.f_last_rows) * p.f_row_bytes : blk_bytes;
+      const long long left = this_bytes - static_cast<long long>(pc) * PIECE;
       sz = left < static_cast<long long>(PIECE) ? static_cast<uint32_t>(left) : PIECE;
       flag = p.f_flags + src * p.f_bpr + blk;
     };
@@ -210,6 +217,9 @@ B2_DEVICE void fused_finish(const GemmParams& p, uint32_t epoch, bool wait_peers
     __threadfence();
     dbg_stamp(p, 5);
   }
+  if (last && p.f_self_clean) {      // every CTA of the grid has passed its last wait: the counters restart from zero next call
+    for (int i = threadIdx.x; i < p.f_world * p.f_bpr; i += blockDim.x) p.f_flags[i] = 0u;
+  }
 }
 
 B2_DEVICE float tanh_approx(float x) {
@@ -260,6 +270,11 @@ B2_DEVICE void decode_tile(const GemmParams& p, int t, int& tm, int& tn, int& ks
   int in_g = r - g * group_sz;
   tm = first_m + in_g % gm;
   tn = in_g / gm;
+  if (p.f_nmajor) {                   // all-gathered B operand: N-major (a column tile's row tiles are consecutive), own columns first
+    tn = r / p.tiles_m + p.n_rot;
+    if (tn >= p.tiles_n) tn -= p.tiles_n;
+    tm = r - (r / p.tiles_m) * p.tiles_m;
+  }
   if (p.m_rot) { tm += p.m_rot; if (tm >= p.tiles_m) tm -= p.tiles_m; }
 }
 
@@ -326,7 +341,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   int nctas = CTA2 ? gridDim.x / 2 : gridDim.x, cta0 = CTA2 ? blockIdx.x / 2 : blockIdx.x;   // tile-loop stride / start
   if constexpr (FUSE != FUSE_NONE) {
     f_epoch = p.f_ctrl[p.f_rank][1] + 1;
-    if constexpr (FUSE == FUSE_AG) {
+    if constexpr (FUSE == FUSE_AG || FUSE == FUSE_AGB) {
       // pair kernels: f_ncomm is even, so a cluster is either two all-gather CTAs or one GEMM pair
       nctas = (static_cast<int>(gridDim.x) - p.f_ncomm) / (CTA2 ? 2 : 1);
       cta0 = (static_cast<int>(blockIdx.x) - p.f_ncomm) / (CTA2 ? 2 : 1);
@@ -385,6 +400,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             wait_ge_gpu(p.f_flags + rb, f_epoch * static_cast<uint32_t>(p.f_npb), 0x103);
             fence_proxy_async_all();
           }
+        }
+        if constexpr (FUSE == FUSE_AGB) {
+          // rows [nb0, nb1) of the gathered B operand that this CTA stages: every 128-row block of every shard they touch
+          // must have landed (own shard: in place since before the launch)
+          const int nb0 = n0, nb1 = min(p.N, n0 + BN_LOAD);
+          for (int rr = nb0; rr < nb1;) {
+            const int sh = rr / p.f_shard_rows, lr = rr - sh * p.f_shard_rows, blk = lr >> 7;
+            if (sh != p.f_rank)
+              wait_ge_gpu(p.f_flags + sh * p.f_bpr + blk, static_cast<uint32_t>(blk == p.f_bpr - 1 ? p.f_npb_last : p.f_npb), 0x105);
+            rr = sh * p.f_shard_rows + min(p.f_shard_rows, (blk + 1) << 7);
+          }
+          fence_proxy_async_all();
         }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -525,7 +552,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       while (retired < issued) retire();
       dbg_stamp(p, 2);
     }
-  } else if (FUSE == FUSE_AG && (warp == 2 || warp == 3)) {
+  } else if (FUSE == FUSE_AG && p.f_xg != nullptr && (warp == 2 || warp == 3)) {
     // ===================== own shard -> gathered operand (background copy, see ag_comm_cta) =====================
     const long long nthr = static_cast<long long>(gridDim.x - p.f_ncomm) * 64;
     const long long tid = static_cast<long long>(blockIdx.x - p.f_ncomm) * 64 + (warp - 2) * 32 + lane;
@@ -906,7 +933,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if constexpr (CTA2) cluster_sync(); else __syncthreads();     // pair: neither CTA may free TMEM / exit while the other still uses it
   if constexpr (FUSE != FUSE_NONE) { if (threadIdx.x == 0) dbg_stamp(p, 4); }
   if (warp == 2) { if constexpr (CTA2) tmem_dealloc_2sm<TMEM_COLS>(tmem_base); else tmem_dealloc<TMEM_COLS>(tmem_base); }
-  if constexpr (FUSE == FUSE_AG) fused_finish(p, f_epoch, true);
+  if constexpr (FUSE == FUSE_AG || FUSE == FUSE_AGB) fused_finish(p, f_epoch, true);
   if constexpr (FUSE == FUSE_RS) {
     // (every epilogue leader has waited for the completion of its TMA stores before the CTA-wide barrier above)
     const bool ar = p.f_armaps != nullptr;
@@ -1262,6 +1289,7 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
   p.m_rot = pair ? rank * (p.f_bpr / 2) : rank * p.f_bpr;
   p.f_row_bytes = static_cast<long long>(K) * 2;
   p.f_npb = static_cast<int>((128LL * p.f_row_bytes + 32767) / 32768);
+  p.f_last_rows = BM; p.f_npb_last = p.f_npb;
   for (int r = 0; r < 8; ++r) { p.f_peer[r] = r < world ? shard_ptrs[r] : nullptr; p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
   p.f_xg = static_cast<uint8_t*>(xg); p.f_flags = flags; p.f_dbg = g_fused_dbg;
   CUtensorMap tA, tB, tC, tC2;
@@ -1292,6 +1320,63 @@ extern "C" int b2_ag_gemm(void* const* shard_ptrs, void* const* ctrls, void* xg,
   }
   const int grid = sms;
   B2_FUSED_DISPATCH(FUSE_AG, false);
+}
+
+// All-gather of a ROW-SHARDED WEIGHT fused into the GEMM that consumes it (ZeRO-3 parameter fetch):
+//   C[M, N] = A[M, K] @ Wfull^T,   Wfull [N, K] = the `world` shards [shard_rows, K] stacked, N = world * shard_rows.
+// `wg` is this rank's full-size gathered weight in symmetric memory with its OWN shard already in place at rows
+// [rank * shard_rows, ...); shard_ptrs[r] = address of rank r's own shard inside rank r's copy of that buffer.  The
+// all-gather CTAs pull the world - 1 remote shards (own region never moves) in row order into `wg`; the GEMM CTAs walk the
+// column tiles N-major, starting with this rank's own rows of W, and wait per 128-row block of W for the counters.  After
+// the launch `wg` holds the complete weight (the backward and later calls read it there).  shard_rows need not be a
+// multiple of 128 (LLaMA's 32000-row head over 8 ranks: 4000); flags: world * ceil(shard_rows / 128) uint32, zero before
+// the first call (the launch leaves them zero).
+extern "C" int b2_agw_gemm(void* const* shard_ptrs, void* const* ctrls, void* wg, unsigned int* flags, const void* A, void* C,
+                           int M, int shard_rows, int K, long long lda, long long ldc, int dtype, int rank, int world,
+                           int n_comm, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (world < 2 || world > 8) { b2host::set_error("agw_gemm: world size %d unsupported", world); return -1; }
+  if ((K % 8) || (lda % 8) || (ldc % 8) || (shard_rows % 8) || M <= 0) { b2host::set_error("agw_gemm: K, shard_rows and leading dimensions must be multiples of 8"); return -1; }
+  const int N = shard_rows * world;
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const int sms = b2host::num_sms();
+  if (n_comm <= 0) n_comm = g_fused_ncomm;
+  if (n_comm > sms / 4) n_comm = sms / 4;
+  n_comm = (n_comm + 1) & ~1;
+  const int res_pairs = g_fused_pair_mode ? fused_resident_pairs() : 0;
+  const bool pair = g_fused_pair_mode && M >= 2 * BM && res_pairs > n_comm / 2 + 1;
+  const int bn = pair ? 256 : 128;          // single-CTA: 128-wide tiles (a CTA then stages exactly one 128-row block of W)
+  GemmParams p{};
+  p.M = M; p.N = N; p.K = K;
+  p.tiles_m = pair ? (M + 2 * BM - 1) / (2 * BM) : (M + BM - 1) / BM; p.tiles_n = (N + bn - 1) / bn; p.split_k = 1;
+  p.num_kb = (K + BK - 1) / BK; p.kb_per_split = p.num_kb;
+  p.epilogue = B2_EPI_NONE; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0; p.alpha = 1.f;
+  p.f_rank = rank; p.f_world = world; p.f_shard_rows = shard_rows; p.f_bpr = (shard_rows + BM - 1) / BM;
+  p.f_ncomm = n_comm;
+  p.f_row_bytes = static_cast<long long>(K) * 2;
+  p.f_npb = static_cast<int>((128LL * p.f_row_bytes + 32767) / 32768);
+  p.f_last_rows = shard_rows - (p.f_bpr - 1) * BM;
+  p.f_npb_last = static_cast<int>((static_cast<long long>(p.f_last_rows) * p.f_row_bytes + 32767) / 32768);
+  p.f_nmajor = 1; p.n_rot = (rank * shard_rows) / bn;      // the column tile that holds the first row of the own shard
+  p.f_self_clean = 1;
+  for (int r = 0; r < 8; ++r) { p.f_peer[r] = r < world ? shard_ptrs[r] : nullptr; p.f_ctrl[r] = r < world ? static_cast<uint32_t*>(ctrls[r]) : nullptr; }
+  p.f_xg = static_cast<uint8_t*>(wg); p.f_flags = flags; p.f_dbg = g_fused_dbg;
+  CUtensorMap tA, tB, tC;
+  if (make_ab_maps(&tA, &tB, A, wg, M, N, K, lda, K, 0, pair ? bn / 2 : bn, dt)) return -1;
+  uint64_t dims[2] = {static_cast<uint64_t>(N), static_cast<uint64_t>(M)}, strides[2] = {0, static_cast<uint64_t>(ldc) * 2};
+  uint32_t box[2] = {64, BM};
+  if (b2host::encode_tmap(&tC, dt, 2, C, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B)) return -1;
+  const CUtensorMap& tC2 = tC;
+  const CUtensorMap& tA2 = tA;
+  const int b_mn_major = 0;
+  if (pair) {
+    int pairs = sms / 2 < res_pairs ? sms / 2 : res_pairs;
+    const int grid = 2 * pairs;
+    if (bn == 256) return launch_fused<256, false, FUSE_AGB, true>(tA, tB, tC, tC2, p, grid, stream, tA2);
+  }
+  (void)b_mn_major;
+  const int grid = sms;
+  return launch_fused<128, false, FUSE_AGB, false>(tA, tB, tC, tC2, p, grid, stream, tA2);
 }
 
 // GEMM -> reduce-scatter in ONE kernel.  Each rank multiplies its K-slice (partial sums for ALL M rows); the

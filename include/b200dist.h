@@ -232,6 +232,13 @@ int b2_gemm_rs(const void* A, const void* B, int M, int N, int K, long long lda,
                void* const* cnt_ptrs, void* const* ctrls, void* const* stage_ptrs, void* out,
                long long ld_out, const void* bias, const void* residual, long long ld_res, int rank, int world,
                void* stream);
+/* All-gather of a row-sharded WEIGHT fused into its consuming GEMM (ZeRO-3 parameter fetch): C[M, world*shard_rows] =
+ * A[M, K] @ Wfull^T.  wg = this rank's full gathered weight (symmetric memory, own shard already in place at row
+ * rank * shard_rows); shard_ptrs[r] = rank r's own shard inside rank r's copy of wg; flags = world * ceil(shard_rows/128)
+ * uint32, zero before the first call.  After the launch wg is complete.  replaces DeepSpeed stage3 all_gather_coalesced +
+ * the cuBLAS GEMM that follows it. */
+int b2_agw_gemm(void* const* shard_ptrs, void* const* ctrls, void* wg, unsigned int* flags, const void* A, void* C, int M,
+                int shard_rows, int K, long long lda, long long ldc, int dtype, int rank, int world, int n_comm, void* stream);
 /* GEMM -> all-reduce (tensor parallelism without sequence parallelism): the b2_gemm_rs kernel whose reducing rank stores
  * each finished row block into EVERY rank's full [M, N] output and which ends with a cross-GPU barrier.  out buffers are
  * symmetric; armaps_dev = `world` tensor maps uploaded once by b2_make_ar_maps (a synchronous cudaMemcpy: set-up time only).

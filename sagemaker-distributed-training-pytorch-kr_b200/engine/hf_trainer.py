@@ -52,7 +52,8 @@ class _HeadUnit(nn.Module):
 class Zero3CausalLM(nn.Module):
     def __init__(self, model: nn.Module, *, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0,
                  gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None,
-                 offload_optimizer="none", gradient_checkpointing=False, max_live_parameters=0, prefetch_bucket_size=0, max_reuse_distance=0):
+                 offload_optimizer="none", gradient_checkpointing=False, max_live_parameters=0, prefetch_bucket_size=0, max_reuse_distance=0,
+                 fuse_head_gather=True):
         super().__init__()
         self.model = model
         self.tied = getattr(model, "lm_head", None) is None
@@ -65,7 +66,9 @@ class Zero3CausalLM(nn.Module):
                                   comm_backend=comm_backend, offload_param=offload_param, offload_optimizer=offload_optimizer,
                                   checkpoint_units=range(1, len(units) - 1) if gradient_checkpointing else (),      # the decoder layers
                                   max_live_parameters=max_live_parameters, prefetch_bucket_size=prefetch_bucket_size,
-                                  max_reuse_distance=max_reuse_distance)
+                                  max_reuse_distance=max_reuse_distance,
+                                  # the untied LM head reaches its GEMM through ops.functional.linear: gather it inside that GEMM
+                                  fuse_gather_gemm_units=() if (self.tied or not fuse_head_gather) else (len(units) - 1,))
         self._units = units
 
     def forward(self, input_ids, attention_mask=None, labels=None):

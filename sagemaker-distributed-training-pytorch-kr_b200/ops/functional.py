@@ -70,7 +70,11 @@ class _Linear(torch.autograd.Function):
         elif residual is not None:
             y = N.gemm(x2, w, bias=b, aux=residual.reshape(-1, w.shape[0]), epilogue=N.EPI_BIAS_RESIDUAL)
         else:
-            y = N.gemm(x2, w, bias=b, epilogue=N.EPI_BIAS if b is not None else N.EPI_NONE)
+            agw = getattr(w, "_zero3_agw", None)
+            if agw is not None and b is None and agw[0]._agw_pending == agw[1]:
+                y = agw[0].agw_linear(agw[1], x2)      # ZeRO-3: the weight's remote shards are gathered inside this GEMM
+            else:
+                y = N.gemm(x2, w, bias=b, epilogue=N.EPI_BIAS if b is not None else N.EPI_NONE)
         ctx.save_for_backward(x2, w, z)
         ctx.params, ctx.shp, ctx.has_res, ctx.act = (w, b), shp, residual is not None, act
         return y.view(*shp[:-1], w.shape[0])

@@ -75,6 +75,8 @@ class Fabric:
             L.b2_gemm_ar.restype = c_i
             L.b2_xent_vocab_parallel.argtypes = [c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_ll, c_i, c_p]
             L.b2_xent_vocab_parallel.restype = c_i
+            L.b2_agw_gemm.argtypes = [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_ll, c_ll, c_i, c_i, c_i, c_i, c_p]
+            L.b2_agw_gemm.restype = c_i
             L.b2_fused_config.argtypes = [c_i, c_i]
             L.b2_fused_config.restype = None
             L.b2_reduce_scatter.argtypes = [c_p, c_p, c_p, c_ll, c_i, c_f, c_i, c_i, c_i, c_p, c_p]
@@ -242,6 +244,30 @@ def _xent_vocab_parallel(self, logits2: torch.Tensor, labels: torch.Tensor, voca
 
 
 Fabric.xent_vocab_parallel = _xent_vocab_parallel
+
+
+def _agw_gemm(self, x2: torch.Tensor, buf: SymmBuffer, elem_offset: int, shard_rows: int, K: int, n_comm: int = 0) -> torch.Tensor:
+    """y [M, world * shard_rows] = x2 @ Wfull^T where Wfull lives in the symmetric buffer `buf` at `elem_offset`, row-sharded
+    over the ranks, and only this rank's shard is in place: the kernel gathers the other shards while it multiplies.  On
+    return (stream order) the buffer holds the complete weight."""
+    M = x2.shape[0]
+    assert x2.shape[1] == K and x2.is_contiguous()
+    esz = buf.tensor.element_size()
+    w = self.world
+    key = ("agw", id(buf), elem_offset, shard_rows, K)
+    st = self._coll.get(key)
+    if st is None:
+        bpr = (shard_rows + 127) // 128
+        st = self._coll[key] = {
+            "flags": torch.zeros(w * bpr, dtype=torch.int32, device=x2.device),
+            "shards": (c_p * w)(*[int(buf.ptrs[r]) + (elem_offset + r * shard_rows * K) * esz for r in range(w)])}
+    out = torch.empty((M, w * shard_rows), dtype=x2.dtype, device=x2.device)
+    N._call("b2_agw_gemm", st["shards"], buf.ctrls, int(buf.ptrs[self.rank]) + elem_offset * esz, N._p(st["flags"]), N._p(x2), N._p(out),
+            M, shard_rows, K, x2.stride(0), out.stride(0), N._dt(x2), self.rank, w, n_comm, N._st())
+    return out
+
+
+Fabric.agw_gemm = _agw_gemm
 
 
 def get_fabric(group=None) -> Fabric:

@@ -120,7 +120,7 @@ class Zero3Engine:
                  gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
                  offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None,
                  offload_optimizer: str = "none", checkpoint_units: Sequence[int] = (), max_live_parameters: float = 0,
-                 prefetch_bucket_size: int = 0, max_reuse_distance: float = 0):
+                 prefetch_bucket_size: int = 0, max_reuse_distance: float = 0, fuse_gather_gemm_units: Sequence[int] = ()):
         self.checkpoint_units = set(checkpoint_units)      # unit indices whose activations are recomputed in backward
         self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         self.world = dist.get_world_size(self.group) if self.group is not None else 1
@@ -242,6 +242,20 @@ class Zero3Engine:
         self.persist_m = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
         self.persist_v = [torch.zeros_like(p, dtype=torch.float32) for p in self.persistent]
         self.persist_fp32 = [p.data.float().clone() for p in self.persistent]
+        # units whose ONE partitioned parameter is a 2-D weight cut into whole rows (the LM head): their all-gather is fused
+        # into the GEMM that consumes the weight (csrc/gemm.cu b2_agw_gemm) instead of a stand-alone gather
+        self._agw_units = set()
+        self._agw_pending: Optional[int] = None
+        # (the caller names the candidates: the weight must reach the GEMM through ops.functional.linear - an embedding
+        # lookup over the same kind of parameter cannot pull its rows on demand)
+        if fuse_gather_gemm_units and self.fabric is not None and offload_param != "cpu" and self.dtype in (torch.bfloat16, torch.float16):
+            for u in self.units:
+                if u.index in set(fuse_gather_gemm_units) and len(u.params) == 1 and u.params[0].dim() == 2:
+                    p = u.params[0]
+                    rows, K = p.shape
+                    if rows % self.world == 0 and (rows // self.world) % 8 == 0 and K % 8 == 0 and u.numel == p.numel():
+                        self._agw_units.add(u.index)
+                        p._zero3_agw = (self, u.index)
         self._resident = [None] * self.n_ws    # which unit currently occupies each workspace
         self._events: Dict[int, torch.cuda.Event] = {}
         self._stream = torch.cuda.Stream() if self.dev.type == "cuda" else None
@@ -289,8 +303,34 @@ class Zero3Engine:
                 dist.all_gather_into_tensor(out.data, mine.data.clone(), group=self.group)
         self._resident[idx % self.n_ws] = idx
 
+    def _stage_own_slice(self, idx: int):
+        """fused gather + GEMM: only this rank's slice is put in place; the consuming GEMM pulls the rest (agw_linear)"""
+        u = self.units[idx]
+        ws = self._param_ws(idx)
+        mine = ws[self.rank * u.slice:(self.rank + 1) * u.slice]
+        N.axpby(self.lp_slices[idx], None, 1.0, 0.0, out=mine)
+        self._resident[idx % self.n_ws] = idx
+        self._agw_pending = idx
+
+    def agw_linear(self, idx: int, x2: torch.Tensor) -> torch.Tensor:
+        """x2 @ W^T for the single weight W of unit idx whose remote shards have not been gathered yet: ONE kernel gathers
+        them over NVLink and multiplies (own rows first); afterwards the workspace holds the whole weight."""
+        assert self._agw_pending == idx
+        u = self.units[idx]
+        p = u.params[0]
+        y = self.fabric.agw_gemm(x2, self._ws_param[idx % self.n_ws], u.offsets[0], p.shape[0] // self.world, p.shape[1])
+        self._agw_pending = None
+        return y
+
     def _ensure(self, idx: int, forward: bool):
         step = 1 if forward else -1
+        if self._agw_pending is not None and self._agw_pending != idx:
+            raise RuntimeError(f"ZeRO-3: unit {self._agw_pending} was staged for a fused gather+GEMM that never ran")
+        if forward and idx in self._agw_units and self._resident[idx % self.n_ws] != idx:
+            if self._stream is not None:
+                torch.cuda.current_stream().wait_stream(self._stream)      # earlier side-stream gathers into this ring are done
+            self._stage_own_slice(idx)
+            return
         if self._stream is None:
             if self._resident[idx % self.n_ws] != idx:
                 self._gather(idx)
@@ -307,6 +347,8 @@ class Zero3Engine:
             cur.wait_event(ev)
         for k in range(1, self.prefetch_depth + 1):
             nxt = idx + step * k
+            if forward and nxt in self._agw_units:
+                continue          # gathered by its own first GEMM
             if 0 <= nxt < len(self.units) and self._resident[nxt % self.n_ws] != nxt:
                 # prefetch into a workspace whose previous occupant is at least n_ws - depth units behind: its compute was
                 # issued earlier on the current stream, which the side stream waits for
@@ -328,6 +370,9 @@ class Zero3Engine:
             y = _CheckpointFn.apply(x, fn, args)
         else:
             y = fn(x, *args)
+        if self._agw_pending == idx:
+            raise RuntimeError(f"ZeRO-3: unit {idx} ({self.units[idx].name}) did not run its weight through ops.functional.linear; "
+                               "do not list it in fuse_gather_gemm_units")
         if torch.is_grad_enabled() and y.requires_grad:
             y = _PreBackwardFn.apply(y, self, idx)
         return y
