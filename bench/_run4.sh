@@ -1,3 +1,5 @@
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 4 --master-addr 127.0.0.1 --master-port"
-timeout 200 $TR 29614 bench.py --gpus 4 --steps 10 --warmup 3 > gpurun_out/bench_n4_final.json 2> gpurun_out/bench_n4_final.err; echo "ours rc=$?"; cut -c1-200 gpurun_out/bench_n4_final.json
-timeout 200 $TR 29616 bench.py --gpus 4 --steps 6 --warmup 3 --comm-backend nccl > gpurun_out/bench_n4_ncclarm.json 2> gpurun_out/bench_n4_ncclarm.err; echo "nccl arm rc=$?"; cut -c1-200 gpurun_out/bench_n4_ncclarm.json
+timeout 150 $TR 29612 bench/comm_check.py agw > gpurun_out/cc4_agw.log 2>&1; echo rc=$? >> gpurun_out/cc4_agw.log
+grep "FAIL\|ALL\|rc=\|graph-timed" gpurun_out/cc4_agw.log; grep -c "^ok" gpurun_out/cc4_agw.log
+timeout 150 $TR 29613 bench/comm_check.py xent > gpurun_out/cc4_xent.log 2>&1; echo rc=$? >> gpurun_out/cc4_xent.log
+grep "FAIL\|ALL\|rc=\|graph-timed" gpurun_out/cc4_xent.log; grep -c "^ok" gpurun_out/cc4_xent.log
