@@ -34,6 +34,8 @@ def main():
     ap.add_argument("--max-live-parameters", type=float, default=1e9)
     ap.add_argument("--max-reuse-distance", type=float, default=1e9)
     ap.add_argument("--no-clocks", action="store_true")
+    ap.add_argument("--full-init", action="store_true", help="materialise the whole model on every rank before partitioning (default: meta-device "
+                    "construction, one unit at a time - the zero.Init way)")
     ap.add_argument("--no-fuse-gather-gemm", action="store_true", help="gather the LM head with the stand-alone kernel instead of inside its GEMM")
     ap.add_argument("--layers", type=int, default=0, help="override the layer count (0 = the model's own)")
     ap.add_argument("--comm-backend", default="native")
@@ -53,9 +55,11 @@ def main():
     t0 = time.time()
     torch.manual_seed(0)
     kw = {"num_hidden_layers": a.layers} if a.layers else {}
-    model = build_causal_lm(a.model, device=dev, dtype=torch.bfloat16, **kw)
+    from b200dist.models.llama import meta_initializer
+    model = build_causal_lm(a.model, device=dev if a.full_init else "meta", dtype=torch.bfloat16, **kw)
     nparams = sum(p.numel() for p in model.parameters())
-    zm = Zero3CausalLM(model, lr=2e-5, weight_decay=0.0, max_grad_norm=a.clip, gradient_accumulation_steps=a.grad_accum,
+    init_kw = {} if a.full_init else {"materialize": meta_initializer(model.config, dev, torch.bfloat16, seed=0), "device": dev}
+    zm = Zero3CausalLM(model, **init_kw, lr=2e-5, weight_decay=0.0, max_grad_norm=a.clip, gradient_accumulation_steps=a.grad_accum,
                        max_live_parameters=a.max_live_parameters, max_reuse_distance=a.max_reuse_distance,
                        prefetch_bucket_size=int(0.9 * model.config.hidden_size ** 2),
                        persistence_threshold=10 * model.config.hidden_size, comm_backend=a.comm_backend if world > 1 else "nccl",
@@ -111,7 +115,7 @@ def main():
                "unit": "tokens/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
                "dtype": "bf16", "data": "synthetic instruction batches (pinned host -> device every step), random-init weights",
                "config": {"model": a.model, "layers": model.config.num_hidden_layers, "params": nparams, "seq_len": a.seq, "micro_batch_per_gpu": a.micro_batch, "grad_accum": a.grad_accum,
-                          "global_batch": world * a.micro_batch * a.grad_accum, "gather_workspaces": zm.engine.n_ws, "fused_gather_gemm_units": sorted(zm.engine._agw_units), "prefetch_depth": zm.engine.prefetch_depth, "parallelism": f"zero3 dp{world}", "comm_backend": a.comm_backend,
+                          "global_batch": world * a.micro_batch * a.grad_accum, "construction": "whole model per rank" if a.full_init else "meta device, one unit at a time", "gather_workspaces": zm.engine.n_ws, "fused_gather_gemm_units": sorted(zm.engine._agw_units), "prefetch_depth": zm.engine.prefetch_depth, "parallelism": f"zero3 dp{world}", "comm_backend": a.comm_backend,
                           "fabric": zm.engine.fabric is not None, "optimizer": f"AdamW fp32 partitioned, clip {a.clip}",
                           "offload_optimizer": a.offload_optimizer, "offload_param": a.offload_param, "gradient_checkpointing": a.gradient_checkpointing},
                "model_tflops_per_gpu": flops / (ms / 1e3) / 1e12, "peak_mem_gib": mem, "setup_s": setup_s, "last_loss": last_loss,

@@ -53,7 +53,7 @@ class Zero3CausalLM(nn.Module):
     def __init__(self, model: nn.Module, *, lr=1e-5, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, max_grad_norm=1.0,
                  gradient_accumulation_steps=1, persistence_threshold=0, comm_backend="native", offload_param="none", group=None,
                  offload_optimizer="none", gradient_checkpointing=False, max_live_parameters=0, prefetch_bucket_size=0, max_reuse_distance=0,
-                 fuse_head_gather=True):
+                 fuse_head_gather=True, materialize=None, device=None):
         super().__init__()
         self.model = model
         self.tied = getattr(model, "lm_head", None) is None
@@ -68,7 +68,8 @@ class Zero3CausalLM(nn.Module):
                                   max_live_parameters=max_live_parameters, prefetch_bucket_size=prefetch_bucket_size,
                                   max_reuse_distance=max_reuse_distance,
                                   # the untied LM head reaches its GEMM through ops.functional.linear: gather it inside that GEMM
-                                  fuse_gather_gemm_units=() if (self.tied or not fuse_head_gather) else (len(units) - 1,))
+                                  fuse_gather_gemm_units=() if (self.tied or not fuse_head_gather) else (len(units) - 1,),
+                                  materialize=materialize, device=device)
         self._units = units
 
     def forward(self, input_ids, attention_mask=None, labels=None):

@@ -229,6 +229,25 @@ class OPTForCausalLM(nn.Module):
         return self.head_loss(h, labels)
 
 
+def meta_initializer(cfg, device, dtype, seed: int = 0):
+    """`materialize(name, meta_param)` for models built with device="meta" (ZeRO-3 construction that never holds the whole
+    model, the role of DeepSpeed's zero.Init): norm weights -> 1, biases -> 0, matrices -> N(0, initializer_range) drawn from a
+    generator seeded by the parameter's NAME, so every rank creates identical values whatever the order of creation."""
+    import zlib
+    std = getattr(cfg, "initializer_range", 0.02)
+    dev = torch.device(device)
+
+    def materialize(name: str, p: torch.Tensor) -> torch.Tensor:
+        leaf = name.rsplit(".", 1)[-1]
+        if p.dim() == 1:
+            ones = leaf in ("norm", "input_layernorm", "post_attention_layernorm", "weight") or leaf.endswith("_w") or leaf.endswith("norm")
+            return (torch.ones if ones else torch.zeros)(p.shape, device=dev, dtype=dtype)
+        g = torch.Generator(device=dev).manual_seed((zlib.crc32(name.encode()) + 1000003 * seed) & 0x7FFFFFFF)
+        return torch.empty(p.shape, device=dev, dtype=torch.float32).normal_(0.0, std, generator=g).to(dtype)
+
+    return materialize
+
+
 def build_causal_lm(name_or_config, device=None, dtype=torch.float32, **config_overrides):
     """`--model_name_or_path` resolution without network access: a known name -> config with random init; a local
     directory with config.json (+ weights) -> ckpt.hf loader."""

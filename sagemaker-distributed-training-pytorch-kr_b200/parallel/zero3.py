@@ -41,6 +41,16 @@ def _align(n, a):
     return (n + a - 1) // a * a
 
 
+def _assign(p: nn.Parameter, t: torch.Tensor):
+    """p.data = t, also when p still lives on the meta device (where `.data =` refuses the device change)"""
+    if p.device.type == "meta":
+        keep = dict(p.__dict__)
+        torch.utils.swap_tensors(p, nn.Parameter(t, requires_grad=p.requires_grad))
+        p.__dict__.update(keep)
+    else:
+        p.data = t
+
+
 class _Unit:
     def __init__(self, index: int, name: str, module: nn.Module, params: List[nn.Parameter], names: List[str]):
         self.index, self.name, self.module, self.params, self.names = index, name, module, params, names
@@ -120,7 +130,12 @@ class Zero3Engine:
                  gradient_accumulation_steps: int = 1, persistence_threshold: int = 0, comm_backend: str = "native",
                  offload_param: str = "none", pin_memory: bool = True, grad_dtype: Optional[torch.dtype] = None,
                  offload_optimizer: str = "none", checkpoint_units: Sequence[int] = (), max_live_parameters: float = 0,
-                 prefetch_bucket_size: int = 0, max_reuse_distance: float = 0, fuse_gather_gemm_units: Sequence[int] = ()):
+                 prefetch_bucket_size: int = 0, max_reuse_distance: float = 0, fuse_gather_gemm_units: Sequence[int] = (),
+                 materialize=None, device=None):
+        """materialize / device: construction without ever holding the whole model (DeepSpeed `zero.Init`): build the modules on
+        the `meta` device and pass `materialize(qualified_name, meta_param) -> tensor on device` (deterministic and identical on
+        every rank, e.g. models.llama.meta_initializer); the engine then creates one unit's parameters at a time, keeps this
+        rank's slice and drops the rest, so the peak is one unit plus the partitioned state."""
         self.checkpoint_units = set(checkpoint_units)      # unit indices whose activations are recomputed in backward
         self.group = group if group is not None else (dist.group.WORLD if dist.is_initialized() else None)
         self.world = dist.get_world_size(self.group) if self.group is not None else 1
@@ -135,6 +150,11 @@ class Zero3Engine:
         self.offload_optimizer = offload_optimizer == "cpu"
         first = next(p for u in units for p in u.parameters())
         self.dev, self.dtype = first.device, first.dtype
+        self._materialize = materialize
+        if self.dev.type == "meta":
+            if materialize is None or device is None:
+                raise ValueError("ZeRO-3: parameters on the meta device need `materialize` and `device`")
+            self.dev = torch.device(device)
         self.grad_dtype = grad_dtype or self.dtype
         self.fabric = None
         if comm_backend == "native" and self.world > 1 and self.dev.type == "cuda":
@@ -155,6 +175,8 @@ class Zero3Engine:
                     continue
                 seen.add(id(p))
                 if p.numel() <= persistence_threshold or getattr(p, "_zero3_persistent", False):
+                    if p.device.type == "meta":            # replicated parameters are created right away (they are small)
+                        _assign(p, materialize(f"{nm}.{n}" if nm else n, p).to(device=self.dev, dtype=self.dtype))
                     self.persistent.append(p)
                     continue
                 ps.append(p); pn.append(n)
@@ -208,8 +230,10 @@ class Zero3Engine:
         a_off = 0
         for u in self.units:
             flat = torch.zeros(u.numel, dtype=self.dtype, device=self.dev)
-            for p, o in zip(u.params, u.offsets):
-                flat[o:o + p.numel()].copy_(p.data.reshape(-1))
+            for p, o, n in zip(u.params, u.offsets, u.names):
+                src = p.data if p.device.type != "meta" else materialize(f"{u.name}.{n}" if u.name else n, p)
+                flat[o:o + p.numel()].copy_(src.reshape(-1))
+                del src
             sl = flat[self.rank * u.slice:(self.rank + 1) * u.slice].clone()
             if offload_param == "cpu":
                 sl = sl.cpu().pin_memory() if (pin_memory and torch.cuda.is_available()) else sl.cpu()
@@ -235,7 +259,7 @@ class Zero3Engine:
             a_off += u.slice
             ws_p, ws_g = self._param_ws(u.index), self._grad_ws(u.index)
             for p, o in zip(u.params, u.offsets):      # parameters become views of the rotating workspace
-                p.data = ws_p[o:o + p.numel()].view(p.shape)
+                _assign(p, ws_p[o:o + p.numel()].view(p.shape))
                 p.grad_buffer = ws_g[o:o + p.numel()].view(p.shape)
                 p.zero3_unit = u.index
             del flat

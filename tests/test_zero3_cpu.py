@@ -128,3 +128,31 @@ def test_zero3_gradient_checkpointing_is_loss_identical():
     for r in range(world):
         assert plain[r][0] == ckpt[r][0], (plain[r][0], ckpt[r][0])
         assert plain[r][1] == ckpt[r][1]
+
+
+def test_zero3_meta_construction_never_holds_the_model_and_matches_the_initializer():
+    """zero.Init-style construction: modules on the meta device + a name-seeded initializer; the engine creates one unit at a
+    time.  Every gathered parameter equals what the initializer returns for its name, and training runs."""
+    import torch
+    from b200dist.engine.hf_trainer import Zero3CausalLM
+    from b200dist.models.llama import build_causal_lm, meta_initializer
+    for name in ("llama-tiny", "opt-tiny"):
+        model = build_causal_lm(name, device="meta", dtype=torch.float32)
+        assert all(p.device.type == "meta" for p in model.parameters())
+        init = meta_initializer(model.config, "cpu", torch.float32, seed=3)
+        zm = Zero3CausalLM(model, lr=1e-2, max_grad_norm=1.0, persistence_threshold=200, comm_backend="nccl", materialize=init, device="cpu")
+        sd = zm.engine.gather_full_state_dict()
+        assert len(sd) > 4
+        for k, v in sd.items():
+            want = init(k, torch.empty(v.shape, device="meta"))
+            assert torch.equal(v, want), k
+        for p in zm.engine.persistent:
+            assert p.device.type == "cpu"
+        ids = torch.randint(0, 512, (2, 32), generator=torch.Generator().manual_seed(0))
+        losses = []
+        for _ in range(4):
+            loss = zm(ids, labels=ids)
+            zm.engine.backward(loss)
+            zm.engine.step()
+            losses.append(float(loss.detach()))
+        assert losses[-1] < losses[0], losses
