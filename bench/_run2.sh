@@ -1,2 +1,2 @@
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port"
-timeout 300 $TR 29621 bench/bench_zero3.py --model llama-7b --layers 4 --steps 2 --warmup 2 --grad-accum 4 > gpurun_out/z3_l4_meta.json 2> gpurun_out/z3_l4_meta.err; echo rc=$?; cut -c1-200 gpurun_out/z3_l4_meta.json; grep -o '"construction[^,]*,\|"peak_mem_gib[^,]*,\|"setup_s[^,]*,\|"last_loss[^,]*,' gpurun_out/z3_l4_meta.json; tail -3 gpurun_out/z3_l4_meta.err | cut -c1-200
+timeout 200 $TR 29614 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/bench_n2_g.json 2> gpurun_out/bench_n2_g.err; echo "ours rc=$?"; cut -c1-230 gpurun_out/bench_n2_g.json; grep -o '"last_loss[^}]*' gpurun_out/bench_n2_g.json
