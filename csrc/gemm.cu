@@ -656,9 +656,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           tmem_ld_wait();
           if (c + TEAMS >= NCH) { tc_fence_before(); acc_release(&tmem_empty[buf]); }
           if (n0 + c * 32 >= p.N) continue;   // uniform across the team
-          uint8_t* sb = stage_of(sctr);
+          // fp32 output never prefetches aux tiles, so in the pair kernels the team's aux tile serves as a third staging
+          // tile: two reduce-adds stay in flight behind the one being staged
+          constexpr bool TRI = EPI_DB && AUX_TMA;
+          uint8_t* sb;
+          if constexpr (TRI) { const int s3 = sctr % 3; sb = s3 == 0 ? team_buf : (s3 == 1 ? team_buf2 : aux_tile); }
+          else sb = stage_of(sctr);
           ++sctr;
-          if (leader) stage_wait();
+          if (leader) { if constexpr (TRI) tma_store_wait_read<2>(); else stage_wait(); }
           named_bar_sync(bar_id, EPI_THREADS);
           if (p.alpha != 1.f) {
 #pragma unroll
@@ -1055,13 +1060,19 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   if (split_k <= 0) {  // auto: only meaningful for fp32 accumulate outputs
     split_k = 1;
     if (out_fp32 && accumulate) {
-      int tiles = tiles_m_eff * tiles_n;
-      const int slots = pair ? sms / 2 : sms;
-      while (tiles * split_k * 2 <= slots && num_kb / (split_k * 2) >= 4) split_k *= 2;
-      if (tiles * split_k < slots && num_kb / (split_k + 1) >= 4) {
-        int want = (slots + tiles - 1) / tiles;
-        if (num_kb / want >= 4) split_k = want;
-      }
+      // cost in k-block units: rounds over the resident CTAs (or pairs) x (k-blocks per item + ramp), floored by the
+      // fp32 reduce epilogue a round has to hide; the smallest split within 4 % of the best keeps the reduce traffic low
+      const int tiles = tiles_m_eff * tiles_n;
+      const int slots = std::max(1, pair ? sms / 2 : sms);
+      auto cost = [&](int s) {
+        const int kbs = (num_kb + s - 1) / s;
+        const int items = tiles * ((num_kb + kbs - 1) / kbs);
+        return 1LL * ((items + slots - 1) / slots) * std::max(kbs + 4, 32);
+      };
+      long long best = cost(1);
+      for (int s = 2; s <= 32 && num_kb / s >= 4; ++s) best = std::min(best, cost(s));
+      for (int s = 1; s <= 32 && (s == 1 || num_kb / s >= 4); ++s)
+        if (cost(s) * 100 <= best * 104) { split_k = s; break; }
     }
   }
   GemmParams p{};
