@@ -350,21 +350,34 @@ def check_embedding(quick):
 
 
 def check_wattn(quick):
-    """Swin window attention (7x7 windows, head_dim 32): fused kernel vs the fp32 PyTorch restatement."""
-    for (Bw, heads, nW) in [(8, 4, 4), (30, 3, 1), (128, 8, 16)]:
-        qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)
+    """Swin window attention (7x7 windows, head_dim 32): fused kernels vs the fp32 PyTorch restatement (tensor-core kernels, then the
+    CUDA-core ones they replaced)."""
+    for impl, tag in ((1, "tc"), (0, "simt")):
+        N.set_window_attn_impl(impl)
+        _check_wattn_numerics(tag)
+    N.set_window_attn_impl(1)
+    _check_wattn_rest(quick)
+
+
+def _check_wattn_numerics(tag):
+    for (Bw, heads, nW, dt) in [(8, 4, 4, torch.bfloat16), (30, 3, 1, torch.bfloat16), (128, 8, 16, torch.bfloat16), (12, 2, 4, torch.float16)]:
+        qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=dt)
         bias = torch.randn(heads, 49, 49, device=dev)
         mask = None if nW == 1 else torch.where(torch.rand(nW, 49, 49, device=dev) < 0.3, -100.0, 0.0)
         scale = 32 ** -0.5
         out, lse = N.window_attn_fwd(qkv, bias, mask, heads, scale)
         outr, lser = N.window_attn_fwd(cpu(qkv), cpu(bias), cpu(mask), heads, scale)
-        report(f"wattn fwd Bw{Bw} heads{heads} nW{nW}", out, outr, 2e-2)
-        report(f"wattn lse Bw{Bw} heads{heads} nW{nW}", lse, lser, 2e-3)
+        report(f"wattn[{tag}] fwd Bw{Bw} heads{heads} nW{nW}", out, outr, 2e-2)
+        report(f"wattn[{tag}] lse Bw{Bw} heads{heads} nW{nW}", lse, lser, 2e-3)
         do = torch.randn_like(out)
         dqkv, dbias = N.window_attn_bwd(qkv, bias, mask, out, do, lse, heads, scale)
-        dqkvr, dbiasr = N.window_attn_bwd(cpu(qkv), cpu(bias), cpu(mask), outr.to(torch.bfloat16), cpu(do), lser, heads, scale)
-        report(f"wattn bwd dqkv Bw{Bw} heads{heads}", dqkv, dqkvr, 4e-2)
-        report(f"wattn bwd dbias Bw{Bw} heads{heads}", dbias, dbiasr, 2e-2)
+        dqkvr, dbiasr = N.window_attn_bwd(cpu(qkv), cpu(bias), cpu(mask), outr.to(dt), cpu(do), lser, heads, scale)
+        for part, name in enumerate(("dq", "dk", "dv")):
+            report(f"wattn[{tag}] bwd {name} Bw{Bw} heads{heads}", dqkv.view(Bw, 49, 3, -1)[:, :, part], dqkvr.view(Bw, 49, 3, -1)[:, :, part], 4e-2)
+        report(f"wattn[{tag}] bwd dbias Bw{Bw} heads{heads}", dbias, dbiasr, 2e-2)
+
+
+def _check_wattn_rest(quick):
     # cyclic shift + window partition and its inverse (one gather pass each) against roll + permute
     for (B, H, W, C, sh) in [(2, 14, 14, 64, (3, 3)), (3, 28, 56, 128, (3, 0)), (1, 7, 7, 32, (0, 0))]:
         x = torch.randn(B, H, W, C, device=dev, dtype=torch.bfloat16)
@@ -381,6 +394,10 @@ def check_wattn(quick):
             do = torch.randn_like(out)
             ms_f = timeit(lambda: N.window_attn_fwd(qkv, bias, mask, heads, 32 ** -0.5))
             ms_b = timeit(lambda: N.window_attn_bwd(qkv, bias, mask, out, do, lse, heads, 32 ** -0.5))
+            N.set_window_attn_impl(0)
+            ms_f0 = timeit(lambda: N.window_attn_fwd(qkv, bias, mask, heads, 32 ** -0.5))
+            ms_b0 = timeit(lambda: N.window_attn_bwd(qkv, bias, mask, out, do, lse, heads, 32 ** -0.5))
+            N.set_window_attn_impl(1)
 
             def eager():
                 q, k, v = qkv.view(Bw, 49, 3, heads, 32).permute(2, 0, 3, 1, 4)
@@ -388,7 +405,9 @@ def check_wattn(quick):
                 a = (a.view(Bw // nW, nW, heads, 49, 49) + mask.to(a.dtype)[None, :, None]).view(Bw, heads, 49, 49)
                 return (torch.softmax(a.float(), -1).to(v.dtype) @ v).transpose(1, 2).reshape(Bw, 49, heads * 32)
             ms_e = timeit(eager)
-            print(f"time wattn {tag}: fwd {ms_f:.4f} ms bwd {ms_b:.4f} ms | eager PyTorch chain fwd {ms_e:.4f} ms", flush=True)
+            byt = Bw * 49 * heads * 32 * 2
+            print(f"time wattn {tag}: fwd {ms_f:.4f} ms ({4 * byt / ms_f / 1e6:.0f} GB/s) bwd {ms_b:.4f} ms ({8 * byt / ms_b / 1e6:.0f} GB/s) | "
+                  f"CUDA-core kernels fwd {ms_f0:.4f} ms bwd {ms_b0:.4f} ms | eager PyTorch chain fwd {ms_e:.4f} ms", flush=True)
 
 
 def check_attn(quick):

@@ -408,4 +408,9 @@ int num_sms();            // SM count minus the reserve set with set_reserved_sm
 int set_spin_timeout_gemm(unsigned long long ns);     // gemm.cu / comm.cu: copy the bound into their translation unit's device word
 int set_spin_timeout_comm(unsigned long long ns);
 void set_reserved_sms(int n);
+// window_attn_tc.cu: tensor-core Swin window attention (49 tokens, head_dim 32); same contracts as b2_window_attn_fwd / _bwd
+int wattn_tc_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW, int heads, float scale,
+                 int dtype, cudaStream_t st);
+int wattn_tc_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout, const float* lse, void* dqkv,
+                 float* dbias, long long Bw, int nW, int heads, float scale, int dtype, cudaStream_t st);
 }  // namespace b2host

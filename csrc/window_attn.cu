@@ -1,4 +1,6 @@
-// Swin shifted-window attention, forward and backward, fused (sm_100a).
+// Swin shifted-window attention, forward and backward, fused (sm_100a): entry points, the CUDA-core kernels (kept as the
+// second implementation: b2_window_attn_set_impl(0)) and the shift / partition gather.  The default kernels are the
+// tensor-core ones of window_attn_tc.cu.
 //
 //   per (window, head):  S = (q * scale) k^T + rel_pos_bias[head] (+ shift mask[window % nW]);  P = softmax(S);  O = P v
 //
@@ -235,10 +237,19 @@ constexpr int BWD_SMEM = (4 * WT * WD + 2 * WT * WT) * static_cast<int>(sizeof(f
 
 }  // namespace
 
+// 1 (default): tensor-core kernels of window_attn_tc.cu;  0: the one-thread-per-row CUDA-core kernels of this file
+static int g_wattn_impl = 1;
+extern "C" int b2_window_attn_set_impl(int impl) {
+  const int prev = g_wattn_impl;
+  if (impl == 0 || impl == 1) g_wattn_impl = impl;
+  return prev;
+}
+
 extern "C" int b2_window_attn_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW,
                                   int heads, int tokens, int head_dim, float scale, int dtype, void* stream) {
   if (tokens != WT || head_dim != WD) { b2host::set_error("window_attn: only 7x7 windows with head_dim 32 (got %d tokens, head_dim %d)", tokens, head_dim); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g_wattn_impl == 1) return b2host::wattn_tc_fwd(qkv, bias, mask, out, lse, Bw, nW, heads, scale, dtype, st);
   const long long pairs = Bw * heads;
   const unsigned grid = static_cast<unsigned>((pairs + 1) / 2);
   if (dtype == B2_DTYPE_BF16)
@@ -254,6 +265,7 @@ extern "C" int b2_window_attn_bwd(const void* qkv, const float* bias, const floa
                                   float scale, int dtype, void* stream) {
   if (tokens != WT || head_dim != WD) { b2host::set_error("window_attn: only 7x7 windows with head_dim 32 (got %d tokens, head_dim %d)", tokens, head_dim); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (g_wattn_impl == 1) return b2host::wattn_tc_bwd(qkv, bias, mask, out, dout, lse, dqkv, dbias, Bw, nW, heads, scale, dtype, st);
   long long per_head = (static_cast<long long>(b2host::num_sms()) * 8 + heads - 1) / heads;
   if (per_head > Bw) per_head = Bw;
   if (per_head < 1) per_head = 1;

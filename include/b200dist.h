@@ -68,6 +68,8 @@ int b2_gemm_resident_pairs(void);   /* CTA pairs of the GEMM kernel that can be 
  * mask[w % nW]); lse fp32 [Bw, heads, 49].  Backward writes dqkv (layout of qkv) and ACCUMULATES d(bias) into dbias.
  * replaces: torchvision ShiftedWindowAttention's matmul / +bias / +mask / softmax / matmul chain.
  */
+/* 1 (default): tensor-core window attention (mma.sync, csrc/window_attn_tc.cu); 0: CUDA-core kernels.  Returns the previous value. */
+int b2_window_attn_set_impl(int impl);
 int b2_window_attn_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW,
                        int heads, int tokens, int head_dim, float scale, int dtype, void* stream);
 int b2_window_attn_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout,

@@ -112,7 +112,18 @@ def lib():
             L.b2_gemm_set_pair_mode.argtypes = [ctypes.c_int]
             L.b2_gemm_set_pair_mode.restype = None
             L.b2_gemm_set_pair_mode(int(os.environ["B2_GEMM_PAIR_MODE"]))
+        if os.environ.get("B2_WATTN_IMPL"):           # A/B switch: 0 = CUDA-core window attention, 1 = tensor-core kernels (default)
+            L.b2_window_attn_set_impl.argtypes = [ctypes.c_int]
+            L.b2_window_attn_set_impl(int(os.environ["B2_WATTN_IMPL"]))
     return _lib
+
+
+def set_window_attn_impl(impl: int) -> int:
+    """Swin window attention kernels: 1 = tensor-core (mma.sync, csrc/window_attn_tc.cu; default), 0 = CUDA-core.  Returns the previous value."""
+    L = lib()
+    L.b2_window_attn_set_impl.argtypes = [ctypes.c_int]
+    L.b2_window_attn_set_impl.restype = ctypes.c_int
+    return L.b2_window_attn_set_impl(int(impl))
 
 
 def set_gemm_pair_mode(mode: int) -> None:

@@ -14,6 +14,10 @@ namespace k_conv {
 namespace k_bn {
 #include "batchnorm.cu"
 }
+#include "mma_emu.h"
+namespace k_wtc {
+#include "window_attn_tc.cu"
+}
 
 namespace {
 template <typename F>
@@ -215,4 +219,35 @@ int b2_bn_bwd_apply(const void* dy, const void* x, const void* y, const float* m
   return 0;
 }
 
+}  // extern "C"
+
+// tensor-core window attention (mma.sync / ldmatrix / cp.async emulated by mma_emu.h); grid (grid_x, heads) like the host launchers
+extern "C" {
+void emu_wattn_tc_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW, int heads,
+                      float scale, int dtype, int grid_x) {
+  namespace W = k_wtc::wtc;
+  if (dtype == 1)
+    emu::launch(dim3(grid_x, heads), dim3(W::THREADS), W::FWD_SMEM, [&] {
+      W::wattn_tc_fwd_kernel<__nv_bfloat16>(static_cast<const __nv_bfloat16*>(qkv), bias, mask, static_cast<__nv_bfloat16*>(out), lse, Bw, nW, heads, scale);
+    });
+  else
+    emu::launch(dim3(grid_x, heads), dim3(W::THREADS), W::FWD_SMEM, [&] {
+      W::wattn_tc_fwd_kernel<__half>(static_cast<const __half*>(qkv), bias, mask, static_cast<__half*>(out), lse, Bw, nW, heads, scale);
+    });
+}
+
+void emu_wattn_tc_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout, const float* lse, void* dqkv,
+                      float* dbias, long long Bw, int nW, int heads, float scale, int dtype, int grid_x) {
+  namespace W = k_wtc::wtc;
+  if (dtype == 1)
+    emu::launch(dim3(grid_x, heads), dim3(W::THREADS), W::BWD_SMEM, [&] {
+      W::wattn_tc_bwd_kernel<__nv_bfloat16>(static_cast<const __nv_bfloat16*>(qkv), bias, mask, static_cast<const __nv_bfloat16*>(out),
+                                            static_cast<const __nv_bfloat16*>(dout), lse, static_cast<__nv_bfloat16*>(dqkv), dbias, Bw, nW, heads, scale);
+    });
+  else
+    emu::launch(dim3(grid_x, heads), dim3(W::THREADS), W::BWD_SMEM, [&] {
+      W::wattn_tc_bwd_kernel<__half>(static_cast<const __half*>(qkv), bias, mask, static_cast<const __half*>(out), static_cast<const __half*>(dout), lse,
+                                     static_cast<__half*>(dqkv), dbias, Bw, nW, heads, scale);
+    });
+}
 }  // extern "C"

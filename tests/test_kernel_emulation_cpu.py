@@ -18,8 +18,8 @@ DT = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
 
 @pytest.fixture(scope="module")
 def emu():
-    srcs = [os.path.join(ROOT, "tests", "emu", f) for f in ("emu_kernels.cpp", "cuda_emu.h")] + \
-           [os.path.join(ROOT, "csrc", f) for f in ("softmax.cu", "conv.cu", "batchnorm.cu")]
+    srcs = [os.path.join(ROOT, "tests", "emu", f) for f in ("emu_kernels.cpp", "cuda_emu.h", "mma_emu.h")] + \
+           [os.path.join(ROOT, "csrc", f) for f in ("softmax.cu", "conv.cu", "batchnorm.cu", "window_attn_tc.cu")]
     if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(s) for s in srcs):
         os.makedirs(os.path.dirname(SO), exist_ok=True)
         r = subprocess.run(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-mf16c", "-mavx2", "-I" + os.path.join(ROOT, "tests", "emu"),
@@ -246,3 +246,40 @@ def test_mnist_model_on_the_emulated_native_ops(native_on_emu):
     la.backward(); lb.backward()
     for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
         assert torch.allclose(p.grad, q.grad, atol=1e-4, rtol=1e-3), (n, (p.grad - q.grad).abs().max())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("Bw,heads,nW,grid_x", [(4, 2, 2, 3), (3, 1, 1, 1), (2, 3, 1, 2)])
+def test_window_attention_tensor_core_kernels_under_emulation(emu, dtype, Bw, heads, nW, grid_x):
+    """csrc/window_attn_tc.cu (mma.sync m16n8k16 + ldmatrix + cp.async double buffer) with the warp-level matrix primitives emulated by
+    tests/emu/mma_emu.h from the PTX fragment tables: every fragment index, the C -> A repacking of P / dS, both score orientations of the
+    backward, the padding rows / columns, the window loop with grid_x < Bw and the d(bias) accumulation, against the fp32 restatement."""
+    from b200dist.ops import native as N
+    torch.manual_seed(4)
+    C = heads * 32
+    qkv = torch.randn(Bw, 49, 3 * C).to(dtype)
+    bias = torch.randn(heads, 49, 49)
+    mask = None if nW == 1 else torch.where(torch.rand(nW, 49, 49) < 0.3, -100.0, 0.0)
+    scale = 32 ** -0.5
+    out = torch.full((Bw, 49, C), float("nan")).to(dtype)
+    lse = torch.full((Bw, heads, 49), float("nan"))
+    emu.emu_wattn_tc_fwd(_p(qkv), _p(bias), _p(mask), _p(out), _p(lse), c_ll(Bw), nW, heads, c_f(scale), DT[dtype], grid_x)
+    outr, lser = N.window_attn_fwd(qkv, bias, mask, heads, scale)
+    assert torch.allclose(lse, lser, atol=2e-5, rtol=1e-5), (lse - lser).abs().max()
+    assert torch.allclose(out.float(), outr.float(), atol=2e-2, rtol=2e-2), (out.float() - outr.float()).abs().max()
+    rel = (out.float() - outr.float()).pow(2).mean().sqrt() / outr.float().pow(2).mean().sqrt()
+    assert rel < 4e-3, rel
+    do = torch.randn(Bw, 49, C).to(dtype)
+    dqkv = torch.full((Bw, 49, 3 * C), float("nan")).to(dtype)
+    dbias = torch.zeros(heads, 49, 49)
+    emu.emu_wattn_tc_bwd(_p(qkv), _p(bias), _p(mask), _p(outr), _p(do), _p(lser), _p(dqkv), _p(dbias), c_ll(Bw), nW, heads, c_f(scale), DT[dtype], grid_x)
+    dqkvr, dbiasr = N.window_attn_bwd(qkv, bias, mask, outr, do, lser, heads, scale)
+    for name, got, ref in (("dq", dqkv.view(Bw, 49, 3, C)[:, :, 0], dqkvr.view(Bw, 49, 3, C)[:, :, 0]),
+                           ("dk", dqkv.view(Bw, 49, 3, C)[:, :, 1], dqkvr.view(Bw, 49, 3, C)[:, :, 1]),
+                           ("dv", dqkv.view(Bw, 49, 3, C)[:, :, 2], dqkvr.view(Bw, 49, 3, C)[:, :, 2]),
+                           ("dbias", dbias, dbiasr)):
+        got, ref = got.float(), ref.float()
+        assert torch.isfinite(got).all(), name
+        rel = (got - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()
+        assert rel < 6e-3, (name, rel)
+        assert (got - ref).abs().max() <= 3e-2 * max(1.0, ref.abs().max().item()), (name, (got - ref).abs().max())
