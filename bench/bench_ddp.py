@@ -32,6 +32,8 @@ def main():
     ap.add_argument("--fp32", action="store_true")
     ap.add_argument("--comm-backend", default="native")
     ap.add_argument("--no-cuda-graph", action="store_true")
+    ap.add_argument("--kernel-profile", default="", help="after the timed steps, trace 2 more with torch.profiler (CUPTI) on rank 0 and write a "
+                                                          "per-kernel table here (diagnostic: never a bench value)")
     a = ap.parse_args()
     real_fd = os.dup(1)
     os.dup2(2, 1)
@@ -113,6 +115,24 @@ def main():
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item() / a.steps
     clocks = sampler.stop() if sampler is not None else None
+    if a.kernel_profile:
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(2):
+                step(i)
+            torch.cuda.synchronize()
+        if rank == 0:
+            rows = {}
+            for ev in prof.events():
+                if ev.device_type is not None and "cuda" in str(ev.device_type).lower():
+                    r = rows.setdefault(ev.name, [0, 0.0])
+                    r[0] += 1; r[1] += ev.device_time if hasattr(ev, "device_time") else ev.cuda_time
+            tot = sum(v[1] for v in rows.values())
+            with open(a.kernel_profile, "w") as f:
+                f.write(f"# per-kernel device time over 2 steps (torch.profiler / CUPTI, rank 0): total {tot / 2e3:.3f} ms per step of kernel time\n")
+                for name, (cnt, us) in sorted(rows.items(), key=lambda kv: -kv[1][1]):
+                    f.write(f"{us / 2e3:9.3f} ms/step {100 * us / tot:5.1f}%  x{cnt / 2:7.1f}  avg {us / cnt:8.1f} us  {name[:150]}\n")
+        dist.barrier()
     if rank == 0:
         out = {"metric": "DDP img/s", "value": world * a.batch_size / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": a.steps,
                "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "dtype": "fp32" if a.fp32 else "bf16",

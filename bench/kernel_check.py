@@ -385,7 +385,27 @@ def _check_wattn_rest(quick):
         report(f"window partition B{B} {H}x{W} C{C} shift{sh}", xw, N.window_shuffle(cpu(x), B, H, W, 7, sh, False), 0.0)
         back = N.window_shuffle(xw, B, H, W, 7, sh, True)
         report(f"window reverse  B{B} {H}x{W} C{C} shift{sh} (round trip)", back, x, 0.0)
+    # residual add + per-sample scale (stochastic depth), identity map and with the window maps folded in
+    for (B, H, W, C, sh, dt) in [(3, 14, 14, 64, (3, 3), torch.bfloat16), (2, 28, 56, 128, (3, 0), torch.float16), (5, 7, 7, 32, (0, 0), torch.bfloat16)]:
+        res = torch.randn(B, H, W, C, device=dev, dtype=dt)
+        xw = torch.randn(B * (H // 7) * (W // 7), 49, C, device=dev, dtype=dt)
+        sc = torch.empty(B, device=dev).bernoulli_(0.6).div_(0.6)
+        for mode, xin, r in ((2, xw, res), (1, res, None), (0, res, res.flip(0)), (0, xw, None)):
+            for scale in (sc, None):
+                got = N.rows_scale_add(xin, r, scale, B, H, W, 7, sh, mode)
+                want = N.rows_scale_add(cpu(xin).float(), cpu(r).float() if r is not None else None, cpu(scale), B, H, W, 7, sh, mode)
+                report(f"rows_scale_add mode{mode} B{B} {H}x{W} C{C} shift{sh} res={int(r is not None)} scale={int(scale is not None)}", got, want, 8e-3)
     if not quick:
+        for (B, H, W, C) in [(64, 56, 56, 128), (64, 14, 14, 512)]:
+            res = torch.randn(B, H, W, C, device=dev, dtype=torch.bfloat16)
+            xw = torch.randn(B * (H // 7) * (W // 7), 49, C, device=dev, dtype=torch.bfloat16)
+            sc = torch.empty(B, device=dev).bernoulli_(0.6).div_(0.6)
+            ms2 = timeit(lambda: N.rows_scale_add(xw, res, sc, B, H, W, 7, (3, 3), 2))
+            ms1 = timeit(lambda: N.rows_scale_add(res, None, sc, B, H, W, 7, (3, 3), 1))
+            ms_e = timeit(lambda: res + N.window_shuffle(xw, B, H, W, 7, (3, 3), True) * sc.to(res.dtype).view(B, 1, 1, 1))
+            byt = res.numel() * 2
+            print(f"time rows_scale_add B{B} {H}x{W} C{C}: fwd (reverse + scale + add) {ms2:.4f} ms {3 * byt / ms2 / 1e6:.0f} GB/s | bwd (partition + scale) "
+                  f"{ms1:.4f} ms {2 * byt / ms1 / 1e6:.0f} GB/s | window_shuffle kernel + ATen multiply + add {ms_e:.4f} ms", flush=True)
         for (Bw, heads, nW, tag) in [(4096, 4, 64, "swin_b stage 1, batch 64"), (256, 16, 4, "swin_b stage 3, batch 64")]:
             qkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)
             bias = torch.randn(heads, 49, 49, device=dev)

@@ -242,9 +242,30 @@ B2_DEVICE float gelu_tanh_grad(float x) {
   float du = fmaf(3.f * k0 * k1, x2, k0);
   return fmaf(0.5f * x * fmaf(-t, t, 1.f), du, fmaf(0.5f, t, 0.5f));
 }
-B2_DEVICE float gelu_erf(float x) { return 0.5f * x * (1.f + erff(x * 0.7071067811865476f)); }
-B2_DEVICE float gelu_erf_grad(float x) {
-  return fmaf(x * 0.3989422804014327f, __expf(-0.5f * x * x), 0.5f * (1.f + erff(x * 0.7071067811865476f)));
+// erf through Abramowitz-Stegun 7.1.26 (absolute error < 6e-7 with fp32 arithmetic, far below 16-bit output rounding): one
+// rcp + one ex2 and six FMAs, no branch - erff() costs about three times as many issue slots, which is what bounds the
+// epilogue warps of the GELU GEMMs.  `e` returns exp(-z^2), which the derivative needs anyway.
+B2_DEVICE float erf_as(float z, float& e) {
+  const float az = fabsf(z);
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, az, 1.f)));
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(az * az * -1.4426950408889634f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  return copysignf(fmaf(-p * t, e, 1.f), z);
+}
+B2_DEVICE float gelu_erf(float x) {
+  float e;
+  const float r = erf_as(x * 0.7071067811865476f, e);
+  const float hx = 0.5f * x;
+  return fmaf(hx, r, hx);
+}
+B2_DEVICE float gelu_erf_grad(float x) {       // Phi(x) + x phi(x);  exp(-x^2 / 2) is erf_as's by-product
+  float e;
+  const float r = erf_as(x * 0.7071067811865476f, e);
+  return fmaf(x * 0.3989422804014327f, e, fmaf(0.5f, r, 0.5f));
 }
 B2_DEVICE uint32_t pack2(float lo, float hi, int fmt) {
   if (fmt == 1) return pack_bf16x2(lo, hi);

@@ -323,6 +323,81 @@ window_shuffle_kernel(const uint4* __restrict__ in, uint4* __restrict__ out, int
 }
 }  // namespace
 
+// ------------------------------------------------------------------------------------------
+// residual add with a per-sample scale (stochastic depth) and, optionally, the window maps above folded in:
+//   out[r, :] = res[r, :] + scale[b(r)] * x[src(r), :]          r = OUTPUT row, b(r) = r / (H * W) = its sample
+//   map 0: src(r) = r;   map 1: out in window order, x in image order (partition);   map 2: out in image order, x in window
+//   order (reverse).  res == NULL: no residual;  scale == NULL: 1.
+// replaces: torchvision's `x + stochastic_depth(branch)` (a broadcast multiply that ATen runs unvectorised, then an add) and
+// the window_reverse pass before it; its backward (d branch = scale * dout through the inverse map) is the same kernel.
+// ------------------------------------------------------------------------------------------
+namespace {
+template <typename T>
+__global__ void __launch_bounds__(256)
+rows_scale_add_kernel(const uint4* __restrict__ x, const uint4* __restrict__ res, const float* __restrict__ scale, uint4* __restrict__ out,
+                      int B, int H, int W, int vecC, int ws, int sh, int sw, int map) {
+  const int nwx = W / ws, nwy = H / ws;
+  const long long per_sample = static_cast<long long>(H) * W;
+  const long long total = static_cast<long long>(B) * per_sample * vecC;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int v = static_cast<int>(idx % vecC);
+    const long long orow = idx / vecC;                // OUTPUT row
+    long long row = orow;
+    long long src = orow;
+    if (map == 1) {
+      const int tx = static_cast<int>(row % ws); row /= ws;
+      const int ty = static_cast<int>(row % ws); row /= ws;
+      const int wx = static_cast<int>(row % nwx); row /= nwx;
+      const int wy = static_cast<int>(row % nwy); row /= nwy;      // row = b
+      int y = wy * ws + ty + sh; if (y >= H) y -= H;
+      int xx = wx * ws + tx + sw; if (xx >= W) xx -= W;
+      src = (row * H + y) * W + xx;
+    } else if (map == 2) {
+      const int xx = static_cast<int>(row % W); row /= W;
+      const int y = static_cast<int>(row % H); row /= H;           // row = b
+      int yp = y - sh; if (yp < 0) yp += H;
+      int xp = xx - sw; if (xp < 0) xp += W;
+      src = (((row * nwy + yp / ws) * nwx + xp / ws) * ws + yp % ws) * ws + xp % ws;
+    }
+    const float sc = scale ? __ldg(scale + orow / per_sample) : 1.f;
+    const uint4 q = x[src * vecC + v];
+    const uint4 r = res ? res[idx] : make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t qi[4] = {q.x, q.y, q.z, q.w}, ri[4] = {r.x, r.y, r.z, r.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 a = WCvt<T>::up(qi[k]), b = WCvt<T>::up(ri[k]);
+      o[k] = WCvt<T>::down(fmaf(sc, a.x, b.x), fmaf(sc, a.y, b.y));
+    }
+    out[idx] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+}  // namespace
+
+// x / res / out: 16-bit rows of C elements (C % 8 == 0), B * H * W rows; scale fp32 [B] or NULL; map 0 / 1 / 2 as above
+// (maps 1 and 2 need H and W multiples of ws and 0 <= shift < extent; map 0 ignores ws and the shifts)
+extern "C" int b2_rows_scale_add(const void* x, const void* res, const float* scale, void* out, int B, int H, int W, int C, int ws,
+                                 int shift_h, int shift_w, int map, int dtype, void* stream) {
+  if ((C % 8) || map < 0 || map > 2 || B <= 0 || H <= 0 || W <= 0) { b2host::set_error("rows_scale_add: need C %% 8 == 0 and map in 0..2"); return -1; }
+  if (map != 0 && (ws <= 0 || (H % ws) || (W % ws) || shift_h < 0 || shift_w < 0 || shift_h >= H || shift_w >= W)) {
+    b2host::set_error("rows_scale_add: window maps need H and W multiples of the window size, 0 <= shift < extent"); return -1;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(b2host::num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
+  if (map == 0) ws = 1;
+  if (dtype == B2_DTYPE_BF16)
+    rows_scale_add_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, st>>>(
+        static_cast<const uint4*>(x), static_cast<const uint4*>(res), scale, static_cast<uint4*>(out), B, H, W, C / 8, ws, shift_h, shift_w, map);
+  else
+    rows_scale_add_kernel<__half><<<static_cast<unsigned>(blocks), 256, 0, st>>>(
+        static_cast<const uint4*>(x), static_cast<const uint4*>(res), scale, static_cast<uint4*>(out), B, H, W, C / 8, ws, shift_h, shift_w, map);
+  return wcheck("rows_scale_add");
+}
+
 // in / out: 16-bit elements, C % 8 == 0, H and W multiples of ws, 0 <= shift < ws
 extern "C" int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int ws, int shift_h, int shift_w, int reverse,
                                  void* stream) {

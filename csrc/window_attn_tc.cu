@@ -54,6 +54,9 @@ B2_DEVICE void ldsm_x4_t(uint32_t r[4], const void* row_ptr) {
 B2_DEVICE void cp_async16(void* smem_dst, const void* gmem_src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
 }
+B2_DEVICE void cp_async4(void* smem_dst, const void* gmem_src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
 B2_DEVICE void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> B2_DEVICE void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
@@ -73,7 +76,7 @@ template <> B2_DEVICE void unpack2<__half>(uint32_t u, float& lo, float& hi) {
   lo = f.x; hi = f.y;
 }
 #else
-using ::mma16816; using ::ldsm_x4; using ::ldsm_x4_t; using ::cp_async16; using ::cp_async_commit; using ::cp_async_wait;
+using ::mma16816; using ::ldsm_x4; using ::ldsm_x4_t; using ::cp_async16; using ::cp_async4; using ::cp_async_commit; using ::cp_async_wait;
 using ::pack2; using ::unpack2;
 #endif
 
@@ -87,7 +90,7 @@ constexpr int BIAS_BYTES = WT * BSTRIDE * 4;
 constexpr int THREADS = 128;
 constexpr int FWD_TILES = 3, BWD_TILES = 5;       // q k v | q k v dO O
 constexpr int FWD_SMEM = BIAS_BYTES + 2 * FWD_TILES * TILE_BYTES;
-constexpr int BWD_SMEM = BIAS_BYTES + 2 * ROWS * 4 + 2 * BWD_TILES * TILE_BYTES;
+constexpr int BWD_SMEM = BIAS_BYTES + 3 * ROWS * 4 + 2 * BWD_TILES * TILE_BYTES;     // + lse [2 stages][64], delta [64]
 
 // address lane `lane` passes to ldmatrix for a 16 x 16 block at (row0, col0) of a tile: matrices are
 // (rows 0-7, cols 0-7), (rows 8-15, cols 0-7), (rows 0-7, cols 8-15), (rows 8-15, cols 8-15).
@@ -110,11 +113,13 @@ B2_DEVICE void zero_pad_rows(unsigned char* tiles, int ntiles, int tid) {
     reinterpret_cast<uint32_t*>(tiles + t * TILE_BYTES + WT * RSTRIDE)[o] = 0u;
   }
 }
-// bias[head] (fp32 [49][49]) -> shared [49][56], padding columns zero
+// bias[head] (fp32 [49][49]) -> shared [49][56], padding columns zero.  4-byte asynchronous copies (rows of 49 floats are only
+// 4-byte aligned): they join the caller's first copy group, so the prologue costs one memory latency instead of twenty
 B2_DEVICE void stage_bias(float* sBias, const float* bias_h, int tid) {
   for (int i = tid; i < WT * BSTRIDE; i += THREADS) {
     const int r = i / BSTRIDE, c = i - r * BSTRIDE;
-    sBias[i] = c < WT ? __ldg(bias_h + r * WT + c) : 0.f;
+    if (c < WT) cp_async4(sBias + i, bias_h + r * WT + c);
+    else sBias[i] = 0.f;
   }
 }
 // 49 rows x 64 bytes of one (window, part, head) -> tile rows (16-byte asynchronous copies, 4 per row)
@@ -160,9 +165,10 @@ wattn_tc_fwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
     cp_async_commit();
   };
   long long w = blockIdx.x;
+  stage_bias(sBias, bias + static_cast<long long>(h) * WT * WT, tid);      // part of the first copy group
   if (w < Bw) issue(w, 0);
   zero_pad_rows(tiles, 2 * FWD_TILES, tid);
-  stage_bias(sBias, bias + static_cast<long long>(h) * WT * WT, tid);
+  const float inv_scale = 1.f / scale;
 
   const int r0 = warp * 16 + g, r1 = r0 + 8;                   // this thread's two query rows
   const bool v0 = r0 < WT, v1 = r1 < WT;
@@ -177,35 +183,40 @@ wattn_tc_fwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
     const unsigned char* sK = sQ + TILE_BYTES;
     const unsigned char* sV = sK + TILE_BYTES;
 
-    // S = q k^T for this warp's 16 rows: 7 key tiles of 8, contraction over the 32 dims in two k-steps
-    uint32_t qa[2][4];
-    ldsm_x4(qa[0], blk16(sQ, warp * 16, 0, lane));
-    ldsm_x4(qa[1], blk16(sQ, warp * 16, 16, lane));
+    // S / scale = (bias + mask) / scale + q k^T for this warp's 16 rows: the accumulators START at the additive terms (their
+    // loads run ahead of the MMAs), 7 key tiles of 8, contraction over the 32 dims in two k-steps
+    const float* m0p = mask ? mask + ((w % nW) * WT + (v0 ? r0 : WT - 1)) * WT : nullptr;
+    const float* m1p = mask ? mask + ((w % nW) * WT + (v1 ? r1 : WT - 1)) * WT : nullptr;
     float sc[7][4];
 #pragma unroll
     for (int nt = 0; nt < 7; ++nt) {
-      sc[nt][0] = sc[nt][1] = sc[nt][2] = sc[nt][3] = 0.f;
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int c = nt * 8 + t4 * 2 + e;
+        float a0 = b0p[c], a1 = b1p[c];
+        if (mask && c < WT) { a0 += __ldg(m0p + c); a1 += __ldg(m1p + c); }
+        sc[nt][e] = a0 * inv_scale; sc[nt][2 + e] = a1 * inv_scale;
+      }
+    }
+    uint32_t qa[2][4];
+    ldsm_x4(qa[0], blk16(sQ, warp * 16, 0, lane));
+    ldsm_x4(qa[1], blk16(sQ, warp * 16, 16, lane));
+#pragma unroll
+    for (int nt = 0; nt < 7; ++nt) {
       uint32_t kb[4];
       ldsm_x4(kb, row8(sK, nt * 8, lane));
       mma16816<T>(sc[nt], qa[0], kb[0], kb[1]);
       mma16816<T>(sc[nt], qa[1], kb[2], kb[3]);
     }
-    // scale, bias, mask, row max
-    const float* m0p = mask ? mask + ((w % nW) * WT + (v0 ? r0 : WT - 1)) * WT : nullptr;
-    const float* m1p = mask ? mask + ((w % nW) * WT + (v1 ? r1 : WT - 1)) * WT : nullptr;
+    // scale, row max (key columns 49..55 do not exist)
     float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
     for (int nt = 0; nt < 7; ++nt) {
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         const int c = nt * 8 + t4 * 2 + e;
-        float s0 = fmaf(sc[nt][e], scale, b0p[c]);
-        float s1 = fmaf(sc[nt][2 + e], scale, b1p[c]);
-        if (c < WT) {
-          if (mask) { s0 += __ldg(m0p + c); s1 += __ldg(m1p + c); }
-        } else {
-          s0 = -INFINITY; s1 = -INFINITY;
-        }
+        const float s0 = c < WT ? sc[nt][e] * scale : -INFINITY;
+        const float s1 = c < WT ? sc[nt][2 + e] * scale : -INFINITY;
         sc[nt][e] = s0; sc[nt][2 + e] = s1;
         mx0 = fmaxf(mx0, s0); mx1 = fmaxf(mx1, s1);
       }
@@ -278,9 +289,9 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
   extern __shared__ __align__(128) unsigned char smem[];
 #endif
   float* sBias = reinterpret_cast<float*>(smem);
-  float* sLse = reinterpret_cast<float*>(smem + BIAS_BYTES);           // [64] (0 beyond row 48)
-  float* sDelta = sLse + ROWS;                                         // [64]
-  unsigned char* tiles = smem + BIAS_BYTES + 2 * ROWS * 4;             // [2 stages][q k v dO O]
+  float* sLse2 = reinterpret_cast<float*>(smem + BIAS_BYTES);          // [2 stages][64] (0 beyond row 48)
+  float* sDelta = sLse2 + 2 * ROWS;                                    // [64]
+  unsigned char* tiles = smem + BIAS_BYTES + 3 * ROWS * 4;             // [2 stages][q k v dO O]
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t4 = lane & 3;
   const int h = blockIdx.y;
   const int C = heads * WD;
@@ -293,12 +304,15 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
     for (int part = 0; part < 3; ++part) issue_rows<T>(st + part * TILE_BYTES, base + part * C, rs, tid);
     issue_rows<T>(st + 3 * TILE_BYTES, dout + w * WT * C + h * WD, C, tid);
     issue_rows<T>(st + 4 * TILE_BYTES, out + w * WT * C + h * WD, C, tid);
+    if (tid < WT) cp_async4(sLse2 + s * ROWS + tid, lse + (w * heads + h) * WT + tid);
     cp_async_commit();
   };
   long long w = blockIdx.x;
+  stage_bias(sBias, bias + static_cast<long long>(h) * WT * WT, tid);      // part of the first copy group
   if (w < Bw) issue(w, 0);
   zero_pad_rows(tiles, 2 * BWD_TILES, tid);
-  stage_bias(sBias, bias + static_cast<long long>(h) * WT * WT, tid);
+  if (tid >= WT && tid < ROWS) { sLse2[tid] = 0.f; sLse2[ROWS + tid] = 0.f; }
+  const float inv_scale = 1.f / scale;
 
   const int r0 = warp * 16 + g, r1 = r0 + 8;       // this thread's two rows: query rows in the first half, key rows in the second
   const bool v0 = r0 < WT, v1 = r1 < WT;
@@ -316,8 +330,9 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
     const unsigned char* sV = sK + TILE_BYTES;
     const unsigned char* sG = sV + TILE_BYTES;      // dO
     const unsigned char* sO = sG + TILE_BYTES;
+    const float* sLse = sLse2 + s * ROWS;
 
-    // delta_i = dO_i . O_i (two threads per row, 16 dims each) and lse_i -> shared
+    // delta_i = dO_i . O_i (two threads per row, 16 dims each) -> shared
     {
       const int row = tid >> 1, half = tid & 1;
       float part = 0.f;
@@ -335,7 +350,6 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
       }
       part += __shfl_xor_sync(0xffffffffu, part, 1);
       if (half == 0) sDelta[row] = part;                               // rows 49..63: 0
-      if (tid < ROWS) sLse[tid] = tid < WT ? lse[(w * heads + h) * WT + tid] : 0.f;
     }
     __syncthreads();
     const float* mbase = mask ? mask + (w % nW) * WT * WT : nullptr;
@@ -362,7 +376,14 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
         for (int j = 0; j < 2; ++j) {
           const int nt = 2 * kt + j;
           if (nt < 7) {
-            float sa[4] = {0.f, 0.f, 0.f, 0.f}, pa[4] = {0.f, 0.f, 0.f, 0.f};
+            float sa[4], pa[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {          // S / scale starts at (bias + mask) / scale
+              const int c = nt * 8 + t4 * 2 + e;
+              float a0 = b0p[c], a1 = b1p[c];
+              if (mbase && c < WT) { a0 += __ldg(m0p + c); a1 += __ldg(m1p + c); }
+              sa[e] = a0 * inv_scale; sa[2 + e] = a1 * inv_scale;
+            }
             uint32_t kb[4], vb[4];
             ldsm_x4(kb, row8(sK, nt * 8, lane));
             mma16816<T>(sa, qa[0], kb[0], kb[1]);
@@ -374,12 +395,8 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int c = nt * 8 + t4 * 2 + e;
-              const int cc = c < WT ? c : WT - 1;
-              float s0 = fmaf(sa[e], scale, b0p[c]);
-              float s1 = fmaf(sa[2 + e], scale, b1p[c]);
-              if (mbase) { s0 += __ldg(m0p + cc); s1 += __ldg(m1p + cc); }
-              const float d0 = __expf(s0 - lse0) * (pa[e] - dl0);
-              const float d1 = __expf(s1 - lse1) * (pa[2 + e] - dl1);
+              const float d0 = __expf(fmaf(sa[e], scale, -lse0)) * (pa[e] - dl0);
+              const float d1 = __expf(fmaf(sa[2 + e], scale, -lse1)) * (pa[2 + e] - dl1);
               ds[e] = (c < WT && v0) ? d0 : 0.f;
               ds[2 + e] = (c < WT && v1) ? d1 : 0.f;
             }
@@ -426,7 +443,15 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
         for (int j = 0; j < 2; ++j) {
           const int nt = 2 * qt + j;
           if (nt < 7) {
-            float sa[4] = {0.f, 0.f, 0.f, 0.f}, pa[4] = {0.f, 0.f, 0.f, 0.f};
+            float sa[4], pa[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {          // S^T / scale starts at (bias + mask)[query][key] / scale
+              const int q = nt * 8 + t4 * 2 + e;
+              const int qc = q < WT ? q : WT - 1;
+              float a0 = sBias[qc * BSTRIDE + rc0], a1 = sBias[qc * BSTRIDE + rc1];
+              if (mbase) { a0 += __ldg(mbase + qc * WT + rc0); a1 += __ldg(mbase + qc * WT + rc1); }
+              sa[e] = a0 * inv_scale; sa[2 + e] = a1 * inv_scale;
+            }
             uint32_t qb[4], gb[4];
             ldsm_x4(qb, row8(sQ, nt * 8, lane));
             mma16816<T>(sa, ka[0], qb[0], qb[1]);
@@ -438,12 +463,8 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
               const int q = nt * 8 + t4 * 2 + e;                       // query index (column)
-              const int qc = q < WT ? q : WT - 1;
               const float lq = sLse[q], dq_ = sDelta[q];
-              float s0 = fmaf(sa[e], scale, sBias[qc * BSTRIDE + rc0]);
-              float s1 = fmaf(sa[2 + e], scale, sBias[qc * BSTRIDE + rc1]);
-              if (mbase) { s0 += __ldg(mbase + qc * WT + rc0); s1 += __ldg(mbase + qc * WT + rc1); }
-              const float p0 = __expf(s0 - lq), p1 = __expf(s1 - lq);
+              const float p0 = __expf(fmaf(sa[e], scale, -lq)), p1 = __expf(fmaf(sa[2 + e], scale, -lq));
               const bool ok0 = q < WT && v0, ok1 = q < WT && v1;
               p[e] = ok0 ? p0 : 0.f;
               p[2 + e] = ok1 ? p1 : 0.f;
@@ -504,12 +525,20 @@ wattn_tc_bwd_kernel(const T* __restrict__ qkv, const float* __restrict__ bias, c
 namespace b2host {
 
 namespace {
-// CTAs per head: enough to fill every SM `per_sm` times over, never more than there are windows
+// CTAs per head: one wave - as many as are resident at once (`per_sm` from the occupancy query) and no more, so that no CTA
+// starts after the others have finished; never more than there are windows
 dim3 wattn_grid(long long Bw, int heads, int per_sm) {
-  long long per_head = (static_cast<long long>(num_sms()) * per_sm + heads - 1) / heads;
+  long long per_head = static_cast<long long>(num_sms()) * per_sm / heads;
   if (per_head > Bw) per_head = Bw;
   if (per_head < 1) per_head = 1;
   return dim3(static_cast<unsigned>(per_head), static_cast<unsigned>(heads));
+}
+int g_grid_override[2] = {0, 0};          // CTAs per SM the grids are sized for (forward, backward); 0 = what the occupancy query says
+template <typename K>
+int resident_ctas(K kernel, int smem_bytes) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, wtc::THREADS, smem_bytes) != cudaSuccess || n < 1) { cudaGetLastError(); n = 1; }
+  return n;
 }
 int wattn_check(const char* what) {
   cudaError_t e = cudaGetLastError();
@@ -521,12 +550,14 @@ int wattn_check(const char* what) {
 int wattn_tc_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW, int heads, float scale,
                  int dtype, cudaStream_t st) {
   static bool cfg = false;
+  static int per_sm = 1;
   if (!cfg) {
     cudaFuncSetAttribute(wtc::wattn_tc_fwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, wtc::FWD_SMEM);
     cudaFuncSetAttribute(wtc::wattn_tc_fwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, wtc::FWD_SMEM);
+    per_sm = resident_ctas(wtc::wattn_tc_fwd_kernel<__nv_bfloat16>, wtc::FWD_SMEM);
     cfg = true;
   }
-  const dim3 grid = wattn_grid(Bw, heads, 4);
+  const dim3 grid = wattn_grid(Bw, heads, g_grid_override[0] > 0 ? g_grid_override[0] : per_sm);
   if (dtype == B2_DTYPE_BF16)
     wtc::wattn_tc_fwd_kernel<__nv_bfloat16><<<grid, wtc::THREADS, wtc::FWD_SMEM, st>>>(
         static_cast<const __nv_bfloat16*>(qkv), bias, mask, static_cast<__nv_bfloat16*>(out), lse, Bw, nW > 0 ? nW : 1, heads, scale);
@@ -539,12 +570,14 @@ int wattn_tc_fwd(const void* qkv, const float* bias, const float* mask, void* ou
 int wattn_tc_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout, const float* lse, void* dqkv,
                  float* dbias, long long Bw, int nW, int heads, float scale, int dtype, cudaStream_t st) {
   static bool cfg = false;
+  static int per_sm = 1;
   if (!cfg) {
     cudaFuncSetAttribute(wtc::wattn_tc_bwd_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, wtc::BWD_SMEM);
     cudaFuncSetAttribute(wtc::wattn_tc_bwd_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, wtc::BWD_SMEM);
+    per_sm = resident_ctas(wtc::wattn_tc_bwd_kernel<__nv_bfloat16>, wtc::BWD_SMEM);
     cfg = true;
   }
-  const dim3 grid = wattn_grid(Bw, heads, 3);
+  const dim3 grid = wattn_grid(Bw, heads, g_grid_override[1] > 0 ? g_grid_override[1] : per_sm);
   if (dtype == B2_DTYPE_BF16)
     wtc::wattn_tc_bwd_kernel<__nv_bfloat16><<<grid, wtc::THREADS, wtc::BWD_SMEM, st>>>(
         static_cast<const __nv_bfloat16*>(qkv), bias, mask, static_cast<const __nv_bfloat16*>(out), static_cast<const __nv_bfloat16*>(dout), lse,
@@ -557,4 +590,10 @@ int wattn_tc_bwd(const void* qkv, const float* bias, const float* mask, const vo
 }
 
 }  // namespace b2host
+
+// tuning knob: size the forward / backward grids for this many CTAs per SM (0 = the occupancy query's answer, the default)
+extern "C" void b2_window_attn_set_grid(int fwd_ctas_per_sm, int bwd_ctas_per_sm) {
+  b2host::g_grid_override[0] = fwd_ctas_per_sm;
+  b2host::g_grid_override[1] = bwd_ctas_per_sm;
+}
 #endif  // !B2_EMU

@@ -70,6 +70,8 @@ int b2_gemm_resident_pairs(void);   /* CTA pairs of the GEMM kernel that can be 
  */
 /* 1 (default): tensor-core window attention (mma.sync, csrc/window_attn_tc.cu); 0: CUDA-core kernels.  Returns the previous value. */
 int b2_window_attn_set_impl(int impl);
+/* tuning knob of the tensor-core kernels: grids sized for this many CTAs per SM (0 = occupancy query, the default) */
+void b2_window_attn_set_grid(int fwd_ctas_per_sm, int bwd_ctas_per_sm);
 int b2_window_attn_fwd(const void* qkv, const float* bias, const float* mask, void* out, float* lse, long long Bw, int nW,
                        int heads, int tokens, int head_dim, float scale, int dtype, void* stream);
 int b2_window_attn_bwd(const void* qkv, const float* bias, const float* mask, const void* out, const void* dout,
@@ -79,6 +81,11 @@ int b2_window_attn_bwd(const void* qkv, const float* bias, const float* mask, co
  * in [B, H, W, C] <-> out [B * (H/ws) * (W/ws), ws*ws, C].  replaces torch.roll + permute copies. */
 int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int ws, int shift_h, int shift_w, int reverse,
                       void* stream);
+/* out[r,:] = res[r,:] + scale[r / (H*W)] * x[src(r),:] over B*H*W rows of C 16-bit elements (C % 8 == 0); res / scale may be NULL
+ * (0 / 1).  map 0: src(r) = r; 1: window partition of x; 2: window reverse of x (the maps of b2_window_shuffle).  The residual add
+ * with stochastic depth, with Swin's window_reverse folded in; the backward is the same kernel with the inverse map. */
+int b2_rows_scale_add(const void* x, const void* res, const float* scale, void* out, int B, int H, int W, int C, int ws,
+                      int shift_h, int shift_w, int map, int dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].

@@ -8,8 +8,10 @@ Conv2d(3,128,k4,s4) + LN; 4 stages with depths [2,2,18,2], dims 128/256/512/1024
 
 Kernel mapping: every Linear (qkv / proj / mlp / patch-merge reduction / head) and the patch-embed convolution
 (non-overlapping 4x4 patches == a [B*H/4*W/4, 48] x [48, 128] GEMM) run on the tcgen05 GEMM with bias fused in
-the epilogue; LayerNorm and erf-GELU are the native kernels.  The 49-token / head_dim-32 window attention core is
-batched matmul + softmax in PyTorch for now (windows are too small for the 128-row flash kernel).
+the epilogue; LayerNorm and erf-GELU are the native kernels.  The 49-token / head_dim-32 window attention core is the fused
+tensor-core kernel of csrc/window_attn_tc.cu (scores + relative-position bias + shift mask + softmax + PV); the cyclic shift and
+window partition are one gather pass, and the way back (un-partition + shift back) is folded into the residual add together with
+stochastic depth (csrc/window_attn.cu: rows_scale_add_kernel).
 """
 from __future__ import annotations
 
@@ -53,6 +55,55 @@ class LayerNorm(nn.Module):
     def forward(self, x):
         return OF.layer_norm(x, self.weight, self.bias, self.eps)
 
+    def with_skip(self, x):
+        """(norm(x), x'): x' == x is what the block's skip connection should use (gradients meet inside the norm backward kernel)."""
+        return OF.layer_norm_residual(x, self.weight, self.bias, self.eps)
+
+
+class _BiasGather(torch.autograd.Function):
+    """relative_position_bias_table [(2 ws - 1)^2, heads] -> fp32 bias [heads, T, T] (T = ws^2) through the fixed index.  The backward is
+    an index_add_ (atomics) instead of autograd's sort-based index_put of the plain `table[index]` expression."""
+
+    @staticmethod
+    def forward(ctx, table, index, n):
+        ctx.save_for_backward(index)
+        ctx.shape, ctx.dtype = table.shape, table.dtype
+        return table.float().t().index_select(1, index).view(-1, n, n)
+
+    @staticmethod
+    def backward(ctx, dbias):
+        (index,) = ctx.saved_tensors
+        heads = ctx.shape[1]
+        dt = torch.zeros((heads, ctx.shape[0]), dtype=torch.float32, device=dbias.device)
+        dt.index_add_(1, index, dbias.reshape(heads, -1).float())
+        return dt.t().to(ctx.dtype), None, None
+
+
+_MASK_CACHE = {}
+
+
+def shift_window_mask(pH: int, pW: int, ws: int, shift, device) -> torch.Tensor:
+    """torchvision's cross-window attention mask of a cyclically shifted map: fp32 [nW, ws^2, ws^2], 0 where two tokens of a window come
+    from the same image region and -100 where they do not.  It depends on the geometry only, so it is built once per geometry and
+    device (torchvision rebuilds it with ~15 small kernels in every forward)."""
+    key = (pH, pW, ws, int(shift[0]), int(shift[1]), str(device))
+    m = _MASK_CACHE.get(key)
+    if m is None:
+        region = torch.zeros((pH, pW), dtype=torch.float32)
+        hs = ((0, -ws), (-ws, -shift[0]), (-shift[0], None))
+        wsl = ((0, -ws), (-ws, -shift[1]), (-shift[1], None))
+        c = 0
+        for h in hs:
+            for w in wsl:
+                region[h[0]:h[1], w[0]:w[1]] = c
+                c += 1
+        nW = (pH // ws) * (pW // ws)
+        region = region.view(pH // ws, ws, pW // ws, ws).permute(0, 2, 1, 3).reshape(nW, ws * ws)
+        diff = region.unsqueeze(1) - region.unsqueeze(2)
+        m = torch.where(diff != 0, torch.tensor(-100.0), torch.tensor(0.0)).contiguous().to(device)
+        _MASK_CACHE[key] = m
+    return m
+
 
 class ShiftedWindowAttention(nn.Module):
     def __init__(self, dim, window, shift, heads):
@@ -64,11 +115,12 @@ class ShiftedWindowAttention(nn.Module):
         self.register_buffer("relative_position_index", _relative_position_index(window))
 
     def _bias(self):
-        n = self.ws * self.ws
-        b = self.relative_position_bias_table[self.relative_position_index].view(n, n, -1)
-        return b.permute(2, 0, 1).contiguous().unsqueeze(0)
+        """fp32 [1, heads, T, T]"""
+        return _BiasGather.apply(self.relative_position_bias_table, self.relative_position_index, self.ws * self.ws).unsqueeze(0)
 
-    def forward(self, x):                      # x: [B, H, W, C]
+    def forward(self, x, skip=None, sd_prob: float = 0.0):
+        """x: [B, H, W, C] (already normalised).  With ``skip`` the block's residual add (skip + stochastic_depth(attention(x))) happens
+        here, fused with the un-partition / shift back of the attention output."""
         B, H, W, C = x.shape
         ws = self.ws
         pad_r, pad_b = (ws - W % ws) % ws, (ws - H % ws) % ws
@@ -78,24 +130,16 @@ class ShiftedWindowAttention(nn.Module):
         nW = (pH // ws) * (pW // ws)
         x = OF.window_partition(x, ws, shift)               # cyclic shift + partition in one pass: [B*nW, ws*ws, C]
         qkv = self.qkv(x)                                   # [B*nW, ws*ws, 3C], last dim = [3][heads][head_dim]
-        mask = None
-        if sum(shift) > 0:
-            mask = x.new_zeros((pH, pW))
-            hs = ((0, -ws), (-ws, -shift[0]), (-shift[0], None))
-            wsl = ((0, -ws), (-ws, -shift[1]), (-shift[1], None))
-            c = 0
-            for h in hs:
-                for w in wsl:
-                    mask[h[0]:h[1], w[0]:w[1]] = c
-                    c += 1
-            mask = mask.view(pH // ws, ws, pW // ws, ws).permute(0, 2, 1, 3).reshape(nW, ws * ws)
-            mask = mask.unsqueeze(1) - mask.unsqueeze(2)
-            mask = mask.masked_fill(mask != 0, float(-100.0)).masked_fill(mask == 0, float(0.0))      # [nW, T, T]
+        mask = shift_window_mask(pH, pW, ws, shift, x.device) if sum(shift) > 0 else None      # [nW, T, T] fp32, cached
         # scores + relative-position bias + shift mask + softmax + PV in one fused kernel (ops/functional.window_attention)
         x = OF.window_attention(qkv, self._bias()[0], mask, self.heads, (C // self.heads) ** -0.5)
         x = self.proj(x)
+        if skip is not None and pH == H and pW == W:
+            # skip + stochastic_depth(window_reverse(x)) in one pass
+            return OF.residual_sd_add(skip, x, sd_prob, self.training, window_geom=(B, pH, pW, ws, shift))
         x = OF.window_reverse(x, B, pH, pW, ws, shift)      # un-partition + shift back in one pass
-        return x if (pH == H and pW == W) else x[:, :H, :W, :].contiguous()
+        x = x if (pH == H and pW == W) else x[:, :H, :W, :].contiguous()
+        return x if skip is None else OF.residual_sd_add(skip, x, sd_prob, self.training)
 
 
 _FUSED_MLP = os.environ.get("B2_SWIN_FUSED_MLP", "1") != "0"
@@ -132,8 +176,10 @@ class SwinBlock(nn.Module):
         self.norm2, self.mlp, self.sd = LayerNorm(dim), MLP(dim, 4 * dim), sd_prob
 
     def forward(self, x):
-        x = x + stochastic_depth(self.attn(self.norm1(x)), self.sd, self.training)
-        return x + stochastic_depth(self.mlp(self.norm2(x)), self.sd, self.training)
+        h, skip = self.norm1.with_skip(x)
+        x = self.attn(h, skip=skip, sd_prob=self.sd)                         # skip + stochastic_depth(attn(norm1(x)))
+        h, skip = self.norm2.with_skip(x)
+        return OF.residual_sd_add(skip, self.mlp(h), self.sd, self.training)   # skip + stochastic_depth(mlp(norm2(x)))
 
 
 class PatchMerging(nn.Module):

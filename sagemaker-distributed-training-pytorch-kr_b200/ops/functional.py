@@ -163,6 +163,77 @@ class _Norm(torch.autograd.Function):
         return dx, _vgrad(ctx.params[0], dg), (_vgrad(ctx.params[1], db) if ctx.params[1] is not None else None), None, None
 
 
+class _NormResidual(torch.autograd.Function):
+    """(LN(x), x): the second output aliases the input, so a pre-norm residual block hands it to its residual add and the two
+    gradients that reach x (through the norm and through the skip connection) are summed INSIDE the norm backward kernel
+    (norm_bwd's `dres`) instead of by a separate autograd accumulation pass."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, eps):
+        xc = x.contiguous()
+        y, mean, rstd = N.norm_fwd(xc, w, b, eps, False)
+        ctx.save_for_backward(xc, w, mean, rstd)
+        ctx.params = (w, b)
+        ctx.set_materialize_grads(False)
+        return y, xc.view_as(xc)
+
+    @staticmethod
+    def backward(ctx, dy, dskip):
+        x, w, mean, rstd = ctx.saved_tensors
+        if dy is None:
+            return dskip, None, None, None
+        dx, dg, db = N.norm_bwd(dy.contiguous(), x, w, mean, rstd, False, dres=dskip.contiguous() if dskip is not None else None)
+        return dx, _vgrad(ctx.params[0], dg), _vgrad(ctx.params[1], db), None
+
+
+def layer_norm_residual(x, weight, bias, eps: float = 1e-5):
+    """Returns (layer_norm(x), x') with x' == x: use x' for the skip connection of a pre-norm block (see _NormResidual)."""
+    if not _lowp(x) or x.shape[-1] % 8:
+        return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps), x
+    return _NormResidual.apply(x, weight, bias, eps)
+
+
+class _ResidualScaleAdd(torch.autograd.Function):
+    """out = res + scale[sample] * map(branch); map = identity or Swin's window_reverse (geom = (B, H, W, ws, shift))."""
+
+    @staticmethod
+    def forward(ctx, res, branch, scale, geom, reverse):
+        B, H, W, ws, shift = geom
+        ctx.geom, ctx.reverse, ctx.scale = geom, reverse, scale
+        return N.rows_scale_add(branch, res, scale, B, H, W, ws, shift, 2 if reverse else 0)
+
+    @staticmethod
+    def backward(ctx, dout):
+        B, H, W, ws, shift = ctx.geom
+        dbranch = None
+        if ctx.needs_input_grad[1]:
+            if ctx.scale is None and not ctx.reverse:
+                dbranch = dout
+            else:
+                dbranch = N.rows_scale_add(dout, None, ctx.scale, B, H, W, ws, shift, 1 if ctx.reverse else 0)
+        return (dout if ctx.needs_input_grad[0] else None), dbranch, None, None, None
+
+
+def residual_sd_add(res, branch, p: float = 0.0, training: bool = False, window_geom=None):
+    """res + stochastic_depth(branch, p, mode='row') in one pass (torchvision semantics: each sample's branch is dropped with
+    probability p and the survivors are scaled by 1 / (1 - p)).  With ``window_geom = (B, H, W, ws, shift)`` the branch is in
+    Swin window order [B*nW, ws*ws, C] and is un-partitioned / shifted back on the fly (res and the result are [B, H, W, C])."""
+    B = res.shape[0]
+    scale = None
+    if p > 0.0 and training:
+        keep = 1.0 - p
+        scale = torch.empty(B, dtype=torch.float32, device=res.device).bernoulli_(keep).div_(keep)
+    rows = res.numel() // (B * res.shape[-1])
+    geom = window_geom if window_geom is not None else (B, rows, 1, 1, (0, 0))
+    if _lowp(res) and res.shape[-1] % 8 == 0:
+        return _ResidualScaleAdd.apply(res, branch, scale, geom, window_geom is not None)
+    if window_geom is not None:
+        branch = window_reverse(branch, *window_geom)
+    if scale is not None:
+        branch = branch * scale.to(branch.dtype).view((B,) + (1,) * (branch.dim() - 1))
+    return res + branch
+
+
 def layer_norm(x, weight, bias, eps: float = 1e-5):
     if not _lowp(x) or x.shape[-1] % 8:
         return torch.nn.functional.layer_norm(x, (x.shape[-1],), weight, bias, eps)

@@ -60,6 +60,7 @@ _SIGS = {
     "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_window_shuffle": [c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_rows_scale_add": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_window_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i] + [c_ll] * 12 + [c_f, c_i, c_f, c_ull, c_p],
@@ -124,6 +125,14 @@ def set_window_attn_impl(impl: int) -> int:
     L.b2_window_attn_set_impl.argtypes = [ctypes.c_int]
     L.b2_window_attn_set_impl.restype = ctypes.c_int
     return L.b2_window_attn_set_impl(int(impl))
+
+
+def set_window_attn_grid(fwd_ctas_per_sm: int = 0, bwd_ctas_per_sm: int = 0) -> None:
+    """Tuning knob of the tensor-core window attention: CTAs per SM the grids are sized for (0 = occupancy query, the default)."""
+    L = lib()
+    L.b2_window_attn_set_grid.argtypes = [ctypes.c_int, ctypes.c_int]
+    L.b2_window_attn_set_grid.restype = None
+    L.b2_window_attn_set_grid(int(fwd_ctas_per_sm), int(bwd_ctas_per_sm))
 
 
 def set_gemm_pair_mode(mode: int) -> None:
@@ -1048,6 +1057,31 @@ def window_attn_bwd(qkv, bias, mask, out, dout, lse, heads: int, scale: float):
     _call("b2_window_attn_bwd", _p(qkv), _p(bias), _p(mask), _p(out), _p(dout.contiguous()), _p(lse), _p(dqkv), _p(dbias), Bw, nW, heads, T,
           C // heads, float(scale), _dt(qkv), _st())
     return dqkv, dbias
+
+
+def rows_scale_add(x, res, scale, B: int, H: int, W: int, ws: int, shift, mode: int):
+    """out = res + scale[sample] * map(x) over B * H * W rows of C elements (res / scale may be None: 0 / 1).
+    mode 0: map = identity (out has x's shape); 1: window partition of x (x [B, H, W, C] -> out [B*nW, ws*ws, C]);
+    2: window reverse (x [B*nW, ws*ws, C] -> out [B, H, W, C]).  scale: fp32 [B].  The stochastic-depth residual add with
+    Swin's window_reverse folded in (csrc/window_attn.cu: rows_scale_add_kernel); its backward is mode 1 <-> 2 without res."""
+    C = x.shape[-1]
+    sh, sw = int(shift[0]), int(shift[1])
+    oshape = tuple(x.shape) if mode == 0 else ((B * (H // ws) * (W // ws), ws * ws, C) if mode == 1 else (B, H, W, C))
+    if x.is_cuda and x.dtype in (torch.bfloat16, torch.float16) and C % 8 == 0:
+        x = x.contiguous()
+        res = res.contiguous() if res is not None else None
+        assert x.numel() == B * H * W * C and (res is None or (res.dtype == x.dtype and res.numel() == x.numel()))
+        assert scale is None or (scale.dtype == torch.float32 and scale.numel() == B and scale.is_contiguous())
+        out = torch.empty(oshape, dtype=x.dtype, device=x.device)
+        _call("b2_rows_scale_add", _p(x), _p(res), _p(scale), _p(out), B, H, W, C, ws if mode else 1, sh, sw, int(mode), _dt(x), _st())
+        return out
+    y = x if mode == 0 else window_shuffle(x, B, H, W, ws, (sh, sw), mode == 2)
+    y = y.reshape(B, -1).float()
+    if scale is not None:
+        y = y * scale.float().reshape(B, 1)
+    if res is not None:
+        y = y + res.reshape(B, -1).float()
+    return y.to(x.dtype).reshape(oshape)
 
 
 def window_shuffle(x, B: int, H: int, W: int, ws: int, shift, reverse: bool):

@@ -2,7 +2,7 @@
 //   mma16816<T>   = mma.sync.aligned.m16n8k16.row.col.f32.{bf16,f16}.{bf16,f16}.f32
 //   ldsm_x4       = ldmatrix.sync.aligned.m8n8.x4.shared.b16
 //   ldsm_x4_t     = ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16
-//   cp_async16 / cp_async_commit / cp_async_wait<N>   (copies happen immediately here)
+//   cp_async16 / cp_async4 / cp_async_commit / cp_async_wait<N>   (copies happen immediately here)
 // The fragment layouts are the ones of the PTX ISA tables: with g = lane / 4 and t = lane % 4,
 //   A (16 x 16, row):  a[i] at row g + 8 * ((i / 2) % 2), column 2 t + (i % 2) + 8 * (i / 4)            i = 0..7, two per register
 //   B (16 x 8,  col):  b[i] at row (k) 2 t + (i % 2) + 8 * (i / 2), column (n) g                        i = 0..3
@@ -63,6 +63,7 @@ inline void ldsm_x4(uint32_t r[4], const void* row_ptr) { ldsm_x4_impl(r, row_pt
 inline void ldsm_x4_t(uint32_t r[4], const void* row_ptr) { ldsm_x4_impl(r, row_ptr, true); }
 
 inline void cp_async16(void* smem_dst, const void* gmem_src) { std::memcpy(smem_dst, gmem_src, 16); }
+inline void cp_async4(void* smem_dst, const void* gmem_src) { std::memcpy(smem_dst, gmem_src, 4); }
 inline void cp_async_commit() {}
 template <int N> inline void cp_async_wait() {}
 

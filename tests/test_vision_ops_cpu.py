@@ -185,3 +185,116 @@ def test_sync_batchnorm_over_two_ranks_equals_full_batch():
     assert np.allclose(np.concatenate([outs[0][1], outs[1][1]]), dx.numpy(), atol=2e-5)
     assert np.allclose(outs[0][2] + outs[1][2], dw.numpy(), atol=2e-5) and np.allclose(outs[0][3] + outs[1][3], db.numpy(), atol=2e-5)
     assert np.allclose(outs[0][4], ref.running_mean.numpy(), atol=1e-6) and np.allclose(outs[1][5], ref.running_var.numpy(), atol=1e-5)
+
+
+def test_rows_scale_add_and_residual_sd_add_match_composition():
+    """ops.native.rows_scale_add (CPU restatement of csrc/window_attn.cu: rows_scale_add_kernel) and the autograd function around it
+    against roll / partition / broadcast-multiply / add composed from plain torch ops, forward and backward."""
+    from b200dist.ops import functional as OF
+    from b200dist.ops import native as N
+    torch.manual_seed(0)
+    B, H, W, C, ws, shift = 3, 14, 14, 16, 7, (3, 3)
+    res = torch.randn(B, H, W, C)
+    xw = torch.randn(B * 4, ws * ws, C)
+    scale = torch.tensor([0.0, 2.0, 1.0])
+    # mode 2: window reverse folded in
+    want = res + N.window_shuffle(xw, B, H, W, ws, shift, True) * scale.view(B, 1, 1, 1)
+    assert torch.allclose(N.rows_scale_add(xw, res, scale, B, H, W, ws, shift, 2), want, atol=1e-6)
+    # mode 1 is its adjoint: <rows_scale_add(x, mode 2), g> == <x, rows_scale_add(g, mode 1)>
+    g = torch.randn(B, H, W, C)
+    lhs = (N.rows_scale_add(xw, None, scale, B, H, W, ws, shift, 2) * g).sum()
+    rhs = (xw * N.rows_scale_add(g, None, scale, B, H, W, ws, shift, 1)).sum()
+    assert torch.allclose(lhs, rhs, rtol=1e-5)
+    # mode 0 on [B, rows, C]
+    x3, r3 = torch.randn(B, 10, C), torch.randn(B, 10, C)
+    assert torch.allclose(N.rows_scale_add(x3, r3, scale, B, 10, 1, 1, (0, 0), 0), r3 + x3 * scale.view(B, 1, 1), atol=1e-6)
+    assert torch.allclose(N.rows_scale_add(x3, r3, None, B, 10, 1, 1, (0, 0), 0), r3 + x3, atol=1e-6)
+    # autograd function in bf16 (the dtype that takes the fused path) against the same math composed in fp32
+    for geom in (None, (B, H, W, ws, shift)):
+        r16 = res.bfloat16().requires_grad_()
+        b16 = (xw if geom else torch.randn(B, H, W, C)).bfloat16().requires_grad_()
+        torch.manual_seed(5)
+        out = OF.residual_sd_add(r16, b16, 0.4, True, window_geom=geom)
+        torch.manual_seed(5)
+        sc = torch.empty(B).bernoulli_(0.6).div_(0.6)
+        rf, bf = r16.detach().float().requires_grad_(), b16.detach().float().requires_grad_()
+        ref = rf + (N.window_shuffle(bf, B, H, W, ws, shift, True) if geom else bf) * sc.view(B, 1, 1, 1)
+        assert torch.allclose(out.float(), ref, atol=3e-2, rtol=2e-2)
+        go = torch.randn_like(ref)
+        out.backward(go.bfloat16())
+        ref.backward(go.bfloat16().float())
+        assert torch.allclose(r16.grad.float(), rf.grad, atol=1e-6)
+        assert torch.allclose(b16.grad.float(), bf.grad, atol=3e-2, rtol=2e-2)
+    # eval / p = 0: a plain add
+    assert torch.equal(OF.residual_sd_add(res, g, 0.3, False), res + g)
+
+
+def test_layer_norm_residual_sums_both_gradients():
+    from b200dist.ops import functional as OF
+    torch.manual_seed(1)
+    x = torch.randn(4, 9, 32).bfloat16().requires_grad_()
+    w, b = torch.randn(32).bfloat16().requires_grad_(), torch.randn(32).bfloat16().requires_grad_()
+    y, skip = OF.layer_norm_residual(x, w, b)
+    g1, g2 = torch.randn_like(y), torch.randn_like(y)
+    (y * g1 + skip * g2).sum().backward()
+    xf, wf, bf = (t.detach().float().requires_grad_() for t in (x, w, b))
+    yr = torch.nn.functional.layer_norm(xf, (32,), wf, bf)
+    (yr * g1.float() + xf * g2.float()).sum().backward()
+    assert torch.allclose(y.float(), yr, atol=3e-2, rtol=2e-2)
+    assert torch.allclose(x.grad.float(), xf.grad, atol=6e-2, rtol=3e-2)
+    assert torch.allclose(w.grad.float(), wf.grad, atol=0.25, rtol=3e-2) and torch.allclose(b.grad.float(), bf.grad, atol=0.1, rtol=3e-2)
+    # only the skip output used: the gradient passes straight through
+    x2 = torch.randn(2, 3, 16).bfloat16().requires_grad_()
+    _, s2 = OF.layer_norm_residual(x2, torch.ones(16).bfloat16(), torch.zeros(16).bfloat16())
+    s2.sum().backward()
+    assert torch.equal(x2.grad, torch.ones_like(x2))
+
+
+def test_swin_bias_gather_and_cached_mask_match_torchvision_expressions():
+    from b200dist.models import swin
+    torch.manual_seed(2)
+    ws, heads = 7, 3
+    table = torch.randn((2 * ws - 1) ** 2, heads, requires_grad=True)
+    index = swin._relative_position_index(ws)
+    got = swin._BiasGather.apply(table, index, ws * ws)
+    t2 = table.detach().clone().requires_grad_()
+    ref = t2[index].view(ws * ws, ws * ws, -1).permute(2, 0, 1)
+    assert torch.equal(got, ref)
+    g = torch.randn_like(ref)
+    got.backward(g)
+    ref.backward(g)
+    assert torch.allclose(table.grad, t2.grad, atol=1e-5)
+    # the cached mask against torchvision's construction
+    pH, pW, shift = 14, 21, (3, 3)
+    m = swin.shift_window_mask(pH, pW, ws, shift, torch.device("cpu"))
+    assert swin.shift_window_mask(pH, pW, ws, shift, torch.device("cpu")) is m
+    am = torch.zeros((pH, pW))
+    c = 0
+    for h in ((0, -ws), (-ws, -shift[0]), (-shift[0], None)):
+        for w in ((0, -ws), (-ws, -shift[1]), (-shift[1], None)):
+            am[h[0]:h[1], w[0]:w[1]] = c
+            c += 1
+    am = am.view(pH // ws, ws, pW // ws, ws).permute(0, 2, 1, 3).reshape(-1, ws * ws)
+    am = am.unsqueeze(1) - am.unsqueeze(2)
+    am = am.masked_fill(am != 0, -100.0).masked_fill(am == 0, 0.0)
+    assert torch.equal(m, am)
+
+
+def test_swin_block_training_step_matches_torchvision_gradients():
+    """train mode, stochastic depth off (its draws are not comparable): the restructured block (skip connection through the norm
+    function, residual add fused with window_reverse) gives torchvision's loss and gradients in fp32"""
+    tv = pytest.importorskip("torchvision")
+    from b200dist.models import swin
+    torch.manual_seed(3)
+    m = swin.SwinTransformer(4, 32, (2, 2), (1, 2), 7, 0.0, 5).train()
+    ref = tv.models.swin_transformer.SwinTransformer([4, 4], 32, [2, 2], [1, 2], [7, 7], stochastic_depth_prob=0.0, num_classes=5).train()
+    ref.load_state_dict(m.state_dict())
+    x = torch.randn(2, 3, 56, 56)
+    y = torch.tensor([1, 3])
+    l1 = torch.nn.functional.cross_entropy(m(x), y)
+    l2 = torch.nn.functional.cross_entropy(ref(x), y)
+    assert torch.allclose(l1, l2, atol=1e-5)
+    l1.backward(); l2.backward()
+    gr = dict(ref.named_parameters())
+    for n, p in m.named_parameters():
+        assert torch.allclose(p.grad, gr[n].grad, atol=2e-4, rtol=1e-3), n
