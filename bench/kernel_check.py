@@ -385,6 +385,25 @@ def _check_wattn_rest(quick):
         report(f"window partition B{B} {H}x{W} C{C} shift{sh}", xw, N.window_shuffle(cpu(x), B, H, W, 7, sh, False), 0.0)
         back = N.window_shuffle(xw, B, H, W, 7, sh, True)
         report(f"window reverse  B{B} {H}x{W} C{C} shift{sh} (round trip)", back, x, 0.0)
+    # 4 x 4 patches as GEMM rows (patch-embedding convolution as one GEMM) against view / permute / reshape
+    for (B, C, H, W, dt) in [(2, 3, 32, 48, torch.bfloat16), (3, 5, 8, 4, torch.float16), (8, 3, 224, 224, torch.bfloat16)]:
+        x = torch.randn(B, C, H, W, device=dev, dtype=dt)
+        report(f"patchify4 B{B} C{C} {H}x{W}", N.patchify(x, 4), N.patchify(cpu(x), 4), 0.0)
+    # LayerNorm writing its rows through a permutation (Swin: norm + cyclic shift + window partition in one pass) and its backward
+    for (B, H, W, C, sh) in [(2, 14, 14, 128, (3, 3)), (3, 28, 56, 64, (3, 0)), (2, 7, 7, 1024, (0, 0))]:
+        from b200dist.ops import functional as OF
+        rm = OF.window_row_map(B, H, W, 7, sh, torch.device(dev))
+        x = torch.randn(B, H, W, C, device=dev, dtype=torch.bfloat16)
+        g, b = torch.randn(C, device=dev, dtype=torch.bfloat16), torch.randn(C, device=dev, dtype=torch.bfloat16)
+        y, mean, rstd = N.norm_fwd(x, g, b, 1e-5, False, row_map=rm)
+        yr, meanr, rstdr = N.norm_fwd(cpu(x), cpu(g), cpu(b), 1e-5, False, row_map=cpu(rm))
+        report(f"norm fwd + window row map B{B} {H}x{W} C{C} shift{sh}", y, yr, 2e-2)
+        dy, dres = torch.randn_like(y), torch.randn_like(x)
+        dx, dg, db = N.norm_bwd(dy, x, g, mean, rstd, False, dres=dres, row_map=rm)
+        dxr, dgr, dbr = N.norm_bwd(cpu(dy), cpu(x), cpu(g), meanr, rstdr, False, dres=cpu(dres), row_map=cpu(rm))
+        report(f"norm bwd + window row map dx B{B} {H}x{W} C{C}", dx, dxr, 3e-2)
+        report(f"norm bwd + window row map dgamma B{B} {H}x{W} C{C}", dg, dgr, 2e-3)
+        report(f"norm bwd + window row map dbeta B{B} {H}x{W} C{C}", db, dbr, 2e-3)
     # residual add + per-sample scale (stochastic depth), identity map and with the window maps folded in
     for (B, H, W, C, sh, dt) in [(3, 14, 14, 64, (3, 3), torch.bfloat16), (2, 28, 56, 128, (3, 0), torch.float16), (5, 7, 7, 32, (0, 0), torch.bfloat16)]:
         res = torch.randn(B, H, W, C, device=dev, dtype=dt)

@@ -60,7 +60,8 @@ B2_DEVICE float team_sum(float v, float* red) {
 template <typename T, int TEAM, bool RMS>
 __global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM)
 norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* __restrict__ beta, T* __restrict__ y,
-                float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int H, float eps) {
+                float* __restrict__ mean_out, float* __restrict__ rstd_out, int rows, int H, float eps,
+                const int* __restrict__ row_map /* optional: y row of x row r is row_map[r] (a permutation) */) {
   __shared__ float red[8];
   constexpr int ROWS_PER_CTA = TEAM == 32 ? CTA_THREADS / 32 : 1;
   const int tid = TEAM == 32 ? (threadIdx.x & 31) : threadIdx.x;
@@ -96,7 +97,7 @@ norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ gamma, const T* _
       if (!RMS && mean_out) mean_out[row] = mean;
       if (rstd_out) rstd_out[row] = rstd;
     }
-    T* yr = y + static_cast<size_t>(row) * H;
+    T* yr = y + static_cast<size_t>(row_map ? row_map[row] : row) * H;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       int vi = tid + i * TEAM;
@@ -120,7 +121,8 @@ __global__ void __launch_bounds__(TEAM == 32 ? CTA_THREADS : TEAM, (TEAM == 32 &
 norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __restrict__ gamma,
                 const float* __restrict__ mean_in, const float* __restrict__ rstd_in,
                 const T* __restrict__ dres /* optional: dx = dres + d(norm) (residual branch gradient) */,
-                T* __restrict__ dx, float* __restrict__ ws /* [gridDim.x, 2, H] */, int rows, int H) {
+                T* __restrict__ dx, float* __restrict__ ws /* [gridDim.x, 2, H] */, int rows, int H,
+                const int* __restrict__ row_map /* optional: the dy row of x row r is row_map[r] (forward wrote y through it) */) {
   extern __shared__ float sm[];  // TEAM == 32: [CTA_THREADS/32][2][H]
   __shared__ float red[8];
   constexpr int ROWS_PER_CTA = TEAM == 32 ? CTA_THREADS / 32 : 1;
@@ -137,7 +139,7 @@ norm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ x, const T* __re
   const int first = blockIdx.x * ROWS_PER_CTA + sub;
   for (int row = first; row < rows; row += gridDim.x * ROWS_PER_CTA) {
     const T* xr = x + static_cast<size_t>(row) * H;
-    const T* dyr = dy + static_cast<size_t>(row) * H;
+    const T* dyr = dy + static_cast<size_t>(row_map ? row_map[row] : row) * H;
     const float mean = RMS ? 0.f : mean_in[row];
     const float rstd = rstd_in[row];
     // the row stays in registers in its packed 16-bit form (half the registers of fp32 copies -> more CTAs per SM,
@@ -258,17 +260,17 @@ norm_bwd_fold_kernel(const float* __restrict__ ws, int nparts, int H, float* __r
 
 template <typename T, bool RMS>
 int fwd_dispatch(const void* x, const void* g, const void* b, void* y, float* mean, float* rstd, int rows, int H,
-                 float eps, cudaStream_t st) {
+                 float eps, const int* row_map, cudaStream_t st) {
   if (H <= 1024) {
     int grid = (rows + 3) / 4;
     int cap = b2host::num_sms() * 16;
     if (grid > cap) grid = cap;
-    norm_fwd_kernel<T, 32, RMS><<<grid, CTA_THREADS, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps);
+    norm_fwd_kernel<T, 32, RMS><<<grid, CTA_THREADS, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps, row_map);
   } else if (H <= 8192) {
     int grid = rows;
     int cap = b2host::num_sms() * 8;
     if (grid > cap) grid = cap;
-    norm_fwd_kernel<T, 256, RMS><<<grid, 256, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps);
+    norm_fwd_kernel<T, 256, RMS><<<grid, 256, 0, st>>>((const T*)x, (const T*)g, (const T*)b, (T*)y, mean, rstd, rows, H, eps, row_map);
   } else { b2host::set_error("norm: hidden size %d > 8192 unsupported", H); return -1; }
   return 0;
 }
@@ -281,15 +283,15 @@ int bwd_parts(int rows, int H) {
 
 template <typename T, bool RMS>
 int bwd_dispatch(const void* dy, const void* x, const void* g, const float* mean, const float* rstd, const void* dres,
-                 void* dx, float* ws, int grid, int rows, int H, cudaStream_t st) {
+                 void* dx, float* ws, int grid, int rows, int H, const int* row_map, cudaStream_t st) {
   if (H <= 1024) {
     size_t smem = static_cast<size_t>(CTA_THREADS / 32) * 2 * H * sizeof(float);
-#define B2_NB(NV_) norm_bwd_kernel<T, 32, RMS, NV_><<<grid, CTA_THREADS, smem, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H)
+#define B2_NB(NV_) norm_bwd_kernel<T, 32, RMS, NV_><<<grid, CTA_THREADS, smem, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H, row_map)
     const int nv = (H + 255) / 256;
     if (nv == 1) B2_NB(1); else if (nv == 2) B2_NB(2); else if (nv == 3) B2_NB(3); else B2_NB(4);
 #undef B2_NB
   } else if (H <= 8192) {
-#define B2_NB(NV_) norm_bwd_kernel<T, 256, RMS, NV_><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H)
+#define B2_NB(NV_) norm_bwd_kernel<T, 256, RMS, NV_><<<grid, 256, 0, st>>>((const T*)dy, (const T*)x, (const T*)g, mean, rstd, (const T*)dres, (T*)dx, ws, rows, H, row_map)
     const int nv = (H + 2047) / 2048;
     if (nv == 1) B2_NB(1); else if (nv == 2) B2_NB(2); else if (nv == 3) B2_NB(3); else B2_NB(4);
 #undef B2_NB
@@ -307,16 +309,21 @@ int check(const char* what) {
 
 extern "C" int b2_norm_bwd_num_parts(int rows, int H) { return bwd_parts(rows, H); }
 
-extern "C" int b2_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
-                                int rows, int H, float eps, int dtype, int rms, void* stream) {
+extern "C" int b2_layernorm_fwd_map(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                                    int rows, int H, float eps, const int* row_map, int dtype, int rms, void* stream) {
   if (H % 8) { b2host::set_error("norm: hidden size must be a multiple of 8"); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int r;
-  if (dtype == B2_DTYPE_BF16) r = rms ? fwd_dispatch<__nv_bfloat16, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, st)
-                                      : fwd_dispatch<__nv_bfloat16, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, st);
-  else r = rms ? fwd_dispatch<__half, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, st)
-               : fwd_dispatch<__half, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, st);
+  if (dtype == B2_DTYPE_BF16) r = rms ? fwd_dispatch<__nv_bfloat16, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, row_map, st)
+                                      : fwd_dispatch<__nv_bfloat16, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, row_map, st);
+  else r = rms ? fwd_dispatch<__half, true>(x, gamma, beta, y, mean, rstd, rows, H, eps, row_map, st)
+               : fwd_dispatch<__half, false>(x, gamma, beta, y, mean, rstd, rows, H, eps, row_map, st);
   return r ? r : check("layernorm_fwd");
+}
+
+extern "C" int b2_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                                int rows, int H, float eps, int dtype, int rms, void* stream) {
+  return b2_layernorm_fwd_map(x, gamma, beta, y, mean, rstd, rows, H, eps, nullptr, dtype, rms, stream);
 }
 
 // ws: fp32 workspace of b2_norm_bwd_num_parts(rows, H) * 2 * H elements
@@ -330,14 +337,22 @@ extern "C" int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma
 extern "C" int b2_layernorm_bwd_res(const void* dy, const void* x, const void* gamma, const float* mean,
                                     const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta, float* ws,
                                     int rows, int H, int dtype, int rms, int accumulate, void* stream) {
+  return b2_layernorm_bwd_map(dy, x, gamma, mean, rstd, dres, dx, dgamma, dbeta, ws, rows, H, nullptr, dtype, rms, accumulate, stream);
+}
+
+// same, for a forward that wrote its rows through `row_map` (b2_layernorm_fwd_map): dy is read through the same permutation, so a
+// row shuffle that follows the norm (Swin: cyclic shift + window partition) costs no pass of its own in either direction
+extern "C" int b2_layernorm_bwd_map(const void* dy, const void* x, const void* gamma, const float* mean,
+                                    const float* rstd, const void* dres, void* dx, float* dgamma, float* dbeta, float* ws,
+                                    int rows, int H, const int* row_map, int dtype, int rms, int accumulate, void* stream) {
   if (H % 8) { b2host::set_error("norm: hidden size must be a multiple of 8"); return -1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int grid = bwd_parts(rows, H);
   int r;
-  if (dtype == B2_DTYPE_BF16) r = rms ? bwd_dispatch<__nv_bfloat16, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st)
-                                      : bwd_dispatch<__nv_bfloat16, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st);
-  else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st)
-               : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, st);
+  if (dtype == B2_DTYPE_BF16) r = rms ? bwd_dispatch<__nv_bfloat16, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, row_map, st)
+                                      : bwd_dispatch<__nv_bfloat16, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, row_map, st);
+  else r = rms ? bwd_dispatch<__half, true>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, row_map, st)
+               : bwd_dispatch<__half, false>(dy, x, gamma, mean, rstd, dres, dx, ws, grid, rows, H, row_map, st);
   if (r) return r;
   norm_bwd_fold_kernel<<<(2 * H + 31) / 32, 1024, 0, st>>>(ws, grid, H, dgamma, rms ? nullptr : dbeta, accumulate);
   return check("layernorm_bwd");

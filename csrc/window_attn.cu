@@ -398,6 +398,41 @@ extern "C" int b2_rows_scale_add(const void* x, const void* res, const float* sc
   return wcheck("rows_scale_add");
 }
 
+// ------------------------------------------------------------------------------------------
+// non-overlapping 4 x 4 patches of an NCHW image as GEMM rows (the patch-embedding convolution, kernel = stride = 4, as one GEMM):
+//   out[(b, py, px), (c, i, j)] = x[b, c, 4 py + i, 4 px + j]        16-bit elements, one 8-byte vector (j = 0..3) per thread
+// reads are fully coalesced along the image row; the 96-byte output rows fill up in L2 before they are written back.
+// replaces: view / permute / contiguous (ATen's generic strided copy, one 2-byte element per thread with 6-D index math)
+// ------------------------------------------------------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256)
+patchify4_kernel(const uint2* __restrict__ x, uint2* __restrict__ out, int B, int C, int H, int W) {
+  const int pw = W >> 2, ph = H >> 2;
+  const long long total = static_cast<long long>(B) * C * H * pw;
+  for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+       idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+    long long t = idx;
+    const int px = static_cast<int>(t % pw); t /= pw;
+    const int y = static_cast<int>(t % H); t /= H;
+    const int c = static_cast<int>(t % C); t /= C;                     // t = b
+    const long long row = (t * ph + (y >> 2)) * pw + px;
+    out[(row * C + c) * 4 + (y & 3)] = x[idx];
+  }
+}
+}  // namespace
+
+// x [B, C, H, W] -> out [B * (H/4) * (W/4), C * 16]; 16-bit elements, H and W multiples of 4, both 8-byte aligned
+extern "C" int b2_patchify4(const void* x, void* out, int B, int C, int H, int W, void* stream) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || (H % 4) || (W % 4)) { b2host::set_error("patchify4: H and W must be multiples of 4"); return -1; }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const long long total = static_cast<long long>(B) * C * H * (W / 4);
+  long long blocks = (total + 255) / 256;
+  const long long cap = static_cast<long long>(b2host::num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
+  patchify4_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(static_cast<const uint2*>(x), static_cast<uint2*>(out), B, C, H, W);
+  return wcheck("patchify4");
+}
+
 // in / out: 16-bit elements, C % 8 == 0, H and W multiples of ws, 0 <= shift < ws
 extern "C" int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int ws, int shift_h, int shift_w, int reverse,
                                  void* stream) {

@@ -86,6 +86,9 @@ int b2_window_shuffle(const void* in, void* out, int B, int H, int W, int C, int
  * with stochastic depth, with Swin's window_reverse folded in; the backward is the same kernel with the inverse map. */
 int b2_rows_scale_add(const void* x, const void* res, const float* scale, void* out, int B, int H, int W, int C, int ws,
                       int shift_h, int shift_w, int map, int dtype, void* stream);
+/* x [B, C, H, W] -> out [B * (H/4) * (W/4), C * 16]: the non-overlapping 4 x 4 patches as GEMM rows (patch-embedding convolution with
+ * kernel = stride = 4 as one GEMM); 16-bit elements, H and W multiples of 4.  replaces view / permute / contiguous. */
+int b2_patchify4(const void* x, void* out, int B, int C, int H, int W, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * LayerNorm / RMSNorm (rms != 0).  x,y,gamma,beta: [rows,H] / [H] in `dtype`; mean,rstd fp32 [rows].
@@ -103,6 +106,14 @@ int b2_layernorm_bwd(const void* dy, const void* x, const void* gamma, const flo
 int b2_layernorm_bwd_res(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
                          const void* dres, void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H, int dtype,
                          int rms, int accumulate, void* stream);
+/* the same pair with a row permutation folded in: the forward writes the normalised row r to y[row_map[r]], the backward reads
+ * the gradient of row r from dy[row_map[r]] (row_map: int32 [rows], a permutation, or NULL).  A row shuffle that follows the
+ * norm - Swin's cyclic shift + window partition - then costs no pass of its own in either direction. */
+int b2_layernorm_fwd_map(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd,
+                         int rows, int H, float eps, const int* row_map, int dtype, int rms, void* stream);
+int b2_layernorm_bwd_map(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd,
+                         const void* dres, void* dx, float* dgamma, float* dbeta, float* ws, int rows, int H,
+                         const int* row_map, int dtype, int rms, int accumulate, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused elementwise ops.  replaces: Megatron jit bias_gelu / bias_dropout_add (K16, K17), HF SwiGLU

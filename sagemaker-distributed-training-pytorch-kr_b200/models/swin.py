@@ -118,6 +118,23 @@ class ShiftedWindowAttention(nn.Module):
         """fp32 [1, heads, T, T]"""
         return _BiasGather.apply(self.relative_position_bias_table, self.relative_position_index, self.ws * self.ws).unsqueeze(0)
 
+    def _shift_for(self, pH: int, pW: int):
+        return [self.shift if self.ws < pH else 0, self.shift if self.ws < pW else 0]
+
+    def _windows(self, xw, pH: int, pW: int, shift):
+        """xw: [B*nW, ws*ws, C] (normalised, shifted, partitioned) -> projected attention output in the same window order"""
+        C = xw.shape[-1]
+        qkv = self.qkv(xw)                                  # [B*nW, ws*ws, 3C], last dim = [3][heads][head_dim]
+        mask = shift_window_mask(pH, pW, self.ws, shift, xw.device) if sum(shift) > 0 else None      # [nW, T, T] fp32, cached
+        # scores + relative-position bias + shift mask + softmax + PV in one fused kernel (ops/functional.window_attention)
+        a = OF.window_attention(qkv, self._bias()[0], mask, self.heads, (C // self.heads) ** -0.5)
+        return self.proj(a)
+
+    def forward_windows(self, xw, B: int, H: int, W: int, shift, skip, sd_prob: float = 0.0):
+        """The block's whole attention branch for an input that is already in window order (the norm wrote it there,
+        ops.functional.layer_norm_partition): skip + stochastic_depth(window_reverse(attention(xw))), the way back fused into the add."""
+        return OF.residual_sd_add(skip, self._windows(xw, H, W, shift), sd_prob, self.training, window_geom=(B, H, W, self.ws, shift))
+
     def forward(self, x, skip=None, sd_prob: float = 0.0):
         """x: [B, H, W, C] (already normalised).  With ``skip`` the block's residual add (skip + stochastic_depth(attention(x))) happens
         here, fused with the un-partition / shift back of the attention output."""
@@ -126,14 +143,9 @@ class ShiftedWindowAttention(nn.Module):
         pad_r, pad_b = (ws - W % ws) % ws, (ws - H % ws) % ws
         x = F.pad(x, (0, 0, 0, pad_r, 0, pad_b))
         _, pH, pW, _ = x.shape
-        shift = [self.shift if ws < pH else 0, self.shift if ws < pW else 0]
-        nW = (pH // ws) * (pW // ws)
+        shift = self._shift_for(pH, pW)
         x = OF.window_partition(x, ws, shift)               # cyclic shift + partition in one pass: [B*nW, ws*ws, C]
-        qkv = self.qkv(x)                                   # [B*nW, ws*ws, 3C], last dim = [3][heads][head_dim]
-        mask = shift_window_mask(pH, pW, ws, shift, x.device) if sum(shift) > 0 else None      # [nW, T, T] fp32, cached
-        # scores + relative-position bias + shift mask + softmax + PV in one fused kernel (ops/functional.window_attention)
-        x = OF.window_attention(qkv, self._bias()[0], mask, self.heads, (C // self.heads) ** -0.5)
-        x = self.proj(x)
+        x = self._windows(x, pH, pW, shift)
         if skip is not None and pH == H and pW == W:
             # skip + stochastic_depth(window_reverse(x)) in one pass
             return OF.residual_sd_add(skip, x, sd_prob, self.training, window_geom=(B, pH, pW, ws, shift))
@@ -176,8 +188,16 @@ class SwinBlock(nn.Module):
         self.norm2, self.mlp, self.sd = LayerNorm(dim), MLP(dim, 4 * dim), sd_prob
 
     def forward(self, x):
-        h, skip = self.norm1.with_skip(x)
-        x = self.attn(h, skip=skip, sd_prob=self.sd)                         # skip + stochastic_depth(attn(norm1(x)))
+        B, H, W, _ = x.shape
+        ws = self.attn.ws
+        if H % ws == 0 and W % ws == 0:
+            # norm1 writes its rows straight into shifted-window order; the way back is folded into the residual add
+            shift = self.attn._shift_for(H, W)
+            xw, skip = OF.layer_norm_partition(x, self.norm1.weight, self.norm1.bias, self.norm1.eps, ws, shift)
+            x = self.attn.forward_windows(xw, B, H, W, shift, skip, self.sd)   # skip + stochastic_depth(attn(norm1(x)))
+        else:
+            h, skip = self.norm1.with_skip(x)
+            x = self.attn(h, skip=skip, sd_prob=self.sd)
         h, skip = self.norm2.with_skip(x)
         return OF.residual_sd_add(skip, self.mlp(h), self.sd, self.training)   # skip + stochastic_depth(mlp(norm2(x)))
 
@@ -207,9 +227,9 @@ class PatchEmbed(nn.Module):
     def forward(self, x):
         conv, norm, p = getattr(self, "0"), getattr(self, "2"), self.patch
         B, C, H, W = x.shape
-        if x.dtype in (torch.bfloat16, torch.float16) and H % p == 0 and W % p == 0:
-            cols = x.view(B, C, H // p, p, W // p, p).permute(0, 2, 4, 1, 3, 5).reshape(B * (H // p) * (W // p), C * p * p)
-            y = OF.linear(cols.contiguous(), conv.weight.view(conv.out_channels, -1), conv.bias).view(B, H // p, W // p, -1)
+        if x.dtype in (torch.bfloat16, torch.float16) and H % p == 0 and W % p == 0 and not x.requires_grad:
+            cols = N.patchify(x, p)                      # [B * H/p * W/p, C*p*p]: the input images need no gradient
+            y = OF.linear(cols, conv.weight.view(conv.out_channels, -1), conv.bias).view(B, H // p, W // p, -1)
         else:
             y = conv(x).permute(0, 2, 3, 1)
         return norm(y)

@@ -193,6 +193,59 @@ def layer_norm_residual(x, weight, bias, eps: float = 1e-5):
     return _NormResidual.apply(x, weight, bias, eps)
 
 
+_ROW_MAPS = {}
+
+
+def window_row_map(B: int, H: int, W: int, ws: int, shift, device) -> torch.Tensor:
+    """int32 [B*H*W]: position, in shifted-window order, of image-order row r (the inverse of the gather window_partition does).
+    Geometry only, so it is built once per (geometry, device)."""
+    key = (B, H, W, ws, int(shift[0]), int(shift[1]), str(device))
+    m = _ROW_MAPS.get(key)
+    if m is None:
+        ids = torch.arange(B * H * W, dtype=torch.int32).view(B, H, W, 1)
+        src = N.window_shuffle(ids, B, H, W, ws, shift, False).reshape(-1)        # image row that lands at window position p
+        m = torch.empty_like(src)
+        m[src.long()] = torch.arange(src.numel(), dtype=torch.int32)
+        m = m.contiguous().to(device)
+        _ROW_MAPS[key] = m
+    return m
+
+
+class _NormPartitionResidual(torch.autograd.Function):
+    """(window_partition(LN(x)), x): the norm kernel writes each normalised row at its place in shifted-window order and its backward
+    reads dy through the same permutation (b2_layernorm_fwd_map / _bwd_map), so neither direction has a shuffle pass; the second
+    output is the skip connection (see _NormResidual)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, eps, row_map, ws):
+        xc = x.contiguous()
+        B, H, W, C = xc.shape
+        y, mean, rstd = N.norm_fwd(xc, w, b, eps, False, row_map=row_map)
+        ctx.save_for_backward(xc, w, mean, rstd, row_map)
+        ctx.params = (w, b)
+        ctx.set_materialize_grads(False)
+        return y.view(B * (H // ws) * (W // ws), ws * ws, C), xc.view_as(xc)
+
+    @staticmethod
+    def backward(ctx, dy, dskip):
+        x, w, mean, rstd, row_map = ctx.saved_tensors
+        if dy is None:
+            return dskip, None, None, None, None, None
+        dx, dg, db = N.norm_bwd(dy.contiguous(), x, w, mean, rstd, False, dres=dskip.contiguous() if dskip is not None else None,
+                                row_map=row_map)
+        return dx, _vgrad(ctx.params[0], dg), _vgrad(ctx.params[1], db), None, None, None
+
+
+def layer_norm_partition(x, weight, bias, eps: float, ws: int, shift):
+    """x [B, H, W, C] (H, W multiples of ws) -> (window_partition(layer_norm(x), ws, shift) as [B*nW, ws*ws, C], x' == x for the skip
+    connection).  16-bit inputs take the fused kernel pair; everything else composes the two ops."""
+    B, H, W, C = x.shape
+    if not _lowp(x) or C % 8:
+        y = torch.nn.functional.layer_norm(x, (C,), weight, bias, eps)
+        return window_partition(y, ws, shift), x
+    return _NormPartitionResidual.apply(x, weight, bias, eps, window_row_map(B, H, W, ws, shift, x.device), ws)
+
+
 class _ResidualScaleAdd(torch.autograd.Function):
     """out = res + scale[sample] * map(branch); map = identity or Swin's window_reverse (geom = (B, H, W, ws, shift))."""
 

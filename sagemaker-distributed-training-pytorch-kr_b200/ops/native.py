@@ -37,6 +37,8 @@ _SIGS = {
     "b2_layernorm_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_cast_rows_from_fp32": [c_p, c_ll, c_p, c_ll, c_i, c_i, c_p],
     "b2_layernorm_bwd_res": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_layernorm_fwd_map": [c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_f, c_p, c_i, c_i, c_p],
+    "b2_layernorm_bwd_map": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i, c_i, c_p, c_i, c_i, c_i, c_p],
     "b2_bias_dropout_add": [c_p, c_p, c_p, c_p, c_ll, c_i, c_f, c_ull, c_i, c_p],
     "b2_dropout_bwd": [c_p, c_p, c_ll, c_f, c_ull, c_i, c_p],
     "b2_bias_act_fwd": [c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_p],
@@ -60,6 +62,7 @@ _SIGS = {
     "b2_embedding_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_embedding_bwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_ll, c_ll, c_i, c_p],
     "b2_window_shuffle": [c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
+    "b2_patchify4": [c_p, c_p, c_i, c_i, c_i, c_i, c_p],
     "b2_rows_scale_add": [c_p, c_p, c_p, c_p, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_i, c_p],
     "b2_window_attn_fwd": [c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
     "b2_window_attn_bwd": [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_ll, c_i, c_i, c_i, c_i, c_f, c_i, c_p],
@@ -279,12 +282,27 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
 # LayerNorm / RMSNorm
 # =============================================================================================
 def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor], eps: float, rms: bool = False,
-             out: Optional[torch.Tensor] = None):
+             out: Optional[torch.Tensor] = None, row_map: Optional[torch.Tensor] = None):
     """Returns (y, mean, rstd); mean is None for RMSNorm.  ``out`` (CUDA only): a contiguous [rows, H] buffer that receives y
-    (e.g. the symmetric shard buffer the fused all-gather->GEMM reads, which saves its staging copy)."""
+    (e.g. the symmetric shard buffer the fused all-gather->GEMM reads, which saves its staging copy).  ``row_map`` (int32 [rows], a
+    permutation): the normalised row r is written to y[row_map[r]] (y is then returned as [rows, H])."""
     H = x.shape[-1]
     x2 = x.reshape(-1, H)
     rows = x2.shape[0]
+    if row_map is not None:
+        assert row_map.dtype == torch.int32 and row_map.numel() == rows and row_map.is_contiguous() and out is None
+        if not x.is_cuda:
+            y, mean, rstd = norm_fwd(x2, gamma, beta, eps, rms)
+            yp = torch.empty_like(y)
+            yp[row_map.long()] = y
+            return yp, mean, rstd
+        assert x2.is_contiguous()
+        y = torch.empty_like(x2)
+        mean = None if rms else torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        _call("b2_layernorm_fwd_map", _p(x2), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), rows, H, float(eps), _p(row_map), _dt(x),
+              int(rms), _st())
+        return y, mean, rstd
     if not x.is_cuda:
         xf = x2.float()
         if rms:
@@ -310,12 +328,16 @@ def norm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: Optional[torch.Tensor],
 
 
 def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch.Tensor] = None,
-             dbeta: Optional[torch.Tensor] = None, accumulate: bool = False, dres: Optional[torch.Tensor] = None):
+             dbeta: Optional[torch.Tensor] = None, accumulate: bool = False, dres: Optional[torch.Tensor] = None,
+             row_map: Optional[torch.Tensor] = None):
     """Returns (dx, dgamma_fp32, dbeta_fp32).  With ``accumulate`` the fp32 grads are added in place (main_grad);
-    ``dres`` is the gradient arriving through the residual branch: dx = dres + d(norm)/dx in the same pass."""
+    ``dres`` is the gradient arriving through the residual branch: dx = dres + d(norm)/dx in the same pass;
+    ``row_map``: the forward wrote row r to y[row_map[r]], so the gradient of row r is dy[row_map[r]]."""
     H = x.shape[-1]
     x2, dy2 = x.reshape(-1, H), dy.reshape(-1, H)
     rows = x2.shape[0]
+    if row_map is not None and not x.is_cuda:
+        dy2, row_map = dy2[row_map.long()], None
     if dgamma is None:
         dgamma = torch.empty(H, dtype=torch.float32, device=x.device)
         accumulate = False
@@ -351,8 +373,13 @@ def norm_bwd(dy, x, gamma, mean, rstd, rms: bool = False, dgamma: Optional[torch
     if dres is not None:
         dres = dres.reshape(-1, H)
         assert dres.is_contiguous() and dres.dtype == x.dtype
-    _call("b2_layernorm_bwd_res", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
-          _p(ws), rows, H, _dt(x), int(rms), int(accumulate), _st())
+    if row_map is not None:
+        assert row_map.dtype == torch.int32 and row_map.numel() == rows and row_map.is_contiguous()
+        _call("b2_layernorm_bwd_map", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
+              _p(ws), rows, H, _p(row_map), _dt(x), int(rms), int(accumulate), _st())
+    else:
+        _call("b2_layernorm_bwd_res", _p(dy2), _p(x2), _p(gamma), _p(mean), _p(rstd), _p(dres), _p(dx), _p(dgamma), _p(dbeta),
+              _p(ws), rows, H, _dt(x), int(rms), int(accumulate), _st())
     return dx.view_as(x), dgamma, dbeta
 
 
@@ -1057,6 +1084,18 @@ def window_attn_bwd(qkv, bias, mask, out, dout, lse, heads: int, scale: float):
     _call("b2_window_attn_bwd", _p(qkv), _p(bias), _p(mask), _p(out), _p(dout.contiguous()), _p(lse), _p(dqkv), _p(dbias), Bw, nW, heads, T,
           C // heads, float(scale), _dt(qkv), _st())
     return dqkv, dbias
+
+
+def patchify(x, p: int):
+    """x [B, C, H, W] -> [B * (H/p) * (W/p), C * p * p]: non-overlapping p x p patches as GEMM rows, columns ordered (c, i, j) like a
+    Conv2d weight viewed [out, C*p*p].  p == 4 with 16-bit elements on the GPU is one coalesced pass (csrc/window_attn.cu: patchify4)."""
+    B, C, H, W = x.shape
+    if x.is_cuda and p == 4 and x.dtype in (torch.bfloat16, torch.float16) and H % 4 == 0 and W % 4 == 0:
+        x = x.contiguous()
+        out = torch.empty((B * (H // 4) * (W // 4), C * 16), dtype=x.dtype, device=x.device)
+        _call("b2_patchify4", _p(x), _p(out), B, C, H, W, _st())
+        return out
+    return x.view(B, C, H // p, p, W // p, p).permute(0, 2, 4, 1, 3, 5).reshape(B * (H // p) * (W // p), C * p * p).contiguous()
 
 
 def rows_scale_add(x, res, scale, B: int, H: int, W: int, ws: int, shift, mode: int):

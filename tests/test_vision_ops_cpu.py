@@ -298,3 +298,41 @@ def test_swin_block_training_step_matches_torchvision_gradients():
     gr = dict(ref.named_parameters())
     for n, p in m.named_parameters():
         assert torch.allclose(p.grad, gr[n].grad, atol=2e-4, rtol=1e-3), n
+
+
+def test_layer_norm_partition_matches_norm_then_partition():
+    """the norm that writes its rows in shifted-window order (row map folded into the kernel pair; CPU: the restatement) against
+    layer_norm followed by window_partition, forward and backward including the skip output"""
+    from b200dist.ops import functional as OF
+    torch.manual_seed(6)
+    B, H, W, C, ws = 2, 14, 21, 16, 7
+    for shift in ((0, 0), (3, 3), (3, 0)):
+        rm = OF.window_row_map(B, H, W, ws, shift, torch.device("cpu"))
+        assert rm.dtype == torch.int32 and sorted(rm.tolist()) == list(range(B * H * W))
+        assert OF.window_row_map(B, H, W, ws, shift, torch.device("cpu")) is rm
+        x = torch.randn(B, H, W, C).bfloat16().requires_grad_()
+        w, b = (torch.rand(C) + 0.5).bfloat16().requires_grad_(), torch.randn(C).bfloat16().requires_grad_()
+        yw, skip = OF.layer_norm_partition(x, w, b, 1e-5, ws, shift)
+        xf, wf, bf = (t.detach().float().requires_grad_() for t in (x, w, b))
+        ref = OF.window_partition(torch.nn.functional.layer_norm(xf, (C,), wf, bf), ws, shift)
+        assert yw.shape == ref.shape and torch.allclose(yw.float(), ref, atol=3e-2, rtol=2e-2)
+        g1, g2 = torch.randn_like(ref), torch.randn(B, H, W, C)
+        (yw.float() * g1).sum().backward(retain_graph=True)
+        (skip.float() * g2).sum().backward()
+        ((ref * g1).sum() + (xf * g2).sum()).backward()
+        assert torch.allclose(x.grad.float(), xf.grad, atol=8e-2, rtol=3e-2)
+        assert torch.allclose(w.grad.float(), wf.grad, atol=0.3, rtol=3e-2) and torch.allclose(b.grad.float(), bf.grad, atol=0.15, rtol=3e-2)
+    # fp32 inputs compose the two ops
+    x32 = torch.randn(B, H, W, C)
+    y32, s32 = OF.layer_norm_partition(x32, torch.ones(C), torch.zeros(C), 1e-5, ws, (3, 3))
+    assert s32 is x32 and torch.allclose(y32, OF.window_partition(torch.nn.functional.layer_norm(x32, (C,)), ws, (3, 3)))
+
+
+def test_patchify_matches_conv_as_gemm():
+    from b200dist.ops import native as N
+    torch.manual_seed(7)
+    x = torch.randn(2, 3, 8, 12)
+    conv = torch.nn.Conv2d(3, 5, 4, 4)
+    cols = N.patchify(x, 4)
+    y = (cols @ conv.weight.view(5, -1).t() + conv.bias).view(2, 2, 3, 5)
+    assert torch.allclose(y, conv(x).permute(0, 2, 3, 1), atol=1e-5)
