@@ -1,7 +1,7 @@
 """SASS evidence listing for the hand-written kernels: for every requested kernel of a built object file, the instructions that
 prove what it is - tcgen05 MMAs (UTC*MMA), TMEM loads (LDTM), TMA tensor / bulk copies (UTMALDG / UTMASTG / UBLKCP / UTMAREDG),
 mbarrier traffic (SYNCS), system-scope loads / stores / reductions (the peer-memory flags of the fused collectives) and
-multimem instructions - each with its SASS address, in program order (a listing, not a count).
+multimem instructions, and for the warp-level kernels HMMA / LDSM (ldmatrix) / LDGSTS (cp.async) - each with its SASS address, in program order (a listing, not a count).
 
     python tools/sass_listing.py build/gemm.cu.o 'gemm_tcgen05_kernelILi256ELb0ELb0ELi1ELb1' [...more name fragments] > profiles/x.txt
 """
@@ -10,7 +10,7 @@ import subprocess
 import sys
 
 KEEP = re.compile(r"\b(UTC[A-Z]*MMA|UTCBAR|UTCCP|LDTM|STTM|UTMALDG|UTMASTG|UTMAREDG|UTMAPF|UBLKCP|UBLKRED|SYNCS|ERRBAR|MEMBAR|CCTL|"
-                  r"MULTIMEM|LDGMC[^ ]*|STGMC[^ ]*|REDGMC[^ ]*|UCGABAR|BAR\.SYNC|BAR\.ARV|ELECT|REDG?\.E[^ ]*|ATOMG?\.E[^ ]*)\b|\.SYS\b|\.STRONG\.GPU|\.MMIO")
+                  r"HMMA[^ ]*|LDSM[^ ]*|LDGSTS[^ ]*|LDGDEPBAR|DEPBAR[^ ]*|MULTIMEM|LDGMC[^ ]*|STGMC[^ ]*|REDGMC[^ ]*|UCGABAR|BAR\.SYNC|BAR\.ARV|ELECT|REDG?\.E[^ ]*|ATOMG?\.E[^ ]*)\b|\.SYS\b|\.STRONG\.GPU|\.MMIO")
 
 
 def main():
