@@ -197,7 +197,8 @@ def check_gemm(quick):
 
 
 def check_norm(quick):
-    for (rows, H, rms) in [(1000, 768, False), (513, 1024, False), (300, 4096, True), (257, 1536, False), (64, 128, False)]:
+    for (rows, H, rms) in [(1000, 768, False), (513, 1024, False), (300, 4096, True), (257, 1536, False), (64, 128, False),
+                           (1001, 256, False), (777, 128, False), (4099, 128, True), (301, 512, False), (131, 64, False), (515, 200, False)]:
         x = torch.randn(rows, H, device=dev, dtype=torch.bfloat16)
         g = torch.randn(H, device=dev, dtype=torch.bfloat16)
         b = None if rms else torch.randn(H, device=dev, dtype=torch.bfloat16)
@@ -219,23 +220,29 @@ def check_norm(quick):
         report(f"norm bwd +dres dx rows{rows} H{H} rms={int(rms)}", dx2, dx2r, 3e-2)
         report(f"norm bwd +dres dgamma(acc) rows{rows} H{H}", mg_w, dg2r + (0.0 if rms else 1.0), 2e-3)
     if not quick:
-        x = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
-        dy = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
-        g = torch.ones(768, device=dev, dtype=torch.bfloat16)
-        b = torch.zeros(768, device=dev, dtype=torch.bfloat16)
-        _, mean, rstd = N.norm_fwd(x, g, b, 1e-5)
-        mg_w, mg_b = torch.zeros(768, device=dev), torch.zeros(768, device=dev)
-        flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-        ms = timeit(lambda: N.norm_bwd(dy, x, g, mean, rstd, dgamma=mg_w, dbeta=mg_b, accumulate=True, dres=dy), flush=flush)
-        gb = 4 * x.numel() * 2 / ms / 1e6
-        print(f"time layernorm bwd(+dres, +fold) 12288x768: {ms:.4f} ms {gb:.0f} GB/s = {gb / PEAKS['hbm_gbs']:.3f} of measured copy bw (L2 flushed)")
-    if not quick:
-        x = torch.randn(12288, 768, device=dev, dtype=torch.bfloat16)
-        g = torch.ones(768, device=dev, dtype=torch.bfloat16)
-        b = torch.zeros(768, device=dev, dtype=torch.bfloat16)
-        ms = timeit(lambda: N.norm_fwd(x, g, b, 1e-5))
-        gb = 2 * x.numel() * 2 / ms / 1e6
-        print(f"time layernorm fwd 12288x768: {ms:.4f} ms {gb:.0f} GB/s = {gb / PEAKS['hbm_gbs']:.3f} of measured copy bw (L2 resident)")
+        # device time without host launch cost: 20 calls captured in a CUDA graph, cycling over 4 input sets so that consecutive calls
+        # never find their rows in L2 (the sets of one shape add up to more than the 126 MB L2, except the 768-wide GPT shape: 75 MB)
+        for (rows, H, tag) in [(12288, 768, "GPT-2 small micro-batch"), (200704, 128, "swin_b stage 1"), (50176, 256, "swin_b stage 2"),
+                               (12544, 512, "swin_b stage 3")]:
+            xs = [torch.randn(rows, H, device=dev, dtype=torch.bfloat16) for _ in range(4)]
+            dys = [torch.randn(rows, H, device=dev, dtype=torch.bfloat16) for _ in range(4)]
+            g = torch.ones(H, device=dev, dtype=torch.bfloat16)
+            b = torch.zeros(H, device=dev, dtype=torch.bfloat16)
+            _, mean, rstd = N.norm_fwd(xs[0], g, b, 1e-5)
+            mg_w, mg_b = torch.zeros(H, device=dev), torch.zeros(H, device=dev)
+            k = [0]
+
+            def fwd():
+                k[0] += 1
+                return N.norm_fwd(xs[k[0] % 4], g, b, 1e-5)
+
+            def bwd():
+                k[0] += 1
+                return N.norm_bwd(dys[k[0] % 4], xs[k[0] % 4], g, mean, rstd, dgamma=mg_w, dbeta=mg_b, accumulate=True, dres=dys[(k[0] + 1) % 4])
+            ms_f, ms_b = graph_timeit(fwd), graph_timeit(bwd)
+            gf, gbw = 2 * rows * H * 2 / ms_f / 1e6, 4 * rows * H * 2 / ms_b / 1e6
+            print(f"time layernorm {rows}x{H} ({tag}): fwd {ms_f * 1e3:.1f} us {gf:.0f} GB/s = {gf / PEAKS['hbm_gbs']:.3f} of measured copy bw | "
+                  f"bwd(+dres, +fold) {ms_b * 1e3:.1f} us {gbw:.0f} GB/s = {gbw / PEAKS['hbm_gbs']:.3f}  (graph-timed)", flush=True)
 
 
 def check_elementwise(quick):

@@ -14,6 +14,10 @@ namespace k_conv {
 namespace k_bn {
 #include "batchnorm.cu"
 }
+#include "vec_emu.h"
+namespace k_norm {
+#include "norm.cu"
+}
 #include "mma_emu.h"
 namespace k_wtc {
 #include "window_attn_tc.cu"
@@ -249,5 +253,65 @@ void emu_wattn_tc_bwd(const void* qkv, const float* bias, const float* mask, con
       W::wattn_tc_bwd_kernel<__half>(static_cast<const __half*>(qkv), bias, mask, static_cast<const __half*>(out), static_cast<const __half*>(dout), lse,
                                      static_cast<__half*>(dqkv), dbias, Bw, nW, heads, scale);
     });
+}
+}  // extern "C"
+
+// LayerNorm / RMSNorm (csrc/norm.cu) with the launch rules of its host dispatch (team by row width, rows per CTA, workspace fold);
+// `grid_cap` stands in for the SM-count caps so that small inputs still exercise the row loops
+extern "C" {
+int emu_norm_team(int H) { return k_norm::team_for(H); }
+
+void emu_norm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean, float* rstd, int rows, int H, float eps,
+                  const int* row_map, int dtype, int rms, int grid_cap) {
+  auto run = [&](auto* tag, auto rms_tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    constexpr bool RMS = decltype(rms_tag)::value;
+    const T *xp = static_cast<const T*>(x), *gp = static_cast<const T*>(gamma), *bp = static_cast<const T*>(beta);
+    T* yp = static_cast<T*>(y);
+    if (H <= 1024) {
+      const int team = k_norm::team_for(H), rpc = 128 / team;
+      const int grid = std::min((rows + rpc - 1) / rpc, grid_cap);
+      if (team == 8) emu::launch(dim3(grid), dim3(128), 0, [&] { k_norm::norm_fwd_kernel<T, 8, RMS>(xp, gp, bp, yp, mean, rstd, rows, H, eps, row_map); });
+      else if (team == 16) emu::launch(dim3(grid), dim3(128), 0, [&] { k_norm::norm_fwd_kernel<T, 16, RMS>(xp, gp, bp, yp, mean, rstd, rows, H, eps, row_map); });
+      else emu::launch(dim3(grid), dim3(128), 0, [&] { k_norm::norm_fwd_kernel<T, 32, RMS>(xp, gp, bp, yp, mean, rstd, rows, H, eps, row_map); });
+    } else {
+      emu::launch(dim3(std::min(rows, grid_cap)), dim3(256), 0, [&] { k_norm::norm_fwd_kernel<T, 256, RMS>(xp, gp, bp, yp, mean, rstd, rows, H, eps, row_map); });
+    }
+  };
+  auto with_rms = [&](auto* tag) { if (rms) run(tag, std::true_type{}); else run(tag, std::false_type{}); };
+  if (dtype == 1) with_rms(static_cast<__nv_bfloat16*>(nullptr)); else with_rms(static_cast<__half*>(nullptr));
+}
+
+void emu_norm_bwd(const void* dy, const void* x, const void* gamma, const float* mean, const float* rstd, const void* dres, void* dx,
+                  float* dgamma, float* dbeta, int rows, int H, const int* row_map, int dtype, int rms, int accumulate, int grid_cap) {
+  auto run = [&](auto* tag, auto rms_tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    constexpr bool RMS = decltype(rms_tag)::value;
+    const T *dyp = static_cast<const T*>(dy), *xp = static_cast<const T*>(x), *gp = static_cast<const T*>(gamma), *rp = static_cast<const T*>(dres);
+    T* dxp = static_cast<T*>(dx);
+    int grid;
+    std::vector<float> ws;
+#define EMU_NB(TEAM_, NV_, THREADS_, SMEM_) emu::launch(dim3(grid), dim3(THREADS_), SMEM_, [&] { \
+      k_norm::norm_bwd_kernel<T, TEAM_, RMS, NV_>(dyp, xp, gp, mean, rstd, rp, dxp, ws.data(), rows, H, row_map); })
+    if (H <= 1024) {
+      const int team = k_norm::team_for(H), rpc = 128 / team, nvec = H >> 3, nv = (nvec + team - 1) / team;
+      grid = std::min((rows + rpc - 1) / rpc, grid_cap);
+      ws.assign(static_cast<size_t>(grid) * 2 * H, std::nanf(""));
+      const size_t smem = static_cast<size_t>(rpc) * 2 * H * sizeof(float);
+      if (team == 8) { if (nv <= 1) EMU_NB(8, 1, 128, smem); else EMU_NB(8, 2, 128, smem); }
+      else if (team == 16) EMU_NB(16, 2, 128, smem);
+      else { if (nv <= 2) EMU_NB(32, 2, 128, smem); else if (nv == 3) EMU_NB(32, 3, 128, smem); else EMU_NB(32, 4, 128, smem); }
+    } else {
+      grid = std::min(rows, grid_cap);
+      ws.assign(static_cast<size_t>(grid) * 2 * H, std::nanf(""));
+      const int nv = (H + 2047) / 2048;
+      if (nv == 1) EMU_NB(256, 1, 256, 0); else if (nv == 2) EMU_NB(256, 2, 256, 0); else if (nv == 3) EMU_NB(256, 3, 256, 0); else EMU_NB(256, 4, 256, 0);
+    }
+#undef EMU_NB
+    const int nparts = grid;
+    emu::launch(dim3((2 * H + 31) / 32), dim3(1024), 0, [&] { k_norm::norm_bwd_fold_kernel(ws.data(), nparts, H, dgamma, rms ? nullptr : dbeta, accumulate); });
+  };
+  auto with_rms = [&](auto* tag) { if (rms) run(tag, std::true_type{}); else run(tag, std::false_type{}); };
+  if (dtype == 1) with_rms(static_cast<__nv_bfloat16*>(nullptr)); else with_rms(static_cast<__half*>(nullptr));
 }
 }  // extern "C"

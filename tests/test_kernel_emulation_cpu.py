@@ -18,8 +18,8 @@ DT = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2}
 
 @pytest.fixture(scope="module")
 def emu():
-    srcs = [os.path.join(ROOT, "tests", "emu", f) for f in ("emu_kernels.cpp", "cuda_emu.h", "mma_emu.h")] + \
-           [os.path.join(ROOT, "csrc", f) for f in ("softmax.cu", "conv.cu", "batchnorm.cu", "window_attn_tc.cu")]
+    srcs = [os.path.join(ROOT, "tests", "emu", f) for f in ("emu_kernels.cpp", "cuda_emu.h", "mma_emu.h", "vec_emu.h")] + \
+           [os.path.join(ROOT, "csrc", f) for f in ("softmax.cu", "conv.cu", "batchnorm.cu", "window_attn_tc.cu", "norm.cu")]
     if not os.path.exists(SO) or os.path.getmtime(SO) < max(os.path.getmtime(s) for s in srcs):
         os.makedirs(os.path.dirname(SO), exist_ok=True)
         r = subprocess.run(["g++", "-std=c++17", "-O1", "-fPIC", "-shared", "-pthread", "-mf16c", "-mavx2", "-I" + os.path.join(ROOT, "tests", "emu"),
@@ -283,3 +283,34 @@ def test_window_attention_tensor_core_kernels_under_emulation(emu, dtype, Bw, he
         rel = (got - ref).pow(2).mean().sqrt() / ref.pow(2).mean().sqrt()
         assert rel < 6e-3, (name, rel)
         assert (got - ref).abs().max() <= 3e-2 * max(1.0, ref.abs().max().item()), (name, (got - ref).abs().max())
+
+
+@pytest.mark.parametrize("rows,H,rms,mapped", [(37, 128, False, True), (21, 256, False, False), (19, 64, True, False), (13, 512, False, True),
+                                               (9, 768, False, False), (7, 1024, True, True), (5, 2048, False, False), (50, 32, False, False), (23, 200, False, True)])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_norm_kernels_under_emulation(emu, rows, H, rms, mapped, dtype):
+    """csrc/norm.cu: 8 / 16 / 32 lanes or a whole CTA per row by row width, several rows per warp with full-mask shuffles (row counts that
+    leave teams of the last warp without a row), the row-map variant, the residual-gradient input and the dgamma / dbeta workspace fold,
+    with grids far smaller than the row count so every loop runs more than once."""
+    from b200dist.ops import native as N
+    torch.manual_seed(8)
+    x = (torch.randn(rows, H) * 2 + 0.5).to(dtype)
+    g, b = (torch.rand(H) + 0.5).to(dtype), torch.randn(H).to(dtype)
+    rm = torch.randperm(rows).to(torch.int32) if mapped else None
+    y = torch.full((rows, H), float("nan")).to(dtype)
+    mean, rstd = torch.full((rows,), float("nan")), torch.full((rows,), float("nan"))
+    assert emu.emu_norm_team(H) == (8 if H <= 128 else 16 if H <= 256 else 32)
+    emu.emu_norm_fwd(_p(x), _p(g), None if rms else _p(b), _p(y), None if rms else _p(mean), _p(rstd), rows, H, c_f(1e-5), _p(rm), DT[dtype], int(rms), 3)
+    yr, meanr, rstdr = N.norm_fwd(x, g, None if rms else b, 1e-5, rms, row_map=rm)
+    assert torch.allclose(y.float(), yr.float(), atol=2e-2, rtol=2e-2), (y.float() - yr.float()).abs().max()
+    assert torch.allclose(rstd, rstdr, rtol=1e-4) and (rms or torch.allclose(mean, meanr, atol=1e-5))
+    dy, dres = torch.randn(rows, H).to(dtype), torch.randn(rows, H).to(dtype)
+    dx = torch.full((rows, H), float("nan")).to(dtype)
+    dg, db = torch.ones(H), torch.ones(H)          # accumulate = 1 adds into them
+    emu.emu_norm_bwd(_p(dy), _p(x), _p(g), None if rms else _p(meanr), _p(rstdr), _p(dres), _p(dx), _p(dg), _p(db), rows, H, _p(rm), DT[dtype],
+                     int(rms), 1, 2)
+    dxr, dgr, dbr = N.norm_bwd(dy, x, g, None if rms else meanr, rstdr, rms, dres=dres, row_map=rm)
+    assert torch.allclose(dx.float(), dxr.float(), atol=4e-2, rtol=3e-2), (dx.float() - dxr.float()).abs().max()
+    assert torch.allclose(dg - 1, dgr, atol=2e-3 * max(1.0, dgr.abs().max().item()))
+    if not rms:
+        assert torch.allclose(db - 1, dbr, atol=2e-3 * max(1.0, dbr.abs().max().item()))
