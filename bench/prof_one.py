@@ -1,4 +1,4 @@
-"""Tiny driver for ncu captures of one kernel at the flagship shape:  python bench/prof_one.py attn_fwd|attn_bwd|gemm|wgrad"""
+"""Tiny driver for ncu captures of one kernel at the flagship shape:  python bench/prof_one.py attn_fwd|attn_bwd|gemm|wgrad|wattn"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
@@ -31,5 +31,13 @@ elif what == "wgrad":
     acc = torch.zeros(3072, 768, device=dev)
     for _ in range(4):
         N.gemm(dy, x, a_mn=True, b_mn=True, out=acc, accumulate=True)
+elif what == "wattn":      # Swin-B stage 3 at batch 64: 256 windows x 16 heads, shifted (masked) block
+    Bw, heads, nW = 256, 16, 4
+    wqkv = torch.randn(Bw, 49, 3 * heads * 32, device=dev, dtype=torch.bfloat16)
+    bias = torch.randn(heads, 49, 49, device=dev)
+    mask = torch.where(torch.rand(nW, 49, 49, device=dev) < 0.3, -100.0, 0.0)
+    for _ in range(2):
+        wo, wlse = N.window_attn_fwd(wqkv, bias, mask, heads, 32 ** -0.5)
+        N.window_attn_bwd(wqkv, bias, mask, wo, torch.ones_like(wo), wlse, heads, 32 ** -0.5)
 torch.cuda.synchronize()
 print("done", what)
