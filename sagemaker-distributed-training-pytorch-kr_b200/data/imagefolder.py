@@ -93,10 +93,11 @@ class EvalTransform:
 class ImageFolderDataset(torch.utils.data.Dataset):
     """<root>/<class>/*.jpg ; cv2.imread + BGR->RGB ; HWC -> CHW float32 (pytorch_oxford_ddp.py:49-57)."""
 
-    def __init__(self, root: str, transform: Optional[Callable] = None):
+    def __init__(self, root: str, transform: Optional[Callable] = None, raw_uint8: bool = False):
         self.classes, self.class_to_idx = find_classes(root)
         self.samples = make_dataset(root, self.class_to_idx)
         self.transform = transform
+        self.raw_uint8 = raw_uint8          # keep the image as uint8 HWC (the device-side pipeline of data/gpu_augment.py takes it from there)
 
     def __len__(self):
         return len(self.samples)
@@ -107,6 +108,8 @@ class ImageFolderDataset(torch.utils.data.Dataset):
         img = cv2.cvtColor(cv2.imread(path), cv2.COLOR_BGR2RGB)
         if self.transform is not None:
             img = self.transform(img)
+        if self.raw_uint8:
+            return torch.from_numpy(np.ascontiguousarray(img, dtype=np.uint8)), target
         return torch.from_numpy(np.ascontiguousarray(img.transpose(2, 0, 1), dtype=np.float32)), target
 
 

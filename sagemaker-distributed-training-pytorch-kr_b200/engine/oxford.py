@@ -65,6 +65,8 @@ def args_fn(argv=None):
     p.add_argument("--max-steps", type=int, default=None)
     p.add_argument("--num-workers", type=int, default=2)
     p.add_argument("--bucket-cap-mb", type=float, default=25.0)
+    p.add_argument("--gpu-augment", action="store_true", help="real images: the loader workers only decode + resize (uint8 over PCIe); the random "
+                                                               "augmentations run as batched tensor ops on the training device (data/gpu_augment.py)")
     p.add_argument("--cuda-graph", action="store_true", help="bf16 path: capture zero-grad + forward + backward + gradient all-reduce once, replay per step")
     return p.parse_args(argv)
 
@@ -90,7 +92,11 @@ def _loaders(args):
         tr = SyntheticImageDataset(args.synthetic_train_size, args.num_classes, args.height, args.width, seed=args.seed)
         va = SyntheticImageDataset(args.synthetic_val_size, args.num_classes, args.height, args.width, seed=args.seed + 1)
     else:
-        tr = ImageFolderDataset(os.path.join(args.data_dir, "train"), TrainAugment(args.height, args.width, args.seed + args.rank))
+        if getattr(args, "gpu_augment", False):
+            from ..data.gpu_augment import DecodeResize
+            tr = ImageFolderDataset(os.path.join(args.data_dir, "train"), DecodeResize(args.height, args.width), raw_uint8=True)
+        else:
+            tr = ImageFolderDataset(os.path.join(args.data_dir, "train"), TrainAugment(args.height, args.width, args.seed + args.rank))
         va = ImageFolderDataset(os.path.join(args.data_dir, "val"), EvalTransform(args.height, args.width))
     pin = torch.cuda.is_available()
     tr_s = torch.utils.data.distributed.DistributedSampler(tr, num_replicas=args.world_size, rank=args.rank) if args.world_size > 1 else None
@@ -153,6 +159,10 @@ def train(args):
     logger.info("Processes {}/{} ({:.0f}%) of test data".format(nv, len(test_loader.dataset), 100.0 * nv / len(test_loader.dataset)))
     print(" local_rank : {}, local_batch_size : {}".format(args.local_rank, args.batch_size))
 
+    gpu_aug = None
+    if getattr(args, "gpu_augment", False) and not args.synthetic:
+        from ..data.gpu_augment import GpuAugment
+        gpu_aug = GpuAugment(args.height, args.width, seed=args.seed + args.rank, dtype=dtype)
     graphed = None      # built lazily from the first full batch (static shapes: the loader drops nothing, so the last partial batch runs eagerly)
 
     def eager_step(data, target):
@@ -173,7 +183,8 @@ def train(args):
         end = time.time()
         since = 0
         for batch_idx, (data, target) in enumerate(train_loader):
-            data = data.to(dev, non_blocking=True).to(dtype)
+            data = data.to(dev, non_blocking=True)
+            data = gpu_aug(data) if gpu_aug is not None else data.to(dtype)
             target = target.to(dev, non_blocking=True)
             use_graph = (getattr(args, "cuda_graph", False) and mixed and dev.type == "cuda" and data.size(0) == args.batch_size
                          and (args.world_size == 1 or getattr(optimizer, "fabric", None) is not None))

@@ -55,9 +55,10 @@ def torch_model(model_name: str, num_classes: int = 0, pretrained: bool = True, 
 
 
 def accuracy(output: torch.Tensor, target: torch.Tensor, topk: Sequence[int] = (1,)) -> List[torch.Tensor]:
-    """precision@k in percent (util.py:69-83)."""
+    """precision@k in percent (util.py:69-83).  k is capped at the number of classes (the reference's top-5 raises on a head with
+    fewer than five outputs)."""
     with torch.no_grad():
-        maxk = max(topk)
+        maxk = min(max(topk), output.shape[1])
         _, pred = output.float().topk(maxk, 1, True, True)
         correct = pred.t().eq(target.view(1, -1).expand_as(pred.t()))
         return [correct[:k].reshape(-1).float().sum(0, keepdim=True).mul_(100.0 / target.size(0)) for k in topk]

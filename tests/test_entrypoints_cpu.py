@@ -101,6 +101,27 @@ def test_oxford_swin_script_synthetic(tmp_path):
     assert "Test_Prec@1=" in out and "Test_Loss=" in out
 
 
+def test_oxford_script_real_image_folder_host_and_device_augmentation(tmp_path):
+    """<data-dir>/{train,val}/<class>/*.jpg through the script: once with the reference's host-side augmentation pipeline and once
+    with --gpu-augment (workers decode + resize, uint8 batches, random ops on the training device)"""
+    cv2 = pytest.importorskip("cv2")
+    import numpy as np
+    rng = np.random.default_rng(0)
+    for split, n in (("train", 6), ("val", 2)):
+        for cls in ("abyssinian", "beagle"):
+            d = tmp_path / "data" / split / cls
+            d.mkdir(parents=True)
+            for i in range(n):
+                cv2.imwrite(str(d / f"{cls}_{i}.jpg"), rng.integers(0, 255, (rng.integers(60, 90), rng.integers(60, 90), 3), dtype=np.uint8))
+    common = ["--model_name", "swin_t", "--num-classes", "2", "--num-epochs", "1", "--batch-size", "4", "--test-batch-size", "2", "--height", "64",
+              "--width", "64", "--backend", "gloo", "--no-pretrained", "--num-workers", "0", "--data-dir", str(tmp_path / "data"), "--print-freq", "1",
+              "--log-interval", "1", "--max-steps", "2"]
+    for extra in ([], ["--gpu-augment"]):
+        out = _run("pytorch_oxford_ddp.py", common + ["--model-dir", str(tmp_path / ("m" + str(len(extra))))] + extra, timeout=900)
+        assert "Train_Loss=" in out and "Test_Prec@1=" in out, out[-2000:]
+        assert os.path.isfile(tmp_path / ("m" + str(len(extra))) / "checkpoint.pth")
+
+
 def test_swin_b_matches_torchvision_structure():
     """same parameter names, shapes and count as torchvision's swin_b (the reference builds it by name, train_util:18-41)."""
     tv = pytest.importorskip("torchvision")

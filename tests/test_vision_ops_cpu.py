@@ -336,3 +336,34 @@ def test_patchify_matches_conv_as_gemm():
     cols = N.patchify(x, 4)
     y = (cols @ conv.weight.view(5, -1).t() + conv.bias).view(2, 2, 3, 5)
     assert torch.allclose(y, conv(x).permute(0, 2, 3, 1), atol=1e-5)
+
+
+def test_gpu_augment_pipeline_semantics():
+    """data/gpu_augment.py on the CPU: the degenerate configuration is resize + normalise, the flip is a flip, HSV agrees with OpenCV,
+    a seed reproduces a batch, and the full pipeline returns normalised images of the requested size and dtype"""
+    cv2 = pytest.importorskip("cv2")
+    import numpy as np
+    from b200dist.data.gpu_augment import GpuAugment, hsv_to_rgb, rgb_to_hsv
+    torch.manual_seed(0)
+    u8 = (torch.rand(5, 40, 50, 3) * 255).byte()
+    mean, std = torch.tensor([0.485, 0.456, 0.406])[None, :, None, None], torch.tensor([0.229, 0.224, 0.225])[None, :, None, None]
+    ref = (u8.permute(0, 3, 1, 2).float() / 255 - mean) / std
+    off = dict(p_noise=0, p_blur=0, p_tone=0, p_hsv=0, scale=(1.0, 1.0), ratio=(1.0, 1.0))
+    assert torch.allclose(GpuAugment(40, 50, seed=1, p_flip=0, **off)(u8), ref, atol=1e-4)
+    assert torch.allclose(GpuAugment(40, 50, seed=1, p_flip=1.0, **off)(u8), ref.flip(2), atol=1e-4)
+    x = torch.rand(3, 3, 9, 9)
+    assert torch.allclose(hsv_to_rgb(rgb_to_hsv(x)), x, atol=1e-5)
+    img = (torch.rand(8, 8, 3) * 255).byte().numpy()
+    cv = cv2.cvtColor(img, cv2.COLOR_RGB2HSV_FULL).astype(np.float32) / 255.0
+    mine = rgb_to_hsv(torch.from_numpy(img).permute(2, 0, 1)[None].float() / 255)[0].permute(1, 2, 0).numpy()
+    assert np.abs(((mine - cv + 0.5) % 1.0 - 0.5)[..., 0]).max() < 0.01 and np.abs(mine - cv)[..., 1:].max() < 0.01      # 8-bit quantisation of cv2's result
+    a, b = GpuAugment(32, 24, seed=7)(u8), GpuAugment(32, 24, seed=7)(u8)
+    assert torch.equal(a, b) and not torch.equal(a, GpuAugment(32, 24, seed=8)(u8))
+    y = GpuAugment(32, 24, seed=3, dtype=torch.bfloat16)(u8)
+    assert y.shape == (5, 3, 32, 24) and y.dtype == torch.bfloat16 and torch.isfinite(y.float()).all()
+    lo, hi = (0 - 0.485) / 0.229 - 1e-2, (1 - 0.406) / 0.225 + 1e-2
+    assert y.float().min() >= lo and y.float().max() <= hi
+    # crops stay inside the image: a constant image stays constant through crop + flip
+    const = torch.full((4, 30, 30, 3), 128, dtype=torch.uint8)
+    z = GpuAugment(16, 16, seed=2, p_noise=0, p_blur=0, p_tone=0, p_hsv=0)(const)
+    assert torch.allclose(z, ((torch.full((4, 3, 16, 16), 128 / 255.0) - mean) / std), atol=1e-4)
