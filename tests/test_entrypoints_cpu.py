@@ -101,6 +101,33 @@ def test_oxford_swin_script_synthetic(tmp_path):
     assert "Test_Prec@1=" in out and "Test_Loss=" in out
 
 
+def test_mnist_script_reads_raw_idx_files(tmp_path):
+    """--data-path with torchvision's on-disk layout (<root>/MNIST/raw/*-idx?-ubyte, plain and gzipped): the script trains on the files,
+    not on the synthetic stand-in (reference: datasets.MNIST(args.data_path, ...), pytorch_mnist_ddp.py:216-228)"""
+    import gzip
+    import numpy as np
+    import torch
+    from b200dist.data.mnist import MNISTTensors, write_idx
+    rng = np.random.default_rng(0)
+    raw = tmp_path / "MNIST" / "raw"
+    tr_x, tr_y = rng.integers(0, 255, (96, 28, 28), dtype=np.uint8), rng.integers(0, 10, (96,), dtype=np.uint8)
+    te_x, te_y = rng.integers(0, 255, (32, 28, 28), dtype=np.uint8), rng.integers(0, 10, (32,), dtype=np.uint8)
+    write_idx(str(raw / "train-images-idx3-ubyte"), tr_x)
+    write_idx(str(raw / "train-labels-idx1-ubyte"), tr_y)
+    for name, arr in (("t10k-images-idx3-ubyte", te_x), ("t10k-labels-idx1-ubyte", te_y)):      # the test split gzipped
+        write_idx(str(raw / name), arr)
+        with open(raw / name, "rb") as f, gzip.open(str(raw / name) + ".gz", "wb") as gz:
+            gz.write(f.read())
+        os.remove(raw / name)
+    ds = MNISTTensors(str(tmp_path), train=True)
+    assert not ds.synthetic and len(ds) == 96 and torch.equal(ds.labels, torch.from_numpy(tr_y.astype(np.int64)))
+    assert torch.allclose(ds.images[:, 0], (torch.from_numpy(tr_x).float() / 255 - 0.1307) / 0.3081)
+    te = MNISTTensors(str(tmp_path), train=False)
+    assert not te.synthetic and len(te) == 32 and torch.equal(te.labels, torch.from_numpy(te_y.astype(np.int64)))
+    out = _run("pytorch_mnist.py", ["--data-path", str(tmp_path), "--epochs", "1", "--batch-size", "32", "--test-batch-size", "16", "--log-interval", "1"])
+    assert "Train Epoch: 1 [64/96" in out and "Test set: Average loss:" in out and "/32 (" in out
+
+
 def test_oxford_script_real_image_folder_host_and_device_augmentation(tmp_path):
     """<data-dir>/{train,val}/<class>/*.jpg through the script: once with the reference's host-side augmentation pipeline and once
     with --gpu-augment (workers decode + resize, uint8 batches, random ops on the training device)"""
