@@ -76,7 +76,7 @@ class _BiasGather(torch.autograd.Function):
         heads = ctx.shape[1]
         dt = torch.zeros((heads, ctx.shape[0]), dtype=torch.float32, device=dbias.device)
         dt.index_add_(1, index, dbias.reshape(heads, -1).float())
-        return dt.t().to(ctx.dtype), None, None
+        return dt.t().contiguous().to(ctx.dtype), None, None          # contiguous like the parameter: AccumulateGrad keeps it as it is
 
 
 _MASK_CACHE = {}
