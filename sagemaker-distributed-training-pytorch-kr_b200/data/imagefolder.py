@@ -105,7 +105,10 @@ class ImageFolderDataset(torch.utils.data.Dataset):
     def __getitem__(self, idx):
         import cv2
         path, target = self.samples[idx]
-        img = cv2.cvtColor(cv2.imread(path), cv2.COLOR_BGR2RGB)
+        raw = cv2.imread(path)
+        if raw is None:         # the reference fails inside cvtColor here; the notebook deletes the 12 known corrupt files beforehand
+            raise RuntimeError(f"{path} does not decode as an image (tools/prepare_oxford_pet.py drops such files)")
+        img = cv2.cvtColor(raw, cv2.COLOR_BGR2RGB)
         if self.transform is not None:
             img = self.transform(img)
         if self.raw_uint8:
