@@ -95,3 +95,44 @@ def test_preprocess_data_tool(tmp_path):
     assert len(ds) == len(CORPUS)
     for i, text in enumerate(CORPUS):
         assert np.array_equal(np.asarray(ds[i]), np.asarray(tok.tokenize(text) + [tok.eod]))
+
+
+def test_notebook_pipeline_preprocess_then_pretrain_on_the_indexed_dataset(tmp_path):
+    """the notebook's actual flow (3_training_megatron-lm.ipynb: preprocess_data.py -> pretrain_gpt.py --data-path ... --vocab-file
+    --merge-file, launch line :542-557) end to end on a toy corpus: GPT2BPETokenizer vocabulary padding, .bin/.idx through the C++ index
+    builders with a --data-cache-path, train / valid / test split, evaluation, and a resumable second run that reuses the index cache"""
+    import re
+    vf, mf = _train_bpe(tmp_path)
+    docs = [CORPUS[i % len(CORPUS)] * (3 + i % 5) for i in range(64)]
+    src = tmp_path / "docs.jsonl"
+    src.write_text("\n".join(json.dumps({"content": t}) for t in docs) + "\n", encoding="utf-8")
+    prefix = str(tmp_path / "cp")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "preprocess_data.py"), "--input", str(src), "--output-prefix", prefix,
+                        "--json-keys", "content", "--vocab-file", vf, "--merge-file", mf, "--append-eod", "--workers", "2"],
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-1500:]
+    cache = tmp_path / "cache"
+    argv = ("--num-layers 2 --hidden-size 64 --num-attention-heads 4 --seq-length 32 --max-position-embeddings 32 --micro-batch-size 2 "
+            "--global-batch-size 4 --lr 1e-3 --lr-decay-style cosine --lr-warmup-iters 2 --weight-decay 0.1 --log-interval 1 --eval-interval 3 "
+            "--eval-iters 2 --tokenizer-type GPT2BPETokenizer --distributed-backend gloo --seed 7 --train-iters 6 --lr-decay-iters 6 "
+            "--data-impl mmap --split 900,50,50").split()
+    argv += ["--data-path", prefix + "_content_document", "--vocab-file", vf, "--merge-file", mf, "--data-cache-path", str(cache),
+             "--save", str(tmp_path / "ck"), "--save-interval", "3"]
+    env = {**os.environ, "OMP_NUM_THREADS": "2"}
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "entrypoints", "pretrain_gpt.py"), *argv], capture_output=True, text=True, timeout=600, env=env)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0, out[-3000:]
+    losses = {int(m.group(1)): float(m.group(2)) for m in re.finditer(r"iteration\s+(\d+)/\s*\d+ \|.*?lm loss: ([0-9.E+-]+)", out)}
+    assert sorted(losses) == [1, 2, 3, 4, 5, 6] and losses[6] < losses[1]
+    assert "validation loss at iteration 3" in out and "padded vocab" in out.lower()
+    assert any(f.endswith(".npy") for f in os.listdir(cache)), os.listdir(cache)
+    # second run: resumes from the iteration-6 checkpoint, finds the index files in the cache, trains two more iterations
+    argv2 = [a for a in argv]
+    argv2[argv2.index("--train-iters") + 1] = "8"
+    argv2 += ["--override-opt_param-scheduler"]             # a longer run changes the scheduler's horizon: the reference asks for this flag too
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "entrypoints", "pretrain_gpt.py"), *argv2, "--load", str(tmp_path / "ck")],
+                       capture_output=True, text=True, timeout=600, env=env)
+    out2 = r.stdout + r.stderr
+    assert r.returncode == 0, out2[-3000:]
+    again = {int(m.group(1)) for m in re.finditer(r"iteration\s+(\d+)/\s*\d+ \|", out2)}
+    assert again == {7, 8}, again
