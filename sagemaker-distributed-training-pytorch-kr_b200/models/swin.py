@@ -101,7 +101,7 @@ def shift_window_mask(pH: int, pW: int, ws: int, shift, device) -> torch.Tensor:
         region = region.view(pH // ws, ws, pW // ws, ws).permute(0, 2, 1, 3).reshape(nW, ws * ws)
         diff = region.unsqueeze(1) - region.unsqueeze(2)
         m = torch.where(diff != 0, torch.tensor(-100.0), torch.tensor(0.0)).contiguous().to(device)
-        _MASK_CACHE[key] = m
+        _MASK_CACHE[key] = m                 # never evicted: captured CUDA graphs read it by address
     return m
 
 

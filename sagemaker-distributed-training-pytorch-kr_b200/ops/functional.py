@@ -207,9 +207,7 @@ def window_row_map(B: int, H: int, W: int, ws: int, shift, device) -> torch.Tens
         m = torch.empty_like(src)
         m[src.long()] = torch.arange(src.numel(), dtype=torch.int32)
         m = m.contiguous().to(device)
-        if len(_ROW_MAPS) >= 64:             # a training run sees a handful of geometries; do not grow without bound on odd batch sizes
-            _ROW_MAPS.clear()
-        _ROW_MAPS[key] = m
+        _ROW_MAPS[key] = m                   # never evicted: a captured CUDA graph (engine/graphed.py) keeps reading this buffer by address
     return m
 
 
