@@ -1038,26 +1038,10 @@ extern "C" void b2_gemm_set_pair_mode(int mode) { g_pair_mode = mode; }
 // number of CTA pairs of the GEMM kernel that can be co-resident on this GPU (0 before the first pair launch)
 extern "C" int b2_gemm_resident_pairs(void) { return g_resident_pairs; }
 
-extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
-                       long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
-                       const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
-                       int split_k, float alpha, int max_ctas, void* stream_) {
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const int act_erf = (epilogue & B2_EPI_ERF) ? 1 : 0;
-  epilogue &= ~B2_EPI_ERF;
-  if (M <= 0 || N <= 0 || K <= 0) { b2host::set_error("gemm: empty problem"); return -1; }
-  if ((lda % 8) || (ldb % 8) || (out_fp32 ? (ldc % 4) : (ldc % 8)) || (N % 8)) {
-    b2host::set_error("gemm: leading dimensions / N must keep 16-byte alignment (lda=%lld ldb=%lld ldc=%lld N=%d)", lda,
-                      ldb, ldc, N);
-    return -1;
-  }
-  if (out_fp32 && epilogue != B2_EPI_NONE) { b2host::set_error("gemm: fp32 output supports no fused epilogue"); return -1; }
-  if (accumulate && !out_fp32) { b2host::set_error("gemm: accumulate requires fp32 output"); return -1; }
-  if (split_k > 1 && !(out_fp32 && accumulate)) { b2host::set_error("gemm: split-K requires fp32 accumulate output"); return -1; }
-  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
-
+// Tile shape, CTA pairing and split-K of one plain GEMM: pure host arithmetic (b2_gemm_plan exposes it to the CPU tests)
+struct GemmPlan { int bn, pair, tiles_m, tiles_n, num_kb, split_k, kb_per_split; };
+static GemmPlan plan_gemm(int M, int N, int K, int out_fp32, int accumulate, int split_k, int sms, int pair_mode) {
   // Tile-N selection: prefer 256 wide tiles unless that leaves most SMs idle.
-  const int sms = max_ctas > 0 ? max_ctas : b2host::num_sms();
   const int tiles_m = (M + BM - 1) / BM;
   int bn = 256;
   {
@@ -1072,9 +1056,9 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
   const int num_kb = (K + BK - 1) / BK;
   // CTA pairs (cta_group::2, 256 x bn tiles): when there are enough 256-row tiles to keep every pair busy
   bool pair = false;
-  if (g_pair_mode > 0 && M >= 256 && bn >= 128) {
+  if (pair_mode > 0 && M >= 256 && bn >= 128) {
     const long long t2 = 1LL * ((M + 255) / 256) * tiles_n;
-    pair = g_pair_mode == 2 || t2 * (out_fp32 && accumulate && split_k <= 0 ? 4 : 1) >= sms / 2;
+    pair = pair_mode == 2 || t2 * (out_fp32 && accumulate && split_k <= 0 ? 4 : 1) >= sms / 2;
   }
   const int tiles_m_eff = pair ? (M + 255) / 256 : tiles_m;
 
@@ -1096,12 +1080,50 @@ extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int 
         if (cost(s) * 100 <= best * 104) { split_k = s; break; }
     }
   }
+  GemmPlan g;
+  g.bn = bn; g.pair = pair ? 1 : 0; g.tiles_m = tiles_m_eff; g.tiles_n = tiles_n; g.num_kb = num_kb;
+  g.kb_per_split = (num_kb + split_k - 1) / split_k;
+  g.split_k = (num_kb + g.kb_per_split - 1) / g.kb_per_split;
+  return g;
+}
+
+// out[7] = {bn, pair, tiles_m, tiles_n, num_kb, split_k, kb_per_split} for the given problem on `sms` SMs (pair_mode as in
+// b2_gemm_set_pair_mode; split_k <= 0 = automatic).  No device needed.
+extern "C" int b2_gemm_plan(int M, int N, int K, int out_fp32, int accumulate, int split_k, int sms, int pair_mode, int* out) {
+  if (M <= 0 || N <= 0 || K <= 0 || sms <= 0 || out == nullptr) return -1;
+  const GemmPlan g = plan_gemm(M, N, K, out_fp32, accumulate, split_k, sms, pair_mode);
+  out[0] = g.bn; out[1] = g.pair; out[2] = g.tiles_m; out[3] = g.tiles_n; out[4] = g.num_kb; out[5] = g.split_k; out[6] = g.kb_per_split;
+  return 0;
+}
+
+extern "C" int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                       long long ldc, int a_mn_major, int b_mn_major, int dtype, int epilogue, const void* bias,
+                       const void* aux, long long ld_aux, void* C2, long long ldc2, int out_fp32, int accumulate,
+                       int split_k, float alpha, int max_ctas, void* stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int act_erf = (epilogue & B2_EPI_ERF) ? 1 : 0;
+  epilogue &= ~B2_EPI_ERF;
+  if (M <= 0 || N <= 0 || K <= 0) { b2host::set_error("gemm: empty problem"); return -1; }
+  if ((lda % 8) || (ldb % 8) || (out_fp32 ? (ldc % 4) : (ldc % 8)) || (N % 8)) {
+    b2host::set_error("gemm: leading dimensions / N must keep 16-byte alignment (lda=%lld ldb=%lld ldc=%lld N=%d)", lda,
+                      ldb, ldc, N);
+    return -1;
+  }
+  if (out_fp32 && epilogue != B2_EPI_NONE) { b2host::set_error("gemm: fp32 output supports no fused epilogue"); return -1; }
+  if (accumulate && !out_fp32) { b2host::set_error("gemm: accumulate requires fp32 output"); return -1; }
+  if (split_k > 1 && !(out_fp32 && accumulate)) { b2host::set_error("gemm: split-K requires fp32 accumulate output"); return -1; }
+  const CUtensorMapDataType dt = dtype == B2_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+
+  const int sms = max_ctas > 0 ? max_ctas : b2host::num_sms();
+  const GemmPlan plan = plan_gemm(M, N, K, out_fp32, accumulate, split_k, sms, g_pair_mode);
+  const int bn = plan.bn;
+  const bool pair = plan.pair != 0;
   GemmParams p{};
   p.M = M; p.N = N; p.K = K;
-  p.tiles_m = tiles_m_eff; p.tiles_n = tiles_n;
-  p.num_kb = num_kb;
-  p.kb_per_split = (num_kb + split_k - 1) / split_k;
-  p.split_k = (num_kb + p.kb_per_split - 1) / p.kb_per_split;
+  p.tiles_m = plan.tiles_m; p.tiles_n = plan.tiles_n;
+  p.num_kb = plan.num_kb;
+  p.kb_per_split = plan.kb_per_split;
+  p.split_k = plan.split_k;
   p.epilogue = epilogue; p.act_erf = act_erf; p.fmt = dtype == B2_DTYPE_BF16 ? 1 : 0;
   p.out_fp32 = out_fp32; p.reduce_add = accumulate;
   p.bias = bias; p.aux = aux; p.ld_aux = ld_aux; p.alpha = alpha;

@@ -59,6 +59,9 @@ int b2_gemm(const void* A, const void* B, void* C, int M, int N, int K, long lon
             int split_k, float alpha, int max_ctas, void* stream);
 /* CTA-pair (tcgen05 cta_group::2, 256-row tiles) selection for b2_gemm: 0 never, 1 heuristic (default), 2 whenever the shape allows */
 void b2_gemm_set_pair_mode(int mode);
+/* the tiling b2_gemm would choose: out[7] = {bn, pair, tiles_m, tiles_n, num_kb, split_k, kb_per_split} for an M x N x K problem on
+ * `sms` SMs (pair_mode as above; split_k <= 0 = automatic, only fp32-accumulate outputs split).  Pure host arithmetic, no device. */
+int b2_gemm_plan(int M, int N, int K, int out_fp32, int accumulate, int split_k, int sms, int pair_mode, int* out);
 int b2_gemm_resident_pairs(void);   /* CTA pairs of the GEMM kernel that can be co-resident (0 before the first pair launch) */
 
 /* ------------------------------------------------------------------------------------------

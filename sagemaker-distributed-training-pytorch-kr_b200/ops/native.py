@@ -138,6 +138,17 @@ def set_window_attn_grid(fwd_ctas_per_sm: int = 0, bwd_ctas_per_sm: int = 0) -> 
     L.b2_window_attn_set_grid(int(fwd_ctas_per_sm), int(bwd_ctas_per_sm))
 
 
+def gemm_plan(M: int, N: int, K: int, out_fp32: bool = False, accumulate: bool = False, split_k: int = 0, sms: int = 148, pair_mode: int = 1) -> dict:
+    """The tile width, CTA pairing and split-K `gemm` would pick for this problem on `sms` SMs (host arithmetic only: works without a GPU)."""
+    L = lib()
+    out = (ctypes.c_int * 7)()
+    L.b2_gemm_plan.argtypes = [ctypes.c_int] * 8 + [ctypes.POINTER(ctypes.c_int)]
+    L.b2_gemm_plan.restype = ctypes.c_int
+    if L.b2_gemm_plan(M, N, K, int(out_fp32), int(accumulate), split_k, sms, pair_mode, out) != 0:
+        raise ValueError("gemm_plan: empty problem")
+    return dict(zip(("bn", "pair", "tiles_m", "tiles_n", "num_kb", "split_k", "kb_per_split"), list(out)))
+
+
 def set_gemm_pair_mode(mode: int) -> None:
     """CTA-pair (cta_group::2) tile selection of `gemm`: 0 never, 1 heuristic (default), 2 whenever the shape allows."""
     L = lib()

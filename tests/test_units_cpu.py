@@ -524,3 +524,41 @@ def test_gpt_dataset_index_cache_goes_to_data_cache_path_on_a_read_only_data_dir
         assert [tr2[i]["text"].tolist() for i in range(4)] == first
     finally:
         os.chmod(data, stat.S_IRWXU)
+
+
+def test_gemm_plan_split_k_cost_model():
+    """csrc/gemm.cu's host-side planning (tile width, CTA pairs, split-K for fp32-accumulate outputs) through b2_gemm_plan: the split it
+    picks is the smallest within 4 % of the best of its own cost model, never leaves a split without k-blocks, and the weight-gradient
+    shapes of the GPT-2 small benchmark get the splits that were measured on the B200 (profiles/r2_kernel_check_gemm_v3_wgrad.log)"""
+    import random
+    from b200dist.ops import native as N
+    if not N.available():
+        pytest.skip("libb200dist.so not built")
+
+    def model(tiles, num_kb, slots):
+        def cost(s):
+            kbs = -(-num_kb // s)
+            items = tiles * -(-num_kb // kbs)
+            return -(-items // slots) * max(kbs + 4, 32)
+        cands = [1] + [s for s in range(2, 33) if num_kb // s >= 4]
+        best = min(cost(s) for s in cands)
+        return next(s for s in cands if cost(s) * 100 <= best * 104)
+    rnd = random.Random(0)
+    shapes = [(2304, 768, 24576), (768, 768, 24576), (3072, 768, 24576), (768, 3072, 24576), (32768, 768, 24576), (1152, 768, 24576)]
+    shapes += [(rnd.randrange(1, 64) * 64, rnd.randrange(1, 64) * 64, rnd.randrange(1, 600) * 64) for _ in range(200)]
+    for (M, Nn, K) in shapes:
+        for sms in (148, 124):
+            g = N.gemm_plan(M, Nn, K, out_fp32=True, accumulate=True, sms=sms)
+            tiles, slots = g["tiles_m"] * g["tiles_n"], max(1, sms // 2 if g["pair"] else sms)
+            want = model(tiles, g["num_kb"], slots)
+            kbs = -(-g["num_kb"] // want)
+            assert g["kb_per_split"] == kbs and g["split_k"] == -(-g["num_kb"] // kbs), (M, Nn, K, sms, g, want)
+            assert (g["split_k"] - 1) * g["kb_per_split"] < g["num_kb"] <= g["split_k"] * g["kb_per_split"]
+            assert g["tiles_m"] == -(-M // (256 if g["pair"] else 128)) and g["tiles_n"] == -(-Nn // g["bn"])
+    assert N.gemm_plan(2304, 768, 24576, True, True)["split_k"] == 5           # 27 pair tiles on 74 pairs: two rounds of 77 k-blocks
+    assert N.gemm_plan(3072, 768, 24576, True, True)["split_k"] == 2           # 36 pair tiles: one round
+    assert N.gemm_plan(768, 768, 24576, True, True)["split_k"] == 8
+    for (M, Nn, K) in [(12288, 2304, 768), (12288, 768, 3072), (4096, 11008, 4096)]:      # forward / dgrad shapes never split
+        g = N.gemm_plan(M, Nn, K)
+        assert g["split_k"] == 1 and g["pair"] == 1 and g["bn"] == 256
+    assert N.gemm_plan(512, 128, 1024)["bn"] == 128
