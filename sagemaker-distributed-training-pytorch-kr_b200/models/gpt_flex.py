@@ -100,23 +100,25 @@ class _SwiGLUNative(torch.autograd.Function):
 
 
 class _RopeNative(torch.autograd.Function):
-    """rotate-half RoPE applied to `nheads` heads of x2 [T, nheads * hd]."""
+    """rotate-half RoPE applied to `nheads` heads of x2 [T, nheads * hd]; with `rot` < hd only the first `rot` dims of every head
+    rotate (--rotary-percent, arguments.py:578) and the rest pass through."""
 
     @staticmethod
-    def forward(ctx, x2, cos_t, sin_t, pos, nheads, hd):
+    def forward(ctx, x2, cos_t, sin_t, pos, nheads, hd, rot=None):
+        rot = hd if rot is None else rot
         ctx.save_for_backward(cos_t, sin_t, pos)
-        ctx.meta = (nheads, hd)
+        ctx.meta = (nheads, hd, rot)
         y = x2.contiguous().clone()
-        N.rope_(y, cos_t, sin_t, pos, nheads, hd, y.stride(0), hd, backward=False)
+        N.rope_(y, cos_t, sin_t, pos, nheads, rot, y.stride(0), hd, backward=False)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         cos_t, sin_t, pos = ctx.saved_tensors
-        nheads, hd = ctx.meta
+        nheads, hd, rot = ctx.meta
         d = dy.contiguous().clone()
-        N.rope_(d, cos_t, sin_t, pos, nheads, hd, d.stride(0), hd, backward=True)
-        return d, None, None, None, None, None
+        N.rope_(d, cos_t, sin_t, pos, nheads, rot, d.stride(0), hd, backward=True)
+        return d, None, None, None, None, None, None
 
 
 def _activation_name(cfg: TransformerConfig) -> str:
@@ -321,16 +323,19 @@ class FlexTransformerLayer(nn.Module):
         self.mlp = SwitchMLP(cfg, comm, base, device) if cfg.num_experts else ParallelMLP(cfg, comm, base, device)
         self.rope = cfg.position_embedding_type == "rope"
         self._rope_tables = None
-        if self.rope:
-            assert cfg.rotary_percent == 1.0, "partial rotary dimensions (--rotary-percent < 1) are not supported"
+        # --rotary-percent: the first int(head_dim * percent) dims of every head rotate (an even number of them)
+        self.rot_dim = self.head_dim
+        if self.rope and cfg.rotary_percent < 1.0:
+            self.rot_dim = int(self.head_dim * cfg.rotary_percent)
+            assert self.rot_dim >= 2 and self.rot_dim % 2 == 0, f"--rotary-percent {cfg.rotary_percent} leaves {self.rot_dim} rotary dims of {self.head_dim}: need an even number >= 2"
 
     def _tables(self, device, S):
         if self._rope_tables is None or self._rope_tables[0].device != device or self._rope_tables[0].shape[0] < S:
             n = max(S, self.cfg.max_position_embeddings)
-            cos_t, sin_t = Fn.rope_tables(n, self.head_dim, device=device)
+            cos_t, sin_t = Fn.rope_tables(n, self.rot_dim, device=device)
             f = self.cfg.rotary_seq_len_interpolation_factor
             if f:
-                inv = 1.0 / (10000.0 ** (torch.arange(0, self.head_dim, 2, device=device).float() / self.head_dim))
+                inv = 1.0 / (10000.0 ** (torch.arange(0, self.rot_dim, 2, device=device).float() / self.rot_dim))
                 ang = (torch.arange(n, device=device).float() / float(f))[:, None] * inv[None]
                 cos_t, sin_t = ang.cos().contiguous(), ang.sin().contiguous()
             self._rope_tables = (cos_t, sin_t)
@@ -357,8 +362,8 @@ class FlexTransformerLayer(nn.Module):
         if self.rope:
             cos_t, sin_t = self._tables(x.device, S)
             pos = torch.arange(S, device=x.device, dtype=torch.int32).repeat_interleave(B)               # token t = s * B + b
-            q = _RopeNative.apply(q, cos_t, sin_t, pos, nh, hd)
-            k = _RopeNative.apply(k, cos_t, sin_t, pos, ng, hd)
+            q = _RopeNative.apply(q, cos_t, sin_t, pos, nh, hd, self.rot_dim)
+            k = _RopeNative.apply(k, cos_t, sin_t, pos, ng, hd, self.rot_dim)
         q4 = q.view(S, B, nh, hd)
         k4, v4 = k.view(S, B, ng, hd), v.view(S, B, ng, hd)
         if nq > 1:                                      # grouped-query: every K/V head serves nq query heads

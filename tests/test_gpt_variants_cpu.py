@@ -325,3 +325,27 @@ def test_scale_mask_softmax_op_and_module():
     assert torch.allclose(m(xb, mask).float(), ref.detach(), atol=2e-2)
     m2 = Fn.FusedScaleMaskSoftmax(input_in_bf16=False, attn_mask_type="causal", scaled_masked_softmax_fusion=False, scale=2.0)
     assert torch.allclose(m2(x.detach()), refc.detach(), atol=1e-6)
+
+
+def test_partial_rotary_rotates_only_the_leading_dims_of_every_head():
+    """--rotary-percent < 1 (arguments.py:578): the first int(head_dim * percent) dims of each head get rotate-half RoPE with frequencies
+    over that sub-dimension, the rest pass through; forward and backward against the formula"""
+    import torch
+    from b200dist.models.gpt_flex import _RopeNative
+    from b200dist.ops import functional as Fn
+    torch.manual_seed(0)
+    T, nh, hd, rot = 6, 3, 16, 8
+    x = torch.randn(T, nh * hd, requires_grad=True)
+    pos = torch.tensor([0, 0, 1, 1, 2, 5], dtype=torch.int32)
+    cos_t, sin_t = Fn.rope_tables(8, rot)
+    y = _RopeNative.apply(x, cos_t, sin_t, pos, nh, hd, rot)
+    xr = x.detach().clone().requires_grad_()
+    xh = xr.view(T, nh, hd)
+    a, b, rest = xh[..., :rot // 2], xh[..., rot // 2:rot], xh[..., rot:]
+    c, s = cos_t[pos.long()][:, None, :], sin_t[pos.long()][:, None, :]
+    ref = torch.cat([a * c - b * s, b * c + a * s, rest], -1).reshape(T, nh * hd)
+    assert torch.allclose(y, ref, atol=1e-6)
+    g = torch.randn_like(ref)
+    y.backward(g); ref.backward(g)
+    assert torch.allclose(x.grad, xr.grad, atol=1e-6)
+    assert torch.equal(y.view(T, nh, hd)[..., rot:], x.detach().view(T, nh, hd)[..., rot:])
