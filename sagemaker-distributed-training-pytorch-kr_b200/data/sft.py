@@ -132,6 +132,12 @@ class SupervisedDataset(torch.utils.data.Dataset):
             src = (PROMPT_DICT["prompt_input"] if ex.get("input", "") != "" else PROMPT_DICT["prompt_no_input"]).format_map(ex)
             tgt = f"{ex['output']}{self.tokenizer.eos_token}"
             d = preprocess([src], [tgt], self.tokenizer)
+            if not getattr(self, "_warned_empty", False) and bool((d["labels"][0] == IGNORE_INDEX).all()):
+                # the prompt alone fills model_max_length: no supervised token is left and the loss of such a batch is NaN (the
+                # reference behaves the same way, silently)
+                self._warned_empty = True
+                logging.warning("example %d has no target tokens left after truncation to model_max_length=%s: its loss is undefined "
+                                "(raise --model_max_length)", i, getattr(self.tokenizer, "model_max_length", "?"))
             self._cache[i] = dict(input_ids=d["input_ids"][0], labels=d["labels"][0])
         return self._cache[i]
 
