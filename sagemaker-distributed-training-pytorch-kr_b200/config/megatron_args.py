@@ -530,6 +530,7 @@ def core_transformer_config_from_args(args) -> TransformerConfig:
     cfg.batch_p2p_comm = not args.overlap_p2p_comm
     cfg.deallocate_pipeline_outputs = True
     cfg.use_cpu_initialization = bool(args.use_cpu_initialization)
+    cfg.standalone_embedding_stage = bool(getattr(args, "standalone_embedding_stage", False))      # read by models.gpt.get_layer_range
     return cfg
 
 

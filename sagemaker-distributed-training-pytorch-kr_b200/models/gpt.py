@@ -521,8 +521,15 @@ def get_layer_range(cfg: TransformerConfig):
     (megatron.model.transformer._get_num_layers + the interleaved offset rule)."""
     pp = mpu.get_pipeline_model_parallel_world_size()
     pr = mpu.get_pipeline_model_parallel_rank()
-    per_stage = cfg.num_layers // pp
     vpp = mpu.get_virtual_pipeline_model_parallel_world_size()
+    if getattr(cfg, "standalone_embedding_stage", False) and pp > 1:
+        # --standalone-embedding-stage (arguments.py:1054): the first pipeline stage holds the input embedding only, the layers are
+        # divided over the remaining pp - 1 stages
+        assert vpp is None, "--standalone-embedding-stage cannot be combined with virtual pipeline stages"
+        assert cfg.num_layers % (pp - 1) == 0, f"num_layers ({cfg.num_layers}) must be divisible by the {pp - 1} transformer pipeline stages"
+        per_stage = cfg.num_layers // (pp - 1)
+        return (0, 0) if pr == 0 else ((pr - 1) * per_stage, per_stage)
+    per_stage = cfg.num_layers // pp
     if vpp is not None:
         per_chunk = per_stage // vpp
         vr = mpu.get_virtual_pipeline_model_parallel_rank()

@@ -101,6 +101,18 @@ def test_oxford_swin_script_synthetic(tmp_path):
     assert "Test_Prec@1=" in out and "Test_Loss=" in out
 
 
+def test_gpt_standalone_embedding_stage_matches_single_process():
+    """--standalone-embedding-stage (arguments.py:1054): pipeline stage 0 holds only the embedding, 3 layers on the other 3 stages of PP=4"""
+    base = [a for a in GPT] + ["--hidden-dropout", "0", "--attention-dropout", "0"]
+    base[base.index("--num-layers") + 1] = "3"
+    base[base.index("--global-batch-size") + 1] = "8"
+    base[base.index("--train-iters") + 1] = "3"
+    base[base.index("--lr-decay-iters") + 1] = "3"
+    single = _losses(_run("pretrain_gpt.py", base))
+    staged = _losses(_run("pretrain_gpt.py", base + ["--pipeline-model-parallel-size", "4", "--standalone-embedding-stage"], nproc=4))
+    assert sorted(single) == [1, 2, 3] and single == staged, (single, staged)
+
+
 def test_mnist_script_reads_raw_idx_files(tmp_path):
     """--data-path with torchvision's on-disk layout (<root>/MNIST/raw/*-idx?-ubyte, plain and gzipped): the script trains on the files,
     not on the synthetic stand-in (reference: datasets.MNIST(args.data_path, ...), pytorch_mnist_ddp.py:216-228)"""
