@@ -53,7 +53,20 @@ def get_batch(data_iterator):
     if args.eod_mask_loss:
         loss_mask[tokens == tokenizer.eod] = 0.0
     position_ids = torch.arange(tokens.shape[1], dtype=torch.long, device=tokens.device).unsqueeze(0).expand_as(tokens)
+    if args.reset_position_ids:
+        position_ids = reset_position_ids_after_eod(tokens, tokenizer.eod)
     return tokens, labels, loss_mask, None, position_ids
+
+
+def reset_position_ids_after_eod(tokens, eod):
+    """--reset-position-ids (get_ltor_masks_and_position_ids, megatron/utils.py): positions restart at 0 after every end-of-document
+    token.  position[i] = i - (index of the last EOD before i, + 1), computed with a running maximum instead of the reference's
+    per-document Python loop."""
+    S = tokens.shape[1]
+    idx = torch.arange(S, dtype=torch.long, device=tokens.device).unsqueeze(0).expand_as(tokens)
+    starts = torch.where(tokens == eod, idx + 1, torch.zeros_like(idx))          # a document starts right after an EOD
+    starts = torch.cat([torch.zeros_like(starts[:, :1]), starts[:, :-1]], 1)     # ... which affects the tokens AFTER it
+    return idx - torch.cummax(starts, dim=1).values
 
 
 def loss_func(loss_mask, output_tensor):

@@ -562,3 +562,23 @@ def test_gemm_plan_split_k_cost_model():
         g = N.gemm_plan(M, Nn, K)
         assert g["split_k"] == 1 and g["pair"] == 1 and g["bn"] == 256
     assert N.gemm_plan(512, 128, 1024)["bn"] == 128
+
+
+def test_reset_position_ids_matches_the_reference_loop():
+    """--reset-position-ids: vectorised restart of the positions after each EOD against get_ltor_masks_and_position_ids' per-document loop"""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("pretrain_gpt_entry", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "entrypoints", "pretrain_gpt.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    g = torch.Generator().manual_seed(0)
+    for _ in range(20):
+        t = torch.randint(0, 6, (4, 33), generator=g)
+        got = mod.reset_position_ids_after_eod(t, 5)
+        ref = torch.arange(33).unsqueeze(0).repeat(4, 1)
+        for b in range(4):
+            prev = 0
+            for i in (t[b] == 5).nonzero().flatten().tolist():
+                ref[b, i + 1:] -= (i + 1 - prev)
+                prev = i + 1
+        assert torch.equal(got, ref)
