@@ -484,6 +484,7 @@ class TransformerConfig:
     attention_dropout: float = 0.1
     layernorm_epsilon: float = 1e-5
     init_method_std: float = 0.02
+    init_method_xavier_uniform: bool = False
     params_dtype: torch.dtype = torch.float32
     add_bias_linear: bool = True
     swiglu: bool = False

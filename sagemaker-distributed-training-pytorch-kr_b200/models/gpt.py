@@ -27,6 +27,7 @@ from ..config.megatron_args import TransformerConfig
 from ..ops import native as N
 from ..parallel import state as mpu
 from ..parallel import tensor as tp_ops
+from ..parallel.layers import init_shard, set_init_method_xavier_uniform
 from ..parallel.tensor import TPComm
 
 
@@ -172,13 +173,9 @@ class _LayerFn(torch.autograd.Function):
 
 
 def _init_normal(shape, std, seed, device, dtype, full_shape=None, shard_dim=None, rank=0, world=1):
-    """Deterministic init that does not depend on the TP size: draw the FULL tensor from a per-parameter
-    seed, then slice this rank's shard (the effect of Megatron's --use-cpu-initialization path)."""
-    g = torch.Generator(device="cpu").manual_seed(seed)
-    full = torch.empty(full_shape or shape, dtype=torch.float32).normal_(0.0, std, generator=g)
-    if shard_dim is not None and world > 1:
-        full = full.chunk(world, dim=shard_dim)[rank]
-    return full.to(device=device, dtype=dtype).contiguous()
+    """TP-size independent init of one parameter (parallel.layers.init_shard: full tensor from a per-parameter seed, then this rank's
+    shard; normal, or Xavier-uniform under --init-method-xavier-uniform)."""
+    return init_shard(full_shape or shape, std, seed, device, dtype, shard_dim, rank, world)
 
 
 class ParallelTransformerLayer(nn.Module):
@@ -418,6 +415,7 @@ class GPTModel(nn.Module):
         self.ignore_index = -100
         self.input_tensor = None
         dt, H = cfg.params_dtype, cfg.hidden_size
+        set_init_method_xavier_uniform(getattr(cfg, "init_method_xavier_uniform", False))
         if layer_offset is None or num_layers_here is None:
             layer_offset, num_layers_here = get_layer_range(cfg)
         self.layer_offset, self.num_layers_here = layer_offset, num_layers_here

@@ -24,9 +24,26 @@ from . import state as mpu
 from .tensor import TPComm
 
 
+_XAVIER_UNIFORM = False        # --init-method-xavier-uniform (arguments.py:435-437, :870): every weight matrix, output projections included
+
+
+def set_init_method_xavier_uniform(on: bool) -> None:
+    global _XAVIER_UNIFORM
+    _XAVIER_UNIFORM = bool(on)
+
+
 def init_shard(full_shape, std: float, seed: int, device, dtype, shard_dim: Optional[int] = None, rank: int = 0, world: int = 1):
+    """Deterministic init that does not depend on the TP size: draw the FULL tensor from a per-parameter seed, then slice this rank's
+    shard (the effect of Megatron's --use-cpu-initialization path).  Normal(0, std), or Xavier-uniform over the full [out, in] matrix
+    when --init-method-xavier-uniform is set."""
     g = torch.Generator(device="cpu").manual_seed(seed)
-    full = torch.empty(full_shape, dtype=torch.float32).normal_(0.0, std, generator=g)
+    fs = tuple(full_shape)
+    if _XAVIER_UNIFORM and len(fs) == 2:
+        import math
+        bound = math.sqrt(6.0 / (fs[0] + fs[1]))
+        full = torch.empty(fs, dtype=torch.float32).uniform_(-bound, bound, generator=g)
+    else:
+        full = torch.empty(fs, dtype=torch.float32).normal_(0.0, std, generator=g)
     if shard_dim is not None and world > 1:
         full = full.chunk(world, dim=shard_dim)[rank]
     return full.to(device=device, dtype=dtype).contiguous()

@@ -349,3 +349,24 @@ def test_partial_rotary_rotates_only_the_leading_dims_of_every_head():
     y.backward(g); ref.backward(g)
     assert torch.allclose(x.grad, xr.grad, atol=1e-6)
     assert torch.equal(y.view(T, nh, hd)[..., rot:], x.detach().view(T, nh, hd)[..., rot:])
+
+
+def test_init_method_xavier_uniform_covers_every_weight_matrix():
+    """--init-method-xavier-uniform (arguments.py:435-437): weights are uniform within sqrt(6 / (fan_in + fan_out)) of the FULL matrix in both
+    layer implementations, and the switch does not leak into the next model"""
+    import math
+    import torch
+    from b200dist.config.megatron_args import TransformerConfig
+    from b200dist.models.gpt import GPTModel
+    kw = dict(num_layers=1, hidden_size=64, num_attention_heads=4, ffn_hidden_size=256, kv_channels=16, seq_length=16, max_position_embeddings=16,
+              padded_vocab_size=128, params_dtype=torch.float32)
+    for extra in ({}, {"swiglu": True}):
+        m = GPTModel(TransformerConfig(init_method_xavier_uniform=True, **kw, **extra), device="cpu", layer_offset=0, num_layers_here=1)
+        for n, p in m.named_parameters():
+            if p.dim() == 2 and "position_embeddings" not in n:
+                bound = math.sqrt(6.0 / (p.shape[0] + p.shape[1]))
+                if "dense_h_to_4h" in n and extra:          # gate and up are drawn as two [F, H] matrices
+                    bound = math.sqrt(6.0 / (256 + 64))
+                assert p.abs().max().item() <= bound + 1e-6 and p.std().item() > 0.5 * bound, n
+    plain = GPTModel(TransformerConfig(**kw), device="cpu", layer_offset=0, num_layers_here=1)
+    assert abs(plain.language_model.encoder.layers[0].mlp.dense_h_to_4h.weight.std().item() - 0.02) < 2e-3
