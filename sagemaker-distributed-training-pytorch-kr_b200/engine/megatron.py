@@ -320,12 +320,16 @@ def train_step(forward_step_func, data_iterator, model, optimizer, opt_param_sch
         losses = pp.forward_backward(forward_step_func, data_iterator, model, nmb, shape, args.params_dtype, forward_only=False,
                                      grad_scale=optimizer.get_loss_scale(), timers=timers if args.timing_log_level >= 2 else None)
     timers("forward-backward").stop()
+    if getattr(args, "empty_unused_memory_level", 0) >= 1 and torch.cuda.is_available():      # --empty-unused-memory-level (training.py train_step)
+        torch.cuda.empty_cache()
     timers("all-grads-sync", log_level=1).start(barrier=args.barrier_with_L1_time)
     optimizer.reduce_model_grads()
     timers("all-grads-sync").stop()
     timers("optimizer", log_level=1).start(barrier=args.barrier_with_L1_time)
     ok, grad_norm, num_zeros = optimizer.step()
     timers("optimizer").stop()
+    if getattr(args, "empty_unused_memory_level", 0) >= 2 and torch.cuda.is_available():
+        torch.cuda.empty_cache()
     if ok:
         increment = nmb * args.micro_batch_size * args.data_parallel_size
         opt_param_scheduler.step(increment=increment)
@@ -400,11 +404,22 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
             if sink is not None:
                 sink.write(**rec)
             if tb is not None and tb.enabled and iteration % args.tensorboard_log_interval == 0:
+                # the reference's switches (arguments.py:652-679): learning rate and loss scale on by default, batch size / world size /
+                # timers / memory on request
+                gate = {"learning_rate": getattr(args, "log_learning_rate_to_tensorboard", True),
+                        "loss_scale": getattr(args, "log_loss_scale_to_tensorboard", True),
+                        "global_batch_size": getattr(args, "log_batch_size_to_tensorboard", False),
+                        "world_size": getattr(args, "log_world_size_to_tensorboard", False)}
                 for k, v in rec.items():
-                    if k not in ("iteration", "time") and isinstance(v, (int, float)):
+                    if k not in ("iteration", "time") and isinstance(v, (int, float)) and gate.get(k, True):
                         tb.add_scalar(k.replace("_", "-"), v, iteration)
-                        if k.endswith("loss"):
+                        if k.endswith("loss") or k in ("learning_rate", "loss_scale", "global_batch_size"):
                             tb.add_scalar(k.replace("_", "-") + " vs samples", v, args.consumed_train_samples)
+                if getattr(args, "log_memory_to_tensorboard", False) and torch.cuda.is_available():
+                    st = torch.cuda.memory_stats()
+                    for tag, key in (("mem-reserved-bytes", "reserved_bytes.all.current"), ("mem-allocated-bytes", "allocated_bytes.all.current"),
+                                     ("mem-allocated-count", "allocation.all.current")):
+                        tb.add_scalar(tag, st.get(key, 0), iteration)
                 tb.flush()
         total_loss_dict[adv] = total_loss_dict[skp] = total_loss_dict[nan] = 0
         print_rank_last(s)
@@ -415,6 +430,9 @@ def training_log(loss_dict, total_loss_dict, learning_rate, iteration, loss_scal
                 torch.cuda.memory_reserved() / mib, torch.cuda.max_memory_reserved() / mib), flush=True)
             report_memory_flag = False
         names = ["forward-backward", "forward-compute", "backward-compute", "batch-generator", "all-grads-sync", "optimizer"]
+        if getattr(args, "log_timers_to_tensorboard", False) and args.tensorboard_dir and iteration % args.tensorboard_log_interval == 0:
+            # collective (max over ranks): every rank calls it, the rank that owns the writer records
+            timers.write(names, tb if (tb is not None and tb.enabled) else None, iteration, normalizer=args.log_interval)
         timers.log(names, normalizer=args.log_interval)
     return report_memory_flag
 
@@ -451,6 +469,16 @@ def evaluate_and_print_results(prefix, forward_step_func, data_iterator, model, 
         val = float(v)
         s += "{} value: {:.6E} | ".format(k, val)
         s += "{} PPL: {:.6E} | ".format(k, math.exp(min(20, val)))
+    tb = _GLOBAL.get("tb")
+    if tb is not None and tb.enabled and isinstance(iteration, int):
+        args = get_args()
+        for k, v in total.items():
+            tb.add_scalar(f"{k} validation", float(v), iteration)
+            tb.add_scalar(f"{k} validation vs samples", float(v), args.consumed_train_samples)
+            if getattr(args, "log_validation_ppl_to_tensorboard", False):
+                tb.add_scalar(f"{k} validation ppl", math.exp(min(20, float(v))), iteration)
+                tb.add_scalar(f"{k} validation ppl vs samples", math.exp(min(20, float(v))), args.consumed_train_samples)
+        tb.flush()
     print_rank_last("-" * (len(s) + 1))
     print_rank_last(s)
     print_rank_last("-" * (len(s) + 1))

@@ -92,6 +92,17 @@ class Timers:
         dist.all_gather_into_tensor(allv.view(-1), local.to(dev)) if dev.type == "cuda" else dist.all_gather(list(allv.unbind(0)), local)
         return allv.cpu()
 
+    def write(self, names: List[str], writer, iteration: int, normalizer: float = 1.0, reset: bool = False, barrier: bool = False) -> None:
+        """--log-timers-to-tensorboard: the maximum over ranks of each named timer as `<name>-time` scalars (megatron.timers.Timers.write)."""
+        assert normalizer > 0.0
+        allv = self._gather(names, reset, barrier) / normalizer
+        for i, n in enumerate(names):
+            col = allv[:, i]
+            if writer is not None and float(col.max()) > 0.0:
+                writer.add_scalar(n + "-time", float(col.max()), iteration)
+        if writer is not None:
+            writer.flush()
+
     def log(self, names: List[str], rank=None, normalizer: float = 1.0, reset=True, barrier=False) -> Optional[str]:
         assert normalizer > 0.0
         allv = self._gather(names, reset, barrier) * (1000.0 / normalizer)

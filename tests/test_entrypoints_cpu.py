@@ -372,3 +372,25 @@ def test_gpt_fp16_dynamic_loss_scale_skips_then_trains():
     scales = [r[2] for r in rows]
     assert scales == sorted(scales, reverse=True)
     assert sum(r[3] for r in rows) >= 3
+
+
+def test_gpt_tensorboard_switches(tmp_path):
+    """--tensorboard-dir with the reference's scalar switches (arguments.py:652-679): timers (a collective over both pipeline ranks),
+    batch size, world size, validation perplexity on; loss scale off"""
+    tb = str(tmp_path / "tb")
+    _run("pretrain_gpt.py", GPT + ["--tensorboard-dir", tb, "--tensorboard-log-interval", "1", "--log-timers-to-tensorboard", "--log-batch-size-to-tensorboard",
+                                   "--log-world-size-to-tensorboard", "--log-validation-ppl-to-tensorboard", "--no-log-loss-scale-to-tensorboard",
+                                   "--timing-log-level", "2", "--pipeline-model-parallel-size", "2", "--eval-interval", "3"], nproc=2)
+    tags = set()
+    if os.path.exists(os.path.join(tb, "scalars.jsonl")):          # no tensorboard package: the JSONL fallback of utils.metrics.ScalarWriter
+        import json
+        tags = {json.loads(l)["tag"] for l in open(os.path.join(tb, "scalars.jsonl"))}
+    else:
+        from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+        ea = EventAccumulator(tb)
+        ea.Reload()
+        tags = set(ea.Tags()["scalars"])
+    for want in ("lm-loss", "learning-rate", "global-batch-size", "world-size", "forward-backward-time", "optimizer-time", "lm loss validation",
+                 "lm loss validation ppl"):
+        assert want in tags, (want, sorted(tags))
+    assert "loss-scale" not in tags
