@@ -55,7 +55,13 @@ def get_batch(data_iterator):
     position_ids = torch.arange(tokens.shape[1], dtype=torch.long, device=tokens.device).unsqueeze(0).expand_as(tokens)
     if args.reset_position_ids:
         position_ids = reset_position_ids_after_eod(tokens, tokenizer.eod)
-    return tokens, labels, loss_mask, None, position_ids
+    attention_mask = None
+    if args.reset_attention_mask:
+        # the reference materialises a [b, 1, s, s] mask; the document id of every token says the same in [b, s]: a token attends to
+        # earlier tokens of its own document only (an EOD closes the document it ends)
+        is_eod = (tokens == tokenizer.eod).long()
+        attention_mask = torch.cumsum(is_eod, dim=1) - is_eod
+    return tokens, labels, loss_mask, attention_mask, position_ids
 
 
 def reset_position_ids_after_eod(tokens, eod):

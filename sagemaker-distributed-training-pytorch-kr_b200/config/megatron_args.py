@@ -264,9 +264,9 @@ def validate_args(args, defaults: Optional[dict] = None, verbose: bool = True):
     args.pipeline_model_parallel_size = min(args.pipeline_model_parallel_size, args.world_size // args.tensor_model_parallel_size)
     args.transformer_pipeline_model_parallel_size = args.pipeline_model_parallel_size - (1 if args.standalone_embedding_stage else 0)
     mp = args.pipeline_model_parallel_size * args.tensor_model_parallel_size
-    _require(not getattr(args, "reset_attention_mask", False),
-             "--reset-attention-mask (block-diagonal attention per document) is not supported: the attention kernels are causal over the "
-             "whole sequence; --reset-position-ids and --eod-mask-loss are")
+    _require(not getattr(args, "reset_attention_mask", False) or getattr(args, "attention_impl", "flash") == "unfused",
+             "--reset-attention-mask (attention within a document only) needs --attention-impl unfused: the flash kernel is causal over "
+             "the whole sequence, the scale/mask/softmax kernel of the unfused path takes the document mask")
     _require(args.world_size % mp == 0, f"world size ({args.world_size}) is not divisible by TP ({args.tensor_model_parallel_size}) x PP ({args.pipeline_model_parallel_size})")
     args.data_parallel_size = args.world_size // mp
     log(f"using world size: {args.world_size}, data-parallel-size: {args.data_parallel_size}, tensor-model-parallel size: "

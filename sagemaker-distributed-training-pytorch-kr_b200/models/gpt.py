@@ -240,6 +240,7 @@ class _RecomputeFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, layers, distribute_group):
         ctx.layers = layers
+        ctx.doc_ids = tp_ops.document_ids()
         ctx.seed_state = tp_ops.dropout_seed_state()
         ctx.cpu_rng = torch.get_rng_state()
         ctx.cuda_rng = torch.cuda.get_rng_state() if x.is_cuda else None
@@ -263,6 +264,8 @@ class _RecomputeFn(torch.autograd.Function):
         if ctx.dist_group is not None:
             x = tp_ops.all_gather_first_dim(x, ctx.dist_group).view(ctx.shape)
         now_seed, now_cpu = tp_ops.dropout_seed_state(), torch.get_rng_state()
+        now_doc = tp_ops.document_ids()
+        tp_ops.set_document_ids(ctx.doc_ids)
         now_cuda = torch.cuda.get_rng_state() if x.is_cuda else None
         tp_ops.set_dropout_seed_state(ctx.seed_state)
         torch.set_rng_state(ctx.cpu_rng)
@@ -277,6 +280,7 @@ class _RecomputeFn(torch.autograd.Function):
             torch.autograd.backward(y, dy)
         finally:
             tp_ops.set_dropout_seed_state(now_seed)
+            tp_ops.set_document_ids(now_doc)
             torch.set_rng_state(now_cpu)
             if now_cuda is not None:
                 torch.cuda.set_rng_state(now_cuda)
@@ -467,6 +471,9 @@ class GPTModel(nn.Module):
         (SURVEY K23).  Returns per-token loss [B, S] on the last stage when labels are given, logits
         [S, B, V/t] when they are not, and hidden states [S_local, B, H] on other stages."""
         lm = self.language_model
+        # --reset-attention-mask: [b, s] document ids (entrypoints/pretrain_gpt.get_batch) for the unfused attention; anything else
+        # (None, or a reference-style [b, 1, s, s] mask) means plain causal attention
+        tp_ops.set_document_ids(attention_mask if (torch.is_tensor(attention_mask) and attention_mask.dim() == 2) else None)
         if self.pre_process:
             if position_ids is None:
                 position_ids = torch.arange(tokens.shape[1], device=tokens.device).unsqueeze(0).expand_as(tokens)

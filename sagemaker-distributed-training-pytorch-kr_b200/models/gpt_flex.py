@@ -397,7 +397,17 @@ def core_attention(self, q4, k4, v4, p_drop):
     q = q4.permute(1, 2, 0, 3).reshape(B * nh, S, hd)
     k = k4.permute(1, 2, 3, 0).reshape(B * nh, hd, S)
     scores = torch.bmm(q, k).view(B, nh, S, S)
-    if self.cfg.masked_softmax_fusion:
+    doc = tp_ops.document_ids()
+    if doc is not None:
+        # --reset-attention-mask: causal AND same document (reference get_ltor_masks_and_position_ids: tokens after an EOD do not see
+        # anything up to it); masked = True, the convention of ScaledMaskedSoftmax
+        masked = (doc[:, :, None] != doc[:, None, :]) | torch.ones(S, S, dtype=torch.bool, device=scores.device).triu(1)
+        masked = masked[:, None]                                                # [b, 1, sq, sk]
+        if self.cfg.masked_softmax_fusion:
+            probs = Fn.scaled_masked_softmax(scores, masked, self.softmax_scale)
+        else:
+            probs = torch.softmax((scores.float() * self.softmax_scale).masked_fill(masked, float("-inf")), dim=-1).to(scores.dtype)
+    elif self.cfg.masked_softmax_fusion:
         probs = Fn.scaled_upper_triang_masked_softmax(scores, self.softmax_scale)
     else:
         keep = torch.ones(S, S, dtype=torch.bool, device=scores.device).tril()

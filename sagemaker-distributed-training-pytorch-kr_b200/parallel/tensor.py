@@ -375,6 +375,21 @@ def model_parallel_cuda_manual_seed(seed: int):
     _SEED_COUNTER["base"], _SEED_COUNTER["calls"] = seed, 0
 
 
+# --reset-attention-mask: document id of every token of the micro-batch in flight ([b, s] int64, or None).  The unfused attention
+# (models/gpt_flex.core_attention) masks pairs from different documents; GPTModel.forward installs it, _RecomputeFn re-installs the
+# one of its own forward when it re-runs layers in the backward.
+_DOC_IDS = None
+
+
+def set_document_ids(doc_ids):
+    global _DOC_IDS
+    _DOC_IDS = doc_ids
+
+
+def document_ids():
+    return _DOC_IDS
+
+
 def dropout_seed_state():
     """(base, calls) of the counter behind next_dropout_seed - saved by activation recomputation so the re-run of a
     layer draws the masks of its first run."""

@@ -370,3 +370,49 @@ def test_init_method_xavier_uniform_covers_every_weight_matrix():
                 assert p.abs().max().item() <= bound + 1e-6 and p.std().item() > 0.5 * bound, n
     plain = GPTModel(TransformerConfig(**kw), device="cpu", layer_offset=0, num_layers_here=1)
     assert abs(plain.language_model.encoder.layers[0].mlp.dense_h_to_4h.weight.std().item() - 0.02) < 2e-3
+
+
+@pytest.mark.parametrize("fused_softmax", [True, False])
+def test_reset_attention_mask_isolates_documents(fused_softmax):
+    """--reset-attention-mask + --reset-position-ids (pretrain_gpt.py:83-88): with the document ids installed, every document of a packed
+    sequence gets the logits it gets when it is run alone; also through the full-recompute backward"""
+    import importlib.util
+    import os
+    import torch
+    from b200dist.config.megatron_args import TransformerConfig
+    from b200dist.models.gpt import GPTModel
+    spec = importlib.util.spec_from_file_location("pretrain_gpt_entry2", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "entrypoints", "pretrain_gpt.py"))
+    entry = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(entry)
+    torch.manual_seed(0)
+    eod, S = 99, 24
+    kw = dict(num_layers=2, hidden_size=64, num_attention_heads=4, ffn_hidden_size=128, kv_channels=16, seq_length=S, max_position_embeddings=S,
+              padded_vocab_size=128, params_dtype=torch.float32, hidden_dropout=0.0, attention_dropout=0.0, attention_impl="unfused",
+              masked_softmax_fusion=fused_softmax)
+    m = GPTModel(TransformerConfig(**kw), device="cpu", layer_offset=0, num_layers_here=2).eval()
+    tokens = torch.randint(0, 90, (2, S))
+    tokens[0, 7], tokens[0, 15], tokens[1, 11] = eod, eod, eod
+    pos = entry.reset_position_ids_after_eod(tokens, eod)
+    is_eod = (tokens == eod).long()
+    doc = torch.cumsum(is_eod, 1) - is_eod
+    with torch.no_grad():
+        full = m(tokens, pos, doc)                                   # [S, B, V]
+        for b, (a, e) in ((0, (0, 8)), (0, (8, 16)), (0, (16, S)), (1, (0, 12)), (1, (12, S))):
+            alone = m(tokens[b:b + 1, a:e].contiguous(), None, None)
+            assert torch.allclose(full[a:e, b], alone[:, 0], atol=2e-5), (b, a, e, (full[a:e, b] - alone[:, 0]).abs().max())
+        causal = m(tokens, pos, None)
+    assert not torch.allclose(full[8:16, 0], causal[8:16, 0], atol=1e-3)            # without the mask the documents leak into each other
+    # backward with full recompute re-installs the document ids of its own forward
+    mt = GPTModel(TransformerConfig(recompute_granularity="full", **kw), device="cpu", layer_offset=0, num_layers_here=2).train()
+    mt.load_state_dict(m.state_dict())
+    labels = torch.randint(0, 90, (2, S))
+    loss = mt(tokens, pos, doc, labels=labels).mean()
+    from b200dist.parallel import tensor as tp_ops
+    tp_ops.set_document_ids(None)                                    # a later micro-batch without document ids is now "in flight"
+    loss.backward()
+    ref = GPTModel(TransformerConfig(**kw), device="cpu", layer_offset=0, num_layers_here=2).train()
+    ref.load_state_dict(m.state_dict())
+    ref(tokens, pos, doc, labels=labels).mean().backward()
+    for (n, p), (_, q) in zip(mt.named_parameters(), ref.named_parameters()):
+        if q.grad is not None:
+            assert torch.allclose(p.grad, q.grad, atol=1e-6), n
